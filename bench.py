@@ -1,0 +1,266 @@
+#!/usr/bin/env python
+"""bench.py — throughput of the hot path on B200 (contract: see DESIGN.md "Measurement").
+
+  python bench.py [--gpus N] [--steps K] [--warmup W] [--sigs S] [--impl ours|reference]
+
+Workload (BASELINE.json configs[1]): single-GPU batched secp256k1_ecdsa_verify on 1,000,000 synthetic
+signatures incl. 1 % corrupted.  A "step" is one pass of the two ECDSA kernels over the whole batch.
+
+  value   sigverifies/s with inputs resident in HBM (CUDA events around K steps on the launching stream)
+  e2e     the same metric through the host-pointer C-ABI call bcp_gpu_ecdsa_verify_batch on PINNED host
+          buffers: host->device copies, kernels and the verdict read-back are all inside the timed region
+  roofline  bound = integer pipe: achieved = sigverifies/s x 151,228 mul32 (SURVEY.md §8d unit of the
+            reference algorithm) vs the 32x32->64 multiply-add peak measured live by
+            bcp_gpu_measure_int_peak (MEASURED_PEAKS.json carries no integer peak); the HBM view
+            (130 B/verify vs MEASURED_PEAKS hbm_gbs) is reported alongside as `hbm`
+  cpu_baseline  the reference's own libsecp256k1 (oracle/_ref, kind "reference"; falls back to the
+                oracle port) on all host threads over a bounded sample of the same batch
+Multi-GPU: one process per GPU under torchrun; signatures shard by index range across ranks, no
+collective on the data path (verdicts are AND-ed / concatenated by the caller); weak scaling.
+`--impl reference` times the reference CPU path only (rank 0), same metric/config.
+"""
+import argparse
+import ctypes as C
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+sys.path.insert(0, os.path.join(ROOT, "tests"))
+
+MUL32_PER_VERIFY = 151228  # 64*(1348+39) + 36*(1482+253)
+BYTES_PER_VERIFY = 32 + 33 + 64 + 1
+
+
+def clocks_sampler(stop, out, gpu_index):
+    q = "clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown," \
+        "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap"
+    while not stop.is_set():
+        try:
+            r = subprocess.run(["nvidia-smi", "-i", str(gpu_index), "--query-gpu=" + q, "--format=csv,noheader,nounits"],
+                               capture_output=True, text=True, timeout=5).stdout.strip().split(",")
+            out.append([x.strip() for x in r])
+        except Exception:
+            pass
+        stop.wait(0.2)
+
+
+def summarize_clocks(samples):
+    sm = sorted(int(s[0]) for s in samples if s and s[0].isdigit())
+    mx = max([int(s[1]) for s in samples if len(s) > 1 and s[1].isdigit()] or [0])
+    reasons = set()
+    names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+    for s in samples:
+        for k, nm in enumerate(names):
+            if len(s) > 2 + k and s[2 + k].lower().startswith("active"):
+                reasons.add(nm)
+    return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": mx or None, "reasons": sorted(reasons),
+            "samples": len(sm)}
+
+
+def cpu_baseline(msg, pub, sig, budget_s=12.0):
+    """Reference libsecp256k1 (or the oracle port) on all host threads over a bounded sample."""
+    from oracle import pyoracle as po
+
+    impl = po.ref() if po.have_ref() else po.oracle()
+    cores = os.cpu_count() or 1
+    n = len(msg)
+    sample = min(n, 2000 * cores)
+    impl.ecdsa_verify_batch(msg[:256 * min(cores, 8)].copy(), pub[:256 * min(cores, 8)].copy(),
+                            sig[:256 * min(cores, 8)].copy(), cores)  # warm-up (context/tables)
+    t0 = time.perf_counter()
+    impl.ecdsa_verify_batch(msg[:sample], pub[:sample], sig[:sample], cores)
+    dt = time.perf_counter() - t0
+    # grow the sample until ~budget_s of wall time is spent (bounded by the batch)
+    target = min(n, int(sample * max(1.0, budget_s / max(dt, 1e-3))))
+    if target > sample * 1.5:
+        sample = target
+        t0 = time.perf_counter()
+        impl.ecdsa_verify_batch(msg[:sample], pub[:sample], sig[:sample], cores)
+        dt = time.perf_counter() - t0
+    return {"value": sample / dt, "unit": "sigverifies/s", "cores": cores, "kind": impl.kind,
+            "sample": "first %d of the %d-signature batch, %.1f s wall, %d threads" % (sample, n, dt, cores)}
+
+
+def run_reference(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    import synth
+
+    n = args.sigs
+    gen_n = min(n, 200000)  # the CPU arm only ever touches a bounded sample
+    msg, pub, sig, _ = synth.sigset(gen_n, corrupt_pct=1)
+    from oracle import pyoracle as po
+
+    impl = po.ref() if po.have_ref() else po.oracle()
+    cores = os.cpu_count() or 1
+    sample = min(gen_n, 1500 * cores)
+    for _ in range(args.warmup):
+        impl.ecdsa_verify_batch(msg[:sample], pub[:sample], sig[:sample], cores)
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        impl.ecdsa_verify_batch(msg[:sample], pub[:sample], sig[:sample], cores)
+    dt = time.perf_counter() - t0
+    v = sample * args.steps / dt
+    line = {"metric": "ecdsa_sigverifies_per_s", "value": v, "unit": "sigverifies/s", "n_gpus": args.gpus,
+            "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * dt / args.steps, "higher_is_better": True,
+            "scaling": "weak", "vs_baseline": None, "dtype": "u32", "data": "synthetic", "impl": "reference",
+            "config": {"workload": "configs[1]: batched secp256k1_ecdsa_verify, %d synthetic signatures incl. 1%% corrupted"
+                       % n, "sigs_per_gpu": n},
+            "cpu_baseline": {"value": v, "unit": "sigverifies/s", "cores": cores, "kind": impl.kind,
+                             "sample": "%d signatures per step (bounded sample of the batch), %d threads" % (sample, cores)},
+            "e2e": {"value": v, "unit": "sigverifies/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+            "gpu_launches": 0}
+    print(json.dumps(line))
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--sigs", type=int, default=1000000, help="signatures per GPU per step")
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+    if args.impl == "reference":
+        return run_reference(args)
+
+    import numpy as np
+    import torch
+
+    import bitcoincashplus_b200 as bcp
+    import synth
+
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    dist = world > 1
+    if dist:
+        import torch.distributed as td
+
+        td.init_process_group("nccl", device_id=torch.device("cuda", local))
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    eng = bcp.Engine(local)
+    n = args.sigs
+
+    # synthetic batch: every rank generates its own shard (disjoint message indices would need a rank offset;
+    # the kernels' run time does not depend on it, so each rank uses the same deterministic set)
+    t0 = time.perf_counter()
+    msg, pub, sig, kinds = synth.sigset(n, corrupt_pct=1)
+    gen_s = time.perf_counter() - t0
+    expected = (kinds < 0) | np.isin(kinds, [synth.CORRUPTIONS.index("hybrid_ok"), synth.CORRUPTIONS.index("msg_plus_n")])
+
+    # ---- device-resident leg
+    d_msg = torch.from_numpy(msg).to(dev)
+    d_pub = torch.from_numpy(pub).to(dev)
+    d_sig = torch.from_numpy(sig).to(dev)
+    d_ok = torch.zeros(n, dtype=torch.uint8, device=dev)
+    eng.ecdsa_reserve(n)
+    stream = torch.cuda.current_stream(dev)
+
+    def step():
+        eng.ecdsa_verify_batch_dev(d_msg.data_ptr(), d_pub.data_ptr(), d_sig.data_ptr(), n, d_ok.data_ptr(), 0,
+                                   stream.cuda_stream)
+
+    for _ in range(args.warmup):
+        step()
+    torch.cuda.synchronize(dev)
+    got = d_ok.cpu().numpy().astype(bool)
+    assert (got == expected).all(), "verdict mismatch in bench batch: %r" % np.nonzero(got != expected)[0][:10]
+
+    samples, stop = [], threading.Event()
+    th = threading.Thread(target=clocks_sampler, args=(stop, samples, local), daemon=True)
+    th.start()
+    if dist:
+        td.barrier()
+    torch.cuda.synchronize(dev)
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record(stream)
+    for _ in range(args.steps):
+        step()
+    e1.record(stream)
+    torch.cuda.synchronize(dev)
+    if dist:
+        td.barrier()
+    ms = e0.elapsed_time(e1)
+
+    # ---- end-to-end leg: pinned host buffers through the host-pointer C-ABI call
+    L = bcp.lib()
+    hm, hp, hs, ho = (L.bcp_gpu_host_alloc(n * 32), L.bcp_gpu_host_alloc(n * 65), L.bcp_gpu_host_alloc(n * 64),
+                      L.bcp_gpu_host_alloc(n))
+    C.memmove(hm, msg.ctypes.data, n * 32)
+    C.memmove(hp, pub.ctypes.data, n * 65)
+    C.memmove(hs, sig.ctypes.data, n * 64)
+    for _ in range(max(1, args.warmup - 1)):
+        eng.ecdsa_verify_batch_ptr(hm, hp, hs, n, ho)
+    if dist:
+        td.barrier()
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        eng.ecdsa_verify_batch_ptr(hm, hp, hs, n, ho)
+    e2e_s = time.perf_counter() - t0
+    stop.set()
+    th.join(timeout=2)
+    ok_host = np.ctypeslib.as_array(C.cast(ho, C.POINTER(C.c_uint8)), shape=(n,)).astype(bool)
+    assert (ok_host == expected).all(), "verdict mismatch in e2e leg"
+
+    if dist:
+        t = torch.tensor([ms, e2e_s * 1e3], device=dev, dtype=torch.float64)
+        td.all_reduce(t, op=td.ReduceOp.MAX)
+        ms, e2e_ms = t[0].item(), t[1].item()
+    else:
+        e2e_ms = e2e_s * 1e3
+    if rank != 0:
+        if dist:
+            td.destroy_process_group()
+        return
+
+    total = n * world
+    value = total * args.steps / (ms * 1e-3)
+    e2e = total * args.steps / (e2e_ms * 1e-3)
+    peak_imad = eng.measure_int_peak(1)   # carry-chained IMAD.WIDE form the field code uses
+    peak_wide = eng.measure_int_peak(0)
+    peak_add = eng.measure_int_peak(2)
+    peaks = {}
+    try:
+        peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+    except Exception:
+        pass
+    hbm_peak = peaks.get("hbm_gbs", 6650.0)
+    per_gpu = value / world
+    achieved = per_gpu * MUL32_PER_VERIFY
+    line = {
+        "metric": "ecdsa_sigverifies_per_s", "value": value, "unit": "sigverifies/s", "n_gpus": world, "steps": args.steps,
+        "warmup": args.warmup, "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak",
+        "vs_baseline": None, "dtype": "u32", "data": "synthetic",
+        "config": {"workload": "configs[1]: batched secp256k1_ecdsa_verify, 1M synthetic signatures incl. 1% corrupted",
+                   "sigs_per_gpu": n, "sharding": "by signature index, one process per GPU, no collective",
+                   "l2_policy": "inputs+scratch per step = %.0f MB (> 126 MB L2 at the default size)"
+                   % ((n * (161 + 80 + 1)) / 1e6)},
+        "roofline": {"bound": "int32-mul pipe (no HBM/tensor bound applies; reported in the contract's shape)",
+                     "achieved": achieved / 1e12, "peak": peak_imad / 1e12, "unit": "Tmul32/s", "frac": achieved / peak_imad,
+                     "traffic": None,
+                     "peak_source": "bcp_gpu_measure_int_peak(1): IMAD.WIDE.U32.X carry chains, measured live",
+                     "imad_wide_plain_peak": peak_wide / 1e12, "iadd_peak_tops": peak_add / 1e12,
+                     "hbm": {"achieved_gbs": per_gpu * BYTES_PER_VERIFY / 1e9, "peak_gbs": hbm_peak,
+                             "frac": per_gpu * BYTES_PER_VERIFY / 1e9 / hbm_peak,
+                             "peak_source": "MEASURED_PEAKS.json" if peaks else "fallback"}},
+        "e2e": {"value": e2e, "unit": "sigverifies/s", "h2d_bytes_per_step": n * 161 * world, "d2h_bytes_per_step": n * world},
+        "gpu_launches": 2 * args.steps, "clocks": summarize_clocks(samples), "gen_seconds": gen_s,
+    }
+    if not args.no_cpu_baseline:
+        line["cpu_baseline"] = cpu_baseline(msg, pub, sig)
+    print(json.dumps(line))
+    if dist:
+        td.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

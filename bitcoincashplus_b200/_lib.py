@@ -1,0 +1,77 @@
+"""Loader for libbcp_b200.so (in-tree build product).  Fails loudly: no fallback of any kind."""
+import ctypes as C
+import os
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+_SO = os.path.join(HERE, "libbcp_b200.so")
+
+
+class BcpError(RuntimeError):
+    pass
+
+
+def lib_path():
+    return _SO
+
+
+_lib = None
+
+u8p = C.POINTER(C.c_uint8)
+u32p = C.POINTER(C.c_uint32)
+vp = C.c_void_p
+sz = C.c_size_t
+
+# name -> (restype, argtypes): exactly the declarations of include/bcp_gpu.h
+SIGNATURES = {
+    "bcp_gpu_device_count": (C.c_int, []),
+    "bcp_gpu_init": (C.c_int, [C.c_int]),
+    "bcp_gpu_shutdown": (C.c_int, [C.c_int]),
+    "bcp_gpu_last_error": (C.c_char_p, []),
+    "bcp_gpu_host_alloc": (vp, [sz]),
+    "bcp_gpu_host_free": (None, [vp]),
+    "bcp_gpu_ecdsa_verify_batch": (C.c_int, [C.c_int, vp, vp, vp, sz, C.c_uint32, vp]),
+    "bcp_gpu_ecdsa_verify_batch_dev": (C.c_int, [C.c_int, vp, vp, vp, sz, C.c_uint32, vp, vp]),
+    "bcp_gpu_ecdsa_scratch_bytes": (sz, [sz]),
+    "bcp_gpu_ecdsa_reserve": (C.c_int, [C.c_int, sz]),
+    "bcp_der_lax_parse": (C.c_int, [vp, sz, vp]),
+    "bcp_block_index": (C.c_long, [vp, sz, C.c_int, vp, sz]),
+    "bcp_gpu_sha256d_txids_merkle": (C.c_int, [C.c_int, vp, sz, vp, sz, vp, vp, C.POINTER(C.c_int)]),
+    "bcp_gpu_merkle_root": (C.c_int, [C.c_int, vp, sz, vp, C.POINTER(C.c_int)]),
+    "bcp_gpu_sha256d_batch": (C.c_int, [C.c_int, vp, sz, vp, sz, vp]),
+    "bcp_gpu_sha256d_batch_dev": (C.c_int, [C.c_int, vp, vp, sz, vp, vp]),
+    "bcp_gpu_merkle_scratch_bytes": (sz, [sz]),
+    "bcp_gpu_merkle_root_dev": (C.c_int, [C.c_int, vp, sz, vp, vp, vp, vp]),
+    "bcp_gpu_equihash_verify_batch": (C.c_int, [C.c_int, C.c_uint, C.c_uint, vp, sz, sz, sz, vp, vp]),
+    "bcp_gpu_equihash_scratch_bytes": (sz, [sz]),
+    "bcp_gpu_equihash_verify_batch_dev": (C.c_int, [C.c_int, C.c_uint, C.c_uint, vp, sz, sz, sz, vp, vp, vp]),
+    "bcp_gpu_measure_int_peak": (C.c_int, [C.c_int, C.c_int, C.POINTER(C.c_double)]),
+}
+
+
+def lib():
+    """The loaded library with argtypes set; raises BcpError if it has not been built."""
+    global _lib
+    if _lib is None:
+        if not os.path.exists(_SO):
+            raise BcpError(
+                "%s is missing: build it with `python -c 'import __graft_entry__ as g; g.build()'` "
+                "(nvcc, sm_100a).  There is no CPU fallback." % _SO)
+        try:
+            L = C.CDLL(_SO)
+        except OSError as e:
+            raise BcpError("cannot load %s: %s" % (_SO, e))
+        for name, (res, args) in SIGNATURES.items():
+            try:
+                f = getattr(L, name)
+            except AttributeError:
+                raise BcpError("%s does not export %s" % (_SO, name))
+            f.restype = res
+            f.argtypes = args
+        _lib = L
+    return _lib
+
+
+def check(rc, what):
+    if rc != 0:
+        msg = lib().bcp_gpu_last_error() or b""
+        raise BcpError("%s failed (%d): %s" % (what, rc, msg.decode("utf-8", "replace")))

@@ -1,0 +1,123 @@
+"""Python face over the C ABI (include/bcp_gpu.h).  numpy in, numpy out; device pointers for the
+`_dev` variants are plain integers (e.g. torch.Tensor.data_ptr()).  Names follow the reference's
+domain: signatures, pubkeys, txids, Merkle root, headers, solutions."""
+import ctypes as C
+
+import numpy as np
+
+from ._lib import BcpError, check, lib
+
+ECDSA_FLAG_NORMALIZE_S = 1
+
+
+def _np(a, shape_last=None):
+    a = np.ascontiguousarray(a, dtype=np.uint8)
+    if shape_last is not None and (a.ndim != 2 or a.shape[1] != shape_last):
+        raise ValueError("expected an (n, %d) uint8 array, got %r" % (shape_last, a.shape))
+    return a
+
+
+def device_count():
+    return lib().bcp_gpu_device_count()
+
+
+def der_lax_parse(der):
+    """ecdsa_signature_parse_der_lax (src/pubkey.cpp:26-168): returns (ok, r||s bytes)."""
+    out = (C.c_uint8 * 64)()
+    buf = bytes(der)
+    ok = lib().bcp_der_lax_parse(buf, len(buf), out)
+    return ok, bytes(out)
+
+
+def block_index(blk, legacy_header=False, max_tx=1 << 22):
+    """Byte offsets of every transaction of a serialized block (host-side framing scan)."""
+    blk = bytes(blk)
+    off = np.zeros(max_tx + 1, dtype=np.uint32)
+    n = lib().bcp_block_index(blk, len(blk), int(legacy_header), off.ctypes.data, max_tx)
+    if n < 0:
+        raise BcpError("malformed block (bcp_block_index returned %d)" % n)
+    return off[: n + 1].copy()
+
+
+class Engine:
+    """One device context (bcp_gpu_init / bcp_gpu_shutdown)."""
+
+    def __init__(self, device=0):
+        self.device = int(device)
+        check(lib().bcp_gpu_init(self.device), "bcp_gpu_init(%d)" % self.device)
+
+    def close(self):
+        lib().bcp_gpu_shutdown(self.device)
+
+    # ---- ECDSA
+    def ecdsa_verify_batch(self, msg32, pub65, sig64, flags=0):
+        """Per-signature verdict bytes for host arrays (n,32) (n,65) (n,64)."""
+        msg32, pub65, sig64 = _np(msg32, 32), _np(pub65, 65), _np(sig64, 64)
+        n = msg32.shape[0]
+        if pub65.shape[0] != n or sig64.shape[0] != n:
+            raise ValueError("batch arrays disagree on n")
+        ok = np.zeros(n, dtype=np.uint8)
+        check(lib().bcp_gpu_ecdsa_verify_batch(self.device, msg32.ctypes.data, pub65.ctypes.data, sig64.ctypes.data, n,
+                                               flags, ok.ctypes.data), "bcp_gpu_ecdsa_verify_batch")
+        return ok
+
+    def ecdsa_verify_batch_ptr(self, msg32_ptr, pub65_ptr, sig64_ptr, n, ok_ptr, flags=0):
+        """Host-pointer form on caller-owned (pinned) buffers; used by bench.py's e2e leg."""
+        check(lib().bcp_gpu_ecdsa_verify_batch(self.device, msg32_ptr, pub65_ptr, sig64_ptr, n, flags, ok_ptr),
+              "bcp_gpu_ecdsa_verify_batch")
+
+    def ecdsa_reserve(self, n):
+        check(lib().bcp_gpu_ecdsa_reserve(self.device, n), "bcp_gpu_ecdsa_reserve")
+
+    def ecdsa_verify_batch_dev(self, d_msg32, d_pub65, d_sig64, n, d_ok, flags=0, stream=0):
+        check(lib().bcp_gpu_ecdsa_verify_batch_dev(self.device, d_msg32, d_pub65, d_sig64, n, flags, d_ok, stream),
+              "bcp_gpu_ecdsa_verify_batch_dev")
+
+    # ---- SHA-256d / Merkle
+    def txids_merkle(self, blk, tx_off, want_txids=True):
+        """(txids (ntx,32), root bytes, mutated bool) of a serialized block given its tx offsets."""
+        blk = np.frombuffer(bytes(blk), dtype=np.uint8) if not isinstance(blk, np.ndarray) else _np(blk)
+        tx_off = np.ascontiguousarray(tx_off, dtype=np.uint32)
+        ntx = len(tx_off) - 1 if len(tx_off) else 0
+        txids = np.zeros((ntx, 32), dtype=np.uint8)
+        root = (C.c_uint8 * 32)()
+        mut = C.c_int(0)
+        check(lib().bcp_gpu_sha256d_txids_merkle(self.device, blk.ctypes.data, blk.size, tx_off.ctypes.data, ntx,
+                                                 txids.ctypes.data if want_txids else None, root, C.byref(mut)),
+              "bcp_gpu_sha256d_txids_merkle")
+        return txids, bytes(root), bool(mut.value)
+
+    def merkle_root(self, leaves32):
+        leaves32 = _np(leaves32).reshape(-1, 32)
+        root = (C.c_uint8 * 32)()
+        mut = C.c_int(0)
+        check(lib().bcp_gpu_merkle_root(self.device, leaves32.ctypes.data if len(leaves32) else None, len(leaves32),
+                                        root, C.byref(mut)), "bcp_gpu_merkle_root")
+        return bytes(root), bool(mut.value)
+
+    def sha256d_batch(self, data, off):
+        data = np.frombuffer(bytes(data), dtype=np.uint8) if not isinstance(data, np.ndarray) else _np(data)
+        off = np.ascontiguousarray(off, dtype=np.uint32)
+        cnt = len(off) - 1
+        out = np.zeros((cnt, 32), dtype=np.uint8)
+        check(lib().bcp_gpu_sha256d_batch(self.device, data.ctypes.data, data.size, off.ctypes.data, cnt,
+                                          out.ctypes.data), "bcp_gpu_sha256d_batch")
+        return out
+
+    # ---- Equihash
+    def equihash_verify_batch(self, n, k, hdrs, want_hash=True):
+        """hdrs: (count, hdr_len) uint8 serialized post-fork headers -> (ok (count,), hash (count,32))."""
+        hdrs = _np(hdrs)
+        count, hdr_len = hdrs.shape
+        ok = np.zeros(count, dtype=np.uint8)
+        hashes = np.zeros((count, 32), dtype=np.uint8)
+        check(lib().bcp_gpu_equihash_verify_batch(self.device, n, k, hdrs.ctypes.data, hdr_len, hdr_len, count,
+                                                  ok.ctypes.data, hashes.ctypes.data if want_hash else None),
+              "bcp_gpu_equihash_verify_batch")
+        return ok, hashes
+
+    # ---- measurement
+    def measure_int_peak(self, which=0):
+        v = C.c_double(0)
+        check(lib().bcp_gpu_measure_int_peak(self.device, which, C.byref(v)), "bcp_gpu_measure_int_peak")
+        return v.value

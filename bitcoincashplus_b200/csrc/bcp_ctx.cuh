@@ -1,0 +1,35 @@
+// bcp_ctx.cuh — per-device context shared by the .cu translation units of libbcp_b200.so.
+#pragma once
+#include <cuda_runtime.h>
+#include <mutex>
+#include <string>
+#include "../../include/bcp_gpu.h"
+
+#define BCP_MAX_DEVICES 16
+
+struct bcp_ctx {
+    bool ready = false;
+    int device = -1;
+    int sm_count = 0;
+    cudaStream_t stream = nullptr;      // work stream of the host-pointer entry points
+    cudaStream_t copy_stream = nullptr; // second stream for chunk pipelining
+    cudaEvent_t ev[4] = {nullptr, nullptr, nullptr, nullptr};
+    uint32_t *gcomb = nullptr;          // fixed-base comb table (BCP_GCOMB_WORDS words)
+    uint8_t *scratch = nullptr;         // phase-1 records and other per-call scratch
+    size_t scratch_bytes = 0;
+    uint8_t *stage = nullptr;           // device staging for the host-pointer entry points
+    size_t stage_bytes = 0;
+    std::mutex mu;
+};
+
+bcp_ctx *bcp_get_ctx(int device);            // nullptr (+ last error set) when not initialised
+void bcp_set_error(const char *fmt, ...);
+int bcp_cuda_fail(cudaError_t e, const char *what);
+int bcp_ctx_reserve_scratch(bcp_ctx *c, size_t bytes);
+int bcp_ctx_reserve_stage(bcp_ctx *c, size_t bytes);
+
+#define BCP_CUDA(call)                                          \
+    do {                                                        \
+        cudaError_t e__ = (call);                               \
+        if (e__ != cudaSuccess) return bcp_cuda_fail(e__, #call); \
+    } while (0)

@@ -1,0 +1,315 @@
+// bcp_hash.cu — SHA-256d kernels: transaction ids, generic message batches (block headers) and the
+// Merkle root with the CVE-2012-2459 `mutated` flag.  C-ABI in include/bcp_gpu.h.
+//
+// Reference functions replaced (per block): CTransaction::ComputeHash (src/primitives/transaction.cpp:
+// 73-75) over every transaction, ComputeMerkleRoot / BlockMerkleRoot (src/consensus/merkle.cpp:47-150,
+// 175-182), CBlockHeader::GetHash (src/primitives/block.cpp:17-28).
+//
+// k_sha256d_msgs   one thread per message (tx or header).  Full 64-byte blocks are read as aligned
+//                  32-bit words and re-aligned + byte-swapped with one PRMT per word; only the tail goes
+//                  through byte loads.  Messages of one warp are adjacent in memory, so the lines a warp
+//                  touches are shared by its lanes.
+// k_merkle_levels  256 nodes per 128-thread block, eight tree levels per launch, staged in shared
+//                  memory; a 41,650-leaf block needs two launches.
+#include "bcp_ctx.cuh"
+#include "sha256.cuh"
+#include <cstring>
+
+#define MERKLE_THREADS 128
+#define MERKLE_NODES 256
+#define MERKLE_LEVELS 8
+
+// off != nullptr: message i is data[off[i] .. off[i+1]);  off == nullptr: message i is data[i*stride .. +fixed_len)
+__global__ void __launch_bounds__(128) k_sha256d_msgs(const uint8_t *__restrict__ data, const uint32_t *__restrict__ off,
+                                                      uint32_t stride, uint32_t fixed_len, size_t count,
+                                                      uint8_t *__restrict__ out32) {
+    size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= count) return;
+    const uint32_t start = off ? off[i] : (uint32_t)(i * stride);
+    const uint32_t len = off ? off[i + 1] - start : fixed_len;
+    const uint32_t *aligned = reinterpret_cast<const uint32_t *>(data);
+    uint32_t s[8];
+    sha256_init(s);
+    uint32_t pos = 0;
+    const uint32_t sh = start & 3u;
+    const uint32_t sel = (sh << 12) | ((sh + 1) << 8) | ((sh + 2) << 4) | (sh + 3);
+#pragma unroll 1
+    for (; pos + 64 <= len; pos += 64) {
+        const uint32_t *a = aligned + ((start + pos) >> 2);
+        uint32_t x[17], w[16];
+#pragma unroll
+        for (int j = 0; j < 17; j++) x[j] = __ldg(a + j); /* may read 3 bytes past the message: buffers are padded */
+#pragma unroll
+        for (int j = 0; j < 16; j++) w[j] = __byte_perm(x[j], x[j + 1], sel);
+        sha256_compress(s, w);
+    }
+    const uint32_t total = ((len + 9 + 63) / 64) * 64;
+#pragma unroll 1
+    for (; pos < total; pos += 64) {
+        uint32_t w[16];
+#pragma unroll
+        for (int j = 0; j < 16; j++) w[j] = sha256_msg_word(data + start, len, total, pos + 4 * j);
+        sha256_compress(s, w);
+    }
+    sha256_second_pass(s);
+    uint4 *o = reinterpret_cast<uint4 *>(out32 + 32 * i);
+    o[0] = make_uint4(__byte_perm(s[0], 0, 0x0123), __byte_perm(s[1], 0, 0x0123), __byte_perm(s[2], 0, 0x0123),
+                      __byte_perm(s[3], 0, 0x0123));
+    o[1] = make_uint4(__byte_perm(s[4], 0, 0x0123), __byte_perm(s[5], 0, 0x0123), __byte_perm(s[6], 0, 0x0123),
+                      __byte_perm(s[7], 0, 0x0123));
+}
+
+// in: `count` nodes of tree level `level0` (each spans 2^level0 leaves) of a tree with `nleaves` leaves.
+// out: ceil(count / 256) nodes of level level0 + 8 (or the root earlier).  A pair (L, R) at level l is
+// hashed as SHA256d(L || R); a missing R (odd tail) is replaced by L.  `mutated` is raised when L == R
+// for a pair whose right node lies wholly inside the real leaves (merkle.cpp:86; the final sweep :109-140
+// never tests).
+__global__ void __launch_bounds__(MERKLE_THREADS)
+    k_merkle_levels(const uint32_t *__restrict__ in, size_t count, int level0, size_t nleaves, uint32_t *__restrict__ out,
+                    int *__restrict__ mutated) {
+    __shared__ uint32_t node[MERKLE_NODES][8 + 1]; /* +1: pad against bank conflicts on the row stride */
+    const size_t base = (size_t)blockIdx.x * MERKLE_NODES;
+    for (int t = threadIdx.x; t < MERKLE_NODES * 8; t += MERKLE_THREADS) {
+        size_t g = base + (t >> 3);
+        node[t >> 3][t & 7] = g < count ? __byte_perm(in[g * 8 + (t & 7)], 0, 0x0123) : 0u;
+    }
+    __syncthreads();
+    size_t cnt = count;          /* nodes at the current level, whole tree */
+    size_t first = base;         /* global index of this block's node 0 at the current level */
+    int mut = 0;
+#pragma unroll 1
+    for (int l = 0; l < MERKLE_LEVELS && cnt > 1; l++) {
+        const int pairs = MERKLE_NODES >> (l + 1);
+        uint32_t s[8];
+        bool active = false;
+        if ((int)threadIdx.x < pairs) {
+            size_t gl = first + 2 * threadIdx.x, gr = gl + 1;
+            if (gl < cnt) {
+                active = true;
+                uint32_t w[16];
+                const bool has_r = gr < cnt;
+                bool same = true;
+#pragma unroll
+                for (int k = 0; k < 8; k++) {
+                    w[k] = node[2 * threadIdx.x][k];
+                    w[8 + k] = has_r ? node[2 * threadIdx.x + 1][k] : w[k];
+                    same = same && (w[k] == w[8 + k]);
+                }
+                const size_t span = (size_t)1 << (level0 + l);
+                if (has_r && same && (gr + 1) * span <= nleaves) mut = 1;
+                sha256d_64(s, w);
+            }
+        }
+        __syncthreads();
+        if (active) {
+#pragma unroll
+            for (int k = 0; k < 8; k++) node[threadIdx.x][k] = s[k];
+        }
+        __syncthreads();
+        cnt = (cnt + 1) >> 1;
+        first >>= 1;
+    }
+    if (mut) atomicOr(mutated, 1);
+    if (threadIdx.x < 8) out[(size_t)blockIdx.x * 8 + threadIdx.x] = __byte_perm(node[0][threadIdx.x], 0, 0x0123);
+}
+
+// root of `n` leaves already on the device; nodes ping-pong between two scratch halves
+static int merkle_dev(bcp_ctx *c, const uint8_t *d_leaves, size_t n, uint8_t *d_root32, int *d_mut, uint32_t *d_tmp,
+                      cudaStream_t st) {
+    BCP_CUDA(cudaMemsetAsync(d_mut, 0, sizeof(int), st));
+    if (n == 0) {
+        BCP_CUDA(cudaMemsetAsync(d_root32, 0, 32, st));
+        return BCP_OK;
+    }
+    const uint32_t *cur = reinterpret_cast<const uint32_t *>(d_leaves);
+    size_t cnt = n;
+    int level = 0;
+    size_t half = ((n + MERKLE_NODES - 1) / MERKLE_NODES) * 8;
+    uint32_t *buf[2] = {d_tmp, d_tmp + half};
+    int k = 0;
+    while (cnt > 1) {
+        unsigned blocks = (unsigned)((cnt + MERKLE_NODES - 1) / MERKLE_NODES);
+        k_merkle_levels<<<blocks, MERKLE_THREADS, 0, st>>>(cur, cnt, level, n, buf[k], d_mut);
+        cur = buf[k];
+        k ^= 1;
+        for (int l = 0; l < MERKLE_LEVELS && cnt > 1; l++) cnt = (cnt + 1) >> 1;
+        level += MERKLE_LEVELS;
+    }
+    BCP_CUDA(cudaGetLastError());
+    BCP_CUDA(cudaMemcpyAsync(d_root32, cur, 32, cudaMemcpyDeviceToDevice, st));
+    return BCP_OK;
+}
+static size_t merkle_tmp_words(size_t n) { return 2 * (((n + MERKLE_NODES - 1) / MERKLE_NODES) * 8) + 16; }
+
+// fixed-size messages at a fixed stride (serialized block headers)
+int bcp_sha256d_strided_dev(bcp_ctx *c, const uint8_t *d_data, size_t stride, size_t len, size_t count, uint8_t *d_out,
+                            cudaStream_t st) {
+    if (count == 0) return BCP_OK;
+    k_sha256d_msgs<<<(unsigned)((count + 127) / 128), 128, 0, st>>>(d_data, nullptr, (uint32_t)stride, (uint32_t)len, count,
+                                                                   d_out);
+    BCP_CUDA(cudaGetLastError());
+    return BCP_OK;
+}
+
+extern "C" {
+
+// Compact-size + transaction framing scan (src/serialize.h:260-300, src/primitives/transaction.h:223-243,
+// header layout src/primitives/block.h:49-73).  Sequential byte parsing: stays on the host by design.
+static int rd_compact(const uint8_t *p, size_t len, size_t *pos, uint64_t *v) {
+    if (*pos >= len) return 0;
+    uint8_t ch = p[(*pos)++];
+    if (ch < 253) { *v = ch; return 1; }
+    int nb = ch == 253 ? 2 : ch == 254 ? 4 : 8;
+    if (*pos + nb > len) return 0;
+    uint64_t x = 0;
+    for (int i = 0; i < nb; i++) x |= (uint64_t)p[*pos + i] << (8 * i);
+    *pos += nb;
+    if ((nb == 2 && x < 253) || (nb == 4 && x < 0x10000ull) || (nb == 8 && x < 0x100000000ull)) return 0; /* non-canonical */
+    if (x > 0x02000000ull) return 0;                                                                        /* MAX_SIZE */
+    *v = x;
+    return 1;
+}
+BCP_API long bcp_block_index(const uint8_t *blk, size_t len, int legacy_header, uint32_t *tx_off, size_t max_tx) {
+    size_t pos;
+    uint64_t v, ntx;
+    if (legacy_header) {
+        pos = 80;
+    } else {
+        pos = 140;
+        if (len < 140 || !rd_compact(blk, len, &pos, &v)) return -1;
+        pos += v;
+    }
+    if (pos > len || !rd_compact(blk, len, &pos, &ntx)) return -1;
+    if (ntx > max_tx) return -2;
+    for (uint64_t t = 0; t < ntx; t++) {
+        tx_off[t] = (uint32_t)pos;
+        uint64_t nin, nout, sl;
+        if (pos + 4 > len) return -1;
+        pos += 4;
+        if (!rd_compact(blk, len, &pos, &nin)) return -1;
+        for (uint64_t i = 0; i < nin; i++) {
+            if (pos + 36 > len) return -1;
+            pos += 36;
+            if (!rd_compact(blk, len, &pos, &sl) || pos + sl + 4 > len) return -1;
+            pos += sl + 4;
+        }
+        if (!rd_compact(blk, len, &pos, &nout)) return -1;
+        for (uint64_t i = 0; i < nout; i++) {
+            if (pos + 8 > len) return -1;
+            pos += 8;
+            if (!rd_compact(blk, len, &pos, &sl) || pos + sl > len) return -1;
+            pos += sl;
+        }
+        if (pos + 4 > len) return -1;
+        pos += 4;
+    }
+    tx_off[ntx] = (uint32_t)pos;
+    return (long)ntx;
+}
+
+BCP_API int bcp_gpu_sha256d_batch_dev(int device, const uint8_t *d_data, const uint32_t *d_off, size_t count,
+                                      uint8_t *d_out32, void *stream) {
+    bcp_ctx *c = bcp_get_ctx(device);
+    if (!c) return BCP_ERR_NOT_INIT;
+    if (count == 0) return BCP_OK;
+    BCP_CUDA(cudaSetDevice(device));
+    cudaStream_t st = stream ? (cudaStream_t)stream : c->stream;
+    k_sha256d_msgs<<<(unsigned)((count + 127) / 128), 128, 0, st>>>(d_data, d_off, 0, 0, count, d_out32);
+    BCP_CUDA(cudaGetLastError());
+    return BCP_OK;
+}
+
+BCP_API size_t bcp_gpu_merkle_scratch_bytes(size_t n) { return merkle_tmp_words(n) * 4 + 64; }
+
+// d_scratch: bcp_gpu_merkle_scratch_bytes(n) bytes; d_root32: 32 bytes; d_mutated: one int
+BCP_API int bcp_gpu_merkle_root_dev(int device, const uint8_t *d_leaves32, size_t n, uint8_t *d_root32, int *d_mutated,
+                                    void *d_scratch, void *stream) {
+    bcp_ctx *c = bcp_get_ctx(device);
+    if (!c) return BCP_ERR_NOT_INIT;
+    BCP_CUDA(cudaSetDevice(device));
+    return merkle_dev(c, d_leaves32, n, d_root32, d_mutated, reinterpret_cast<uint32_t *>(d_scratch),
+                      stream ? (cudaStream_t)stream : c->stream);
+}
+
+// Host-pointer forms.  Staging layout in c->stage: [data + pad][offsets][digests][merkle tmp][root][mutated]
+static int hash_host(bcp_ctx *c, const uint8_t *data, size_t len, const uint32_t *off, size_t count, bool want_root,
+                     uint8_t *out32, uint8_t *root32, int *mutated) {
+    size_t o_data = 0, o_off = (len + 8 + 255) / 256 * 256, o_out = o_off + ((count + 1) * 4 + 255) / 256 * 256;
+    size_t o_tmp = o_out + (count * 32 + 255) / 256 * 256, o_root = o_tmp + (merkle_tmp_words(count) * 4 + 255) / 256 * 256;
+    size_t total = o_root + 256;
+    int rc = bcp_ctx_reserve_stage(c, total);
+    if (rc != BCP_OK) return rc;
+    uint8_t *d = c->stage;
+    cudaStream_t st = c->stream;
+    if (count) {
+        BCP_CUDA(cudaMemcpyAsync(d + o_data, data, len, cudaMemcpyHostToDevice, st));
+        BCP_CUDA(cudaMemcpyAsync(d + o_off, off, (count + 1) * 4, cudaMemcpyHostToDevice, st));
+        k_sha256d_msgs<<<(unsigned)((count + 127) / 128), 128, 0, st>>>(d + o_data, reinterpret_cast<uint32_t *>(d + o_off),
+                                                                       0, 0, count, d + o_out);
+        BCP_CUDA(cudaGetLastError());
+        if (out32) BCP_CUDA(cudaMemcpyAsync(out32, d + o_out, count * 32, cudaMemcpyDeviceToHost, st));
+    }
+    if (want_root) {
+        rc = merkle_dev(c, d + o_out, count, d + o_root, reinterpret_cast<int *>(d + o_root + 32),
+                        reinterpret_cast<uint32_t *>(d + o_tmp), st);
+        if (rc != BCP_OK) return rc;
+        uint8_t res[36];
+        BCP_CUDA(cudaMemcpyAsync(res, d + o_root, 36, cudaMemcpyDeviceToHost, st));
+        BCP_CUDA(cudaStreamSynchronize(st));
+        memcpy(root32, res, 32);
+        int m;
+        memcpy(&m, res + 32, 4);
+        if (mutated) *mutated = m ? 1 : 0;
+    } else {
+        BCP_CUDA(cudaStreamSynchronize(st));
+    }
+    return BCP_OK;
+}
+
+BCP_API int bcp_gpu_sha256d_batch(int device, const uint8_t *data, size_t len, const uint32_t *off, size_t count,
+                                  uint8_t *out32) {
+    bcp_ctx *c = bcp_get_ctx(device);
+    if (!c) return BCP_ERR_NOT_INIT;
+    if (count && (!data || !off || !out32)) { bcp_set_error("bcp_gpu_sha256d_batch: NULL buffer"); return BCP_ERR_INVALID; }
+    if (count && (off[count] > len || len > 0xFFFFFFF0ull)) { bcp_set_error("bcp_gpu_sha256d_batch: offsets exceed buffer"); return BCP_ERR_INVALID; }
+    std::lock_guard<std::mutex> lk(c->mu);
+    BCP_CUDA(cudaSetDevice(device));
+    return hash_host(c, data, len, off, count, false, out32, nullptr, nullptr);
+}
+
+BCP_API int bcp_gpu_sha256d_txids_merkle(int device, const uint8_t *blk, size_t len, const uint32_t *tx_off, size_t ntx,
+                                         uint8_t *txids, uint8_t root32[32], int *mutated) {
+    bcp_ctx *c = bcp_get_ctx(device);
+    if (!c) return BCP_ERR_NOT_INIT;
+    if (!root32 || (ntx && (!blk || !tx_off))) { bcp_set_error("bcp_gpu_sha256d_txids_merkle: NULL buffer"); return BCP_ERR_INVALID; }
+    if (ntx && (tx_off[ntx] > len || len > 0xFFFFFFF0ull)) { bcp_set_error("bcp_gpu_sha256d_txids_merkle: offsets exceed buffer"); return BCP_ERR_INVALID; }
+    std::lock_guard<std::mutex> lk(c->mu);
+    BCP_CUDA(cudaSetDevice(device));
+    return hash_host(c, blk, len, tx_off, ntx, true, txids, root32, mutated);
+}
+
+BCP_API int bcp_gpu_merkle_root(int device, const uint8_t *leaves32, size_t n, uint8_t root32[32], int *mutated) {
+    bcp_ctx *c = bcp_get_ctx(device);
+    if (!c) return BCP_ERR_NOT_INIT;
+    if (!root32 || (n && !leaves32)) { bcp_set_error("bcp_gpu_merkle_root: NULL buffer"); return BCP_ERR_INVALID; }
+    std::lock_guard<std::mutex> lk(c->mu);
+    BCP_CUDA(cudaSetDevice(device));
+    size_t o_tmp = (n * 32 + 255) / 256 * 256, o_root = o_tmp + (merkle_tmp_words(n) * 4 + 255) / 256 * 256;
+    int rc = bcp_ctx_reserve_stage(c, o_root + 256);
+    if (rc != BCP_OK) return rc;
+    uint8_t *d = c->stage;
+    if (n) BCP_CUDA(cudaMemcpyAsync(d, leaves32, n * 32, cudaMemcpyHostToDevice, c->stream));
+    rc = merkle_dev(c, d, n, d + o_root, reinterpret_cast<int *>(d + o_root + 32), reinterpret_cast<uint32_t *>(d + o_tmp),
+                    c->stream);
+    if (rc != BCP_OK) return rc;
+    uint8_t res[36];
+    BCP_CUDA(cudaMemcpyAsync(res, d + o_root, 36, cudaMemcpyDeviceToHost, c->stream));
+    BCP_CUDA(cudaStreamSynchronize(c->stream));
+    memcpy(root32, res, 32);
+    int m;
+    memcpy(&m, res + 32, 4);
+    if (mutated) *mutated = m ? 1 : 0;
+    return BCP_OK;
+}
+
+} // extern "C"

@@ -1,0 +1,292 @@
+// ecdsa.cuh — the two device phases of one ECDSA verification.
+//
+// Together they compute exactly the verdict of the reference chain
+//   secp256k1_ec_pubkey_parse (src/secp256k1/src/secp256k1.c:150-163, eckey_impl.h:17-35)
+//   secp256k1_ecdsa_signature_parse_compact (:228-247)  [+ _normalize (:274-291) when BCP_ECDSA_NORMALIZE_S]
+//   secp256k1_ecdsa_verify (:293-308) -> secp256k1_ecdsa_sig_verify (ecdsa_impl.h:201-269)
+// i.e. accept iff  pubkey parses,  r,s in [1,n-1],  s <= n/2,  R = (m/s)G + (r/s)Q != infinity  and
+// x(R) == r or (r < p-n and x(R) == r+n)  (the comparison is done projectively, r*Z^2 == X, like
+// gej_eq_x_var group_impl.h:246-252, so no field inversion is needed).
+//
+// How the multiplication is evaluated is NOT the reference's (wNAF Strauss with a 1 MiB G table,
+// ecmult_impl.h:286-404): a warp must stay convergent, so
+//   phase 1 (prep, one thread per K signatures): range checks, ONE scalar inversion per K signatures
+//           (Montgomery's trick), u1 = m/s, u2 = r/s, lattice split u2 = k1 + k2*lambda, signed 4-bit
+//           window recoding.  Output: a 80-byte record per signature in scratch memory.
+//   phase 2 (point, one thread per signature): decompress Q, build {1..8}Q on a common Z without any
+//           inversion (z-ratio rescaling, the idea of ge_globalz_set_table_gej group_impl.h:173-194),
+//           34 windows of 4 doublings + 2 mixed additions (Q and lambda*Q share the table: lambda*(x,y) =
+//           (beta*x, y)), then u1*G from a fixed-position comb table (22 windows of 12 bits, no doublings),
+//           then the projective x comparison.
+#pragma once
+#include "ge.cuh"
+#include "scalar.cuh"
+
+#define BCP_ECDSA_NORMALIZE_S 1u /* CPubKey::Verify semantics: s := min(s, n-s) instead of rejecting high s */
+
+#define BCP_REC_WORDS 20 /* u1[8] k1[5] k2[5] flags pad  = 80 bytes */
+#define BCP_REC_VALID 1u
+#define BCP_REC_NEG1 2u
+#define BCP_REC_NEG2 4u
+
+#define BCP_GCOMB_BITS 12
+#define BCP_GCOMB_WINDOWS 22                 /* ceil(256 / 12) */
+#define BCP_GCOMB_ENTRIES (1 << BCP_GCOMB_BITS)
+#define BCP_GCOMB_WORDS (BCP_GCOMB_WINDOWS * BCP_GCOMB_ENTRIES * 16) /* 16 words (x,y) per entry; entry 0 unused */
+
+#define BCP_QTAB_ENTRIES 8
+#define BCP_QTAB_WORDS (BCP_QTAB_ENTRIES * 16)
+
+// ---------------------------------------------------------------- phase 1: scalar side
+struct sig_scalars {
+    scalar r, s, m;
+    bool valid;
+};
+// parse + range rules for one signature (msg is reduced mod n silently, secp256k1.c:303)
+BCP_DEV void sig_load(sig_scalars &o, const uint8_t *msg32, const uint8_t *sig64, uint32_t flags) {
+    bool ov_r = sc_set_b32(o.r, sig64);
+    bool ov_s = sc_set_b32(o.s, sig64 + 32);
+    sc_set_b32(o.m, msg32);
+    bool ok = !(ov_r || ov_s);                          /* parse_compact overflow => rejected            */
+    ok = ok && !sc_is_zero(o.r) && !sc_is_zero(o.s);    /* ecdsa_impl.h:210                              */
+    if (sc_is_high(o.s)) {
+        if (flags & BCP_ECDSA_NORMALIZE_S) sc_negate(o.s, o.s);
+        else ok = false;                                /* secp256k1.c:305                               */
+    }
+    o.valid = ok;
+    if (!ok) { /* keep the batch product invertible */
+        BCP_UNROLL
+        for (int i = 0; i < 8; i++) o.s.v[i] = (i == 0);
+    }
+}
+// signed 4-bit window recoding of a magnitude < 2^132 held in 5 limbs: after adding 8 to every
+// nibble 0..32 (with carries), digit_w = nibble_w - 8 in [-8,7] for w <= 32 and digit_33 = nibble_33 in {0,1}
+BCP_DEV void recode_w4(uint32_t *k /*5, in place*/) {
+    uint32_t add[5] = {0x88888888u, 0x88888888u, 0x88888888u, 0x88888888u, 0x00000008u};
+    addn_cc<5>(k, k, add);
+}
+BCP_DEV int digit_w4(const uint32_t *k, int w) {
+    int nib = (int)((k[w >> 3] >> ((w & 7) * 4)) & 15u);
+    return w <= 32 ? nib - 8 : nib;
+}
+// finish one signature once 1/s is known: write the scratch record
+BCP_DEV void sig_finish(uint32_t *rec /*BCP_REC_WORDS*/, const sig_scalars &g, const scalar &sinv) {
+    scalar u1, u2;
+    sc_mul(u1, g.m, sinv);
+    sc_mul(u2, g.r, sinv);
+    uint32_t k1[5], k2[5];
+    bool n1, n2;
+    sc_split_lambda(k1, n1, k2, n2, u2);
+    recode_w4(k1);
+    recode_w4(k2);
+    BCP_UNROLL
+    for (int i = 0; i < 8; i++) rec[i] = u1.v[i];
+    BCP_UNROLL
+    for (int i = 0; i < 5; i++) { rec[8 + i] = k1[i]; rec[13 + i] = k2[i]; }
+    rec[18] = (g.valid ? BCP_REC_VALID : 0u) | (n1 ? BCP_REC_NEG1 : 0u) | (n2 ? BCP_REC_NEG2 : 0u);
+    rec[19] = 0;
+}
+
+// ---------------------------------------------------------------- phase 2: point side
+// Per-thread table of 8 affine-like points in a strided word array (shared memory on the GPU:
+// word (e*16 + i) of thread t lives at base[(e*16 + i) * stride + t], so a warp reading "entry
+// e_lane, limb i" touches 32 different banks whatever the per-lane entries are).
+struct qtable {
+    uint32_t *base;
+    int stride;
+    BCP_DEV_M void store(int e, const fe &x, const fe &y) {
+        BCP_UNROLL
+        for (int i = 0; i < 8; i++) {
+            base[(e * 16 + i) * stride] = x.v[i];
+            base[(e * 16 + 8 + i) * stride] = y.v[i];
+        }
+    }
+    BCP_DEV_M void load(int e, fe &x, fe &y) const {
+        BCP_UNROLL
+        for (int i = 0; i < 8; i++) {
+            x.v[i] = base[(e * 16 + i) * stride];
+            y.v[i] = base[(e * 16 + 8 + i) * stride];
+        }
+    }
+    BCP_DEV_M void load_x(int e, fe &x) const {
+        BCP_UNROLL
+        for (int i = 0; i < 8; i++) x.v[i] = base[(e * 16 + i) * stride];
+    }
+    BCP_DEV_M void load_y(int e, fe &y) const {
+        BCP_UNROLL
+        for (int i = 0; i < 8; i++) y.v[i] = base[(e * 16 + 8 + i) * stride];
+    }
+};
+
+// Build tab[e] = (e+1)*Q for e = 0..7 as affine points of the curve isomorphic under the common
+// Z (returned in zglob): (X_k, Y_k, Z_k) -> (X_k f^2, Y_k f^3) with f = Z_8 / Z_k, the product of the
+// later z-ratios.  No inversion.  kQ (k <= 8) is never infinity nor +-Q, so every addition is generic.
+BCP_DEV void qtable_build(qtable tab, fe &zglob, const fe &qx, const fe &qy) {
+    fe zr[BCP_QTAB_ENTRIES]; /* zr[k] = Z_{k+1} / Z_k  (1-based multiples); dynamic indexing -> local memory */
+    gej p;
+    p.x = qx; p.y = qy; fe_set_u32(p.z, 1); p.inf = false;
+    tab.store(0, qx, qy);
+    {
+        gej d;
+        gej_double(d, p);
+        zr[1] = d.z; /* Z_2 / Z_1 with Z_1 = 1 */
+        p = d;
+        tab.store(1, p.x, p.y);
+    }
+#if BCP_PTX
+#pragma unroll 1
+#endif
+    for (int k = 2; k < BCP_QTAB_ENTRIES; k++) {
+        gej_add_ge(p, qx, qy, &zr[k]);
+        tab.store(k, p.x, p.y);
+    }
+    zglob = p.z;
+    fe zs = zr[BCP_QTAB_ENTRIES - 1];
+#if BCP_PTX
+#pragma unroll 1
+#endif
+    for (int k = BCP_QTAB_ENTRIES - 2; k >= 0; k--) {
+        fe x, y, zs2, zs3;
+        tab.load(k, x, y);
+        fe_sqr(zs2, zs);
+        fe_mul(zs3, zs2, zs);
+        fe_mul(x, x, zs2);
+        fe_mul(y, y, zs3);
+        tab.store(k, x, y);
+        if (k > 0) fe_mul(zs, zs, zr[k]);
+    }
+}
+
+// acc += sign * tab[|d| - 1], optionally through the endomorphism (x -> beta*x)
+BCP_DEV void add_digit(gej &acc, const qtable &tab, int d, bool flip, bool endo) {
+    if (d == 0) return;
+    bool neg = (d < 0) != flip;
+    int e = (d < 0 ? -d : d) - 1;
+    fe x, y;
+    tab.load(e, x, y);
+    if (endo) {
+        fe beta;
+        BCP_UNROLL
+        for (int i = 0; i < 8; i++) beta.v[i] = FE_BETA[i];
+        fe_mul(x, x, beta);
+    }
+    if (neg) fe_neg(y, y);
+    gej_add_ge(acc, x, y, nullptr);
+}
+
+// The whole point phase for one signature.  rec = scratch record from phase 1; gcomb = fixed-base
+// comb table; returns the verdict.
+BCP_DEV bool ecdsa_point_phase(const uint32_t *rec, const uint8_t *pub65, const uint8_t *sig64, qtable tab,
+                               const uint32_t *gcomb) {
+    uint32_t fl = rec[18];
+    if (!(fl & BCP_REC_VALID)) return false;
+    fe qx, qy;
+    if (!pubkey_parse(qx, qy, pub65)) return false;
+
+    fe zglob;
+    qtable_build(tab, zglob, qx, qy);
+
+    uint32_t k1[5], k2[5];
+    BCP_UNROLL
+    for (int i = 0; i < 5; i++) { k1[i] = rec[8 + i]; k2[i] = rec[13 + i]; }
+    const bool n1 = fl & BCP_REC_NEG1, n2 = fl & BCP_REC_NEG2;
+
+    gej acc;
+    fe_set_zero(acc.x); fe_set_zero(acc.y); fe_set_zero(acc.z);
+    acc.inf = true;
+#if BCP_PTX
+#pragma unroll 1
+#endif
+    for (int w = 33; w >= 0; w--) {
+        if (!acc.inf) {
+            gej_double(acc, acc); gej_double(acc, acc); gej_double(acc, acc); gej_double(acc, acc);
+        }
+        add_digit(acc, tab, digit_w4(k1, w), n1, false);
+        add_digit(acc, tab, digit_w4(k2, w), n2, true);
+    }
+    // leave the isomorphic curve: true Z = Z * zglob
+    if (!acc.inf) fe_mul(acc.z, acc.z, zglob);
+
+    // u1 * G: one table lookup + mixed addition per 12-bit window, no doublings
+#if BCP_PTX
+#pragma unroll 1
+#endif
+    for (int j = 0; j < BCP_GCOMB_WINDOWS; j++) {
+        int bit = j * BCP_GCOMB_BITS;
+        int limb = bit >> 5, sh = bit & 31;
+        uint32_t lo = rec[limb];
+        uint32_t hi = (limb + 1 < 8) ? rec[limb + 1] : 0u;
+        uint32_t d = (sh == 0 ? lo : ((lo >> sh) | (hi << (32 - sh)))) & (BCP_GCOMB_ENTRIES - 1);
+        if (d == 0) continue;
+        const uint32_t *e = gcomb + ((size_t)j * BCP_GCOMB_ENTRIES + d) * 16;
+        fe x, y;
+#if BCP_PTX
+        const uint4 *e4 = reinterpret_cast<const uint4 *>(e);
+        uint4 a = __ldg(e4), b = __ldg(e4 + 1), c = __ldg(e4 + 2), dd = __ldg(e4 + 3);
+        x.v[0] = a.x; x.v[1] = a.y; x.v[2] = a.z; x.v[3] = a.w; x.v[4] = b.x; x.v[5] = b.y; x.v[6] = b.z; x.v[7] = b.w;
+        y.v[0] = c.x; y.v[1] = c.y; y.v[2] = c.z; y.v[3] = c.w; y.v[4] = dd.x; y.v[5] = dd.y; y.v[6] = dd.z; y.v[7] = dd.w;
+#else
+        for (int i = 0; i < 8; i++) { x.v[i] = e[i]; y.v[i] = e[8 + i]; }
+#endif
+        gej_add_ge(acc, x, y, nullptr);
+    }
+    if (acc.inf) return false; /* ecdsa_impl.h:220 */
+
+    // x(R) == r (mod n), projectively: r * Z^2 == X, then the r + n < p second chance (:246-266)
+    scalar r;
+    sc_set_b32(r, sig64); /* already known to be in range */
+    fe z2, t, fr;
+    fe_sqr(z2, acc.z);
+    BCP_UNROLL
+    for (int i = 0; i < 8; i++) fr.v[i] = r.v[i];
+    fe_mul(t, fr, z2);
+    if (fe_equal(t, acc.x)) return true;
+    uint32_t pmn[8], n[8];
+    BCP_UNROLL
+    for (int i = 0; i < 8; i++) { pmn[i] = SC_P_MINUS_N[i]; n[i] = SC_N[i]; }
+    if (u256_ge(r.v, pmn)) return false;
+    addn_cc<8>(fr.v, r.v, n); /* r + n < p: no overflow */
+    fe_mul(t, fr, z2);
+    return fe_equal(t, acc.x);
+}
+
+// ---------------------------------------------------------------- one-time: fixed-base comb entry
+// entry (j, d) = d * 2^(12 j) * G as a normalized affine point (d >= 1).  Run once per device by the
+// table-generation kernel (plain double-and-add with two true field inversions: not a hot path).
+BCP_DEV void gej_to_affine(fe &ax, fe &ay, const gej &p) {
+    fe zi, zi2, zi3;
+    fe_inv(zi, p.z);
+    fe_sqr(zi2, zi);
+    fe_mul(zi3, zi2, zi);
+    fe_mul(ax, p.x, zi2);
+    fe_mul(ay, p.y, zi3);
+    fe_normalize(ax);
+    fe_normalize(ay);
+}
+BCP_DEV void gcomb_entry(uint32_t *out16, int j, uint32_t d) {
+    gej base;
+    BCP_UNROLL
+    for (int i = 0; i < 8; i++) { base.x.v[i] = FE_GX[i]; base.y.v[i] = FE_GY[i]; }
+    fe_set_u32(base.z, 1);
+    base.inf = false;
+#if BCP_PTX
+#pragma unroll 1
+#endif
+    for (int i = 0; i < j * BCP_GCOMB_BITS; i++) gej_double(base, base);
+    fe bx, by;
+    gej_to_affine(bx, by, base);
+    gej acc;
+    fe_set_zero(acc.x); fe_set_zero(acc.y); fe_set_zero(acc.z);
+    acc.inf = true;
+#if BCP_PTX
+#pragma unroll 1
+#endif
+    for (int b = BCP_GCOMB_BITS - 1; b >= 0; b--) {
+        if (!acc.inf) gej_double(acc, acc);
+        if ((d >> b) & 1u) gej_add_ge(acc, bx, by, nullptr);
+    }
+    fe ax, ay;
+    gej_to_affine(ax, ay, acc);
+    BCP_UNROLL
+    for (int i = 0; i < 8; i++) { out16[i] = ax.v[i]; out16[8 + i] = ay.v[i]; }
+}

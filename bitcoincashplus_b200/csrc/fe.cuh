@@ -1,0 +1,403 @@
+// fe.cuh — arithmetic in F_p, p = 2^256 - 2^32 - 977, for sm_100a.
+//
+// Replaces (functionally) the reference's CPU field layer src/secp256k1/src/field_10x26_impl.h /
+// field_5x52_impl.h (fe_mul :1059, fe_sqr :1074, fe_normalize :43-264, fe_set_b32 :323, fe_negate/
+// fe_add :386-453) and field_impl.h (fe_sqrt :38-134).  It is NOT a port: the reference keeps 10x26 or
+// 5x52 limbs with lazy "magnitudes"; here an element is 8 x 32-bit limbs (little-endian) holding
+// a value in [0, 2^256) ("weakly reduced": it may exceed p by less than 2^32+977), because B200
+// has no 64-bit multiplier and the 32x32->64 IMAD.WIDE with carry (IMAD.WIDE.U32.X) is the
+// widest native multiply-accumulate.  Products are formed as two interleaved accumulators (even and
+// odd limb positions) so every multiply-accumulate is a 64-bit-aligned IMAD.WIDE on a carry chain,
+// then folded with 2^256 == 2^32 + 977 (mod p).
+//
+// Algorithmic cost convention used for the roofline: one field multiplication =
+// 64 mul32, one squaring = 36 mul32 (reduction not counted).
+#pragma once
+#include "bcp_common.cuh"
+
+struct fe {
+    uint32_t v[8];
+};
+
+#define BCP_P0 0xFFFFFC2Fu
+#define BCP_P1 0xFFFFFFFEu
+#define BCP_FOLD 977u /* 2^256 = 2^32 + 977 (mod p) */
+
+// ------------------------------------------------------------------ limb primitives
+// X[0..7] = { a0*b, a2*b, a4*b, a6*b } as four independent 64-bit products
+BCP_DEV void row_set(uint32_t *X, uint32_t a0, uint32_t a2, uint32_t a4, uint32_t a6, uint32_t b) {
+#if BCP_PTX
+    asm("mul.lo.u32 %0, %8, %12;\n\tmul.hi.u32 %1, %8, %12;\n\t"
+        "mul.lo.u32 %2, %9, %12;\n\tmul.hi.u32 %3, %9, %12;\n\t"
+        "mul.lo.u32 %4, %10, %12;\n\tmul.hi.u32 %5, %10, %12;\n\t"
+        "mul.lo.u32 %6, %11, %12;\n\tmul.hi.u32 %7, %11, %12;"
+        : "=r"(X[0]), "=r"(X[1]), "=r"(X[2]), "=r"(X[3]), "=r"(X[4]), "=r"(X[5]), "=r"(X[6]), "=r"(X[7])
+        : "r"(a0), "r"(a2), "r"(a4), "r"(a6), "r"(b));
+#else
+    uint64_t p;
+    p = (uint64_t)a0 * b; X[0] = (uint32_t)p; X[1] = (uint32_t)(p >> 32);
+    p = (uint64_t)a2 * b; X[2] = (uint32_t)p; X[3] = (uint32_t)(p >> 32);
+    p = (uint64_t)a4 * b; X[4] = (uint32_t)p; X[5] = (uint32_t)(p >> 32);
+    p = (uint64_t)a6 * b; X[6] = (uint32_t)p; X[7] = (uint32_t)(p >> 32);
+#endif
+}
+// X[0..8] += { a0*b, a2*b, a4*b, a6*b } placed at limbs (0,1),(2,3),(4,5),(6,7); X[8] absorbs the carry
+BCP_DEV void row_acc9(uint32_t *X, uint32_t a0, uint32_t a2, uint32_t a4, uint32_t a6, uint32_t b) {
+#if BCP_PTX
+    asm("mad.lo.cc.u32 %0, %9, %13, %0;\n\tmadc.hi.cc.u32 %1, %9, %13, %1;\n\t"
+        "madc.lo.cc.u32 %2, %10, %13, %2;\n\tmadc.hi.cc.u32 %3, %10, %13, %3;\n\t"
+        "madc.lo.cc.u32 %4, %11, %13, %4;\n\tmadc.hi.cc.u32 %5, %11, %13, %5;\n\t"
+        "madc.lo.cc.u32 %6, %12, %13, %6;\n\tmadc.hi.cc.u32 %7, %12, %13, %7;\n\t"
+        "addc.u32 %8, %8, 0;"
+        : "+r"(X[0]), "+r"(X[1]), "+r"(X[2]), "+r"(X[3]), "+r"(X[4]), "+r"(X[5]), "+r"(X[6]), "+r"(X[7]), "+r"(X[8])
+        : "r"(a0), "r"(a2), "r"(a4), "r"(a6), "r"(b));
+#else
+    uint64_t c = 0;
+    const uint32_t a[4] = {a0, a2, a4, a6};
+    for (int j = 0; j < 4; j++) {
+        uint64_t p = (uint64_t)a[j] * b;
+        uint64_t lo = (uint64_t)X[2 * j] + (uint32_t)p + c;
+        X[2 * j] = (uint32_t)lo;
+        uint64_t hi = (uint64_t)X[2 * j + 1] + (uint32_t)(p >> 32) + (lo >> 32);
+        X[2 * j + 1] = (uint32_t)hi;
+        c = hi >> 32;
+    }
+    X[8] += (uint32_t)c;
+#endif
+}
+// same, carry-out known to be zero (top of the product) and dropped
+BCP_DEV void row_acc8(uint32_t *X, uint32_t a0, uint32_t a2, uint32_t a4, uint32_t a6, uint32_t b) {
+#if BCP_PTX
+    asm("mad.lo.cc.u32 %0, %8, %12, %0;\n\tmadc.hi.cc.u32 %1, %8, %12, %1;\n\t"
+        "madc.lo.cc.u32 %2, %9, %12, %2;\n\tmadc.hi.cc.u32 %3, %9, %12, %3;\n\t"
+        "madc.lo.cc.u32 %4, %10, %12, %4;\n\tmadc.hi.cc.u32 %5, %10, %12, %5;\n\t"
+        "madc.lo.cc.u32 %6, %11, %12, %6;\n\tmadc.hi.u32 %7, %11, %12, %7;"
+        : "+r"(X[0]), "+r"(X[1]), "+r"(X[2]), "+r"(X[3]), "+r"(X[4]), "+r"(X[5]), "+r"(X[6]), "+r"(X[7])
+        : "r"(a0), "r"(a2), "r"(a4), "r"(a6), "r"(b));
+#else
+    uint32_t t[9];
+    for (int j = 0; j < 8; j++) t[j] = X[j];
+    t[8] = 0;
+    row_acc9(t, a0, a2, a4, a6, b);
+    for (int j = 0; j < 8; j++) X[j] = t[j];
+#endif
+}
+// r[0..n-1] = a + b, returns carry (0/1).  One asm statement per chain: the carry flag never has to
+// survive between statements.  (Outputs go through temporaries so that r may alias a or b.)
+template <int N>
+BCP_DEV uint32_t addn_cc(uint32_t *r, const uint32_t *a, const uint32_t *b) {
+    uint32_t c;
+#if BCP_PTX
+    static_assert(N == 8 || N == 5 || N == 3 || N == 2, "unsupported chain length");
+    if (N == 8) {
+        uint32_t r0, r1, r2, r3, r4, r5, r6, r7;
+        asm("add.cc.u32 %0, %9, %17;\n\t"
+            "addc.cc.u32 %1, %10, %18;\n\t"
+            "addc.cc.u32 %2, %11, %19;\n\t"
+            "addc.cc.u32 %3, %12, %20;\n\t"
+            "addc.cc.u32 %4, %13, %21;\n\t"
+            "addc.cc.u32 %5, %14, %22;\n\t"
+            "addc.cc.u32 %6, %15, %23;\n\t"
+            "addc.cc.u32 %7, %16, %24;\n\t"
+            "addc.u32 %8, 0, 0;"
+            : "=r"(r0), "=r"(r1), "=r"(r2), "=r"(r3), "=r"(r4), "=r"(r5), "=r"(r6), "=r"(r7), "=r"(c)
+            : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(a[4]), "r"(a[5]), "r"(a[6]), "r"(a[7]), "r"(b[0]), "r"(b[1]), "r"(b[2]), "r"(b[3]), "r"(b[4]), "r"(b[5]), "r"(b[6]), "r"(b[7]));
+        r[0] = r0;
+        r[1] = r1;
+        r[2] = r2;
+        r[3] = r3;
+        r[4] = r4;
+        r[5] = r5;
+        r[6] = r6;
+        r[7] = r7;
+    } else if (N == 5) {
+        uint32_t r0, r1, r2, r3, r4;
+        asm("add.cc.u32 %0, %6, %11;\n\t"
+            "addc.cc.u32 %1, %7, %12;\n\t"
+            "addc.cc.u32 %2, %8, %13;\n\t"
+            "addc.cc.u32 %3, %9, %14;\n\t"
+            "addc.cc.u32 %4, %10, %15;\n\t"
+            "addc.u32 %5, 0, 0;"
+            : "=r"(r0), "=r"(r1), "=r"(r2), "=r"(r3), "=r"(r4), "=r"(c)
+            : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(a[4]), "r"(b[0]), "r"(b[1]), "r"(b[2]), "r"(b[3]), "r"(b[4]));
+        r[0] = r0;
+        r[1] = r1;
+        r[2] = r2;
+        r[3] = r3;
+        r[4] = r4;
+    } else if (N == 3) {
+        uint32_t r0, r1, r2;
+        asm("add.cc.u32 %0, %4, %7;\n\t"
+            "addc.cc.u32 %1, %5, %8;\n\t"
+            "addc.cc.u32 %2, %6, %9;\n\t"
+            "addc.u32 %3, 0, 0;"
+            : "=r"(r0), "=r"(r1), "=r"(r2), "=r"(c)
+            : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(b[0]), "r"(b[1]), "r"(b[2]));
+        r[0] = r0;
+        r[1] = r1;
+        r[2] = r2;
+    } else {
+        uint32_t r0, r1;
+        asm("add.cc.u32 %0, %3, %5;\n\t"
+            "addc.cc.u32 %1, %4, %6;\n\t"
+            "addc.u32 %2, 0, 0;"
+            : "=r"(r0), "=r"(r1), "=r"(c)
+            : "r"(a[0]), "r"(a[1]), "r"(b[0]), "r"(b[1]));
+        r[0] = r0;
+        r[1] = r1;
+    }
+#else
+    uint64_t t = 0;
+    for (int i = 0; i < N; i++) {
+        t += (uint64_t)a[i] + b[i];
+        r[i] = (uint32_t)t;
+        t >>= 32;
+    }
+    c = (uint32_t)t;
+#endif
+    return c;
+}
+// r = a - b, returns borrow (0/1)
+template <int N>
+BCP_DEV uint32_t subn_cc(uint32_t *r, const uint32_t *a, const uint32_t *b) {
+    uint32_t c;
+#if BCP_PTX
+    static_assert(N == 8 || N == 2, "unsupported chain length");
+    if (N == 8) {
+        uint32_t r0, r1, r2, r3, r4, r5, r6, r7;
+        asm("sub.cc.u32 %0, %9, %17;\n\t"
+            "subc.cc.u32 %1, %10, %18;\n\t"
+            "subc.cc.u32 %2, %11, %19;\n\t"
+            "subc.cc.u32 %3, %12, %20;\n\t"
+            "subc.cc.u32 %4, %13, %21;\n\t"
+            "subc.cc.u32 %5, %14, %22;\n\t"
+            "subc.cc.u32 %6, %15, %23;\n\t"
+            "subc.cc.u32 %7, %16, %24;\n\t"
+            "subc.u32 %8, 0, 0;"
+            : "=r"(r0), "=r"(r1), "=r"(r2), "=r"(r3), "=r"(r4), "=r"(r5), "=r"(r6), "=r"(r7), "=r"(c)
+            : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(a[4]), "r"(a[5]), "r"(a[6]), "r"(a[7]), "r"(b[0]), "r"(b[1]), "r"(b[2]), "r"(b[3]), "r"(b[4]), "r"(b[5]), "r"(b[6]), "r"(b[7]));
+        r[0] = r0;
+        r[1] = r1;
+        r[2] = r2;
+        r[3] = r3;
+        r[4] = r4;
+        r[5] = r5;
+        r[6] = r6;
+        r[7] = r7;
+    } else {
+        uint32_t r0, r1;
+        asm("sub.cc.u32 %0, %3, %5;\n\t"
+            "subc.cc.u32 %1, %4, %6;\n\t"
+            "subc.u32 %2, 0, 0;"
+            : "=r"(r0), "=r"(r1), "=r"(c)
+            : "r"(a[0]), "r"(a[1]), "r"(b[0]), "r"(b[1]));
+        r[0] = r0;
+        r[1] = r1;
+    }
+    c &= 1u; /* subc 0 - 0 - borrow gives 0 or 0xFFFFFFFF */
+#else
+    uint64_t br = 0;
+    for (int i = 0; i < N; i++) {
+        uint64_t t = (uint64_t)a[i] - b[i] - br;
+        r[i] = (uint32_t)t;
+        br = (t >> 32) & 1;
+    }
+    c = (uint32_t)br;
+#endif
+    return c;
+}
+
+// ------------------------------------------------------------------ 256x256 -> 512
+BCP_DEV void mul_wide(uint32_t *r /*16*/, const uint32_t *a, const uint32_t *b) {
+    uint32_t E[16], O[16]; /* E[k] sits at limb k, O[k] at limb k+1 */
+    row_set(E, a[0], a[2], a[4], a[6], b[0]);
+    row_set(O, a[1], a[3], a[5], a[7], b[0]);
+    BCP_UNROLL
+    for (int k = 8; k < 16; k++) { E[k] = 0; O[k] = 0; }
+    BCP_UNROLL
+    for (int i = 1; i < 8; i++) {
+        if (i & 1) {
+            row_acc9(O + i - 1, a[0], a[2], a[4], a[6], b[i]);
+            if (i < 7) row_acc9(E + i + 1, a[1], a[3], a[5], a[7], b[i]);
+            else row_acc8(E + 8, a[1], a[3], a[5], a[7], b[i]);
+        } else {
+            row_acc9(E + i, a[0], a[2], a[4], a[6], b[i]);
+            row_acc9(O + i, a[1], a[3], a[5], a[7], b[i]);
+        }
+    }
+    r[0] = E[0];
+#if BCP_PTX
+    asm("add.cc.u32 %0, %15, %30;\n\t"
+        "addc.cc.u32 %1, %16, %31;\n\t"
+        "addc.cc.u32 %2, %17, %32;\n\t"
+        "addc.cc.u32 %3, %18, %33;\n\t"
+        "addc.cc.u32 %4, %19, %34;\n\t"
+        "addc.cc.u32 %5, %20, %35;\n\t"
+        "addc.cc.u32 %6, %21, %36;\n\t"
+        "addc.cc.u32 %7, %22, %37;\n\t"
+        "addc.cc.u32 %8, %23, %38;\n\t"
+        "addc.cc.u32 %9, %24, %39;\n\t"
+        "addc.cc.u32 %10, %25, %40;\n\t"
+        "addc.cc.u32 %11, %26, %41;\n\t"
+        "addc.cc.u32 %12, %27, %42;\n\t"
+        "addc.cc.u32 %13, %28, %43;\n\t"
+        "addc.u32 %14, %29, %44;"
+        : "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]), "=r"(r[8]), "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15])
+        : "r"(E[1]), "r"(E[2]), "r"(E[3]), "r"(E[4]), "r"(E[5]), "r"(E[6]), "r"(E[7]), "r"(E[8]), "r"(E[9]), "r"(E[10]), "r"(E[11]), "r"(E[12]), "r"(E[13]), "r"(E[14]), "r"(E[15]), "r"(O[0]), "r"(O[1]), "r"(O[2]), "r"(O[3]), "r"(O[4]), "r"(O[5]), "r"(O[6]), "r"(O[7]), "r"(O[8]), "r"(O[9]), "r"(O[10]), "r"(O[11]), "r"(O[12]), "r"(O[13]), "r"(O[14]));
+#else
+    uint64_t t = 0;
+    for (int k = 1; k < 16; k++) {
+        t += (uint64_t)E[k] + O[k - 1];
+        r[k] = (uint32_t)t;
+        t >>= 32;
+    }
+#endif
+}
+
+// ------------------------------------------------------------------ 512 -> [0, 2^256) mod p
+BCP_DEV void fe_reduce_wide(fe &r, const uint32_t *t /*16*/) {
+    // first fold: S = L + H*977 + (H << 32), accumulated in place as two interleaved arrays
+    uint32_t EV[9], OD[9];
+    BCP_UNROLL
+    for (int k = 0; k < 8; k++) { EV[k] = t[k]; OD[k] = t[8 + k]; }
+    EV[8] = 0; OD[8] = 0;
+    row_acc9(EV, t[8], t[10], t[12], t[14], BCP_FOLD);  /* limbs (0,1),(2,3),(4,5),(6,7) += H_even*977        */
+    row_acc9(OD, t[9], t[11], t[13], t[15], BCP_FOLD);  /* OD sits at limb 1: (H << 32) + H_odd*977 << 32      */
+    uint32_t s[10];
+    s[0] = EV[0];
+    s[9] = OD[8] + addn_cc<8>(s + 1, EV + 1, OD);       /* S < 2^290, so s[9] <= 3 and s[9]:s[8] < 2^34      */
+    // second fold: T = s[9]:s[8];  S' = s[0..7] + T*977 + (T << 32)
+    uint64_t m = (uint64_t)s[8] * BCP_FOLD + ((uint64_t)(s[9] * BCP_FOLD) << 32);
+    uint64_t a1 = (m >> 32) + s[8];
+    uint32_t A[8] = {(uint32_t)m, (uint32_t)a1, s[9] + (uint32_t)(a1 >> 32), 0, 0, 0, 0, 0};
+    uint32_t c = addn_cc<8>(r.v, s, A);
+    // third fold: a carry means S' wrapped past 2^256 (== 2^32+977); the wrapped value is < 2^67,
+    // so only limbs 0..2 can change and no further wrap is possible
+    uint32_t B[3] = {c * BCP_FOLD, c, 0};
+    addn_cc<3>(r.v, r.v, B);
+}
+
+BCP_DEV void fe_mul(fe &r, const fe &a, const fe &b) {
+    uint32_t t[16];
+    mul_wide(t, a.v, b.v);
+    fe_reduce_wide(r, t);
+}
+#ifndef BCP_FE_SQR_DEDICATED
+BCP_DEV void fe_sqr(fe &r, const fe &a) { fe_mul(r, a, a); }
+#endif
+
+// ------------------------------------------------------------------ add / sub / neg (weakly reduced in and out)
+BCP_DEV void fe_add(fe &r, const fe &a, const fe &b) {
+    uint32_t c = addn_cc<8>(r.v, a.v, b.v);
+    // a + b - 2^256 == a + b - 2^256 + (2^32 + 977) (mod p)
+    uint32_t A[8] = {c * BCP_FOLD, c, 0, 0, 0, 0, 0, 0};
+    uint32_t c2 = addn_cc<8>(r.v, r.v, A);
+    // a second wrap needs both inputs within 2^33 of 2^256; afterwards the value is < 2^34
+    uint32_t B[2] = {c2 * BCP_FOLD, c2};
+    addn_cc<2>(r.v, r.v, B);
+}
+BCP_DEV void fe_sub(fe &r, const fe &a, const fe &b) {
+    uint32_t bw = subn_cc<8>(r.v, a.v, b.v);
+    // a - b + 2^256 == a - b + 2^256 - (2^32 + 977) (mod p)
+    uint32_t A[8] = {bw * BCP_FOLD, bw, 0, 0, 0, 0, 0, 0};
+    uint32_t bw2 = subn_cc<8>(r.v, r.v, A);
+    // second borrow: value is now within 2^34 of 2^256, subtracting again cannot borrow
+    uint32_t B[2] = {bw2 * BCP_FOLD, bw2};
+    subn_cc<2>(r.v, r.v, B);
+}
+BCP_DEV void fe_set_zero(fe &r) {
+    BCP_UNROLL
+    for (int i = 0; i < 8; i++) r.v[i] = 0;
+}
+BCP_DEV void fe_set_u32(fe &r, uint32_t x) {
+    fe_set_zero(r);
+    r.v[0] = x;
+}
+BCP_DEV void fe_neg(fe &r, const fe &a) {
+    fe z;
+    fe_set_zero(z);
+    fe_sub(r, z, a);
+}
+BCP_DEV void fe_dbl(fe &r, const fe &a) { fe_add(r, a, a); }
+
+// canonical representative in [0, p)
+BCP_DEV void fe_normalize(fe &a) {
+    // a >= p  <=>  a + (2^32 + 977) >= 2^256
+    uint32_t A[8] = {BCP_FOLD, 1, 0, 0, 0, 0, 0, 0}, t[8];
+    uint32_t c = addn_cc<8>(t, a.v, A);
+    BCP_UNROLL
+    for (int i = 0; i < 8; i++) a.v[i] = c ? t[i] : a.v[i];
+}
+// value == 0 (mod p) for a weakly reduced element: a == 0 or a == p
+BCP_DEV bool fe_is_zero(const fe &a) {
+    uint32_t z = a.v[0] | a.v[1] | a.v[2] | a.v[3] | a.v[4] | a.v[5] | a.v[6] | a.v[7];
+    uint32_t q = (a.v[0] ^ BCP_P0) | (a.v[1] ^ BCP_P1) | ~(a.v[2] & a.v[3] & a.v[4] & a.v[5] & a.v[6] & a.v[7]);
+    return z == 0 || q == 0;
+}
+BCP_DEV bool fe_equal(const fe &a, const fe &b) {
+    fe d;
+    fe_sub(d, a, b);
+    return fe_is_zero(d);
+}
+BCP_DEV bool fe_is_odd_normalized(const fe &a) { return a.v[0] & 1u; }
+
+// big-endian 32 bytes -> limbs; returns false when the value is >= p (fe_set_b32, field_10x26_impl.h:323-338)
+BCP_DEV bool fe_set_b32(fe &r, const uint8_t *b) {
+    BCP_UNROLL
+    for (int i = 0; i < 8; i++) {
+        const uint8_t *q = b + 4 * (7 - i);
+        r.v[i] = ((uint32_t)q[0] << 24) | ((uint32_t)q[1] << 16) | ((uint32_t)q[2] << 8) | q[3];
+    }
+    bool top = (r.v[2] & r.v[3] & r.v[4] & r.v[5] & r.v[6] & r.v[7]) == 0xFFFFFFFFu;
+    bool ge = top && (r.v[1] == 0xFFFFFFFFu || (r.v[1] == BCP_P1 && r.v[0] >= BCP_P0));
+    return !ge;
+}
+
+// r = a^(2^n)
+BCP_DEV void fe_sqrn(fe &r, const fe &a, int n) {
+    r = a;
+#if BCP_PTX
+#pragma unroll 1
+#endif
+    for (int i = 0; i < n; i++) fe_sqr(r, r);
+}
+// candidate square root a^((p+1)/4); the caller checks r^2 == a (fe_sqrt, field_impl.h:38-134).
+// (p+1)/4 = 2^254 - 2^30 - 244 has the bit pattern 1^223 0 1^22 0000 11 00, hence the chain below
+// (x_k = a^(2^k - 1)).
+BCP_DEV void fe_sqrt_candidate(fe &r, const fe &a) {
+    fe x2, x3, x6, x9, x11, x22, x44, x88, x176, x220, x223, t;
+    fe_sqr(t, a); fe_mul(x2, t, a);
+    fe_sqr(t, x2); fe_mul(x3, t, a);
+    fe_sqrn(t, x3, 3); fe_mul(x6, t, x3);
+    fe_sqrn(t, x6, 3); fe_mul(x9, t, x3);
+    fe_sqrn(t, x9, 2); fe_mul(x11, t, x2);
+    fe_sqrn(t, x11, 11); fe_mul(x22, t, x11);
+    fe_sqrn(t, x22, 22); fe_mul(x44, t, x22);
+    fe_sqrn(t, x44, 44); fe_mul(x88, t, x44);
+    fe_sqrn(t, x88, 88); fe_mul(x176, t, x88);
+    fe_sqrn(t, x176, 44); fe_mul(x220, t, x44);
+    fe_sqrn(t, x220, 3); fe_mul(x223, t, x3);
+    fe_sqrn(t, x223, 23); fe_mul(t, t, x22);
+    fe_sqrn(t, t, 6); fe_mul(t, t, x2);
+    fe_sqrn(r, t, 2);
+}
+// a^(p-2) (only used by one-time table generation)
+BCP_DEV void fe_inv(fe &r, const fe &a) {
+    // p - 2 = 1^223 0 1^22 0000 101101
+    fe x2, x3, x6, x9, x11, x22, x44, x88, x176, x220, x223, t;
+    fe_sqr(t, a); fe_mul(x2, t, a);
+    fe_sqr(t, x2); fe_mul(x3, t, a);
+    fe_sqrn(t, x3, 3); fe_mul(x6, t, x3);
+    fe_sqrn(t, x6, 3); fe_mul(x9, t, x3);
+    fe_sqrn(t, x9, 2); fe_mul(x11, t, x2);
+    fe_sqrn(t, x11, 11); fe_mul(x22, t, x11);
+    fe_sqrn(t, x22, 22); fe_mul(x44, t, x22);
+    fe_sqrn(t, x44, 44); fe_mul(x88, t, x44);
+    fe_sqrn(t, x88, 88); fe_mul(x176, t, x88);
+    fe_sqrn(t, x176, 44); fe_mul(x220, t, x44);
+    fe_sqrn(t, x220, 3); fe_mul(x223, t, x3);
+    fe_sqrn(t, x223, 23); fe_mul(t, t, x22);
+    fe_sqrn(t, t, 5); fe_mul(t, t, a);
+    fe_sqrn(t, t, 3); fe_mul(t, t, x2);
+    fe_sqrn(t, t, 2); fe_mul(r, t, a);
+}

@@ -1,0 +1,125 @@
+// ge.cuh — secp256k1 group law in Jacobian coordinates for sm_100a (y^2 = x^3 + 7, a = 0).
+//
+// Same maps as the reference's src/secp256k1/src/group_impl.h — gej_double_var (:301-354),
+// gej_add_ge_var (:414-461) with its degenerate branches (P==Q -> double :438-441, P==-Q -> infinity
+// :442-447, infinity operands :417-421), ge_set_xo_var (:216-237), ge_is_valid_var (:287-299) — on the
+// 8x32 weakly-reduced field of fe.cuh.  Results (as group elements) are identical; limb layout
+// and evaluation order are this project's own.
+#pragma once
+#include "fe.cuh"
+
+struct gej {
+    fe x, y, z;
+    bool inf;
+};
+
+BCP_CONST uint32_t FE_BETA[8] = {0x719501eeu, 0xc1396c28u, 0x12f58995u, 0x9cf04975u,
+                                 0xac3434e9u, 0x6e64479eu, 0x657c0710u, 0x7ae96a2bu};
+BCP_CONST uint32_t FE_GX[8] = {0x16f81798u, 0x59f2815bu, 0x2dce28d9u, 0x029bfcdbu,
+                               0xce870b07u, 0x55a06295u, 0xf9dcbbacu, 0x79be667eu};
+BCP_CONST uint32_t FE_GY[8] = {0xfb10d4b8u, 0x9c47d08fu, 0xa6855419u, 0xfd17b448u,
+                               0x0e1108a8u, 0x5da4fbfcu, 0x26a3c465u, 0x483ada77u};
+
+// r = 2a.  3M + 4S.  (No point of order two exists on this curve, so y = 0 never occurs for a
+// finite point and the only special case is infinity, :320-326.)
+BCP_DEV void gej_double(gej &r, const gej &a) {
+    if (a.inf) { r = a; return; }
+    fe t, A, B, C, S, M;
+    fe_mul(t, a.y, a.z);
+    fe_sqr(A, a.x);
+    fe_sqr(B, a.y);
+    fe_dbl(r.z, t);                 /* Z3 = 2YZ */
+    fe_dbl(M, A); fe_add(M, M, A);  /* M = 3X^2 */
+    fe_mul(S, a.x, B);
+    fe_dbl(S, S); fe_dbl(S, S);     /* S = 4XY^2 */
+    fe_sqr(C, B);
+    fe_dbl(C, C); fe_dbl(C, C); fe_dbl(C, C); /* 8Y^4 */
+    fe_sqr(t, M);
+    fe_sub(t, t, S); fe_sub(r.x, t, S);       /* X3 = M^2 - 2S */
+    fe_sub(t, S, r.x);
+    fe_mul(t, M, t);
+    fe_sub(r.y, t, C);              /* Y3 = M(S - X3) - 8Y^4 */
+    r.inf = false;
+}
+
+// a += (bx, by) with (bx, by) affine and finite.  8M + 3S.  If rzr != nullptr it receives the
+// ratio Z3/Z1 (only meaningful on the generic path; table construction never hits the others).
+BCP_DEV void gej_add_ge(gej &a, const fe &bx, const fe &by, fe *rzr) {
+    if (a.inf) {
+        a.x = bx; a.y = by;
+        fe_set_u32(a.z, 1);
+        a.inf = false;
+        return;
+    }
+    fe z2, u2, s2, h, rr, h2, h3, v, t;
+    fe_sqr(z2, a.z);
+    fe_mul(u2, bx, z2);
+    fe_mul(t, a.z, z2);
+    fe_mul(s2, by, t);
+    fe_sub(h, u2, a.x);
+    fe_sub(rr, s2, a.y);
+    if (fe_is_zero(h)) {
+        if (fe_is_zero(rr)) {
+            gej d = a;
+            gej_double(a, d);
+        } else {
+            a.inf = true;
+        }
+        return;
+    }
+    if (rzr) *rzr = h;
+    fe_sqr(h2, h);
+    fe_mul(h3, h2, h);
+    fe_mul(v, a.x, h2);
+    fe_mul(a.z, a.z, h);
+    fe_sqr(t, rr);
+    fe_sub(t, t, h3); fe_sub(t, t, v); fe_sub(a.x, t, v); /* X3 = R^2 - H^3 - 2V */
+    fe_sub(t, v, a.x);
+    fe_mul(t, t, rr);
+    fe_mul(h3, h3, a.y);
+    fe_sub(a.y, t, h3);                                    /* Y3 = R(V - X3) - Y1 H^3 */
+}
+
+// y^2 == x^3 + 7 ?
+BCP_DEV bool ge_on_curve(const fe &x, const fe &y) {
+    fe l, r, seven;
+    fe_sqr(l, y);
+    fe_sqr(r, x);
+    fe_mul(r, r, x);
+    fe_set_u32(seven, 7);
+    fe_add(r, r, seven);
+    return fe_equal(l, r);
+}
+
+// secp256k1_eckey_pubkey_parse (eckey_impl.h:17-35): 33-byte 02/03 -> decompress (x < p, residue test,
+// parity), 65-byte 04/06/07 -> range + (hybrid) parity + curve check.  `len` is decided by the caller
+// from the prefix byte as CPubKey does (src/pubkey.h:47-51).  Outputs a normalized affine point.
+BCP_DEV bool pubkey_parse(fe &qx, fe &qy, const uint8_t *pub) {
+    uint8_t pre = pub[0];
+    if (pre == 2 || pre == 3) {
+        if (!fe_set_b32(qx, pub + 1)) return false;
+        fe c, seven, y, chk;
+        fe_sqr(c, qx);
+        fe_mul(c, c, qx);
+        fe_set_u32(seven, 7);
+        fe_add(c, c, seven);
+        fe_sqrt_candidate(y, c);
+        fe_sqr(chk, y);
+        if (!fe_equal(chk, c)) return false;
+        fe_normalize(y);
+        fe ny;
+        fe_neg(ny, y);
+        fe_normalize(ny);
+        bool flip = (bool)(y.v[0] & 1u) != (pre == 3);
+        BCP_UNROLL
+        for (int i = 0; i < 8; i++) qy.v[i] = flip ? ny.v[i] : y.v[i];
+        return true;
+    }
+    if (pre == 4 || pre == 6 || pre == 7) {
+        if (!fe_set_b32(qx, pub + 1)) return false;
+        if (!fe_set_b32(qy, pub + 33)) return false;
+        if (pre != 4 && ((bool)(qy.v[0] & 1u) != (pre == 7))) return false;
+        return ge_on_curve(qx, qy);
+    }
+    return false;
+}

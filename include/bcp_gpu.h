@@ -1,0 +1,134 @@
+/* bcp_gpu.h — C ABI of libbcp_b200.so: the B200 (sm_100a) block-validation hot path.
+ *
+ * This is the "B4" boundary of SURVEY.md §8(b): thin extern "C" entry points that take a whole
+ * batch (all inputs of a block, all headers of a sync window) in plain host or device buffers.
+ * The reference-side shims that call them — include/compat/secp256k1.h (same-name libsecp256k1
+ * C API), include/compat/checkqueue.h (CCheckQueue drop-in) — and the cgo/ctypes-style stubs a
+ * maintainer would add are shown in INTEGRATION.md.
+ *
+ * Conventions
+ *   - every function returns BCP_OK (0) or a negative BCP_ERR_* code; a verdict is NEVER produced on
+ *     error (no CPU fallback exists: without a CUDA device every call fails with BCP_ERR_NO_DEVICE);
+ *   - `device` is a CUDA ordinal; bcp_gpu_init(device) must have succeeded for it;
+ *   - "_dev" variants take DEVICE pointers and a cudaStream_t (as void*), enqueue work and do not
+ *     synchronise; the plain variants take HOST pointers (pinned memory from bcp_gpu_host_alloc gives
+ *     full PCIe bandwidth; pageable memory works, slower), copy in, run, copy out and synchronise;
+ *   - one context per device; calls on the same device are serialised by an internal mutex, calls
+ *     on different devices run concurrently (shard a block's inputs across devices by index range and
+ *     AND the verdicts on the host, like `fAllOk &= fOk` in src/checkqueue.h:77 — no NCCL is involved).
+ */
+#ifndef BCP_GPU_H
+#define BCP_GPU_H
+#include <stddef.h>
+#include <stdint.h>
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#if defined(__GNUC__)
+#define BCP_API __attribute__((visibility("default")))
+#else
+#define BCP_API
+#endif
+
+#define BCP_OK 0
+#define BCP_ERR_NO_DEVICE (-1)   /* no CUDA device / driver, or device ordinal out of range */
+#define BCP_ERR_CUDA (-2)        /* a CUDA runtime call failed: see bcp_gpu_last_error()     */
+#define BCP_ERR_NOT_INIT (-3)    /* bcp_gpu_init(device) has not been called                 */
+#define BCP_ERR_INVALID (-4)     /* bad argument (NULL buffer, size beyond a stated limit)   */
+
+/* flag for the ECDSA entry points: normalise a high s (s := n - s) instead of rejecting it, which is
+ * what CPubKey::Verify does before calling libsecp256k1 (src/pubkey.cpp:186-191).  Without the flag
+ * the verdict is that of a bare secp256k1_ecdsa_verify (src/secp256k1/src/secp256k1.c:293-308). */
+#define BCP_ECDSA_FLAG_NORMALIZE_S 1u
+
+/* ---- life cycle ------------------------------------------------------------------------------- */
+/* Number of usable CUDA devices (0 when there is no driver/GPU). */
+BCP_API int bcp_gpu_device_count(void);
+/* Create the per-device context: stream, fixed-base comb table for G (generated on the device; the
+ * counterpart of secp256k1_ecmult_context_build, src/secp256k1/src/ecmult_impl.h:164-194, which
+ * secp256k1_context_create(SECP256K1_CONTEXT_VERIFY) runs, src/secp256k1/src/secp256k1.c:59-83).
+ * Idempotent. */
+BCP_API int bcp_gpu_init(int device);
+/* Destroy it (secp256k1_context_destroy, secp256k1.c:96-105). */
+BCP_API int bcp_gpu_shutdown(int device);
+/* Text of the last error on the calling thread. */
+BCP_API const char *bcp_gpu_last_error(void);
+/* Pinned host memory for staging buffers (what "pinned buffers" in the north star refers to). */
+BCP_API void *bcp_gpu_host_alloc(size_t bytes);
+BCP_API void bcp_gpu_host_free(void *p);
+
+/* ---- ECDSA: replaces the per-input work of CPubKey::Verify (src/pubkey.cpp:170-193) ==
+ *      secp256k1_ec_pubkey_parse (secp256k1.c:150) + secp256k1_ecdsa_signature_parse_compact (:228)
+ *      [+ _normalize (:274)] + secp256k1_ecdsa_verify (:293), for n signatures at once.
+ *   msg32  n x 32  sighash digests, raw bytes as uint256::begin() passes them (pubkey.cpp:191)
+ *   pub65  n x 65  serialized public keys, each left-aligned in a 65-byte slot; the length is implied
+ *                  by the first byte exactly as CPubKey::GetLen does (src/pubkey.h:47-51): 02/03 -> 33,
+ *                  04/06/07 -> 65, anything else -> invalid key -> verdict 0
+ *   sig64  n x 64  r || s big-endian (the output of the lax DER parser, see bcp_der_lax_parse)
+ *   ok     n       verdict bytes, 1 = valid, 0 = invalid
+ */
+BCP_API int bcp_gpu_ecdsa_verify_batch(int device, const uint8_t *msg32, const uint8_t *pub65, const uint8_t *sig64,
+                               size_t n, uint32_t flags, uint8_t *ok);
+BCP_API int bcp_gpu_ecdsa_verify_batch_dev(int device, const uint8_t *d_msg32, const uint8_t *d_pub65,
+                                   const uint8_t *d_sig64, size_t n, uint32_t flags, uint8_t *d_ok, void *stream);
+/* Bytes of device scratch bcp_gpu_ecdsa_verify_batch_dev needs for n signatures (it grows the
+ * context's scratch buffer on demand; calling this first with the largest n avoids a reallocation
+ * inside a timed region). */
+BCP_API size_t bcp_gpu_ecdsa_scratch_bytes(size_t n);
+BCP_API int bcp_gpu_ecdsa_reserve(int device, size_t n);
+
+/* Host-side byte parsing that stays on the CPU by design (branchy, a few dozen bytes):
+ * ecdsa_signature_parse_der_lax (src/pubkey.cpp:26-168).  Returns 1 and writes r||s (zeros when a
+ * component overflows, which later verifies as invalid), or 0 on a structural failure. */
+BCP_API int bcp_der_lax_parse(const uint8_t *der, size_t len, uint8_t sig64[64]);
+
+/* ---- SHA-256d: transaction ids, Merkle root, header hashes ---------------------------------------
+ * Host-side framing scan (sequential byte parsing, stays on the CPU by design): fills tx_off[0..ntx]
+ * with the byte offset of every transaction of a serialized block (tx_off[ntx] = end), following
+ * ReadCompactSize (src/serialize.h:260-300), UnserializeTransaction (src/primitives/transaction.h:223-234)
+ * and the header layout (src/primitives/block.h:49-73; legacy_header = 1 for the 80-byte format).
+ * Returns ntx, -1 on malformed input, -2 if ntx > max_tx. */
+BCP_API long bcp_block_index(const uint8_t *blk, size_t len, int legacy_header, uint32_t *tx_off, size_t max_tx);
+/* txid[i] = SHA256d(blk[tx_off[i] .. tx_off[i+1])) for every transaction — CTransaction::ComputeHash
+ * (src/primitives/transaction.cpp:73-75) — then BlockMerkleRoot (src/consensus/merkle.cpp:175-182):
+ * root32 and the CVE-2012-2459 `mutated` flag exactly as ComputeMerkleRoot (:47-150) reports them
+ * (ntx == 0 gives a zero root).  txids may be NULL. */
+BCP_API int bcp_gpu_sha256d_txids_merkle(int device, const uint8_t *blk, size_t len, const uint32_t *tx_off, size_t ntx,
+                                         uint8_t *txids, uint8_t root32[32], int *mutated);
+/* ComputeMerkleRoot (src/consensus/merkle.cpp:146-150) over n 32-byte leaves. */
+BCP_API int bcp_gpu_merkle_root(int device, const uint8_t *leaves32, size_t n, uint8_t root32[32], int *mutated);
+/* out32[i] = SHA256d(data[off[i] .. off[i+1])) — CHash256 (src/hash.h:21-43) over a batch of messages. */
+BCP_API int bcp_gpu_sha256d_batch(int device, const uint8_t *data, size_t len, const uint32_t *off, size_t count,
+                                  uint8_t *out32);
+/* Device-pointer forms (enqueue only).  d_data must be 4-byte aligned and readable 4 bytes past its end. */
+BCP_API int bcp_gpu_sha256d_batch_dev(int device, const uint8_t *d_data, const uint32_t *d_off, size_t count,
+                                      uint8_t *d_out32, void *stream);
+BCP_API size_t bcp_gpu_merkle_scratch_bytes(size_t n);
+BCP_API int bcp_gpu_merkle_root_dev(int device, const uint8_t *d_leaves32, size_t n, uint8_t *d_root32, int *d_mutated,
+                                    void *d_scratch, void *stream);
+
+/* ---- Equihash: CheckEquihashSolution (src/pow.cpp:298-323) == Equihash<N,K>::IsValidSolution
+ *      (src/crypto/equihash.cpp:724-770) for `count` serialized post-fork headers (140 bytes || compact
+ *      size || solution; src/primitives/block.h:49-73) laid out at `stride` bytes, each `hdr_len` long.
+ *      (n,k) in {(200,9) main/test, (48,5) regtest, (96,5), (96,3)} as src/crypto/equihash.h:196-272.
+ *   ok      count verdict bytes
+ *   hash32  optional: SHA-256d of each header's hdr_len bytes = CBlockHeader::GetHash
+ *           (src/primitives/block.cpp:17-28), raw digest byte order (uint256 memory order) */
+BCP_API int bcp_gpu_equihash_verify_batch(int device, unsigned n, unsigned k, const uint8_t *hdrs, size_t stride,
+                                          size_t hdr_len, size_t count, uint8_t *ok, uint8_t *hash32);
+BCP_API size_t bcp_gpu_equihash_scratch_bytes(size_t count);
+BCP_API int bcp_gpu_equihash_verify_batch_dev(int device, unsigned n, unsigned k, const uint8_t *d_hdrs, size_t stride,
+                                              size_t hdr_len, size_t count, uint8_t *d_ok, void *d_scratch,
+                                              void *stream);
+
+/* ---- measurement helper: integer-pipe peak (SURVEY.md §8d asks the build to measure it) ----------
+ * Runs a dependency-free IMAD.WIDE.U32 loop on every SM and returns 32x32->64 multiply-adds per second
+ * (which == 0), the carry-chained form mad.lo.cc/madc.hi.cc used by the field code (which == 1), or
+ * IADD3-class adds per second (which == 2). */
+BCP_API int bcp_gpu_measure_int_peak(int device, int which, double *ops_per_second);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

@@ -1,0 +1,219 @@
+"""Deterministic synthetic inputs for the hot path, shared by tests/ and bench.py.
+
+Signature sets come from the ORACLE's RFC 6979 signer (bit-identical to the reference's
+secp256k1_ecdsa_sign — pinned by tests/test_oracle_pinning.py), so this module is test/bench
+infrastructure and is never imported by the product package.
+"""
+import hashlib
+import os
+import sys
+
+import numpy as np
+
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+from oracle import pyoracle as po  # noqa: E402
+
+SEED = b"bcp-b200-v1"
+P = 2**256 - 2**32 - 977
+N = 0xFFFFFFFFFFFFFFFFFFFFFFFFFFFFFFFEBAAEDCE6AF48A03BBFD25E8CD0364141
+
+CORRUPTIONS = [
+    "flip_r", "flip_s", "flip_msg", "swap_pubkey", "high_s", "r_zero", "s_zero", "r_eq_n", "s_eq_n_plus_1",
+    "pub_x_ge_p", "pub_x_nonresidue", "prefix_05", "hybrid_ok", "hybrid_bad_parity", "msg_plus_n",
+    "uncompressed_off_curve", "prefix_00", "r_eq_n_minus_1", "s_eq_half_n", "s_eq_half_n_plus_1",
+]
+
+
+def prng(i, tag=b"prng"):
+    return int.from_bytes(hashlib.sha256(SEED + tag + i.to_bytes(8, "little")).digest(), "little")
+
+
+def _be(x):
+    return np.frombuffer(x.to_bytes(32, "big"), dtype=np.uint8)
+
+
+def sigset(n, nkeys=4096, corrupt_pct=1, nthreads=None):
+    """n signatures (msg32 (n,32), pub65 (n,65), sig64 (n,64)) with ~corrupt_pct % corrupted entries cycling
+    through CORRUPTIONS.  Returns (msg, pub, sig, kinds) where kinds[i] is -1 or the corruption index."""
+    o = po.oracle()
+    msg, pub, sig = o.gen_sigset(n, nkeys=nkeys, seed=SEED, nthreads=nthreads)
+    kinds = np.full(n, -1, dtype=np.int32)
+    if corrupt_pct <= 0:
+        return msg, pub, sig, kinds
+    period = max(1, 100 // corrupt_pct)
+    c = 0
+    for i in range(n):
+        if prng(i) % period != 0:
+            continue
+        kind = c % len(CORRUPTIONS)
+        c += 1
+        kinds[i] = kind
+        apply_corruption(CORRUPTIONS[kind], i, msg, pub, sig, nkeys)
+    return msg, pub, sig, kinds
+
+
+def apply_corruption(name, i, msg, pub, sig, nkeys):
+    bit = prng(i, b"bit")
+    if name == "flip_r":
+        sig[i, (bit >> 3) % 32] ^= 1 << (bit & 7)
+    elif name == "flip_s":
+        sig[i, 32 + (bit >> 3) % 32] ^= 1 << (bit & 7)
+    elif name == "flip_msg":
+        msg[i, (bit >> 3) % 32] ^= 1 << (bit & 7)
+    elif name == "swap_pubkey":
+        j = (i + 1) % len(pub)
+        if (j % nkeys) == (i % nkeys):
+            j = (i + 2) % len(pub)
+        pub[i] = pub[j]
+    elif name == "high_s":
+        s = int.from_bytes(sig[i, 32:].tobytes(), "big")
+        sig[i, 32:] = _be(N - s)
+    elif name == "r_zero":
+        sig[i, :32] = 0
+    elif name == "s_zero":
+        sig[i, 32:] = 0
+    elif name == "r_eq_n":
+        sig[i, :32] = _be(N)
+    elif name == "s_eq_n_plus_1":
+        sig[i, 32:] = _be(N + 1)
+    elif name == "r_eq_n_minus_1":
+        sig[i, :32] = _be(N - 1)
+    elif name == "s_eq_half_n":
+        sig[i, 32:] = _be(N // 2)
+    elif name == "s_eq_half_n_plus_1":
+        sig[i, 32:] = _be(N // 2 + 1)
+    elif name == "pub_x_ge_p":
+        pub[i, :] = 0
+        pub[i, 0] = 2
+        pub[i, 1:33] = _be(P + (bit % 900))
+    elif name == "pub_x_nonresidue":
+        x = bit % P
+        while pow((x**3 + 7) % P, (P - 1) // 2, P) == 1:
+            x += 1
+        pub[i, :] = 0
+        pub[i, 0] = 2 + (bit & 1)
+        pub[i, 1:33] = _be(x)
+    elif name == "prefix_05":
+        pub[i, 0] = 5
+    elif name == "prefix_00":
+        pub[i, 0] = 0
+    elif name in ("hybrid_ok", "hybrid_bad_parity", "uncompressed_off_curve"):
+        o = po.oracle()
+        ok, xy = o.pubkey_parse(pub[i, : 33 if pub[i, 0] in (2, 3) else 65].tobytes())
+        assert ok
+        y_odd = xy[63] & 1
+        pub[i, 1:] = np.frombuffer(xy, dtype=np.uint8)
+        if name == "hybrid_ok":
+            pub[i, 0] = 7 if y_odd else 6
+        elif name == "hybrid_bad_parity":
+            pub[i, 0] = 6 if y_odd else 7
+        else:
+            pub[i, 0] = 4
+            pub[i, 64] ^= 1
+    elif name == "msg_plus_n":
+        m = int.from_bytes(msg[i].tobytes(), "big")
+        if m + N < 2**256:
+            msg[i] = _be(m + N)  # reduced silently mod n: still VALID
+    else:
+        raise ValueError(name)
+
+
+def edge_cases():
+    """Hand-built adversarial cases beyond random corruption: tiny/huge scalars, r in the r+n<p band
+    handled generically by differential testing.  Returns (msg, pub, sig)."""
+    o = po.oracle()
+    rows = []
+    for sk in [1, 2, 3, N - 1, N - 2, (N + 1) // 2, 2**128, 2**255]:
+        skb = sk.to_bytes(32, "big")
+        for m in [0, 1, N - 1, N, N + 1, 2**256 - 1, 2**255]:
+            mb = m.to_bytes(32, "big")
+            s = o.sign(skb, mb)
+            for comp in (True, False):
+                pk = o.pubkey_create(skb, comp)
+                rows.append((mb, pk, s))
+    msg = np.zeros((len(rows), 32), np.uint8)
+    pub = np.zeros((len(rows), 65), np.uint8)
+    sig = np.zeros((len(rows), 64), np.uint8)
+    for i, (m, pk, s) in enumerate(rows):
+        msg[i] = np.frombuffer(m, np.uint8)
+        pub[i, : len(pk)] = np.frombuffer(pk, np.uint8)
+        sig[i] = np.frombuffer(s, np.uint8)
+    return msg, pub, sig
+
+
+# ------------------------------------------------------------------ synthetic blocks
+def _compact(n):
+    if n < 253:
+        return bytes([n])
+    if n <= 0xFFFF:
+        return b"\xfd" + n.to_bytes(2, "little")
+    if n <= 0xFFFFFFFF:
+        return b"\xfe" + n.to_bytes(4, "little")
+    return b"\xff" + n.to_bytes(8, "little")
+
+
+def seckey(j):
+    d = int.from_bytes(hashlib.sha256(SEED + b"key" + j.to_bytes(8, "little")).digest(), "big") % N
+    return (d or 1).to_bytes(32, "big")
+
+
+def p2pkh_script(pubkey):
+    return b"\x76\xa9\x14" + po.oracle().hash160(pubkey) + b"\x88\xac"
+
+
+def synthetic_header(height=600000, merkle_root=bytes(32), nonce_tag=0, soln=None, n=200, k=9):
+    """Serialized post-fork header (src/primitives/block.h:49-73): 140 bytes || compactsize || solution."""
+    soln_len = (1 << k) * (n // (k + 1) + 1) // 8
+    if soln is None:
+        soln = bytes(soln_len)
+    h = (4).to_bytes(4, "little") + hashlib.sha256(SEED + b"prevblk").digest() + merkle_root
+    h += height.to_bytes(4, "little") + bytes(28) + (1541030400).to_bytes(4, "little") + (0x1f07ffff).to_bytes(4, "little")
+    h += hashlib.sha256(SEED + b"nonce" + nonce_tag.to_bytes(8, "little")).digest()
+    assert len(h) == 140
+    return h + _compact(len(soln)) + soln
+
+
+def synthetic_block(ntx=41650, sign=True, nkeys=4096, bad_inputs=(), with_prevouts=False):
+    """Post-fork block of `ntx` 1-in/1-out P2PKH transactions (+ coinbase).  With sign=True every input
+    carries a valid SIGHASH_ALL|FORKID signature over the FORKID sighash (inputs listed in bad_inputs get a
+    flipped signature bit); otherwise scriptSigs are deterministic filler of the same shape.
+    Returns the block bytes, or (block, prevout_spk list, prevout_amounts) when with_prevouts."""
+    o = po.oracle()
+    nk = min(nkeys, max(1, ntx))
+    keys = [seckey(j) for j in range(nk)]
+    pubs = [o.pubkey_create(kb, True) for kb in keys]
+    spks = [p2pkh_script(pb) for pb in pubs]
+    amount = 10000
+    cb = (2).to_bytes(4, "little") + b"\x01" + bytes(32) + b"\xff\xff\xff\xff" + b"\x04" + (600000).to_bytes(4, "little")
+    cb += b"\xff\xff\xff\xff" + b"\x01" + (1250000000).to_bytes(8, "little") + bytes([25]) + spks[0] + bytes(4)
+    txs = [cb]
+    prev_spk, prev_amt = [], []
+    bad = set(bad_inputs)
+    for i in range(ntx):
+        j = i % nk
+        prev = hashlib.sha256(hashlib.sha256(SEED + b"prev" + i.to_bytes(8, "little")).digest()).digest()
+        out = (amount - 500).to_bytes(8, "little") + bytes([25]) + spks[(i + 1) % nk]
+
+        def build(script_sig):
+            return ((2).to_bytes(4, "little") + b"\x01" + prev + bytes(4) + _compact(len(script_sig)) + script_sig
+                    + b"\xff\xff\xff\xff" + b"\x01" + out + bytes(4))
+
+        if sign:
+            sh = o.sighash_forkid(spks[j], build(b""), 0, 0x41, amount)
+            s64 = bytearray(o.sign(keys[j], sh))
+            if i in bad:
+                s64[7] ^= 0x10
+            der = o.sig_to_der(bytes(s64)) + b"\x41"
+            script_sig = bytes([len(der)]) + der + bytes([33]) + pubs[j]
+        else:
+            filler = hashlib.sha256(SEED + b"fill" + i.to_bytes(8, "little")).digest()
+            script_sig = bytes([72]) + (filler * 3)[:72] + bytes([33]) + pubs[j]
+        txs.append(build(script_sig))
+        prev_spk.append(spks[j])
+        prev_amt.append(amount)
+    body = _compact(len(txs)) + b"".join(txs)
+    root, _ = o.merkle_root(b"".join(o.sha256d(t) for t in txs))
+    blk = synthetic_header(merkle_root=root) + body
+    if with_prevouts:
+        return blk, prev_spk, prev_amt
+    return blk
