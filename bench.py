@@ -163,7 +163,9 @@ def main():
     d_sig = torch.from_numpy(sig).to(dev)
     d_ok = torch.zeros(n, dtype=torch.uint8, device=dev)
     eng.ecdsa_reserve(n)
-    stream = torch.cuda.current_stream(dev)
+    torch.cuda.synchronize(dev)
+    stream = torch.cuda.Stream(dev)  # a real (non-default) stream: the C ABI launches on exactly this handle
+    assert stream.cuda_stream != 0
 
     def step():
         eng.ecdsa_verify_batch_dev(d_msg.data_ptr(), d_pub.data_ptr(), d_sig.data_ptr(), n, d_ok.data_ptr(), 0,
@@ -228,6 +230,9 @@ def main():
     peak_imad = eng.measure_int_peak(1)   # carry-chained IMAD.WIDE form the field code uses
     peak_wide = eng.measure_int_peak(0)
     peak_add = eng.measure_int_peak(2)
+    pipes = {"imad_wide_x": peak_imad / 1e12, "imad_wide": peak_wide / 1e12, "iadd": peak_add / 1e12,
+             "imad_lo": eng.measure_int_peak(3) / 1e12, "imad_hi": eng.measure_int_peak(4) / 1e12,
+             "dfma": eng.measure_int_peak(5) / 1e12, "ffma": eng.measure_int_peak(6) / 1e12}
     peaks = {}
     try:
         peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
@@ -248,7 +253,7 @@ def main():
                      "achieved": achieved / 1e12, "peak": peak_imad / 1e12, "unit": "Tmul32/s", "frac": achieved / peak_imad,
                      "traffic": None,
                      "peak_source": "bcp_gpu_measure_int_peak(1): IMAD.WIDE.U32.X carry chains, measured live",
-                     "imad_wide_plain_peak": peak_wide / 1e12, "iadd_peak_tops": peak_add / 1e12,
+                     "pipes_tops_measured": pipes,
                      "hbm": {"achieved_gbs": per_gpu * BYTES_PER_VERIFY / 1e9, "peak_gbs": hbm_peak,
                              "frac": per_gpu * BYTES_PER_VERIFY / 1e9 / hbm_peak,
                              "peak_source": "MEASURED_PEAKS.json" if peaks else "fallback"}},

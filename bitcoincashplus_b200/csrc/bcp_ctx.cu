@@ -223,11 +223,39 @@ __global__ void __launch_bounds__(256) int_peak_kernel(uint32_t *out, uint32_t a
                       "+r"(x[8]), "+r"(x[9]), "+r"(x[10]), "+r"(x[11]), "+r"(x[12]), "+r"(x[13]), "+r"(x[14]), "+r"(x[15])
                     : "r"(m), "r"(a), "r"(b));
             }
-        } else {
+        } else if (WHICH == 2) {
 #pragma unroll
             for (int k = 0; k < 4; k++) {
 #pragma unroll
                 for (int i = 0; i < 16; i++) asm volatile("add.u32 %0, %0, %1;" : "+r"(x[i]) : "r"(m));
+            }
+        } else if (WHICH == 3) {
+#pragma unroll
+            for (int k = 0; k < 4; k++) {
+#pragma unroll
+                for (int i = 0; i < 16; i++) asm volatile("mad.lo.u32 %0, %0, %1, %2;" : "+r"(x[i]) : "r"(m), "r"(a));
+            }
+        } else if (WHICH == 4) {
+#pragma unroll
+            for (int k = 0; k < 4; k++) {
+#pragma unroll
+                for (int i = 0; i < 16; i++) asm volatile("mad.hi.u32 %0, %0, %1, %2;" : "+r"(x[i]) : "r"(m), "r"(a));
+            }
+        } else if (WHICH == 5) {
+            double *d = reinterpret_cast<double *>(x); /* 8 independent DFMA chains */
+            double dm = __longlong_as_double(0x3ff0000000000001LL + m);
+#pragma unroll
+            for (int k = 0; k < 8; k++) {
+#pragma unroll
+                for (int i = 0; i < 8; i++) asm volatile("fma.rn.f64 %0, %0, %1, %1;" : "+d"(d[i]) : "d"(dm));
+            }
+        } else {
+            float *f = reinterpret_cast<float *>(x);
+            float fm = __int_as_float(0x3f800001 + m);
+#pragma unroll
+            for (int k = 0; k < 4; k++) {
+#pragma unroll
+                for (int i = 0; i < 16; i++) asm volatile("fma.rn.f32 %0, %0, %1, %1;" : "+f"(f[i]) : "f"(fm));
             }
         }
     }
@@ -240,7 +268,7 @@ __global__ void __launch_bounds__(256) int_peak_kernel(uint32_t *out, uint32_t a
 extern "C" int bcp_gpu_measure_int_peak(int device, int which, double *ops_per_second) {
     bcp_ctx *c = bcp_get_ctx(device);
     if (!c) return BCP_ERR_NOT_INIT;
-    if (!ops_per_second || which < 0 || which > 2) return BCP_ERR_INVALID;
+    if (!ops_per_second || which < 0 || which > 6) return BCP_ERR_INVALID;
     std::lock_guard<std::mutex> lk(c->mu);
     BCP_CUDA(cudaSetDevice(device));
     const int blocks = c->sm_count * 8, threads = 256, iters = 4096;
@@ -254,7 +282,11 @@ extern "C" int bcp_gpu_measure_int_peak(int device, int which, double *ops_per_s
         BCP_CUDA(cudaEventRecord(e0, c->stream));
         if (which == 0) int_peak_kernel<0><<<blocks, threads, 0, c->stream>>>(out, 3, 5, iters);
         else if (which == 1) int_peak_kernel<1><<<blocks, threads, 0, c->stream>>>(out, 3, 5, iters);
-        else int_peak_kernel<2><<<blocks, threads, 0, c->stream>>>(out, 3, 5, iters);
+        else if (which == 2) int_peak_kernel<2><<<blocks, threads, 0, c->stream>>>(out, 3, 5, iters);
+        else if (which == 3) int_peak_kernel<3><<<blocks, threads, 0, c->stream>>>(out, 3, 5, iters);
+        else if (which == 4) int_peak_kernel<4><<<blocks, threads, 0, c->stream>>>(out, 3, 5, iters);
+        else if (which == 5) int_peak_kernel<5><<<blocks, threads, 0, c->stream>>>(out, 3, 5, iters);
+        else int_peak_kernel<6><<<blocks, threads, 0, c->stream>>>(out, 3, 5, iters);
         BCP_CUDA(cudaEventRecord(e1, c->stream));
         BCP_CUDA(cudaEventSynchronize(e1));
         float ms = 0;
@@ -264,7 +296,7 @@ extern "C" int bcp_gpu_measure_int_peak(int device, int which, double *ops_per_s
     BCP_CUDA(cudaGetLastError());
     // per thread per iteration: which 0: 4*8 = 32 wide MADs; which 1: 2*8 = 16 fused lo/hi pairs
     // (= 16 IMAD.WIDE); which 2: 64 adds
-    double per_iter = which == 0 ? 32.0 : which == 1 ? 16.0 : 64.0;
+    double per_iter = which == 0 ? 32.0 : which == 1 ? 16.0 : 64.0; /* which 2,3,4,6: 64 ops; 5: 64 DFMA */
     *ops_per_second = per_iter * iters * (double)blocks * threads / (best * 1e-3);
     cudaEventDestroy(e0);
     cudaEventDestroy(e1);

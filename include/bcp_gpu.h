@@ -125,7 +125,8 @@ BCP_API int bcp_gpu_equihash_verify_batch_dev(int device, unsigned n, unsigned k
 /* ---- measurement helper: integer-pipe peak (SURVEY.md §8d asks the build to measure it) ----------
  * Runs a dependency-free IMAD.WIDE.U32 loop on every SM and returns 32x32->64 multiply-adds per second
  * (which == 0), the carry-chained form mad.lo.cc/madc.hi.cc used by the field code (which == 1), or
- * IADD3-class adds per second (which == 2). */
+ * IADD3-class adds per second (which == 2); 3: mad.lo.u32, 4: mad.hi.u32, 5: fma.rn.f64, 6: fma.rn.f32
+ * (the last four only to place the wide multiply against the other pipes). */
 BCP_API int bcp_gpu_measure_int_peak(int device, int which, double *ops_per_second);
 
 #ifdef __cplusplus
