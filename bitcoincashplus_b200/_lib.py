@@ -41,6 +41,7 @@ SIGNATURES = {
     "bcp_gpu_sha256d_batch_dev": (C.c_int, [C.c_int, vp, vp, sz, vp, vp]),
     "bcp_gpu_merkle_scratch_bytes": (sz, [sz]),
     "bcp_gpu_merkle_root_dev": (C.c_int, [C.c_int, vp, sz, vp, vp, vp, vp]),
+    "bcp_gpu_merkle_root_dev_static": (C.c_int, [C.c_int, vp, sz, vp, vp, vp]),
     "bcp_gpu_equihash_verify_batch": (C.c_int, [C.c_int, C.c_uint, C.c_uint, vp, sz, sz, sz, vp, vp]),
     "bcp_gpu_equihash_scratch_bytes": (sz, [sz]),
     "bcp_gpu_equihash_verify_batch_dev": (C.c_int, [C.c_int, C.c_uint, C.c_uint, vp, sz, sz, sz, vp, vp, vp]),

@@ -231,6 +231,48 @@ BCP_API int bcp_gpu_merkle_root_dev(int device, const uint8_t *d_leaves32, size_
                       stream ? (cudaStream_t)stream : c->stream);
 }
 
+// ---- allocation-free Merkle root ---------------------------------------------------------------------
+// Same tree walk as bcp_gpu_merkle_root_dev, for callers that must not allocate device memory at all:
+// the thread that runs ConnectBlock holds the node's main lock, and cudaMalloc / cudaFree synchronise
+// the whole device, so a validation thread that allocates stalls every other stream on that GPU; an
+// embedder that hands the library a fixed VRAM budget has nothing left to allocate from either.  The
+// inner-node ping-pong buffers therefore live in this file-scope device array instead of a
+// caller-supplied or context-owned buffer.  Every GPU that loads the library carries the array
+// (BCP_MERKLE_STATIC_BYTES, about 256 KiB) until the process exits.
+#define BCP_MERKLE_STATIC_WORDS (2 * ((BCP_MERKLE_STATIC_MAX_LEAVES / MERKLE_NODES) * 8) + 16)
+static __device__ __align__(256) uint32_t g_merkle_static_scratch[BCP_MERKLE_STATIC_WORDS];
+// In host code the name above is only a handle for the symbol, not an address a kernel can use; the
+// device address is looked up once per device (with that device current) and cached here.
+static uint32_t *g_merkle_static_ptr[BCP_MAX_DEVICES];
+
+BCP_API int bcp_gpu_merkle_root_dev_static(int device, const uint8_t *d_leaves32, size_t n, uint8_t *d_root32,
+                                           int *d_mutated, void *stream) {
+    bcp_ctx *c = bcp_get_ctx(device);
+    if (!c) return BCP_ERR_NOT_INIT;
+    if (!d_root32 || !d_mutated || (n && !d_leaves32)) {
+        bcp_set_error("bcp_gpu_merkle_root_dev_static: NULL buffer");
+        return BCP_ERR_INVALID;
+    }
+    if (n > BCP_MERKLE_STATIC_MAX_LEAVES) {
+        bcp_set_error("bcp_gpu_merkle_root_dev_static: %zu leaves exceed the built-in scratch (max %u leaves); "
+                      "use bcp_gpu_merkle_root_dev with caller-provided scratch",
+                      n, (unsigned)BCP_MERKLE_STATIC_MAX_LEAVES);
+        return BCP_ERR_INVALID;
+    }
+    std::lock_guard<std::mutex> lk(c->mu);
+    BCP_CUDA(cudaSetDevice(device));
+    if (!g_merkle_static_ptr[device]) { /* first call on this device: resolve the symbol's device address */
+        uint32_t *p = nullptr;
+        BCP_CUDA(cudaGetSymbolAddress((void **)&p, g_merkle_static_scratch));
+        g_merkle_static_ptr[device] = p;
+    }
+    // Nothing in the array has to start at zero: each launch writes every node the next launch reads, and
+    // the mutated flag (caller memory) is cleared by merkle_dev on every call.  Stale nodes of an earlier,
+    // larger tree are never read.
+    return merkle_dev(c, d_leaves32, n, d_root32, d_mutated, g_merkle_static_ptr[device],
+                      stream ? (cudaStream_t)stream : c->stream);
+}
+
 // Host-pointer forms.  Staging layout in c->stage: [data + pad][offsets][digests][merkle tmp][root][mutated]
 static int hash_host(bcp_ctx *c, const uint8_t *data, size_t len, const uint32_t *off, size_t count, bool want_root,
                      uint8_t *out32, uint8_t *root32, int *mutated) {

@@ -108,6 +108,22 @@ BCP_API size_t bcp_gpu_merkle_scratch_bytes(size_t n);
 BCP_API int bcp_gpu_merkle_root_dev(int device, const uint8_t *d_leaves32, size_t n, uint8_t *d_root32, int *d_mutated,
                                     void *d_scratch, void *stream);
 
+/* Allocation-free variant of bcp_gpu_merkle_root_dev.  It has no counterpart in the reference; it exists
+ * for callers that cannot allocate device memory: a validation thread that must never trigger the
+ * device-wide synchronisation of cudaMalloc/cudaFree while it holds the node's main lock, or an embedder
+ * that runs the library inside a fixed VRAM budget.  The inner-node scratch is a static device array built
+ * into the library (about 256 KiB per GPU, held until process exit) sized for at most
+ * BCP_MERKLE_STATIC_MAX_LEAVES = 1,048,576 leaves; larger n returns BCP_ERR_INVALID with a message.  The call itself performs no cudaMalloc, cudaFree or other allocating call; inputs and outputs
+ * (d_leaves32, d_root32[32], d_mutated[1]) are the caller's device buffers.
+ *   - The first call on a device looks up the array's device address (cudaGetSymbolAddress); make that
+ *     first call before starting any stream capture.
+ *   - All calls on one device share the one array.  It keeps whatever the previous call left there (no
+ *     part of it needs clearing: every node is written before it is read), so two calls whose GPU work
+ *     overlaps — different streams, or different host threads — race on it.  Order them on one stream. */
+#define BCP_MERKLE_STATIC_MAX_LEAVES (1u << 20)
+BCP_API int bcp_gpu_merkle_root_dev_static(int device, const uint8_t *d_leaves32, size_t n, uint8_t *d_root32,
+                                           int *d_mutated, void *stream);
+
 /* ---- Equihash: CheckEquihashSolution (src/pow.cpp:298-323) == Equihash<N,K>::IsValidSolution
  *      (src/crypto/equihash.cpp:724-770) for `count` serialized post-fork headers (140 bytes || compact
  *      size || solution; src/primitives/block.h:49-73) laid out at `stride` bytes, each `hdr_len` long.
