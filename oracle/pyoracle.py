@@ -64,10 +64,10 @@ class Impl:
         self._sig_to_der = L.fn("sig_to_der", i, u8p, u8p, C.POINTER(sz))
         self._equihash_verify = L.fn("equihash_verify", i, C.c_uint, C.c_uint, u8p, sz)
         self._equihash_verify_batch = L.fn("equihash_verify_batch", None, C.c_uint, C.c_uint, u8p, sz, sz, sz, i, u8p)
+        self._pubkey_parse = L.fn("pubkey_parse", i, u8p, sz, u8p)
         if prefix == "orc_":
             self._sign = L.fn("sign_rfc6979", i, u8p, u8p, u8p)
             self._header_hash = L.fn("header_hash", None, u8p, sz, u8p)
-            self._pubkey_parse = L.fn("pubkey_parse", i, u8p, sz, u8p)
             self._der_lax = L.fn("der_lax_parse", i, u8p, sz, u8p)
             self._gen_sigset = L.fn("gen_sigset", None, u8p, sz, sz, sz, i, u8p, u8p, u8p)
             self._blake2b = L.fn("blake2b", None, u8p, sz, u8p, sz, u8p)

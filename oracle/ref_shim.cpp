@@ -95,6 +95,19 @@ int ref_ecdsa_verify(const uint8_t *msg32, const uint8_t *pub, size_t publen, co
     return secp256k1_ecdsa_verify(g_ctx, &sig, msg32, &pk);
 }
 
+// secp256k1_ec_pubkey_parse (secp256k1.c:150-163) + uncompressed re-serialization: xy64 = x || y
+int ref_pubkey_parse(const uint8_t *in, size_t len, uint8_t *xy64) {
+    ensure_init();
+    secp256k1_pubkey pk;
+    memset(xy64, 0, 64);
+    if (!secp256k1_ec_pubkey_parse(g_ctx, &pk, in, len)) return 0;
+    uint8_t out[65];
+    size_t ol = 65;
+    secp256k1_ec_pubkey_serialize(g_ctx, out, &ol, &pk, SECP256K1_EC_UNCOMPRESSED);
+    memcpy(xy64, out + 1, 64);
+    return 1;
+}
+
 // Batch form in the B4 layout: pubkeys at stride 65 (length decided by the prefix byte as
 // CPubKey::GetLen does, src/pubkey.h:47-51; unknown prefix => length 0 => reject).
 static inline size_t publen_by_prefix(uint8_t h) {
