@@ -4,15 +4,34 @@
 // Launch shape
 //   k_ecdsa_prep   one thread per BCP_PREP_K signatures (thread t takes signatures t, t+T, t+2T, ...
 //                  so that the byte loads of a warp stay adjacent), 128 threads per block
-//   k_ecdsa_point  one thread per signature, 128 threads per block, 64 KB dynamic shared memory for
-//                  the per-thread {1..8}Q tables (8 entries x 64 B x 128 threads), three blocks per SM
+//   k_ecdsa_point  one thread per signature, 128 threads per block, four blocks per SM; the per-thread
+//                  {1..8}Q tables (512 B) live in global scratch next to the phase-1 records (the first
+//                  version kept them in shared memory, which capped occupancy at 12 warps per SM)
+// A batch is processed in slices of BCP_SLICE signatures (16 full waves) so that scratch is bounded (718 MB).
 //   k_gcomb_build  one thread per comb-table entry, once per device at bcp_gpu_init
 #include "bcp_ctx.cuh"
+#ifndef BCP_POINT_VARIANT
+#define BCP_POINT_VARIANT 1 /* 0: field mul/sqr as called functions; 1: fully inlined + one block barrier per step */
+#endif
+#if BCP_POINT_VARIANT == 1
+#define BCP_FE_CALLS 0
+#define BCP_STEP_SYNC() __syncthreads()
+#endif
 #include "ecdsa.cuh"
 
-#define BCP_PREP_K 8
+#define BCP_PREP_K 32
+#if BCP_POINT_VARIANT == 1
+#define BCP_POINT_THREADS 256
+#define BCP_POINT_BLOCKS_PER_SM 2
+#else
 #define BCP_POINT_THREADS 128
-#define BCP_POINT_SMEM (BCP_QTAB_WORDS * BCP_POINT_THREADS * 4)
+#define BCP_POINT_BLOCKS_PER_SM 4
+#endif
+/* signatures per slice: 16 full waves of the point kernel on a 148-SM part (148 SMs x 512 resident threads) */
+#define BCP_WAVE ((size_t)148 * 512)
+#define BCP_SLICE (16 * BCP_WAVE)
+#define BCP_E2E_CHUNK (3 * BCP_WAVE)
+#define BCP_SIG_SCRATCH_WORDS (BCP_REC_WORDS + BCP_QTAB_WORDS) /* 80-byte record + 512-byte table per signature */
 
 __global__ void __launch_bounds__(128) k_gcomb_build(uint32_t *gcomb) {
     int idx = blockIdx.x * blockDim.x + threadIdx.x;
@@ -34,8 +53,9 @@ __global__ void __launch_bounds__(128) k_ecdsa_prep(const uint8_t *__restrict__ 
     const size_t T = (size_t)gridDim.x * blockDim.x;
     const size_t t = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (t >= n) return;
-    // Montgomery's trick over this thread's signatures: pre[j] = s_0 * ... * s_{j-1}
-    sig_scalars g[BCP_PREP_K];
+    // Montgomery's trick over this thread's signatures: pre[j] = s_0 * ... * s_{j-1}.  Only the prefix products
+    // are kept (local memory); the second pass re-parses each signature, which is far cheaper than holding
+    // K x (r, s, m) per thread.  K = 32: one 334-multiplication inversion per 32 signatures.
     scalar pre[BCP_PREP_K];
     scalar acc;
 #pragma unroll
@@ -45,9 +65,10 @@ __global__ void __launch_bounds__(128) k_ecdsa_prep(const uint8_t *__restrict__ 
     for (int j = 0; j < BCP_PREP_K; j++) {
         size_t i = t + (size_t)j * T;
         if (i >= n) break;
-        sig_load(g[j], msg32 + 32 * i, sig64 + 64 * i, flags);
+        sig_scalars g;
+        sig_load(g, msg32 + 32 * i, sig64 + 64 * i, flags);
         pre[j] = acc;
-        sc_mul(acc, acc, g[j].s);
+        sc_mul(acc, acc, g.s);
         cnt++;
     }
     scalar inv;
@@ -55,35 +76,29 @@ __global__ void __launch_bounds__(128) k_ecdsa_prep(const uint8_t *__restrict__ 
 #pragma unroll 1
     for (int j = cnt - 1; j >= 0; j--) {
         size_t i = t + (size_t)j * T;
+        sig_scalars g;
+        sig_load(g, msg32 + 32 * i, sig64 + 64 * i, flags);
         scalar sinv;
         sc_mul(sinv, inv, pre[j]);
-        sc_mul(inv, inv, g[j].s);
+        sc_mul(inv, inv, g.s);
         uint32_t r[BCP_REC_WORDS];
-        sig_finish(r, g[j], sinv);
+        sig_finish(r, g, sinv);
         uint4 *dst = reinterpret_cast<uint4 *>(rec + i * BCP_REC_WORDS);
 #pragma unroll
         for (int q = 0; q < BCP_REC_WORDS / 4; q++) dst[q] = make_uint4(r[4 * q], r[4 * q + 1], r[4 * q + 2], r[4 * q + 3]);
     }
 }
 
-__global__ void __launch_bounds__(BCP_POINT_THREADS, 3)
+__global__ void __launch_bounds__(BCP_POINT_THREADS, BCP_POINT_BLOCKS_PER_SM)
     k_ecdsa_point(const uint8_t *__restrict__ pub65, const uint8_t *__restrict__ sig64, size_t n,
-                  const uint32_t *__restrict__ rec, const uint32_t *__restrict__ gcomb, uint8_t *__restrict__ ok) {
-    extern __shared__ uint32_t smem[];
-    const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= n) return;
-    uint32_t r[BCP_REC_WORDS];
-    const uint4 *src = reinterpret_cast<const uint4 *>(rec + i * BCP_REC_WORDS);
-#pragma unroll
-    for (int q = 0; q < BCP_REC_WORDS / 4; q++) {
-        uint4 v = src[q];
-        r[4 * q] = v.x; r[4 * q + 1] = v.y; r[4 * q + 2] = v.z; r[4 * q + 3] = v.w;
-    }
-    qtable tab;
-    tab.base = smem + threadIdx.x;
-    tab.stride = BCP_POINT_THREADS;
-    bool v = ecdsa_point_phase(r, pub65 + 65 * i, sig64 + 64 * i, tab, gcomb);
-    ok[i] = v ? 1 : 0;
+                  const uint32_t *__restrict__ rec, uint32_t *__restrict__ qtabs, const uint32_t *__restrict__ gcomb,
+                  uint8_t *__restrict__ ok) {
+    const size_t gi = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    const size_t i = gi < n ? gi : n - 1; /* tail threads shadow the last signature (they must reach the barriers) */
+    qtable_packed tab;
+    tab.base = qtabs + gi * BCP_QTAB_WORDS; /* own slab even when shadowing: scratch is sized for whole blocks */
+    bool v = ecdsa_point_phase(rec + i * BCP_REC_WORDS, pub65 + 65 * i, sig64 + 64 * i, tab, gcomb);
+    if (gi < n) ok[gi] = v ? 1 : 0;
 }
 
 int bcp_ecdsa_build_tables(bcp_ctx *c) {
@@ -91,26 +106,36 @@ int bcp_ecdsa_build_tables(bcp_ctx *c) {
     int total = BCP_GCOMB_WINDOWS * BCP_GCOMB_ENTRIES;
     k_gcomb_build<<<(total + 127) / 128, 128, 0, c->stream>>>(c->gcomb);
     BCP_CUDA(cudaGetLastError());
-    BCP_CUDA(cudaFuncSetAttribute(k_ecdsa_point, cudaFuncAttributeMaxDynamicSharedMemorySize, BCP_POINT_SMEM));
     BCP_CUDA(cudaStreamSynchronize(c->stream));
     return BCP_OK;
 }
 
+// d_scratch: bcp_gpu_ecdsa_scratch_bytes(n) bytes = [records of one slice][tables of one slice]
 static int launch_verify(bcp_ctx *c, const uint8_t *d_msg, const uint8_t *d_pub, const uint8_t *d_sig, size_t n,
-                         uint32_t flags, uint8_t *d_ok, uint32_t *d_rec, cudaStream_t st) {
-    if (n == 0) return BCP_OK;
-    size_t prep_threads = (n + BCP_PREP_K - 1) / BCP_PREP_K;
-    unsigned prep_blocks = (unsigned)((prep_threads + 127) / 128);
-    k_ecdsa_prep<<<prep_blocks, 128, 0, st>>>(d_msg, d_sig, n, flags, d_rec);
-    unsigned blocks = (unsigned)((n + BCP_POINT_THREADS - 1) / BCP_POINT_THREADS);
-    k_ecdsa_point<<<blocks, BCP_POINT_THREADS, BCP_POINT_SMEM, st>>>(d_pub, d_sig, n, d_rec, c->gcomb, d_ok);
+                         uint32_t flags, uint8_t *d_ok, uint32_t *d_scratch, cudaStream_t st) {
+    size_t cap = n < BCP_SLICE ? n : BCP_SLICE;
+    cap = (cap + BCP_POINT_THREADS - 1) / BCP_POINT_THREADS * BCP_POINT_THREADS;
+    uint32_t *d_rec = d_scratch, *d_tab = d_scratch + cap * BCP_REC_WORDS;
+    for (size_t off = 0; off < n; off += BCP_SLICE) {
+        const size_t m = n - off < BCP_SLICE ? n - off : BCP_SLICE;
+        size_t prep_threads = (m + BCP_PREP_K - 1) / BCP_PREP_K;
+        unsigned prep_blocks = (unsigned)((prep_threads + 127) / 128);
+        k_ecdsa_prep<<<prep_blocks, 128, 0, st>>>(d_msg + 32 * off, d_sig + 64 * off, m, flags, d_rec);
+        unsigned blocks = (unsigned)((m + BCP_POINT_THREADS - 1) / BCP_POINT_THREADS);
+        k_ecdsa_point<<<blocks, BCP_POINT_THREADS, 0, st>>>(d_pub + 65 * off, d_sig + 64 * off, m, d_rec, d_tab, c->gcomb,
+                                                           d_ok + off);
+    }
     BCP_CUDA(cudaGetLastError());
     return BCP_OK;
 }
 
 extern "C" {
 
-size_t bcp_gpu_ecdsa_scratch_bytes(size_t n) { return n * BCP_REC_WORDS * 4; }
+size_t bcp_gpu_ecdsa_scratch_bytes(size_t n) {
+    size_t cap = n < BCP_SLICE ? n : BCP_SLICE;
+    cap = (cap + BCP_POINT_THREADS - 1) / BCP_POINT_THREADS * BCP_POINT_THREADS; /* whole blocks */
+    return cap * BCP_SIG_SCRATCH_WORDS * 4 + 256;
+}
 
 int bcp_gpu_ecdsa_reserve(int device, size_t n) {
     bcp_ctx *c = bcp_get_ctx(device);
@@ -149,7 +174,7 @@ int bcp_gpu_ecdsa_verify_batch(int device, const uint8_t *msg32, const uint8_t *
     if (n == 0) return BCP_OK;
     std::lock_guard<std::mutex> lk(c->mu);
     BCP_CUDA(cudaSetDevice(device));
-    const size_t CH = 1u << 18; // signatures per chunk
+    const size_t CH = BCP_E2E_CHUNK; // signatures per chunk: three full waves
     const size_t per = 32 + 65 + 64 + 1;
     const size_t chunk = n < CH ? n : CH;
     const size_t slot = ((chunk * per + 255) / 256) * 256;

@@ -13,7 +13,7 @@
 //   phase 1 (prep, one thread per K signatures): range checks, ONE scalar inversion per K signatures
 //           (Montgomery's trick), u1 = m/s, u2 = r/s, lattice split u2 = k1 + k2*lambda, signed 4-bit
 //           window recoding.  Output: a 80-byte record per signature in scratch memory.
-//   phase 2 (point, one thread per signature): decompress Q, build {1..8}Q on a common Z without any
+//   phase 2 (point, one thread per signature; one rolled loop, see ecdsa_point_phase): decompress Q, build {1..8}Q on a common Z without any
 //           inversion (z-ratio rescaling, the idea of ge_globalz_set_table_gej group_impl.h:173-194),
 //           34 windows of 4 doublings + 2 mixed additions (Q and lambda*Q share the table: lambda*(x,y) =
 //           (beta*x, y)), then u1*G from a fixed-position comb table (22 windows of 12 bits, no doublings),
@@ -21,6 +21,10 @@
 #pragma once
 #include "ge.cuh"
 #include "scalar.cuh"
+
+#ifndef BCP_STEP_SYNC
+#define BCP_STEP_SYNC() ((void)0)
+#endif
 
 #define BCP_ECDSA_NORMALIZE_S 1u /* CPubKey::Verify semantics: s := min(s, n-s) instead of rejecting high s */
 
@@ -118,136 +122,203 @@ struct qtable {
     }
 };
 
-// Build tab[e] = (e+1)*Q for e = 0..7 as affine points of the curve isomorphic under the common
-// Z (returned in zglob): (X_k, Y_k, Z_k) -> (X_k f^2, Y_k f^3) with f = Z_8 / Z_k, the product of the
-// later z-ratios.  No inversion.  kQ (k <= 8) is never infinity nor +-Q, so every addition is generic.
-BCP_DEV void qtable_build(qtable tab, fe &zglob, const fe &qx, const fe &qy) {
-    fe zr[BCP_QTAB_ENTRIES]; /* zr[k] = Z_{k+1} / Z_k  (1-based multiples); dynamic indexing -> local memory */
-    gej p;
-    p.x = qx; p.y = qy; fe_set_u32(p.z, 1); p.inf = false;
-    tab.store(0, qx, qy);
-    {
-        gej d;
-        gej_double(d, p);
-        zr[1] = d.z; /* Z_2 / Z_1 with Z_1 = 1 */
-        p = d;
-        tab.store(1, p.x, p.y);
-    }
+// Same table, one contiguous 512-byte slab per signature in global memory (entry e = 64 bytes at word e*16):
+// every lookup is four 16-byte loads of one lane's own 64 bytes, i.e. fully used sectors whatever entry each
+// lane picks.  Frees the shared memory that capped the point kernel at 12 warps per SM.
+struct qtable_packed {
+    uint32_t *base; /* this signature's slab, 16-byte aligned */
+    BCP_DEV_M void store(int e, const fe &x, const fe &y) {
 #if BCP_PTX
-#pragma unroll 1
-#endif
-    for (int k = 2; k < BCP_QTAB_ENTRIES; k++) {
-        gej_add_ge(p, qx, qy, &zr[k]);
-        tab.store(k, p.x, p.y);
-    }
-    zglob = p.z;
-    fe zs = zr[BCP_QTAB_ENTRIES - 1];
-#if BCP_PTX
-#pragma unroll 1
-#endif
-    for (int k = BCP_QTAB_ENTRIES - 2; k >= 0; k--) {
-        fe x, y, zs2, zs3;
-        tab.load(k, x, y);
-        fe_sqr(zs2, zs);
-        fe_mul(zs3, zs2, zs);
-        fe_mul(x, x, zs2);
-        fe_mul(y, y, zs3);
-        tab.store(k, x, y);
-        if (k > 0) fe_mul(zs, zs, zr[k]);
-    }
-}
-
-// acc += sign * tab[|d| - 1], optionally through the endomorphism (x -> beta*x)
-BCP_DEV void add_digit(gej &acc, const qtable &tab, int d, bool flip, bool endo) {
-    if (d == 0) return;
-    bool neg = (d < 0) != flip;
-    int e = (d < 0 ? -d : d) - 1;
-    fe x, y;
-    tab.load(e, x, y);
-    if (endo) {
-        fe beta;
-        BCP_UNROLL
-        for (int i = 0; i < 8; i++) beta.v[i] = FE_BETA[i];
-        fe_mul(x, x, beta);
-    }
-    if (neg) fe_neg(y, y);
-    gej_add_ge(acc, x, y, nullptr);
-}
-
-// The whole point phase for one signature.  rec = scratch record from phase 1; gcomb = fixed-base
-// comb table; returns the verdict.
-BCP_DEV bool ecdsa_point_phase(const uint32_t *rec, const uint8_t *pub65, const uint8_t *sig64, qtable tab,
-                               const uint32_t *gcomb) {
-    uint32_t fl = rec[18];
-    if (!(fl & BCP_REC_VALID)) return false;
-    fe qx, qy;
-    if (!pubkey_parse(qx, qy, pub65)) return false;
-
-    fe zglob;
-    qtable_build(tab, zglob, qx, qy);
-
-    uint32_t k1[5], k2[5];
-    BCP_UNROLL
-    for (int i = 0; i < 5; i++) { k1[i] = rec[8 + i]; k2[i] = rec[13 + i]; }
-    const bool n1 = fl & BCP_REC_NEG1, n2 = fl & BCP_REC_NEG2;
-
-    gej acc;
-    fe_set_zero(acc.x); fe_set_zero(acc.y); fe_set_zero(acc.z);
-    acc.inf = true;
-#if BCP_PTX
-#pragma unroll 1
-#endif
-    for (int w = 33; w >= 0; w--) {
-        if (!acc.inf) {
-            gej_double(acc, acc); gej_double(acc, acc); gej_double(acc, acc); gej_double(acc, acc);
-        }
-        add_digit(acc, tab, digit_w4(k1, w), n1, false);
-        add_digit(acc, tab, digit_w4(k2, w), n2, true);
-    }
-    // leave the isomorphic curve: true Z = Z * zglob
-    if (!acc.inf) fe_mul(acc.z, acc.z, zglob);
-
-    // u1 * G: one table lookup + mixed addition per 12-bit window, no doublings
-#if BCP_PTX
-#pragma unroll 1
-#endif
-    for (int j = 0; j < BCP_GCOMB_WINDOWS; j++) {
-        int bit = j * BCP_GCOMB_BITS;
-        int limb = bit >> 5, sh = bit & 31;
-        uint32_t lo = rec[limb];
-        uint32_t hi = (limb + 1 < 8) ? rec[limb + 1] : 0u;
-        uint32_t d = (sh == 0 ? lo : ((lo >> sh) | (hi << (32 - sh)))) & (BCP_GCOMB_ENTRIES - 1);
-        if (d == 0) continue;
-        const uint32_t *e = gcomb + ((size_t)j * BCP_GCOMB_ENTRIES + d) * 16;
-        fe x, y;
-#if BCP_PTX
-        const uint4 *e4 = reinterpret_cast<const uint4 *>(e);
-        uint4 a = __ldg(e4), b = __ldg(e4 + 1), c = __ldg(e4 + 2), dd = __ldg(e4 + 3);
-        x.v[0] = a.x; x.v[1] = a.y; x.v[2] = a.z; x.v[3] = a.w; x.v[4] = b.x; x.v[5] = b.y; x.v[6] = b.z; x.v[7] = b.w;
-        y.v[0] = c.x; y.v[1] = c.y; y.v[2] = c.z; y.v[3] = c.w; y.v[4] = dd.x; y.v[5] = dd.y; y.v[6] = dd.z; y.v[7] = dd.w;
+        uint4 *p = reinterpret_cast<uint4 *>(base + e * 16);
+        p[0] = make_uint4(x.v[0], x.v[1], x.v[2], x.v[3]);
+        p[1] = make_uint4(x.v[4], x.v[5], x.v[6], x.v[7]);
+        p[2] = make_uint4(y.v[0], y.v[1], y.v[2], y.v[3]);
+        p[3] = make_uint4(y.v[4], y.v[5], y.v[6], y.v[7]);
 #else
-        for (int i = 0; i < 8; i++) { x.v[i] = e[i]; y.v[i] = e[8 + i]; }
+        for (int i = 0; i < 8; i++) { base[e * 16 + i] = x.v[i]; base[e * 16 + 8 + i] = y.v[i]; }
 #endif
-        gej_add_ge(acc, x, y, nullptr);
     }
-    if (acc.inf) return false; /* ecdsa_impl.h:220 */
+    BCP_DEV_M void load(int e, fe &x, fe &y) const {
+#if BCP_PTX
+        const uint4 *p = reinterpret_cast<const uint4 *>(base + e * 16);
+        uint4 a = p[0], b = p[1], c = p[2], d = p[3];
+        x.v[0] = a.x; x.v[1] = a.y; x.v[2] = a.z; x.v[3] = a.w; x.v[4] = b.x; x.v[5] = b.y; x.v[6] = b.z; x.v[7] = b.w;
+        y.v[0] = c.x; y.v[1] = c.y; y.v[2] = c.z; y.v[3] = c.w; y.v[4] = d.x; y.v[5] = d.y; y.v[6] = d.z; y.v[7] = d.w;
+#else
+        for (int i = 0; i < 8; i++) { x.v[i] = base[e * 16 + i]; y.v[i] = base[e * 16 + 8 + i]; }
+#endif
+    }
+};
+
+// The whole point phase for one signature, written as ONE loop over "steps" so that the kernel contains a
+// single instance of the doubling and of the mixed addition (the fully unrolled first version was 800 KB of
+// SASS and stalled on instruction fetch; profiles/r01_*).  rec = phase-1 record (global memory), gcomb =
+// fixed-base comb table.  Step schedule:
+//   t in [0, 7)            table build: acc = Q; double, then add Q six times; after each step store acc.(x,y)
+//                          as table entry t+1 and remember the z-ratio (Z_{k+1} / Z_k)
+//   t == 7                 (before the step) rescale entries 0..6 to the common Z = Z_8 with the products of
+//                          the later ratios — no inversion (idea of ge_globalz_set_table_gej, group_impl.h:173-194;
+//                          kQ, k <= 8, is never infinity nor +-Q, so every table addition is generic) — then acc = infinity
+//   t in [7, 7 + 34*6)     window w = 33..0: four doublings, add digit(k1,w)*Q, add digit(k2,w)*lambda*Q
+//   next step              leave the isomorphic curve: Z *= Z_8
+//   last 22 steps          u1*G: one comb lookup + mixed addition per 12-bit window, no doublings
+template <class Table>
+BCP_DEV bool ecdsa_point_phase(const uint32_t *rec, const uint8_t *pub65, const uint8_t *sig64, Table tab,
+                               const uint32_t *gcomb) {
+    const uint32_t fl = rec[18];
+    gej acc;
+    // A signature that is already known to be invalid keeps walking (on the generator instead of its own
+    // key) so that every thread of the block reaches every BCP_STEP_SYNC; its verdict is forced to false.
+    bool valid = (fl & BCP_REC_VALID) != 0;
+    valid = pubkey_parse(acc.x, acc.y, pub65) && valid;
+    if (!valid) {
+        BCP_UNROLL
+        for (int i = 0; i < 8; i++) { acc.x.v[i] = FE_GX[i]; acc.y.v[i] = FE_GY[i]; }
+    }
+    fe_set_u32(acc.z, 1);
+    acc.inf = false;
+    tab.store(0, acc.x, acc.y);
+    const bool n1 = fl & BCP_REC_NEG1, n2 = fl & BCP_REC_NEG2;
+    fe zr[BCP_QTAB_ENTRIES]; /* zr[k] = Z_{k+1} / Z_k  (1-based multiples); run-time index -> local memory */
+    fe zglob;
+    fe_set_u32(zglob, 1);
+    const int T_TAB = BCP_QTAB_ENTRIES - 1, T_MAIN = 34 * 6, T_ALL = T_TAB + T_MAIN + 1 + BCP_GCOMB_WINDOWS;
+#if BCP_PTX
+#pragma unroll 1
+#endif
+    for (int t = 0; t < T_ALL; t++) {
+        BCP_STEP_SYNC(); /* keeps the warps of a block in the same code region (instruction-cache locality) */
+        bool dbl = false, have = false;
+        fe x, y, h;
+        if (t < T_TAB) {
+            if (t == 0) dbl = true;
+            else { tab.load(0, x, y); have = true; }
+        } else if (t < T_TAB + T_MAIN) {
+            const int u = t - T_TAB;
+            if (u == 0) {
+                zglob = acc.z;
+                fe zs = zr[BCP_QTAB_ENTRIES - 1];
+#if BCP_PTX
+#pragma unroll 1
+#endif
+                for (int k = BCP_QTAB_ENTRIES - 2; k >= 0; k--) {
+                    fe ex, ey, zs2, zs3;
+                    tab.load(k, ex, ey);
+                    fe_sqr(zs2, zs);
+                    fe_mul(zs3, zs2, zs);
+                    fe_mul(ex, ex, zs2);
+                    fe_mul(ey, ey, zs3);
+                    tab.store(k, ex, ey);
+                    if (k > 0) fe_mul(zs, zs, zr[k]);
+                }
+                acc.inf = true;
+            }
+            const int w = 33 - u / 6, ph = u % 6;
+            if (ph < 4) {
+                dbl = true;
+            } else {
+                const bool second = ph == 5;
+                const uint32_t word = rec[(second ? 13 : 8) + (w >> 3)];
+                int d = (int)((word >> ((w & 7) * 4)) & 15u);
+                if (w <= 32) d -= 8;
+                if (d != 0) {
+                    const bool neg = (d < 0) != (second ? n2 : n1);
+                    tab.load((d < 0 ? -d : d) - 1, x, y);
+                    if (second) { /* lambda * (x, y) = (beta * x, y) */
+                        fe beta;
+                        BCP_UNROLL
+                        for (int i = 0; i < 8; i++) beta.v[i] = FE_BETA[i];
+                        fe_mul(x, x, beta);
+                    }
+                    if (neg) fe_neg(y, y);
+                    have = true;
+                }
+            }
+        } else if (t == T_TAB + T_MAIN) {
+            if (!acc.inf) fe_mul(acc.z, acc.z, zglob);
+            continue;
+        } else {
+            const int j = t - (T_TAB + T_MAIN + 1);
+            const int bit = j * BCP_GCOMB_BITS;
+            const int limb = bit >> 5, sh = bit & 31;
+            const uint32_t lo = rec[limb];
+            const uint32_t hi = (limb + 1 < 8) ? rec[limb + 1] : 0u;
+            const uint32_t d = (sh == 0 ? lo : ((lo >> sh) | (hi << (32 - sh)))) & (BCP_GCOMB_ENTRIES - 1);
+            if (d != 0) {
+                const uint32_t *e = gcomb + ((size_t)j * BCP_GCOMB_ENTRIES + d) * 16;
+#if BCP_PTX
+                const uint4 *e4 = reinterpret_cast<const uint4 *>(e);
+                uint4 qa = __ldg(e4), qb = __ldg(e4 + 1), qc = __ldg(e4 + 2), qd = __ldg(e4 + 3);
+                x.v[0] = qa.x; x.v[1] = qa.y; x.v[2] = qa.z; x.v[3] = qa.w; x.v[4] = qb.x; x.v[5] = qb.y; x.v[6] = qb.z; x.v[7] = qb.w;
+                y.v[0] = qc.x; y.v[1] = qc.y; y.v[2] = qc.z; y.v[3] = qc.w; y.v[4] = qd.x; y.v[5] = qd.y; y.v[6] = qd.z; y.v[7] = qd.w;
+#else
+                for (int i = 0; i < 8; i++) { x.v[i] = e[i]; y.v[i] = e[8 + i]; }
+#endif
+                have = true;
+            }
+        }
+        if (!dbl) {
+            if (!have) continue;
+            if (acc.inf) { /* first addition into infinity copies the operand (group_impl.h:417-421) */
+                acc.x = x; acc.y = y;
+                fe_set_u32(acc.z, 1);
+                acc.inf = false;
+                continue;
+            }
+            // mixed addition acc += (x, y): 8M + 3S, with the degenerate branches of gej_add_ge_var (:438-448)
+            fe z2, u2, s2, rr, h2, h3, v, tt;
+            fe_sqr(z2, acc.z);
+            fe_mul(u2, x, z2);
+            fe_mul(tt, acc.z, z2);
+            fe_mul(s2, y, tt);
+            fe_sub(h, u2, acc.x);
+            fe_sub(rr, s2, acc.y);
+            if (fe_is_zero(h)) {
+                if (fe_is_zero(rr)) dbl = true;           /* P + P: fall through to the shared doubling  */
+                else { acc.inf = true; continue; }        /* P + (-P)                                       */
+            } else {
+                fe_sqr(h2, h);
+                fe_mul(h3, h2, h);
+                fe_mul(v, acc.x, h2);
+                fe_mul(acc.z, acc.z, h);
+                fe_sqr(tt, rr);
+                fe_sub(tt, tt, h3); fe_sub(tt, tt, v); fe_sub(acc.x, tt, v);
+                fe_sub(tt, v, acc.x);
+                fe_mul(tt, tt, rr);
+                fe_mul(h3, h3, acc.y);
+                fe_sub(acc.y, tt, h3);
+            }
+        }
+        if (dbl && !acc.inf) gej_double(acc, acc);
+        if (t < T_TAB) {
+            tab.store(t + 1, acc.x, acc.y);
+            zr[t + 1] = (t == 0) ? acc.z : h;
+        }
+    }
+    if (acc.inf || !valid) return false; /* ecdsa_impl.h:220 */
 
     // x(R) == r (mod n), projectively: r * Z^2 == X, then the r + n < p second chance (:246-266)
     scalar r;
     sc_set_b32(r, sig64); /* already known to be in range */
-    fe z2, t, fr;
+    fe z2, t1, fr;
     fe_sqr(z2, acc.z);
     BCP_UNROLL
     for (int i = 0; i < 8; i++) fr.v[i] = r.v[i];
-    fe_mul(t, fr, z2);
-    if (fe_equal(t, acc.x)) return true;
     uint32_t pmn[8], n[8];
     BCP_UNROLL
     for (int i = 0; i < 8; i++) { pmn[i] = SC_P_MINUS_N[i]; n[i] = SC_N[i]; }
-    if (u256_ge(r.v, pmn)) return false;
-    addn_cc<8>(fr.v, r.v, n); /* r + n < p: no overflow */
-    fe_mul(t, fr, z2);
-    return fe_equal(t, acc.x);
+    const bool second_chance = !u256_ge(r.v, pmn);
+    bool ok = false;
+#if BCP_PTX
+#pragma unroll 1
+#endif
+    for (int pass = 0; pass < 2; pass++) {
+        fe_mul(t1, fr, z2);
+        if (fe_equal(t1, acc.x)) ok = true;
+        if (ok || !second_chance) break;
+        addn_cc<8>(fr.v, r.v, n); /* r + n < p: no overflow */
+    }
+    return ok;
 }
 
 // ---------------------------------------------------------------- one-time: fixed-base comb entry

@@ -82,6 +82,58 @@ BCP_DEV void row_acc8(uint32_t *X, uint32_t a0, uint32_t a2, uint32_t a4, uint32
     for (int j = 0; j < 8; j++) X[j] = t[j];
 #endif
 }
+// X[0..2K-1] += { a[0]*b, ..., a[K-1]*b } at limb pairs (0,1),(2,3),...; X[2K] absorbs the carry
+template <int K>
+BCP_DEV void row_acc_k(uint32_t *X, const uint32_t *a, uint32_t b) {
+#if BCP_PTX
+    static_assert(K >= 1 && K <= 3, "row width");
+    if (K == 1) {
+        asm("mad.lo.cc.u32 %0, %3, %4, %0;\n\t"
+            "madc.hi.cc.u32 %1, %3, %4, %1;\n\t"
+            "addc.u32 %2, %2, 0;"
+            : "+r"(X[0]), "+r"(X[1]), "+r"(X[2])
+            : "r"(a[0]), "r"(b));
+    } else if (K == 2) {
+        asm("mad.lo.cc.u32 %0, %5, %7, %0;\n\t"
+            "madc.hi.cc.u32 %1, %5, %7, %1;\n\t"
+            "madc.lo.cc.u32 %2, %6, %7, %2;\n\t"
+            "madc.hi.cc.u32 %3, %6, %7, %3;\n\t"
+            "addc.u32 %4, %4, 0;"
+            : "+r"(X[0]), "+r"(X[1]), "+r"(X[2]), "+r"(X[3]), "+r"(X[4])
+            : "r"(a[0]), "r"(a[1]), "r"(b));
+    } else {
+        asm("mad.lo.cc.u32 %0, %7, %10, %0;\n\t"
+            "madc.hi.cc.u32 %1, %7, %10, %1;\n\t"
+            "madc.lo.cc.u32 %2, %8, %10, %2;\n\t"
+            "madc.hi.cc.u32 %3, %8, %10, %3;\n\t"
+            "madc.lo.cc.u32 %4, %9, %10, %4;\n\t"
+            "madc.hi.cc.u32 %5, %9, %10, %5;\n\t"
+            "addc.u32 %6, %6, 0;"
+            : "+r"(X[0]), "+r"(X[1]), "+r"(X[2]), "+r"(X[3]), "+r"(X[4]), "+r"(X[5]), "+r"(X[6])
+            : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(b));
+    }
+#else
+    uint64_t c = 0;
+    for (int j = 0; j < K; j++) {
+        uint64_t p = (uint64_t)a[j] * b;
+        uint64_t lo = (uint64_t)X[2 * j] + (uint32_t)p + c;
+        X[2 * j] = (uint32_t)lo;
+        uint64_t hi = (uint64_t)X[2 * j + 1] + (uint32_t)(p >> 32) + (lo >> 32);
+        X[2 * j + 1] = (uint32_t)hi;
+        c = hi >> 32;
+    }
+    X[2 * K] += (uint32_t)c;
+#endif
+}
+BCP_DEV void wide_mul(uint32_t &lo, uint32_t &hi, uint32_t a, uint32_t b) {
+#if BCP_PTX
+    asm("mul.lo.u32 %0, %2, %3;\n\tmul.hi.u32 %1, %2, %3;" : "=r"(lo), "=r"(hi) : "r"(a), "r"(b));
+#else
+    uint64_t p = (uint64_t)a * b;
+    lo = (uint32_t)p;
+    hi = (uint32_t)(p >> 32);
+#endif
+}
 // r[0..n-1] = a + b, returns carry (0/1).  One asm statement per chain: the carry flag never has to
 // survive between statements.  (Outputs go through temporaries so that r may alias a or b.)
 template <int N>
@@ -207,24 +259,8 @@ BCP_DEV uint32_t subn_cc(uint32_t *r, const uint32_t *a, const uint32_t *b) {
     return c;
 }
 
-// ------------------------------------------------------------------ 256x256 -> 512
-BCP_DEV void mul_wide(uint32_t *r /*16*/, const uint32_t *a, const uint32_t *b) {
-    uint32_t E[16], O[16]; /* E[k] sits at limb k, O[k] at limb k+1 */
-    row_set(E, a[0], a[2], a[4], a[6], b[0]);
-    row_set(O, a[1], a[3], a[5], a[7], b[0]);
-    BCP_UNROLL
-    for (int k = 8; k < 16; k++) { E[k] = 0; O[k] = 0; }
-    BCP_UNROLL
-    for (int i = 1; i < 8; i++) {
-        if (i & 1) {
-            row_acc9(O + i - 1, a[0], a[2], a[4], a[6], b[i]);
-            if (i < 7) row_acc9(E + i + 1, a[1], a[3], a[5], a[7], b[i]);
-            else row_acc8(E + 8, a[1], a[3], a[5], a[7], b[i]);
-        } else {
-            row_acc9(E + i, a[0], a[2], a[4], a[6], b[i]);
-            row_acc9(O + i, a[1], a[3], a[5], a[7], b[i]);
-        }
-    }
+// r = E + (O << 32): E[k] sits at limb k, O[k] at limb k+1 (O[15] is always zero)
+BCP_DEV void merge_even_odd(uint32_t *r /*16*/, const uint32_t *E, const uint32_t *O) {
     r[0] = E[0];
 #if BCP_PTX
     asm("add.cc.u32 %0, %15, %30;\n\t"
@@ -253,6 +289,56 @@ BCP_DEV void mul_wide(uint32_t *r /*16*/, const uint32_t *a, const uint32_t *b) 
     }
 #endif
 }
+// r = a + b over 16 limbs (no carry out: callers guarantee the sum fits)
+BCP_DEV void add16(uint32_t *r, const uint32_t *a, const uint32_t *b) {
+#if BCP_PTX
+    asm("add.cc.u32 %0, %16, %32;\n\t"
+        "addc.cc.u32 %1, %17, %33;\n\t"
+        "addc.cc.u32 %2, %18, %34;\n\t"
+        "addc.cc.u32 %3, %19, %35;\n\t"
+        "addc.cc.u32 %4, %20, %36;\n\t"
+        "addc.cc.u32 %5, %21, %37;\n\t"
+        "addc.cc.u32 %6, %22, %38;\n\t"
+        "addc.cc.u32 %7, %23, %39;\n\t"
+        "addc.cc.u32 %8, %24, %40;\n\t"
+        "addc.cc.u32 %9, %25, %41;\n\t"
+        "addc.cc.u32 %10, %26, %42;\n\t"
+        "addc.cc.u32 %11, %27, %43;\n\t"
+        "addc.cc.u32 %12, %28, %44;\n\t"
+        "addc.cc.u32 %13, %29, %45;\n\t"
+        "addc.cc.u32 %14, %30, %46;\n\t"
+        "addc.u32 %15, %31, %47;"
+        : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]), "=r"(r[8]), "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15])
+        : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(a[4]), "r"(a[5]), "r"(a[6]), "r"(a[7]), "r"(a[8]), "r"(a[9]), "r"(a[10]), "r"(a[11]), "r"(a[12]), "r"(a[13]), "r"(a[14]), "r"(a[15]), "r"(b[0]), "r"(b[1]), "r"(b[2]), "r"(b[3]), "r"(b[4]), "r"(b[5]), "r"(b[6]), "r"(b[7]), "r"(b[8]), "r"(b[9]), "r"(b[10]), "r"(b[11]), "r"(b[12]), "r"(b[13]), "r"(b[14]), "r"(b[15]));
+#else
+    uint64_t t = 0;
+    for (int k = 0; k < 16; k++) {
+        t += (uint64_t)a[k] + b[k];
+        r[k] = (uint32_t)t;
+        t >>= 32;
+    }
+#endif
+}
+// ------------------------------------------------------------------ 256x256 -> 512
+BCP_DEV void mul_wide(uint32_t *r /*16*/, const uint32_t *a, const uint32_t *b) {
+    uint32_t E[16], O[16]; /* E[k] sits at limb k, O[k] at limb k+1 */
+    row_set(E, a[0], a[2], a[4], a[6], b[0]);
+    row_set(O, a[1], a[3], a[5], a[7], b[0]);
+    BCP_UNROLL
+    for (int k = 8; k < 16; k++) { E[k] = 0; O[k] = 0; }
+    BCP_UNROLL
+    for (int i = 1; i < 8; i++) {
+        if (i & 1) {
+            row_acc9(O + i - 1, a[0], a[2], a[4], a[6], b[i]);
+            if (i < 7) row_acc9(E + i + 1, a[1], a[3], a[5], a[7], b[i]);
+            else row_acc8(E + 8, a[1], a[3], a[5], a[7], b[i]);
+        } else {
+            row_acc9(E + i, a[0], a[2], a[4], a[6], b[i]);
+            row_acc9(O + i, a[1], a[3], a[5], a[7], b[i]);
+        }
+    }
+    merge_even_odd(r, E, O);
+}
 
 // ------------------------------------------------------------------ 512 -> [0, 2^256) mod p
 BCP_DEV void fe_reduce_wide(fe &r, const uint32_t *t /*16*/) {
@@ -273,36 +359,88 @@ BCP_DEV void fe_reduce_wide(fe &r, const uint32_t *t /*16*/) {
     uint32_t c = addn_cc<8>(r.v, s, A);
     // third fold: a carry means S' wrapped past 2^256 (== 2^32+977); the wrapped value is < 2^67,
     // so only limbs 0..2 can change and no further wrap is possible
-    uint32_t B[3] = {c * BCP_FOLD, c, 0};
+    uint32_t B[3] = {(0u - c) & BCP_FOLD, c, 0}; /* c is 0/1: mask instead of a multiply (keeps the IMAD pipe free) */
     addn_cc<3>(r.v, r.v, B);
 }
 
-BCP_DEV void fe_mul(fe &r, const fe &a, const fe &b) {
+// The multiplication and the squaring are real (non-inlined) device functions taking and returning the
+// element BY VALUE: ptxas passes the 8+8 limbs in registers (no local-memory traffic, checked in SASS), a call
+// costs a CALL/RET pair plus a few moves, and every kernel holds exactly one copy of each.  The fully
+// inlined first version of the point kernel was 800 KB of SASS, later 105 KB with a 45 KB hot loop, and in
+// both the top stall reason was instruction fetch (profiles/r01_*); with calls the hot loop fits the
+// instruction cache.
+#ifndef BCP_FE_CALLS
+#define BCP_FE_CALLS 1
+#endif
+#if BCP_FE_CALLS
+#define BCP_FE_FN BCP_DEV_NOINLINE
+#else
+#define BCP_FE_FN BCP_DEV
+#endif
+BCP_FE_FN fe fe_mul_f(fe a, fe b) {
     uint32_t t[16];
+    fe r;
     mul_wide(t, a.v, b.v);
     fe_reduce_wide(r, t);
+    return r;
 }
-#ifndef BCP_FE_SQR_DEDICATED
-BCP_DEV void fe_sqr(fe &r, const fe &a) { fe_mul(r, a, a); }
-#endif
+BCP_DEV void fe_mul(fe &r, const fe &a, const fe &b) { r = fe_mul_f(a, b); }
+// a^2 as 512 bits: 28 off-diagonal products (same even/odd carry-chain layout as mul_wide, rows shrink as i
+// grows), doubled by a funnel shift, plus the 8 diagonal squares: 36 IMAD.WIDE instead of 64.
+BCP_DEV void sqr_wide(uint32_t *r /*16*/, const uint32_t *a) {
+    uint32_t E[16], O[16];
+    BCP_UNROLL
+    for (int k = 0; k < 16; k++) { E[k] = 0; O[k] = 0; }
+    // i = 0: a0 * {a1,a3,a5,a7} -> limbs 1,3,5,7 (O 0,2,4,6);  a0 * {a2,a4,a6} -> limbs 2,4,6
+    wide_mul(O[0], O[1], a[1], a[0]); wide_mul(O[2], O[3], a[3], a[0]);
+    wide_mul(O[4], O[5], a[5], a[0]); wide_mul(O[6], O[7], a[7], a[0]);
+    wide_mul(E[2], E[3], a[2], a[0]); wide_mul(E[4], E[5], a[4], a[0]); wide_mul(E[6], E[7], a[6], a[0]);
+    { const uint32_t m[3] = {a[2], a[4], a[6]}; row_acc_k<3>(O + 2, m, a[1]); }   /* limbs 3,5,7   */
+    { const uint32_t m[3] = {a[3], a[5], a[7]}; row_acc_k<3>(E + 4, m, a[1]); }   /* limbs 4,6,8   */
+    { const uint32_t m[3] = {a[3], a[5], a[7]}; row_acc_k<3>(O + 4, m, a[2]); }   /* limbs 5,7,9   */
+    { const uint32_t m[2] = {a[4], a[6]}; row_acc_k<2>(E + 6, m, a[2]); }         /* limbs 6,8     */
+    { const uint32_t m[2] = {a[4], a[6]}; row_acc_k<2>(O + 6, m, a[3]); }         /* limbs 7,9     */
+    { const uint32_t m[2] = {a[5], a[7]}; row_acc_k<2>(E + 8, m, a[3]); }         /* limbs 8,10    */
+    { const uint32_t m[2] = {a[5], a[7]}; row_acc_k<2>(O + 8, m, a[4]); }         /* limbs 9,11    */
+    { const uint32_t m[1] = {a[6]}; row_acc_k<1>(E + 10, m, a[4]); }              /* limb 10       */
+    { const uint32_t m[1] = {a[6]}; row_acc_k<1>(O + 10, m, a[5]); }              /* limb 11       */
+    { const uint32_t m[1] = {a[7]}; row_acc_k<1>(E + 12, m, a[5]); }              /* limb 12       */
+    { const uint32_t m[1] = {a[7]}; row_acc_k<1>(O + 12, m, a[6]); }              /* limb 13       */
+    uint32_t S[16], T[16], D[16];
+    merge_even_odd(S, E, O);
+    T[0] = S[0] << 1;
+    BCP_UNROLL
+    for (int k = 1; k < 16; k++) T[k] = (S[k] << 1) | (S[k - 1] >> 31);
+    BCP_UNROLL
+    for (int i = 0; i < 8; i++) wide_mul(D[2 * i], D[2 * i + 1], a[i], a[i]);
+    add16(r, T, D);
+}
+BCP_FE_FN fe fe_sqr_f(fe a) {
+    uint32_t t[16];
+    fe r;
+    sqr_wide(t, a.v);
+    fe_reduce_wide(r, t);
+    return r;
+}
+BCP_DEV void fe_sqr(fe &r, const fe &a) { r = fe_sqr_f(a); }
 
 // ------------------------------------------------------------------ add / sub / neg (weakly reduced in and out)
 BCP_DEV void fe_add(fe &r, const fe &a, const fe &b) {
     uint32_t c = addn_cc<8>(r.v, a.v, b.v);
     // a + b - 2^256 == a + b - 2^256 + (2^32 + 977) (mod p)
-    uint32_t A[8] = {c * BCP_FOLD, c, 0, 0, 0, 0, 0, 0};
+    uint32_t A[8] = {(0u - c) & BCP_FOLD, c, 0, 0, 0, 0, 0, 0};
     uint32_t c2 = addn_cc<8>(r.v, r.v, A);
     // a second wrap needs both inputs within 2^33 of 2^256; afterwards the value is < 2^34
-    uint32_t B[2] = {c2 * BCP_FOLD, c2};
+    uint32_t B[2] = {(0u - c2) & BCP_FOLD, c2};
     addn_cc<2>(r.v, r.v, B);
 }
 BCP_DEV void fe_sub(fe &r, const fe &a, const fe &b) {
     uint32_t bw = subn_cc<8>(r.v, a.v, b.v);
     // a - b + 2^256 == a - b + 2^256 - (2^32 + 977) (mod p)
-    uint32_t A[8] = {bw * BCP_FOLD, bw, 0, 0, 0, 0, 0, 0};
+    uint32_t A[8] = {(0u - bw) & BCP_FOLD, bw, 0, 0, 0, 0, 0, 0};
     uint32_t bw2 = subn_cc<8>(r.v, r.v, A);
     // second borrow: value is now within 2^34 of 2^256, subtracting again cannot borrow
-    uint32_t B[2] = {bw2 * BCP_FOLD, bw2};
+    uint32_t B[2] = {(0u - bw2) & BCP_FOLD, bw2};
     subn_cc<2>(r.v, r.v, B);
 }
 BCP_DEV void fe_set_zero(fe &r) {
@@ -362,24 +500,45 @@ BCP_DEV void fe_sqrn(fe &r, const fe &a, int n) {
     for (int i = 0; i < n; i++) fe_sqr(r, r);
 }
 // candidate square root a^((p+1)/4); the caller checks r^2 == a (fe_sqrt, field_impl.h:38-134).
-// (p+1)/4 = 2^254 - 2^30 - 244 has the bit pattern 1^223 0 1^22 0000 11 00, hence the chain below
-// (x_k = a^(2^k - 1)).
+// (p+1)/4 = 2^254 - 2^30 - 244 has the bit pattern 1^223 0 1^22 0000 11 00.  With x_k = a^(2^k - 1) the chain is
+//   x2 x3 x6 x9 x11 x22 x44 x88 x176 x220 x223, then ((x223 << 23) x22 << 6) x2 << 2
+// i.e. 14 steps "square n times, multiply by a saved value".  It is driven from a table in ONE rolled loop so
+// that the kernel holds a single squaring and a single multiplication instance for it (code size, not
+// arithmetic, was the top stall reason of the fully unrolled version: see profiles/r01_*).
 BCP_DEV void fe_sqrt_candidate(fe &r, const fe &a) {
-    fe x2, x3, x6, x9, x11, x22, x44, x88, x176, x220, x223, t;
-    fe_sqr(t, a); fe_mul(x2, t, a);
-    fe_sqr(t, x2); fe_mul(x3, t, a);
-    fe_sqrn(t, x3, 3); fe_mul(x6, t, x3);
-    fe_sqrn(t, x6, 3); fe_mul(x9, t, x3);
-    fe_sqrn(t, x9, 2); fe_mul(x11, t, x2);
-    fe_sqrn(t, x11, 11); fe_mul(x22, t, x11);
-    fe_sqrn(t, x22, 22); fe_mul(x44, t, x22);
-    fe_sqrn(t, x44, 44); fe_mul(x88, t, x44);
-    fe_sqrn(t, x88, 88); fe_mul(x176, t, x88);
-    fe_sqrn(t, x176, 44); fe_mul(x220, t, x44);
-    fe_sqrn(t, x220, 3); fe_mul(x223, t, x3);
-    fe_sqrn(t, x223, 23); fe_mul(t, t, x22);
-    fe_sqrn(t, t, 6); fe_mul(t, t, x2);
-    fe_sqrn(r, t, 2);
+    // saved values: 0:a 1:x2 2:x3 3:x11 4:x22 5:x44 6:x88 ; 7 = "do not save"/"no multiply"
+    fe sv[7];
+    sv[0] = a;
+    fe cur = a;
+#if BCP_PTX
+#pragma unroll 1
+#endif
+    for (int step = 0; step < 14; step++) {
+        int nsq, mi, si;
+        switch (step) {
+            case 0: nsq = 1; mi = 0; si = 1; break;   /* x2  */
+            case 1: nsq = 1; mi = 0; si = 2; break;   /* x3  */
+            case 2: nsq = 3; mi = 2; si = 7; break;   /* x6  */
+            case 3: nsq = 3; mi = 2; si = 7; break;   /* x9  */
+            case 4: nsq = 2; mi = 1; si = 3; break;   /* x11 */
+            case 5: nsq = 11; mi = 3; si = 4; break;  /* x22 */
+            case 6: nsq = 22; mi = 4; si = 5; break;  /* x44 */
+            case 7: nsq = 44; mi = 5; si = 6; break;  /* x88 */
+            case 8: nsq = 88; mi = 6; si = 7; break;  /* x176 */
+            case 9: nsq = 44; mi = 5; si = 7; break;  /* x220 */
+            case 10: nsq = 3; mi = 2; si = 7; break;  /* x223 */
+            case 11: nsq = 23; mi = 4; si = 7; break;
+            case 12: nsq = 6; mi = 1; si = 7; break;
+            default: nsq = 2; mi = 7; si = 7; break;
+        }
+#if BCP_PTX
+#pragma unroll 1
+#endif
+        for (int i = 0; i < nsq; i++) fe_sqr(cur, cur);
+        if (mi != 7) fe_mul(cur, cur, sv[mi]);
+        if (si != 7) sv[si] = cur;
+    }
+    r = cur;
 }
 // a^(p-2) (only used by one-time table generation)
 BCP_DEV void fe_inv(fe &r, const fe &a) {
