@@ -66,6 +66,16 @@ class Engine:
         check(lib().bcp_gpu_ecdsa_verify_batch(self.device, msg32_ptr, pub65_ptr, sig64_ptr, n, flags, ok_ptr),
               "bcp_gpu_ecdsa_verify_batch")
 
+    def pubkey_parse_batch(self, pub65):
+        """secp256k1_ec_pubkey_parse for (n,65) key slots -> (xy (n,64), ok (n,))."""
+        pub65 = _np(pub65, 65)
+        n = pub65.shape[0]
+        xy = np.zeros((n, 64), dtype=np.uint8)
+        ok = np.zeros(n, dtype=np.uint8)
+        check(lib().bcp_gpu_pubkey_parse_batch(self.device, pub65.ctypes.data, n, xy.ctypes.data, ok.ctypes.data),
+              "bcp_gpu_pubkey_parse_batch")
+        return xy, ok
+
     def ecdsa_reserve(self, n):
         check(lib().bcp_gpu_ecdsa_reserve(self.device, n), "bcp_gpu_ecdsa_reserve")
 

@@ -101,6 +101,25 @@ __global__ void __launch_bounds__(BCP_POINT_THREADS, BCP_POINT_BLOCKS_PER_SM)
     if (gi < n) ok[gi] = v ? 1 : 0;
 }
 
+// secp256k1_ec_pubkey_parse for a batch: affine x || y (big-endian) per key, ok byte per key
+__global__ void __launch_bounds__(128) k_pubkey_parse(const uint8_t *__restrict__ pub65, size_t n, uint8_t *__restrict__ xy64,
+                                                      uint8_t *__restrict__ ok) {
+    const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    fe x, y;
+    bool v = pubkey_parse(x, y, pub65 + 65 * i);
+    fe_normalize(x);
+    fe_normalize(y);
+    uint8_t *o = xy64 + 64 * i;
+#pragma unroll
+    for (int k = 0; k < 8; k++) {
+        uint32_t a = v ? x.v[7 - k] : 0u, b = v ? y.v[7 - k] : 0u;
+        o[4 * k] = a >> 24; o[4 * k + 1] = a >> 16; o[4 * k + 2] = a >> 8; o[4 * k + 3] = a;
+        o[32 + 4 * k] = b >> 24; o[32 + 4 * k + 1] = b >> 16; o[32 + 4 * k + 2] = b >> 8; o[32 + 4 * k + 3] = b;
+    }
+    ok[i] = v ? 1 : 0;
+}
+
 int bcp_ecdsa_build_tables(bcp_ctx *c) {
     BCP_CUDA(cudaMalloc(&c->gcomb, (size_t)BCP_GCOMB_WORDS * 4));
     int total = BCP_GCOMB_WINDOWS * BCP_GCOMB_ENTRIES;
@@ -159,6 +178,29 @@ int bcp_gpu_ecdsa_verify_batch_dev(int device, const uint8_t *d_msg32, const uin
     if (rc != BCP_OK) return rc;
     return launch_verify(c, d_msg32, d_pub65, d_sig64, n, flags, d_ok, reinterpret_cast<uint32_t *>(c->scratch),
                          stream ? (cudaStream_t)stream : c->stream);
+}
+
+// secp256k1_ec_pubkey_parse (src/secp256k1/src/secp256k1.c:150-163) for n keys in the 65-byte-slot layout.
+int bcp_gpu_pubkey_parse_batch(int device, const uint8_t *pub65, size_t n, uint8_t *xy64, uint8_t *ok) {
+    bcp_ctx *c = bcp_get_ctx(device);
+    if (!c) return BCP_ERR_NOT_INIT;
+    if (n == 0) return BCP_OK;
+    if (!pub65 || !xy64 || !ok) {
+        bcp_set_error("bcp_gpu_pubkey_parse_batch: NULL buffer");
+        return BCP_ERR_INVALID;
+    }
+    std::lock_guard<std::mutex> lk(c->mu);
+    BCP_CUDA(cudaSetDevice(device));
+    int rc = bcp_ctx_reserve_stage(c, n * (65 + 64 + 1) + 512);
+    if (rc != BCP_OK) return rc;
+    uint8_t *d_pub = c->stage, *d_xy = d_pub + ((n * 65 + 255) / 256) * 256, *d_ok = d_xy + n * 64;
+    BCP_CUDA(cudaMemcpyAsync(d_pub, pub65, n * 65, cudaMemcpyHostToDevice, c->stream));
+    k_pubkey_parse<<<(unsigned)((n + 127) / 128), 128, 0, c->stream>>>(d_pub, n, d_xy, d_ok);
+    BCP_CUDA(cudaGetLastError());
+    BCP_CUDA(cudaMemcpyAsync(xy64, d_xy, n * 64, cudaMemcpyDeviceToHost, c->stream));
+    BCP_CUDA(cudaMemcpyAsync(ok, d_ok, n, cudaMemcpyDeviceToHost, c->stream));
+    BCP_CUDA(cudaStreamSynchronize(c->stream));
+    return BCP_OK;
 }
 
 // Host-pointer form: the batch is cut into chunks; chunk k+1's host->device copy overlaps chunk k's

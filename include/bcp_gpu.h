@@ -78,6 +78,10 @@ BCP_API int bcp_gpu_ecdsa_verify_batch_dev(int device, const uint8_t *d_msg32, c
 BCP_API size_t bcp_gpu_ecdsa_scratch_bytes(size_t n);
 BCP_API int bcp_gpu_ecdsa_reserve(int device, size_t n);
 
+/* secp256k1_ec_pubkey_parse (src/secp256k1/src/secp256k1.c:150-163, eckey_impl.h:17-35) for n keys in the
+ * same 65-byte-slot layout: xy64[i] = affine x || y big-endian (zeros when invalid), ok[i] = 1/0. */
+BCP_API int bcp_gpu_pubkey_parse_batch(int device, const uint8_t *pub65, size_t n, uint8_t *xy64, uint8_t *ok);
+
 /* Host-side byte parsing that stays on the CPU by design (branchy, a few dozen bytes):
  * ecdsa_signature_parse_der_lax (src/pubkey.cpp:26-168).  Returns 1 and writes r||s (zeros when a
  * component overflows, which later verifies as invalid), or 0 on a structural failure. */

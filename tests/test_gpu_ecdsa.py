@@ -82,3 +82,42 @@ def test_chunked_large_batch_properties(engine, oracle):
     assert (got[idx] == want).all()
     # idempotence
     assert (engine.ecdsa_verify_batch(msg, pub, sig) == got).all()
+
+
+def test_tests_c_vectors_on_gpu(engine):
+    """The reference's own self-test vectors (src/secp256k1/src/tests.c: run_ec_pubkey_parse_test :2787-3111,
+    test_ecdsa_edge_cases :3973-4340; tests/golden/secp_vectors.json) through the CUDA path."""
+    import json
+
+    import bitcoincashplus_b200 as bcp
+
+    v = json.load(open(os.path.join(os.path.dirname(__file__), "golden", "secp_vectors.json")))
+    pp = [e for e in v["pubkey_parse"] if bcp and (len(e["pub"]) // 2 == (33 if e["pub"][:2] in ("02", "03") else 65 if e["pub"][:2] in ("04", "06", "07") else -1))]
+    assert len(pp) > 100
+    pub = np.zeros((len(pp), 65), np.uint8)
+    for i, e in enumerate(pp):
+        b = bytes.fromhex(e["pub"])
+        pub[i, : len(b)] = np.frombuffer(b, np.uint8)
+    xy, ok = engine.pubkey_parse_batch(pub)
+    for i, e in enumerate(pp):
+        assert ok[i] == e["ok"], e["pub"]
+        if e["ok"]:
+            assert xy[i].tobytes().hex() == e["xy"]
+    ed = v["ecdsa_edge"]
+    msg = np.stack([np.frombuffer(bytes.fromhex(e["msg"]), np.uint8) for e in ed])
+    sig = np.stack([np.frombuffer(bytes.fromhex(e["sig"]), np.uint8) for e in ed])
+    pk = np.zeros((len(ed), 65), np.uint8)
+    for i, e in enumerate(ed):
+        b = bytes.fromhex(e["pub"])
+        pk[i, : len(b)] = np.frombuffer(b, np.uint8)
+    assert list(engine.ecdsa_verify_batch(msg, pk, sig)) == [e["verdict_raw"] for e in ed]
+    assert list(engine.ecdsa_verify_batch(msg, pk, sig, flags=bcp.ECDSA_FLAG_NORMALIZE_S)) == [e["verdict_normalized"] for e in ed]
+
+
+def test_reference_golden_verdicts_on_gpu(engine):
+    """tests/golden/ecdsa_ref.npz: verdicts computed by the reference at both API levels."""
+    import bitcoincashplus_b200 as bcp
+
+    z = np.load(os.path.join(os.path.dirname(__file__), "golden", "ecdsa_ref.npz"))
+    assert (engine.ecdsa_verify_batch(z["msg"], z["pub"], z["sig"]) == z["verdict_raw"]).all()
+    assert (engine.ecdsa_verify_batch(z["msg"], z["pub"], z["sig"], flags=bcp.ECDSA_FLAG_NORMALIZE_S) == z["verdict_cpubkey"]).all()
