@@ -3,7 +3,8 @@ import ctypes as C
 import os
 
 HERE = os.path.dirname(os.path.abspath(__file__))
-_SO = os.path.join(HERE, "libbcp_b200.so")
+# BCP_B200_LIB lets tools/quick_bench.py A/B-test alternative builds of the same C ABI; the default is the in-tree build
+_SO = os.environ.get("BCP_B200_LIB") or os.path.join(HERE, "libbcp_b200.so")
 
 
 class BcpError(RuntimeError):

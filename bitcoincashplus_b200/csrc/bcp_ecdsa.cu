@@ -21,8 +21,10 @@
 
 #define BCP_PREP_K 32
 #if BCP_POINT_VARIANT == 1
+#ifndef BCP_POINT_THREADS
 #define BCP_POINT_THREADS 256
-#define BCP_POINT_BLOCKS_PER_SM 2
+#endif
+#define BCP_POINT_BLOCKS_PER_SM (512 / BCP_POINT_THREADS)
 #else
 #define BCP_POINT_THREADS 128
 #define BCP_POINT_BLOCKS_PER_SM 4

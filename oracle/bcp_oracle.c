@@ -1224,3 +1224,123 @@ int orc_sighash_forkid(const uint8_t *script_code, size_t sc_len, const uint8_t 
     orc_sha256(t, 32, out32);
     return 1;
 }
+
+/* ============================================================== P2PKH input checks ========== */
+/* IsValidSignatureEncoding (src/script/interpreter.cpp:107-174): strict DER + one hashtype byte */
+int orc_is_valid_signature_encoding(const uint8_t *sig, size_t len) {
+    if (len < 9 || len > 73) return 0;
+    if (sig[0] != 0x30) return 0;
+    if (sig[1] != len - 3) return 0;
+    unsigned lenR = sig[3];
+    if (5 + lenR >= len) return 0;
+    unsigned lenS = sig[5 + lenR];
+    if ((size_t)(lenR + lenS + 7) != len) return 0;
+    if (sig[2] != 0x02) return 0;
+    if (lenR == 0) return 0;
+    if (sig[4] & 0x80) return 0;
+    if (lenR > 1 && sig[4] == 0x00 && !(sig[5] & 0x80)) return 0;
+    if (sig[lenR + 4] != 0x02) return 0;
+    if (lenS == 0) return 0;
+    if (sig[lenR + 6] & 0x80) return 0;
+    if (lenS > 1 && sig[lenR + 6] == 0x00 && !(sig[lenR + 7] & 0x80)) return 0;
+    return 1;
+}
+/* same scan as orc_block_index, also listing every non-coinbase input: byte offset of its outpoint, its
+ * transaction and its ordinal within the transaction (CTransaction::IsCoinBase: one input with a null prevout) */
+long orc_block_index_inputs(const uint8_t *blk, size_t len, int legacy, uint32_t *tx_off, size_t max_tx, uint32_t *in_off,
+                            uint32_t *in_tx, uint32_t *in_n, size_t max_inputs, long *ntx_out) {
+    long ntx = orc_block_index(blk, len, legacy, tx_off, max_tx);
+    if (ntx < 0) return ntx;
+    if (ntx_out) *ntx_out = ntx;
+    size_t cnt = 0;
+    for (long t = 0; t < ntx; t++) {
+        size_t pos = tx_off[t] + 4;
+        uint64_t nin, sl;
+        read_compact(blk, len, &pos, &nin);
+        int coinbase = 0;
+        if (nin == 1) {
+            coinbase = 1;
+            for (int b = 0; b < 32; b++) if (blk[pos + b]) coinbase = 0;
+            if (ld64(blk + pos + 28) >> 32 != 0xFFFFFFFFu) coinbase = 0;
+        }
+        for (uint64_t i = 0; i < nin; i++) {
+            if (!coinbase) {
+                if (cnt >= max_inputs) return -2;
+                in_off[cnt] = (uint32_t)pos; in_tx[cnt] = (uint32_t)t; in_n[cnt] = (uint32_t)i;
+                cnt++;
+            }
+            pos += 36;
+            read_compact(blk, len, &pos, &sl);
+            pos += sl + 4;
+        }
+    }
+    return (long)cnt;
+}
+#define ORC_SCRIPT_FLAGS_POSTFORK ((1u << 1) | (1u << 2) | (1u << 3) | (1u << 14) | (1u << 16))
+typedef struct {
+    const uint8_t *blk; const uint32_t *tx_off, *in_off, *in_tx, *in_n; const uint8_t *spk; const uint32_t *spk_off;
+    const int64_t *amounts; uint8_t *err;
+} pk_arg;
+static uint8_t p2pkh_one(const uint8_t *blk, const uint32_t *tx_off, uint32_t in_off, uint32_t t, uint32_t nin_idx,
+                         const uint8_t *spk, size_t spk_len, int64_t amount) {
+    if (spk_len != 25 || spk[0] != 0x76 || spk[1] != 0xa9 || spk[2] != 0x14 || spk[23] != 0x88 || spk[24] != 0xac) return 255;
+    const uint8_t *tx = blk + tx_off[t];
+    size_t txlen = tx_off[t + 1] - tx_off[t];
+    size_t pos = in_off + 36 - tx_off[t];
+    uint64_t sl;
+    if (!read_compact(tx, txlen, &pos, &sl)) return 255;
+    const uint8_t *ss = tx + pos;
+    /* scriptSig must be exactly two direct pushes (opcodes 0x00..0x4b) */
+    if (sl < 2) return 255;
+    size_t siglen = ss[0];
+    if (siglen > 75 || 1 + siglen >= sl) return 255;
+    size_t publen = ss[1 + siglen];
+    if (publen == 0 || publen > 75 || 1 + siglen + 1 + publen != sl) return 255;
+    const uint8_t *sig = ss + 1, *pub = ss + 2 + siglen;
+    uint8_t h160[20];
+    orc_hash160(pub, publen, h160);
+    if (memcmp(h160, spk + 3, 20) != 0) return 11;                       /* SCRIPT_ERR_EQUALVERIFY */
+    uint8_t rs[64];
+    memset(rs, 0, 64);
+    if (siglen) { /* CheckSignatureEncoding (:221-254) */
+        if (!orc_is_valid_signature_encoding(sig, siglen)) return 23;   /* SIG_DER */
+        if (!orc_check_low_s(sig, siglen - 1)) return 26;                /* SIG_HIGH_S */
+        uint8_t ht = sig[siglen - 1];
+        uint8_t base = ht & ~(0x80 | 0x40);
+        if (base < 1 || base > 3) return 22;                             /* SIG_HASHTYPE */
+        if (!(ht & 0x40)) return 36;                                     /* MUST_USE_FORKID */
+    }
+    /* CheckPubKeyEncoding (:256-269, :62-82) */
+    if (publen < 33) return 28;
+    if (pub[0] == 0x04) { if (publen != 65) return 28; }
+    else if (pub[0] == 0x02 || pub[0] == 0x03) { if (publen != 33) return 28; }
+    else return 28;
+    if (!siglen) return 2;                                               /* empty signature: FALSE on the stack -> EVAL_FALSE */
+    uint8_t sh[32];
+    if (!orc_sighash_forkid(spk, 25, tx, txlen, nin_idx, sig[siglen - 1], amount, sh)) return 1;
+    if (!orc_pubkey_verify(sh, pub, publen, sig, siglen - 1)) return 31; /* SIG_NULLFAIL */
+    return 0;
+}
+static void pk_run(size_t lo, size_t hi, void *p) {
+    pk_arg *a = (pk_arg *)p;
+    for (size_t i = lo; i < hi; i++)
+        a->err[i] = p2pkh_one(a->blk, a->tx_off, a->in_off[i], a->in_tx[i], a->in_n[i], a->spk + a->spk_off[i],
+                              a->spk_off[i + 1] - a->spk_off[i], a->amounts[i]);
+}
+long orc_block_verify_p2pkh(const uint8_t *blk, size_t len, int legacy, const uint8_t *spk, const uint32_t *spk_off,
+                            const int64_t *amounts, uint32_t flags, int nthreads, uint8_t *err, size_t max_inputs) {
+    if ((flags & ORC_SCRIPT_FLAGS_POSTFORK) != ORC_SCRIPT_FLAGS_POSTFORK || (flags & (1u << 17))) return -3;
+    size_t max_tx = len / 60 + 2;
+    uint32_t *tx_off = (uint32_t *)malloc(4 * (max_tx + 1));
+    uint32_t *in_off = (uint32_t *)malloc(4 * max_inputs), *in_tx = (uint32_t *)malloc(4 * max_inputs),
+             *in_n = (uint32_t *)malloc(4 * max_inputs);
+    long ntx = 0;
+    long n = orc_block_index_inputs(blk, len, legacy, tx_off, max_tx, in_off, in_tx, in_n, max_inputs, &ntx);
+    if (n > 0) {
+        pk_arg a = {blk, tx_off, in_off, in_tx, in_n, spk, spk_off, amounts, err};
+        pthread_once(&g_tab_once, build_g_tab);
+        parallel_for((size_t)n, nthreads, pk_run, &a);
+    }
+    free(tx_off); free(in_off); free(in_tx); free(in_n);
+    return n;
+}

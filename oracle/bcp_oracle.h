@@ -73,6 +73,18 @@ void orc_gen_sigset(const uint8_t *seed, size_t seedlen, size_t n, size_t nkeys,
 int orc_sighash_forkid(const uint8_t *script_code, size_t sc_len, const uint8_t *tx, size_t txlen, unsigned nin,
                        uint32_t hashtype, int64_t amount, uint8_t out32[32]);
 
+/* ---- P2PKH fast path of CScriptCheck::operator() (src/validation.cpp:1350-1359 -> VerifyScript
+ *      src/script/interpreter.cpp:1551-1630 on scriptSig = <sig> <pubkey>, scriptPubKey = DUP HASH160 <20> EQUALVERIFY
+ *      CHECKSIG) under the post-fork flag set (P2SH|STRICTENC|DERSIG|LOW_S|NULLFAIL|FORKID [+CLTV|CSV]).
+ *      Per non-coinbase input, in block order, err[i] = the ScriptError VerifyScript reports (0 = OK), or 255 when
+ *      the input is not of this shape (the caller then runs the full interpreter).  spk/spk_off/amounts describe
+ *      the spent outputs.  Returns the number of inputs, <0 on a malformed block. */
+long orc_block_index_inputs(const uint8_t *blk, size_t len, int legacy, uint32_t *tx_off, size_t max_tx, uint32_t *in_off,
+                            uint32_t *in_tx, uint32_t *in_n, size_t max_inputs, long *ntx_out);
+long orc_block_verify_p2pkh(const uint8_t *blk, size_t len, int legacy, const uint8_t *spk, const uint32_t *spk_off,
+                            const int64_t *amounts, uint32_t flags, int nthreads, uint8_t *err, size_t max_inputs);
+int orc_is_valid_signature_encoding(const uint8_t *sig, size_t len);
+
 #ifdef __cplusplus
 }
 #endif

@@ -75,6 +75,9 @@ class Impl:
             self._block_index = L.fn("block_index", C.c_long, u8p, sz, i, C.POINTER(u32), sz)
             self._check_pow = L.fn("check_pow", i, u8p, u32, u8p)
             self._ripemd160 = L.fn("ripemd160", None, u8p, sz, u8p)
+            self._block_verify_p2pkh = L.fn("block_verify_p2pkh", C.c_long, u8p, sz, i, u8p, C.POINTER(u32), C.POINTER(i64),
+                                            u32, i, u8p, sz)
+            self._is_valid_sig_enc = L.fn("is_valid_signature_encoding", i, u8p, sz)
         else:
             L.fn("init", i)()
             self._sign = L.fn("sign", i, u8p, u8p, u8p)
@@ -83,7 +86,7 @@ class Impl:
             self._sighash_ref = L.fn("sighash", i, u8p, sz, u8p, sz, C.c_uint, u32, i64, u32, u8p)
             self._verify_script = L.fn("verify_script", i, u8p, sz, u8p, sz, u8p, sz, C.c_uint, i64, u32, C.POINTER(i))
             self._block_verify_inputs = L.fn("block_verify_inputs", C.c_long, u8p, sz, i, u8p, C.POINTER(u32),
-                                             C.POINTER(i64), u32, i, u8p, sz)
+                                             C.POINTER(i64), u32, i, u8p, sz, u8p)
 
     # ---- hashing
     def _h(self, f, data, n):
@@ -211,6 +214,27 @@ class Impl:
         ok = self._verify_script(_p(bytes(script_sig)), len(script_sig), _p(bytes(script_pubkey)), len(script_pubkey),
                                  _p(bytes(tx)), len(tx), nin, amount, flags, C.byref(err))
         return ok, err.value
+
+    def block_script_errors(self, blk, legacy, spks, amounts, flags, nthreads=1):
+        """Per non-coinbase input ScriptError of the block's spends (spks: list of scriptPubKey bytes, amounts: ints).
+        Oracle: P2PKH fast path (255 = not that shape).  Reference: full VerifyScript."""
+        n = len(spks)
+        cat = b"".join(spks) or b"\x00"
+        off = np.zeros(n + 1, dtype=np.uint32)
+        off[1:] = np.cumsum([len(s) for s in spks])
+        am = np.asarray(amounts, dtype=np.int64)
+        err = np.full(n, 254, dtype=np.uint8)
+        u32p, i64p = C.POINTER(C.c_uint32), C.POINTER(C.c_int64)
+        if self.kind == "port":
+            r = self._block_verify_p2pkh(_p(bytes(blk)), len(blk), int(legacy), _p(cat), off.ctypes.data_as(u32p),
+                                         am.ctypes.data_as(i64p), flags, nthreads, _p(err), n)
+        else:
+            ok = np.zeros(n, dtype=np.uint8)
+            r = self._block_verify_inputs(_p(bytes(blk)), len(blk), int(legacy), _p(cat), off.ctypes.data_as(u32p),
+                                          am.ctypes.data_as(i64p), flags, nthreads, _p(ok), n, _p(err))
+            assert r < 0 or ((ok == 1) == (err == 0)).all()
+        assert r == n, (r, n)
+        return err
 
     def block_index(self, blk, legacy, max_tx=1 << 20):
         off = (C.c_uint32 * (max_tx + 1))()

@@ -324,7 +324,8 @@ int ref_verify_script(const uint8_t *script_sig, size_t ss_len, const uint8_t *s
 // skipped), multi-threaded; this is the per-input work CScriptCheck::operator() does
 // (src/validation.cpp:1350-1359) with the non-caching checker.  ok[i] per input.
 long ref_block_verify_inputs(const uint8_t *blk, size_t len, int legacy, const uint8_t *spk, const uint32_t *spk_off,
-                             const int64_t *amounts, uint32_t flags, int nthreads, uint8_t *ok, size_t max_inputs) {
+                             const int64_t *amounts, uint32_t flags, int nthreads, uint8_t *ok, size_t max_inputs,
+                             uint8_t *err_out) {
     ensure_init();
     try {
         CDataStream ss((const char *)blk, (const char *)blk + len, SER_NETWORK,
@@ -356,10 +357,11 @@ long ref_block_verify_inputs(const uint8_t *blk, size_t len, int legacy, const u
             for (size_t j = lo; j < hi; j++) {
                 const Job &jb = jobs[j];
                 CScript spkj(spk + spk_off[j], spk + spk_off[j + 1]);
-                ScriptError e;
+                ScriptError e = SCRIPT_ERR_UNKNOWN_ERROR;
                 ok[j] = VerifyScript(jb.tx->vin[jb.nIn].scriptSig, spkj, flags,
                                      TransactionSignatureChecker(jb.tx, jb.nIn, Amount(amounts[j]), txd[txidx[j]]), &e)
                             ? 1 : 0;
+                if (err_out) err_out[j] = (uint8_t)e;
             }
         });
         return (long)jobs.size();

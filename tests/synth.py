@@ -173,10 +173,32 @@ def synthetic_header(height=600000, merkle_root=bytes(32), nonce_tag=0, soln=Non
     return h + _compact(len(soln)) + soln
 
 
-def synthetic_block(ntx=41650, sign=True, nkeys=4096, bad_inputs=(), with_prevouts=False):
+POSTFORK_FLAGS = (1 << 0) | (1 << 1) | (1 << 2) | (1 << 3) | (1 << 9) | (1 << 10) | (1 << 14) | (1 << 16)
+
+# input mutations understood by synthetic_block(mutations={index: kind}) and the ScriptError the reference reports
+INPUT_MUTATIONS = {
+    "bad_sig": 31, "der_padding": 23, "high_s": 26, "hashtype_01": 36, "hashtype_45": 22, "hashtype_c1": 0,
+    "hashtype_42": 0, "hashtype_43": 0, "hashtype_c2": 0, "hashtype_c3": 0, "wrong_pubkey": 11, "hybrid_pubkey": 28,
+    "uncompressed_pubkey": 0, "empty_sig": 2, "r_34_bytes": 31, "s_zero": 31, "der_trailing": 23, "der_short": 23,
+    "three_pushes": None, "pushdata1": None,  # not the P2PKH shape: fast path answers 255, the interpreter decides
+}
+
+
+def _der(r, s):
+    def enc(v):
+        b = v.to_bytes(40, "big").lstrip(b"\x00") or b"\x00"
+        if b[0] & 0x80:
+            b = b"\x00" + b
+        return b"\x02" + bytes([len(b)]) + b
+    body = enc(r) + enc(s)
+    return b"\x30" + bytes([len(body)]) + body
+
+
+def synthetic_block(ntx=41650, sign=True, nkeys=4096, bad_inputs=(), with_prevouts=False, mutations=None):
     """Post-fork block of `ntx` 1-in/1-out P2PKH transactions (+ coinbase).  With sign=True every input
     carries a valid SIGHASH_ALL|FORKID signature over the FORKID sighash (inputs listed in bad_inputs get a
-    flipped signature bit); otherwise scriptSigs are deterministic filler of the same shape.
+    flipped signature bit; `mutations` maps an input index to one of INPUT_MUTATIONS); otherwise scriptSigs are
+    deterministic filler of the same shape.
     Returns the block bytes, or (block, prevout_spk list, prevout_amounts) when with_prevouts."""
     o = po.oracle()
     nk = min(nkeys, max(1, ntx))
@@ -189,6 +211,9 @@ def synthetic_block(ntx=41650, sign=True, nkeys=4096, bad_inputs=(), with_prevou
     txs = [cb]
     prev_spk, prev_amt = [], []
     bad = set(bad_inputs)
+    mutations = dict(mutations or {})
+    for i in bad:
+        mutations.setdefault(i, "bad_sig")
     for i in range(ntx):
         j = i % nk
         prev = hashlib.sha256(hashlib.sha256(SEED + b"prev" + i.to_bytes(8, "little")).digest()).digest()
@@ -198,18 +223,54 @@ def synthetic_block(ntx=41650, sign=True, nkeys=4096, bad_inputs=(), with_prevou
             return ((2).to_bytes(4, "little") + b"\x01" + prev + bytes(4) + _compact(len(script_sig)) + script_sig
                     + b"\xff\xff\xff\xff" + b"\x01" + out + bytes(4))
 
+        pub, spk = pubs[j], spks[j]
         if sign:
-            sh = o.sighash_forkid(spks[j], build(b""), 0, 0x41, amount)
-            s64 = bytearray(o.sign(keys[j], sh))
-            if i in bad:
-                s64[7] ^= 0x10
-            der = o.sig_to_der(bytes(s64)) + b"\x41"
-            script_sig = bytes([len(der)]) + der + bytes([33]) + pubs[j]
+            kind = mutations.get(i)
+            ht = {"hashtype_c1": 0xC1, "hashtype_42": 0x42, "hashtype_43": 0x43, "hashtype_c2": 0xC2,
+                  "hashtype_c3": 0xC3}.get(kind, 0x41)
+            if kind == "uncompressed_pubkey":
+                pub = o.pubkey_create(keys[j], False)
+                spk = p2pkh_script(pub)
+            elif kind == "hybrid_pubkey":
+                u = o.pubkey_create(keys[j], False)
+                pub = bytes([6 + (u[64] & 1)]) + u[1:]
+                spk = p2pkh_script(pub)
+            sh = o.sighash_forkid(spk, build(b""), 0, ht, amount)
+            s64 = o.sign(keys[j], sh)
+            r_, s_ = int.from_bytes(s64[:32], "big"), int.from_bytes(s64[32:], "big")
+            der = _der(r_, s_)
+            if kind == "bad_sig":
+                der = _der(r_ ^ (1 << 100), s_)
+            elif kind == "der_padding":
+                body = b"\x02" + bytes([len(der[4:4 + der[3]]) + 1]) + b"\x00" + der[4:4 + der[3]] + der[4 + der[3]:]
+                der = b"\x30" + bytes([len(body)]) + body
+            elif kind == "high_s":
+                der = _der(r_, N - s_)
+            elif kind == "r_34_bytes":
+                der = _der((0x7F << 264) | r_, s_)
+            elif kind == "s_zero":
+                der = _der(r_, 0)
+            elif kind == "der_trailing":
+                der = der + b"\x00"
+            elif kind == "der_short":
+                der = der[:-1]
+            htb = {"hashtype_01": 0x01, "hashtype_45": 0x45}.get(kind, ht)
+            sigpush = der + bytes([htb])
+            if kind == "wrong_pubkey":
+                pub = pubs[(j + 1) % nk] if nk > 1 else o.pubkey_create(seckey(10**6), True)
+            if kind == "empty_sig":
+                script_sig = b"\x00" + bytes([len(pub)]) + pub
+            elif kind == "three_pushes":
+                script_sig = b"\x01\x07" + bytes([len(sigpush)]) + sigpush + bytes([len(pub)]) + pub
+            elif kind == "pushdata1":
+                script_sig = b"\x4c" + bytes([len(sigpush)]) + sigpush + bytes([len(pub)]) + pub
+            else:
+                script_sig = bytes([len(sigpush)]) + sigpush + bytes([len(pub)]) + pub
         else:
             filler = hashlib.sha256(SEED + b"fill" + i.to_bytes(8, "little")).digest()
             script_sig = bytes([72]) + (filler * 3)[:72] + bytes([33]) + pubs[j]
         txs.append(build(script_sig))
-        prev_spk.append(spks[j])
+        prev_spk.append(spk)
         prev_amt.append(amount)
     body = _compact(len(txs)) + b"".join(txs)
     root, _ = o.merkle_root(b"".join(o.sha256d(t) for t in txs))
