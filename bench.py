@@ -86,6 +86,53 @@ def cpu_baseline(msg, pub, sig, budget_s=12.0):
             "sample": "first %d of the %d-signature batch, %.1f s wall, %d threads" % (sample, n, dt, cores)}
 
 
+def block_bench(eng, args):
+    """Secondary measurement (BASELINE.json configs[2], "8 MB blocks validated/sec"): one synthetic post-fork block of
+    41,650 one-input P2PKH transactions through bcp_gpu_block_connect_p2pkh (host framing scan, H2D of the raw
+    block + spent outputs, txids, Merkle root, per-input script checks, batched ECDSA, verdict read-back — all
+    inside the timed region), next to the reference's CPU path for the same block: CBlock deserialization + txids +
+    BlockMerkleRoot (single thread, as in CheckBlock) and VerifyScript per input on all host threads
+    (what CCheckQueue<CScriptCheck> fans out)."""
+    import numpy as np
+    import synth
+    from oracle import pyoracle as po
+
+    t0 = time.perf_counter()
+    blk, spk, amt = synth.synthetic_block(args.block_txs, True, with_prevouts=True)
+    gen_s = time.perf_counter() - t0
+    res = eng.block_connect_p2pkh(blk, spk, amt, synth.POSTFORK_FLAGS)  # warm-up + correctness
+    assert res["all_ok"] and res["root"] == blk[36:68] and not res["mutated"]
+    reps = 5
+    t0 = time.perf_counter()
+    for _ in range(reps):
+        res = eng.block_connect_p2pkh(blk, spk, amt, synth.POSTFORK_FLAGS)
+    gpu_s = (time.perf_counter() - t0) / reps
+    out = {"block_bytes": len(blk), "inputs": len(spk), "gpu_ms_per_block": gpu_s * 1e3, "gpu_blocks_per_s": 1.0 / gpu_s,
+           "gpu_inputs_per_s": len(spk) / gpu_s, "gen_seconds": gen_s,
+           "timed": "bcp_gpu_block_connect_p2pkh end to end (host scan + H2D + kernels + D2H), pageable host buffers"}
+    cores = os.cpu_count() or 1
+    if po.have_ref():
+        r = po.ref()
+        t0 = time.perf_counter()
+        n, _, root, _ = r.block_txids(blk, False, max_tx=len(spk) + 8)
+        t_hash = time.perf_counter() - t0
+        t0 = time.perf_counter()
+        err = r.block_script_errors(blk, False, spk, amt, synth.POSTFORK_FLAGS, cores)
+        t_chk = time.perf_counter() - t0
+        assert not err.any() and root == blk[36:68]
+        out.update({"cpu_kind": "reference", "cpu_cores": cores, "cpu_ms_txids_merkle_1thread": t_hash * 1e3,
+                    "cpu_ms_script_checks_all_threads": t_chk * 1e3, "cpu_blocks_per_s": 1.0 / (t_hash + t_chk)})
+    else:
+        o = po.oracle()
+        t0 = time.perf_counter()
+        err = o.block_script_errors(blk, False, spk, amt, synth.POSTFORK_FLAGS, cores)
+        o.block_txids(blk, False, max_tx=len(spk) + 8)
+        t_all = time.perf_counter() - t0
+        out.update({"cpu_kind": "port", "cpu_cores": cores, "cpu_blocks_per_s": 1.0 / t_all})
+    out["speedup_vs_cpu"] = out["gpu_blocks_per_s"] / out["cpu_blocks_per_s"]
+    return out
+
+
 def run_reference(args):
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
@@ -127,6 +174,8 @@ def main():
     ap.add_argument("--sigs", type=int, default=1000000, help="signatures per GPU per step")
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-block", action="store_true", help="skip the secondary 8 MB block measurement (configs[2])")
+    ap.add_argument("--block-txs", type=int, default=41650)
     args = ap.parse_args()
     if args.impl == "reference":
         return run_reference(args)
@@ -262,6 +311,8 @@ def main():
     }
     if not args.no_cpu_baseline:
         line["cpu_baseline"] = cpu_baseline(msg, pub, sig)
+    if not args.no_block:
+        line["block8mb"] = block_bench(eng, args)
     print(json.dumps(line))
     if dist:
         td.destroy_process_group()

@@ -114,6 +114,25 @@ class Engine:
                                           out.ctypes.data), "bcp_gpu_sha256d_batch")
         return out
 
+    # ---- whole block
+    def block_connect_p2pkh(self, blk, spks, amounts, flags, legacy_header=False, want_txids=False):
+        """One call per block: returns dict(txids, root, mutated, script_err (n_inputs,), all_ok)."""
+        blk = np.frombuffer(bytes(blk), dtype=np.uint8) if not isinstance(blk, np.ndarray) else _np(blk)
+        n = len(spks)
+        cat = np.frombuffer(b"".join(spks) or b"\x00", dtype=np.uint8)
+        off = np.zeros(n + 1, dtype=np.uint32)
+        off[1:] = np.cumsum([len(s) for s in spks])
+        am = np.ascontiguousarray(amounts, dtype=np.int64)
+        err = np.full(n, 253, dtype=np.uint8)
+        root = (C.c_uint8 * 32)()
+        mut, allok = C.c_int(0), C.c_int(0)
+        txids = np.zeros((blk.size // 60 + 2, 32), dtype=np.uint8) if want_txids else None
+        check(lib().bcp_gpu_block_connect_p2pkh(self.device, blk.ctypes.data, blk.size, int(legacy_header), cat.ctypes.data,
+                                                off.ctypes.data, am.ctypes.data if n else None, n, flags,
+                                                txids.ctypes.data if want_txids else None, root, C.byref(mut),
+                                                err.ctypes.data if n else None, C.byref(allok)), "bcp_gpu_block_connect_p2pkh")
+        return {"txids": txids, "root": bytes(root), "mutated": bool(mut.value), "script_err": err, "all_ok": bool(allok.value)}
+
     # ---- Equihash
     def equihash_verify_batch(self, n, k, hdrs, want_hash=True):
         """hdrs: (count, hdr_len) uint8 serialized post-fork headers -> (ok (count,), hash (count,32))."""

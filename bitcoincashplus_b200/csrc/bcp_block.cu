@@ -1,0 +1,202 @@
+// bcp_block.cu — one call per block: txids + Merkle root + per-input P2PKH script checks with batched ECDSA.
+// This is row N1 of SURVEY.md §8(f) ("GPU sighash + P2PKH template matcher") on top of the §8(a) kernels: the
+// per-input work of CScriptCheck::operator() (src/validation.cpp:1350-1359) for the dominant script shape is
+// moved to the device, so a block is validated from its raw bytes plus the spent outputs (scriptPubKey, amount)
+// that ConnectBlock already fetched from the UTXO view (src/validation.cpp:1460-1471).
+//
+//   host     bcp_block_index_inputs: framing scan (tx offsets, per-input offsets; sequential byte parsing)
+//   k_sha256d_msgs + k_merkle_levels   txids, Merkle root, mutated flag              (bcp_hash.cu)
+//   k_tx_midstate    one thread per transaction: hashPrevouts / hashSequence / hashOutputs
+//   k_p2pkh_extract  one thread per input: template match, HASH160, DER / low-S / hashtype / pubkey rules,
+//                    FORKID sighash -> (sighash, pubkey, r||s) triple + status
+//   k_ecdsa_prep + k_ecdsa_point       the batched verification                      (bcp_ecdsa.cu)
+//   k_script_finish  status + verdict -> ScriptError per input
+#include "bcp_ctx.cuh"
+#include "script.cuh"
+#include <cstring>
+#include <vector>
+
+__global__ void __launch_bounds__(128) k_tx_midstate(const uint8_t *__restrict__ blk, const uint32_t *__restrict__ tx_off,
+                                                     size_t ntx, uint8_t *__restrict__ mid) {
+    size_t t = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (t >= ntx) return;
+    tx_midstate(mid + t * BCP_TXMID_BYTES, blk + tx_off[t], tx_off[t + 1] - tx_off[t]);
+}
+
+__global__ void __launch_bounds__(128)
+    k_p2pkh_extract(const uint8_t *__restrict__ blk, const uint32_t *__restrict__ tx_off, const uint32_t *__restrict__ in_off,
+                    const uint32_t *__restrict__ in_tx, const uint32_t *__restrict__ in_n, size_t nin,
+                    const uint8_t *__restrict__ spk, const uint32_t *__restrict__ spk_off, const int64_t *__restrict__ amounts,
+                    const uint8_t *__restrict__ mid, uint8_t *__restrict__ status, uint8_t *__restrict__ msg32,
+                    uint8_t *__restrict__ pub65, uint8_t *__restrict__ sig64) {
+    size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= nin) return;
+    const uint32_t t = in_tx[i];
+    const uint32_t o = tx_off[t];
+    status[i] = (uint8_t)p2pkh_extract_one(blk + o, tx_off[t + 1] - o, in_off[i] - o, in_n[i], spk + spk_off[i],
+                                           spk_off[i + 1] - spk_off[i], amounts[i], mid + (size_t)t * BCP_TXMID_BYTES,
+                                           msg32 + 32 * i, pub65 + 65 * i, sig64 + 64 * i);
+}
+
+__global__ void k_script_finish(const uint8_t *__restrict__ status, const uint8_t *__restrict__ ok, size_t nin,
+                                uint8_t *__restrict__ err, int *__restrict__ all_ok) {
+    size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= nin) return;
+    uint8_t s = status[i];
+    uint8_t e = s == BCP_SCRIPT_PENDING ? (ok[i] ? BCP_SCRIPT_OK : BCP_SCRIPT_ERR_SIG_NULLFAIL) : s;
+    err[i] = e;
+    if (e != BCP_SCRIPT_OK) atomicAnd(all_ok, 0);
+}
+
+static int rd_compact_h(const uint8_t *p, size_t len, size_t *pos, uint64_t *v) {
+    if (*pos >= len) return 0;
+    uint8_t ch = p[(*pos)++];
+    if (ch < 253) { *v = ch; return 1; }
+    int nb = ch == 253 ? 2 : ch == 254 ? 4 : 8;
+    if (*pos + nb > len) return 0;
+    uint64_t x = 0;
+    for (int i = 0; i < nb; i++) x |= (uint64_t)p[*pos + i] << (8 * i);
+    *pos += nb;
+    *v = x;
+    return 1;
+}
+
+extern "C" {
+
+// Framing scan that also lists every non-coinbase input (CTransaction::IsCoinBase: a single input with a null
+// prevout, src/primitives/transaction.h): in_off = byte offset of the input's outpoint, in_tx = its transaction,
+// in_n = its ordinal in that transaction.  Returns the number of inputs (-1 malformed, -2 capacity); *ntx_out = ntx.
+BCP_API long bcp_block_index_inputs(const uint8_t *blk, size_t len, int legacy_header, uint32_t *tx_off, size_t max_tx,
+                                    uint32_t *in_off, uint32_t *in_tx, uint32_t *in_n, size_t max_inputs, long *ntx_out) {
+    long ntx = bcp_block_index(blk, len, legacy_header, tx_off, max_tx);
+    if (ntx < 0) return ntx;
+    if (ntx_out) *ntx_out = ntx;
+    size_t cnt = 0;
+    for (long t = 0; t < ntx; t++) {
+        size_t pos = tx_off[t] + 4;
+        uint64_t nin, sl;
+        if (!rd_compact_h(blk, len, &pos, &nin)) return -1;
+        bool coinbase = false;
+        if (nin == 1 && pos + 36 <= len) {
+            coinbase = true;
+            for (int b = 0; b < 32; b++) coinbase = coinbase && blk[pos + b] == 0;
+            for (int b = 32; b < 36; b++) coinbase = coinbase && blk[pos + b] == 0xFF;
+        }
+        for (uint64_t i = 0; i < nin; i++) {
+            if (!coinbase) {
+                if (cnt >= max_inputs) return -2;
+                in_off[cnt] = (uint32_t)pos; in_tx[cnt] = (uint32_t)t; in_n[cnt] = (uint32_t)i;
+                cnt++;
+            }
+            pos += 36;
+            if (!rd_compact_h(blk, len, &pos, &sl)) return -1;
+            pos += sl + 4;
+        }
+    }
+    return (long)cnt;
+}
+
+#define BCP_FLAGS_POSTFORK_REQUIRED ((1u << 1) | (1u << 2) | (1u << 3) | (1u << 14) | (1u << 16))
+#define BCP_FLAG_ALLOW_NON_FORKID (1u << 17)
+
+BCP_API int bcp_gpu_block_connect_p2pkh(int device, const uint8_t *blk, size_t len, int legacy_header, const uint8_t *spk,
+                                        const uint32_t *spk_off, const int64_t *amounts, size_t n_inputs, uint32_t flags,
+                                        uint8_t *txids, uint8_t root32[32], int *mutated, uint8_t *script_err, int *all_ok) {
+    bcp_ctx *c = bcp_get_ctx(device);
+    if (!c) return BCP_ERR_NOT_INIT;
+    if (!blk || !root32 || (n_inputs && (!spk || !spk_off || !amounts || !script_err))) {
+        bcp_set_error("bcp_gpu_block_connect_p2pkh: NULL buffer");
+        return BCP_ERR_INVALID;
+    }
+    if ((flags & BCP_FLAGS_POSTFORK_REQUIRED) != BCP_FLAGS_POSTFORK_REQUIRED || (flags & BCP_FLAG_ALLOW_NON_FORKID)) {
+        bcp_set_error("bcp_gpu_block_connect_p2pkh: the fast path implements the post-fork script flags "
+                      "(STRICTENC|DERSIG|LOW_S|NULLFAIL|SIGHASH_FORKID, no ALLOW_NON_FORKID); got 0x%x", flags);
+        return BCP_ERR_INVALID;
+    }
+    if (len > 0xFFFFFFF0ull) { bcp_set_error("block too large"); return BCP_ERR_INVALID; }
+    // host: framing scan
+    const size_t max_tx = len / 60 + 2, max_in = len / 41 + 2;
+    std::vector<uint32_t> tx_off(max_tx + 1), in_off(max_in), in_tx(max_in), in_n(max_in);
+    long ntx = 0;
+    long nin = bcp_block_index_inputs(blk, len, legacy_header, tx_off.data(), max_tx, in_off.data(), in_tx.data(), in_n.data(),
+                                      max_in, &ntx);
+    if (nin < 0) { bcp_set_error("bcp_gpu_block_connect_p2pkh: malformed block"); return BCP_ERR_INVALID; }
+    if ((size_t)nin != n_inputs) {
+        bcp_set_error("bcp_gpu_block_connect_p2pkh: block has %ld non-coinbase inputs, caller described %zu spent outputs", nin,
+                      n_inputs);
+        return BCP_ERR_INVALID;
+    }
+    std::lock_guard<std::mutex> lk(c->mu);
+    BCP_CUDA(cudaSetDevice(device));
+    auto up = [](size_t x) { return (x + 255) / 256 * 256; };
+    const size_t spk_bytes = n_inputs ? spk_off[n_inputs] : 0;
+    size_t o = 0;
+    const size_t o_blk = o; o += up(len + 8);
+    const size_t o_txoff = o; o += up((ntx + 1) * 4);
+    const size_t o_inoff = o; o += up(nin * 4 + 4);
+    const size_t o_intx = o; o += up(nin * 4 + 4);
+    const size_t o_inn = o; o += up(nin * 4 + 4);
+    const size_t o_spk = o; o += up(spk_bytes + 8);
+    const size_t o_spkoff = o; o += up((nin + 1) * 4);
+    const size_t o_amt = o; o += up(nin * 8 + 8);
+    const size_t o_txid = o; o += up((size_t)ntx * 32 + 32);
+    const size_t o_mtmp = o; o += up(bcp_merkle_tmp_words(ntx) * 4);
+    const size_t o_root = o; o += 256; /* root[32], mutated(int), all_ok(int) */
+    const size_t o_mid = o; o += up((size_t)ntx * BCP_TXMID_BYTES + 16);
+    const size_t o_stat = o; o += up(nin + 8);
+    const size_t o_msg = o; o += up((size_t)nin * 32 + 32);
+    const size_t o_pub = o; o += up((size_t)nin * 65 + 65);
+    const size_t o_sig = o; o += up((size_t)nin * 64 + 64);
+    const size_t o_ok = o; o += up(nin + 8);
+    const size_t o_err = o; o += up(nin + 8);
+    int rc = bcp_ctx_reserve_stage(c, o);
+    if (rc != BCP_OK) return rc;
+    rc = bcp_ctx_reserve_scratch(c, bcp_gpu_ecdsa_scratch_bytes(nin));
+    if (rc != BCP_OK) return rc;
+    uint8_t *d = c->stage;
+    cudaStream_t st = c->stream;
+    BCP_CUDA(cudaMemcpyAsync(d + o_blk, blk, len, cudaMemcpyHostToDevice, st));
+    BCP_CUDA(cudaMemcpyAsync(d + o_txoff, tx_off.data(), (ntx + 1) * 4, cudaMemcpyHostToDevice, st));
+    uint32_t *d_txoff = reinterpret_cast<uint32_t *>(d + o_txoff);
+    // txids + Merkle
+    rc = bcp_sha256d_offsets_dev(c, d + o_blk, d_txoff, ntx, d + o_txid, st);
+    if (rc != BCP_OK) return rc;
+    int *d_flags = reinterpret_cast<int *>(d + o_root + 32);
+    rc = bcp_merkle_dev(c, d + o_txid, ntx, d + o_root, d_flags, reinterpret_cast<uint32_t *>(d + o_mtmp), st);
+    if (rc != BCP_OK) return rc;
+    int one = 1;
+    BCP_CUDA(cudaMemcpyAsync(d_flags + 1, &one, sizeof(int), cudaMemcpyHostToDevice, st));
+    if (nin) {
+        BCP_CUDA(cudaMemcpyAsync(d + o_inoff, in_off.data(), nin * 4, cudaMemcpyHostToDevice, st));
+        BCP_CUDA(cudaMemcpyAsync(d + o_intx, in_tx.data(), nin * 4, cudaMemcpyHostToDevice, st));
+        BCP_CUDA(cudaMemcpyAsync(d + o_inn, in_n.data(), nin * 4, cudaMemcpyHostToDevice, st));
+        BCP_CUDA(cudaMemcpyAsync(d + o_spk, spk, spk_bytes, cudaMemcpyHostToDevice, st));
+        BCP_CUDA(cudaMemcpyAsync(d + o_spkoff, spk_off, (nin + 1) * 4, cudaMemcpyHostToDevice, st));
+        BCP_CUDA(cudaMemcpyAsync(d + o_amt, amounts, nin * 8, cudaMemcpyHostToDevice, st));
+        k_tx_midstate<<<(unsigned)((ntx + 127) / 128), 128, 0, st>>>(d + o_blk, d_txoff, ntx, d + o_mid);
+        k_p2pkh_extract<<<(unsigned)((nin + 127) / 128), 128, 0, st>>>(
+            d + o_blk, d_txoff, reinterpret_cast<uint32_t *>(d + o_inoff), reinterpret_cast<uint32_t *>(d + o_intx),
+            reinterpret_cast<uint32_t *>(d + o_inn), nin, d + o_spk, reinterpret_cast<uint32_t *>(d + o_spkoff),
+            reinterpret_cast<int64_t *>(d + o_amt), d + o_mid, d + o_stat, d + o_msg, d + o_pub, d + o_sig);
+        BCP_CUDA(cudaGetLastError());
+        rc = bcp_ecdsa_launch(c, d + o_msg, d + o_pub, d + o_sig, nin, BCP_ECDSA_FLAG_NORMALIZE_S, d + o_ok,
+                              reinterpret_cast<uint32_t *>(c->scratch), st);
+        if (rc != BCP_OK) return rc;
+        k_script_finish<<<(unsigned)((nin + 255) / 256), 256, 0, st>>>(d + o_stat, d + o_ok, nin, d + o_err, d_flags + 1);
+        BCP_CUDA(cudaGetLastError());
+        BCP_CUDA(cudaMemcpyAsync(script_err, d + o_err, nin, cudaMemcpyDeviceToHost, st));
+    }
+    if (txids) BCP_CUDA(cudaMemcpyAsync(txids, d + o_txid, (size_t)ntx * 32, cudaMemcpyDeviceToHost, st));
+    uint8_t res[40];
+    BCP_CUDA(cudaMemcpyAsync(res, d + o_root, 40, cudaMemcpyDeviceToHost, st));
+    BCP_CUDA(cudaStreamSynchronize(st));
+    memcpy(root32, res, 32);
+    int m, a;
+    memcpy(&m, res + 32, 4);
+    memcpy(&a, res + 36, 4);
+    if (mutated) *mutated = m ? 1 : 0;
+    if (all_ok) *all_ok = a ? 1 : 0;
+    return BCP_OK;
+}
+
+} // extern "C"

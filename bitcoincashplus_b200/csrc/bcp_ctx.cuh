@@ -28,6 +28,15 @@ int bcp_cuda_fail(cudaError_t e, const char *what);
 int bcp_ctx_reserve_scratch(bcp_ctx *c, size_t bytes);
 int bcp_ctx_reserve_stage(bcp_ctx *c, size_t bytes);
 
+// internal cross-file entry points
+int bcp_ecdsa_launch(bcp_ctx *c, const uint8_t *d_msg, const uint8_t *d_pub, const uint8_t *d_sig, size_t n, uint32_t flags,
+                     uint8_t *d_ok, uint32_t *d_scratch, cudaStream_t st);            // bcp_ecdsa.cu
+int bcp_sha256d_offsets_dev(bcp_ctx *c, const uint8_t *d_data, const uint32_t *d_off, size_t count, uint8_t *d_out,
+                            cudaStream_t st);                                          // bcp_hash.cu
+int bcp_merkle_dev(bcp_ctx *c, const uint8_t *d_leaves, size_t n, uint8_t *d_root32, int *d_mut, uint32_t *d_tmp,
+                   cudaStream_t st);                                                   // bcp_hash.cu
+size_t bcp_merkle_tmp_words(size_t n);                                                 // bcp_hash.cu
+
 #define BCP_CUDA(call)                                          \
     do {                                                        \
         cudaError_t e__ = (call);                               \

@@ -132,7 +132,7 @@ int bcp_ecdsa_build_tables(bcp_ctx *c) {
 }
 
 // d_scratch: bcp_gpu_ecdsa_scratch_bytes(n) bytes = [records of one slice][tables of one slice]
-static int launch_verify(bcp_ctx *c, const uint8_t *d_msg, const uint8_t *d_pub, const uint8_t *d_sig, size_t n,
+int bcp_ecdsa_launch(bcp_ctx *c, const uint8_t *d_msg, const uint8_t *d_pub, const uint8_t *d_sig, size_t n,
                          uint32_t flags, uint8_t *d_ok, uint32_t *d_scratch, cudaStream_t st) {
     size_t cap = n < BCP_SLICE ? n : BCP_SLICE;
     cap = (cap + BCP_POINT_THREADS - 1) / BCP_POINT_THREADS * BCP_POINT_THREADS;
@@ -178,7 +178,7 @@ int bcp_gpu_ecdsa_verify_batch_dev(int device, const uint8_t *d_msg32, const uin
     BCP_CUDA(cudaSetDevice(device));
     int rc = bcp_ctx_reserve_scratch(c, bcp_gpu_ecdsa_scratch_bytes(n));
     if (rc != BCP_OK) return rc;
-    return launch_verify(c, d_msg32, d_pub65, d_sig64, n, flags, d_ok, reinterpret_cast<uint32_t *>(c->scratch),
+    return bcp_ecdsa_launch(c, d_msg32, d_pub65, d_sig64, n, flags, d_ok, reinterpret_cast<uint32_t *>(c->scratch),
                          stream ? (cudaStream_t)stream : c->stream);
 }
 
@@ -237,7 +237,7 @@ int bcp_gpu_ecdsa_verify_batch(int device, const uint8_t *msg32, const uint8_t *
         BCP_CUDA(cudaMemcpyAsync(d_msg, msg32 + off * 32, m * 32, cudaMemcpyHostToDevice, st[k]));
         BCP_CUDA(cudaMemcpyAsync(d_pub, pub65 + off * 65, m * 65, cudaMemcpyHostToDevice, st[k]));
         BCP_CUDA(cudaMemcpyAsync(d_sig, sig64 + off * 64, m * 64, cudaMemcpyHostToDevice, st[k]));
-        rc = launch_verify(c, d_msg, d_pub, d_sig, m, flags, d_ok, d_rec, st[k]);
+        rc = bcp_ecdsa_launch(c, d_msg, d_pub, d_sig, m, flags, d_ok, d_rec, st[k]);
         if (rc != BCP_OK) return rc;
         BCP_CUDA(cudaMemcpyAsync(ok + off, d_ok, m, cudaMemcpyDeviceToHost, st[k]));
     }

@@ -141,6 +141,19 @@ static int merkle_dev(bcp_ctx *c, const uint8_t *d_leaves, size_t n, uint8_t *d_
 }
 static size_t merkle_tmp_words(size_t n) { return 2 * (((n + MERKLE_NODES - 1) / MERKLE_NODES) * 8) + 16; }
 
+int bcp_sha256d_offsets_dev(bcp_ctx *c, const uint8_t *d_data, const uint32_t *d_off, size_t count, uint8_t *d_out,
+                            cudaStream_t st) {
+    if (count == 0) return BCP_OK;
+    k_sha256d_msgs<<<(unsigned)((count + 127) / 128), 128, 0, st>>>(d_data, d_off, 0, 0, count, d_out);
+    BCP_CUDA(cudaGetLastError());
+    return BCP_OK;
+}
+int bcp_merkle_dev(bcp_ctx *c, const uint8_t *d_leaves, size_t n, uint8_t *d_root32, int *d_mut, uint32_t *d_tmp,
+                   cudaStream_t st) {
+    return merkle_dev(c, d_leaves, n, d_root32, d_mut, d_tmp, st);
+}
+size_t bcp_merkle_tmp_words(size_t n) { return merkle_tmp_words(n); }
+
 // fixed-size messages at a fixed stride (serialized block headers)
 int bcp_sha256d_strided_dev(bcp_ctx *c, const uint8_t *d_data, size_t stride, size_t len, size_t count, uint8_t *d_out,
                             cudaStream_t st) {

@@ -128,6 +128,26 @@ BCP_API int bcp_gpu_merkle_root_dev(int device, const uint8_t *d_leaves32, size_
 BCP_API int bcp_gpu_merkle_root_dev_static(int device, const uint8_t *d_leaves32, size_t n, uint8_t *d_root32,
                                            int *d_mutated, void *stream);
 
+/* ---- Whole-block fast path: txids + Merkle root + every input's script check for the
+ *      dominant script shape, from the raw block bytes and the spent outputs ConnectBlock fetched from the UTXO
+ *      view (src/validation.cpp:1460-1471).  Replaces, for P2PKH inputs, the body of CScriptCheck::operator()
+ *      (src/validation.cpp:1350-1359): VerifyScript (src/script/interpreter.cpp:1551) over scriptSig `<sig> <pubkey>` and
+ *      scriptPubKey `DUP HASH160 <20> EQUALVERIFY CHECKSIG`, including SignatureHash's FORKID branch (:1357-1404) and
+ *      PrecomputedTransactionData (:1347-1352), under the post-fork flags of GetBlockScriptFlags (validation.cpp:1803-1852).
+ *   spk / spk_off / amounts   the spent scriptPubKeys (concatenated, spk_off[n_inputs+1]) and values, one per
+ *                             non-coinbase input in block order
+ *   flags                     SCRIPT_VERIFY_* bits as in src/script/interpreter.h:32-121; must contain
+ *                             STRICTENC|DERSIG|LOW_S|NULLFAIL|ENABLE_SIGHASH_FORKID and not ALLOW_NON_FORKID
+ *   script_err[i]             the ScriptError VerifyScript reports for input i (src/script/script_error.h; 0 = OK), or
+ *                             255 when the input is not of this shape and must be run through the host interpreter
+ *   all_ok                    1 iff every script_err is 0 (the `fAllOk` of the check queue)
+ *   txids (optional), root32, mutated   as bcp_gpu_sha256d_txids_merkle */
+BCP_API long bcp_block_index_inputs(const uint8_t *blk, size_t len, int legacy_header, uint32_t *tx_off, size_t max_tx,
+                                    uint32_t *in_off, uint32_t *in_tx, uint32_t *in_n, size_t max_inputs, long *ntx_out);
+BCP_API int bcp_gpu_block_connect_p2pkh(int device, const uint8_t *blk, size_t len, int legacy_header, const uint8_t *spk,
+                                        const uint32_t *spk_off, const int64_t *amounts, size_t n_inputs, uint32_t flags,
+                                        uint8_t *txids, uint8_t root32[32], int *mutated, uint8_t *script_err, int *all_ok);
+
 /* ---- Equihash: CheckEquihashSolution (src/pow.cpp:298-323) == Equihash<N,K>::IsValidSolution
  *      (src/crypto/equihash.cpp:724-770) for `count` serialized post-fork headers (140 bytes || compact
  *      size || solution; src/primitives/block.h:49-73) laid out at `stride` bytes, each `hdr_len` long.

@@ -11,6 +11,8 @@
 #include "../../bitcoincashplus_b200/csrc/ecdsa.cuh"
 #include "../../bitcoincashplus_b200/csrc/sha256.cuh"
 #include "../../bitcoincashplus_b200/csrc/blake2b.cuh"
+#include "../../bitcoincashplus_b200/csrc/ripemd160.cuh"
+#include "../../bitcoincashplus_b200/csrc/script.cuh"
 
 static void fe_from_be(fe &r, const uint8_t *b) { fe_set_b32(r, b); }
 static void fe_to_be(uint8_t *b, fe a) {
@@ -184,6 +186,27 @@ void hs_ecdsa_verify_batch(const uint8_t *msg32, const uint8_t *pub65, const uin
 // ---- hashing device functions
 void hs_sha256d(const uint8_t *data, size_t len, uint8_t *out32) { dev_sha256d_bytes(out32, data, len); }
 void hs_sha256(const uint8_t *data, size_t len, uint8_t *out32) { dev_sha256_bytes(out32, data, len); }
+void hs_hash160(const uint8_t *data, size_t len, uint8_t *out20) {
+    uint32_t s[8], r[5];
+    dev_sha256_words(s, data, len);
+    ripemd160_of_sha256(r, s);
+    for (int i = 0; i < 5; i++)
+        for (int b = 0; b < 4; b++) out20[4 * i + b] = (uint8_t)(r[i] >> (8 * b));
+}
+// Emulates k_tx_midstate + k_p2pkh_extract: status per input and the ECDSA triples
+void hs_block_p2pkh_extract(const uint8_t *blk, const uint32_t *tx_off, size_t ntx, const uint32_t *in_off,
+                            const uint32_t *in_tx, const uint32_t *in_n, size_t nin, const uint8_t *spk,
+                            const uint32_t *spk_off, const int64_t *amounts, uint8_t *status, uint8_t *msg32, uint8_t *pub65,
+                            uint8_t *sig64) {
+    std::vector<uint8_t> mid(ntx * BCP_TXMID_BYTES);
+    for (size_t t = 0; t < ntx; t++) tx_midstate(&mid[t * BCP_TXMID_BYTES], blk + tx_off[t], tx_off[t + 1] - tx_off[t]);
+    for (size_t i = 0; i < nin; i++) {
+        uint32_t t = in_tx[i];
+        status[i] = (uint8_t)p2pkh_extract_one(blk + tx_off[t], tx_off[t + 1] - tx_off[t], in_off[i] - tx_off[t], in_n[i],
+                                               spk + spk_off[i], spk_off[i + 1] - spk_off[i], amounts[i],
+                                               &mid[t * BCP_TXMID_BYTES], msg32 + 32 * i, pub65 + 65 * i, sig64 + 64 * i);
+    }
+}
 void hs_blake2b_final_block(const uint64_t *h_mid, const uint8_t *blk128, uint64_t t0, uint64_t *h_out) {
     uint64_t h[8], m[16];
     for (int i = 0; i < 8; i++) h[i] = h_mid[i];

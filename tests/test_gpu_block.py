@@ -1,0 +1,61 @@
+"""-m gpu: the whole-block fast path (txids + Merkle + P2PKH script checks + batched ECDSA) vs the oracle."""
+import os
+
+import numpy as np
+import pytest
+
+import synth
+
+pytestmark = pytest.mark.gpu
+NT = os.cpu_count() or 1
+
+
+def test_block_with_every_mutation(engine, oracle):
+    kinds = list(synth.INPUT_MUTATIONS)
+    mut = {5 + 7 * i: k for i, k in enumerate(kinds)}
+    blk, spk, amt = synth.synthetic_block(400, True, nkeys=32, with_prevouts=True, mutations=mut)
+    res = engine.block_connect_p2pkh(blk, spk, amt, synth.POSTFORK_FLAGS, want_txids=True)
+    want = oracle.block_script_errors(blk, False, spk, amt, synth.POSTFORK_FLAGS, NT)
+    assert (res["script_err"] == want).all(), np.nonzero(res["script_err"] != want)[0]
+    for i, k in mut.items():
+        exp = synth.INPUT_MUTATIONS[k]
+        assert res["script_err"][i] == (255 if exp is None else exp), k
+    assert not res["all_ok"]
+    n, txids, root, mutated = oracle.block_txids(blk, False)
+    assert res["root"] == root == blk[36:68] and res["mutated"] == mutated
+    assert (res["txids"][:n] == txids).all()
+
+
+def test_all_valid_block_and_single_bad_input(engine, oracle):
+    blk, spk, amt = synth.synthetic_block(3000, True, nkeys=64, with_prevouts=True)
+    res = engine.block_connect_p2pkh(blk, spk, amt, synth.POSTFORK_FLAGS)
+    assert res["all_ok"] and not res["script_err"].any()
+    blk2, spk2, amt2 = synth.synthetic_block(3000, True, nkeys=64, with_prevouts=True, bad_inputs=(1777,))
+    res2 = engine.block_connect_p2pkh(blk2, spk2, amt2, synth.POSTFORK_FLAGS)
+    assert not res2["all_ok"]
+    assert list(np.nonzero(res2["script_err"])[0]) == [1777] and res2["script_err"][1777] == 31
+    # wrong amount in the UTXO side table changes the sighash: NULLFAIL exactly there
+    amt3 = list(amt)
+    amt3[5] += 1
+    res3 = engine.block_connect_p2pkh(blk, spk, amt3, synth.POSTFORK_FLAGS)
+    assert list(np.nonzero(res3["script_err"])[0]) == [5] and res3["script_err"][5] == 31
+    want = oracle.block_script_errors(blk, False, spk, amt3, synth.POSTFORK_FLAGS, NT)
+    assert (res3["script_err"] == want).all()
+
+
+def test_flag_sets_outside_the_fast_path_are_refused(engine):
+    import bitcoincashplus_b200 as bcp
+
+    blk, spk, amt = synth.synthetic_block(3, True, nkeys=2, with_prevouts=True)
+    for flags in (0, synth.POSTFORK_FLAGS & ~(1 << 14), synth.POSTFORK_FLAGS | (1 << 17)):
+        with pytest.raises(bcp.BcpError):
+            engine.block_connect_p2pkh(blk, spk, amt, flags)
+    with pytest.raises(bcp.BcpError):
+        engine.block_connect_p2pkh(blk, spk[:-1], amt[:-1], synth.POSTFORK_FLAGS)
+
+
+def test_empty_block_only_coinbase(engine, oracle):
+    blk = synth.synthetic_block(0, True)
+    res = engine.block_connect_p2pkh(blk, [], [], synth.POSTFORK_FLAGS)
+    n, txids, root, mutated = oracle.block_txids(blk, False)
+    assert n == 1 and res["root"] == root == txids[0].tobytes() and res["all_ok"]

@@ -194,3 +194,35 @@ def test_hash_device_functions(hs, oracle):
         assert bytes(out) == oracle.sha256d(d)
         hs.hs_sha256(C.cast(C.c_char_p(d), u8p), C.c_size_t(ln), out)
         assert bytes(out) == oracle.sha256(d)
+
+
+def test_p2pkh_fast_path_matches_oracle(hs, gcomb, oracle):
+    """Device code of the block fast path (script.cuh: per-tx midstates, per-input template checks, FORKID sighash,
+    HASH160) + the ECDSA pipeline vs the oracle's ScriptError per input, on a block holding every mutation kind."""
+    import synth
+
+    kinds = list(synth.INPUT_MUTATIONS)
+    mut = {2 + 3 * i: k for i, k in enumerate(kinds)}
+    blk, spk, amt = synth.synthetic_block(80, True, nkeys=8, with_prevouts=True, mutations=mut)
+    want = oracle.block_script_errors(blk, False, spk, amt, synth.POSTFORK_FLAGS, os.cpu_count() or 1)
+    ntx, tx_off = oracle.block_index(blk, False)
+    # input index (coinbase skipped): every synthetic tx has one input at offset 5 of the tx
+    nin = ntx - 1
+    in_off = (tx_off[1:ntx] + 5).astype(np.uint32)
+    in_tx = np.arange(1, ntx, dtype=np.uint32)
+    in_n = np.zeros(nin, dtype=np.uint32)
+    cat = np.frombuffer(b"".join(spk), dtype=np.uint8).copy()
+    spk_off = np.zeros(nin + 1, dtype=np.uint32)
+    spk_off[1:] = np.cumsum([len(s) for s in spk])
+    am = np.asarray(amt, dtype=np.int64)
+    status = np.zeros(nin, np.uint8)
+    msg, pub, sig = np.zeros((nin, 32), np.uint8), np.zeros((nin, 65), np.uint8), np.zeros((nin, 64), np.uint8)
+    b = np.frombuffer(blk, dtype=np.uint8).copy()
+    hs.hs_block_p2pkh_extract(b.ctypes.data_as(u8p), tx_off.ctypes.data_as(u32p), C.c_size_t(ntx), in_off.ctypes.data_as(u32p),
+                              in_tx.ctypes.data_as(u32p), in_n.ctypes.data_as(u32p), C.c_size_t(nin), cat.ctypes.data_as(u8p),
+                              spk_off.ctypes.data_as(u32p), am.ctypes.data_as(C.POINTER(C.c_int64)), status.ctypes.data_as(u8p),
+                              msg.ctypes.data_as(u8p), pub.ctypes.data_as(u8p), sig.ctypes.data_as(u8p))
+    ok = _run(hs, gcomb, msg, pub, sig, flags=1)
+    got = np.where(status == 254, np.where(ok == 1, 0, 31), status).astype(np.uint8)
+    assert (got == want).all(), [(i, mut.get(i), int(got[i]), int(want[i])) for i in np.nonzero(got != want)[0]]
+    assert set(want) >= {0, 2, 11, 22, 23, 26, 28, 31, 36, 255}
