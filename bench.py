@@ -86,7 +86,7 @@ def cpu_baseline(msg, pub, sig, budget_s=12.0):
             "sample": "first %d of the %d-signature batch, %.1f s wall, %d threads" % (sample, n, dt, cores)}
 
 
-def block_bench(eng, args):
+def block_bench(eng, args, bcp):
     """Secondary measurement (BASELINE.json configs[2], "8 MB blocks validated/sec"): one synthetic post-fork block of
     41,650 one-input P2PKH transactions through bcp_gpu_block_connect_p2pkh (host framing scan, H2D of the raw
     block + spent outputs, txids, Merkle root, per-input script checks, batched ECDSA, verdict read-back — all
@@ -100,16 +100,30 @@ def block_bench(eng, args):
     t0 = time.perf_counter()
     blk, spk, amt = synth.synthetic_block(args.block_txs, True, with_prevouts=True)
     gen_s = time.perf_counter() - t0
-    res = eng.block_connect_p2pkh(blk, spk, amt, synth.POSTFORK_FLAGS)  # warm-up + correctness
+    # marshal once, as a node would hand over its buffers: raw block bytes, concatenated scriptPubKeys + offsets, amounts
+    L = bcp.lib()
+
+    def pinned(a):
+        """copy a numpy array into pinned host memory (bcp_gpu_host_alloc) and view it as numpy"""
+        p = L.bcp_gpu_host_alloc(max(a.nbytes, 1))
+        out = np.ctypeslib.as_array(C.cast(p, C.POINTER(C.c_uint8)), shape=(max(a.nbytes, 1),))[: a.nbytes].view(a.dtype)
+        out[...] = a
+        return out
+
+    off0 = np.zeros(len(spk) + 1, dtype=np.uint32)
+    off0[1:] = np.cumsum([len(x) for x in spk])
+    blk_np = pinned(np.frombuffer(blk, dtype=np.uint8))
+    cat, off, am = pinned(np.frombuffer(b"".join(spk), dtype=np.uint8)), pinned(off0), pinned(np.asarray(amt, dtype=np.int64))
+    res = eng.block_connect_p2pkh(blk_np, (cat, off), am, synth.POSTFORK_FLAGS)  # warm-up + correctness
     assert res["all_ok"] and res["root"] == blk[36:68] and not res["mutated"]
-    reps = 5
+    reps = 10
     t0 = time.perf_counter()
     for _ in range(reps):
-        res = eng.block_connect_p2pkh(blk, spk, amt, synth.POSTFORK_FLAGS)
+        res = eng.block_connect_p2pkh(blk_np, (cat, off), am, synth.POSTFORK_FLAGS)
     gpu_s = (time.perf_counter() - t0) / reps
     out = {"block_bytes": len(blk), "inputs": len(spk), "gpu_ms_per_block": gpu_s * 1e3, "gpu_blocks_per_s": 1.0 / gpu_s,
            "gpu_inputs_per_s": len(spk) / gpu_s, "gen_seconds": gen_s,
-           "timed": "bcp_gpu_block_connect_p2pkh end to end (host scan + H2D + kernels + D2H), pageable host buffers"}
+           "timed": "bcp_gpu_block_connect_p2pkh end to end (host framing scan + H2D + kernels + D2H), pinned host buffers"}
     cores = os.cpu_count() or 1
     if po.have_ref():
         r = po.ref()
@@ -131,6 +145,38 @@ def block_bench(eng, args):
         out.update({"cpu_kind": "port", "cpu_cores": cores, "cpu_blocks_per_s": 1.0 / t_all})
     out["speedup_vs_cpu"] = out["gpu_blocks_per_s"] / out["cpu_blocks_per_s"]
     return out
+
+
+def equihash_bench(eng):
+    """Secondary measurement (BASELINE.json configs[3]): Equihash (200,9) verification + SHA-256d header hashing over
+    10,000 serialized headers (the committed solver-found solutions tiled, half of them corrupted), through the
+    host-pointer C-ABI call, next to the reference's IsValidSolution on all host threads."""
+    import numpy as np
+    from oracle import pyoracle as po
+
+    hdrs = np.load(os.path.join(ROOT, "tests", "golden", "equihash_200_9.npz"))["headers"]
+    rng = np.random.default_rng(4)
+    allh = np.tile(hdrs, ((10000 + len(hdrs) - 1) // len(hdrs), 1))[:10000].copy()
+    corrupt = rng.random(10000) < 0.5
+    for i in np.nonzero(corrupt)[0]:
+        allh[i, 143 + int(rng.integers(0, 1344))] ^= 1 << int(rng.integers(0, 8))
+    ok, hashes = eng.equihash_verify_batch(200, 9, allh)
+    assert ok[~corrupt].all() and not ok[corrupt].all()
+    reps = 5
+    t0 = time.perf_counter()
+    for _ in range(reps):
+        eng.equihash_verify_batch(200, 9, allh)
+    gpu_s = (time.perf_counter() - t0) / reps
+    cores = os.cpu_count() or 1
+    impl = po.ref() if po.have_ref() else po.oracle()
+    t0 = time.perf_counter()
+    want = impl.equihash_verify_batch(200, 9, allh, cores)
+    cpu_s = time.perf_counter() - t0
+    assert (want.astype(bool) == ok.astype(bool)).all()
+    return {"headers": 10000, "header_bytes": int(allh.shape[1]), "gpu_ms": gpu_s * 1e3, "gpu_headers_per_s": 10000 / gpu_s,
+            "cpu_kind": impl.kind, "cpu_cores": cores, "cpu_headers_per_s": 10000 / cpu_s,
+            "speedup_vs_cpu": (10000 / gpu_s) / (10000 / cpu_s),
+            "timed": "bcp_gpu_equihash_verify_batch incl. H2D of 14.9 MB, verdicts + header hashes D2H"}
 
 
 def run_reference(args):
@@ -312,7 +358,8 @@ def main():
     if not args.no_cpu_baseline:
         line["cpu_baseline"] = cpu_baseline(msg, pub, sig)
     if not args.no_block:
-        line["block8mb"] = block_bench(eng, args)
+        line["block8mb"] = block_bench(eng, args, bcp)
+        line["equihash10k"] = equihash_bench(eng)
     print(json.dumps(line))
     if dist:
         td.destroy_process_group()

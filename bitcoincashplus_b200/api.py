@@ -118,10 +118,14 @@ class Engine:
     def block_connect_p2pkh(self, blk, spks, amounts, flags, legacy_header=False, want_txids=False):
         """One call per block: returns dict(txids, root, mutated, script_err (n_inputs,), all_ok)."""
         blk = np.frombuffer(bytes(blk), dtype=np.uint8) if not isinstance(blk, np.ndarray) else _np(blk)
-        n = len(spks)
-        cat = np.frombuffer(b"".join(spks) or b"\x00", dtype=np.uint8)
-        off = np.zeros(n + 1, dtype=np.uint32)
-        off[1:] = np.cumsum([len(s) for s in spks])
+        if isinstance(spks, tuple):  # already marshalled: (concatenated scriptPubKeys, offsets)
+            cat, off = spks
+            n = len(off) - 1
+        else:
+            n = len(spks)
+            cat = np.frombuffer(b"".join(spks) or b"\x00", dtype=np.uint8)
+            off = np.zeros(n + 1, dtype=np.uint32)
+            off[1:] = np.cumsum([len(s) for s in spks])
         am = np.ascontiguousarray(amounts, dtype=np.int64)
         err = np.full(n, 253, dtype=np.uint8)
         root = (C.c_uint8 * 32)()

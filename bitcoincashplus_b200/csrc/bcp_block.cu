@@ -114,48 +114,56 @@ BCP_API int bcp_gpu_block_connect_p2pkh(int device, const uint8_t *blk, size_t l
         return BCP_ERR_INVALID;
     }
     if (len > 0xFFFFFFF0ull) { bcp_set_error("block too large"); return BCP_ERR_INVALID; }
-    // host: framing scan
+    // Device layout is sized from upper bounds (a transaction is at least 60 bytes, an input at least 41) so that
+    // the raw block can start its way to the device BEFORE the host framing scan runs; with a pinned `blk` the copy
+    // and the scan overlap.
     const size_t max_tx = len / 60 + 2, max_in = len / 41 + 2;
-    std::vector<uint32_t> tx_off(max_tx + 1), in_off(max_in), in_tx(max_in), in_n(max_in);
-    long ntx = 0;
-    long nin = bcp_block_index_inputs(blk, len, legacy_header, tx_off.data(), max_tx, in_off.data(), in_tx.data(), in_n.data(),
-                                      max_in, &ntx);
-    if (nin < 0) { bcp_set_error("bcp_gpu_block_connect_p2pkh: malformed block"); return BCP_ERR_INVALID; }
-    if ((size_t)nin != n_inputs) {
-        bcp_set_error("bcp_gpu_block_connect_p2pkh: block has %ld non-coinbase inputs, caller described %zu spent outputs", nin,
-                      n_inputs);
-        return BCP_ERR_INVALID;
-    }
+    if (n_inputs > max_in) { bcp_set_error("bcp_gpu_block_connect_p2pkh: more inputs than the block can hold"); return BCP_ERR_INVALID; }
     std::lock_guard<std::mutex> lk(c->mu);
     BCP_CUDA(cudaSetDevice(device));
     auto up = [](size_t x) { return (x + 255) / 256 * 256; };
     const size_t spk_bytes = n_inputs ? spk_off[n_inputs] : 0;
+    const size_t cap_in = n_inputs + 1;
     size_t o = 0;
     const size_t o_blk = o; o += up(len + 8);
-    const size_t o_txoff = o; o += up((ntx + 1) * 4);
-    const size_t o_inoff = o; o += up(nin * 4 + 4);
-    const size_t o_intx = o; o += up(nin * 4 + 4);
-    const size_t o_inn = o; o += up(nin * 4 + 4);
+    const size_t o_txoff = o; o += up((max_tx + 1) * 4);
+    const size_t o_inoff = o; o += up(cap_in * 4 + 4);
+    const size_t o_intx = o; o += up(cap_in * 4 + 4);
+    const size_t o_inn = o; o += up(cap_in * 4 + 4);
     const size_t o_spk = o; o += up(spk_bytes + 8);
-    const size_t o_spkoff = o; o += up((nin + 1) * 4);
-    const size_t o_amt = o; o += up(nin * 8 + 8);
-    const size_t o_txid = o; o += up((size_t)ntx * 32 + 32);
-    const size_t o_mtmp = o; o += up(bcp_merkle_tmp_words(ntx) * 4);
+    const size_t o_spkoff = o; o += up((cap_in + 1) * 4);
+    const size_t o_amt = o; o += up(cap_in * 8 + 8);
+    const size_t o_txid = o; o += up(max_tx * 32 + 32);
+    const size_t o_mtmp = o; o += up(bcp_merkle_tmp_words(max_tx) * 4);
     const size_t o_root = o; o += 256; /* root[32], mutated(int), all_ok(int) */
-    const size_t o_mid = o; o += up((size_t)ntx * BCP_TXMID_BYTES + 16);
-    const size_t o_stat = o; o += up(nin + 8);
-    const size_t o_msg = o; o += up((size_t)nin * 32 + 32);
-    const size_t o_pub = o; o += up((size_t)nin * 65 + 65);
-    const size_t o_sig = o; o += up((size_t)nin * 64 + 64);
-    const size_t o_ok = o; o += up(nin + 8);
-    const size_t o_err = o; o += up(nin + 8);
+    const size_t o_mid = o; o += up(max_tx * BCP_TXMID_BYTES + 16);
+    const size_t o_stat = o; o += up(cap_in + 8);
+    const size_t o_msg = o; o += up(cap_in * 32 + 32);
+    const size_t o_pub = o; o += up(cap_in * 65 + 65);
+    const size_t o_sig = o; o += up(cap_in * 64 + 64);
+    const size_t o_ok = o; o += up(cap_in + 8);
+    const size_t o_err = o; o += up(cap_in + 8);
     int rc = bcp_ctx_reserve_stage(c, o);
     if (rc != BCP_OK) return rc;
-    rc = bcp_ctx_reserve_scratch(c, bcp_gpu_ecdsa_scratch_bytes(nin));
+    rc = bcp_ctx_reserve_scratch(c, bcp_gpu_ecdsa_scratch_bytes(n_inputs));
     if (rc != BCP_OK) return rc;
     uint8_t *d = c->stage;
     cudaStream_t st = c->stream;
     BCP_CUDA(cudaMemcpyAsync(d + o_blk, blk, len, cudaMemcpyHostToDevice, st));
+    // host: framing scan (overlaps the copy above when blk is pinned)
+    std::vector<uint32_t> &tx_off = c->h_tx_off, &in_off = c->h_in_off, &in_tx = c->h_in_tx, &in_n = c->h_in_n;
+    if (tx_off.size() < max_tx + 1) tx_off.resize(max_tx + 1);
+    if (in_off.size() < cap_in) { in_off.resize(cap_in); in_tx.resize(cap_in); in_n.resize(cap_in); }
+    long ntx = 0;
+    long nin = bcp_block_index_inputs(blk, len, legacy_header, tx_off.data(), max_tx, in_off.data(), in_tx.data(), in_n.data(),
+                                      cap_in, &ntx);
+    if (nin < 0 || (size_t)nin != n_inputs) {
+        cudaStreamSynchronize(st);
+        if (nin == -1) bcp_set_error("bcp_gpu_block_connect_p2pkh: malformed block");
+        else bcp_set_error("bcp_gpu_block_connect_p2pkh: the block's non-coinbase inputs (%ld) do not match the %zu spent "
+                           "outputs the caller described", nin, n_inputs);
+        return BCP_ERR_INVALID;
+    }
     BCP_CUDA(cudaMemcpyAsync(d + o_txoff, tx_off.data(), (ntx + 1) * 4, cudaMemcpyHostToDevice, st));
     uint32_t *d_txoff = reinterpret_cast<uint32_t *>(d + o_txoff);
     // txids + Merkle

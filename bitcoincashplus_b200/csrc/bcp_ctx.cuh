@@ -3,6 +3,7 @@
 #include <cuda_runtime.h>
 #include <mutex>
 #include <string>
+#include <vector>
 #include "../../include/bcp_gpu.h"
 
 #define BCP_MAX_DEVICES 16
@@ -19,6 +20,7 @@ struct bcp_ctx {
     size_t scratch_bytes = 0;
     uint8_t *stage = nullptr;           // device staging for the host-pointer entry points
     size_t stage_bytes = 0;
+    std::vector<uint32_t> h_tx_off, h_in_off, h_in_tx, h_in_n; // host scratch of the block framing scan (reused)
     std::mutex mu;
 };
 
