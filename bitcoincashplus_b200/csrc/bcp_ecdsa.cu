@@ -24,7 +24,9 @@
 #ifndef BCP_POINT_THREADS
 #define BCP_POINT_THREADS 256
 #endif
+#ifndef BCP_POINT_BLOCKS_PER_SM
 #define BCP_POINT_BLOCKS_PER_SM (512 / BCP_POINT_THREADS)
+#endif
 #else
 #define BCP_POINT_THREADS 128
 #define BCP_POINT_BLOCKS_PER_SM 4

@@ -26,13 +26,13 @@ def hs():
     src = os.path.join(HS, "hostsim.cpp")
     hdrs = [os.path.join(ROOT, "bitcoincashplus_b200", "csrc", f) for f in os.listdir(os.path.join(ROOT, "bitcoincashplus_b200", "csrc")) if f.endswith(".cuh")]
     if not os.path.exists(so) or os.path.getmtime(so) < max(os.path.getmtime(p) for p in hdrs + [src]):
-        subprocess.check_call(["g++", "-O2", "-std=c++17", "-fPIC", "-shared", "-o", so, src, "-lpthread"])
+        subprocess.check_call(["g++", "-O2", "-std=c++17", "-DBCP_GCOMB_BITS=12", "-fPIC", "-shared", "-o", so, src, "-lpthread"])
     return C.CDLL(so)
 
 
 @pytest.fixture(scope="module")
 def gcomb(hs):
-    g = np.zeros(22 * 4096 * 16, dtype=np.uint32)
+    g = np.zeros(22 * 4096 * 16, dtype=np.uint32)  # the host build is compiled with -DBCP_GCOMB_BITS=12
     hs.hs_gcomb_build(g.ctypes.data_as(u32p))
     return g
 
