@@ -278,3 +278,52 @@ def synthetic_block(ntx=41650, sign=True, nkeys=4096, bad_inputs=(), with_prevou
     if with_prevouts:
         return blk, prev_spk, prev_amt
     return blk
+
+
+def synthetic_block_multi(ntx=60, nkeys=8, seed=1):
+    """Post-fork block whose transactions have 1..5 inputs and 1..4 outputs, every input signed with a hashtype drawn
+    from all six FORKID types (so SIGHASH_SINGLE with and without a matching output, ANYONECANPAY, NONE are all
+    present).  Returns (block, prevout_spk list, prevout_amounts)."""
+    import random
+
+    o = po.oracle()
+    rnd = random.Random(seed)
+    keys = [seckey(1000 + j) for j in range(nkeys)]
+    pubs = [o.pubkey_create(kb, j % 3 != 2) for j, kb in enumerate(keys)]  # every third key uncompressed
+    spks = [p2pkh_script(pb) for pb in pubs]
+    cb = (2).to_bytes(4, "little") + b"\x01" + bytes(32) + b"\xff\xff\xff\xff" + b"\x04" + (600001).to_bytes(4, "little")
+    cb += b"\xff\xff\xff\xff" + b"\x01" + (1250000000).to_bytes(8, "little") + bytes([25]) + spks[0] + bytes(4)
+    txs = [cb]
+    prev_spk, prev_amt = [], []
+    serial = 0
+    for t in range(ntx):
+        nin, nout = rnd.randint(1, 5), rnd.randint(1, 4)
+        ins = []
+        for i in range(nin):
+            j = rnd.randrange(nkeys)
+            prev = hashlib.sha256(SEED + b"mprev" + serial.to_bytes(8, "little")).digest()
+            serial += 1
+            ins.append((j, prev, rnd.randrange(4), rnd.randrange(1000, 10**9), rnd.choice([0xFFFFFFFF, 0xFFFFFFFE, 5])))
+        outs = b"".join((rnd.randrange(1, 10**8)).to_bytes(8, "little") + bytes([25]) + spks[rnd.randrange(nkeys)] for _ in range(nout))
+        locktime = rnd.choice([0, 0, 500000])
+
+        def build(sigs):
+            b = (2).to_bytes(4, "little") + _compact(nin)
+            for (j, prev, vout, amt_, seq), ss in zip(ins, sigs):
+                b += prev + vout.to_bytes(4, "little") + _compact(len(ss)) + ss + seq.to_bytes(4, "little")
+            return b + _compact(nout) + outs + locktime.to_bytes(4, "little")
+
+        unsigned = build([b""] * nin)
+        sigs = []
+        for i, (j, prev, vout, amt_, seq) in enumerate(ins):
+            ht = rnd.choice([0x41, 0x42, 0x43, 0xC1, 0xC2, 0xC3])
+            sh = o.sighash_forkid(spks[j], unsigned, i, ht, amt_)
+            s64 = o.sign(keys[j], sh)
+            der = _der(int.from_bytes(s64[:32], "big"), int.from_bytes(s64[32:], "big")) + bytes([ht])
+            sigs.append(bytes([len(der)]) + der + bytes([len(pubs[j])]) + pubs[j])
+            prev_spk.append(spks[j])
+            prev_amt.append(amt_)
+        txs.append(build(sigs))
+    body = _compact(len(txs)) + b"".join(txs)
+    root, _ = o.merkle_root(b"".join(o.sha256d(t) for t in txs))
+    return synthetic_header(merkle_root=root) + body, prev_spk, prev_amt

@@ -59,3 +59,41 @@ def test_empty_block_only_coinbase(engine, oracle):
     res = engine.block_connect_p2pkh(blk, [], [], synth.POSTFORK_FLAGS)
     n, txids, root, mutated = oracle.block_txids(blk, False)
     assert n == 1 and res["root"] == root == txids[0].tobytes() and res["all_ok"]
+
+
+def test_multi_input_output_transactions_all_hashtypes(engine, oracle):
+    """1..5 inputs, 1..4 outputs per transaction, all six FORKID hashtypes, compressed and uncompressed keys."""
+    blk, spk, amt = synth.synthetic_block_multi(500, seed=21)
+    res = engine.block_connect_p2pkh(blk, spk, amt, synth.POSTFORK_FLAGS, want_txids=True)
+    assert res["all_ok"] and not res["script_err"].any()
+    n, txids, root, mutated = oracle.block_txids(blk, False)
+    assert res["root"] == root == blk[36:68] and (res["txids"][:n] == txids).all()
+    amt2 = list(amt)
+    bad = [0, 17, len(amt) - 1]
+    for i in bad:
+        amt2[i] ^= 1
+    res2 = engine.block_connect_p2pkh(blk, spk, amt2, synth.POSTFORK_FLAGS)
+    want = oracle.block_script_errors(blk, False, spk, amt2, synth.POSTFORK_FLAGS, NT)
+    assert (res2["script_err"] == want).all() and list(np.nonzero(want)[0]) == bad
+
+
+def test_block_index_inputs_matches_oracle(engine, oracle):
+    import ctypes as C
+
+    import bitcoincashplus_b200 as bcp
+
+    blk, spk, amt = synth.synthetic_block_multi(80, seed=5)
+    L = bcp.lib()
+    b = np.frombuffer(blk, dtype=np.uint8)
+    tx_off = np.zeros(300, np.uint32)
+    arrs = [np.zeros(len(spk), np.uint32) for _ in range(3)]
+    ntx = C.c_long(0)
+    nin = L.bcp_block_index_inputs(b.ctypes.data, len(blk), 0, tx_off.ctypes.data, 299, arrs[0].ctypes.data, arrs[1].ctypes.data,
+                                   arrs[2].ctypes.data, len(spk), C.byref(ntx))
+    assert nin == len(spk) and ntx.value == 81
+    n, ooff = oracle.block_index(blk, False)
+    assert (tx_off[: n + 1] == ooff).all()
+    assert (arrs[1][:-1] <= arrs[1][1:]).all() and arrs[1].min() == 1  # coinbase (tx 0) skipped, block order
+    # capacity error
+    assert L.bcp_block_index_inputs(b.ctypes.data, len(blk), 0, tx_off.ctypes.data, 299, arrs[0].ctypes.data, arrs[1].ctypes.data,
+                                    arrs[2].ctypes.data, 3, C.byref(ntx)) == -2

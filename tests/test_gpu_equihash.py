@@ -74,3 +74,47 @@ def test_equihash_10k_headers(engine, oracle):
     assert (got[idx] == want).all()
     for i in idx[:50]:
         assert hashes[i].tobytes() == oracle.header_hash(allh[i].tobytes())
+
+
+def _unpack(soln, bits):
+    v = int.from_bytes(soln, "big")
+    n = len(soln) * 8 // bits
+    return [(v >> (bits * (n - 1 - i))) & ((1 << bits) - 1) for i in range(n)]
+
+
+def _pack(idx, bits):
+    v = 0
+    for x in idx:
+        v = (v << bits) | x
+    return v.to_bytes(len(idx) * bits // 8, "big")
+
+
+@pytest.mark.parametrize("n,k,fixture", [(48, 5, "equihash_48_5.npz"), (200, 9, "equihash_200_9.npz")])
+def test_equihash_structural_corruptions(engine, oracle, n, k, fixture):
+    """Index-level corruptions that keep the solution well-formed: duplicated index, swapped siblings at every
+    tree level (ordering rule), index +-1 (collision rule), all-equal indices, indices = 0..2^k-1."""
+    hdrs = _load(fixture)[:6]
+    bits = n // (k + 1) + 1
+    pre = hdrs.shape[1] - (1 << k) * bits // 8
+    out = []
+    for h in hdrs:
+        idx = _unpack(h[pre:].tobytes(), bits)
+        variants = []
+        v = list(idx); v[1] = v[0]; variants.append(v)                              # duplicate
+        v = list(idx); v[-1] = v[0]; variants.append(v)                             # duplicate across the root
+        for lvl in range(k):                                                        # swap the first sibling pair at each level
+            w = 1 << lvl
+            v = list(idx); v[0:w], v[w:2 * w] = idx[w:2 * w], idx[0:w]; variants.append(v)
+        v = list(idx); v[5] ^= 1; variants.append(v)                                # neighbour index: collision fails
+        variants.append([idx[0]] * len(idx))
+        variants.append(list(range(len(idx))))
+        variants.append(sorted(idx))
+        for v in variants:
+            b = h.copy()
+            b[pre:] = np.frombuffer(_pack(v, bits), dtype=np.uint8)
+            out.append(b)
+    allh = np.stack(out)
+    got, _ = engine.equihash_verify_batch(n, k, allh, want_hash=False)
+    want = oracle.equihash_verify_batch(n, k, allh, nthreads=os.cpu_count() or 1)
+    assert (got == want).all(), np.nonzero(got != want)[0]
+    assert not want.any()

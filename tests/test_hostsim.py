@@ -226,3 +226,40 @@ def test_p2pkh_fast_path_matches_oracle(hs, gcomb, oracle):
     got = np.where(status == 254, np.where(ok == 1, 0, 31), status).astype(np.uint8)
     assert (got == want).all(), [(i, mut.get(i), int(got[i]), int(want[i])) for i in np.nonzero(got != want)[0]]
     assert set(want) >= {0, 2, 11, 22, 23, 26, 28, 31, 36, 255}
+
+
+def test_p2pkh_fast_path_multi_input_output(hs, gcomb, oracle):
+    """Transactions with several inputs/outputs and all six FORKID hashtypes (SINGLE with and without a matching
+    output, ANYONECANPAY, NONE): per-tx midstates and per-input sighash of the device code vs the oracle."""
+    import synth
+
+    blk, spk, amt = synth.synthetic_block_multi(40, seed=11)
+    amt = list(amt)
+    amt[3] += 1  # one wrong amount: NULLFAIL exactly there
+    want = oracle.block_script_errors(blk, False, spk, amt, synth.POSTFORK_FLAGS, os.cpu_count() or 1)
+    assert want[3] == 31 and (np.delete(want, 3) == 0).all()
+    b = np.frombuffer(blk, dtype=np.uint8).copy()
+    max_tx, max_in = 200, len(spk)
+    tx_off = np.zeros(max_tx + 1, np.uint32)
+    in_off, in_tx, in_n = np.zeros(max_in, np.uint32), np.zeros(max_in, np.uint32), np.zeros(max_in, np.uint32)
+    ntx = C.c_long(0)
+    import ctypes
+    orc = ctypes.CDLL(os.path.join(ROOT, "oracle", "libbcp_oracle.so"))
+    orc.orc_block_index_inputs.restype = C.c_long
+    nin = orc.orc_block_index_inputs(b.ctypes.data_as(u8p), C.c_size_t(len(blk)), 0, tx_off.ctypes.data_as(u32p), C.c_size_t(max_tx),
+                                     in_off.ctypes.data_as(u32p), in_tx.ctypes.data_as(u32p), in_n.ctypes.data_as(u32p),
+                                     C.c_size_t(max_in), C.byref(ntx))
+    assert nin == len(spk)
+    cat = np.frombuffer(b"".join(spk), dtype=np.uint8).copy()
+    spk_off = np.zeros(nin + 1, dtype=np.uint32)
+    spk_off[1:] = np.cumsum([len(s) for s in spk])
+    am = np.asarray(amt, dtype=np.int64)
+    status = np.zeros(nin, np.uint8)
+    msg, pub, sig = np.zeros((nin, 32), np.uint8), np.zeros((nin, 65), np.uint8), np.zeros((nin, 64), np.uint8)
+    hs.hs_block_p2pkh_extract(b.ctypes.data_as(u8p), tx_off.ctypes.data_as(u32p), C.c_size_t(ntx.value), in_off.ctypes.data_as(u32p),
+                              in_tx.ctypes.data_as(u32p), in_n.ctypes.data_as(u32p), C.c_size_t(nin), cat.ctypes.data_as(u8p),
+                              spk_off.ctypes.data_as(u32p), am.ctypes.data_as(C.POINTER(C.c_int64)), status.ctypes.data_as(u8p),
+                              msg.ctypes.data_as(u8p), pub.ctypes.data_as(u8p), sig.ctypes.data_as(u8p))
+    ok = _run(hs, gcomb, msg, pub, sig, flags=1)
+    got = np.where(status == 254, np.where(ok == 1, 0, 31), status).astype(np.uint8)
+    assert (got == want).all(), np.nonzero(got != want)[0]
