@@ -61,6 +61,9 @@ static int rd_compact_h(const uint8_t *p, size_t len, size_t *pos, uint64_t *v) 
     return 1;
 }
 
+#define BCP_FLAGS_POSTFORK_REQUIRED ((1u << 1) | (1u << 2) | (1u << 3) | (1u << 14) | (1u << 16))
+#define BCP_FLAG_ALLOW_NON_FORKID (1u << 17)
+
 extern "C" {
 
 // Framing scan that also lists every non-coinbase input (CTransaction::IsCoinBase: a single input with a null
@@ -96,8 +99,89 @@ BCP_API long bcp_block_index_inputs(const uint8_t *blk, size_t len, int legacy_h
     return (long)cnt;
 }
 
-#define BCP_FLAGS_POSTFORK_REQUIRED ((1u << 1) | (1u << 2) | (1u << 3) | (1u << 14) | (1u << 16))
-#define BCP_FLAG_ALLOW_NON_FORKID (1u << 17)
+// Script checks only, for an arbitrary subset of a block's inputs (the caller did the framing scan and picked the
+// inputs): this is the unit that shards across devices — each GPU gets the raw block plus its own index range of
+// inputs and returns its ScriptError bytes; the host ANDs them (src/checkqueue.h:77), nothing is exchanged
+// between devices.  in_off / in_tx / in_n / spk_off / amounts / script_err all describe the SUBSET (n_inputs
+// entries, spk_off rebased to the subset's first scriptPubKey).
+BCP_API int bcp_gpu_block_scripts_p2pkh(int device, const uint8_t *blk, size_t len, const uint32_t *tx_off, size_t ntx,
+                                        const uint32_t *in_off, const uint32_t *in_tx, const uint32_t *in_n, size_t n_inputs,
+                                        const uint8_t *spk, const uint32_t *spk_off, const int64_t *amounts, uint32_t flags,
+                                        uint8_t *script_err, int *all_ok) {
+    bcp_ctx *c = bcp_get_ctx(device);
+    if (!c) return BCP_ERR_NOT_INIT;
+    if (all_ok) *all_ok = 1;
+    if (n_inputs == 0) return BCP_OK;
+    if (!blk || !tx_off || !in_off || !in_tx || !in_n || !spk || !spk_off || !amounts || !script_err) {
+        bcp_set_error("bcp_gpu_block_scripts_p2pkh: NULL buffer");
+        return BCP_ERR_INVALID;
+    }
+    if ((flags & BCP_FLAGS_POSTFORK_REQUIRED) != BCP_FLAGS_POSTFORK_REQUIRED || (flags & BCP_FLAG_ALLOW_NON_FORKID)) {
+        bcp_set_error("bcp_gpu_block_scripts_p2pkh: unsupported script flags 0x%x for the fast path", flags);
+        return BCP_ERR_INVALID;
+    }
+    if (len > 0xFFFFFFF0ull || tx_off[ntx] > len) { bcp_set_error("bcp_gpu_block_scripts_p2pkh: offsets exceed the block"); return BCP_ERR_INVALID; }
+    std::lock_guard<std::mutex> lk(c->mu);
+    BCP_CUDA(cudaSetDevice(device));
+    auto up = [](size_t x) { return (x + 255) / 256 * 256; };
+    const size_t nin = n_inputs, spk_bytes = spk_off[nin] - spk_off[0];
+    size_t o = 0;
+    const size_t o_blk = o; o += up(len + 8);
+    const size_t o_txoff = o; o += up((ntx + 1) * 4);
+    const size_t o_inoff = o; o += up(nin * 4 + 4);
+    const size_t o_intx = o; o += up(nin * 4 + 4);
+    const size_t o_inn = o; o += up(nin * 4 + 4);
+    const size_t o_spk = o; o += up(spk_bytes + 8);
+    const size_t o_spkoff = o; o += up((nin + 1) * 4);
+    const size_t o_amt = o; o += up(nin * 8 + 8);
+    const size_t o_flag = o; o += 256;
+    const size_t o_mid = o; o += up(ntx * BCP_TXMID_BYTES + 16);
+    const size_t o_stat = o; o += up(nin + 8);
+    const size_t o_msg = o; o += up(nin * 32 + 32);
+    const size_t o_pub = o; o += up(nin * 65 + 65);
+    const size_t o_sig = o; o += up(nin * 64 + 64);
+    const size_t o_ok = o; o += up(nin + 8);
+    const size_t o_err = o; o += up(nin + 8);
+    int rc = bcp_ctx_reserve_stage(c, o);
+    if (rc != BCP_OK) return rc;
+    rc = bcp_ctx_reserve_scratch(c, bcp_gpu_ecdsa_scratch_bytes(nin));
+    if (rc != BCP_OK) return rc;
+    uint8_t *d = c->stage;
+    cudaStream_t st = c->stream;
+    // spk_off may start anywhere in the caller's array: rebase on the host (tiny)
+    std::vector<uint32_t> &reb = c->h_in_n;
+    if (reb.size() < nin + 1) reb.resize(nin + 1);
+    for (size_t i = 0; i <= nin; i++) reb[i] = spk_off[i] - spk_off[0];
+    int one = 1;
+    BCP_CUDA(cudaMemcpyAsync(d + o_blk, blk, len, cudaMemcpyHostToDevice, st));
+    BCP_CUDA(cudaMemcpyAsync(d + o_txoff, tx_off, (ntx + 1) * 4, cudaMemcpyHostToDevice, st));
+    BCP_CUDA(cudaMemcpyAsync(d + o_inoff, in_off, nin * 4, cudaMemcpyHostToDevice, st));
+    BCP_CUDA(cudaMemcpyAsync(d + o_intx, in_tx, nin * 4, cudaMemcpyHostToDevice, st));
+    BCP_CUDA(cudaMemcpyAsync(d + o_inn, in_n, nin * 4, cudaMemcpyHostToDevice, st));
+    BCP_CUDA(cudaMemcpyAsync(d + o_spk, spk + spk_off[0], spk_bytes, cudaMemcpyHostToDevice, st));
+    BCP_CUDA(cudaMemcpyAsync(d + o_spkoff, reb.data(), (nin + 1) * 4, cudaMemcpyHostToDevice, st));
+    BCP_CUDA(cudaMemcpyAsync(d + o_amt, amounts, nin * 8, cudaMemcpyHostToDevice, st));
+    BCP_CUDA(cudaMemcpyAsync(d + o_flag, &one, sizeof(int), cudaMemcpyHostToDevice, st));
+    uint32_t *d_txoff = reinterpret_cast<uint32_t *>(d + o_txoff);
+    k_tx_midstate<<<(unsigned)((ntx + 127) / 128), 128, 0, st>>>(d + o_blk, d_txoff, ntx, d + o_mid);
+    k_p2pkh_extract<<<(unsigned)((nin + 127) / 128), 128, 0, st>>>(
+        d + o_blk, d_txoff, reinterpret_cast<uint32_t *>(d + o_inoff), reinterpret_cast<uint32_t *>(d + o_intx),
+        reinterpret_cast<uint32_t *>(d + o_inn), nin, d + o_spk, reinterpret_cast<uint32_t *>(d + o_spkoff),
+        reinterpret_cast<int64_t *>(d + o_amt), d + o_mid, d + o_stat, d + o_msg, d + o_pub, d + o_sig);
+    BCP_CUDA(cudaGetLastError());
+    rc = bcp_ecdsa_launch(c, d + o_msg, d + o_pub, d + o_sig, nin, BCP_ECDSA_FLAG_NORMALIZE_S, d + o_ok,
+                          reinterpret_cast<uint32_t *>(c->scratch), st);
+    if (rc != BCP_OK) return rc;
+    k_script_finish<<<(unsigned)((nin + 255) / 256), 256, 0, st>>>(d + o_stat, d + o_ok, nin, d + o_err,
+                                                                   reinterpret_cast<int *>(d + o_flag));
+    BCP_CUDA(cudaGetLastError());
+    BCP_CUDA(cudaMemcpyAsync(script_err, d + o_err, nin, cudaMemcpyDeviceToHost, st));
+    int a = 0;
+    BCP_CUDA(cudaMemcpyAsync(&a, d + o_flag, sizeof(int), cudaMemcpyDeviceToHost, st));
+    BCP_CUDA(cudaStreamSynchronize(st));
+    if (all_ok) *all_ok = a ? 1 : 0;
+    return BCP_OK;
+}
 
 BCP_API int bcp_gpu_block_connect_p2pkh(int device, const uint8_t *blk, size_t len, int legacy_header, const uint8_t *spk,
                                         const uint32_t *spk_off, const int64_t *amounts, size_t n_inputs, uint32_t flags,

@@ -1,0 +1,45 @@
+// bcp_chain.cpp — C face over bcp::ChainValidator (include/compat/bcp_chain.h) so that the tests and bench.py can
+// drive the host-side block connector through ctypes.  Built into bitcoincashplus_b200/libbcp_chain.so by
+// csrc/Makefile (plain g++, links libbcp_b200.so).
+#include <cstdio>
+#include <cstring>
+#include <string>
+
+#include "../../include/compat/bcp_chain.h"
+
+#define CHAIN_API extern "C" __attribute__((visibility("default")))
+
+CHAIN_API void *bcp_chain_new(const int *devices, int ndev, uint32_t script_flags, unsigned eh_n, unsigned eh_k, char *err,
+                              size_t errlen) {
+    std::vector<int> d(devices, devices + ndev);
+    auto *v = new bcp::ChainValidator(d, script_flags, eh_n, eh_k);
+    std::string e;
+    if (!v->Init(e)) {
+        if (err && errlen) snprintf(err, errlen, "%s", e.c_str());
+        delete v;
+        return nullptr;
+    }
+    return v;
+}
+CHAIN_API void bcp_chain_free(void *h) { delete static_cast<bcp::ChainValidator *>(h); }
+CHAIN_API void bcp_chain_add_coin(void *h, const uint8_t *txid32, uint32_t vout, const uint8_t *spk, size_t len, int64_t amount) {
+    static_cast<bcp::ChainValidator *>(h)->AddCoin(txid32, vout, spk, len, amount);
+}
+CHAIN_API size_t bcp_chain_utxo_size(void *h) { return static_cast<bcp::ChainValidator *>(h)->UtxoSize(); }
+CHAIN_API size_t bcp_chain_inputs_checked(void *h) { return static_cast<bcp::ChainValidator *>(h)->InputsChecked(); }
+CHAIN_API int bcp_chain_connect_block(void *h, const uint8_t *blk, size_t len, char *reason, size_t reasonlen) {
+    std::string r;
+    bool ok = static_cast<bcp::ChainValidator *>(h)->ConnectBlock(blk, len, r);
+    if (reason && reasonlen) snprintf(reason, reasonlen, "%s", r.c_str());
+    return ok ? 1 : 0;
+}
+CHAIN_API long bcp_chain_connect_file(void *h, const uint8_t *data, size_t len, const uint8_t *magic4, char *reason, size_t reasonlen,
+                                      long *failed_index) {
+    std::string r;
+    long fi = -1;
+    long n = static_cast<bcp::ChainValidator *>(h)->ConnectFile(data, len, magic4, r, fi);
+    if (reason && reasonlen) snprintf(reason, reasonlen, "%s", r.c_str());
+    if (failed_index) *failed_index = fi;
+    return n;
+}
+CHAIN_API void bcp_chain_last_hash(void *h, uint8_t *out32) { memcpy(out32, static_cast<bcp::ChainValidator *>(h)->LastBlockHash(), 32); }

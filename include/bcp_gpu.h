@@ -144,6 +144,13 @@ BCP_API int bcp_gpu_merkle_root_dev_static(int device, const uint8_t *d_leaves32
  *   txids (optional), root32, mutated   as bcp_gpu_sha256d_txids_merkle */
 BCP_API long bcp_block_index_inputs(const uint8_t *blk, size_t len, int legacy_header, uint32_t *tx_off, size_t max_tx,
                                     uint32_t *in_off, uint32_t *in_tx, uint32_t *in_n, size_t max_inputs, long *ntx_out);
+/* The script checks alone, for any subset of a block's inputs chosen by the caller (arrays describe the subset;
+ * spk_off may point into a larger offsets array).  This is the unit that shards across GPUs: one call per device
+ * over its index range, verdicts AND-ed on the host like `fAllOk &= fOk` (src/checkqueue.h:77). */
+BCP_API int bcp_gpu_block_scripts_p2pkh(int device, const uint8_t *blk, size_t len, const uint32_t *tx_off, size_t ntx,
+                                        const uint32_t *in_off, const uint32_t *in_tx, const uint32_t *in_n, size_t n_inputs,
+                                        const uint8_t *spk, const uint32_t *spk_off, const int64_t *amounts, uint32_t flags,
+                                        uint8_t *script_err, int *all_ok);
 BCP_API int bcp_gpu_block_connect_p2pkh(int device, const uint8_t *blk, size_t len, int legacy_header, const uint8_t *spk,
                                         const uint32_t *spk_off, const int64_t *amounts, size_t n_inputs, uint32_t flags,
                                         uint8_t *txids, uint8_t root32[32], int *mutated, uint8_t *script_err, int *all_ok);

@@ -327,3 +327,111 @@ def synthetic_block_multi(ntx=60, nkeys=8, seed=1):
     body = _compact(len(txs)) + b"".join(txs)
     root, _ = o.merkle_root(b"".join(o.sha256d(t) for t in txs))
     return synthetic_header(merkle_root=root) + body, prev_spk, prev_amt
+
+
+# ------------------------------------------------------------------ tiny Equihash (48,5) solver (regtest parameters)
+def equihash_solve_48_5(input140):
+    """Wagner's algorithm for the regtest parameters (N=48, K=5: 512 leaves of 6 bytes, five collision rounds on one
+    byte, the last on two).  Pure Python + hashlib; used to give synthetic chain headers VALID solutions on machines
+    that have neither the reference nor its solver.  Returns a list of 36-byte minimal encodings."""
+    pers = b"ZcashPoW" + (48).to_bytes(4, "little") + (5).to_bytes(4, "little")
+    rows = []
+    for g in range(52):  # 512 indices / 10 per hash output
+        d = hashlib.blake2b(input140 + g.to_bytes(4, "little"), digest_size=60, person=pers).digest()
+        for j in range(10):
+            i = g * 10 + j
+            if i < 512:
+                rows.append((d[6 * j:6 * j + 6], (i,)))
+    for rnd in range(5):
+        width = 2 if rnd == 4 else 1
+        buckets = {}
+        for h, idx in rows:
+            buckets.setdefault(h[:width], []).append((h, idx))
+        nxt = []
+        for grp in buckets.values():
+            for a in range(len(grp)):
+                for b in range(a + 1, len(grp)):
+                    (ha, ia), (hb, ib) = grp[a], grp[b]
+                    if set(ia) & set(ib):
+                        continue
+                    x = bytes(p ^ q for p, q in zip(ha[width:], hb[width:]))
+                    nxt.append((x, ia + ib if ia[0] < ib[0] else ib + ia))
+        rows = nxt
+        if not rows:
+            return []
+    sols = []
+    for h, idx in rows:
+        if len(set(idx)) == 32:
+            v = 0
+            for x in idx:
+                v = (v << 9) | x
+            sols.append(v.to_bytes(36, "big"))
+    return sorted(set(sols))
+
+
+def synthetic_chain(nblocks=6, ntx=20, nkeys=8, equihash=True, corrupt=None):
+    """A chain of post-fork blocks with REAL UTXO dependencies: block b's transaction j spends
+    output 0 of block b-1's transaction j; block 0 spends seeded "prev" coins.  With equihash=True every header
+    carries a valid regtest (48,5) solution.  corrupt = (block, kind) with kind in {"bad_sig", "double_spend",
+    "bad_merkle", "missing_input", "bad_equihash"} damages exactly one block.
+    Returns (list of block bytes, list of seed coins (txid, vout, spk, amount), per-block (spk list, amounts) of the
+    coins each block's inputs were built to spend)."""
+    o = po.oracle()
+    keys = [seckey(5000 + j) for j in range(nkeys)]
+    pubs = [o.pubkey_create(kb, True) for kb in keys]
+    spks = [p2pkh_script(pb) for pb in pubs]
+    amount = 10**7
+    seeds = []
+    prev_out = []  # (txid, vout, key index, amount) spendable by tx j of the next block
+    for j in range(ntx):
+        txid = hashlib.sha256(hashlib.sha256(SEED + b"chainprev" + j.to_bytes(8, "little")).digest()).digest()
+        seeds.append((txid, 0, spks[j % nkeys], amount))
+        prev_out.append((txid, 0, j % nkeys, amount))
+    blocks, prevs = [], []
+    for b in range(nblocks):
+        prevs.append(([spks[p[2]] for p in prev_out], [p[3] for p in prev_out]))
+        cb = (2).to_bytes(4, "little") + b"\x01" + bytes(32) + b"\xff\xff\xff\xff" + b"\x04" + (700000 + b).to_bytes(4, "little")
+        cb += b"\xff\xff\xff\xff" + b"\x01" + (1250000000).to_bytes(8, "little") + bytes([25]) + spks[0] + bytes(4)
+        txs = [cb]
+        new_out = []
+        kind = corrupt[1] if corrupt and corrupt[0] == b else None
+        for j in range(ntx):
+            txid, vout, kj, amt_ = prev_out[j]
+            if kind == "double_spend" and j == 1:
+                txid, vout, kj, amt_ = prev_out[0]
+            if kind == "missing_input" and j == 2:
+                txid = hashlib.sha256(b"nowhere").digest()
+            nk = (kj + 1) % nkeys
+            out = (amt_ - 1000).to_bytes(8, "little") + bytes([25]) + spks[nk]
+
+            def build(ss):
+                return ((2).to_bytes(4, "little") + b"\x01" + txid + vout.to_bytes(4, "little") + _compact(len(ss)) + ss
+                        + b"\xff\xff\xff\xff" + b"\x01" + out + bytes(4))
+            sh = o.sighash_forkid(spks[kj], build(b""), 0, 0x41, amt_)
+            s64 = o.sign(keys[kj], sh)
+            r_, s_ = int.from_bytes(s64[:32], "big"), int.from_bytes(s64[32:], "big")
+            if kind == "bad_sig" and j == 3:
+                r_ ^= 2
+            der = _der(r_, s_) + b"\x41"
+            tx = build(bytes([len(der)]) + der + bytes([33]) + pubs[kj])
+            txs.append(tx)
+            new_out.append((o.sha256d(tx), 0, nk, amt_ - 1000))
+        root, _ = o.merkle_root(b"".join(o.sha256d(t) for t in txs))
+        if kind == "bad_merkle":
+            root = bytes([root[0] ^ 1]) + root[1:]
+        nonce = 0
+        while True:
+            hdr = synthetic_header(height=700000 + b, merkle_root=root, nonce_tag=(b << 20) | nonce, n=48, k=5)
+            if not equihash:
+                break
+            sols = equihash_solve_48_5(hdr[:140])
+            if sols:
+                soln = sols[0]
+                if kind == "bad_equihash":
+                    soln = bytes([soln[0] ^ 0x80]) + soln[1:]
+                hdr = hdr[:140] + _compact(36) + soln
+                break
+            nonce += 1
+        blocks.append(hdr + _compact(len(txs)) + b"".join(txs))
+        prev_out = new_out
+    return blocks, seeds, prevs
