@@ -140,8 +140,21 @@ template <int N>
 BCP_DEV uint32_t addn_cc(uint32_t *r, const uint32_t *a, const uint32_t *b) {
     uint32_t c;
 #if BCP_PTX
-    static_assert(N == 8 || N == 5 || N == 3 || N == 2, "unsupported chain length");
-    if (N == 8) {
+    static_assert(N == 8 || N == 5 || N == 4 || N == 3 || N == 2, "unsupported chain length");
+    if (N == 4) {
+        uint32_t r0, r1, r2, r3;
+        asm("add.cc.u32 %0, %5, %9;\n\t"
+            "addc.cc.u32 %1, %6, %10;\n\t"
+            "addc.cc.u32 %2, %7, %11;\n\t"
+            "addc.cc.u32 %3, %8, %12;\n\t"
+            "addc.u32 %4, 0, 0;"
+            : "=r"(r0), "=r"(r1), "=r"(r2), "=r"(r3), "=r"(c)
+            : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(b[0]), "r"(b[1]), "r"(b[2]), "r"(b[3]));
+        r[0] = r0;
+        r[1] = r1;
+        r[2] = r2;
+        r[3] = r3;
+    } else if (N == 8) {
         uint32_t r0, r1, r2, r3, r4, r5, r6, r7;
         asm("add.cc.u32 %0, %9, %17;\n\t"
             "addc.cc.u32 %1, %10, %18;\n\t"
@@ -214,8 +227,21 @@ template <int N>
 BCP_DEV uint32_t subn_cc(uint32_t *r, const uint32_t *a, const uint32_t *b) {
     uint32_t c;
 #if BCP_PTX
-    static_assert(N == 8 || N == 2, "unsupported chain length");
-    if (N == 8) {
+    static_assert(N == 8 || N == 4 || N == 2, "unsupported chain length");
+    if (N == 4) {
+        uint32_t r0, r1, r2, r3;
+        asm("sub.cc.u32 %0, %5, %9;\n\t"
+            "subc.cc.u32 %1, %6, %10;\n\t"
+            "subc.cc.u32 %2, %7, %11;\n\t"
+            "subc.cc.u32 %3, %8, %12;\n\t"
+            "subc.u32 %4, 0, 0;"
+            : "=r"(r0), "=r"(r1), "=r"(r2), "=r"(r3), "=r"(c)
+            : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(b[0]), "r"(b[1]), "r"(b[2]), "r"(b[3]));
+        r[0] = r0;
+        r[1] = r1;
+        r[2] = r2;
+        r[3] = r3;
+    } else if (N == 8) {
         uint32_t r0, r1, r2, r3, r4, r5, r6, r7;
         asm("sub.cc.u32 %0, %9, %17;\n\t"
             "subc.cc.u32 %1, %10, %18;\n\t"
@@ -259,6 +285,62 @@ BCP_DEV uint32_t subn_cc(uint32_t *r, const uint32_t *a, const uint32_t *b) {
     return c;
 }
 
+// r = a + b + cin (cin is 0/1), returns the carry out.  The carry flag is primed with cin by adding 0xFFFFFFFF to it.
+template <int N>
+BCP_DEV uint32_t addn_cin(uint32_t *r, const uint32_t *a, const uint32_t *b, uint32_t cin) {
+    uint32_t c;
+#if BCP_PTX
+    static_assert(N == 8 || N == 4, "unsupported chain length");
+    if (N == 8) {
+        uint32_t r0, r1, r2, r3, r4, r5, r6, r7, scratch;
+        asm("add.cc.u32 %9, %26, 0xffffffff;\n\t"
+            "addc.cc.u32 %0, %10, %18;\n\t"
+            "addc.cc.u32 %1, %11, %19;\n\t"
+            "addc.cc.u32 %2, %12, %20;\n\t"
+            "addc.cc.u32 %3, %13, %21;\n\t"
+            "addc.cc.u32 %4, %14, %22;\n\t"
+            "addc.cc.u32 %5, %15, %23;\n\t"
+            "addc.cc.u32 %6, %16, %24;\n\t"
+            "addc.cc.u32 %7, %17, %25;\n\t"
+            "addc.u32 %8, 0, 0;"
+            : "=r"(r0), "=r"(r1), "=r"(r2), "=r"(r3), "=r"(r4), "=r"(r5), "=r"(r6), "=r"(r7), "=r"(c), "=r"(scratch)
+            : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(a[4]), "r"(a[5]), "r"(a[6]), "r"(a[7]), "r"(b[0]), "r"(b[1]), "r"(b[2]), "r"(b[3]), "r"(b[4]), "r"(b[5]), "r"(b[6]), "r"(b[7]), "r"(cin));
+        r[0] = r0;
+        r[1] = r1;
+        r[2] = r2;
+        r[3] = r3;
+        r[4] = r4;
+        r[5] = r5;
+        r[6] = r6;
+        r[7] = r7;
+        (void)scratch;
+    } else {
+        uint32_t r0, r1, r2, r3, scratch;
+        asm("add.cc.u32 %5, %14, 0xffffffff;\n\t"
+            "addc.cc.u32 %0, %6, %10;\n\t"
+            "addc.cc.u32 %1, %7, %11;\n\t"
+            "addc.cc.u32 %2, %8, %12;\n\t"
+            "addc.cc.u32 %3, %9, %13;\n\t"
+            "addc.u32 %4, 0, 0;"
+            : "=r"(r0), "=r"(r1), "=r"(r2), "=r"(r3), "=r"(c), "=r"(scratch)
+            : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(b[0]), "r"(b[1]), "r"(b[2]), "r"(b[3]), "r"(cin));
+        r[0] = r0;
+        r[1] = r1;
+        r[2] = r2;
+        r[3] = r3;
+        (void)scratch;
+    }
+#else
+    uint64_t t = cin;
+    for (int i = 0; i < N; i++) {
+        t += (uint64_t)a[i] + b[i];
+        r[i] = (uint32_t)t;
+        t >>= 32;
+    }
+    c = (uint32_t)t;
+#endif
+    return c;
+}
 // r = E + (O << 32): E[k] sits at limb k, O[k] at limb k+1 (O[15] is always zero)
 BCP_DEV void merge_even_odd(uint32_t *r /*16*/, const uint32_t *E, const uint32_t *O) {
     r[0] = E[0];
@@ -340,6 +422,64 @@ BCP_DEV void mul_wide(uint32_t *r /*16*/, const uint32_t *a, const uint32_t *b) 
     merge_even_odd(r, E, O);
 }
 
+// ------------------------------------------------------------------ 128x128 -> 256 and one Karatsuba level
+// same even/odd carry-chain layout as mul_wide, rows of two products: 16 IMAD.WIDE
+BCP_DEV void mul4_wide(uint32_t *r /*8*/, const uint32_t *a, const uint32_t *b) {
+    uint32_t E[9], O[9];
+    wide_mul(E[0], E[1], a[0], b[0]); wide_mul(E[2], E[3], a[2], b[0]);
+    wide_mul(O[0], O[1], a[1], b[0]); wide_mul(O[2], O[3], a[3], b[0]);
+    BCP_UNROLL
+    for (int k = 4; k < 9; k++) { E[k] = 0; O[k] = 0; }
+    const uint32_t ev[2] = {a[0], a[2]}, od[2] = {a[1], a[3]};
+    row_acc_k<2>(O + 0, ev, b[1]); /* limbs 1,3 */
+    row_acc_k<2>(E + 2, od, b[1]); /* limbs 2,4 */
+    row_acc_k<2>(E + 2, ev, b[2]); /* limbs 2,4 */
+    row_acc_k<2>(O + 2, od, b[2]); /* limbs 3,5 */
+    row_acc_k<2>(O + 2, ev, b[3]); /* limbs 3,5 */
+    row_acc_k<2>(E + 4, od, b[3]); /* limbs 4,6; the product fits 8 limbs, E[8] stays 0 */
+    uint32_t t[8];
+    addn_cc<8>(t, E + 1, O); /* t[k] = E[k+1] + O[k]; t[7] = E[8] + O[7] = 0 */
+    r[0] = E[0];
+    BCP_UNROLL
+    for (int k = 1; k < 8; k++) r[k] = t[k - 1];
+}
+// d = |x - y| over 4 limbs, returns 1 when x < y
+BCP_DEV uint32_t absdiff4(uint32_t *d, const uint32_t *x, const uint32_t *y) {
+    uint32_t t[4];
+    const uint32_t bw = subn_cc<4>(t, x, y);
+    const uint32_t mask = 0u - bw;
+    uint32_t f[4], z[4] = {0, 0, 0, 0};
+    BCP_UNROLL
+    for (int i = 0; i < 4; i++) f[i] = t[i] ^ mask;
+    addn_cin<4>(d, f, z, bw); /* two's complement negate when the difference was negative */
+    return bw;
+}
+// 256x256 -> 512 with one level of (subtractive) Karatsuba: 48 IMAD.WIDE instead of 64.
+// MEASURED SLOWER on B200 (39.8 vs 42.5 M sigverifies/s): the 16 saved IMAD.WIDE (64 pipe cycles) cost ~65 extra ALU
+// instructions, longer carry chains and spills at the 128-register budget; kept behind BCP_FE_KARATSUBA (default 0)
+// as a recorded experiment, exercised by tests/test_hostsim.py.
+//   a*b = z0 + (z0 + z2 + (a_lo - a_hi)(b_hi - b_lo)) * 2^128 + z2 * 2^256,  z0 = a_lo*b_lo, z2 = a_hi*b_hi
+BCP_DEV void mul_wide_karatsuba(uint32_t *r /*16*/, const uint32_t *a, const uint32_t *b) {
+    uint32_t z0[8], z2[8], m[8], da[4], db[4];
+    mul4_wide(z0, a, b);
+    mul4_wide(z2, a + 4, b + 4);
+    const uint32_t sa = absdiff4(da, a, a + 4);
+    const uint32_t sb = absdiff4(db, b + 4, b);
+    mul4_wide(m, da, db);
+    const uint32_t neg = sa ^ sb, mask = 0u - neg;
+    uint32_t mid[9], mx[8];
+    mid[8] = addn_cc<8>(mid, z0, z2);
+    BCP_UNROLL
+    for (int i = 0; i < 8; i++) mx[i] = m[i] ^ mask;
+    mid[8] += addn_cin<8>(mid, mid, mx, neg) - neg; /* +m, or +(~m + 1) - 2^256 = -m; the true middle term is >= 0 */
+    BCP_UNROLL
+    for (int i = 0; i < 4; i++) r[i] = z0[i];
+    uint32_t x[8] = {z0[4], z0[5], z0[6], z0[7], z2[0], z2[1], z2[2], z2[3]};
+    uint32_t c = addn_cc<8>(r + 4, x, mid);
+    uint32_t y[4] = {mid[8], 0, 0, 0};
+    addn_cin<4>(r + 12, z2 + 4, y, c);
+}
+
 // ------------------------------------------------------------------ 512 -> [0, 2^256) mod p
 BCP_DEV void fe_reduce_wide(fe &r, const uint32_t *t /*16*/) {
     // first fold: S = L + H*977 + (H << 32), accumulated in place as two interleaved arrays
@@ -377,10 +517,17 @@ BCP_DEV void fe_reduce_wide(fe &r, const uint32_t *t /*16*/) {
 #else
 #define BCP_FE_FN BCP_DEV
 #endif
+#ifndef BCP_FE_KARATSUBA
+#define BCP_FE_KARATSUBA 0
+#endif
 BCP_FE_FN fe fe_mul_f(fe a, fe b) {
     uint32_t t[16];
     fe r;
+#if BCP_FE_KARATSUBA
+    mul_wide_karatsuba(t, a.v, b.v);
+#else
     mul_wide(t, a.v, b.v);
+#endif
     fe_reduce_wide(r, t);
     return r;
 }

@@ -51,6 +51,18 @@ void hs_fe_op(int op, const uint8_t *a32, const uint8_t *b32, uint8_t *out32) {
     }
     fe_to_be(out32, r);
 }
+// 512-bit product via the Karatsuba variant (an experiment kept in fe.cuh), big-endian in/out
+void hs_mul_wide_karatsuba(const uint8_t *a32, const uint8_t *b32, uint8_t *out64) {
+    uint32_t a[8], b[8], r[16], r2[16];
+    words_from_be(a, a32);
+    words_from_be(b, b32);
+    mul_wide_karatsuba(r, a, b);
+    mul_wide(r2, a, b);
+    for (int i = 0; i < 16; i++) {
+        if (r[i] != r2[i]) r[i] = ~r2[i]; /* make any disagreement with the schoolbook product visible */
+        out64[4 * (15 - i)] = r[i] >> 24; out64[4 * (15 - i) + 1] = r[i] >> 16; out64[4 * (15 - i) + 2] = r[i] >> 8; out64[4 * (15 - i) + 3] = r[i];
+    }
+}
 int hs_fe_is_zero(const uint8_t *a32) {
     fe a;
     words_from_be(a.v, a32);

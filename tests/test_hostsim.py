@@ -68,6 +68,16 @@ def test_field_ops_on_weakly_reduced_inputs(hs):
         assert bool(hs.hs_fe_is_zero(b32(a))) == (a % P == 0)
 
 
+def test_wide_products_schoolbook_and_karatsuba(hs):
+    rnd = random.Random(17)
+    vals = EDGE + [2**128 - 1, 2**128, 2**128 + 1, (2**128 - 1) << 128, 2**256 - 2**128] + [rnd.randrange(2**256) for _ in range(200)]
+    for a in vals[:40]:
+        for b in vals[:40]:
+            out = (C.c_uint8 * 64)()
+            hs.hs_mul_wide_karatsuba(b32(a), b32(b), out)
+            assert int.from_bytes(bytes(out), "big") == a * b, (hex(a), hex(b))
+
+
 def test_scalar_ops_and_reduction(hs):
     from secp_consts import lam
 
