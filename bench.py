@@ -179,6 +179,79 @@ def equihash_bench(eng):
             "timed": "bcp_gpu_equihash_verify_batch incl. H2D of 14.9 MB, verdicts + header hashes D2H"}
 
 
+def chain_bench(args, device):
+    """Secondary measurement in the shape of BASELINE.json configs[4]: a synthetic chain of 8 MB blocks with real UTXO
+    dependencies (block b spends block b-1) and valid regtest Equihash (48,5) headers, connected block by block by the
+    host-side connector (include/compat/bcp_chain.h): Equihash + header hash, txids + Merkle, UTXO lookups, P2PKH script
+    checks + batched ECDSA, UTXO commit.  CPU side: the reference's deserialization + txids + Merkle + VerifyScript on
+    all threads for a 2-block sample of the same chain."""
+    import ctypes as C
+    import numpy as np
+    import synth
+    from oracle import pyoracle as po
+
+    nb, ntx = args.chain_blocks, args.block_txs
+    t0 = time.perf_counter()
+    blocks = list(synth.synthetic_chain_fast(nb, ntx))
+    seeds = synth.chain_seeds(ntx, 4096)
+    gen_s = time.perf_counter() - t0
+    L = C.CDLL(os.path.join(ROOT, "bitcoincashplus_b200", "libbcp_chain.so"))
+    L.bcp_chain_new.restype = C.c_void_p
+    L.bcp_chain_new.argtypes = [C.POINTER(C.c_int), C.c_int, C.c_uint32, C.c_uint, C.c_uint, C.c_char_p, C.c_size_t]
+    L.bcp_chain_add_coin.argtypes = [C.c_void_p, C.c_char_p, C.c_uint32, C.c_char_p, C.c_size_t, C.c_int64]
+    L.bcp_chain_connect_block.argtypes = [C.c_void_p, C.c_char_p, C.c_size_t, C.c_char_p, C.c_size_t]
+    L.bcp_chain_free.argtypes = [C.c_void_p]
+    err = C.create_string_buffer(256)
+    h = L.bcp_chain_new((C.c_int * 1)(device), 1, synth.POSTFORK_FLAGS, 48, 5, err, 256)
+    assert h, err.value
+    for txid, vout, spk, amount in seeds:
+        L.bcp_chain_add_coin(h, txid, vout, spk, len(spk), amount)
+    reason = C.create_string_buffer(256)
+    # the block bytes live in pinned host memory, as a reader of blk*.dat would arrange
+    import bitcoincashplus_b200 as bcp
+    G = bcp.lib()
+    L.bcp_chain_connect_block.argtypes = [C.c_void_p, C.c_void_p, C.c_size_t, C.c_char_p, C.c_size_t]
+    pinned = []
+    for b in blocks:
+        p = G.bcp_gpu_host_alloc(len(b))
+        C.memmove(p, b, len(b))
+        pinned.append((p, len(b)))
+    per_block = []
+    t0 = time.perf_counter()
+    for p, ln in pinned:
+        t1 = time.perf_counter()
+        ok = L.bcp_chain_connect_block(h, p, ln, reason, 256)
+        per_block.append(time.perf_counter() - t1)
+        assert ok == 1, reason.value
+    total = time.perf_counter() - t0
+    ph = (C.c_double * 5)()
+    L.bcp_chain_phase_seconds.argtypes = [C.c_void_p, C.POINTER(C.c_double)]
+    L.bcp_chain_phase_seconds(h, ph)
+    phases = dict(zip(["header_equihash", "framing_scan", "txids_merkle", "utxo_walk", "script_checks"], [1e3 * x / nb for x in ph]))
+    for p, _ in pinned:
+        G.bcp_gpu_host_free(p)
+    L.bcp_chain_free(h)
+    out = {"blocks": nb, "inputs_per_block": ntx, "block_bytes": len(blocks[0]), "gpu_seconds_total": total,
+           "gpu_blocks_per_s": nb / total, "gpu_ms_per_block_median": sorted(per_block)[len(per_block) // 2] * 1e3,
+           "gpu_ms_first_block": per_block[0] * 1e3, "ms_per_block_by_phase": phases, "gen_seconds": gen_s,
+           "timed": "bcp::ChainValidator::ConnectBlock per block (block bytes in pinned host memory, in-memory UTXO table on the host)"}
+    if po.have_ref():
+        r = po.ref()
+        cores = os.cpu_count() or 1
+        spk = [s[2] for s in seeds]
+        amt = [s[3] for s in seeds]
+        t0 = time.perf_counter()
+        n, txids, root, _ = r.block_txids(blocks[0], False, max_tx=ntx + 8)
+        e = r.block_script_errors(blocks[0], False, spk, amt, synth.POSTFORK_FLAGS, cores)
+        okh = r.equihash_verify(48, 5, blocks[0][:177])
+        cpu_s = time.perf_counter() - t0
+        assert not e.any() and okh == 1 and root == blocks[0][36:68]
+        out.update({"cpu_kind": "reference", "cpu_cores": cores, "cpu_ms_per_block": cpu_s * 1e3,
+                    "cpu_blocks_per_s": 1.0 / cpu_s, "speedup_vs_cpu": (nb / total) * cpu_s,
+                    "cpu_sample": "block 0 of the chain: CBlock deserialize + txids + Merkle (1 thread), VerifyScript per input (all threads), Equihash; no UTXO map work"})
+    return out
+
+
 def run_reference(args):
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
@@ -222,6 +295,7 @@ def main():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-block", action="store_true", help="skip the secondary 8 MB block measurement (configs[2])")
     ap.add_argument("--block-txs", type=int, default=41650)
+    ap.add_argument("--chain-blocks", type=int, default=20, help="blocks of the synthetic chain reindex (configs[4] shape); 0 = skip")
     args = ap.parse_args()
     if args.impl == "reference":
         return run_reference(args)
@@ -360,6 +434,8 @@ def main():
     if not args.no_block:
         line["block8mb"] = block_bench(eng, args, bcp)
         line["equihash10k"] = equihash_bench(eng)
+        if args.chain_blocks > 0:
+            line["chain"] = chain_bench(args, local)
     print(json.dumps(line))
     if dist:
         td.destroy_process_group()

@@ -43,3 +43,6 @@ CHAIN_API long bcp_chain_connect_file(void *h, const uint8_t *data, size_t len, 
     return n;
 }
 CHAIN_API void bcp_chain_last_hash(void *h, uint8_t *out32) { memcpy(out32, static_cast<bcp::ChainValidator *>(h)->LastBlockHash(), 32); }
+CHAIN_API void bcp_chain_phase_seconds(void *h, double *out5) {
+    for (int i = 0; i < 5; i++) out5[i] = static_cast<bcp::ChainValidator *>(h)->phase[i];
+}

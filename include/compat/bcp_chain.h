@@ -18,11 +18,11 @@
 #ifndef BCP_COMPAT_CHAIN_H
 #define BCP_COMPAT_CHAIN_H
 
+#include <chrono>
 #include <cstdint>
 #include <cstring>
 #include <string>
 #include <thread>
-#include <unordered_map>
 #include <vector>
 
 #include "../bcp_gpu.h"
@@ -42,9 +42,98 @@ struct OutPointHash {
         return (size_t)(h ^ (0x9E3779B97F4A7C15ull * v));
     }
 };
-struct Coin {
-    std::vector<uint8_t> spk;
+// Open-addressing UTXO table (linear probing, tombstones), coins stored inline: scriptPubKeys up to 40 bytes live in
+// the slot (P2PKH is 25), longer ones in a side vector.  One table serves lookups, in-block creations and spends;
+// a per-block journal undoes everything when the block is rejected, so no second map is needed.
+struct CoinSlot {
+    OutPoint key;
     int64_t amount;
+    uint32_t spk_len;
+    uint8_t state; // 0 empty, 1 live, 2 tombstone
+    uint8_t spk[40];
+    std::vector<uint8_t> *big; // only for scripts longer than 40 bytes
+};
+class CoinTable {
+public:
+    explicit CoinTable(size_t cap_pow2 = 1 << 16) : slots(cap_pow2), mask(cap_pow2 - 1) {
+        for (auto &s : slots) { s.state = 0; s.big = nullptr; }
+    }
+    ~CoinTable() { for (auto &s : slots) delete s.big; }
+    size_t size() const { return live; }
+    // the table is far larger than the CPU caches and every probe is a random access: callers hint the slots of the
+    // next few outpoints while they work on the current one
+    void prefetch(const OutPoint &k) const { __builtin_prefetch(&slots[OutPointHash()(k) & mask]); }
+    CoinSlot *find(const OutPoint &k) {
+        size_t i = OutPointHash()(k) & mask;
+        for (;;) {
+            CoinSlot &s = slots[i];
+            if (s.state == 0) return nullptr;
+            if (s.state == 1 && s.key == k) return &s;
+            i = (i + 1) & mask;
+        }
+    }
+    CoinSlot *insert(const OutPoint &k, const uint8_t *spk, size_t len, int64_t amount) {
+        if ((used + 1) * 10 > slots.size() * 7) grow();
+        size_t i = OutPointHash()(k) & mask;
+        CoinSlot *tomb = nullptr;
+        for (;;) {
+            CoinSlot &s = slots[i];
+            if (s.state == 0) break;
+            if (s.state == 1 && s.key == k) { fill(s, spk, len, amount); return &s; } // overwrite (BIP30-style duplicates)
+            if (s.state == 2 && !tomb) tomb = &s;
+            i = (i + 1) & mask;
+        }
+        CoinSlot &d = tomb ? *tomb : slots[i];
+        if (!tomb) used++;
+        d.key = k;
+        d.state = 1;
+        fill(d, spk, len, amount);
+        live++;
+        return &d;
+    }
+    void erase(CoinSlot *s) {
+        s->state = 2;
+        live--;
+    }
+    void revive(CoinSlot *s) { // undo of erase
+        s->state = 1;
+        live++;
+    }
+    static const uint8_t *script(const CoinSlot &s) { return s.big ? s.big->data() : s.spk; }
+
+private:
+    void fill(CoinSlot &s, const uint8_t *spk, size_t len, int64_t amount) {
+        s.amount = amount;
+        s.spk_len = (uint32_t)len;
+        if (len <= sizeof s.spk) {
+            memcpy(s.spk, spk, len);
+            delete s.big;
+            s.big = nullptr;
+        } else {
+            if (!s.big) s.big = new std::vector<uint8_t>();
+            s.big->assign(spk, spk + len);
+        }
+    }
+    void grow() {
+        std::vector<CoinSlot> old;
+        old.swap(slots);
+        slots.resize(old.size() * 2);
+        mask = slots.size() - 1;
+        for (auto &s : slots) { s.state = 0; s.big = nullptr; }
+        used = live = 0;
+        for (auto &o : old)
+            if (o.state == 1) {
+                CoinSlot *n = insert(o.key, script(o), o.spk_len, o.amount);
+                (void)n;
+                delete o.big;
+                o.big = nullptr;
+            } else {
+                delete o.big;
+                o.big = nullptr;
+            }
+    }
+    std::vector<CoinSlot> slots;
+    size_t mask, used = 0, live = 0;
 };
 
 class ChainValidator {
@@ -62,14 +151,23 @@ public:
         OutPoint op;
         memcpy(op.b, txid, 32);
         memcpy(op.b + 32, &vout, 4);
-        utxo[op] = Coin{std::vector<uint8_t>(spk, spk + len), amount};
+        utxo.insert(op, spk, len, amount);
     }
     size_t UtxoSize() const { return utxo.size(); }
     size_t InputsChecked() const { return nInputs; }
 
     // Returns true and updates the UTXO set, or false with `reason` (the reference's reject strings where one exists).
+    // seconds spent per phase since construction: header (Equihash + hash), framing scan, txids + Merkle, UTXO walk,
+    // script checks (GPU calls incl. copies)
+    double phase[5] = {0, 0, 0, 0, 0};
+
     bool ConnectBlock(const uint8_t *blk, size_t len, std::string &reason) {
         const int dev0 = devs[0];
+        auto now = [] { return std::chrono::steady_clock::now(); };
+        auto secs = [](std::chrono::steady_clock::time_point a, std::chrono::steady_clock::time_point b) {
+            return std::chrono::duration<double>(b - a).count();
+        };
+        auto t0 = now();
         // header: Equihash + hash (ehN == 0 skips it, for chains built without solutions)
         const size_t soln = ehN ? ((size_t)1 << ehK) * (ehN / (ehK + 1) + 1) / 8 : 0;
         const size_t hdr_len = 140 + (soln < 253 ? 1 : 3) + soln;
@@ -83,6 +181,8 @@ public:
             if (!ok) { reason = "invalid-solution"; return false; } // CheckEquihashSolution (src/pow.cpp:298-323)
             memcpy(lastHash, hash, 32);
         }
+        auto t1 = now();
+        phase[0] += secs(t0, t1);
         // framing
         const size_t max_tx = len / 60 + 2, max_in = len / 41 + 2;
         tx_off.resize(max_tx + 1);
@@ -90,6 +190,8 @@ public:
         long ntx = 0;
         long nin = bcp_block_index_inputs(blk, len, 0, tx_off.data(), max_tx, in_off.data(), in_tx.data(), in_n.data(), max_in, &ntx);
         if (nin < 0 || ntx < 1) { reason = "bad-blk-framing"; return false; }
+        auto t2 = now();
+        phase[1] += secs(t1, t2);
         // txids + Merkle root (CheckBlock, src/validation.cpp:3236-3252)
         txids.resize((size_t)ntx * 32);
         uint8_t root[32];
@@ -100,37 +202,45 @@ public:
         }
         if (memcmp(root, blk + 36, 32) != 0) { reason = "bad-txnmrklroot"; return false; }
         if (mutated) { reason = "bad-txns-duplicate"; return false; }
-        // spent coins, transaction by transaction, seeing outputs created earlier in this block
-        std::unordered_map<OutPoint, Coin, OutPointHash> created;
-        std::vector<OutPoint> spent;
+        auto t3 = now();
+        phase[2] += secs(t2, t3);
+        // spent coins, transaction by transaction, seeing outputs created earlier in this block; everything is applied
+        // to the one table and journalled so that a rejected block can be rolled back
         spk_cat.clear();
         spk_off.assign(1, 0);
         amounts.clear();
-        spent.reserve(nin);
+        journalSpent.clear();
+        journalCreated.clear();
         size_t i = 0;
+        const size_t AHEAD = 16;
         for (long t = 0; t < ntx; t++) {
+            if ((size_t)t + AHEAD < (size_t)ntx) { // where transaction t+AHEAD's first output will land
+                OutPoint nx;
+                memcpy(nx.b, &txids[((size_t)t + AHEAD) * 32], 32);
+                memset(nx.b + 32, 0, 4);
+                utxo.prefetch(nx);
+            }
             for (; i < (size_t)nin && in_tx[i] == (uint32_t)t; i++) {
+                if (i + AHEAD < (size_t)nin) {
+                    OutPoint nx;
+                    memcpy(nx.b, blk + in_off[i + AHEAD], 36);
+                    utxo.prefetch(nx);
+                }
                 OutPoint op;
                 memcpy(op.b, blk + in_off[i], 36);
-                const Coin *c = nullptr;
-                auto it = created.find(op);
-                if (it != created.end()) c = &it->second;
-                else {
-                    auto iu = utxo.find(op);
-                    if (iu != utxo.end()) c = &iu->second;
-                }
-                bool again = false;
-                for (const OutPoint &s : spentThisTx) again = again || s == op;
-                if (!c || again || spentInBlock.count(op)) { Reset(); reason = "bad-txns-inputs-missingorspent"; return false; }
-                spk_cat.insert(spk_cat.end(), c->spk.begin(), c->spk.end());
+                CoinSlot *c = utxo.find(op); // a coin spent earlier in this block (or this tx) is already a tombstone
+                if (!c) { Rollback(); reason = "bad-txns-inputs-missingorspent"; return false; }
+                const uint8_t *sp = CoinTable::script(*c);
+                spk_cat.insert(spk_cat.end(), sp, sp + c->spk_len);
                 spk_off.push_back((uint32_t)spk_cat.size());
                 amounts.push_back(c->amount);
-                spentThisTx.push_back(op);
+                utxo.erase(c);
+                journalSpent.push_back(op);
             }
-            for (const OutPoint &s : spentThisTx) { spentInBlock.emplace(s, true); spent.push_back(s); }
-            spentThisTx.clear();
-            AddOutputs(blk, (uint32_t)t, created);
+            AddOutputs(blk, (uint32_t)t);
         }
+        auto t4 = now();
+        phase[3] += secs(t3, t4);
         // script checks, sharded by input index range over the devices
         errs.assign((size_t)nin, 0);
         const size_t G = devs.size(), per = ((size_t)nin + G - 1) / G;
@@ -150,22 +260,21 @@ public:
             else th.emplace_back(work);
         }
         for (auto &t : th) t.join();
+        phase[4] += secs(t4, now());
         for (size_t g = 0; g < G; g++)
-            if (rc[g] != BCP_OK) { Reset(); reason = "device-error: " + msg[g]; return false; }
+            if (rc[g] != BCP_OK) { Rollback(); reason = "device-error: " + msg[g]; return false; }
         for (size_t k = 0; k < (size_t)nin; k++) {
-            if (errs[k] == 255) { Reset(); reason = "script-not-in-fast-path (input " + std::to_string(k) + ")"; return false; }
+            if (errs[k] == 255) { Rollback(); reason = "script-not-in-fast-path (input " + std::to_string(k) + ")"; return false; }
             if (errs[k] != 0) { // ConnectBlock: "blk-bad-inputs" (src/validation.cpp:2124-2128)
-                Reset();
+                Rollback();
                 reason = "blk-bad-inputs (input " + std::to_string(k) + ", script error " + std::to_string(errs[k]) + ")";
                 return false;
             }
         }
-        // commit
-        for (const OutPoint &s : spent) utxo.erase(s);
-        for (auto &kv : created)
-            if (!spentInBlock.count(kv.first)) utxo[kv.first] = std::move(kv.second);
+        // commit: the table already holds the new state
         nInputs += (size_t)nin;
-        Reset();
+        journalSpent.clear();
+        journalCreated.clear();
         return true;
     }
     const uint8_t *LastBlockHash() const { return lastHash; }
@@ -190,7 +299,7 @@ public:
     }
 
 private:
-    void AddOutputs(const uint8_t *blk, uint32_t t, std::unordered_map<OutPoint, Coin, OutPointHash> &created) {
+    void AddOutputs(const uint8_t *blk, uint32_t t) {
         // skip inputs to reach the outputs of transaction t
         size_t pos = tx_off[t] + 4;
         uint64_t nin = ReadCompact(blk, pos);
@@ -209,7 +318,8 @@ private:
             memcpy(op.b, &txids[(size_t)t * 32], 32);
             uint32_t vv = (uint32_t)v;
             memcpy(op.b + 32, &vv, 4);
-            created[op] = Coin{std::vector<uint8_t>(blk + pos, blk + pos + sl), amt};
+            utxo.insert(op, blk + pos, sl, amt);
+            journalCreated.push_back(op);
             pos += sl;
         }
     }
@@ -222,17 +332,25 @@ private:
         pos += nb;
         return v;
     }
-    void Reset() {
-        spentInBlock.clear();
-        spentThisTx.clear();
+    // Undo a partially applied block: drop what it created, then put back what it spent.  The spent coins are
+    // re-inserted from the block's own staging arrays (outpoint journal + the scriptPubKey / amount arrays that were
+    // built for the GPU call), because a coin created by this block may have reused a spent coin's slot.
+    void Rollback() {
+        for (const OutPoint &op : journalCreated) {
+            CoinSlot *c = utxo.find(op);
+            if (c) utxo.erase(c);
+        }
+        for (size_t i = 0; i < journalSpent.size(); i++)
+            utxo.insert(journalSpent[i], &spk_cat[spk_off[i]], spk_off[i + 1] - spk_off[i], amounts[i]);
+        journalSpent.clear();
+        journalCreated.clear();
     }
 
     std::vector<int> devs;
     uint32_t flags;
     unsigned ehN, ehK;
-    std::unordered_map<OutPoint, Coin, OutPointHash> utxo;
-    std::unordered_map<OutPoint, bool, OutPointHash> spentInBlock;
-    std::vector<OutPoint> spentThisTx;
+    CoinTable utxo;
+    std::vector<OutPoint> journalSpent, journalCreated;
     std::vector<uint32_t> tx_off, in_off, in_tx, in_n, spk_off;
     std::vector<uint8_t> txids, spk_cat, errs;
     std::vector<int64_t> amounts;

@@ -1344,3 +1344,87 @@ long orc_block_verify_p2pkh(const uint8_t *blk, size_t len, int legacy, const ui
     free(tx_off); free(in_off); free(in_tx); free(in_n);
     return n;
 }
+
+/* ============================================================== synthetic chain generator ==== */
+/* Transactions of one block of the synthetic chain: tx j spends output 0 of prev_txid[j]
+ * (value prev_amt[j], locked to key prev_key[j]) and pays value-1000 to key (prev_key[j]+1) % nkeys; 1-in/1-out
+ * P2PKH, SIGHASH_ALL|FORKID, RFC 6979 signatures — the same shape tests/synth.py builds in Python, at C speed.
+ * On return prev_* describe the new outputs (for the next block) and out holds the serialized transactions back to
+ * back; returns their total size. */
+typedef struct {
+    const uint8_t *seed; size_t seedlen, key_base, nkeys; uint8_t *keys, *pubs, *spks;
+    uint8_t *prev_txid; uint32_t *prev_key; int64_t *prev_amt; uint8_t *slots; uint32_t *lens;
+} gc_arg;
+static void gc_keys(size_t lo, size_t hi, void *p) {
+    gc_arg *a = (gc_arg *)p;
+    for (size_t j = lo; j < hi; j++) {
+        uint8_t *k = a->keys + 32 * j;
+        tagged(a->seed, a->seedlen, "key", a->key_base + j, 0, k);
+        u256 d;
+        sc_set_b32(&d, k);
+        if (u256_is_zero(&d)) d.v[0] = 1;
+        u256_to_be(k, &d);
+        size_t l;
+        orc_pubkey_create(k, 1, a->pubs + 33 * j, &l);
+        uint8_t *spk = a->spks + 25 * j;
+        spk[0] = 0x76; spk[1] = 0xa9; spk[2] = 0x14; spk[23] = 0x88; spk[24] = 0xac;
+        orc_hash160(a->pubs + 33 * j, 33, spk + 3);
+    }
+}
+static void gc_txs(size_t lo, size_t hi, void *p) {
+    gc_arg *a = (gc_arg *)p;
+    for (size_t j = lo; j < hi; j++) {
+        uint32_t kj = a->prev_key[j], nk = (uint32_t)((kj + 1) % a->nkeys);
+        int64_t amt = a->prev_amt[j], outv = amt - 1000;
+        uint8_t tx[256], un[128];
+        /* unsigned form for the sighash: empty scriptSig */
+        size_t q = 0;
+        un[q++] = 2; un[q++] = 0; un[q++] = 0; un[q++] = 0; un[q++] = 1;
+        memcpy(un + q, a->prev_txid + 32 * j, 32); q += 32;
+        memset(un + q, 0, 4); q += 4;
+        un[q++] = 0;
+        memset(un + q, 0xff, 4); q += 4;
+        un[q++] = 1;
+        for (int b = 0; b < 8; b++) un[q++] = (uint8_t)((uint64_t)outv >> (8 * b));
+        un[q++] = 25;
+        memcpy(un + q, a->spks + 25 * nk, 25); q += 25;
+        memset(un + q, 0, 4); q += 4;
+        uint8_t sh[32], sig64[64], der[80];
+        orc_sighash_forkid(a->spks + 25 * kj, 25, un, q, 0, 0x41, amt, sh);
+        orc_sign_rfc6979(a->keys + 32 * kj, sh, sig64);
+        size_t dl = sizeof der;
+        orc_sig_to_der(sig64, der, &dl);
+        size_t w = 0;
+        memcpy(tx, un, 41); w = 41; /* version, count, outpoint */
+        tx[w++] = (uint8_t)(1 + dl + 1 + 1 + 33);
+        tx[w++] = (uint8_t)(dl + 1);
+        memcpy(tx + w, der, dl); w += dl;
+        tx[w++] = 0x41;
+        tx[w++] = 33;
+        memcpy(tx + w, a->pubs + 33 * kj, 33); w += 33;
+        memcpy(tx + w, un + 42, q - 42); w += q - 42; /* sequence, outputs, locktime */
+        memcpy(a->slots + 256 * j, tx, w);
+        a->lens[j] = (uint32_t)w;
+        orc_sha256d(tx, w, a->prev_txid + 32 * j);
+        a->prev_key[j] = nk;
+        a->prev_amt[j] = outv;
+    }
+}
+size_t orc_gen_chain_txs(const uint8_t *seed, size_t seedlen, size_t key_base, size_t nkeys, size_t ntx, uint8_t *prev_txid,
+                         uint32_t *prev_key, int64_t *prev_amt, int nthreads, uint8_t *out, size_t out_cap) {
+    if (seedlen > 200) seedlen = 200;
+    gc_arg a = {seed, seedlen, key_base, nkeys, NULL, NULL, NULL, prev_txid, prev_key, prev_amt, NULL, NULL};
+    a.keys = (uint8_t *)malloc(32 * nkeys); a.pubs = (uint8_t *)malloc(33 * nkeys); a.spks = (uint8_t *)malloc(25 * nkeys);
+    a.slots = (uint8_t *)malloc(256 * ntx); a.lens = (uint32_t *)malloc(4 * ntx);
+    pthread_once(&g_tab_once, build_g_tab);
+    parallel_for(nkeys, nthreads, gc_keys, &a);
+    parallel_for(ntx, nthreads, gc_txs, &a);
+    size_t tot = 0;
+    for (size_t j = 0; j < ntx; j++) {
+        if (tot + a.lens[j] > out_cap) { tot = 0; break; }
+        memcpy(out + tot, a.slots + 256 * j, a.lens[j]);
+        tot += a.lens[j];
+    }
+    free(a.keys); free(a.pubs); free(a.spks); free(a.slots); free(a.lens);
+    return tot;
+}

@@ -84,6 +84,9 @@ long orc_block_index_inputs(const uint8_t *blk, size_t len, int legacy, uint32_t
 long orc_block_verify_p2pkh(const uint8_t *blk, size_t len, int legacy, const uint8_t *spk, const uint32_t *spk_off,
                             const int64_t *amounts, uint32_t flags, int nthreads, uint8_t *err, size_t max_inputs);
 int orc_is_valid_signature_encoding(const uint8_t *sig, size_t len);
+/* synthetic chain generator at C speed (same shapes as tests/synth.py) */
+size_t orc_gen_chain_txs(const uint8_t *seed, size_t seedlen, size_t key_base, size_t nkeys, size_t ntx, uint8_t *prev_txid,
+                         uint32_t *prev_key, int64_t *prev_amt, int nthreads, uint8_t *out, size_t out_cap);
 
 #ifdef __cplusplus
 }

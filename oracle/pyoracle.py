@@ -78,6 +78,7 @@ class Impl:
             self._block_verify_p2pkh = L.fn("block_verify_p2pkh", C.c_long, u8p, sz, i, u8p, C.POINTER(u32), C.POINTER(i64),
                                             u32, i, u8p, sz)
             self._is_valid_sig_enc = L.fn("is_valid_signature_encoding", i, u8p, sz)
+            self._gen_chain_txs = L.fn("gen_chain_txs", sz, u8p, sz, sz, sz, sz, u8p, C.POINTER(u32), C.POINTER(i64), i, u8p, sz)
         else:
             L.fn("init", i)()
             self._sign = L.fn("sign", i, u8p, u8p, u8p)
@@ -235,6 +236,15 @@ class Impl:
             assert r < 0 or ((ok == 1) == (err == 0)).all()
         assert r == n, (r, n)
         return err
+
+    def gen_chain_txs(self, seed, key_base, nkeys, prev_txid, prev_key, prev_amt, nthreads=None):
+        """In place: advances (prev_txid (n,32) u8, prev_key (n,) u32, prev_amt (n,) i64) by one block; returns the txs."""
+        n = len(prev_key)
+        out = np.zeros(n * 200, dtype=np.uint8)
+        tot = self._gen_chain_txs(_p(seed), len(seed), key_base, nkeys, n, _p(prev_txid), prev_key.ctypes.data_as(C.POINTER(C.c_uint32)),
+                                  prev_amt.ctypes.data_as(C.POINTER(C.c_int64)), nthreads or os.cpu_count() or 1, _p(out), out.size)
+        assert tot > 0
+        return out[:tot].tobytes()
 
     def block_index(self, blk, legacy, max_tx=1 << 20):
         off = (C.c_uint32 * (max_tx + 1))()

@@ -435,3 +435,45 @@ def synthetic_chain(nblocks=6, ntx=20, nkeys=8, equihash=True, corrupt=None):
         blocks.append(hdr + _compact(len(txs)) + b"".join(txs))
         prev_out = new_out
     return blocks, seeds, prevs
+
+
+def synthetic_chain_fast(nblocks=100, ntx=41650, nkeys=4096, equihash=True):
+    """The chain of synthetic_chain() at full size, with the transactions built by the oracle's C generator
+    (orc_gen_chain_txs): ~0.2 s per 8 MB block.  Yields blocks one at a time; seeds via chain_seeds()."""
+    o = po.oracle()
+    prev_txid, prev_key, prev_amt = chain_seed_arrays(ntx, nkeys)
+    spk0 = p2pkh_script(o.pubkey_create(seckey(5000), True))
+    for b in range(nblocks):
+        body = o.gen_chain_txs(SEED, 5000, nkeys, prev_txid, prev_key, prev_amt)
+        cb = (2).to_bytes(4, "little") + b"\x01" + bytes(32) + b"\xff\xff\xff\xff" + b"\x04" + (700000 + b).to_bytes(4, "little")
+        cb += b"\xff\xff\xff\xff" + b"\x01" + (1250000000).to_bytes(8, "little") + bytes([25]) + spk0 + bytes(4)
+        leaves = o.sha256d(cb) + prev_txid.tobytes()  # prev_txid now holds this block's txids
+        root, _ = o.merkle_root(leaves)
+        nonce = 0
+        while True:
+            hdr = synthetic_header(height=700000 + b, merkle_root=root, nonce_tag=(b << 20) | nonce, n=48, k=5)
+            if not equihash:
+                break
+            sols = equihash_solve_48_5(hdr[:140])
+            if sols:
+                hdr = hdr[:140] + _compact(36) + sols[0]
+                break
+            nonce += 1
+        yield hdr + _compact(ntx + 1) + cb + body
+
+
+def chain_seed_arrays(ntx, nkeys):
+    prev_txid = np.zeros((ntx, 32), dtype=np.uint8)
+    for j in range(ntx):
+        prev_txid[j] = np.frombuffer(hashlib.sha256(hashlib.sha256(SEED + b"chainprev" + j.to_bytes(8, "little")).digest()).digest(), np.uint8)
+    prev_key = (np.arange(ntx) % nkeys).astype(np.uint32)
+    prev_amt = np.full(ntx, 10**7, dtype=np.int64)
+    return prev_txid, prev_key, prev_amt
+
+
+def chain_seeds(ntx, nkeys):
+    """(txid, vout, spk, amount) of the coins block 0 of synthetic_chain_fast spends."""
+    o = po.oracle()
+    spks = [p2pkh_script(o.pubkey_create(seckey(5000 + j), True)) for j in range(nkeys)]
+    t, k, a = chain_seed_arrays(ntx, nkeys)
+    return [(t[j].tobytes(), 0, spks[int(k[j])], int(a[j])) for j in range(ntx)]
