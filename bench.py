@@ -311,6 +311,9 @@ def main():
     local = int(os.environ.get("LOCAL_RANK", "0"))
     dist = world > 1
     if dist:
+        # stdout carries exactly one JSON line: keep NCCL's own banner ("NCCL version ...", printed to stdout under
+        # NCCL_DEBUG=VERSION/INFO) out of it
+        os.environ["NCCL_DEBUG"] = "WARN"
         import torch.distributed as td
 
         td.init_process_group("nccl", device_id=torch.device("cuda", local))
@@ -390,6 +393,7 @@ def main():
         e2e_ms = e2e_s * 1e3
     if rank != 0:
         if dist:
+            td.barrier()  # rank 0 is still measuring its secondary sections; leave together
             td.destroy_process_group()
         return
 
@@ -436,8 +440,9 @@ def main():
         line["equihash10k"] = equihash_bench(eng)
         if args.chain_blocks > 0:
             line["chain"] = chain_bench(args, local)
-    print(json.dumps(line))
+    print(json.dumps(line), flush=True)
     if dist:
+        td.barrier()
         td.destroy_process_group()
 
 
