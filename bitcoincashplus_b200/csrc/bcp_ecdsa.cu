@@ -2,7 +2,7 @@
 // points (include/bcp_gpu.h).  The arithmetic lives in fe.cuh / scalar.cuh / ge.cuh / ecdsa.cuh.
 //
 // Launch shape
-//   k_ecdsa_prep   one thread per BCP_PREP_K signatures (thread t takes signatures t, t+T, t+2T, ...
+//   k_ecdsa_prep   one thread per K signatures (K = 8, 16 or 32 by batch size) (thread t takes signatures t, t+T, t+2T, ...
 //                  so that the byte loads of a warp stay adjacent), 128 threads per block
 //   k_ecdsa_point  one thread per signature, 128 threads per block, four blocks per SM; the per-thread
 //                  {1..8}Q tables (512 B) live in global scratch next to the phase-1 records (the first
@@ -18,8 +18,8 @@
 #define BCP_STEP_SYNC() __syncthreads()
 #endif
 #include "ecdsa.cuh"
+#include <cstdlib>
 
-#define BCP_PREP_K 32
 #if BCP_POINT_VARIANT == 1
 #ifndef BCP_POINT_THREADS
 #define BCP_POINT_THREADS 256
@@ -52,6 +52,7 @@ __global__ void __launch_bounds__(128) k_gcomb_build(uint32_t *gcomb) {
     for (int i = 0; i < 16; i++) out[i] = e[i];
 }
 
+template <int K>
 __global__ void __launch_bounds__(128) k_ecdsa_prep(const uint8_t *__restrict__ msg32, const uint8_t *__restrict__ sig64,
                                                     size_t n, uint32_t flags, uint32_t *__restrict__ rec) {
     const size_t T = (size_t)gridDim.x * blockDim.x;
@@ -60,13 +61,13 @@ __global__ void __launch_bounds__(128) k_ecdsa_prep(const uint8_t *__restrict__ 
     // Montgomery's trick over this thread's signatures: pre[j] = s_0 * ... * s_{j-1}.  Only the prefix products
     // are kept (local memory); the second pass re-parses each signature, which is far cheaper than holding
     // K x (r, s, m) per thread.  K = 32: one 334-multiplication inversion per 32 signatures.
-    scalar pre[BCP_PREP_K];
+    scalar pre[K];
     scalar acc;
 #pragma unroll
     for (int i = 0; i < 8; i++) acc.v[i] = (i == 0);
     int cnt = 0;
 #pragma unroll 1
-    for (int j = 0; j < BCP_PREP_K; j++) {
+    for (int j = 0; j < K; j++) {
         size_t i = t + (size_t)j * T;
         if (i >= n) break;
         sig_scalars g;
@@ -141,9 +142,17 @@ int bcp_ecdsa_launch(bcp_ctx *c, const uint8_t *d_msg, const uint8_t *d_pub, con
     uint32_t *d_rec = d_scratch, *d_tab = d_scratch + cap * BCP_REC_WORDS;
     for (size_t off = 0; off < n; off += BCP_SLICE) {
         const size_t m = n - off < BCP_SLICE ? n - off : BCP_SLICE;
-        size_t prep_threads = (m + BCP_PREP_K - 1) / BCP_PREP_K;
+        // signatures per prep thread: one 334-multiplication inversion is shared by K signatures, but a thread's work is
+        // serial, so small batches trade total work for parallelism (measured on B200 with tools/prep_sweep.py:
+        // 41,650 signatures K=4 1.96 ms vs K=32 2.25 ms; 227k K=16 best; 1M K=32 best)
+        static const int forced = getenv("BCP_PREP_K") ? atoi(getenv("BCP_PREP_K")) : 0;
+        const int K = forced ? forced : (m >= 600000 ? 32 : m >= 150000 ? 16 : m >= 100000 ? 8 : 4);
+        size_t prep_threads = (m + K - 1) / K;
         unsigned prep_blocks = (unsigned)((prep_threads + 127) / 128);
-        k_ecdsa_prep<<<prep_blocks, 128, 0, st>>>(d_msg + 32 * off, d_sig + 64 * off, m, flags, d_rec);
+        if (K >= 32) k_ecdsa_prep<32><<<prep_blocks, 128, 0, st>>>(d_msg + 32 * off, d_sig + 64 * off, m, flags, d_rec);
+        else if (K >= 16) k_ecdsa_prep<16><<<prep_blocks, 128, 0, st>>>(d_msg + 32 * off, d_sig + 64 * off, m, flags, d_rec);
+        else if (K >= 8) k_ecdsa_prep<8><<<prep_blocks, 128, 0, st>>>(d_msg + 32 * off, d_sig + 64 * off, m, flags, d_rec);
+        else k_ecdsa_prep<4><<<prep_blocks, 128, 0, st>>>(d_msg + 32 * off, d_sig + 64 * off, m, flags, d_rec);
         unsigned blocks = (unsigned)((m + BCP_POINT_THREADS - 1) / BCP_POINT_THREADS);
         k_ecdsa_point<<<blocks, BCP_POINT_THREADS, 0, st>>>(d_pub + 65 * off, d_sig + 64 * off, m, d_rec, d_tab, c->gcomb,
                                                            d_ok + off);
