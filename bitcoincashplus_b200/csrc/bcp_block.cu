@@ -64,6 +64,22 @@ static int rd_compact_h(const uint8_t *p, size_t len, size_t *pos, uint64_t *v) 
 #define BCP_FLAGS_POSTFORK_REQUIRED ((1u << 1) | (1u << 2) | (1u << 3) | (1u << 14) | (1u << 16))
 #define BCP_FLAG_ALLOW_NON_FORKID (1u << 17)
 
+// compact size with the canonical-encoding and MAX_SIZE rules of ReadCompactSize (src/serialize.h:260-300)
+static int rd_compact_canon(const uint8_t *p, size_t len, size_t *pos, uint64_t *v) {
+    if (*pos >= len) return 0;
+    const uint8_t ch = p[(*pos)++];
+    if (ch < 253) { *v = ch; return 1; }
+    const int nb = ch == 253 ? 2 : ch == 254 ? 4 : 8;
+    if (*pos + nb > len) return 0;
+    uint64_t x = 0;
+    for (int i = 0; i < nb; i++) x |= (uint64_t)p[*pos + i] << (8 * i);
+    *pos += nb;
+    if ((nb == 2 && x < 253) || (nb == 4 && x < 0x10000ull) || (nb == 8 && x < 0x100000000ull)) return 0; /* non-canonical */
+    if (x > 0x02000000ull) return 0;                                                                        /* MAX_SIZE */
+    *v = x;
+    return 1;
+}
+
 extern "C" {
 
 // Framing scan that also lists every non-coinbase input (CTransaction::IsCoinBase: a single input with a null
@@ -71,14 +87,31 @@ extern "C" {
 // in_n = its ordinal in that transaction.  Returns the number of inputs (-1 malformed, -2 capacity); *ntx_out = ntx.
 BCP_API long bcp_block_index_inputs(const uint8_t *blk, size_t len, int legacy_header, uint32_t *tx_off, size_t max_tx,
                                     uint32_t *in_off, uint32_t *in_tx, uint32_t *in_n, size_t max_inputs, long *ntx_out) {
-    long ntx = bcp_block_index(blk, len, legacy_header, tx_off, max_tx);
-    if (ntx < 0) return ntx;
-    if (ntx_out) *ntx_out = ntx;
+    // One pass (this scan sits on the critical path of a block: nothing can launch before the offsets exist).
+    // Same acceptance rules as bcp_block_index: canonical compact sizes, MAX_SIZE, everything inside the buffer.
+    size_t pos;
+    uint64_t v, ntx;
+    if (legacy_header) {
+        pos = 80;
+    } else {
+        pos = 140;
+        if (len < 140 || !rd_compact_h(blk, len, &pos, &v)) return -1;
+        pos += v;
+    }
+    if (pos > len || !rd_compact_h(blk, len, &pos, &ntx)) return -1;
+    if (ntx > max_tx) return -2;
     size_t cnt = 0;
-    for (long t = 0; t < ntx; t++) {
-        size_t pos = tx_off[t] + 4;
-        uint64_t nin, sl;
-        if (!rd_compact_h(blk, len, &pos, &nin)) return -1;
+#define BCP_RD_COMPACT(dst)                                                                  \
+    do {                                                                                     \
+        if (pos < len && blk[pos] < 253) { dst = blk[pos++]; }                               \
+        else if (!rd_compact_canon(blk, len, &pos, &dst)) return -1;                         \
+    } while (0)
+    for (uint64_t t = 0; t < ntx; t++) {
+        tx_off[t] = (uint32_t)pos;
+        uint64_t nin, nout, sl;
+        if (pos + 4 > len) return -1;
+        pos += 4;
+        BCP_RD_COMPACT(nin);
         bool coinbase = false;
         if (nin == 1 && pos + 36 <= len) {
             coinbase = true;
@@ -86,16 +119,31 @@ BCP_API long bcp_block_index_inputs(const uint8_t *blk, size_t len, int legacy_h
             for (int b = 32; b < 36; b++) coinbase = coinbase && blk[pos + b] == 0xFF;
         }
         for (uint64_t i = 0; i < nin; i++) {
+            if (pos + 36 > len) return -1;
             if (!coinbase) {
                 if (cnt >= max_inputs) return -2;
                 in_off[cnt] = (uint32_t)pos; in_tx[cnt] = (uint32_t)t; in_n[cnt] = (uint32_t)i;
                 cnt++;
             }
             pos += 36;
-            if (!rd_compact_h(blk, len, &pos, &sl)) return -1;
+            BCP_RD_COMPACT(sl);
+            if (pos + sl + 4 > len) return -1;
             pos += sl + 4;
         }
+        BCP_RD_COMPACT(nout);
+        for (uint64_t i = 0; i < nout; i++) {
+            if (pos + 8 > len) return -1;
+            pos += 8;
+            BCP_RD_COMPACT(sl);
+            if (pos + sl > len) return -1;
+            pos += sl;
+        }
+        if (pos + 4 > len) return -1;
+        pos += 4;
     }
+#undef BCP_RD_COMPACT
+    tx_off[ntx] = (uint32_t)pos;
+    if (ntx_out) *ntx_out = (long)ntx;
     return (long)cnt;
 }
 
