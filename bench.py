@@ -86,6 +86,16 @@ def cpu_baseline(msg, pub, sig, budget_s=12.0):
             "sample": "first %d of the %d-signature batch, %.1f s wall, %d threads" % (sample, n, dt, cores)}
 
 
+def traffic_from_profile(n):
+    """dram__bytes_read.sum + dram__bytes_write.sum of k_ecdsa_point for one launch, from the committed ncu --set full
+    capture (profiles/ecdsa_point_traffic.json, taken at the default batch size); None for other sizes."""
+    try:
+        t = json.load(open(os.path.join(ROOT, "profiles", "ecdsa_point_traffic.json")))
+        return t["dram_bytes_per_launch"] if t.get("sigs") == n else None
+    except Exception:
+        return None
+
+
 def block_bench(eng, args, bcp):
     """Secondary measurement (BASELINE.json configs[2], "8 MB blocks validated/sec"): one synthetic post-fork block of
     41,650 one-input P2PKH transactions through bcp_gpu_block_connect_p2pkh (host framing scan, H2D of the raw
@@ -420,11 +430,13 @@ def main():
         "vs_baseline": None, "dtype": "u32", "data": "synthetic",
         "config": {"workload": "configs[1]: batched secp256k1_ecdsa_verify, 1M synthetic signatures incl. 1% corrupted",
                    "sigs_per_gpu": n, "sharding": "by signature index, one process per GPU, no collective",
-                   "l2_policy": "inputs+scratch per step = %.0f MB (> 126 MB L2 at the default size)"
-                   % ((n * (161 + 80 + 1)) / 1e6)},
-        "roofline": {"bound": "int32-mul pipe (no HBM/tensor bound applies; reported in the contract's shape)",
+                   "l2_policy": "inputs + scratch touched per step = %.0f MB (> 126 MB L2 at the default size)"
+                   % ((n * (161 + 80 + 512 + 1)) / 1e6)},
+        "roofline": {"bound": "int32",
+                     "bound_note": "32x32->64 multiply-add pipe (IMAD.WIDE on fmaheavy): nothing on this path is HBM- or "
+                                   "tensor-bound (SURVEY.md 8d); the HBM view is under 'hbm'",
                      "achieved": achieved / 1e12, "peak": peak_imad / 1e12, "unit": "Tmul32/s", "frac": achieved / peak_imad,
-                     "traffic": None,
+                     "traffic": traffic_from_profile(n),
                      "peak_source": "bcp_gpu_measure_int_peak(1): IMAD.WIDE.U32.X carry chains, measured live",
                      "pipes_tops_measured": pipes,
                      "hbm": {"achieved_gbs": per_gpu * BYTES_PER_VERIFY / 1e9, "peak_gbs": hbm_peak,

@@ -72,7 +72,9 @@ BCP_API int bcp_gpu_ecdsa_verify_batch(int device, const uint8_t *msg32, const u
                                size_t n, uint32_t flags, uint8_t *ok);
 BCP_API int bcp_gpu_ecdsa_verify_batch_dev(int device, const uint8_t *d_msg32, const uint8_t *d_pub65,
                                    const uint8_t *d_sig64, size_t n, uint32_t flags, uint8_t *d_ok, void *stream);
-/* Bytes of device scratch bcp_gpu_ecdsa_verify_batch_dev needs for n signatures (it grows the
+/* NOTE on the "_dev" forms: they use the context's scratch buffer.  Work enqueued by two "_dev" calls on the same
+ * device must not overlap on the GPU (use one stream, or synchronise between calls on different streams).
+ * Bytes of device scratch bcp_gpu_ecdsa_verify_batch_dev needs for n signatures (it grows the
  * context's scratch buffer on demand; calling this first with the largest n avoids a reallocation
  * inside a timed region). */
 BCP_API size_t bcp_gpu_ecdsa_scratch_bytes(size_t n);
