@@ -96,8 +96,10 @@ def traffic_from_profile(n):
         return None
 
 
-def block_bench(eng, args, bcp):
-    """Secondary measurement (BASELINE.json configs[2], "8 MB blocks validated/sec"): one synthetic post-fork block of
+def block_bench(eng, args, bcp, sync=None):
+    """`sync` (multi-GPU runs): callable(seconds) -> max over ranks, entered by every rank; each rank validates its own
+    copy of the block on its own GPU (weak scaling, no collective on the data path) and rank 0 adds the CPU side.
+    Secondary measurement (BASELINE.json configs[2], "8 MB blocks validated/sec"): one synthetic post-fork block of
     41,650 one-input P2PKH transactions through bcp_gpu_block_connect_p2pkh (host framing scan, H2D of the raw
     block + spent outputs, txids, Merkle root, per-input script checks, batched ECDSA, verdict read-back — all
     inside the timed region), next to the reference's CPU path for the same block: CBlock deserialization + txids +
@@ -127,13 +129,21 @@ def block_bench(eng, args, bcp):
     res = eng.block_connect_p2pkh(blk_np, (cat, off), am, synth.POSTFORK_FLAGS)  # warm-up + correctness
     assert res["all_ok"] and res["root"] == blk[36:68] and not res["mutated"]
     reps = 10
+    world = 1
+    if sync is not None:
+        world = sync(0.0, count=True)
     t0 = time.perf_counter()
     for _ in range(reps):
         res = eng.block_connect_p2pkh(blk_np, (cat, off), am, synth.POSTFORK_FLAGS)
     gpu_s = (time.perf_counter() - t0) / reps
-    out = {"block_bytes": len(blk), "inputs": len(spk), "gpu_ms_per_block": gpu_s * 1e3, "gpu_blocks_per_s": 1.0 / gpu_s,
-           "gpu_inputs_per_s": len(spk) / gpu_s, "gen_seconds": gen_s,
-           "timed": "bcp_gpu_block_connect_p2pkh end to end (host framing scan + H2D + kernels + D2H), pinned host buffers"}
+    if sync is not None:
+        gpu_s = sync(gpu_s)
+        if int(os.environ.get("RANK", "0")) != 0:
+            return None
+    out = {"block_bytes": len(blk), "inputs": len(spk), "gpus": world, "gpu_ms_per_block": gpu_s * 1e3,
+           "gpu_blocks_per_s": world / gpu_s, "gpu_inputs_per_s": world * len(spk) / gpu_s, "gen_seconds": gen_s,
+           "timed": "bcp_gpu_block_connect_p2pkh end to end (host framing scan + H2D + kernels + D2H), pinned host buffers; "
+                    "one block per GPU per repetition, max over ranks"}
     cores = os.cpu_count() or 1
     if po.have_ref():
         r = po.ref()
@@ -189,7 +199,7 @@ def equihash_bench(eng):
             "timed": "bcp_gpu_equihash_verify_batch incl. H2D of 14.9 MB, verdicts + header hashes D2H"}
 
 
-def chain_bench(args, device):
+def chain_bench(args, devices):
     """Secondary measurement in the shape of BASELINE.json configs[4]: a synthetic chain of 8 MB blocks with real UTXO
     dependencies (block b spends block b-1) and valid regtest Equihash (48,5) headers, connected block by block by the
     host-side connector (include/compat/bcp_chain.h): Equihash + header hash, txids + Merkle, UTXO lookups, P2PKH script
@@ -212,7 +222,7 @@ def chain_bench(args, device):
     L.bcp_chain_connect_block.argtypes = [C.c_void_p, C.c_char_p, C.c_size_t, C.c_char_p, C.c_size_t]
     L.bcp_chain_free.argtypes = [C.c_void_p]
     err = C.create_string_buffer(256)
-    h = L.bcp_chain_new((C.c_int * 1)(device), 1, synth.POSTFORK_FLAGS, 48, 5, err, 256)
+    h = L.bcp_chain_new((C.c_int * len(devices))(*devices), len(devices), synth.POSTFORK_FLAGS, 48, 5, err, 256)
     assert h, err.value
     for txid, vout, spk, amount in seeds:
         L.bcp_chain_add_coin(h, txid, vout, spk, len(spk), amount)
@@ -241,7 +251,9 @@ def chain_bench(args, device):
     for p, _ in pinned:
         G.bcp_gpu_host_free(p)
     L.bcp_chain_free(h)
-    out = {"blocks": nb, "inputs_per_block": ntx, "block_bytes": len(blocks[0]), "gpu_seconds_total": total,
+    out = {"blocks": nb, "inputs_per_block": ntx, "block_bytes": len(blocks[0]), "gpus": len(devices),
+           "sharding": "one host chain walk; each block's inputs split by index across the GPUs, verdicts ANDed on the host",
+           "gpu_seconds_total": total,
            "gpu_blocks_per_s": nb / total, "gpu_ms_per_block_median": sorted(per_block)[len(per_block) // 2] * 1e3,
            "gpu_ms_first_block": per_block[0] * 1e3, "ms_per_block_by_phase": phases, "gen_seconds": gen_s,
            "timed": "bcp::ChainValidator::ConnectBlock per block (block bytes in pinned host memory, in-memory UTXO table on the host)"}
@@ -327,6 +339,7 @@ def main():
         import torch.distributed as td
 
         td.init_process_group("nccl", device_id=torch.device("cuda", local))
+        hostgrp = td.new_group(backend="gloo")  # host-side barriers/maxima for the secondary sections (no GPU spin)
     torch.cuda.set_device(local)
     dev = torch.device("cuda", local)
     eng = bcp.Engine(local)
@@ -401,9 +414,18 @@ def main():
         ms, e2e_ms = t[0].item(), t[1].item()
     else:
         e2e_ms = e2e_s * 1e3
+    def host_sync(seconds, count=False):
+        """barrier over the host-side group; returns the max of `seconds` over ranks (or the world size)"""
+        t = torch.tensor([seconds], dtype=torch.float64)
+        td.all_reduce(t, op=td.ReduceOp.MAX, group=hostgrp)
+        return world if count else t[0].item()
+
+    blk_section = None
+    if not args.no_block:
+        blk_section = block_bench(eng, args, bcp, host_sync if dist else None)
     if rank != 0:
         if dist:
-            td.barrier()  # rank 0 is still measuring its secondary sections; leave together
+            td.barrier(group=hostgrp)  # rank 0 is still measuring its secondary sections; leave together
             td.destroy_process_group()
         return
 
@@ -448,13 +470,13 @@ def main():
     if not args.no_cpu_baseline:
         line["cpu_baseline"] = cpu_baseline(msg, pub, sig)
     if not args.no_block:
-        line["block8mb"] = block_bench(eng, args, bcp)
+        line["block8mb"] = blk_section
         line["equihash10k"] = equihash_bench(eng)
         if args.chain_blocks > 0:
-            line["chain"] = chain_bench(args, local)
+            line["chain"] = chain_bench(args, list(range(world)))
     print(json.dumps(line), flush=True)
     if dist:
-        td.barrier()
+        td.barrier(group=hostgrp)
         td.destroy_process_group()
 
 

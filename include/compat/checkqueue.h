@@ -16,8 +16,17 @@
 // calling thread's batch and answers true.  Wait() then hands the concatenated batch to the GPUs
 // (bcp_gpu_ecdsa_verify_batch with BCP_ECDSA_FLAG_NORMALIZE_S == CPubKey::Verify semantics), sharded by index
 // range over every initialised device, and returns host_result AND all(verdicts) — the same `fAllOk &= fOk`
-// reduction as :77, with no exchange between devices.  Exact for OP_CHECKSIG under SCRIPT_VERIFY_NULLFAIL (the
-// post-fork flag set); see INTEGRATION.md §2 for the callers that must stay synchronous.
+// reduction as :77, with no exchange between devices.
+//
+// Replay.  "true" is only an assumption, and a script may legitimately see a failing
+// comparison: OP_CHECKMULTISIG walks the keys until one matches (src/script/interpreter.cpp:1054-1187), and
+// without SCRIPT_VERIFY_NULLFAIL a script may branch on a failed OP_CHECKSIG.  So every check that reached a
+// signature comparison is kept until Wait().  A check whose assumptions the devices all confirmed is final with
+// the result it returned.  A check with at least one refuted assumption is run again with the verdicts known so
+// far answered exactly and only new comparisons assumed; those go to the devices in the next round.  A run is
+// final as soon as everything it assumed has been confirmed, and each round settles at least one new comparison
+// per open check, so this ends after at most (number of distinct comparisons the script can make) rounds — two
+// for an m-of-n multisig signed by keys in order.  No signature is ever verified on the CPU.
 // A device error makes Wait() return false (never a silent accept).
 //
 // Threading primitives are std:: (the reference uses boost::mutex / condition_variable; Boost is not a
@@ -45,12 +54,82 @@ private:
     bool fResult = true;
     bool fQuit = false;
     const unsigned int nBatchSize;
-    std::vector<std::unique_ptr<bcp::Recorder>> recorders; // one per thread that evaluated checks for this block
-    unsigned long nEpoch = 0;       // bumped by Wait(): a thread's recorder is only valid within one block
+    // One per thread that evaluated checks for this block: its batch, and the checks that reached at least one
+    // signature comparison (moved in), each with the end of its range in the batch and the result it returned.
+    struct Lane {
+        bcp::Recorder rec;
+        std::vector<T> kept;
+        std::vector<size_t> end;
+        std::vector<uint8_t> result;
+    };
+    std::vector<std::unique_ptr<Lane>> lanes;
+    unsigned long nEpoch = 0;       // bumped by Wait(): a thread's lane is only valid within one block
 
-    bcp::Recorder *NewRecorder() { // called with mtx held
-        recorders.emplace_back(new bcp::Recorder());
-        return recorders.back().get();
+    Lane *NewLane() { // called with mtx held
+        lanes.emplace_back(new Lane());
+        return lanes.back().get();
+    }
+
+    // Settles the assumed verdicts (see "Replay" above).  Runs on the thread that called Wait().
+    static bool Resolve(std::vector<std::unique_ptr<Lane>> &ls) {
+        std::vector<bcp::Recorder *> recs;
+        for (auto &l : ls) recs.push_back(&l->rec);
+        std::vector<uint8_t> ok;
+        if (!bcp::VerifyRecorders(recs, ok)) return false;
+        bcp::KnownVerdicts known;
+        std::vector<T *> open;
+        size_t base = 0;
+        for (auto &l : ls) {
+            size_t b = 0;
+            for (size_t i = 0; i < l->kept.size(); i++) {
+                const size_t e = l->end[i];
+                bool confirmed = true;
+                for (size_t j = b; j < e; j++) confirmed = confirmed && ok[base + j];
+                if (confirmed) {
+                    if (!l->result[i]) return false;
+                } else {
+                    for (size_t j = b; j < e; j++) known[l->rec.keyAt(j)] = ok[base + j] != 0;
+                    open.push_back(&l->kept[i]);
+                }
+                b = e;
+            }
+            base += l->rec.size();
+        }
+        while (!open.empty()) {
+            bcp::Recorder rr;
+            rr.known = &known;
+            std::vector<size_t> end;
+            std::vector<uint8_t> result;
+            {
+                bcp::Recorder::Scope scope(&rr);
+                for (T *c : open) {
+                    const size_t before = rr.size();
+                    const bool r = (*c)();
+                    if (rr.size() == before && !r) return false; // nothing assumed: final
+                    end.push_back(rr.size());
+                    result.push_back(r);
+                }
+            }
+            if (rr.size() == 0) return true;
+            std::vector<bcp::Recorder *> one{&rr};
+            if (!bcp::VerifyRecorders(one, ok)) return false;
+            std::vector<T *> next;
+            size_t b = 0;
+            for (size_t i = 0; i < open.size(); i++) {
+                const size_t e = end[i];
+                bool confirmed = true;
+                for (size_t j = b; j < e; j++) confirmed = confirmed && ok[j];
+                if (confirmed) {
+                    if (!result[i]) return false;
+                } else {
+                    for (size_t j = b; j < e; j++) known[rr.keyAt(j)] = ok[j] != 0;
+                    next.push_back(open[i]);
+                }
+                b = e;
+            }
+            open.swap(next);
+        }
+        return true;
     }
 
     // Shared by workers and the master.  A worker sleeps when the queue is empty; the master returns once
@@ -58,8 +137,8 @@ private:
     bool Run(bool fMaster) {
         std::vector<T> mine;
         mine.reserve(nBatchSize);
-        bcp::Recorder *rec = nullptr;
-        unsigned long recEpoch = 0;
+        Lane *lane = nullptr;
+        unsigned long laneEpoch = 0;
         bool fRegistered = false;
         unsigned int nDone = 0;
         bool fOk = true;
@@ -98,14 +177,25 @@ private:
                     pending.pop_back();
                 }
                 fOk = fResult; // once a check has failed the rest is only drained, not evaluated (:121-126)
-                if (rec == nullptr || recEpoch != nEpoch) {
-                    rec = NewRecorder();
-                    recEpoch = nEpoch;
+                if (lane == nullptr || laneEpoch != nEpoch) {
+                    lane = NewLane();
+                    laneEpoch = nEpoch;
                 }
             }
-            bcp::Recorder::Scope scope(rec);
-            for (T &check : mine)
-                if (fOk) fOk = check();
+            bcp::Recorder::Scope scope(&lane->rec);
+            for (T &check : mine) {
+                if (!fOk) continue;
+                const size_t before = lane->rec.size();
+                const bool r = check();
+                if (lane->rec.size() == before) {
+                    fOk = r; // no signature comparison was reached: the result is final
+                } else {     // the result rests on assumed verdicts: settled in Wait()
+                    lane->kept.emplace_back();
+                    check.swap(lane->kept.back());
+                    lane->end.push_back(lane->rec.size());
+                    lane->result.push_back(r);
+                }
+            }
             nDone = (unsigned int)mine.size();
             mine.clear();
         }
@@ -121,17 +211,17 @@ public:
     //! Wait until all queued checks are evaluated, run the deferred signature batch, return the AND, reset.
     bool Wait() {
         Run(true);
-        std::vector<std::unique_ptr<bcp::Recorder>> recs;
+        std::vector<std::unique_ptr<Lane>> ls;
         bool hostOk;
         {
             std::lock_guard<std::mutex> lock(mtx);
             hostOk = fResult;
             fResult = true;
-            recs.swap(recorders); // nothing is outstanding: no thread is inside a check
+            ls.swap(lanes); // nothing is outstanding: no thread is inside a check
             nEpoch++;
         }
         if (!hostOk) return false; // the reference would have stopped evaluating too: nothing to launch
-        return bcp::VerifyRecorded(recs);
+        return Resolve(ls);
     }
 
     //! Add a batch of checks; the elements are moved out of vChecks (:147-149).
