@@ -149,6 +149,21 @@ class Engine:
               "bcp_gpu_equihash_verify_batch")
         return ok, hashes
 
+    def header_check_batch(self, n, k, hdrs, pow_limit, pow_limit_legacy, fork_height=0):
+        """CheckBlockHeader for a batch (src/validation.cpp:3202-3220) + in-batch linkage.  pow limits: 32 bytes each,
+        uint256 memory order.  -> dict(ok_solution, ok_pow, linked, hash)."""
+        hdrs = _np(hdrs)
+        count, hdr_len = hdrs.shape
+        out = {k_: np.zeros(count, dtype=np.uint8) for k_ in ("ok_solution", "ok_pow", "linked")}
+        out["hash"] = np.zeros((count, 32), dtype=np.uint8)
+        lim, liml = _np(np.frombuffer(bytes(pow_limit), dtype=np.uint8)), _np(np.frombuffer(bytes(pow_limit_legacy), dtype=np.uint8))
+        assert lim.size == 32 and liml.size == 32
+        check(lib().bcp_gpu_header_check_batch(self.device, n, k, hdrs.ctypes.data, hdr_len, hdr_len, count, lim.ctypes.data,
+                                               liml.ctypes.data, fork_height, out["ok_solution"].ctypes.data,
+                                               out["ok_pow"].ctypes.data, out["linked"].ctypes.data, out["hash"].ctypes.data),
+              "bcp_gpu_header_check_batch")
+        return out
+
     # ---- measurement
     def measure_int_peak(self, which=0):
         v = C.c_double(0)

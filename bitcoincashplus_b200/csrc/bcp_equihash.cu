@@ -20,6 +20,7 @@
 //                slice, then a shared-memory XOR tree.  512 / 2^K headers per 512-thread block.
 #include "bcp_ctx.cuh"
 #include "blake2b.cuh"
+#include "pow.cuh"
 #include <cstring>
 
 template <unsigned N, unsigned K>
@@ -214,6 +215,30 @@ static int eh_dispatch(bcp_ctx *c, unsigned n, unsigned k, const uint8_t *d_hdrs
 int bcp_sha256d_strided_dev(bcp_ctx *c, const uint8_t *d_data, size_t stride, size_t len, size_t count, uint8_t *d_out,
                             cudaStream_t st); // bcp_hash.cu
 
+// Per header: CheckProofOfWork(GetHash(), nBits, IsBCPEnabled(nHeight)) (src/validation.cpp:3214-3217, src/pow.cpp:141-161)
+// and whether hashPrevBlock equals the hash of the header before it in the batch.
+struct pow_limits {
+    uint32_t post[8], legacy[8];
+};
+__global__ void __launch_bounds__(128) k_header_pow(const uint8_t *__restrict__ hdrs, size_t stride, size_t count,
+                                                    const uint8_t *__restrict__ hash, pow_limits lim, uint32_t fork_height,
+                                                    uint8_t *__restrict__ ok_pow, uint8_t *__restrict__ linked) {
+    const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= count) return;
+    const uint8_t *h = hdrs + i * stride;
+    auto le32 = [](const uint8_t *p) { return (uint32_t)p[0] | (uint32_t)p[1] << 8 | (uint32_t)p[2] << 16 | (uint32_t)p[3] << 24; };
+    const uint32_t height = le32(h + 68), nbits = le32(h + 104);
+    uint32_t hw[8];
+    for (int j = 0; j < 8; j++) hw[j] = le32(hash + i * 32 + 4 * j);
+    ok_pow[i] = pow_check(hw, nbits, height >= fork_height ? lim.post : lim.legacy) ? 1 : 0;
+    if (linked) {
+        bool same = true;
+        if (i > 0)
+            for (int j = 0; j < 32; j++) same = same && h[4 + j] == hash[(i - 1) * 32 + j];
+        linked[i] = same ? 1 : 0;
+    }
+}
+
 extern "C" {
 
 BCP_API size_t bcp_gpu_equihash_scratch_bytes(size_t count) { return count * 64 + 256; }
@@ -261,6 +286,53 @@ BCP_API int bcp_gpu_equihash_verify_batch(int device, unsigned n, unsigned k, co
         if (rc != BCP_OK) return rc;
         BCP_CUDA(cudaMemcpyAsync(hash32, d + o_hash, count * 32, cudaMemcpyDeviceToHost, st));
     }
+    BCP_CUDA(cudaStreamSynchronize(st));
+    return BCP_OK;
+}
+
+// Headers-first pipeline: everything CheckBlockHeader needs (src/validation.cpp:3202-3220) plus the
+// in-batch linkage, for `count` serialized post-fork headers in one pass over one upload.
+BCP_API int bcp_gpu_header_check_batch(int device, unsigned n, unsigned k, const uint8_t *hdrs, size_t stride, size_t hdr_len,
+                                       size_t count, const uint8_t pow_limit32[32], const uint8_t pow_limit_legacy32[32],
+                                       uint32_t fork_height, uint8_t *ok_solution, uint8_t *ok_pow, uint8_t *linked,
+                                       uint8_t *hash32) {
+    bcp_ctx *c = bcp_get_ctx(device);
+    if (!c) return BCP_ERR_NOT_INIT;
+    if (count == 0) return BCP_OK;
+    if (!hdrs || !ok_solution || !ok_pow || !hash32 || !pow_limit32 || !pow_limit_legacy32) {
+        bcp_set_error("bcp_gpu_header_check_batch: NULL buffer");
+        return BCP_ERR_INVALID;
+    }
+    if (hdr_len > stride || hdr_len < 140 || count * stride > 0xFFFFFFF0ull) {
+        bcp_set_error("header check: bad header length/stride/count");
+        return BCP_ERR_INVALID;
+    }
+    std::lock_guard<std::mutex> lk(c->mu);
+    BCP_CUDA(cudaSetDevice(device));
+    const size_t bytes = count * stride;
+    const size_t o_mid = (bytes + 8 + 255) / 256 * 256, o_ok = o_mid + count * 64, o_pow = o_ok + count, o_link = o_pow + count,
+                 o_hash = (o_link + count + 255) / 256 * 256, total = o_hash + count * 32 + 256;
+    int rc = bcp_ctx_reserve_stage(c, total);
+    if (rc != BCP_OK) return rc;
+    uint8_t *d = c->stage;
+    cudaStream_t st = c->stream;
+    BCP_CUDA(cudaMemcpyAsync(d, hdrs, bytes, cudaMemcpyHostToDevice, st));
+    rc = eh_dispatch(c, n, k, d, stride, hdr_len, count, reinterpret_cast<uint64_t *>(d + o_mid), d + o_ok, st);
+    if (rc != BCP_OK) return rc;
+    rc = bcp_sha256d_strided_dev(c, d, stride, hdr_len, count, d + o_hash, st);
+    if (rc != BCP_OK) return rc;
+    pow_limits lim;
+    for (int j = 0; j < 8; j++) {
+        memcpy(&lim.post[j], pow_limit32 + 4 * j, 4); // uint256 memory order is little-endian limbs on this host
+        memcpy(&lim.legacy[j], pow_limit_legacy32 + 4 * j, 4);
+    }
+    k_header_pow<<<(unsigned)((count + 127) / 128), 128, 0, st>>>(d, stride, count, d + o_hash, lim, fork_height, d + o_pow,
+                                                                 d + o_link);
+    BCP_CUDA(cudaGetLastError());
+    BCP_CUDA(cudaMemcpyAsync(ok_solution, d + o_ok, count, cudaMemcpyDeviceToHost, st));
+    BCP_CUDA(cudaMemcpyAsync(ok_pow, d + o_pow, count, cudaMemcpyDeviceToHost, st));
+    if (linked) BCP_CUDA(cudaMemcpyAsync(linked, d + o_link, count, cudaMemcpyDeviceToHost, st));
+    BCP_CUDA(cudaMemcpyAsync(hash32, d + o_hash, count * 32, cudaMemcpyDeviceToHost, st));
     BCP_CUDA(cudaStreamSynchronize(st));
     return BCP_OK;
 }

@@ -171,6 +171,22 @@ BCP_API int bcp_gpu_equihash_verify_batch_dev(int device, unsigned n, unsigned k
                                               size_t hdr_len, size_t count, uint8_t *d_ok, void *d_scratch,
                                               void *stream);
 
+/* ---- Header pipeline (headers-first sync): for `count` serialized post-fork headers, everything
+ *      CheckBlockHeader computes (src/validation.cpp:3202-3220) in one pass over one upload:
+ *   ok_solution  CheckEquihashSolution (src/pow.cpp:298-323)
+ *   ok_pow       CheckProofOfWork(GetHash(), nBits, IsBCPEnabled(nHeight)) (src/pow.cpp:141-161): target from the
+ *                compact form (arith_uint256::SetCompact, src/arith_uint256.cpp:181-199), not negative / zero /
+ *                overflowing / above the limit, hash <= target.  The limit is pow_limit32 for headers whose own
+ *                nHeight field is >= fork_height, pow_limit_legacy32 otherwise (Consensus::Params::PowLimit,
+ *                src/consensus/params.h:88); both as uint256 memory bytes (little-endian).
+ *   linked       optional: 1 for header 0, else hashPrevBlock == hash of the header before it in the batch
+ *   hash32       CBlockHeader::GetHash of each header
+ * The sequential rest (difficulty, median time past, versions) is host work: include/compat/bcp_headers.h. */
+BCP_API int bcp_gpu_header_check_batch(int device, unsigned n, unsigned k, const uint8_t *hdrs, size_t stride, size_t hdr_len,
+                                       size_t count, const uint8_t pow_limit32[32], const uint8_t pow_limit_legacy32[32],
+                                       uint32_t fork_height, uint8_t *ok_solution, uint8_t *ok_pow, uint8_t *linked,
+                                       uint8_t *hash32);
+
 /* ---- measurement helper: integer-pipe peak (SURVEY.md §8d asks the build to measure it) ----------
  * Runs a dependency-free IMAD.WIDE.U32 loop on every SM and returns 32x32->64 multiply-adds per second
  * (which == 0), the carry-chained form mad.lo.cc/madc.hi.cc used by the field code (which == 1), or

@@ -49,6 +49,7 @@ class Impl:
 
     def __init__(self, path, prefix):
         L = _Lib(path, prefix)
+        self.lib = L.lib  # the raw CDLL, for the few functions only one of the libraries has
         self.kind = "port" if prefix == "orc_" else "reference"
         sz, i, u32, i64 = C.c_size_t, C.c_int, C.c_uint32, C.c_int64
         self._sha256 = L.fn("sha256", None, u8p, sz, u8p)

@@ -36,6 +36,7 @@
 #include "pubkey.h"
 #include "hash.h"
 #include "uint256.h"
+#include "arith_uint256.h"
 #include "streams.h"
 #include "version.h"
 #include "crypto/sha256.h"
@@ -368,6 +369,121 @@ long ref_block_verify_inputs(const uint8_t *blk, size_t len, int legacy, const u
     } catch (...) {
         return -1;
     }
+}
+
+// ---- proof-of-work arithmetic (row N4).  src/pow.cpp itself does not compile outside the node (it includes
+// util.h / validation.h, i.e. Boost), so its control flow is RESTATED here — but every 256-bit operation is the
+// reference's own arith_uint256 (src/arith_uint256.cpp, compiled in place), which is what pins the product's U256.
+struct ref_pow_params {
+    uint8_t pow_limit[32], pow_limit_legacy[32], pow_limit_start[32];
+    int32_t allow_min_difficulty, no_retargeting;
+    int64_t target_spacing, target_timespan_legacy;
+    int32_t bcp_height, premine_window;
+    int64_t averaging_window;
+    int32_t bip34_height, bip65_height, bip66_height;
+    uint32_t eh_n, eh_k;
+};
+static arith_uint256 from_le(const uint8_t *b) {
+    uint256 u;
+    memcpy(u.begin(), b, 32);
+    return UintToArith256(u);
+}
+static void to_le(const arith_uint256 &a, uint8_t *out) {
+    uint256 u = ArithToUint256(a);
+    memcpy(out, u.begin(), 32);
+}
+void ref_compact_to_target(uint32_t compact, uint8_t *out32, int *negative, int *overflow) {
+    bool n, o;
+    arith_uint256 t;
+    t.SetCompact(compact, &n, &o);
+    to_le(t, out32);
+    *negative = n;
+    *overflow = o;
+}
+uint32_t ref_compact_from_target(const uint8_t *t32) { return from_le(t32).GetCompact(); }
+// GetBlockProof (src/chain.cpp:132-145)
+static arith_uint256 block_proof(uint32_t nBits) {
+    arith_uint256 t;
+    bool n, o;
+    t.SetCompact(nBits, &n, &o);
+    if (n || o || t == 0) return 0;
+    return (~t / (t + 1)) + 1;
+}
+void ref_block_proof(uint32_t nbits, uint8_t *out32) { to_le(block_proof(nbits), out32); }
+// CheckProofOfWork (src/pow.cpp:141-161)
+int ref_check_pow(const uint8_t *hash32, uint32_t nBits, const uint8_t *limit32) {
+    bool fNegative, fOverflow;
+    arith_uint256 bnTarget;
+    bnTarget.SetCompact(nBits, &fNegative, &fOverflow);
+    if (fNegative || bnTarget == 0 || fOverflow || bnTarget > from_le(limit32)) return 0;
+    if (from_le(hash32) > bnTarget) return 0;
+    return 1;
+}
+// GetNextWorkRequired(pindexPrev = block n-1 of the given chain, pblock->nTime = new_time) (src/pow.cpp:72-105) with
+// BitcoinGetNextWorkRequired (:27-67), CalculateNextWorkRequired (:110-134), GetNextCashPlusWorkRequired (:252-295).
+// which: 0 = GetNextWorkRequired, 1 = CalculateNextWorkRequired(prev, first_time = new_time), 2 = GetNextCashPlusWorkRequired
+uint32_t ref_next_work(const ref_pow_params *p, const uint32_t *times, const uint32_t *bits, size_t n, int64_t new_time, int which) {
+    const arith_uint256 limPost = from_le(p->pow_limit), limLegacy = from_le(p->pow_limit_legacy);
+    auto limit = [&](bool postfork) { return postfork ? limPost : limLegacy; };
+    if (n == 0) return limLegacy.GetCompact();
+    const int prev = (int)n - 1;
+    auto calc = [&](int64_t nFirstBlockTime) -> uint32_t {
+        if (p->no_retargeting) return bits[prev];
+        int64_t nActualTimespan = (int64_t)times[prev] - nFirstBlockTime;
+        if (nActualTimespan < p->target_timespan_legacy / 4) nActualTimespan = p->target_timespan_legacy / 4;
+        if (nActualTimespan > p->target_timespan_legacy * 4) nActualTimespan = p->target_timespan_legacy * 4;
+        arith_uint256 bnNew;
+        bnNew.SetCompact(bits[prev]);
+        bnNew *= nActualTimespan;
+        bnNew /= p->target_timespan_legacy;
+        if (bnNew > limLegacy) bnNew = limLegacy;
+        return bnNew.GetCompact();
+    };
+    auto cashplus = [&]() -> uint32_t {
+        const bool postfork = prev >= p->bcp_height;
+        if (p->allow_min_difficulty && new_time > (int64_t)times[prev] + 2 * p->target_spacing) return limit(postfork).GetCompact();
+        std::vector<arith_uint256> work(n);
+        for (size_t i = 0; i < n; i++) work[i] = (i ? work[i - 1] : arith_uint256(0)) + block_proof(bits[i]);
+        auto suitable = [&](int h) {
+            int b[3] = {h - 2, h - 1, h};
+            if (times[b[0]] > times[b[2]]) std::swap(b[0], b[2]);
+            if (times[b[0]] > times[b[1]]) std::swap(b[0], b[1]);
+            if (times[b[1]] > times[b[2]]) std::swap(b[1], b[2]);
+            return b[1];
+        };
+        const int last = suitable(prev), first = suitable(prev - 144);
+        arith_uint256 w = work[last] - work[first];
+        w *= p->target_spacing;
+        int64_t nActualTimespan = int64_t(times[last]) - int64_t(times[first]);
+        if (nActualTimespan > 288 * p->target_spacing) nActualTimespan = 288 * p->target_spacing;
+        else if (nActualTimespan < 72 * p->target_spacing) nActualTimespan = 72 * p->target_spacing;
+        w /= nActualTimespan;
+        const arith_uint256 nextTarget = (-w) / w;
+        if (nextTarget > limit(postfork)) return limit(postfork).GetCompact();
+        return nextTarget.GetCompact();
+    };
+    if (which == 1) return calc(new_time);
+    if (which == 2) return cashplus();
+    if (p->no_retargeting) return bits[prev];
+    const int nHeight = prev + 1;
+    const bool postfork = nHeight >= p->bcp_height;
+    if (!postfork) {
+        const uint32_t nProofOfWorkLimit = limLegacy.GetCompact();
+        const int64_t interval = p->target_timespan_legacy / p->target_spacing;
+        if ((prev + 1) % interval != 0) {
+            if (p->allow_min_difficulty) {
+                if (new_time > (int64_t)times[prev] + p->target_spacing * 2) return nProofOfWorkLimit;
+                int i = prev;
+                while (i > 0 && i % interval != 0 && bits[i] == nProofOfWorkLimit) i--;
+                return bits[i];
+            }
+            return bits[prev];
+        }
+        return calc((int64_t)times[prev - (interval - 1)]);
+    }
+    if (nHeight < p->bcp_height + p->premine_window) return limPost.GetCompact();
+    if (nHeight < p->bcp_height + p->premine_window + p->averaging_window) return from_le(p->pow_limit_start).GetCompact();
+    return cashplus();
 }
 
 }  // extern "C"

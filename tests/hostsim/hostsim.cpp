@@ -13,6 +13,7 @@
 #include "../../bitcoincashplus_b200/csrc/blake2b.cuh"
 #include "../../bitcoincashplus_b200/csrc/ripemd160.cuh"
 #include "../../bitcoincashplus_b200/csrc/script.cuh"
+#include "../../bitcoincashplus_b200/csrc/pow.cuh"
 
 static void fe_from_be(fe &r, const uint8_t *b) { fe_set_b32(r, b); }
 static void fe_to_be(uint8_t *b, fe a) {
@@ -218,6 +219,18 @@ void hs_block_p2pkh_extract(const uint8_t *blk, const uint32_t *tx_off, size_t n
                                                spk + spk_off[i], spk_off[i + 1] - spk_off[i], amounts[i],
                                                &mid[t * BCP_TXMID_BYTES], msg32 + 32 * i, pub65 + 65 * i, sig64 + 64 * i);
     }
+}
+// pow.cuh: CheckProofOfWork on the device limbs; hash / limit as uint256 memory bytes
+int hs_pow_check(const uint8_t *hash32, uint32_t nbits, const uint8_t *limit32, uint8_t *target32, int *neg, int *ovf) {
+    uint32_t h[8], l[8], t[8];
+    memcpy(h, hash32, 32);
+    memcpy(l, limit32, 32);
+    bool n, o;
+    pow_set_compact(nbits, t, n, o);
+    memcpy(target32, t, 32);
+    *neg = n;
+    *ovf = o;
+    return pow_check(h, nbits, l) ? 1 : 0;
 }
 void hs_blake2b_final_block(const uint64_t *h_mid, const uint8_t *blk128, uint64_t t0, uint64_t *h_out) {
     uint64_t h[8], m[16];

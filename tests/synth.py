@@ -477,3 +477,27 @@ def chain_seeds(ntx, nkeys):
     spks = [p2pkh_script(o.pubkey_create(seckey(5000 + j), True)) for j in range(nkeys)]
     t, k, a = chain_seed_arrays(ntx, nkeys)
     return [(t[j].tobytes(), 0, spks[int(k[j])], int(a[j])) for j in range(ntx)]
+
+
+# ------------------------------------------------------------------ header chains (row N4)
+def make_header(version, prev_hash, merkle_root, height, time, bits, nonce_tag, want_pow=None, limit=(1 << 255) - 1,
+                corrupt_solution=False):
+    """One serialized post-fork header with a VALID Equihash (48,5) solution; the nonce is ground until
+    CheckProofOfWork(hash, bits) has the wanted outcome (None: any).  Returns (header bytes, hash)."""
+    from oracle import pow_oracle as PO
+
+    for attempt in range(4000):
+        nonce = hashlib.sha256(SEED + b"hn" + nonce_tag.to_bytes(8, "little") + attempt.to_bytes(4, "little")).digest()
+        h140 = (version & 0xFFFFFFFF).to_bytes(4, "little") + prev_hash + merkle_root + height.to_bytes(4, "little") + bytes(28) \
+            + time.to_bytes(4, "little") + bits.to_bytes(4, "little") + nonce
+        for sol in equihash_solve_48_5(h140):
+            hdr = h140 + _compact(len(sol)) + sol
+            hh = hashlib.sha256(hashlib.sha256(hdr).digest()).digest()
+            if want_pow is None or PO.check_pow(hh, bits, limit) == want_pow:
+                if corrupt_solution:
+                    b = bytearray(hdr)
+                    b[150] ^= 0x10
+                    hdr = bytes(b)
+                    hh = hashlib.sha256(hashlib.sha256(hdr).digest()).digest()
+                return hdr, hh
+    raise RuntimeError("no nonce found")

@@ -20,14 +20,18 @@ P = 2**256 - 2**32 - 977
 N = 0xFFFFFFFFFFFFFFFFFFFFFFFFFFFFFFFEBAAEDCE6AF48A03BBFD25E8CD0364141
 
 
-@pytest.fixture(scope="module")
-def hs():
+def build_hostsim():
     so = os.path.join(HS, "libhostsim.so")
     src = os.path.join(HS, "hostsim.cpp")
     hdrs = [os.path.join(ROOT, "bitcoincashplus_b200", "csrc", f) for f in os.listdir(os.path.join(ROOT, "bitcoincashplus_b200", "csrc")) if f.endswith(".cuh")]
     if not os.path.exists(so) or os.path.getmtime(so) < max(os.path.getmtime(p) for p in hdrs + [src]):
         subprocess.check_call(["g++", "-O2", "-std=c++17", "-DBCP_GCOMB_BITS=12", "-fPIC", "-shared", "-o", so, src, "-lpthread"])
     return C.CDLL(so)
+
+
+@pytest.fixture(scope="module")
+def hs():
+    return build_hostsim()
 
 
 @pytest.fixture(scope="module")
