@@ -42,62 +42,83 @@ struct OutPointHash {
         return (size_t)(h ^ (0x9E3779B97F4A7C15ull * v));
     }
 };
-// Open-addressing UTXO table (linear probing, tombstones), coins stored inline: scriptPubKeys up to 40 bytes live in
-// the slot (P2PKH is 25), longer ones in a side vector.  One table serves lookups, in-block creations and spends;
-// a per-block journal undoes everything when the block is rejected, so no second map is needed.
-struct CoinSlot {
-    OutPoint key;
-    int64_t amount;
+// Open-addressing UTXO table: linear probing, deletion by backward shift (no tombstones, so the table never needs
+// a clean-up rehash and probe sequences stay short however many blocks have been connected), coins stored inline in
+// 128-byte slots = two adjacent cache lines that prefetch() pulls in together.  scriptPubKeys up to 64 bytes live
+// in the slot (P2PKH is 25), longer ones in a side vector.  One table serves lookups, in-block creations and
+// spends; a per-block journal undoes everything when the block is rejected, so no second map is needed.
+struct alignas(128) CoinSlot {
+    // first cache line: everything a probe looks at
+    uint8_t state;      // 0 empty, 1 live
+    uint8_t pad[3];
     uint32_t spk_len;
-    uint8_t state; // 0 empty, 1 live, 2 tombstone
-    uint8_t spk[40];
-    std::vector<uint8_t> *big; // only for scripts longer than 40 bytes
+    OutPoint key;       // bytes 8..43
+    uint32_t pad2;
+    int64_t amount;     // 48
+    std::vector<uint8_t> *big; // 56; only for scripts longer than the inline space
+    // second cache line
+    uint8_t spk[64];
 };
+static_assert(sizeof(CoinSlot) == 128, "CoinSlot is two cache lines");
 class CoinTable {
 public:
-    explicit CoinTable(size_t cap_pow2 = 1 << 16) : slots(cap_pow2), mask(cap_pow2 - 1) {
+    explicit CoinTable(size_t cap_pow2 = 1 << 17) : slots(cap_pow2), mask(cap_pow2 - 1) {
         for (auto &s : slots) { s.state = 0; s.big = nullptr; }
     }
     ~CoinTable() { for (auto &s : slots) delete s.big; }
+    CoinTable(const CoinTable &) = delete;
+    CoinTable &operator=(const CoinTable &) = delete;
     size_t size() const { return live; }
     // the table is far larger than the CPU caches and every probe is a random access: callers hint the slots of the
     // next few outpoints while they work on the current one
-    void prefetch(const OutPoint &k) const { __builtin_prefetch(&slots[OutPointHash()(k) & mask]); }
+    void prefetch(const OutPoint &k) const {
+        const char *p = reinterpret_cast<const char *>(&slots[OutPointHash()(k) & mask]);
+        __builtin_prefetch(p);
+        __builtin_prefetch(p + 64);
+        __builtin_prefetch(p + 128); // probe line of the next slot: erase() and colliding inserts look at it
+    }
     CoinSlot *find(const OutPoint &k) {
         size_t i = OutPointHash()(k) & mask;
         for (;;) {
             CoinSlot &s = slots[i];
             if (s.state == 0) return nullptr;
-            if (s.state == 1 && s.key == k) return &s;
+            if (s.key == k) return &s;
             i = (i + 1) & mask;
         }
     }
     CoinSlot *insert(const OutPoint &k, const uint8_t *spk, size_t len, int64_t amount) {
-        if ((used + 1) * 10 > slots.size() * 7) grow();
+        if ((live + 1) * 2 > slots.size()) grow();
         size_t i = OutPointHash()(k) & mask;
-        CoinSlot *tomb = nullptr;
         for (;;) {
             CoinSlot &s = slots[i];
             if (s.state == 0) break;
-            if (s.state == 1 && s.key == k) { fill(s, spk, len, amount); return &s; } // overwrite (BIP30-style duplicates)
-            if (s.state == 2 && !tomb) tomb = &s;
+            if (s.key == k) { fill(s, spk, len, amount); return &s; } // overwrite (BIP30-style duplicates)
             i = (i + 1) & mask;
         }
-        CoinSlot &d = tomb ? *tomb : slots[i];
-        if (!tomb) used++;
+        CoinSlot &d = slots[i];
         d.key = k;
         d.state = 1;
+        d.big = nullptr;
         fill(d, spk, len, amount);
         live++;
         return &d;
     }
+    // Removes the coin and closes the gap: every following entry of the probe run moves back one hole if its home
+    // position allows it, so find() can keep stopping at the first empty slot.  Invalidates CoinSlot pointers.
     void erase(CoinSlot *s) {
-        s->state = 2;
+        delete s->big;
+        size_t i = (size_t)(s - slots.data()), j = i;
+        for (;;) {
+            j = (j + 1) & mask;
+            if (slots[j].state == 0) break;
+            const size_t h = OutPointHash()(slots[j].key) & mask;
+            if (i <= j ? (i < h && h <= j) : (i < h || h <= j)) continue; // home lies after the hole: must stay
+            slots[i] = slots[j];
+            i = j;
+        }
+        slots[i].state = 0;
+        slots[i].big = nullptr;
         live--;
-    }
-    void revive(CoinSlot *s) { // undo of erase
-        s->state = 1;
-        live++;
     }
     static const uint8_t *script(const CoinSlot &s) { return s.big ? s.big->data() : s.spk; }
 
@@ -120,20 +141,17 @@ private:
         slots.resize(old.size() * 2);
         mask = slots.size() - 1;
         for (auto &s : slots) { s.state = 0; s.big = nullptr; }
-        used = live = 0;
+        live = 0;
         for (auto &o : old)
             if (o.state == 1) {
                 CoinSlot *n = insert(o.key, script(o), o.spk_len, o.amount);
                 (void)n;
                 delete o.big;
                 o.big = nullptr;
-            } else {
-                delete o.big;
-                o.big = nullptr;
             }
     }
     std::vector<CoinSlot> slots;
-    size_t mask, used = 0, live = 0;
+    size_t mask, live = 0;
 };
 
 class ChainValidator {
@@ -192,75 +210,90 @@ public:
         if (nin < 0 || ntx < 1) { reason = "bad-blk-framing"; return false; }
         auto t2 = now();
         phase[1] += secs(t1, t2);
-        // txids + Merkle root (CheckBlock, src/validation.cpp:3236-3252)
+        // txids + Merkle root (CheckBlock, src/validation.cpp:3236-3252) on the device, from a helper thread, while
+        // this thread looks up the spent coins: the lookups need the previous outputs, not this block's txids
         txids.resize((size_t)ntx * 32);
         uint8_t root[32];
-        int mutated = 0;
-        if (bcp_gpu_sha256d_txids_merkle(dev0, blk, len, tx_off.data(), (size_t)ntx, txids.data(), root, &mutated) != BCP_OK) {
-            reason = std::string("device-error: ") + bcp_gpu_last_error();
-            return false;
-        }
-        if (memcmp(root, blk + 36, 32) != 0) { reason = "bad-txnmrklroot"; return false; }
-        if (mutated) { reason = "bad-txns-duplicate"; return false; }
-        auto t3 = now();
-        phase[2] += secs(t2, t3);
-        // spent coins, transaction by transaction, seeing outputs created earlier in this block; everything is applied
-        // to the one table and journalled so that a rejected block can be rolled back
+        int mutated = 0, rcTx = BCP_OK;
+        std::string errTx;
+        std::thread thTx([&] {
+            rcTx = bcp_gpu_sha256d_txids_merkle(dev0, blk, len, tx_off.data(), (size_t)ntx, txids.data(), root, &mutated);
+            if (rcTx != BCP_OK) errTx = bcp_gpu_last_error();
+        });
+        // Spent coins.  Everything is applied to the one table and journalled so that a rejected block can be rolled
+        // back.  Pass A takes the inputs in block order for as long as they are found in the table as it was before
+        // this block (the normal case: all of them); the first miss — an output created earlier in this block, or a
+        // missing coin — ends it at input `m`.
         spk_cat.clear();
         spk_off.assign(1, 0);
         amounts.clear();
         journalSpent.clear();
         journalCreated.clear();
-        size_t i = 0;
         const size_t AHEAD = 16;
-        for (long t = 0; t < ntx; t++) {
+        size_t m = 0;
+        for (; m < (size_t)nin; m++) {
+            if (m + AHEAD < (size_t)nin) {
+                OutPoint nx;
+                memcpy(nx.b, blk + in_off[m + AHEAD], 36);
+                utxo.prefetch(nx);
+            }
+            if (!Spend(blk + in_off[m])) break;
+        }
+        auto t3 = now();
+        thTx.join();
+        auto t3b = now();
+        phase[3] += secs(t2, t3);
+        phase[2] += secs(t3, t3b); // what the lookups did not hide
+        if (rcTx != BCP_OK) { Rollback(); reason = "device-error: " + errTx; return false; }
+        if (memcmp(root, blk + 36, 32) != 0) { Rollback(); reason = "bad-txnmrklroot"; return false; }
+        if (mutated) { Rollback(); reason = "bad-txns-duplicate"; return false; }
+        // Script checks, sharded by input index range over the devices.  When pass A resolved every input they start
+        // now, from helper threads, and run while this thread inserts the block's outputs (pass B).
+        errs.assign((size_t)nin, 0);
+        const size_t G = devs.size(), per = ((size_t)nin + G - 1) / G;
+        std::vector<int> rc(G, BCP_OK);
+        std::vector<std::string> msg(G);
+        std::vector<std::thread> th;
+        auto launchScripts = [&] {
+            for (size_t g = 0; g < G && nin > 0; g++) {
+                const size_t lo = std::min((size_t)nin, g * per), hi = std::min((size_t)nin, lo + per);
+                if (lo >= hi) continue;
+                th.emplace_back([&, g, lo, hi] {
+                    int all = 0;
+                    rc[g] = bcp_gpu_block_scripts_p2pkh(devs[g], blk, len, tx_off.data(), (size_t)ntx, &in_off[lo], &in_tx[lo],
+                                                        &in_n[lo], hi - lo, spk_cat.data(), &spk_off[lo], &amounts[lo], flags,
+                                                        &errs[lo], &all);
+                    if (rc[g] != BCP_OK) msg[g] = bcp_gpu_last_error();
+                });
+            }
+        };
+        const bool overlapped = m == (size_t)nin;
+        if (overlapped) launchScripts();
+        // Pass B, transaction by transaction: the inputs pass A did not reach (they may spend outputs created earlier in
+        // this block, and only those), then the transaction's own outputs.
+        size_t i = m;
+        bool missing = false;
+        for (long t = 0; t < ntx && !missing; t++) {
             if ((size_t)t + AHEAD < (size_t)ntx) { // where transaction t+AHEAD's first output will land
                 OutPoint nx;
                 memcpy(nx.b, &txids[((size_t)t + AHEAD) * 32], 32);
                 memset(nx.b + 32, 0, 4);
                 utxo.prefetch(nx);
             }
-            for (; i < (size_t)nin && in_tx[i] == (uint32_t)t; i++) {
-                if (i + AHEAD < (size_t)nin) {
-                    OutPoint nx;
-                    memcpy(nx.b, blk + in_off[i + AHEAD], 36);
-                    utxo.prefetch(nx);
-                }
-                OutPoint op;
-                memcpy(op.b, blk + in_off[i], 36);
-                CoinSlot *c = utxo.find(op); // a coin spent earlier in this block (or this tx) is already a tombstone
-                if (!c) { Rollback(); reason = "bad-txns-inputs-missingorspent"; return false; }
-                const uint8_t *sp = CoinTable::script(*c);
-                spk_cat.insert(spk_cat.end(), sp, sp + c->spk_len);
-                spk_off.push_back((uint32_t)spk_cat.size());
-                amounts.push_back(c->amount);
-                utxo.erase(c);
-                journalSpent.push_back(op);
-            }
-            AddOutputs(blk, (uint32_t)t);
+            for (; i < (size_t)nin && in_tx[i] == (uint32_t)t; i++)
+                if (!Spend(blk + in_off[i])) { missing = true; break; }
+            if (!missing) AddOutputs(blk, (uint32_t)t);
         }
         auto t4 = now();
-        phase[3] += secs(t3, t4);
-        // script checks, sharded by input index range over the devices
-        errs.assign((size_t)nin, 0);
-        const size_t G = devs.size(), per = ((size_t)nin + G - 1) / G;
-        std::vector<int> rc(G, BCP_OK);
-        std::vector<std::string> msg(G);
-        std::vector<std::thread> th;
-        for (size_t g = 0; g < G && nin > 0; g++) {
-            const size_t lo = std::min((size_t)nin, g * per), hi = std::min((size_t)nin, lo + per);
-            if (lo >= hi) continue;
-            auto work = [&, g, lo, hi] {
-                int all = 0;
-                rc[g] = bcp_gpu_block_scripts_p2pkh(devs[g], blk, len, tx_off.data(), (size_t)ntx, &in_off[lo], &in_tx[lo], &in_n[lo],
-                                                    hi - lo, spk_cat.data(), &spk_off[lo], &amounts[lo], flags, &errs[lo], &all);
-                if (rc[g] != BCP_OK) msg[g] = bcp_gpu_last_error();
-            };
-            if (G == 1) work();
-            else th.emplace_back(work);
+        phase[3] += secs(t3b, t4);
+        if (missing) { // only reachable when the scripts were not started
+            Rollback();
+            reason = "bad-txns-inputs-missingorspent";
+            return false;
         }
+        if (!overlapped) launchScripts();
         for (auto &t : th) t.join();
-        phase[4] += secs(t4, now());
+        phase[4] += secs(t4, now()); // what pass B did not hide (everything when the passes could not overlap)
         for (size_t g = 0; g < G; g++)
             if (rc[g] != BCP_OK) { Rollback(); reason = "device-error: " + msg[g]; return false; }
         for (size_t k = 0; k < (size_t)nin; k++) {
@@ -299,6 +332,21 @@ public:
     }
 
 private:
+    // Looks up the coin an input spends, appends its scriptPubKey / amount to the staging arrays of the script checks,
+    // removes it from the table and journals it.  false: no such coin (already spent, or never there).
+    bool Spend(const uint8_t *outpoint36) {
+        OutPoint op;
+        memcpy(op.b, outpoint36, 36);
+        CoinSlot *c = utxo.find(op);
+        if (!c) return false;
+        const uint8_t *sp = CoinTable::script(*c);
+        spk_cat.insert(spk_cat.end(), sp, sp + c->spk_len);
+        spk_off.push_back((uint32_t)spk_cat.size());
+        amounts.push_back(c->amount);
+        utxo.erase(c);
+        journalSpent.push_back(op);
+        return true;
+    }
     void AddOutputs(const uint8_t *blk, uint32_t t) {
         // skip inputs to reach the outputs of transaction t
         size_t pos = tx_off[t] + 4;
