@@ -167,6 +167,40 @@ def block_bench(eng, args, bcp, sync=None):
     return out
 
 
+def window_bench(eng, args, bcp, W=8):
+    """Throughput form of the 8 MB block measurement (reindex / initial block download, blocks at hand): W blocks per call
+    through bcp_gpu_blocks_connect_p2pkh — one pass of the per-input kernels over the union of the window's inputs.
+    The W blocks are the same synthetic block in W separate pinned buffers (run time does not depend on the content)."""
+    import numpy as np
+    import synth
+
+    blk, spk, amt = synth.synthetic_block(args.block_txs, True, with_prevouts=True)
+    L = bcp.lib()
+
+    def pinned(a):
+        p = L.bcp_gpu_host_alloc(max(a.nbytes, 1))
+        out = np.ctypeslib.as_array(C.cast(p, C.POINTER(C.c_uint8)), shape=(max(a.nbytes, 1),))[: a.nbytes].view(a.dtype)
+        out[...] = a
+        return out
+
+    n = len(spk)
+    lens = np.array([len(x) for x in spk] * W, dtype=np.uint64)
+    off0 = np.zeros(n * W + 1, dtype=np.uint32)
+    off0[1:] = np.cumsum(lens)
+    blks = [pinned(np.frombuffer(blk, dtype=np.uint8)) for _ in range(W)]
+    cat, off, am = pinned(np.frombuffer(b"".join(spk) * W, dtype=np.uint8)), pinned(off0), pinned(np.asarray(list(amt) * W, dtype=np.int64))
+    res = eng.blocks_connect_p2pkh(blks, cat, off, am, [n] * W, synth.POSTFORK_FLAGS)
+    assert all(res["all_ok"]) and all(bytes(r) == blk[36:68] for r in res["roots"]) and not any(res["mutated"])
+    reps = 5
+    t0 = time.perf_counter()
+    for _ in range(reps):
+        eng.blocks_connect_p2pkh(blks, cat, off, am, [n] * W, synth.POSTFORK_FLAGS)
+    s = (time.perf_counter() - t0) / reps
+    return {"window_blocks": W, "inputs_per_block": n, "gpu_ms_per_window": s * 1e3, "gpu_ms_per_block": s * 1e3 / W,
+            "gpu_blocks_per_s": W / s, "gpu_inputs_per_s": W * n / s,
+            "timed": "bcp_gpu_blocks_connect_p2pkh end to end (host framing scans on W threads + H2D + kernels + D2H), pinned host buffers"}
+
+
 def equihash_bench(eng):
     """Secondary measurement (BASELINE.json configs[3]): Equihash (200,9) verification + SHA-256d header hashing over
     10,000 serialized headers (the committed solver-found solutions tiled, half of them corrupted), through the
@@ -471,6 +505,7 @@ def main():
         line["cpu_baseline"] = cpu_baseline(msg, pub, sig)
     if not args.no_block:
         line["block8mb"] = blk_section
+        line["block8mb_window"] = window_bench(eng, args, bcp)
         line["equihash10k"] = equihash_bench(eng)
         if args.chain_blocks > 0:
             line["chain"] = chain_bench(args, list(range(world)))

@@ -50,6 +50,7 @@ SIGNATURES = {
     "bcp_gpu_block_connect_p2pkh": (C.c_int, [C.c_int, vp, sz, C.c_int, vp, vp, vp, sz, C.c_uint32, vp, vp, C.POINTER(C.c_int),
                                               vp, C.POINTER(C.c_int)]),
     "bcp_gpu_equihash_verify_batch": (C.c_int, [C.c_int, C.c_uint, C.c_uint, vp, sz, sz, sz, vp, vp]),
+    "bcp_gpu_blocks_connect_p2pkh": (C.c_int, [C.c_int, sz, vp, vp, C.c_int, vp, vp, vp, vp, C.c_uint32, vp, vp, vp, vp, vp, vp]),
     "bcp_gpu_equihash_scratch_bytes": (sz, [sz]),
     "bcp_gpu_header_check_batch": (C.c_int, [C.c_int, C.c_uint, C.c_uint, vp, sz, sz, sz, vp, vp, C.c_uint32, vp, vp, vp, vp]),
     "bcp_gpu_equihash_verify_batch_dev": (C.c_int, [C.c_int, C.c_uint, C.c_uint, vp, sz, sz, sz, vp, vp, vp]),

@@ -137,6 +137,31 @@ class Engine:
                                                 err.ctypes.data if n else None, C.byref(allok)), "bcp_gpu_block_connect_p2pkh")
         return {"txids": txids, "root": bytes(root), "mutated": bool(mut.value), "script_err": err, "all_ok": bool(allok.value)}
 
+    def blocks_connect_p2pkh(self, blks, spk_cat, spk_off, amounts, n_inputs, flags, legacy_header=False, want_txids=False):
+        """A window of blocks in one pass.  blks: list of uint8 arrays (pinned for overlap); spk_cat / spk_off / amounts:
+        the concatenation over all blocks' inputs; n_inputs: per block.  Returns dict(roots (nblk,32), mutated, all_ok,
+        script_err (total inputs,), ntx, txids)."""
+        nb = len(blks)
+        arrs = [b if isinstance(b, np.ndarray) else np.frombuffer(bytes(b), dtype=np.uint8) for b in blks]
+        ptrs = (C.c_void_p * nb)(*[a.ctypes.data for a in arrs])
+        lens = (C.c_size_t * nb)(*[a.size for a in arrs])
+        nin = (C.c_size_t * nb)(*[int(x) for x in n_inputs])
+        total = int(sum(n_inputs))
+        cat, off, am = _np(spk_cat), np.ascontiguousarray(spk_off, dtype=np.uint32), np.ascontiguousarray(amounts, dtype=np.int64)
+        assert off.size == total + 1 and am.size == total
+        err = np.full(total, 253, dtype=np.uint8)
+        roots = np.zeros((nb, 32), dtype=np.uint8)
+        mut, allok = (C.c_int * nb)(), (C.c_int * nb)()
+        ntx = (C.c_size_t * nb)()
+        txids = np.zeros((sum(a.size // 60 + 2 for a in arrs), 32), dtype=np.uint8) if want_txids else None
+        check(lib().bcp_gpu_blocks_connect_p2pkh(self.device, nb, ptrs, lens, int(legacy_header), cat.ctypes.data if total else None,
+                                                 off.ctypes.data, am.ctypes.data if total else None, nin, flags,
+                                                 txids.ctypes.data if want_txids else None, ntx, roots.ctypes.data, mut,
+                                                 err.ctypes.data if total else None, allok), "bcp_gpu_blocks_connect_p2pkh")
+        ntx = [int(x) for x in ntx]
+        return {"roots": roots, "mutated": [bool(x) for x in mut], "all_ok": [bool(x) for x in allok], "script_err": err,
+                "ntx": ntx, "txids": txids[:sum(ntx)] if want_txids else None}
+
     # ---- Equihash
     def equihash_verify_batch(self, n, k, hdrs, want_hash=True):
         """hdrs: (count, hdr_len) uint8 serialized post-fork headers -> (ok (count,), hash (count,32))."""

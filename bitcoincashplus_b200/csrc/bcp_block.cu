@@ -13,7 +13,9 @@
 //   k_script_finish  status + verdict -> ScriptError per input
 #include "bcp_ctx.cuh"
 #include "script.cuh"
+#include <algorithm>
 #include <cstring>
+#include <thread>
 #include <vector>
 
 __global__ void __launch_bounds__(128) k_tx_midstate(const uint8_t *__restrict__ blk, const uint32_t *__restrict__ tx_off,
@@ -336,6 +338,195 @@ BCP_API int bcp_gpu_block_connect_p2pkh(int device, const uint8_t *blk, size_t l
     memcpy(&a, res + 36, 4);
     if (mutated) *mutated = m ? 1 : 0;
     if (all_ok) *all_ok = a ? 1 : 0;
+    return BCP_OK;
+}
+
+// A window of blocks in one pass (reindex / initial block download, where the next blocks are already at hand).
+// Only the transaction bytes of each block go to the device, laid back to back with no gap, so that ONE offsets
+// array describes every transaction of the window and the per-transaction and per-input kernels (txids, sighash
+// midstates, template match + sighash, ECDSA prep + point, verdict) each run once over the union; only the Merkle
+// reduction is per block, on the second stream, next to the ECDSA kernels.  A single 8 MB block fills barely half
+// of one wave of the point kernel; a window fills several.
+static long first_tx_offset(const uint8_t *blk, size_t len, int legacy_header) {
+    size_t pos;
+    uint64_t v;
+    if (legacy_header) {
+        pos = 80;
+    } else {
+        pos = 140;
+        if (len < 140 || !rd_compact_h(blk, len, &pos, &v)) return -1;
+        pos += v;
+    }
+    if (pos > len || !rd_compact_h(blk, len, &pos, &v)) return -1;
+    return pos <= len ? (long)pos : -1;
+}
+
+BCP_API int bcp_gpu_blocks_connect_p2pkh(int device, size_t nblk, const uint8_t *const *blks, const size_t *lens,
+                                         int legacy_header, const uint8_t *spk, const uint32_t *spk_off,
+                                         const int64_t *amounts, const size_t *n_inputs, uint32_t flags, uint8_t *txids,
+                                         size_t *ntx_out, uint8_t *roots32, int *mutated, uint8_t *script_err, int *all_ok) {
+    bcp_ctx *c = bcp_get_ctx(device);
+    if (!c) return BCP_ERR_NOT_INIT;
+    if (nblk == 0) return BCP_OK;
+    if (!blks || !lens || !n_inputs || !roots32) { bcp_set_error("bcp_gpu_blocks_connect_p2pkh: NULL buffer"); return BCP_ERR_INVALID; }
+    if ((flags & BCP_FLAGS_POSTFORK_REQUIRED) != BCP_FLAGS_POSTFORK_REQUIRED || (flags & BCP_FLAG_ALLOW_NON_FORKID)) {
+        bcp_set_error("bcp_gpu_blocks_connect_p2pkh: the fast path implements the post-fork script flags "
+                      "(STRICTENC|DERSIG|LOW_S|NULLFAIL|SIGHASH_FORKID, no ALLOW_NON_FORKID); got 0x%x", flags);
+        return BCP_ERR_INVALID;
+    }
+    auto up = [](size_t x) { return (x + 255) / 256 * 256; };
+    // body[b] = where block b's transactions start in its host buffer; base[b] = where they start in the device buffer
+    std::vector<size_t> body(nblk), base(nblk + 1, 0), in_base(nblk + 1, 0);
+    size_t max_tx_all = 0, max_tx_one = 0;
+    for (size_t b = 0; b < nblk; b++) {
+        if (!blks[b]) { bcp_set_error("bcp_gpu_blocks_connect_p2pkh: NULL block"); return BCP_ERR_INVALID; }
+        const long f = first_tx_offset(blks[b], lens[b], legacy_header);
+        if (f < 0) { bcp_set_error("bcp_gpu_blocks_connect_p2pkh: block %zu is malformed", b); return BCP_ERR_INVALID; }
+        body[b] = (size_t)f;
+        base[b + 1] = base[b] + (lens[b] - body[b]);
+        in_base[b + 1] = in_base[b] + n_inputs[b];
+        if (n_inputs[b] > lens[b] / 41 + 2) { bcp_set_error("bcp_gpu_blocks_connect_p2pkh: more inputs than block %zu can hold", b); return BCP_ERR_INVALID; }
+        max_tx_all += lens[b] / 60 + 2;
+        max_tx_one = std::max(max_tx_one, lens[b] / 60 + 2);
+    }
+    const size_t total_in = in_base[nblk];
+    if (base[nblk] > 0xFFFFFFF0ull) { bcp_set_error("bcp_gpu_blocks_connect_p2pkh: window larger than 4 GiB"); return BCP_ERR_INVALID; }
+    if (total_in && (!spk || !spk_off || !amounts || !script_err)) { bcp_set_error("bcp_gpu_blocks_connect_p2pkh: NULL buffer"); return BCP_ERR_INVALID; }
+    std::lock_guard<std::mutex> lk(c->mu);
+    BCP_CUDA(cudaSetDevice(device));
+    const size_t spk_bytes = total_in ? spk_off[total_in] : 0, cap_in = total_in + 1;
+    size_t o = 0;
+    const size_t o_blk = o; o += up(base[nblk] + 64);
+    const size_t o_txoff = o; o += up((max_tx_all + 1) * 4);
+    const size_t o_inoff = o; o += up(cap_in * 4 + 4);
+    const size_t o_intx = o; o += up(cap_in * 4 + 4);
+    const size_t o_inn = o; o += up(cap_in * 4 + 4);
+    const size_t o_spk = o; o += up(spk_bytes + 8);
+    const size_t o_spkoff = o; o += up((cap_in + 1) * 4);
+    const size_t o_amt = o; o += up(cap_in * 8 + 8);
+    const size_t o_txid = o; o += up(max_tx_all * 32 + 32);
+    const size_t o_mtmp = o; o += up(bcp_merkle_tmp_words(max_tx_one) * 4);
+    const size_t o_root = o; o += up(nblk * 64); /* per block: root[32], mutated(int), pad */
+    const size_t o_flag = o; o += 256;
+    const size_t o_mid = o; o += up(max_tx_all * BCP_TXMID_BYTES + 16);
+    const size_t o_stat = o; o += up(cap_in + 8);
+    const size_t o_msg = o; o += up(cap_in * 32 + 32);
+    const size_t o_pub = o; o += up(cap_in * 65 + 65);
+    const size_t o_sig = o; o += up(cap_in * 64 + 64);
+    const size_t o_ok = o; o += up(cap_in + 8);
+    const size_t o_err = o; o += up(cap_in + 8);
+    int rc = bcp_ctx_reserve_stage(c, o);
+    if (rc != BCP_OK) return rc;
+    rc = bcp_ctx_reserve_scratch(c, bcp_gpu_ecdsa_scratch_bytes(total_in));
+    if (rc != BCP_OK) return rc;
+    uint8_t *d = c->stage;
+    cudaStream_t st = c->stream, st2 = c->copy_stream;
+    for (size_t b = 0; b < nblk; b++)
+        BCP_CUDA(cudaMemcpyAsync(d + o_blk + base[b], blks[b] + body[b], lens[b] - body[b], cudaMemcpyHostToDevice, st));
+    // host: one framing scan per block, on as many threads as there are blocks (up to the core count)
+    struct scan_t { std::vector<uint32_t> tx_off, in_off, in_tx, in_n; long ntx = 0, nin = 0; };
+    std::vector<scan_t> sc(nblk);
+    {
+        const unsigned T = (unsigned)std::min<size_t>(nblk, std::max(1u, std::thread::hardware_concurrency()));
+        std::vector<std::thread> th;
+        for (unsigned w = 0; w < T; w++)
+            th.emplace_back([&, w] {
+                for (size_t b = w; b < nblk; b += T) {
+                    scan_t &x = sc[b];
+                    const size_t mt = lens[b] / 60 + 2, mi = n_inputs[b] + 1;
+                    x.tx_off.resize(mt + 1); x.in_off.resize(mi); x.in_tx.resize(mi); x.in_n.resize(mi);
+                    x.nin = bcp_block_index_inputs(blks[b], lens[b], legacy_header, x.tx_off.data(), mt, x.in_off.data(),
+                                                   x.in_tx.data(), x.in_n.data(), mi, &x.ntx);
+                }
+            });
+        for (auto &t : th) t.join();
+    }
+    // one index space for the window: byte offsets rebased to the device buffer, transaction numbers to the window
+    std::vector<size_t> t_base(nblk + 1, 0);
+    for (size_t b = 0; b < nblk; b++) {
+        if (sc[b].nin < 0 || (size_t)sc[b].nin != n_inputs[b]) {
+            cudaStreamSynchronize(st);
+            if (sc[b].nin == -1) bcp_set_error("bcp_gpu_blocks_connect_p2pkh: block %zu is malformed", b);
+            else bcp_set_error("bcp_gpu_blocks_connect_p2pkh: block %zu: its non-coinbase inputs (%ld) do not match the %zu spent "
+                               "outputs the caller described", b, sc[b].nin, n_inputs[b]);
+            return BCP_ERR_INVALID;
+        }
+        if (sc[b].tx_off[sc[b].ntx] != lens[b]) { // the gap-free layout needs each block to end with its last transaction
+            cudaStreamSynchronize(st);
+            bcp_set_error("bcp_gpu_blocks_connect_p2pkh: block %zu has %zu bytes after its last transaction (use the "
+                          "single-block call for such a buffer)", b, lens[b] - (size_t)sc[b].tx_off[sc[b].ntx]);
+            return BCP_ERR_INVALID;
+        }
+        t_base[b + 1] = t_base[b] + (size_t)sc[b].ntx;
+    }
+    const size_t total_tx = t_base[nblk];
+    std::vector<uint32_t> &tx_off = c->h_tx_off, &in_off = c->h_in_off, &in_tx = c->h_in_tx, &in_n = c->h_in_n;
+    if (tx_off.size() < total_tx + 1) tx_off.resize(total_tx + 1);
+    if (in_off.size() < cap_in) { in_off.resize(cap_in); in_tx.resize(cap_in); in_n.resize(cap_in); }
+    for (size_t b = 0; b < nblk; b++) {
+        const scan_t &x = sc[b];
+        const uint32_t shift = (uint32_t)base[b] - (uint32_t)body[b], tb = (uint32_t)t_base[b]; // modulo 2^32 on purpose
+        for (long t = 0; t < x.ntx; t++) tx_off[t_base[b] + t] = x.tx_off[t] + shift;
+        for (long i = 0; i < x.nin; i++) {
+            in_off[in_base[b] + i] = x.in_off[i] + shift;
+            in_tx[in_base[b] + i] = x.in_tx[i] + tb;
+            in_n[in_base[b] + i] = x.in_n[i];
+        }
+    }
+    tx_off[total_tx] = (uint32_t)base[nblk]; // a block's transactions end where the next block's begin
+    BCP_CUDA(cudaMemcpyAsync(d + o_txoff, tx_off.data(), (total_tx + 1) * 4, cudaMemcpyHostToDevice, st));
+    uint32_t *d_txoff = reinterpret_cast<uint32_t *>(d + o_txoff);
+    rc = bcp_sha256d_offsets_dev(c, d + o_blk, d_txoff, total_tx, d + o_txid, st);
+    if (rc != BCP_OK) return rc;
+    // Merkle roots on the second stream, beside the script checks
+    BCP_CUDA(cudaEventRecord(c->ev[0], st));
+    BCP_CUDA(cudaStreamWaitEvent(st2, c->ev[0], 0));
+    for (size_t b = 0; b < nblk; b++) {
+        rc = bcp_merkle_dev(c, d + o_txid + t_base[b] * 32, (size_t)sc[b].ntx, d + o_root + b * 64,
+                            reinterpret_cast<int *>(d + o_root + b * 64 + 32), reinterpret_cast<uint32_t *>(d + o_mtmp), st2);
+        if (rc != BCP_OK) return rc;
+    }
+    std::vector<uint8_t> res(nblk * 64);
+    BCP_CUDA(cudaMemcpyAsync(res.data(), d + o_root, nblk * 64, cudaMemcpyDeviceToHost, st2));
+    if (txids) BCP_CUDA(cudaMemcpyAsync(txids, d + o_txid, total_tx * 32, cudaMemcpyDeviceToHost, st2));
+    BCP_CUDA(cudaEventRecord(c->ev[1], st2));
+    if (total_in) {
+        int one = 1;
+        int *d_flag = reinterpret_cast<int *>(d + o_flag);
+        BCP_CUDA(cudaMemcpyAsync(d_flag, &one, sizeof(int), cudaMemcpyHostToDevice, st));
+        BCP_CUDA(cudaMemcpyAsync(d + o_inoff, in_off.data(), total_in * 4, cudaMemcpyHostToDevice, st));
+        BCP_CUDA(cudaMemcpyAsync(d + o_intx, in_tx.data(), total_in * 4, cudaMemcpyHostToDevice, st));
+        BCP_CUDA(cudaMemcpyAsync(d + o_inn, in_n.data(), total_in * 4, cudaMemcpyHostToDevice, st));
+        BCP_CUDA(cudaMemcpyAsync(d + o_spk, spk, spk_bytes, cudaMemcpyHostToDevice, st));
+        BCP_CUDA(cudaMemcpyAsync(d + o_spkoff, spk_off, (total_in + 1) * 4, cudaMemcpyHostToDevice, st));
+        BCP_CUDA(cudaMemcpyAsync(d + o_amt, amounts, total_in * 8, cudaMemcpyHostToDevice, st));
+        k_tx_midstate<<<(unsigned)((total_tx + 127) / 128), 128, 0, st>>>(d + o_blk, d_txoff, total_tx, d + o_mid);
+        k_p2pkh_extract<<<(unsigned)((total_in + 127) / 128), 128, 0, st>>>(
+            d + o_blk, d_txoff, reinterpret_cast<uint32_t *>(d + o_inoff), reinterpret_cast<uint32_t *>(d + o_intx),
+            reinterpret_cast<uint32_t *>(d + o_inn), total_in, d + o_spk, reinterpret_cast<uint32_t *>(d + o_spkoff),
+            reinterpret_cast<int64_t *>(d + o_amt), d + o_mid, d + o_stat, d + o_msg, d + o_pub, d + o_sig);
+        BCP_CUDA(cudaGetLastError());
+        rc = bcp_ecdsa_launch(c, d + o_msg, d + o_pub, d + o_sig, total_in, BCP_ECDSA_FLAG_NORMALIZE_S, d + o_ok,
+                              reinterpret_cast<uint32_t *>(c->scratch), st);
+        if (rc != BCP_OK) return rc;
+        k_script_finish<<<(unsigned)((total_in + 255) / 256), 256, 0, st>>>(d + o_stat, d + o_ok, total_in, d + o_err, d_flag);
+        BCP_CUDA(cudaGetLastError());
+        BCP_CUDA(cudaMemcpyAsync(script_err, d + o_err, total_in, cudaMemcpyDeviceToHost, st));
+    }
+    BCP_CUDA(cudaStreamWaitEvent(st, c->ev[1], 0));
+    BCP_CUDA(cudaStreamSynchronize(st));
+    for (size_t b = 0; b < nblk; b++) {
+        memcpy(roots32 + b * 32, &res[b * 64], 32);
+        int m;
+        memcpy(&m, &res[b * 64 + 32], 4);
+        if (mutated) mutated[b] = m ? 1 : 0;
+        if (ntx_out) ntx_out[b] = (size_t)sc[b].ntx;
+        if (all_ok) {
+            int a = 1;
+            for (size_t i = in_base[b]; i < in_base[b + 1]; i++) a &= script_err[i] == 0;
+            all_ok[b] = a;
+        }
+    }
     return BCP_OK;
 }
 

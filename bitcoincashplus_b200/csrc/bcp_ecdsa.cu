@@ -5,7 +5,7 @@
 //   k_ecdsa_prep   one thread per K signatures (K = 8, 16 or 32 by batch size) (thread t takes signatures t, t+T, t+2T, ...
 //                  so that the byte loads of a warp stay adjacent), 128 threads per block
 //   k_ecdsa_point  one thread per signature, 128 threads per block, four blocks per SM; the per-thread
-//                  {1..8}Q tables (512 B) live in global scratch next to the phase-1 records (the first
+//                  {1..8}Q tables (768 B: x, y, beta*x per entry) live in global scratch next to the phase-1 records (the first
 //                  version kept them in shared memory, which capped occupancy at 12 warps per SM)
 // A batch is processed in slices of BCP_SLICE signatures (16 full waves) so that scratch is bounded (718 MB).
 //   k_gcomb_build  one thread per comb-table entry, once per device at bcp_gpu_init
@@ -35,7 +35,7 @@
 #define BCP_WAVE ((size_t)148 * 512)
 #define BCP_SLICE (16 * BCP_WAVE)
 #define BCP_E2E_CHUNK (3 * BCP_WAVE)
-#define BCP_SIG_SCRATCH_WORDS (BCP_REC_WORDS + BCP_QTAB_WORDS) /* 80-byte record + 512-byte table per signature */
+#define BCP_SIG_SCRATCH_WORDS (BCP_REC_WORDS + BCP_QTAB_WORDS) /* 80-byte record + 768-byte table per signature */
 
 __global__ void __launch_bounds__(128) k_gcomb_build(uint32_t *gcomb) {
     int idx = blockIdx.x * blockDim.x + threadIdx.x;

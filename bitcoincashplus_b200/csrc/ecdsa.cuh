@@ -44,7 +44,8 @@
 #define BCP_GCOMB_WORDS (BCP_GCOMB_WINDOWS * BCP_GCOMB_ENTRIES * 16) /* 16 words (x,y) per entry; entry 0 unused */
 
 #define BCP_QTAB_ENTRIES 8
-#define BCP_QTAB_WORDS (BCP_QTAB_ENTRIES * 16)
+#define BCP_QTAB_EWORDS 24 /* per entry: x, y and beta*x (the x of lambda*P), 8 limbs each */
+#define BCP_QTAB_WORDS (BCP_QTAB_ENTRIES * BCP_QTAB_EWORDS)
 
 // ---------------------------------------------------------------- phase 1: scalar side
 struct sig_scalars {
@@ -106,51 +107,66 @@ struct qtable {
     BCP_DEV_M void store(int e, const fe &x, const fe &y) {
         BCP_UNROLL
         for (int i = 0; i < 8; i++) {
-            base[(e * 16 + i) * stride] = x.v[i];
-            base[(e * 16 + 8 + i) * stride] = y.v[i];
+            base[(e * BCP_QTAB_EWORDS + i) * stride] = x.v[i];
+            base[(e * BCP_QTAB_EWORDS + 8 + i) * stride] = y.v[i];
         }
+    }
+    BCP_DEV_M void store_xb(int e, const fe &xb) {
+        BCP_UNROLL
+        for (int i = 0; i < 8; i++) base[(e * BCP_QTAB_EWORDS + 16 + i) * stride] = xb.v[i];
     }
     BCP_DEV_M void load(int e, fe &x, fe &y) const {
         BCP_UNROLL
         for (int i = 0; i < 8; i++) {
-            x.v[i] = base[(e * 16 + i) * stride];
-            y.v[i] = base[(e * 16 + 8 + i) * stride];
+            x.v[i] = base[(e * BCP_QTAB_EWORDS + i) * stride];
+            y.v[i] = base[(e * BCP_QTAB_EWORDS + 8 + i) * stride];
         }
     }
-    BCP_DEV_M void load_x(int e, fe &x) const {
+    BCP_DEV_M void load_b(int e, fe &xb, fe &y) const { /* lambda * entry = (beta * x, y) */
         BCP_UNROLL
-        for (int i = 0; i < 8; i++) x.v[i] = base[(e * 16 + i) * stride];
-    }
-    BCP_DEV_M void load_y(int e, fe &y) const {
-        BCP_UNROLL
-        for (int i = 0; i < 8; i++) y.v[i] = base[(e * 16 + 8 + i) * stride];
+        for (int i = 0; i < 8; i++) {
+            xb.v[i] = base[(e * BCP_QTAB_EWORDS + 16 + i) * stride];
+            y.v[i] = base[(e * BCP_QTAB_EWORDS + 8 + i) * stride];
+        }
     }
 };
 
-// Same table, one contiguous 512-byte slab per signature in global memory (entry e = 64 bytes at word e*16):
-// every lookup is four 16-byte loads of one lane's own 64 bytes, i.e. fully used sectors whatever entry each
-// lane picks.  Frees the shared memory that capped the point kernel at 12 warps per SM.
+// Same table, one contiguous 768-byte slab per signature in global memory (entry e = 96 bytes at word e*24:
+// x, y, beta*x): every lookup is four 16-byte loads of one lane's own entry, i.e. fully used sectors whatever
+// entry each lane picks.  Frees the shared memory that capped the point kernel at 12 warps per SM.
 struct qtable_packed {
     uint32_t *base; /* this signature's slab, 16-byte aligned */
     BCP_DEV_M void store(int e, const fe &x, const fe &y) {
 #if BCP_PTX
-        uint4 *p = reinterpret_cast<uint4 *>(base + e * 16);
+        uint4 *p = reinterpret_cast<uint4 *>(base + e * BCP_QTAB_EWORDS);
         p[0] = make_uint4(x.v[0], x.v[1], x.v[2], x.v[3]);
         p[1] = make_uint4(x.v[4], x.v[5], x.v[6], x.v[7]);
         p[2] = make_uint4(y.v[0], y.v[1], y.v[2], y.v[3]);
         p[3] = make_uint4(y.v[4], y.v[5], y.v[6], y.v[7]);
 #else
-        for (int i = 0; i < 8; i++) { base[e * 16 + i] = x.v[i]; base[e * 16 + 8 + i] = y.v[i]; }
+        for (int i = 0; i < 8; i++) { base[e * BCP_QTAB_EWORDS + i] = x.v[i]; base[e * BCP_QTAB_EWORDS + 8 + i] = y.v[i]; }
 #endif
     }
-    BCP_DEV_M void load(int e, fe &x, fe &y) const {
+    BCP_DEV_M void store_xb(int e, const fe &xb) {
 #if BCP_PTX
-        const uint4 *p = reinterpret_cast<const uint4 *>(base + e * 16);
-        uint4 a = p[0], b = p[1], c = p[2], d = p[3];
+        uint4 *p = reinterpret_cast<uint4 *>(base + e * BCP_QTAB_EWORDS + 16);
+        p[0] = make_uint4(xb.v[0], xb.v[1], xb.v[2], xb.v[3]);
+        p[1] = make_uint4(xb.v[4], xb.v[5], xb.v[6], xb.v[7]);
+#else
+        for (int i = 0; i < 8; i++) base[e * BCP_QTAB_EWORDS + 16 + i] = xb.v[i];
+#endif
+    }
+    BCP_DEV_M void load(int e, fe &x, fe &y) const { load_at(e, 0, x, y); }
+    BCP_DEV_M void load_b(int e, fe &xb, fe &y) const { load_at(e, 16, xb, y); } /* lambda * entry = (beta * x, y) */
+    BCP_DEV_M void load_at(int e, int xo, fe &x, fe &y) const {
+#if BCP_PTX
+        const uint4 *px = reinterpret_cast<const uint4 *>(base + e * BCP_QTAB_EWORDS + xo);
+        const uint4 *py = reinterpret_cast<const uint4 *>(base + e * BCP_QTAB_EWORDS + 8);
+        uint4 a = px[0], b = px[1], c = py[0], d = py[1];
         x.v[0] = a.x; x.v[1] = a.y; x.v[2] = a.z; x.v[3] = a.w; x.v[4] = b.x; x.v[5] = b.y; x.v[6] = b.z; x.v[7] = b.w;
         y.v[0] = c.x; y.v[1] = c.y; y.v[2] = c.z; y.v[3] = c.w; y.v[4] = d.x; y.v[5] = d.y; y.v[6] = d.z; y.v[7] = d.w;
 #else
-        for (int i = 0; i < 8; i++) { x.v[i] = base[e * 16 + i]; y.v[i] = base[e * 16 + 8 + i]; }
+        for (int i = 0; i < 8; i++) { x.v[i] = base[e * BCP_QTAB_EWORDS + xo + i]; y.v[i] = base[e * BCP_QTAB_EWORDS + 8 + i]; }
 #endif
     }
 };
@@ -202,19 +218,26 @@ BCP_DEV bool ecdsa_point_phase(const uint32_t *rec, const uint8_t *pub65, const 
             const int u = t - T_TAB;
             if (u == 0) {
                 zglob = acc.z;
-                fe zs = zr[BCP_QTAB_ENTRIES - 1];
+                fe zs = zr[BCP_QTAB_ENTRIES - 1], beta;
+                BCP_UNROLL
+                for (int i = 0; i < 8; i++) beta.v[i] = FE_BETA[i];
+                /* k = ENTRIES-1 is already on the common Z and only gets its beta*x; the others are rescaled first */
 #if BCP_PTX
 #pragma unroll 1
 #endif
-                for (int k = BCP_QTAB_ENTRIES - 2; k >= 0; k--) {
+                for (int k = BCP_QTAB_ENTRIES - 1; k >= 0; k--) {
                     fe ex, ey, zs2, zs3;
                     tab.load(k, ex, ey);
-                    fe_sqr(zs2, zs);
-                    fe_mul(zs3, zs2, zs);
-                    fe_mul(ex, ex, zs2);
-                    fe_mul(ey, ey, zs3);
-                    tab.store(k, ex, ey);
-                    if (k > 0) fe_mul(zs, zs, zr[k]);
+                    if (k < BCP_QTAB_ENTRIES - 1) {
+                        fe_sqr(zs2, zs);
+                        fe_mul(zs3, zs2, zs);
+                        fe_mul(ex, ex, zs2);
+                        fe_mul(ey, ey, zs3);
+                        tab.store(k, ex, ey);
+                        if (k > 0) fe_mul(zs, zs, zr[k]);
+                    }
+                    fe_mul(ex, ex, beta); /* x of lambda * (k+1)Q: one product per entry instead of one per use */
+                    tab.store_xb(k, ex);
                 }
                 acc.inf = true;
             }
@@ -228,13 +251,8 @@ BCP_DEV bool ecdsa_point_phase(const uint32_t *rec, const uint8_t *pub65, const 
                 if (w <= 32) d -= 8;
                 if (d != 0) {
                     const bool neg = (d < 0) != (second ? n2 : n1);
-                    tab.load((d < 0 ? -d : d) - 1, x, y);
-                    if (second) { /* lambda * (x, y) = (beta * x, y) */
-                        fe beta;
-                        BCP_UNROLL
-                        for (int i = 0; i < 8; i++) beta.v[i] = FE_BETA[i];
-                        fe_mul(x, x, beta);
-                    }
+                    if (second) tab.load_b((d < 0 ? -d : d) - 1, x, y); /* lambda * (x, y) = (beta * x, y) */
+                    else tab.load((d < 0 ? -d : d) - 1, x, y);
                     if (neg) fe_neg(y, y);
                     have = true;
                 }

@@ -157,6 +157,20 @@ BCP_API int bcp_gpu_block_connect_p2pkh(int device, const uint8_t *blk, size_t l
                                         const uint32_t *spk_off, const int64_t *amounts, size_t n_inputs, uint32_t flags,
                                         uint8_t *txids, uint8_t root32[32], int *mutated, uint8_t *script_err, int *all_ok);
 
+/* A WINDOW of blocks in one pass (reindex / initial block download: LoadExternalBlockFile hands over block after
+ * block, src/validation.cpp:4486-4560).  Same results per block as bcp_gpu_block_connect_p2pkh; the per-input kernels
+ * run once over the union of the window's inputs, so the GPU sees several waves of work instead of half of one.
+ *   blks/lens     nblk raw blocks, each ending with its last transaction (as blk*.dat stores them); pinned memory
+ *                 lets the copies overlap the host scans, which run one thread per block
+ *   n_inputs      non-coinbase inputs of each block; spk / spk_off / amounts / script_err cover the concatenation of
+ *                 all blocks' inputs in window order (spk_off has sum(n_inputs)+1 entries)
+ *   txids         optional, the concatenation of every block's txids; ntx_out (optional) = transactions per block
+ *   roots32, mutated, all_ok   one entry per block */
+BCP_API int bcp_gpu_blocks_connect_p2pkh(int device, size_t nblk, const uint8_t *const *blks, const size_t *lens,
+                                         int legacy_header, const uint8_t *spk, const uint32_t *spk_off,
+                                         const int64_t *amounts, const size_t *n_inputs, uint32_t flags, uint8_t *txids,
+                                         size_t *ntx_out, uint8_t *roots32, int *mutated, uint8_t *script_err, int *all_ok);
+
 /* ---- Equihash: CheckEquihashSolution (src/pow.cpp:298-323) == Equihash<N,K>::IsValidSolution
  *      (src/crypto/equihash.cpp:724-770) for `count` serialized post-fork headers (140 bytes || compact
  *      size || solution; src/primitives/block.h:49-73) laid out at `stride` bytes, each `hdr_len` long.

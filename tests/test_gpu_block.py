@@ -97,3 +97,63 @@ def test_block_index_inputs_matches_oracle(engine, oracle):
     # capacity error
     assert L.bcp_block_index_inputs(b.ctypes.data, len(blk), 0, tx_off.ctypes.data, 299, arrs[0].ctypes.data, arrs[1].ctypes.data,
                                     arrs[2].ctypes.data, 3, C.byref(ntx)) == -2
+
+
+def _window(blocks):
+    """marshals [(blk, spk list, amounts)] for the window call"""
+    cat = np.frombuffer(b"".join(b"".join(s) for _, s, _ in blocks) or b"\x00", dtype=np.uint8)
+    lens = [len(x) for _, s, _ in blocks for x in s]
+    off = np.zeros(len(lens) + 1, dtype=np.uint32)
+    off[1:] = np.cumsum(lens)
+    am = np.array([a for _, _, aa in blocks for a in aa], dtype=np.int64)
+    return [np.frombuffer(b, dtype=np.uint8) for b, _, _ in blocks], cat, off, am, [len(s) for _, s, _ in blocks]
+
+
+def test_window_of_blocks_matches_per_block_calls(engine, oracle):
+    """bcp_gpu_blocks_connect_p2pkh over a window of different blocks (mutated inputs, multi-input transactions, an
+    empty block, a block with a broken Merkle root, a duplicated last transaction) == the single-block call per block
+    == the oracle."""
+    kinds = list(synth.INPUT_MUTATIONS)
+    b0 = synth.synthetic_block(300, True, nkeys=32, with_prevouts=True, mutations={3 + 5 * i: k for i, k in enumerate(kinds)})
+    b1 = synth.synthetic_block_multi(200, seed=5)
+    b2 = (synth.synthetic_block(0, True), [], [])
+    b3 = synth.synthetic_block(1000, True, nkeys=64, with_prevouts=True, bad_inputs=(999,))
+    blk4, spk4, amt4 = synth.synthetic_block(64, True, nkeys=8, with_prevouts=True)
+    blk4 = bytearray(blk4)
+    blk4[40] ^= 1  # header Merkle root no longer matches: the call reports the real root, the caller compares
+    b4 = (bytes(blk4), spk4, amt4)
+    b5 = synth.synthetic_block(777, True, nkeys=16, with_prevouts=True)
+    blocks = [b0, b1, b2, b3, b4, b5]
+    arrs, cat, off, am, nin = _window(blocks)
+    res = engine.blocks_connect_p2pkh(arrs, cat, off, am, nin, synth.POSTFORK_FLAGS, want_txids=True)
+    pos = tpos = 0
+    for b, (blk, spk, amt) in enumerate(blocks):
+        one = engine.block_connect_p2pkh(blk, spk, amt, synth.POSTFORK_FLAGS, want_txids=True)
+        n, txids, root, mutated = oracle.block_txids(blk, False)
+        assert res["ntx"][b] == n
+        assert bytes(res["roots"][b]) == one["root"] == root, b
+        assert res["mutated"][b] == one["mutated"] == mutated
+        assert (res["txids"][tpos:tpos + n] == txids).all()
+        err = res["script_err"][pos:pos + len(spk)]
+        assert (err == one["script_err"]).all(), b
+        if spk:
+            want = oracle.block_script_errors(blk, False, spk, amt, synth.POSTFORK_FLAGS, NT)
+            assert (err == want).all(), b
+        assert res["all_ok"][b] == one["all_ok"] == (not err.any())
+        pos += len(spk)
+        tpos += n
+    assert res["all_ok"] == [False, True, True, False, True, True]
+
+
+def test_window_rejects_malformed_block_and_wrong_counts(engine):
+    import bitcoincashplus_b200 as bcp
+
+    good = synth.synthetic_block(50, True, nkeys=4, with_prevouts=True)
+    arrs, cat, off, am, nin = _window([good, good])
+    bad = arrs[1].copy()[:-7]  # truncated
+    with pytest.raises(bcp.BcpError):
+        engine.blocks_connect_p2pkh([arrs[0], bad], cat, off, am, nin, synth.POSTFORK_FLAGS)
+    with pytest.raises(bcp.BcpError):  # input counts swapped between blocks of different size
+        other = synth.synthetic_block(20, True, nkeys=4, with_prevouts=True)
+        a2, c2, o2, m2, n2 = _window([good, other])
+        engine.blocks_connect_p2pkh(a2, c2, o2, m2, n2[::-1], synth.POSTFORK_FLAGS)
