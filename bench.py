@@ -167,7 +167,7 @@ def block_bench(eng, args, bcp, sync=None):
     return out
 
 
-def window_bench(eng, args, bcp, W=8):
+def window_bench(eng, args, bcp, sync=None, W=8):
     """Throughput form of the 8 MB block measurement (reindex / initial block download, blocks at hand): W blocks per call
     through bcp_gpu_blocks_connect_p2pkh — one pass of the per-input kernels over the union of the window's inputs.
     The W blocks are the same synthetic block in W separate pinned buffers (run time does not depend on the content)."""
@@ -192,13 +192,41 @@ def window_bench(eng, args, bcp, W=8):
     res = eng.blocks_connect_p2pkh(blks, cat, off, am, [n] * W, synth.POSTFORK_FLAGS)
     assert all(res["all_ok"]) and all(bytes(r) == blk[36:68] for r in res["roots"]) and not any(res["mutated"])
     reps = 5
+    if sync is not None:
+        sync(0.0)  # ranks enter the timed region together
     t0 = time.perf_counter()
     for _ in range(reps):
         eng.blocks_connect_p2pkh(blks, cat, off, am, [n] * W, synth.POSTFORK_FLAGS)
     s = (time.perf_counter() - t0) / reps
-    return {"window_blocks": W, "inputs_per_block": n, "gpu_ms_per_window": s * 1e3, "gpu_ms_per_block": s * 1e3 / W,
-            "gpu_blocks_per_s": W / s, "gpu_inputs_per_s": W * n / s,
-            "timed": "bcp_gpu_blocks_connect_p2pkh end to end (host framing scans on W threads + H2D + kernels + D2H), pinned host buffers"}
+    # two host threads, each with its own lane of the same GPU: one window's copies and scans run under the other's kernels
+    eng2 = bcp.Engine(eng.device & 0xFF, lane=1)
+    eng2.blocks_connect_p2pkh(blks, cat, off, am, [n] * W, synth.POSTFORK_FLAGS)
+
+    def worker(e):
+        for _ in range(reps):
+            r = e.blocks_connect_p2pkh(blks, cat, off, am, [n] * W, synth.POSTFORK_FLAGS)
+            assert all(r["all_ok"])
+
+    th = [threading.Thread(target=worker, args=(e,)) for e in (eng, eng2)]
+    if sync is not None:
+        sync(0.0)
+    t0 = time.perf_counter()
+    for t in th:
+        t.start()
+    for t in th:
+        t.join()
+    s2 = (time.perf_counter() - t0) / (2 * reps)
+    world = 1
+    if sync is not None:  # every rank measured its own GPU at the same time: take the slowest
+        world = sync(0.0, count=True)
+        s, s2 = sync(s), sync(s2)
+        if int(os.environ.get("RANK", "0")) != 0:
+            return None
+    return {"window_blocks": W, "inputs_per_block": n, "gpus": world, "gpu_ms_per_window": s * 1e3, "gpu_ms_per_block": s * 1e3 / W,
+            "gpu_blocks_per_s": world * W / s, "gpu_inputs_per_s": world * W * n / s,
+            "two_lanes": {"gpu_ms_per_window": s2 * 1e3, "gpu_blocks_per_s": world * W / s2, "gpu_inputs_per_s": world * W * n / s2},
+            "timed": "bcp_gpu_blocks_connect_p2pkh end to end (host framing scans on W threads + H2D + kernels + D2H), pinned "
+                     "host buffers; two_lanes = two host threads on two lanes of the same GPU"}
 
 
 def equihash_bench(eng):
@@ -244,7 +272,7 @@ def chain_bench(args, devices):
     import synth
     from oracle import pyoracle as po
 
-    nb, ntx = args.chain_blocks, args.block_txs
+    nb, ntx = args.chain_blocks + 1, args.block_txs
     t0 = time.perf_counter()
     blocks = list(synth.synthetic_chain_fast(nb, ntx))
     seeds = synth.chain_seeds(ntx, 4096)
@@ -271,17 +299,32 @@ def chain_bench(args, devices):
         C.memmove(p, b, len(b))
         pinned.append((p, len(b)))
     per_block = []
+    # block 0 is the warm-up (device staging buffers are allocated on first use); the timed region is blocks 1..nb-1
+    ok = L.bcp_chain_connect_block(h, pinned[0][0], pinned[0][1], reason, 256)
+    assert ok == 1, reason.value
+    ph0 = (C.c_double * 5)()
+    L.bcp_chain_phase_seconds.argtypes = [C.c_void_p, C.POINTER(C.c_double)]
+    L.bcp_chain_phase_seconds(h, ph0)
+    nb -= 1
     t0 = time.perf_counter()
-    for p, ln in pinned:
+    L.bcp_chain_connect_block_hint.argtypes = [C.c_void_p, C.c_void_p, C.c_size_t, C.c_void_p, C.c_size_t, C.c_char_p, C.c_size_t]
+    for j, (p, ln) in enumerate(pinned[1:], start=1):
+        nxt = pinned[j + 1] if j + 1 < len(pinned) else (None, 0)  # reindex: the next block is at hand, its scan runs ahead
         t1 = time.perf_counter()
-        ok = L.bcp_chain_connect_block(h, p, ln, reason, 256)
+        ok = L.bcp_chain_connect_block_hint(h, p, ln, nxt[0], nxt[1], reason, 256)
         per_block.append(time.perf_counter() - t1)
         assert ok == 1, reason.value
     total = time.perf_counter() - t0
     ph = (C.c_double * 5)()
     L.bcp_chain_phase_seconds.argtypes = [C.c_void_p, C.POINTER(C.c_double)]
     L.bcp_chain_phase_seconds(h, ph)
-    phases = dict(zip(["header_equihash", "framing_scan", "txids_merkle", "utxo_walk", "script_checks"], [1e3 * x / nb for x in ph]))
+    phases = dict(zip(["header_equihash", "framing_scan", "txids_wait_after_lookups", "utxo_walk", "scripts_wait_after_inserts"],
+                      [1e3 * (x - x0) / nb for x, x0 in zip(ph, ph0)]))
+    wk = (C.c_double * 4)()
+    L.bcp_chain_walk_seconds.argtypes = [C.c_void_p, C.POINTER(C.c_double)]
+    L.bcp_chain_walk_seconds(h, wk)
+    phases["utxo_walk_parts"] = dict(zip(["pass_a_lookups", "staging_and_launch", "pass_b_inserts", "pass_c_in_block"],
+                                         [1e3 * x / (nb + 1) for x in wk]))
     for p, _ in pinned:
         G.bcp_gpu_host_free(p)
     L.bcp_chain_free(h)
@@ -289,8 +332,9 @@ def chain_bench(args, devices):
            "sharding": "one host chain walk; each block's inputs split by index across the GPUs, verdicts ANDed on the host",
            "gpu_seconds_total": total,
            "gpu_blocks_per_s": nb / total, "gpu_ms_per_block_median": sorted(per_block)[len(per_block) // 2] * 1e3,
-           "gpu_ms_first_block": per_block[0] * 1e3, "ms_per_block_by_phase": phases, "gen_seconds": gen_s,
-           "timed": "bcp::ChainValidator::ConnectBlock per block (block bytes in pinned host memory, in-memory UTXO table on the host)"}
+           "ms_per_block_by_phase": phases, "gen_seconds": gen_s, "warmup_blocks": 1,
+           "timed": "bcp::ChainValidator::ConnectBlock per block, the next block's framing scan running one block ahead (block "
+                    "bytes in pinned host memory, in-memory UTXO table on the host)"}
     if po.have_ref():
         r = po.ref()
         cores = os.cpu_count() or 1
@@ -454,9 +498,10 @@ def main():
         td.all_reduce(t, op=td.ReduceOp.MAX, group=hostgrp)
         return world if count else t[0].item()
 
-    blk_section = None
+    blk_section = win_section = None
     if not args.no_block:
         blk_section = block_bench(eng, args, bcp, host_sync if dist else None)
+        win_section = window_bench(eng, args, bcp, host_sync if dist else None)
     if rank != 0:
         if dist:
             td.barrier(group=hostgrp)  # rank 0 is still measuring its secondary sections; leave together
@@ -505,7 +550,7 @@ def main():
         line["cpu_baseline"] = cpu_baseline(msg, pub, sig)
     if not args.no_block:
         line["block8mb"] = blk_section
-        line["block8mb_window"] = window_bench(eng, args, bcp)
+        line["block8mb_window"] = win_section
         line["equihash10k"] = equihash_bench(eng)
         if args.chain_blocks > 0:
             line["chain"] = chain_bench(args, list(range(world)))

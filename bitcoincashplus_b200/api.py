@@ -40,11 +40,12 @@ def block_index(blk, legacy_header=False, max_tx=1 << 22):
 
 
 class Engine:
-    """One device context (bcp_gpu_init / bcp_gpu_shutdown)."""
+    """One device context (bcp_gpu_init / bcp_gpu_shutdown).  `lane` (0..3) selects an independent context on the same
+    GPU (BCP_DEVICE_LANE in include/bcp_gpu.h): engines on different lanes run their calls concurrently."""
 
-    def __init__(self, device=0):
-        self.device = int(device)
-        check(lib().bcp_gpu_init(self.device), "bcp_gpu_init(%d)" % self.device)
+    def __init__(self, device=0, lane=0):
+        self.device = int(device) | (int(lane) << 8)
+        check(lib().bcp_gpu_init(self.device), "bcp_gpu_init(0x%x)" % self.device)
 
     def close(self):
         lib().bcp_gpu_shutdown(self.device)

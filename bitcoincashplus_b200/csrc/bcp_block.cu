@@ -89,6 +89,19 @@ extern "C" {
 // in_n = its ordinal in that transaction.  Returns the number of inputs (-1 malformed, -2 capacity); *ntx_out = ntx.
 BCP_API long bcp_block_index_inputs(const uint8_t *blk, size_t len, int legacy_header, uint32_t *tx_off, size_t max_tx,
                                     uint32_t *in_off, uint32_t *in_tx, uint32_t *in_n, size_t max_inputs, long *ntx_out) {
+    return bcp_block_index_full(blk, len, legacy_header, tx_off, nullptr, max_tx, in_off, in_tx, in_n, max_inputs, ntx_out,
+                                nullptr, nullptr, nullptr, 0, nullptr);
+}
+
+// The same scan, additionally reporting where each transaction's output list starts (the offset of its output count)
+// and, flat like the inputs, every output: out_off = offset of its 8-byte amount, out_tx = its transaction, out_n = its
+// index.  A block connector inserts the new coins from these without parsing anything again.  The extra arrays may be
+// NULL (max_outputs is then ignored); more than max_outputs outputs is the capacity error -2.
+BCP_API long bcp_block_index_full(const uint8_t *blk, size_t len, int legacy_header, uint32_t *tx_off, uint32_t *tx_out_off,
+                                  size_t max_tx, uint32_t *in_off, uint32_t *in_tx, uint32_t *in_n, size_t max_inputs,
+                                  long *ntx_out, uint32_t *out_off, uint32_t *out_tx, uint32_t *out_n, size_t max_outputs,
+                                  long *nout_out) {
+    size_t ocnt = 0;
     // One pass (this scan sits on the critical path of a block: nothing can launch before the offsets exist).
     // Same acceptance rules as bcp_block_index: canonical compact sizes, MAX_SIZE, everything inside the buffer.
     size_t pos;
@@ -132,9 +145,15 @@ BCP_API long bcp_block_index_inputs(const uint8_t *blk, size_t len, int legacy_h
             if (pos + sl + 4 > len) return -1;
             pos += sl + 4;
         }
+        if (tx_out_off) tx_out_off[t] = (uint32_t)pos;
         BCP_RD_COMPACT(nout);
         for (uint64_t i = 0; i < nout; i++) {
             if (pos + 8 > len) return -1;
+            if (out_off) {
+                if (ocnt >= max_outputs) return -2;
+                out_off[ocnt] = (uint32_t)pos; out_tx[ocnt] = (uint32_t)t; out_n[ocnt] = (uint32_t)i;
+                ocnt++;
+            }
             pos += 8;
             BCP_RD_COMPACT(sl);
             if (pos + sl > len) return -1;
@@ -146,6 +165,7 @@ BCP_API long bcp_block_index_inputs(const uint8_t *blk, size_t len, int legacy_h
 #undef BCP_RD_COMPACT
     tx_off[ntx] = (uint32_t)pos;
     if (ntx_out) *ntx_out = (long)ntx;
+    if (nout_out) *nout_out = (long)ocnt;
     return (long)cnt;
 }
 
@@ -172,7 +192,7 @@ BCP_API int bcp_gpu_block_scripts_p2pkh(int device, const uint8_t *blk, size_t l
     }
     if (len > 0xFFFFFFF0ull || tx_off[ntx] > len) { bcp_set_error("bcp_gpu_block_scripts_p2pkh: offsets exceed the block"); return BCP_ERR_INVALID; }
     std::lock_guard<std::mutex> lk(c->mu);
-    BCP_CUDA(cudaSetDevice(device));
+    BCP_CUDA(cudaSetDevice(c->device));
     auto up = [](size_t x) { return (x + 255) / 256 * 256; };
     const size_t nin = n_inputs, spk_bytes = spk_off[nin] - spk_off[0];
     size_t o = 0;
@@ -254,7 +274,7 @@ BCP_API int bcp_gpu_block_connect_p2pkh(int device, const uint8_t *blk, size_t l
     const size_t max_tx = len / 60 + 2, max_in = len / 41 + 2;
     if (n_inputs > max_in) { bcp_set_error("bcp_gpu_block_connect_p2pkh: more inputs than the block can hold"); return BCP_ERR_INVALID; }
     std::lock_guard<std::mutex> lk(c->mu);
-    BCP_CUDA(cudaSetDevice(device));
+    BCP_CUDA(cudaSetDevice(c->device));
     auto up = [](size_t x) { return (x + 255) / 256 * 256; };
     const size_t spk_bytes = n_inputs ? spk_off[n_inputs] : 0;
     const size_t cap_in = n_inputs + 1;
@@ -393,7 +413,7 @@ BCP_API int bcp_gpu_blocks_connect_p2pkh(int device, size_t nblk, const uint8_t 
     if (base[nblk] > 0xFFFFFFF0ull) { bcp_set_error("bcp_gpu_blocks_connect_p2pkh: window larger than 4 GiB"); return BCP_ERR_INVALID; }
     if (total_in && (!spk || !spk_off || !amounts || !script_err)) { bcp_set_error("bcp_gpu_blocks_connect_p2pkh: NULL buffer"); return BCP_ERR_INVALID; }
     std::lock_guard<std::mutex> lk(c->mu);
-    BCP_CUDA(cudaSetDevice(device));
+    BCP_CUDA(cudaSetDevice(c->device));
     const size_t spk_bytes = total_in ? spk_off[total_in] : 0, cap_in = total_in + 1;
     size_t o = 0;
     const size_t o_blk = o; o += up(base[nblk] + 64);

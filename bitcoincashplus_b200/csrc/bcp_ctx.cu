@@ -7,7 +7,7 @@
 
 int bcp_ecdsa_build_tables(bcp_ctx *c); // bcp_ecdsa.cu
 
-static bcp_ctx g_ctx[BCP_MAX_DEVICES];
+static bcp_ctx g_ctx[BCP_MAX_DEVICES][BCP_MAX_LANES];
 static std::mutex g_init_mu;
 static thread_local char g_err[512] = "";
 
@@ -22,12 +22,13 @@ int bcp_cuda_fail(cudaError_t e, const char *what) {
     cudaGetLastError(); // clear the sticky-less error state
     return e == cudaErrorNoDevice || e == cudaErrorInsufficientDriver ? BCP_ERR_NO_DEVICE : BCP_ERR_CUDA;
 }
-bcp_ctx *bcp_get_ctx(int device) {
-    if (device < 0 || device >= BCP_MAX_DEVICES || !g_ctx[device].ready) {
-        bcp_set_error("device %d not initialised: call bcp_gpu_init first", device);
+bcp_ctx *bcp_get_ctx(int id) {
+    const int device = id & 0xFF, lane = id >> 8;
+    if (id < 0 || device >= BCP_MAX_DEVICES || lane >= BCP_MAX_LANES || !g_ctx[device][lane].ready) {
+        bcp_set_error("device %d lane %d not initialised: call bcp_gpu_init first", device, lane);
         return nullptr;
     }
-    return &g_ctx[device];
+    return &g_ctx[device][lane];
 }
 int bcp_ctx_reserve_scratch(bcp_ctx *c, size_t bytes) {
     if (bytes <= c->scratch_bytes) return BCP_OK;
@@ -64,8 +65,23 @@ int bcp_gpu_device_count(void) {
     return n;
 }
 
-int bcp_gpu_init(int device) {
+static int init_locked(int device, int lane);
+
+int bcp_gpu_init(int id) {
     std::lock_guard<std::mutex> lk(g_init_mu);
+    const int device = id & 0xFF, lane = id >> 8;
+    if (id < 0 || lane >= BCP_MAX_LANES) {
+        bcp_set_error("bad device id 0x%x (device | lane << 8, lanes 0..%d)", id, BCP_MAX_LANES - 1);
+        return BCP_ERR_INVALID;
+    }
+    if (lane > 0) { // lane 0 owns the comb table every lane of the GPU reads
+        int rc = init_locked(device, 0);
+        if (rc != BCP_OK) return rc;
+    }
+    return init_locked(device, lane);
+}
+
+static int init_locked(int device, int lane) {
     int n = 0;
     cudaError_t e = cudaGetDeviceCount(&n);
     if (e != cudaSuccess || n == 0) {
@@ -78,7 +94,7 @@ int bcp_gpu_init(int device) {
         bcp_set_error("device ordinal %d out of range (0..%d)", device, n - 1);
         return BCP_ERR_NO_DEVICE;
     }
-    bcp_ctx *c = &g_ctx[device];
+    bcp_ctx *c = &g_ctx[device][lane];
     if (c->ready) return BCP_OK;
     BCP_CUDA(cudaSetDevice(device));
     cudaDeviceProp prop;
@@ -93,29 +109,38 @@ int bcp_gpu_init(int device) {
     BCP_CUDA(cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking));
     BCP_CUDA(cudaStreamCreateWithFlags(&c->copy_stream, cudaStreamNonBlocking));
     for (int i = 0; i < 4; i++) BCP_CUDA(cudaEventCreateWithFlags(&c->ev[i], cudaEventDisableTiming));
-    int rc = bcp_ecdsa_build_tables(c);
-    if (rc != BCP_OK) return rc;
+    if (lane == 0) {
+        int rc = bcp_ecdsa_build_tables(c);
+        if (rc != BCP_OK) return rc;
+    } else {
+        c->gcomb = g_ctx[device][0].gcomb;
+    }
     c->ready = true;
     return BCP_OK;
 }
 
-int bcp_gpu_shutdown(int device) {
+int bcp_gpu_shutdown(int id) { // lane 0 (the plain device ordinal) takes the GPU's other lanes down with it
     std::lock_guard<std::mutex> lk(g_init_mu);
-    if (device < 0 || device >= BCP_MAX_DEVICES || !g_ctx[device].ready) return BCP_OK;
-    bcp_ctx *c = &g_ctx[device];
-    std::lock_guard<std::mutex> lk2(c->mu);
-    cudaSetDevice(device);
-    cudaStreamSynchronize(c->stream);
-    cudaStreamSynchronize(c->copy_stream);
-    if (c->gcomb) cudaFree(c->gcomb);
-    if (c->scratch) cudaFree(c->scratch);
-    if (c->stage) cudaFree(c->stage);
-    for (int i = 0; i < 4; i++) cudaEventDestroy(c->ev[i]);
-    cudaStreamDestroy(c->stream);
-    cudaStreamDestroy(c->copy_stream);
-    c->gcomb = nullptr; c->scratch = nullptr; c->stage = nullptr;
-    c->scratch_bytes = c->stage_bytes = 0;
-    c->ready = false;
+    const int device = id & 0xFF, lane0 = id >> 8;
+    if (id < 0 || device >= BCP_MAX_DEVICES || lane0 >= BCP_MAX_LANES) return BCP_OK;
+    for (int lane = BCP_MAX_LANES - 1; lane >= lane0; lane--) {
+        bcp_ctx *c = &g_ctx[device][lane];
+        if (!c->ready) continue;
+        if (lane != lane0 && lane0 != 0) continue;
+        std::lock_guard<std::mutex> lk2(c->mu);
+        cudaSetDevice(device);
+        cudaStreamSynchronize(c->stream);
+        cudaStreamSynchronize(c->copy_stream);
+        if (c->gcomb && lane == 0) cudaFree(c->gcomb);
+        if (c->scratch) cudaFree(c->scratch);
+        if (c->stage) cudaFree(c->stage);
+        for (int i = 0; i < 4; i++) cudaEventDestroy(c->ev[i]);
+        cudaStreamDestroy(c->stream);
+        cudaStreamDestroy(c->copy_stream);
+        c->gcomb = nullptr; c->scratch = nullptr; c->stage = nullptr;
+        c->scratch_bytes = c->stage_bytes = 0;
+        c->ready = false;
+    }
     return BCP_OK;
 }
 
@@ -270,7 +295,7 @@ extern "C" int bcp_gpu_measure_int_peak(int device, int which, double *ops_per_s
     if (!c) return BCP_ERR_NOT_INIT;
     if (!ops_per_second || which < 0 || which > 6) return BCP_ERR_INVALID;
     std::lock_guard<std::mutex> lk(c->mu);
-    BCP_CUDA(cudaSetDevice(device));
+    BCP_CUDA(cudaSetDevice(c->device));
     const int blocks = c->sm_count * 8, threads = 256, iters = 4096;
     uint32_t *out = nullptr;
     BCP_CUDA(cudaMalloc(&out, (size_t)blocks * threads * 4));

@@ -7,6 +7,7 @@
 #include "../../include/bcp_gpu.h"
 
 #define BCP_MAX_DEVICES 16
+#define BCP_MAX_LANES 4 /* independent contexts (streams, staging, scratch) per GPU: id = device | lane << 8 */
 
 struct bcp_ctx {
     bool ready = false;

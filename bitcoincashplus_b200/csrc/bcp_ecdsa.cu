@@ -173,7 +173,7 @@ int bcp_gpu_ecdsa_reserve(int device, size_t n) {
     bcp_ctx *c = bcp_get_ctx(device);
     if (!c) return BCP_ERR_NOT_INIT;
     std::lock_guard<std::mutex> lk(c->mu);
-    BCP_CUDA(cudaSetDevice(device));
+    BCP_CUDA(cudaSetDevice(c->device));
     return bcp_ctx_reserve_scratch(c, bcp_gpu_ecdsa_scratch_bytes(n));
 }
 
@@ -186,7 +186,7 @@ int bcp_gpu_ecdsa_verify_batch_dev(int device, const uint8_t *d_msg32, const uin
         return BCP_ERR_INVALID;
     }
     std::lock_guard<std::mutex> lk(c->mu);
-    BCP_CUDA(cudaSetDevice(device));
+    BCP_CUDA(cudaSetDevice(c->device));
     int rc = bcp_ctx_reserve_scratch(c, bcp_gpu_ecdsa_scratch_bytes(n));
     if (rc != BCP_OK) return rc;
     return bcp_ecdsa_launch(c, d_msg32, d_pub65, d_sig64, n, flags, d_ok, reinterpret_cast<uint32_t *>(c->scratch),
@@ -203,7 +203,7 @@ int bcp_gpu_pubkey_parse_batch(int device, const uint8_t *pub65, size_t n, uint8
         return BCP_ERR_INVALID;
     }
     std::lock_guard<std::mutex> lk(c->mu);
-    BCP_CUDA(cudaSetDevice(device));
+    BCP_CUDA(cudaSetDevice(c->device));
     int rc = bcp_ctx_reserve_stage(c, n * (65 + 64 + 1) + 512);
     if (rc != BCP_OK) return rc;
     uint8_t *d_pub = c->stage, *d_xy = d_pub + ((n * 65 + 255) / 256) * 256, *d_ok = d_xy + n * 64;
@@ -228,7 +228,7 @@ int bcp_gpu_ecdsa_verify_batch(int device, const uint8_t *msg32, const uint8_t *
     }
     if (n == 0) return BCP_OK;
     std::lock_guard<std::mutex> lk(c->mu);
-    BCP_CUDA(cudaSetDevice(device));
+    BCP_CUDA(cudaSetDevice(c->device));
     const size_t CH = BCP_E2E_CHUNK; // signatures per chunk: three full waves
     const size_t per = 32 + 65 + 64 + 1;
     const size_t chunk = n < CH ? n : CH;

@@ -251,7 +251,7 @@ BCP_API int bcp_gpu_equihash_verify_batch_dev(int device, unsigned n, unsigned k
     if (!c) return BCP_ERR_NOT_INIT;
     if (count == 0) return BCP_OK;
     if (hdr_len > stride || hdr_len < 140) { bcp_set_error("equihash: bad header length/stride"); return BCP_ERR_INVALID; }
-    BCP_CUDA(cudaSetDevice(device));
+    BCP_CUDA(cudaSetDevice(c->device));
     return eh_dispatch(c, n, k, d_hdrs, stride, hdr_len, count, reinterpret_cast<uint64_t *>(d_scratch), d_ok,
                        stream ? (cudaStream_t)stream : c->stream);
 }
@@ -269,7 +269,7 @@ BCP_API int bcp_gpu_equihash_verify_batch(int device, unsigned n, unsigned k, co
         return BCP_ERR_INVALID;
     }
     std::lock_guard<std::mutex> lk(c->mu);
-    BCP_CUDA(cudaSetDevice(device));
+    BCP_CUDA(cudaSetDevice(c->device));
     size_t bytes = count * stride;
     size_t o_mid = (bytes + 8 + 255) / 256 * 256, o_ok = o_mid + count * 64, o_hash = (o_ok + count + 255) / 256 * 256;
     size_t total = o_hash + count * 32 + 256;
@@ -308,7 +308,7 @@ BCP_API int bcp_gpu_header_check_batch(int device, unsigned n, unsigned k, const
         return BCP_ERR_INVALID;
     }
     std::lock_guard<std::mutex> lk(c->mu);
-    BCP_CUDA(cudaSetDevice(device));
+    BCP_CUDA(cudaSetDevice(c->device));
     const size_t bytes = count * stride;
     const size_t o_mid = (bytes + 8 + 255) / 256 * 256, o_ok = o_mid + count * 64, o_pow = o_ok + count, o_link = o_pow + count,
                  o_hash = (o_link + count + 255) / 256 * 256, total = o_hash + count * 32 + 256;

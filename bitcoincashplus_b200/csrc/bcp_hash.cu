@@ -225,7 +225,7 @@ BCP_API int bcp_gpu_sha256d_batch_dev(int device, const uint8_t *d_data, const u
     bcp_ctx *c = bcp_get_ctx(device);
     if (!c) return BCP_ERR_NOT_INIT;
     if (count == 0) return BCP_OK;
-    BCP_CUDA(cudaSetDevice(device));
+    BCP_CUDA(cudaSetDevice(c->device));
     cudaStream_t st = stream ? (cudaStream_t)stream : c->stream;
     k_sha256d_msgs<<<(unsigned)((count + 127) / 128), 128, 0, st>>>(d_data, d_off, 0, 0, count, d_out32);
     BCP_CUDA(cudaGetLastError());
@@ -239,7 +239,7 @@ BCP_API int bcp_gpu_merkle_root_dev(int device, const uint8_t *d_leaves32, size_
                                     void *d_scratch, void *stream) {
     bcp_ctx *c = bcp_get_ctx(device);
     if (!c) return BCP_ERR_NOT_INIT;
-    BCP_CUDA(cudaSetDevice(device));
+    BCP_CUDA(cudaSetDevice(c->device));
     return merkle_dev(c, d_leaves32, n, d_root32, d_mutated, reinterpret_cast<uint32_t *>(d_scratch),
                       stream ? (cudaStream_t)stream : c->stream);
 }
@@ -273,7 +273,7 @@ BCP_API int bcp_gpu_merkle_root_dev_static(int device, const uint8_t *d_leaves32
         return BCP_ERR_INVALID;
     }
     std::lock_guard<std::mutex> lk(c->mu);
-    BCP_CUDA(cudaSetDevice(device));
+    BCP_CUDA(cudaSetDevice(c->device));
     if (!g_merkle_static_ptr[device]) { /* first call on this device: resolve the symbol's device address */
         uint32_t *p = nullptr;
         BCP_CUDA(cudaGetSymbolAddress((void **)&p, g_merkle_static_scratch));
@@ -328,7 +328,7 @@ BCP_API int bcp_gpu_sha256d_batch(int device, const uint8_t *data, size_t len, c
     if (count && (!data || !off || !out32)) { bcp_set_error("bcp_gpu_sha256d_batch: NULL buffer"); return BCP_ERR_INVALID; }
     if (count && (off[count] > len || len > 0xFFFFFFF0ull)) { bcp_set_error("bcp_gpu_sha256d_batch: offsets exceed buffer"); return BCP_ERR_INVALID; }
     std::lock_guard<std::mutex> lk(c->mu);
-    BCP_CUDA(cudaSetDevice(device));
+    BCP_CUDA(cudaSetDevice(c->device));
     return hash_host(c, data, len, off, count, false, out32, nullptr, nullptr);
 }
 
@@ -339,7 +339,7 @@ BCP_API int bcp_gpu_sha256d_txids_merkle(int device, const uint8_t *blk, size_t 
     if (!root32 || (ntx && (!blk || !tx_off))) { bcp_set_error("bcp_gpu_sha256d_txids_merkle: NULL buffer"); return BCP_ERR_INVALID; }
     if (ntx && (tx_off[ntx] > len || len > 0xFFFFFFF0ull)) { bcp_set_error("bcp_gpu_sha256d_txids_merkle: offsets exceed buffer"); return BCP_ERR_INVALID; }
     std::lock_guard<std::mutex> lk(c->mu);
-    BCP_CUDA(cudaSetDevice(device));
+    BCP_CUDA(cudaSetDevice(c->device));
     return hash_host(c, blk, len, tx_off, ntx, true, txids, root32, mutated);
 }
 
@@ -348,7 +348,7 @@ BCP_API int bcp_gpu_merkle_root(int device, const uint8_t *leaves32, size_t n, u
     if (!c) return BCP_ERR_NOT_INIT;
     if (!root32 || (n && !leaves32)) { bcp_set_error("bcp_gpu_merkle_root: NULL buffer"); return BCP_ERR_INVALID; }
     std::lock_guard<std::mutex> lk(c->mu);
-    BCP_CUDA(cudaSetDevice(device));
+    BCP_CUDA(cudaSetDevice(c->device));
     size_t o_tmp = (n * 32 + 255) / 256 * 256, o_root = o_tmp + (merkle_tmp_words(n) * 4 + 255) / 256 * 256;
     int rc = bcp_ctx_reserve_stage(c, o_root + 256);
     if (rc != BCP_OK) return rc;

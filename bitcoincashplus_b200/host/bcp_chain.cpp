@@ -9,6 +9,18 @@
 
 #define CHAIN_API extern "C" __attribute__((visibility("default")))
 
+CHAIN_API void *bcp_chain_new_threads(const int *devices, int ndev, uint32_t script_flags, unsigned eh_n, unsigned eh_k,
+                                      int walk_threads, char *err, size_t errlen) {
+    std::vector<int> d(devices, devices + ndev);
+    auto *v = new bcp::ChainValidator(d, script_flags, eh_n, eh_k, walk_threads);
+    std::string e;
+    if (!v->Init(e)) {
+        if (err && errlen) snprintf(err, errlen, "%s", e.c_str());
+        delete v;
+        return nullptr;
+    }
+    return v;
+}
 CHAIN_API void *bcp_chain_new(const int *devices, int ndev, uint32_t script_flags, unsigned eh_n, unsigned eh_k, char *err,
                               size_t errlen) {
     std::vector<int> d(devices, devices + ndev);
@@ -27,6 +39,13 @@ CHAIN_API void bcp_chain_add_coin(void *h, const uint8_t *txid32, uint32_t vout,
 }
 CHAIN_API size_t bcp_chain_utxo_size(void *h) { return static_cast<bcp::ChainValidator *>(h)->UtxoSize(); }
 CHAIN_API size_t bcp_chain_inputs_checked(void *h) { return static_cast<bcp::ChainValidator *>(h)->InputsChecked(); }
+CHAIN_API int bcp_chain_connect_block_hint(void *h, const uint8_t *blk, size_t len, const uint8_t *next, size_t next_len, char *reason,
+                                           size_t reasonlen) {
+    std::string r;
+    bool ok = static_cast<bcp::ChainValidator *>(h)->ConnectBlock(blk, len, r, next, next_len);
+    if (reason && reasonlen) snprintf(reason, reasonlen, "%s", r.c_str());
+    return ok ? 1 : 0;
+}
 CHAIN_API int bcp_chain_connect_block(void *h, const uint8_t *blk, size_t len, char *reason, size_t reasonlen) {
     std::string r;
     bool ok = static_cast<bcp::ChainValidator *>(h)->ConnectBlock(blk, len, r);
@@ -45,4 +64,9 @@ CHAIN_API long bcp_chain_connect_file(void *h, const uint8_t *data, size_t len, 
 CHAIN_API void bcp_chain_last_hash(void *h, uint8_t *out32) { memcpy(out32, static_cast<bcp::ChainValidator *>(h)->LastBlockHash(), 32); }
 CHAIN_API void bcp_chain_phase_seconds(void *h, double *out5) {
     for (int i = 0; i < 5; i++) out5[i] = static_cast<bcp::ChainValidator *>(h)->phase[i];
+}
+
+CHAIN_API void bcp_chain_walk_seconds(void *h, double out4[4]) {
+    auto *v = static_cast<bcp::ChainValidator *>(h);
+    for (int i = 0; i < 4; i++) out4[i] = v->walk[i];
 }

@@ -48,9 +48,14 @@ BCP_API int bcp_gpu_device_count(void);
 /* Create the per-device context: stream, fixed-base comb table for G (generated on the device; the
  * counterpart of secp256k1_ecmult_context_build, src/secp256k1/src/ecmult_impl.h:164-194, which
  * secp256k1_context_create(SECP256K1_CONTEXT_VERIFY) runs, src/secp256k1/src/secp256k1.c:59-83).
- * Idempotent. */
+ * Idempotent.
+ * Lanes: every `device` argument of this API may carry a lane number, BCP_DEVICE_LANE(ordinal, lane) with lane in
+ * 0..3.  A lane is an independent context on the same GPU — its own streams, staging buffer and scratch; the comb
+ * table is shared — so host threads that each use their own lane run their calls concurrently (one's copies under
+ * the other's kernels).  Calls on the SAME lane are serialised by a mutex.  Lane 0 is the plain ordinal. */
+#define BCP_DEVICE_LANE(ordinal, lane) ((ordinal) | ((lane) << 8))
 BCP_API int bcp_gpu_init(int device);
-/* Destroy it (secp256k1_context_destroy, secp256k1.c:96-105). */
+/* Destroy it (secp256k1_context_destroy, secp256k1.c:96-105); the plain ordinal also destroys the GPU's other lanes. */
 BCP_API int bcp_gpu_shutdown(int device);
 /* Text of the last error on the calling thread. */
 BCP_API const char *bcp_gpu_last_error(void);
@@ -146,6 +151,14 @@ BCP_API int bcp_gpu_merkle_root_dev_static(int device, const uint8_t *d_leaves32
  *   txids (optional), root32, mutated   as bcp_gpu_sha256d_txids_merkle */
 BCP_API long bcp_block_index_inputs(const uint8_t *blk, size_t len, int legacy_header, uint32_t *tx_off, size_t max_tx,
                                     uint32_t *in_off, uint32_t *in_tx, uint32_t *in_n, size_t max_inputs, long *ntx_out);
+/* Same scan for callers that go on to read the outputs (a block connector inserting the new coins):
+ *   tx_out_off[t] (optional)            offset of transaction t's output count
+ *   out_off / out_tx / out_n (optional) every output, flat like the inputs: offset of its 8-byte amount, its
+ *                                       transaction, its index; *nout_out = how many (max_outputs = capacity, -2 beyond) */
+BCP_API long bcp_block_index_full(const uint8_t *blk, size_t len, int legacy_header, uint32_t *tx_off, uint32_t *tx_out_off,
+                                  size_t max_tx, uint32_t *in_off, uint32_t *in_tx, uint32_t *in_n, size_t max_inputs,
+                                  long *ntx_out, uint32_t *out_off, uint32_t *out_tx, uint32_t *out_n, size_t max_outputs,
+                                  long *nout_out);
 /* The script checks alone, for any subset of a block's inputs chosen by the caller (arrays describe the subset;
  * spk_off may point into a larger offsets array).  This is the unit that shards across GPUs: one call per device
  * over its index range, verdicts AND-ed on the host like `fAllOk &= fOk` (src/checkqueue.h:77). */

@@ -18,11 +18,17 @@
 #ifndef BCP_COMPAT_CHAIN_H
 #define BCP_COMPAT_CHAIN_H
 
+#include <algorithm>
 #include <chrono>
+#include <condition_variable>
 #include <cstdint>
 #include <cstring>
+#include <functional>
+#include <memory>
+#include <mutex>
 #include <string>
 #include <thread>
+#include <unordered_map>
 #include <vector>
 
 #include "../bcp_gpu.h"
@@ -154,10 +160,81 @@ private:
     size_t mask, live = 0;
 };
 
+// A fixed team of host threads for the two table passes of a block: Run(f) calls f(worker) on every worker (the
+// caller is worker 0) and returns when all are done.
+class WorkerTeam {
+public:
+    explicit WorkerTeam(int n) : n_(n < 1 ? 1 : n) {
+        for (int w = 1; w < n_; w++) th_.emplace_back([this, w] { Loop(w); });
+    }
+    ~WorkerTeam() {
+        {
+            std::lock_guard<std::mutex> l(mu_);
+            quit_ = true;
+            gen_++;
+        }
+        cv_.notify_all();
+        for (auto &t : th_) t.join();
+    }
+    int size() const { return n_; }
+    void Run(const std::function<void(int)> &f) {
+        if (n_ == 1) { f(0); return; }
+        {
+            std::lock_guard<std::mutex> l(mu_);
+            job_ = &f;
+            pending_ = n_ - 1;
+            gen_++;
+        }
+        cv_.notify_all();
+        f(0);
+        std::unique_lock<std::mutex> l(mu_);
+        done_.wait(l, [this] { return pending_ == 0; });
+        job_ = nullptr;
+    }
+
+private:
+    void Loop(int w) {
+        unsigned long seen = 0;
+        for (;;) {
+            const std::function<void(int)> *f;
+            {
+                std::unique_lock<std::mutex> l(mu_);
+                cv_.wait(l, [&] { return gen_ != seen; });
+                seen = gen_;
+                if (quit_) return;
+                f = job_;
+            }
+            (*f)(w);
+            {
+                std::lock_guard<std::mutex> l(mu_);
+                if (--pending_ == 0) done_.notify_one();
+            }
+        }
+    }
+    int n_;
+    std::vector<std::thread> th_;
+    std::mutex mu_;
+    std::condition_variable cv_, done_;
+    const std::function<void(int)> *job_ = nullptr;
+    int pending_ = 0;
+    unsigned long gen_ = 0;
+    bool quit_ = false;
+};
+
 class ChainValidator {
 public:
-    ChainValidator(const std::vector<int> &devices, uint32_t script_flags, unsigned eh_n, unsigned eh_k)
-        : devs(devices), flags(script_flags), ehN(eh_n), ehK(eh_k) {}
+    // walk_threads: host threads for the UTXO passes (rounded down to a power of two, at most 16).  The table is split
+    // into that many shards by the top bits of the outpoint hash; during a pass every shard is touched by exactly one
+    // thread, so the passes need no locks.
+    ChainValidator(const std::vector<int> &devices, uint32_t script_flags, unsigned eh_n, unsigned eh_k, int walk_threads = 8)
+        : devs(devices), flags(script_flags), ehN(eh_n), ehK(eh_k), shardBits(0) {
+        while ((2 << shardBits) <= walk_threads && shardBits < 4) shardBits++;
+        for (int i = 0; i < (1 << shardBits); i++) shards.emplace_back(new CoinTable());
+        team.reset(new WorkerTeam(1 << shardBits));
+    }
+    ~ChainValidator() {
+        if (ahead.th.joinable()) ahead.th.join();
+    }
 
     bool Init(std::string &err) {
         if (devs.empty()) { err = "no device"; return false; }
@@ -169,17 +246,25 @@ public:
         OutPoint op;
         memcpy(op.b, txid, 32);
         memcpy(op.b + 32, &vout, 4);
-        utxo.insert(op, spk, len, amount);
+        ShardOf(op).insert(op, spk, len, amount);
     }
-    size_t UtxoSize() const { return utxo.size(); }
+    size_t UtxoSize() const {
+        size_t n = 0;
+        for (const auto &t : shards) n += t->size();
+        return n;
+    }
     size_t InputsChecked() const { return nInputs; }
 
-    // Returns true and updates the UTXO set, or false with `reason` (the reference's reject strings where one exists).
-    // seconds spent per phase since construction: header (Equihash + hash), framing scan, txids + Merkle, UTXO walk,
-    // script checks (GPU calls incl. copies)
+    // seconds since construction: [0] header (Equihash + hash), [1] framing scan on the connecting thread (0 when the
+    // scan ran ahead), [2] waiting for the txids after the lookups, [3] the UTXO passes, [4] waiting for the script
+    // checks after the inserts
     double phase[5] = {0, 0, 0, 0, 0};
+    double walk[4] = {0, 0, 0, 0}; // inside [3]: pass A, staging for the script call, pass B, pass C
 
-    bool ConnectBlock(const uint8_t *blk, size_t len, std::string &reason) {
+    // Returns true and updates the UTXO set, or false with `reason` (the reference's reject strings where one exists).
+    // `next` / `next_len` (optional): the block that will be connected after this one; its framing scan then runs on a
+    // helper thread while this block is being connected.  Those bytes must stay valid until that block is connected.
+    bool ConnectBlock(const uint8_t *blk, size_t len, std::string &reason, const uint8_t *next = nullptr, size_t next_len = 0) {
         const int dev0 = devs[0];
         auto now = [] { return std::chrono::steady_clock::now(); };
         auto secs = [](std::chrono::steady_clock::time_point a, std::chrono::steady_clock::time_point b) {
@@ -201,17 +286,19 @@ public:
         }
         auto t1 = now();
         phase[0] += secs(t0, t1);
-        // framing
-        const size_t max_tx = len / 60 + 2, max_in = len / 41 + 2;
-        tx_off.resize(max_tx + 1);
-        in_off.resize(max_in); in_tx.resize(max_in); in_n.resize(max_in);
-        long ntx = 0;
-        long nin = bcp_block_index_inputs(blk, len, 0, tx_off.data(), max_tx, in_off.data(), in_tx.data(), in_n.data(), max_in, &ntx);
+        // framing: taken from the scan-ahead slot when it holds this very block, else done now
+        if (ahead.th.joinable()) ahead.th.join();
+        if (ahead.blk == blk && ahead.len == len && ahead.valid) SwapScan(cur, ahead);
+        else cur.Run(blk, len, shardBits);
+        ahead.valid = false;
+        if (next) ScanAhead(next, next_len);
+        const long ntx = cur.ntx, nin = cur.nin, nout = cur.nout;
+        const std::vector<uint32_t> &tx_off = cur.tx_off, &in_off = cur.in_off, &in_tx = cur.in_tx, &in_n = cur.in_n;
         if (nin < 0 || ntx < 1) { reason = "bad-blk-framing"; return false; }
         auto t2 = now();
         phase[1] += secs(t1, t2);
-        // txids + Merkle root (CheckBlock, src/validation.cpp:3236-3252) on the device, from a helper thread, while
-        // this thread looks up the spent coins: the lookups need the previous outputs, not this block's txids
+        // txids + Merkle root (CheckBlock, src/validation.cpp:3236-3252) on the device, from a helper thread, while the
+        // team looks up the spent coins: the lookups need the previous outputs, not this block's txids
         txids.resize((size_t)ntx * 32);
         uint8_t root[32];
         int mutated = 0, rcTx = BCP_OK;
@@ -220,41 +307,53 @@ public:
             rcTx = bcp_gpu_sha256d_txids_merkle(dev0, blk, len, tx_off.data(), (size_t)ntx, txids.data(), root, &mutated);
             if (rcTx != BCP_OK) errTx = bcp_gpu_last_error();
         });
-        // Spent coins.  Everything is applied to the one table and journalled so that a rejected block can be rolled
-        // back.  Pass A takes the inputs in block order for as long as they are found in the table as it was before
-        // this block (the normal case: all of them); the first miss — an output created earlier in this block, or a
-        // missing coin — ends it at input `m`.
-        spk_cat.clear();
-        spk_off.assign(1, 0);
-        amounts.clear();
-        journalSpent.clear();
-        journalCreated.clear();
-        const size_t AHEAD = 16;
-        size_t m = 0;
-        for (; m < (size_t)nin; m++) {
-            if (m + AHEAD < (size_t)nin) {
-                OutPoint nx;
-                memcpy(nx.b, blk + in_off[m + AHEAD], 36);
-                utxo.prefetch(nx);
+        // Pass A, all shards in parallel: every input whose coin is in the table as it was BEFORE this block is staged
+        // (amount + scriptPubKey for the script checks) and removed.  What is not found is either created earlier in
+        // this block or missing; pass C settles that.
+        if (stage.size() < (size_t)nin) stage.resize((size_t)nin);
+        bigStore.clear();
+        spentUpTo = (size_t)nin;
+        createdUpTo = 0;
+        team->Run([&](int w) { PassA(w, blk, (size_t)nin); });
+        walk[0] += secs(t2, now());
+        size_t unresolved = 0;
+        for (size_t i = 0; i < (size_t)nin; i++) {
+            if (stage[i].state == ST_BIG) { // rare: a script too long for the staging slot; done here, on one thread
+                OutPoint op;
+                memcpy(op.b, blk + in_off[i], 36);
+                CoinTable &T = ShardOf(op);
+                CoinSlot *c = T.find(op);
+                if (!c) { // spent a moment ago by another input of this block
+                    stage[i].state = ST_MISS;
+                    unresolved++;
+                    continue;
+                }
+                stage[i].amount = c->amount;
+                stage[i].len = c->spk_len;
+                stage[i].big = (uint32_t)bigStore.size();
+                bigStore.emplace_back(CoinTable::script(*c), CoinTable::script(*c) + c->spk_len);
+                T.erase(c);
+            } else if (stage[i].state == ST_MISS) {
+                unresolved++;
             }
-            if (!Spend(blk + in_off[m])) break;
         }
         auto t3 = now();
         thTx.join();
         auto t3b = now();
         phase[3] += secs(t2, t3);
         phase[2] += secs(t3, t3b); // what the lookups did not hide
-        if (rcTx != BCP_OK) { Rollback(); reason = "device-error: " + errTx; return false; }
-        if (memcmp(root, blk + 36, 32) != 0) { Rollback(); reason = "bad-txnmrklroot"; return false; }
-        if (mutated) { Rollback(); reason = "bad-txns-duplicate"; return false; }
+        if (rcTx != BCP_OK) { Rollback(blk); reason = "device-error: " + errTx; return false; }
+        if (memcmp(root, blk + 36, 32) != 0) { Rollback(blk); reason = "bad-txnmrklroot"; return false; }
+        if (mutated) { Rollback(blk); reason = "bad-txns-duplicate"; return false; }
         // Script checks, sharded by input index range over the devices.  When pass A resolved every input they start
-        // now, from helper threads, and run while this thread inserts the block's outputs (pass B).
+        // now, from helper threads, and run while the team inserts the block's outputs (pass B).
         errs.assign((size_t)nin, 0);
         const size_t G = devs.size(), per = ((size_t)nin + G - 1) / G;
         std::vector<int> rc(G, BCP_OK);
         std::vector<std::string> msg(G);
         std::vector<std::thread> th;
         auto launchScripts = [&] {
+            BuildStaging((size_t)nin);
             for (size_t g = 0; g < G && nin > 0; g++) {
                 const size_t lo = std::min((size_t)nin, g * per), hi = std::min((size_t)nin, lo + per);
                 if (lo >= hi) continue;
@@ -267,27 +366,58 @@ public:
                 });
             }
         };
-        const bool overlapped = m == (size_t)nin;
+        const bool overlapped = unresolved == 0;
         if (overlapped) launchScripts();
-        // Pass B, transaction by transaction: the inputs pass A did not reach (they may spend outputs created earlier in
-        // this block, and only those), then the transaction's own outputs.
-        size_t i = m;
+        auto tb0 = now();
+        walk[1] += secs(t3b, tb0);
+        // Pass B, all shards in parallel: the block's outputs become coins.
+        createdUpTo = (size_t)nout;
+        team->Run([&](int w) { PassB(w, blk, (size_t)nout); });
+        auto tb1 = now();
+        walk[2] += secs(tb0, tb1);
+        // Pass C, only when pass A left inputs open: they may spend coins created EARLIER in this block (the creating
+        // transaction must come first, src/validation.cpp:2095 applies each transaction before the next is looked at) and
+        // each such coin only once.
         bool missing = false;
-        for (long t = 0; t < ntx && !missing; t++) {
-            if ((size_t)t + AHEAD < (size_t)ntx) { // where transaction t+AHEAD's first output will land
-                OutPoint nx;
-                memcpy(nx.b, &txids[((size_t)t + AHEAD) * 32], 32);
-                memset(nx.b + 32, 0, 4);
-                utxo.prefetch(nx);
+        if (unresolved) {
+            std::unordered_map<uint64_t, uint32_t> txIndex; // first 8 bytes of a txid -> transaction number (verified below)
+            txIndex.reserve((size_t)ntx * 2);
+            for (long t = 0; t < ntx; t++) {
+                uint64_t k;
+                memcpy(&k, &txids[(size_t)t * 32], 8);
+                txIndex.emplace(k, (uint32_t)t);
             }
-            for (; i < (size_t)nin && in_tx[i] == (uint32_t)t; i++)
-                if (!Spend(blk + in_off[i])) { missing = true; break; }
-            if (!missing) AddOutputs(blk, (uint32_t)t);
+            for (size_t i = 0; i < (size_t)nin && !missing; i++) {
+                if (stage[i].state != ST_MISS) continue;
+                OutPoint op;
+                memcpy(op.b, blk + in_off[i], 36);
+                uint64_t k;
+                memcpy(&k, op.b, 8);
+                auto it = txIndex.find(k);
+                CoinTable &T = ShardOf(op);
+                CoinSlot *c = T.find(op);
+                if (!c || it == txIndex.end() || memcmp(&txids[(size_t)it->second * 32], op.b, 32) != 0 || it->second >= in_tx[i]) {
+                    missing = true;
+                    break;
+                }
+                stage[i].amount = c->amount;
+                stage[i].len = c->spk_len;
+                if (c->spk_len <= STAGE_SPK) {
+                    memcpy(stage[i].spk, CoinTable::script(*c), c->spk_len);
+                    stage[i].state = ST_INBLOCK;
+                } else {
+                    stage[i].big = (uint32_t)bigStore.size();
+                    bigStore.emplace_back(CoinTable::script(*c), CoinTable::script(*c) + c->spk_len);
+                    stage[i].state = ST_INBLOCK_BIG;
+                }
+                T.erase(c);
+            }
         }
         auto t4 = now();
+        walk[3] += secs(tb1, t4);
         phase[3] += secs(t3b, t4);
         if (missing) { // only reachable when the scripts were not started
-            Rollback();
+            Rollback(blk);
             reason = "bad-txns-inputs-missingorspent";
             return false;
         }
@@ -295,20 +425,26 @@ public:
         for (auto &t : th) t.join();
         phase[4] += secs(t4, now()); // what pass B did not hide (everything when the passes could not overlap)
         for (size_t g = 0; g < G; g++)
-            if (rc[g] != BCP_OK) { Rollback(); reason = "device-error: " + msg[g]; return false; }
+            if (rc[g] != BCP_OK) { Rollback(blk); reason = "device-error: " + msg[g]; return false; }
         for (size_t k = 0; k < (size_t)nin; k++) {
-            if (errs[k] == 255) { Rollback(); reason = "script-not-in-fast-path (input " + std::to_string(k) + ")"; return false; }
+            if (errs[k] == 255) { Rollback(blk); reason = "script-not-in-fast-path (input " + std::to_string(k) + ")"; return false; }
             if (errs[k] != 0) { // ConnectBlock: "blk-bad-inputs" (src/validation.cpp:2124-2128)
-                Rollback();
+                Rollback(blk);
                 reason = "blk-bad-inputs (input " + std::to_string(k) + ", script error " + std::to_string(errs[k]) + ")";
                 return false;
             }
         }
         // commit: the table already holds the new state
         nInputs += (size_t)nin;
-        journalSpent.clear();
-        journalCreated.clear();
+        spentUpTo = createdUpTo = 0;
         return true;
+    }
+    //! Optional: start the framing scan of the block that will be connected next on a helper thread, before the first
+    //! ConnectBlock of a run (afterwards the `next` argument of ConnectBlock keeps the scans one block ahead).
+    void ScanAhead(const uint8_t *blk, size_t len) {
+        if (ahead.th.joinable()) ahead.th.join();
+        ahead.valid = false;
+        ahead.th = std::thread([this, blk, len] { ahead.Run(blk, len, shardBits); });
     }
     const uint8_t *LastBlockHash() const { return lastHash; }
     const std::vector<uint8_t> &LastScriptErrors() const { return errs; }
@@ -324,7 +460,15 @@ public:
             uint32_t sz;
             memcpy(&sz, data + pos + 4, 4);
             if (pos + 8 + sz > len) break;
-            if (!ConnectBlock(data + pos + 8, sz, reason)) { failed_index = n; return n; }
+            // the next block's framing scan runs on a helper thread while this block is being connected
+            const uint8_t *next = nullptr;
+            uint32_t nsz = 0;
+            const size_t nx = pos + 8 + (size_t)sz;
+            if (nx + 8 <= len && memcmp(data + nx, magic, 4) == 0) {
+                memcpy(&nsz, data + nx + 4, 4);
+                if (nx + 8 + nsz <= len) next = data + nx + 8;
+            }
+            if (!ConnectBlock(data + pos + 8, sz, reason, next, nsz)) { failed_index = n; return n; }
             pos += 8 + (size_t)sz;
             n++;
         }
@@ -332,44 +476,151 @@ public:
     }
 
 private:
-    // Looks up the coin an input spends, appends its scriptPubKey / amount to the staging arrays of the script checks,
-    // removes it from the table and journals it.  false: no such coin (already spent, or never there).
-    bool Spend(const uint8_t *outpoint36) {
-        OutPoint op;
-        memcpy(op.b, outpoint36, 36);
-        CoinSlot *c = utxo.find(op);
-        if (!c) return false;
-        const uint8_t *sp = CoinTable::script(*c);
-        spk_cat.insert(spk_cat.end(), sp, sp + c->spk_len);
-        spk_off.push_back((uint32_t)spk_cat.size());
-        amounts.push_back(c->amount);
-        utxo.erase(c);
-        journalSpent.push_back(op);
-        return true;
-    }
-    void AddOutputs(const uint8_t *blk, uint32_t t) {
-        // skip inputs to reach the outputs of transaction t
-        size_t pos = tx_off[t] + 4;
-        uint64_t nin = ReadCompact(blk, pos);
-        for (uint64_t k = 0; k < nin; k++) {
-            pos += 36;
-            uint64_t sl = ReadCompact(blk, pos);
-            pos += sl + 4;
+    struct Scan { // result of the framing scan of one block
+        std::vector<uint32_t> tx_off, tx_out_off, in_off, in_tx, in_n, out_off, out_tx, out_n;
+        std::vector<uint32_t> by_shard, shard_start; // input numbers grouped by table shard (block order inside a group)
+        long ntx = 0, nin = -1, nout = 0;
+        const uint8_t *blk = nullptr;
+        size_t len = 0;
+        bool valid = false;
+        std::thread th;
+        void Run(const uint8_t *b, size_t l, int shardBits) {
+            const size_t max_tx = l / 60 + 2, max_in = l / 41 + 2, max_out = l / 9 + 2;
+            if (tx_off.size() < max_tx + 1) { tx_off.resize(max_tx + 1); tx_out_off.resize(max_tx + 1); }
+            if (in_off.size() < max_in) { in_off.resize(max_in); in_tx.resize(max_in); in_n.resize(max_in); }
+            if (out_off.size() < max_out) { out_off.resize(max_out); out_tx.resize(max_out); out_n.resize(max_out); }
+            ntx = nout = 0;
+            nin = bcp_block_index_full(b, l, 0, tx_off.data(), tx_out_off.data(), max_tx, in_off.data(), in_tx.data(), in_n.data(),
+                                       max_in, &ntx, out_off.data(), out_tx.data(), out_n.data(), max_out, &nout);
+            // counting sort of the inputs by shard, here (on the scan-ahead thread) so that each worker of pass A only
+            // ever touches its own inputs
+            const size_t S = (size_t)1 << shardBits;
+            shard_start.assign(S + 1, 0);
+            if (nin > 0) {
+                by_shard.resize((size_t)nin);
+                std::vector<uint8_t> sh((size_t)nin);
+                for (long i = 0; i < nin; i++) {
+                    OutPoint op;
+                    memcpy(op.b, b + in_off[(size_t)i], 36);
+                    sh[(size_t)i] = shardBits ? (uint8_t)(OutPointHash()(op) >> (64 - shardBits)) : 0;
+                    shard_start[sh[(size_t)i] + 1]++;
+                }
+                for (size_t k = 0; k < S; k++) shard_start[k + 1] += shard_start[k];
+                std::vector<uint32_t> fill(shard_start.begin(), shard_start.end() - 1);
+                for (long i = 0; i < nin; i++) by_shard[fill[sh[(size_t)i]]++] = (uint32_t)i;
+            }
+            blk = b;
+            len = l;
+            valid = true;
         }
-        uint64_t nout = ReadCompact(blk, pos);
-        for (uint64_t v = 0; v < nout; v++) {
+    };
+    static void SwapScan(Scan &a, Scan &b) {
+        a.tx_off.swap(b.tx_off); a.tx_out_off.swap(b.tx_out_off); a.in_off.swap(b.in_off); a.in_tx.swap(b.in_tx); a.in_n.swap(b.in_n);
+        a.out_off.swap(b.out_off); a.out_tx.swap(b.out_tx); a.out_n.swap(b.out_n);
+        a.by_shard.swap(b.by_shard); a.shard_start.swap(b.shard_start);
+        std::swap(a.ntx, b.ntx); std::swap(a.nin, b.nin); std::swap(a.nout, b.nout); std::swap(a.blk, b.blk); std::swap(a.len, b.len);
+        std::swap(a.valid, b.valid);
+    }
+    Scan cur, ahead;
+
+    // what pass A / C found for one input; 128 bytes so that two threads never write the same cache line
+    enum : uint8_t { ST_MISS = 0, ST_TAKEN = 1, ST_BIG = 2, ST_INBLOCK = 3, ST_INBLOCK_BIG = 4 };
+    static const size_t STAGE_SPK = 64;
+    struct alignas(128) Staged {
+        int64_t amount;
+        uint32_t len, big;
+        uint8_t state;
+        uint8_t spk[STAGE_SPK];
+    };
+
+    int ShardIndex(const OutPoint &op) const { return shardBits ? (int)(OutPointHash()(op) >> (64 - shardBits)) : 0; }
+    CoinTable &ShardOf(const OutPoint &op) { return *shards[(size_t)ShardIndex(op)]; }
+
+    // One worker's share of pass A: the inputs whose outpoint hashes to its shard, in block order, with the table slots
+    // of the next few prefetched while the current one is handled.
+    void PassA(int w, const uint8_t *blk, size_t nin) {
+        CoinTable &T = *shards[(size_t)w];
+        const size_t RING = 8;
+        size_t ring[RING], head = 0, count = 0;
+        auto take = [&](size_t i) {
+            OutPoint op;
+            memcpy(op.b, blk + cur.in_off[i], 36);
+            Staged &s = stage[i];
+            CoinSlot *c = T.find(op);
+            if (!c) { s.state = ST_MISS; return; }
+            if (c->spk_len > STAGE_SPK) { s.state = ST_BIG; return; } // left in the table for the connecting thread
+            s.amount = c->amount;
+            s.len = c->spk_len;
+            memcpy(s.spk, CoinTable::script(*c), c->spk_len);
+            s.state = ST_TAKEN;
+            T.erase(c);
+        };
+        (void)nin;
+        for (size_t q = cur.shard_start[(size_t)w]; q < cur.shard_start[(size_t)w + 1]; q++) {
+            const size_t i = cur.by_shard[q];
+            OutPoint op;
+            memcpy(op.b, blk + cur.in_off[i], 36);
+            T.prefetch(op);
+            if (count == RING) {
+                take(ring[head]);
+                ring[head] = i;
+                head = (head + 1) % RING;
+            } else {
+                ring[(head + count++) % RING] = i;
+            }
+        }
+        for (size_t k = 0; k < count; k++) take(ring[(head + k) % RING]);
+    }
+    // One worker's share of pass B: the outputs whose outpoint hashes to its shard.
+    void PassB(int w, const uint8_t *blk, size_t nout) {
+        CoinTable &T = *shards[(size_t)w];
+        const size_t RING = 8;
+        size_t ring[RING], head = 0, count = 0;
+        auto put = [&](size_t o) {
+            OutPoint op;
+            memcpy(op.b, &txids[(size_t)cur.out_tx[o] * 32], 32);
+            memcpy(op.b + 32, &cur.out_n[o], 4);
+            size_t pos = cur.out_off[o];
             int64_t amt;
             memcpy(&amt, blk + pos, 8);
             pos += 8;
-            uint64_t sl = ReadCompact(blk, pos);
+            const uint64_t sl = ReadCompact(blk, pos);
+            T.insert(op, blk + pos, sl, amt);
+        };
+        for (size_t o = 0; o < nout; o++) {
             OutPoint op;
-            memcpy(op.b, &txids[(size_t)t * 32], 32);
-            uint32_t vv = (uint32_t)v;
-            memcpy(op.b + 32, &vv, 4);
-            utxo.insert(op, blk + pos, sl, amt);
-            journalCreated.push_back(op);
-            pos += sl;
+            memcpy(op.b, &txids[(size_t)cur.out_tx[o] * 32], 8); // the hash reads the first 8 bytes and the index only
+            memcpy(op.b + 32, &cur.out_n[o], 4);
+            if (ShardIndex(op) != w) continue;
+            memcpy(op.b + 8, &txids[(size_t)cur.out_tx[o] * 32 + 8], 24);
+            T.prefetch(op);
+            if (count == RING) {
+                put(ring[head]);
+                ring[head] = o;
+                head = (head + 1) % RING;
+            } else {
+                ring[(head + count++) % RING] = o;
+            }
         }
+        for (size_t k = 0; k < count; k++) put(ring[(head + k) % RING]);
+    }
+    // staging records -> the concatenated scriptPubKeys / offsets / amounts the script-check call takes
+    void BuildStaging(size_t nin) {
+        spk_off.resize(nin + 1);
+        amounts.resize(nin);
+        size_t total = 0;
+        for (size_t i = 0; i < nin; i++) total += stage[i].len;
+        spk_cat.resize(total + 1);
+        uint32_t o = 0;
+        for (size_t i = 0; i < nin; i++) {
+            const Staged &s = stage[i];
+            spk_off[i] = o;
+            amounts[i] = s.amount;
+            const uint8_t *src = (s.state == ST_BIG || s.state == ST_INBLOCK_BIG) ? bigStore[s.big].data() : s.spk;
+            memcpy(&spk_cat[o], src, s.len);
+            o += s.len;
+        }
+        spk_off[nin] = o;
     }
     static uint64_t ReadCompact(const uint8_t *p, size_t &pos) { // already validated by the framing scan
         uint8_t c = p[pos++];
@@ -380,26 +631,38 @@ private:
         pos += nb;
         return v;
     }
-    // Undo a partially applied block: drop what it created, then put back what it spent.  The spent coins are
-    // re-inserted from the block's own staging arrays (outpoint journal + the scriptPubKey / amount arrays that were
-    // built for the GPU call), because a coin created by this block may have reused a spent coin's slot.
-    void Rollback() {
-        for (const OutPoint &op : journalCreated) {
-            CoinSlot *c = utxo.find(op);
-            if (c) utxo.erase(c);
+    // Undo a partially applied block (one thread; a rejected block is the rare case): drop the coins it created, then
+    // put back the coins it spent that existed before it — from the staging records, which still hold them.
+    void Rollback(const uint8_t *blk) {
+        for (size_t o = 0; o < createdUpTo; o++) {
+            OutPoint op;
+            memcpy(op.b, &txids[(size_t)cur.out_tx[o] * 32], 32);
+            memcpy(op.b + 32, &cur.out_n[o], 4);
+            CoinTable &T = ShardOf(op);
+            CoinSlot *c = T.find(op);
+            if (c) T.erase(c);
         }
-        for (size_t i = 0; i < journalSpent.size(); i++)
-            utxo.insert(journalSpent[i], &spk_cat[spk_off[i]], spk_off[i + 1] - spk_off[i], amounts[i]);
-        journalSpent.clear();
-        journalCreated.clear();
+        for (size_t i = 0; i < spentUpTo; i++) {
+            const Staged &s = stage[i];
+            if (s.state != ST_TAKEN && s.state != ST_BIG) continue; // misses, and coins this block itself had created
+            OutPoint op;
+            memcpy(op.b, blk + cur.in_off[i], 36);
+            const uint8_t *src = s.state == ST_BIG ? bigStore[s.big].data() : s.spk;
+            ShardOf(op).insert(op, src, s.len, s.amount);
+        }
+        spentUpTo = createdUpTo = 0;
     }
 
     std::vector<int> devs;
     uint32_t flags;
     unsigned ehN, ehK;
-    CoinTable utxo;
-    std::vector<OutPoint> journalSpent, journalCreated;
-    std::vector<uint32_t> tx_off, in_off, in_tx, in_n, spk_off;
+    int shardBits;
+    std::vector<std::unique_ptr<CoinTable>> shards;
+    std::unique_ptr<WorkerTeam> team;
+    std::vector<Staged> stage;
+    std::vector<std::vector<uint8_t>> bigStore;
+    size_t spentUpTo = 0, createdUpTo = 0; // how far the current block has been applied (for Rollback)
+    std::vector<uint32_t> spk_off;
     std::vector<uint8_t> txids, spk_cat, errs;
     std::vector<int64_t> amounts;
     uint8_t lastHash[32] = {0};

@@ -369,11 +369,15 @@ def equihash_solve_48_5(input140):
     return sorted(set(sols))
 
 
-def synthetic_chain(nblocks=6, ntx=20, nkeys=8, equihash=True, corrupt=None):
+def synthetic_chain(nblocks=6, ntx=20, nkeys=8, equihash=True, corrupt=None, inblock=()):
     """A chain of post-fork blocks with REAL UTXO dependencies: block b's transaction j spends
     output 0 of block b-1's transaction j; block 0 spends seeded "prev" coins.  With equihash=True every header
     carries a valid regtest (48,5) solution.  corrupt = (block, kind) with kind in {"bad_sig", "double_spend",
-    "bad_merkle", "missing_input", "bad_equihash"} damages exactly one block.
+    "bad_merkle", "missing_input", "bad_equihash", "inblock_reversed", "inblock_double"} damages exactly one block.
+    inblock = positions j (>= 1) whose transaction spends output 0 of transaction j-1 of the SAME block in every block
+    (the coin it would have spent stays unspent and is handed to the next block's transaction j-1 instead);
+    "inblock_reversed" makes transaction 5 spend the output of transaction 6 (created AFTER it), "inblock_double" makes
+    transactions 6 and 7 both spend the output of transaction 5.
     Returns (list of block bytes, list of seed coins (txid, vout, spk, amount), per-block (spk list, amounts) of the
     coins each block's inputs were built to spend)."""
     o = po.oracle()
@@ -389,18 +393,30 @@ def synthetic_chain(nblocks=6, ntx=20, nkeys=8, equihash=True, corrupt=None):
         prev_out.append((txid, 0, j % nkeys, amount))
     blocks, prevs = [], []
     for b in range(nblocks):
-        prevs.append(([spks[p[2]] for p in prev_out], [p[3] for p in prev_out]))
         cb = (2).to_bytes(4, "little") + b"\x01" + bytes(32) + b"\xff\xff\xff\xff" + b"\x04" + (700000 + b).to_bytes(4, "little")
         cb += b"\xff\xff\xff\xff" + b"\x01" + (1250000000).to_bytes(8, "little") + bytes([25]) + spks[0] + bytes(4)
         txs = [cb]
         new_out = []
         kind = corrupt[1] if corrupt and corrupt[0] == b else None
-        for j in range(ntx):
+        order = list(range(ntx))
+        if kind == "inblock_reversed":
+            order[5], order[6] = 6, 5  # build transaction 6 first so that 5 can refer to it
+        built = {}
+        for j in order:
             txid, vout, kj, amt_ = prev_out[j]
             if kind == "double_spend" and j == 1:
                 txid, vout, kj, amt_ = prev_out[0]
             if kind == "missing_input" and j == 2:
                 txid = hashlib.sha256(b"nowhere").digest()
+            src = None
+            if j in inblock and j >= 1:
+                src = j - 1
+            if kind == "inblock_reversed" and j == 5:
+                src = 6
+            if kind == "inblock_double" and j in (6, 7):
+                src = 5
+            if src is not None:
+                txid, vout, kj, amt_ = built[src]
             nk = (kj + 1) % nkeys
             out = (amt_ - 1000).to_bytes(8, "little") + bytes([25]) + spks[nk]
 
@@ -414,8 +430,15 @@ def synthetic_chain(nblocks=6, ntx=20, nkeys=8, equihash=True, corrupt=None):
                 r_ ^= 2
             der = _der(r_, s_) + b"\x41"
             tx = build(bytes([len(der)]) + der + bytes([33]) + pubs[kj])
-            txs.append(tx)
-            new_out.append((o.sha256d(tx), 0, nk, amt_ - 1000))
+            built[j] = (o.sha256d(tx), 0, nk, amt_ - 1000)
+            built[("tx", j)] = tx
+            built[("prev", j)] = (spks[kj], amt_)
+            if src is not None and j in inblock:
+                built[("keep", src)] = prev_out[j]  # the coin this transaction did not spend goes to the next block
+        for j in range(ntx):
+            txs.append(built[("tx", j)])
+            new_out.append(built.get(("keep", j), built[j]))
+        prevs.append(([built[("prev", j)][0] for j in range(ntx)], [built[("prev", j)][1] for j in range(ntx)]))
         root, _ = o.merkle_root(b"".join(o.sha256d(t) for t in txs))
         if kind == "bad_merkle":
             root = bytes([root[0] ^ 1]) + root[1:]

@@ -157,3 +157,33 @@ def test_window_rejects_malformed_block_and_wrong_counts(engine):
         other = synth.synthetic_block(20, True, nkeys=4, with_prevouts=True)
         a2, c2, o2, m2, n2 = _window([good, other])
         engine.blocks_connect_p2pkh(a2, c2, o2, m2, n2[::-1], synth.POSTFORK_FLAGS)
+
+
+def test_two_lanes_of_one_gpu_run_concurrently_and_agree(engine, oracle):
+    """BCP_DEVICE_LANE: a second context on the same GPU; both lanes validate different blocks from two host threads at
+    the same time and each returns what the oracle says."""
+    import threading
+
+    import bitcoincashplus_b200 as bcp
+
+    lane1 = bcp.Engine(0, lane=1)
+    blocks = [synth.synthetic_block(600 + 50 * i, True, nkeys=16, with_prevouts=True, bad_inputs=(17 * i + 3,)) for i in range(4)]
+    want = [oracle.block_script_errors(b, False, s, a, synth.POSTFORK_FLAGS, NT) for b, s, a in blocks]
+    got = {}
+
+    def run(e, ids):
+        for _ in range(5):
+            for i in ids:
+                b, s, a = blocks[i]
+                got[(e.device, i)] = e.block_connect_p2pkh(b, s, a, synth.POSTFORK_FLAGS)
+
+    th = [threading.Thread(target=run, args=(engine, [0, 1, 2, 3])), threading.Thread(target=run, args=(lane1, [3, 2, 1, 0]))]
+    for t in th:
+        t.start()
+    for t in th:
+        t.join()
+    for (dev, i), r in got.items():
+        assert (r["script_err"] == want[i]).all() and r["root"] == blocks[i][0][36:68], (dev, i)
+    assert len(got) == 8
+    with pytest.raises(bcp.BcpError):
+        bcp.Engine(0, lane=9)

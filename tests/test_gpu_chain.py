@@ -17,6 +17,8 @@ def chain_lib():
     L = C.CDLL(os.path.join(ROOT, "bitcoincashplus_b200", "libbcp_chain.so"))
     L.bcp_chain_new.restype = C.c_void_p
     L.bcp_chain_new.argtypes = [C.POINTER(C.c_int), C.c_int, C.c_uint32, C.c_uint, C.c_uint, C.c_char_p, C.c_size_t]
+    L.bcp_chain_new_threads.restype = C.c_void_p
+    L.bcp_chain_new_threads.argtypes = [C.POINTER(C.c_int), C.c_int, C.c_uint32, C.c_uint, C.c_uint, C.c_int, C.c_char_p, C.c_size_t]
     L.bcp_chain_free.argtypes = [C.c_void_p]
     L.bcp_chain_add_coin.argtypes = [C.c_void_p, C.c_char_p, C.c_uint32, C.c_char_p, C.c_size_t, C.c_int64]
     L.bcp_chain_utxo_size.restype = C.c_size_t
@@ -30,10 +32,13 @@ def chain_lib():
     return L
 
 
-def new_chain(L, seeds, devices=(0,), eh=(48, 5)):
+def new_chain(L, seeds, devices=(0,), eh=(48, 5), walk_threads=None):
     devs = (C.c_int * len(devices))(*devices)
     err = C.create_string_buffer(256)
-    h = L.bcp_chain_new(devs, len(devices), synth.POSTFORK_FLAGS, eh[0], eh[1], err, 256)
+    if walk_threads is None:
+        h = L.bcp_chain_new(devs, len(devices), synth.POSTFORK_FLAGS, eh[0], eh[1], err, 256)
+    else:
+        h = L.bcp_chain_new_threads(devs, len(devices), synth.POSTFORK_FLAGS, eh[0], eh[1], walk_threads, err, 256)
     assert h, err.value
     for txid, vout, spk, amount in seeds:
         L.bcp_chain_add_coin(h, txid, vout, spk, len(spk), amount)
@@ -93,3 +98,55 @@ def test_chain_shards_inputs_over_two_devices_when_present():
     res = [L.bcp_chain_connect_block(h, b, len(b), reason, 256) for b in blocks[:3]]
     assert res == [1, 1, 0] and reason.value.startswith(b"blk-bad-inputs (input 3")
     L.bcp_chain_free(h)
+
+
+def test_chain_in_block_spends_and_their_failure_modes(oracle):
+    """Transactions that spend outputs created earlier in the SAME block (chains of them), over several blocks; then the
+    two ways this can go wrong: spending an output of a LATER transaction, and spending an in-block output twice.  After a
+    rejection the UTXO set is exactly what it was, so the undamaged version of the same block still connects."""
+    L = chain_lib()
+    inb = (2, 7, 8, 9, 15)
+    blocks, seeds, prevs = synth.synthetic_chain(4, 20, inblock=inb)
+    for b, (spk, amt) in zip(blocks, prevs):
+        assert not oracle.block_script_errors(b, False, spk, amt, synth.POSTFORK_FLAGS, os.cpu_count() or 1).any()
+    reason = C.create_string_buffer(256)
+    for threads in (1, 8):
+        h = new_chain(L, seeds, walk_threads=threads)
+        for i, b in enumerate(blocks):
+            assert L.bcp_chain_connect_block(h, b, len(b), reason, 256) == 1, (threads, i, reason.value)
+            assert L.bcp_chain_utxo_size(h) == 20 + (i + 1)
+        L.bcp_chain_free(h)
+    for kind in ("inblock_reversed", "inblock_double"):
+        bad, seeds2, _ = synth.synthetic_chain(3, 20, corrupt=(1, kind))
+        good, _, _ = synth.synthetic_chain(3, 20)
+        assert bad[0] == good[0] and bad[1] != good[1]
+        for threads in (1, 4):
+            h = new_chain(L, seeds2, walk_threads=threads)
+            assert L.bcp_chain_connect_block(h, bad[0], len(bad[0]), reason, 256) == 1
+            assert L.bcp_chain_connect_block(h, bad[1], len(bad[1]), reason, 256) == 0
+            assert reason.value == b"bad-txns-inputs-missingorspent", (kind, reason.value)
+            assert L.bcp_chain_utxo_size(h) == 20 + 1
+            assert L.bcp_chain_connect_block(h, good[1], len(good[1]), reason, 256) == 1, (kind, reason.value)
+            assert L.bcp_chain_connect_block(h, good[2], len(good[2]), reason, 256) == 1, (kind, reason.value)
+            assert L.bcp_chain_utxo_size(h) == 20 + 3
+            L.bcp_chain_free(h)
+
+
+def test_chain_rollback_restores_coins_with_long_scripts():
+    """Coins whose scriptPubKey does not fit the staging slot (> 64 bytes) take the one-thread path; a block spending one
+    is refused by the P2PKH fast path (script-not-in-fast-path), and the rollback must put every coin back, long ones
+    included — shown by the same block failing the same way again and by the count."""
+    L = chain_lib()
+    blocks, seeds, _ = synth.synthetic_chain(2, 16)
+    long_spk = bytes([0x6a, 0x4c, 100]) + bytes(100)  # OP_RETURN-style, 103 bytes
+    seeds = list(seeds)
+    seeds[4] = (seeds[4][0], seeds[4][1], long_spk, seeds[4][3])
+    seeds[9] = (seeds[9][0], seeds[9][1], long_spk + b"\x00", seeds[9][3])
+    reason = C.create_string_buffer(256)
+    for threads in (1, 8):
+        h = new_chain(L, seeds, walk_threads=threads)
+        for _ in range(2):
+            assert L.bcp_chain_connect_block(h, blocks[0], len(blocks[0]), reason, 256) == 0
+            assert reason.value.startswith(b"script-not-in-fast-path (input 4)"), reason.value
+            assert L.bcp_chain_utxo_size(h) == 16
+        L.bcp_chain_free(h)
