@@ -167,6 +167,41 @@ def block_bench(eng, args, bcp, sync=None):
     return out
 
 
+def queue_dropin_bench(args):
+    """Level B1 measured with the reference's own interpreter: the 8 MB block's inputs as CScriptCheck-shaped closures
+    calling the reference's VerifyScript, through this project's CCheckQueue drop-in on all host threads; signatures
+    recorded and verified on the GPU in Wait() ("gpu") vs the reference's CPubKey::Verify in the same queue ("cpu").
+    The binary is oracle/_ref/bench_queue_ref (tests/cpp/bench_queue_ref.cpp, built where /root/reference exists)."""
+    import subprocess
+    import tempfile
+
+    import numpy as np
+    import synth
+
+    exe = os.path.join(ROOT, "oracle", "_ref", "bench_queue_ref")
+    if not os.path.exists(exe):
+        return {"unavailable": "oracle/_ref/bench_queue_ref not built (reference sources absent at build time)"}
+    blk, spk, amt = synth.synthetic_block(args.block_txs, True, with_prevouts=True)
+    off = np.zeros(len(spk) + 1, dtype=np.uint32)
+    off[1:] = np.cumsum([len(x) for x in spk])
+    threads = os.cpu_count() or 1
+    with tempfile.NamedTemporaryFile(suffix=".bin", delete=False) as f:
+        f.write(len(blk).to_bytes(8, "little") + blk + len(spk).to_bytes(8, "little") + off.tobytes() + b"".join(spk)
+                + np.asarray(amt, dtype=np.int64).tobytes())
+        path = f.name
+    try:
+        out = subprocess.run([exe, path, str(threads), "3"], capture_output=True, text=True, timeout=600)
+    finally:
+        os.unlink(path)
+    if out.returncode != 0:
+        return {"error": (out.stdout + out.stderr)[-300:]}
+    r = json.loads(out.stdout.strip().splitlines()[-1])
+    r["timed"] = ("ConnectBlock's check loop per block: PrecomputedTransactionData per tx, one closure per input through "
+                  "CCheckQueueControl::Add, Wait(); best of 3 after a warm-up; host interpreter + sighash on %d threads in both "
+                  "arms" % threads)
+    return r
+
+
 def window_bench(eng, args, bcp, sync=None, W=8):
     """Throughput form of the 8 MB block measurement (reindex / initial block download, blocks at hand): W blocks per call
     through bcp_gpu_blocks_connect_p2pkh — one pass of the per-input kernels over the union of the window's inputs.
@@ -551,6 +586,7 @@ def main():
     if not args.no_block:
         line["block8mb"] = blk_section
         line["block8mb_window"] = win_section
+        line["checkqueue_dropin"] = queue_dropin_bench(args)
         line["equihash10k"] = equihash_bench(eng)
         if args.chain_blocks > 0:
             line["chain"] = chain_bench(args, list(range(world)))

@@ -210,6 +210,10 @@ public:
 
     //! Wait until all queued checks are evaluated, run the deferred signature batch, return the AND, reset.
     bool Wait() {
+        {
+            std::lock_guard<std::mutex> lock(mtx);
+            if (!pending.empty()) cvWorker.notify_all();
+        }
         Run(true);
         std::vector<std::unique_ptr<Lane>> ls;
         bool hostOk;
@@ -232,8 +236,15 @@ public:
             check.swap(pending.back());
         }
         nOutstanding += (unsigned int)vChecks.size();
-        if (vChecks.size() == 1) cvWorker.notify_one();
-        else if (vChecks.size() > 1) cvWorker.notify_all();
+        // Workers are woken only when a batch worth of work has piled up (the reference wakes one per Add, :152-155).
+        // With the signature arithmetic deferred a check takes a few microseconds — less than waking a thread — and
+        // ConnectBlock adds one transaction at a time; waking per Add made sixteen threads fight over the mutex and
+        // slowed the producer 3x.  Nothing is lost by waiting: under a backlog every further Add wakes one more worker,
+        // and Wait() wakes everybody and joins the work itself.
+        if (pending.size() >= nBatchSize) {
+            if (vChecks.size() > nBatchSize) cvWorker.notify_all();
+            else cvWorker.notify_one();
+        }
     }
 
     bool IsIdle() {

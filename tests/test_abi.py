@@ -108,3 +108,74 @@ def test_block_index_matches_oracle(oracle):
     assert n == 1557 and (off == ooff).all() and off[-1] == len(raw)
     with pytest.raises(bcp.BcpError):
         bcp.block_index(raw[:5000], legacy_header=True)
+
+
+def _py_scan(blk, legacy):
+    """independent Python parse of a block: per-tx offsets, output-count offsets, flat non-coinbase inputs and outputs"""
+    def cs(pos):
+        c = blk[pos]
+        if c < 253:
+            return c, pos + 1
+        nb = {253: 2, 254: 4, 255: 8}[c]
+        return int.from_bytes(blk[pos + 1:pos + 1 + nb], "little"), pos + 1 + nb
+    pos = 80 if legacy else 140
+    if not legacy:
+        n, pos = cs(pos)
+        pos += n
+    ntx, pos = cs(pos)
+    tx_off, tx_out, ins, outs = [], [], [], []
+    for t in range(ntx):
+        tx_off.append(pos)
+        pos += 4
+        nin, pos = cs(pos)
+        cb = nin == 1 and blk[pos:pos + 32] == bytes(32) and blk[pos + 32:pos + 36] == b"\xff" * 4
+        for i in range(nin):
+            if not cb:
+                ins.append((pos, t, i))
+            pos += 36
+            sl, pos = cs(pos)
+            pos += sl + 4
+        tx_out.append(pos)
+        nout, pos = cs(pos)
+        for v in range(nout):
+            outs.append((pos, t, v))
+            pos += 8
+            sl, pos = cs(pos)
+            pos += sl
+        pos += 4
+    tx_off.append(pos)
+    return tx_off, tx_out, ins, outs
+
+
+def test_block_index_full_lists_inputs_and_outputs():
+    """bcp_block_index_full (host-side framing scan with the flat input and output lists) against an independent Python
+    parse: the reference's own bench block (legacy header, 1,557 transactions of every shape) and synthetic blocks."""
+    import ctypes as C
+
+    import bitcoincashplus_b200 as bcp
+    import synth
+
+    L = bcp.lib()
+    raw = open(os.path.join(ROOT, "tests", "golden", "block413567.raw"), "rb").read()
+    cases = [(raw, True), (synth.synthetic_block(ntx=40, sign=False), False), (synth.synthetic_block_multi(60, seed=3)[0], False),
+             (synth.synthetic_block(0, True), False)]
+    for blk, legacy in cases:
+        tx_off, tx_out, ins, outs = _py_scan(blk, legacy)
+        mt, mi, mo = len(blk) // 60 + 2, len(blk) // 41 + 2, len(blk) // 9 + 2
+        a = {k: np.zeros(n, dtype=np.uint32) for k, n in (("tx", mt + 1), ("txo", mt + 1), ("io", mi), ("it", mi), ("in", mi),
+                                                          ("oo", mo), ("ot", mo), ("on", mo))}
+        ntx, nout = C.c_long(0), C.c_long(0)
+        nin = L.bcp_block_index_full(blk, len(blk), int(legacy), a["tx"].ctypes.data, a["txo"].ctypes.data, mt, a["io"].ctypes.data,
+                                     a["it"].ctypes.data, a["in"].ctypes.data, mi, C.byref(ntx), a["oo"].ctypes.data,
+                                     a["ot"].ctypes.data, a["on"].ctypes.data, mo, C.byref(nout))
+        assert (nin, ntx.value, nout.value) == (len(ins), len(tx_off) - 1, len(outs))
+        assert list(a["tx"][:ntx.value + 1]) == tx_off and list(a["txo"][:ntx.value]) == tx_out
+        assert list(zip(a["io"][:nin], a["it"][:nin], a["in"][:nin])) == ins
+        assert list(zip(a["oo"][:nout.value], a["ot"][:nout.value], a["on"][:nout.value])) == outs
+        # capacity error for the outputs, and the optional arrays may be absent
+        if len(outs) > 1:
+            assert L.bcp_block_index_full(blk, len(blk), int(legacy), a["tx"].ctypes.data, None, mt, a["io"].ctypes.data,
+                                          a["it"].ctypes.data, a["in"].ctypes.data, mi, C.byref(ntx), a["oo"].ctypes.data,
+                                          a["ot"].ctypes.data, a["on"].ctypes.data, len(outs) - 1, C.byref(nout)) == -2
+        assert L.bcp_block_index_full(blk, len(blk), int(legacy), a["tx"].ctypes.data, None, mt, a["io"].ctypes.data,
+                                      a["it"].ctypes.data, a["in"].ctypes.data, mi, C.byref(ntx), None, None, None, 0, None) == len(ins)
