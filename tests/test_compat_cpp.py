@@ -49,3 +49,18 @@ def test_secp256k1_api_and_recording_queue_gpu(tmp_path):
     out = subprocess.run([EXE, "gpu", str(path)], capture_output=True, text=True, timeout=300)
     assert out.returncode == 0, out.stdout + out.stderr
     assert "gpu ok" in out.stdout
+
+
+def test_cointable_and_worker_team_cpu():
+    """bcp::CoinTable (backward-shift deletion, growth, long scripts) against std::map over 800,000 random operations,
+    and bcp::WorkerTeam; pure host code, no GPU call."""
+    exe = os.path.join(ROOT, "tests", "cpp", "test_cointable")
+    src = os.path.join(ROOT, "tests", "cpp", "test_cointable.cpp")
+    hdr = os.path.join(ROOT, "include", "compat", "bcp_chain.h")
+    if not os.path.exists(exe) or os.path.getmtime(exe) < max(os.path.getmtime(src), os.path.getmtime(hdr)):
+        subprocess.check_call(["g++", "-O2", "-std=c++17", "-I" + os.path.join(ROOT, "include"), "-o", exe, src,
+                               "-L" + os.path.join(ROOT, "bitcoincashplus_b200"), "-lbcp_b200",
+                               "-Wl,-rpath," + os.path.join(ROOT, "bitcoincashplus_b200"), "-lpthread"])
+    out = subprocess.run([exe], capture_output=True, text=True, timeout=300)
+    assert out.returncode == 0, out.stdout + out.stderr
+    assert "cointable ok" in out.stdout
