@@ -324,32 +324,30 @@ def chain_bench(args, devices):
     for txid, vout, spk, amount in seeds:
         L.bcp_chain_add_coin(h, txid, vout, spk, len(spk), amount)
     reason = C.create_string_buffer(256)
-    # the block bytes live in pinned host memory, as a reader of blk*.dat would arrange
+    # the blocks live in ONE pinned buffer in blk*.dat framing (magic | size | block), as the import loop of -reindex reads
+    # them (LoadExternalBlockFile, src/validation.cpp:4486-4516); block 0 is connected separately as the warm-up
     import bitcoincashplus_b200 as bcp
     G = bcp.lib()
+    magic = bytes.fromhex("e48f1d1c")
+    framed = b"".join(magic + len(b).to_bytes(4, "little") + b for b in blocks[1:])
+    p0 = G.bcp_gpu_host_alloc(len(blocks[0]))
+    C.memmove(p0, blocks[0], len(blocks[0]))
+    pf = G.bcp_gpu_host_alloc(len(framed))
+    C.memmove(pf, framed, len(framed))
     L.bcp_chain_connect_block.argtypes = [C.c_void_p, C.c_void_p, C.c_size_t, C.c_char_p, C.c_size_t]
-    pinned = []
-    for b in blocks:
-        p = G.bcp_gpu_host_alloc(len(b))
-        C.memmove(p, b, len(b))
-        pinned.append((p, len(b)))
-    per_block = []
-    # block 0 is the warm-up (device staging buffers are allocated on first use); the timed region is blocks 1..nb-1
-    ok = L.bcp_chain_connect_block(h, pinned[0][0], pinned[0][1], reason, 256)
+    ok = L.bcp_chain_connect_block(h, p0, len(blocks[0]), reason, 256)
     assert ok == 1, reason.value
     ph0 = (C.c_double * 5)()
     L.bcp_chain_phase_seconds.argtypes = [C.c_void_p, C.POINTER(C.c_double)]
     L.bcp_chain_phase_seconds(h, ph0)
     nb -= 1
+    L.bcp_chain_connect_file.restype = C.c_long
+    L.bcp_chain_connect_file.argtypes = [C.c_void_p, C.c_void_p, C.c_size_t, C.c_char_p, C.c_char_p, C.c_size_t, C.POINTER(C.c_long)]
+    failed = C.c_long(-1)
     t0 = time.perf_counter()
-    L.bcp_chain_connect_block_hint.argtypes = [C.c_void_p, C.c_void_p, C.c_size_t, C.c_void_p, C.c_size_t, C.c_char_p, C.c_size_t]
-    for j, (p, ln) in enumerate(pinned[1:], start=1):
-        nxt = pinned[j + 1] if j + 1 < len(pinned) else (None, 0)  # reindex: the next block is at hand, its scan runs ahead
-        t1 = time.perf_counter()
-        ok = L.bcp_chain_connect_block_hint(h, p, ln, nxt[0], nxt[1], reason, 256)
-        per_block.append(time.perf_counter() - t1)
-        assert ok == 1, reason.value
+    n_ok = L.bcp_chain_connect_file(h, pf, len(framed), magic, reason, 256, C.byref(failed))
     total = time.perf_counter() - t0
+    assert n_ok == nb, (n_ok, failed.value, reason.value)
     ph = (C.c_double * 5)()
     L.bcp_chain_phase_seconds.argtypes = [C.c_void_p, C.POINTER(C.c_double)]
     L.bcp_chain_phase_seconds(h, ph)
@@ -360,16 +358,17 @@ def chain_bench(args, devices):
     L.bcp_chain_walk_seconds(h, wk)
     phases["utxo_walk_parts"] = dict(zip(["pass_a_lookups", "staging_and_launch", "pass_b_inserts", "pass_c_in_block"],
                                          [1e3 * x / (nb + 1) for x in wk]))
-    for p, _ in pinned:
-        G.bcp_gpu_host_free(p)
+    G.bcp_gpu_host_free(p0)
+    G.bcp_gpu_host_free(pf)
     L.bcp_chain_free(h)
     out = {"blocks": nb, "inputs_per_block": ntx, "block_bytes": len(blocks[0]), "gpus": len(devices),
            "sharding": "one host chain walk; each block's inputs split by index across the GPUs, verdicts ANDed on the host",
            "gpu_seconds_total": total,
-           "gpu_blocks_per_s": nb / total, "gpu_ms_per_block_median": sorted(per_block)[len(per_block) // 2] * 1e3,
+           "gpu_blocks_per_s": nb / total, "gpu_ms_per_block": 1e3 * total / nb,
            "ms_per_block_by_phase": phases, "gen_seconds": gen_s, "warmup_blocks": 1,
-           "timed": "bcp::ChainValidator::ConnectBlock per block, the next block's framing scan running one block ahead (block "
-                    "bytes in pinned host memory, in-memory UTXO table on the host)"}
+           "timed": "bcp::ChainValidator::ConnectFile over the blocks in blk*.dat framing in one pinned buffer: two blocks in "
+                    "flight (block b+1 is scanned, looked up and applied while the devices check block b's scripts), in-memory "
+                    "UTXO table on the host"}
     if po.have_ref():
         r = po.ref()
         cores = os.cpu_count() or 1

@@ -233,13 +233,21 @@ public:
         team.reset(new WorkerTeam(1 << shardBits));
     }
     ~ChainValidator() {
-        if (ahead.th.joinable()) ahead.th.join();
+        for (Scan &a : ahead)
+            if (a.th.joinable()) a.th.join();
+        for (Work &w : work)
+            for (auto &t : w.th)
+                if (t.joinable()) t.join();
     }
 
     bool Init(std::string &err) {
         if (devs.empty()) { err = "no device"; return false; }
         for (int d : devs)
             if (bcp_gpu_init(d) != BCP_OK) { err = bcp_gpu_last_error(); return false; }
+        // header checks and txids go through a lane of their own, so that they do not queue behind the script checks of
+        // the block before (ConnectFile keeps two blocks in flight)
+        devAux = BCP_DEVICE_LANE(devs[0] & 0xFF, ((devs[0] >> 8) + 1) % 4);
+        if (bcp_gpu_init(devAux) != BCP_OK) { err = bcp_gpu_last_error(); return false; }
         return true;
     }
     void AddCoin(const uint8_t txid[32], uint32_t vout, const uint8_t *spk, size_t len, int64_t amount) {
@@ -256,8 +264,7 @@ public:
     size_t InputsChecked() const { return nInputs; }
 
     // seconds since construction: [0] header (Equihash + hash), [1] framing scan on the connecting thread (0 when the
-    // scan ran ahead), [2] waiting for the txids after the lookups, [3] the UTXO passes, [4] waiting for the script
-    // checks after the inserts
+    // scan ran ahead), [2] waiting for the txids after the lookups, [3] the UTXO passes, [4] waiting for script checks
     double phase[5] = {0, 0, 0, 0, 0};
     double walk[4] = {0, 0, 0, 0}; // inside [3]: pass A, staging for the script call, pass B, pass C
 
@@ -265,212 +272,81 @@ public:
     // `next` / `next_len` (optional): the block that will be connected after this one; its framing scan then runs on a
     // helper thread while this block is being connected.  Those bytes must stay valid until that block is connected.
     bool ConnectBlock(const uint8_t *blk, size_t len, std::string &reason, const uint8_t *next = nullptr, size_t next_len = 0) {
-        const int dev0 = devs[0];
-        auto now = [] { return std::chrono::steady_clock::now(); };
-        auto secs = [](std::chrono::steady_clock::time_point a, std::chrono::steady_clock::time_point b) {
-            return std::chrono::duration<double>(b - a).count();
-        };
-        auto t0 = now();
-        // header: Equihash + hash (ehN == 0 skips it, for chains built without solutions)
-        const size_t soln = ehN ? ((size_t)1 << ehK) * (ehN / (ehK + 1) + 1) / 8 : 0;
-        const size_t hdr_len = 140 + (soln < 253 ? 1 : 3) + soln;
-        if (ehN) {
-            if (len < hdr_len) { reason = "bad-blk-length"; return false; }
-            uint8_t ok = 0, hash[32];
-            if (bcp_gpu_equihash_verify_batch(dev0, ehN, ehK, blk, hdr_len, hdr_len, 1, &ok, hash) != BCP_OK) {
-                reason = std::string("device-error: ") + bcp_gpu_last_error();
-                return false;
-            }
-            if (!ok) { reason = "invalid-solution"; return false; } // CheckEquihashSolution (src/pow.cpp:298-323)
-            memcpy(lastHash, hash, 32);
-        }
-        auto t1 = now();
-        phase[0] += secs(t0, t1);
-        // framing: taken from the scan-ahead slot when it holds this very block, else done now
-        if (ahead.th.joinable()) ahead.th.join();
-        if (ahead.blk == blk && ahead.len == len && ahead.valid) SwapScan(cur, ahead);
-        else cur.Run(blk, len, shardBits);
-        ahead.valid = false;
-        if (next) ScanAhead(next, next_len);
-        const long ntx = cur.ntx, nin = cur.nin, nout = cur.nout;
-        const std::vector<uint32_t> &tx_off = cur.tx_off, &in_off = cur.in_off, &in_tx = cur.in_tx, &in_n = cur.in_n;
-        if (nin < 0 || ntx < 1) { reason = "bad-blk-framing"; return false; }
-        auto t2 = now();
-        phase[1] += secs(t1, t2);
-        // txids + Merkle root (CheckBlock, src/validation.cpp:3236-3252) on the device, from a helper thread, while the
-        // team looks up the spent coins: the lookups need the previous outputs, not this block's txids
-        txids.resize((size_t)ntx * 32);
-        uint8_t root[32];
-        int mutated = 0, rcTx = BCP_OK;
-        std::string errTx;
-        std::thread thTx([&] {
-            rcTx = bcp_gpu_sha256d_txids_merkle(dev0, blk, len, tx_off.data(), (size_t)ntx, txids.data(), root, &mutated);
-            if (rcTx != BCP_OK) errTx = bcp_gpu_last_error();
-        });
-        // Pass A, all shards in parallel: every input whose coin is in the table as it was BEFORE this block is staged
-        // (amount + scriptPubKey for the script checks) and removed.  What is not found is either created earlier in
-        // this block or missing; pass C settles that.
-        if (stage.size() < (size_t)nin) stage.resize((size_t)nin);
-        bigStore.clear();
-        spentUpTo = (size_t)nin;
-        createdUpTo = 0;
-        team->Run([&](int w) { PassA(w, blk, (size_t)nin); });
-        walk[0] += secs(t2, now());
-        size_t unresolved = 0;
-        for (size_t i = 0; i < (size_t)nin; i++) {
-            if (stage[i].state == ST_BIG) { // rare: a script too long for the staging slot; done here, on one thread
-                OutPoint op;
-                memcpy(op.b, blk + in_off[i], 36);
-                CoinTable &T = ShardOf(op);
-                CoinSlot *c = T.find(op);
-                if (!c) { // spent a moment ago by another input of this block
-                    stage[i].state = ST_MISS;
-                    unresolved++;
-                    continue;
-                }
-                stage[i].amount = c->amount;
-                stage[i].len = c->spk_len;
-                stage[i].big = (uint32_t)bigStore.size();
-                bigStore.emplace_back(CoinTable::script(*c), CoinTable::script(*c) + c->spk_len);
-                T.erase(c);
-            } else if (stage[i].state == ST_MISS) {
-                unresolved++;
-            }
-        }
-        auto t3 = now();
-        thTx.join();
-        auto t3b = now();
-        phase[3] += secs(t2, t3);
-        phase[2] += secs(t3, t3b); // what the lookups did not hide
-        if (rcTx != BCP_OK) { Rollback(blk); reason = "device-error: " + errTx; return false; }
-        if (memcmp(root, blk + 36, 32) != 0) { Rollback(blk); reason = "bad-txnmrklroot"; return false; }
-        if (mutated) { Rollback(blk); reason = "bad-txns-duplicate"; return false; }
-        // Script checks, sharded by input index range over the devices.  When pass A resolved every input they start
-        // now, from helper threads, and run while the team inserts the block's outputs (pass B).
-        errs.assign((size_t)nin, 0);
-        const size_t G = devs.size(), per = ((size_t)nin + G - 1) / G;
-        std::vector<int> rc(G, BCP_OK);
-        std::vector<std::string> msg(G);
-        std::vector<std::thread> th;
-        auto launchScripts = [&] {
-            BuildStaging((size_t)nin);
-            for (size_t g = 0; g < G && nin > 0; g++) {
-                const size_t lo = std::min((size_t)nin, g * per), hi = std::min((size_t)nin, lo + per);
-                if (lo >= hi) continue;
-                th.emplace_back([&, g, lo, hi] {
-                    int all = 0;
-                    rc[g] = bcp_gpu_block_scripts_p2pkh(devs[g], blk, len, tx_off.data(), (size_t)ntx, &in_off[lo], &in_tx[lo],
-                                                        &in_n[lo], hi - lo, spk_cat.data(), &spk_off[lo], &amounts[lo], flags,
-                                                        &errs[lo], &all);
-                    if (rc[g] != BCP_OK) msg[g] = bcp_gpu_last_error();
-                });
-            }
-        };
-        const bool overlapped = unresolved == 0;
-        if (overlapped) launchScripts();
-        auto tb0 = now();
-        walk[1] += secs(t3b, tb0);
-        // Pass B, all shards in parallel: the block's outputs become coins.
-        createdUpTo = (size_t)nout;
-        team->Run([&](int w) { PassB(w, blk, (size_t)nout); });
-        auto tb1 = now();
-        walk[2] += secs(tb0, tb1);
-        // Pass C, only when pass A left inputs open: they may spend coins created EARLIER in this block (the creating
-        // transaction must come first, src/validation.cpp:2095 applies each transaction before the next is looked at) and
-        // each such coin only once.
-        bool missing = false;
-        if (unresolved) {
-            std::unordered_map<uint64_t, uint32_t> txIndex; // first 8 bytes of a txid -> transaction number (verified below)
-            txIndex.reserve((size_t)ntx * 2);
-            for (long t = 0; t < ntx; t++) {
-                uint64_t k;
-                memcpy(&k, &txids[(size_t)t * 32], 8);
-                txIndex.emplace(k, (uint32_t)t);
-            }
-            for (size_t i = 0; i < (size_t)nin && !missing; i++) {
-                if (stage[i].state != ST_MISS) continue;
-                OutPoint op;
-                memcpy(op.b, blk + in_off[i], 36);
-                uint64_t k;
-                memcpy(&k, op.b, 8);
-                auto it = txIndex.find(k);
-                CoinTable &T = ShardOf(op);
-                CoinSlot *c = T.find(op);
-                if (!c || it == txIndex.end() || memcmp(&txids[(size_t)it->second * 32], op.b, 32) != 0 || it->second >= in_tx[i]) {
-                    missing = true;
-                    break;
-                }
-                stage[i].amount = c->amount;
-                stage[i].len = c->spk_len;
-                if (c->spk_len <= STAGE_SPK) {
-                    memcpy(stage[i].spk, CoinTable::script(*c), c->spk_len);
-                    stage[i].state = ST_INBLOCK;
-                } else {
-                    stage[i].big = (uint32_t)bigStore.size();
-                    bigStore.emplace_back(CoinTable::script(*c), CoinTable::script(*c) + c->spk_len);
-                    stage[i].state = ST_INBLOCK_BIG;
-                }
-                T.erase(c);
-            }
-        }
-        auto t4 = now();
-        walk[3] += secs(tb1, t4);
-        phase[3] += secs(t3b, t4);
-        if (missing) { // only reachable when the scripts were not started
-            Rollback(blk);
-            reason = "bad-txns-inputs-missingorspent";
-            return false;
-        }
-        if (!overlapped) launchScripts();
-        for (auto &t : th) t.join();
-        phase[4] += secs(t4, now()); // what pass B did not hide (everything when the passes could not overlap)
-        for (size_t g = 0; g < G; g++)
-            if (rc[g] != BCP_OK) { Rollback(blk); reason = "device-error: " + msg[g]; return false; }
-        for (size_t k = 0; k < (size_t)nin; k++) {
-            if (errs[k] == 255) { Rollback(blk); reason = "script-not-in-fast-path (input " + std::to_string(k) + ")"; return false; }
-            if (errs[k] != 0) { // ConnectBlock: "blk-bad-inputs" (src/validation.cpp:2124-2128)
-                Rollback(blk);
-                reason = "blk-bad-inputs (input " + std::to_string(k) + ", script error " + std::to_string(errs[k]) + ")";
-                return false;
-            }
-        }
-        // commit: the table already holds the new state
-        nInputs += (size_t)nin;
-        spentUpTo = createdUpTo = 0;
+        Work &w = work[0];
+        const Hint h(next, next_len);
+        if (!Begin(w, blk, len, reason, &h, next ? 1 : 0)) return false;
+        if (!Collect(w, reason)) { Rollback(w); return false; }
+        Commit(w);
         return true;
     }
     //! Optional: start the framing scan of the block that will be connected next on a helper thread, before the first
     //! ConnectBlock of a run (afterwards the `next` argument of ConnectBlock keeps the scans one block ahead).
     void ScanAhead(const uint8_t *blk, size_t len) {
-        if (ahead.th.joinable()) ahead.th.join();
-        ahead.valid = false;
-        ahead.th = std::thread([this, blk, len] { ahead.Run(blk, len, shardBits); });
+        for (Scan &a : ahead)
+            if (a.blk == blk && a.len == len && (a.th.joinable() || a.valid)) return; // already on its way
+        Scan &a = ahead[(nextSlot++) % 2];
+        if (a.th.joinable()) a.th.join();
+        a.valid = false;
+        a.blk = blk;
+        a.len = len;
+        const int dev = devAux, sb = shardBits;
+        const unsigned n_ = ehN, k_ = ehK;
+        Scan *pa = &a;
+        a.th = std::thread([pa, blk, len, sb, dev, n_, k_] {
+            pa->Frame(blk, len, sb);
+            pa->Device(dev, n_, k_);
+        });
     }
     const uint8_t *LastBlockHash() const { return lastHash; }
-    const std::vector<uint8_t> &LastScriptErrors() const { return errs; }
+    const std::vector<uint8_t> &LastScriptErrors() const { return work[lastWork].errs; }
 
     // blk*.dat framing (src/validation.cpp:4486-4516): [magic 4][size u32 LE][block] ... ; returns blocks connected,
-    // stops at the first failure (reason set, failed_index = its ordinal).
+    // stops at the first failure (reason set, failed_index = its ordinal).  Two blocks are in flight: while the devices
+    // run block b's script checks, the host already scans, looks up and applies block b+1 on top of b's (still
+    // unconfirmed) result; if b turns out invalid, b+1 is undone first, then b.
     long ConnectFile(const uint8_t *data, size_t len, const uint8_t magic[4], std::string &reason, long &failed_index) {
         size_t pos = 0;
         long n = 0;
         failed_index = -1;
+        Work *prev = nullptr;
         while (pos + 8 <= len) {
             if (memcmp(data + pos, magic, 4) != 0) { pos++; continue; } // resynchronise on the magic like :4489-4498
             uint32_t sz;
             memcpy(&sz, data + pos + 4, 4);
             if (pos + 8 + sz > len) break;
-            // the next block's framing scan runs on a helper thread while this block is being connected
-            const uint8_t *next = nullptr;
-            uint32_t nsz = 0;
-            const size_t nx = pos + 8 + (size_t)sz;
-            if (nx + 8 <= len && memcmp(data + nx, magic, 4) == 0) {
+            // the framing scans and device pre-checks of the next two blocks run on helper threads meanwhile
+            Hint hints[2];
+            size_t nh = 0, nx = pos + 8 + (size_t)sz;
+            while (nh < 2 && nx + 8 <= len && memcmp(data + nx, magic, 4) == 0) {
+                uint32_t nsz;
                 memcpy(&nsz, data + nx + 4, 4);
-                if (nx + 8 + nsz <= len) next = data + nx + 8;
+                if (nx + 8 + nsz > len) break;
+                hints[nh++] = Hint(data + nx + 8, nsz);
+                nx += 8 + (size_t)nsz;
             }
-            if (!ConnectBlock(data + pos + 8, sz, reason, next, nsz)) { failed_index = n; return n; }
+            Work &w = work[n & 1];
+            std::string r;
+            const bool begun = Begin(w, data + pos + 8, sz, r, hints, nh); // on failure this block is already undone
+            if (prev) {
+                std::string rp;
+                if (!Collect(*prev, rp)) { // the block before is invalid: this one goes first, then that one
+                    if (begun) { Abandon(w); Rollback(w); }
+                    Rollback(*prev);
+                    reason = rp;
+                    failed_index = n - 1;
+                    return n - 1;
+                }
+                Commit(*prev);
+                prev = nullptr;
+            }
+            if (!begun) { reason = r; failed_index = n; return n; }
+            prev = &w;
             pos += 8 + (size_t)sz;
             n++;
+        }
+        if (prev) {
+            if (!Collect(*prev, reason)) { Rollback(*prev); failed_index = n - 1; return n - 1; }
+            Commit(*prev);
         }
         return n;
     }
@@ -482,9 +358,32 @@ private:
         long ntx = 0, nin = -1, nout = 0;
         const uint8_t *blk = nullptr;
         size_t len = 0;
-        bool valid = false;
+        bool valid = false, deviceDone = false;
         std::thread th;
-        void Run(const uint8_t *b, size_t l, int shardBits) {
+        // device pre-checks, which need nothing but the block's own bytes: header (Equihash + hash), txids + Merkle root
+        std::vector<uint8_t> txids;
+        uint8_t root[32], hash[32];
+        int mutated = 0, rcTx = BCP_OK, rcEq = BCP_OK;
+        uint8_t eqOk = 1;
+        std::string errTx, errEq;
+        void Device(int dev, unsigned ehN, unsigned ehK) {
+            const size_t soln = ehN ? ((size_t)1 << ehK) * (ehN / (ehK + 1) + 1) / 8 : 0;
+            const size_t hdr_len = 140 + (soln < 253 ? 1 : 3) + soln;
+            rcEq = rcTx = BCP_OK;
+            eqOk = 1;
+            if (ehN && len >= hdr_len) {
+                rcEq = bcp_gpu_equihash_verify_batch(dev, ehN, ehK, blk, hdr_len, hdr_len, 1, &eqOk, hash);
+                if (rcEq != BCP_OK) errEq = bcp_gpu_last_error();
+            }
+            if (nin >= 0 && ntx >= 1) {
+                txids.resize((size_t)ntx * 32);
+                rcTx = bcp_gpu_sha256d_txids_merkle(dev, blk, len, tx_off.data(), (size_t)ntx, txids.data(), root, &mutated);
+                if (rcTx != BCP_OK) errTx = bcp_gpu_last_error();
+            }
+            deviceDone = true;
+        }
+        void Frame(const uint8_t *b, size_t l, int shardBits) {
+            deviceDone = false;
             const size_t max_tx = l / 60 + 2, max_in = l / 41 + 2, max_out = l / 9 + 2;
             if (tx_off.size() < max_tx + 1) { tx_off.resize(max_tx + 1); tx_out_off.resize(max_tx + 1); }
             if (in_off.size() < max_in) { in_off.resize(max_in); in_tx.resize(max_in); in_n.resize(max_in); }
@@ -518,10 +417,12 @@ private:
         a.tx_off.swap(b.tx_off); a.tx_out_off.swap(b.tx_out_off); a.in_off.swap(b.in_off); a.in_tx.swap(b.in_tx); a.in_n.swap(b.in_n);
         a.out_off.swap(b.out_off); a.out_tx.swap(b.out_tx); a.out_n.swap(b.out_n);
         a.by_shard.swap(b.by_shard); a.shard_start.swap(b.shard_start);
+        a.txids.swap(b.txids); a.errTx.swap(b.errTx); a.errEq.swap(b.errEq);
+        std::swap(a.root, b.root); std::swap(a.hash, b.hash); std::swap(a.mutated, b.mutated); std::swap(a.rcTx, b.rcTx);
+        std::swap(a.rcEq, b.rcEq); std::swap(a.eqOk, b.eqOk); std::swap(a.deviceDone, b.deviceDone);
         std::swap(a.ntx, b.ntx); std::swap(a.nin, b.nin); std::swap(a.nout, b.nout); std::swap(a.blk, b.blk); std::swap(a.len, b.len);
         std::swap(a.valid, b.valid);
     }
-    Scan cur, ahead;
 
     // what pass A / C found for one input; 128 bytes so that two threads never write the same cache line
     enum : uint8_t { ST_MISS = 0, ST_TAKEN = 1, ST_BIG = 2, ST_INBLOCK = 3, ST_INBLOCK_BIG = 4 };
@@ -532,20 +433,238 @@ private:
         uint8_t state;
         uint8_t spk[STAGE_SPK];
     };
+    // Everything that belongs to one block on its way through: its framing, txids, the staging records of its inputs
+    // (also the undo log), the arrays of the script-check call and the helper threads running that call.
+    struct Work {
+        Scan cur;
+        const uint8_t *blk = nullptr;
+        size_t len = 0;
+        std::vector<uint8_t> spk_cat, errs;
+        std::vector<uint32_t> spk_off;
+        std::vector<int64_t> amounts;
+        std::vector<Staged> stage;
+        std::vector<std::vector<uint8_t>> bigStore;
+        size_t spentUpTo = 0, createdUpTo = 0; // how far the block has been applied to the table (for Rollback)
+        std::vector<std::thread> th;
+        std::vector<int> rc;
+        std::vector<std::string> msg;
+        uint8_t hash[32];
+    };
 
     int ShardIndex(const OutPoint &op) const { return shardBits ? (int)(OutPointHash()(op) >> (64 - shardBits)) : 0; }
     CoinTable &ShardOf(const OutPoint &op) { return *shards[(size_t)ShardIndex(op)]; }
+    static double Secs(std::chrono::steady_clock::time_point a, std::chrono::steady_clock::time_point b) {
+        return std::chrono::duration<double>(b - a).count();
+    }
 
-    // One worker's share of pass A: the inputs whose outpoint hashes to its shard, in block order, with the table slots
-    // of the next few prefetched while the current one is handled.
-    void PassA(int w, const uint8_t *blk, size_t nin) {
+    // Header, framing, txids + Merkle, the table passes, and the launch of the script checks.  true: the block is
+    // applied to the table and its script checks are running (Collect gives the verdict); false: rejected, nothing of it
+    // is left in the table.
+    typedef std::pair<const uint8_t *, size_t> Hint;
+    bool Begin(Work &w, const uint8_t *blk, size_t len, std::string &reason, const Hint *hints, size_t nhints) {
+        auto now = [] { return std::chrono::steady_clock::now(); };
+        w.blk = blk;
+        w.len = len;
+        w.spentUpTo = w.createdUpTo = 0;
+        auto t0 = now();
+        const size_t soln = ehN ? ((size_t)1 << ehK) * (ehN / (ehK + 1) + 1) / 8 : 0;
+        const size_t hdr_len = 140 + (soln < 253 ? 1 : 3) + soln;
+        if (ehN && len < hdr_len) { reason = "bad-blk-length"; return false; }
+        // Framing and the device pre-checks (header, txids + Merkle) come from a scan-ahead slot when one holds this very
+        // block; otherwise the framing is done now and the device part runs on a helper thread under pass A.
+        Scan *slot = nullptr;
+        for (Scan &a : ahead)
+            if (a.blk == blk && a.len == len && (a.th.joinable() || a.valid)) slot = &a;
+        std::thread thDev;
+        if (slot) {
+            if (slot->th.joinable()) slot->th.join();
+            SwapScan(w.cur, *slot);
+            slot->valid = false;
+            slot->blk = nullptr;
+        } else {
+            w.cur.Frame(blk, len, shardBits);
+            Scan *pc = &w.cur;
+            const int dev = devAux;
+            const unsigned n_ = ehN, k_ = ehK;
+            thDev = std::thread([pc, dev, n_, k_] { pc->Device(dev, n_, k_); });
+        }
+        for (size_t k = 0; k < nhints; k++) ScanAhead(hints[k].first, hints[k].second);
+        const Scan &cur = w.cur;
+        const long ntx = cur.ntx, nin = cur.nin, nout = cur.nout;
+        auto t2 = now();
+        phase[1] += Secs(t0, t2);
+        if (nin < 0 || ntx < 1) {
+            if (thDev.joinable()) thDev.join();
+            if (cur.rcEq == BCP_OK && !cur.eqOk) reason = "invalid-solution"; // the header is looked at before the body
+            else reason = "bad-blk-framing";
+            return false;
+        }
+        // Pass A, all shards in parallel: every input whose coin is in the table as it was BEFORE this block is staged
+        // (amount + scriptPubKey for the script checks) and removed.  What is not found is either created earlier in
+        // this block or missing; pass C settles that.
+        if (w.stage.size() < (size_t)nin) w.stage.resize((size_t)nin);
+        w.bigStore.clear();
+        w.spentUpTo = (size_t)nin;
+        team->Run([&](int s_) { PassA(w, s_); });
+        walk[0] += Secs(t2, now());
+        size_t unresolved = 0;
+        for (size_t i = 0; i < (size_t)nin; i++) {
+            Staged &st = w.stage[i];
+            if (st.state == ST_BIG) { // rare: a script too long for the staging slot; done here, on one thread
+                OutPoint op;
+                memcpy(op.b, blk + cur.in_off[i], 36);
+                CoinTable &T = ShardOf(op);
+                CoinSlot *c = T.find(op);
+                if (!c) { // spent a moment ago by another input of this block
+                    st.state = ST_MISS;
+                    unresolved++;
+                    continue;
+                }
+                st.amount = c->amount;
+                st.len = c->spk_len;
+                st.big = (uint32_t)w.bigStore.size();
+                w.bigStore.emplace_back(CoinTable::script(*c), CoinTable::script(*c) + c->spk_len);
+                T.erase(c);
+            } else if (st.state == ST_MISS) {
+                unresolved++;
+            }
+        }
+        auto t3 = now();
+        if (thDev.joinable()) thDev.join();
+        auto t3b = now();
+        phase[3] += Secs(t2, t3);
+        phase[2] += Secs(t3, t3b); // device pre-checks the lookups did not hide
+        if (cur.rcEq != BCP_OK) { Rollback(w); reason = "device-error: " + cur.errEq; return false; }
+        if (!cur.eqOk) { Rollback(w); reason = "invalid-solution"; return false; } // CheckEquihashSolution (src/pow.cpp:298-323)
+        if (cur.rcTx != BCP_OK) { Rollback(w); reason = "device-error: " + cur.errTx; return false; }
+        if (memcmp(cur.root, blk + 36, 32) != 0) { Rollback(w); reason = "bad-txnmrklroot"; return false; }
+        if (cur.mutated) { Rollback(w); reason = "bad-txns-duplicate"; return false; }
+        memcpy(w.hash, cur.hash, 32);
+        // Script checks, sharded by input index range over the devices.  When pass A resolved every input they start
+        // now, from helper threads, and run while the team inserts the block's outputs (pass B).
+        w.errs.assign((size_t)nin, 0);
+        const size_t G = devs.size(), per = ((size_t)nin + G - 1) / G;
+        w.rc.assign(G, BCP_OK);
+        w.msg.assign(G, std::string());
+        w.th.clear();
+        auto launchScripts = [&] {
+            BuildStaging(w);
+            for (size_t g = 0; g < G && nin > 0; g++) {
+                const size_t lo = std::min((size_t)nin, g * per), hi = std::min((size_t)nin, lo + per);
+                if (lo >= hi) continue;
+                Work *pw = &w;
+                const int dev = devs[g];
+                const uint32_t fl = flags;
+                w.th.emplace_back([pw, g, lo, hi, dev, fl] {
+                    int all = 0;
+                    const Scan &c = pw->cur;
+                    pw->rc[g] = bcp_gpu_block_scripts_p2pkh(dev, pw->blk, pw->len, c.tx_off.data(), (size_t)c.ntx, &c.in_off[lo],
+                                                            &c.in_tx[lo], &c.in_n[lo], hi - lo, pw->spk_cat.data(), &pw->spk_off[lo],
+                                                            &pw->amounts[lo], fl, &pw->errs[lo], &all);
+                    if (pw->rc[g] != BCP_OK) pw->msg[g] = bcp_gpu_last_error();
+                });
+            }
+        };
+        const bool overlapped = unresolved == 0;
+        if (overlapped) launchScripts();
+        auto tb0 = now();
+        walk[1] += Secs(t3b, tb0);
+        // Pass B, all shards in parallel: the block's outputs become coins.
+        w.createdUpTo = (size_t)nout;
+        team->Run([&](int s_) { PassB(w, s_); });
+        auto tb1 = now();
+        walk[2] += Secs(tb0, tb1);
+        // Pass C, only when pass A left inputs open: they may spend coins created EARLIER in this block (the creating
+        // transaction must come first, src/validation.cpp:2095 applies each transaction before the next is looked at) and
+        // each such coin only once.
+        bool missing = false;
+        if (unresolved) {
+            std::unordered_map<uint64_t, uint32_t> txIndex; // first 8 bytes of a txid -> transaction number (verified below)
+            txIndex.reserve((size_t)ntx * 2);
+            for (long t = 0; t < ntx; t++) {
+                uint64_t k;
+                memcpy(&k, &cur.txids[(size_t)t * 32], 8);
+                txIndex.emplace(k, (uint32_t)t);
+            }
+            for (size_t i = 0; i < (size_t)nin && !missing; i++) {
+                Staged &st = w.stage[i];
+                if (st.state != ST_MISS) continue;
+                OutPoint op;
+                memcpy(op.b, blk + cur.in_off[i], 36);
+                uint64_t k;
+                memcpy(&k, op.b, 8);
+                auto it = txIndex.find(k);
+                CoinTable &T = ShardOf(op);
+                CoinSlot *c = T.find(op);
+                if (!c || it == txIndex.end() || memcmp(&cur.txids[(size_t)it->second * 32], op.b, 32) != 0 ||
+                    it->second >= cur.in_tx[i]) {
+                    missing = true;
+                    break;
+                }
+                st.amount = c->amount;
+                st.len = c->spk_len;
+                if (c->spk_len <= STAGE_SPK) {
+                    memcpy(st.spk, CoinTable::script(*c), c->spk_len);
+                    st.state = ST_INBLOCK;
+                } else {
+                    st.big = (uint32_t)w.bigStore.size();
+                    w.bigStore.emplace_back(CoinTable::script(*c), CoinTable::script(*c) + c->spk_len);
+                    st.state = ST_INBLOCK_BIG;
+                }
+                T.erase(c);
+            }
+        }
+        auto t4 = now();
+        walk[3] += Secs(tb1, t4);
+        phase[3] += Secs(t3b, t4);
+        if (missing) { // only reachable when the scripts were not started
+            Rollback(w);
+            reason = "bad-txns-inputs-missingorspent";
+            return false;
+        }
+        if (!overlapped) launchScripts();
+        return true;
+    }
+    // Waits for the block's script checks; false + reason when they reject it (the table is NOT touched here).
+    bool Collect(Work &w, std::string &reason) {
+        auto t0 = std::chrono::steady_clock::now();
+        for (auto &t : w.th) t.join();
+        w.th.clear();
+        phase[4] += Secs(t0, std::chrono::steady_clock::now());
+        lastWork = (int)(&w - work);
+        for (size_t g = 0; g < w.rc.size(); g++)
+            if (w.rc[g] != BCP_OK) { reason = "device-error: " + w.msg[g]; return false; }
+        for (size_t k = 0; k < (size_t)w.cur.nin; k++) {
+            if (w.errs[k] == 255) { reason = "script-not-in-fast-path (input " + std::to_string(k) + ")"; return false; }
+            if (w.errs[k] != 0) { // ConnectBlock: "blk-bad-inputs" (src/validation.cpp:2124-2128)
+                reason = "blk-bad-inputs (input " + std::to_string(k) + ", script error " + std::to_string(w.errs[k]) + ")";
+                return false;
+            }
+        }
+        return true;
+    }
+    void Abandon(Work &w) { // a block whose verdict no longer matters: just let its device calls finish
+        for (auto &t : w.th) t.join();
+        w.th.clear();
+    }
+    void Commit(Work &w) { // the table already holds the new state
+        nInputs += (size_t)w.cur.nin;
+        memcpy(lastHash, w.hash, 32);
+        w.spentUpTo = w.createdUpTo = 0;
+    }
+
+    // One worker's share of pass A: the inputs whose outpoint hashes to its shard (grouped by the scan), in block order,
+    // with the table slots of the next few prefetched while the current one is handled.
+    void PassA(Work &wk, int w) {
         CoinTable &T = *shards[(size_t)w];
+        const Scan &cur = wk.cur;
+        const uint8_t *blk = wk.blk;
         const size_t RING = 8;
         size_t ring[RING], head = 0, count = 0;
         auto take = [&](size_t i) {
             OutPoint op;
             memcpy(op.b, blk + cur.in_off[i], 36);
-            Staged &s = stage[i];
+            Staged &s = wk.stage[i];
             CoinSlot *c = T.find(op);
             if (!c) { s.state = ST_MISS; return; }
             if (c->spk_len > STAGE_SPK) { s.state = ST_BIG; return; } // left in the table for the connecting thread
@@ -555,7 +674,6 @@ private:
             s.state = ST_TAKEN;
             T.erase(c);
         };
-        (void)nin;
         for (size_t q = cur.shard_start[(size_t)w]; q < cur.shard_start[(size_t)w + 1]; q++) {
             const size_t i = cur.by_shard[q];
             OutPoint op;
@@ -572,8 +690,12 @@ private:
         for (size_t k = 0; k < count; k++) take(ring[(head + k) % RING]);
     }
     // One worker's share of pass B: the outputs whose outpoint hashes to its shard.
-    void PassB(int w, const uint8_t *blk, size_t nout) {
+    void PassB(Work &wk, int w) {
         CoinTable &T = *shards[(size_t)w];
+        const Scan &cur = wk.cur;
+        const uint8_t *blk = wk.blk;
+        const std::vector<uint8_t> &txids = cur.txids;
+        const size_t nout = (size_t)cur.nout;
         const size_t RING = 8;
         size_t ring[RING], head = 0, count = 0;
         auto put = [&](size_t o) {
@@ -605,22 +727,23 @@ private:
         for (size_t k = 0; k < count; k++) put(ring[(head + k) % RING]);
     }
     // staging records -> the concatenated scriptPubKeys / offsets / amounts the script-check call takes
-    void BuildStaging(size_t nin) {
-        spk_off.resize(nin + 1);
-        amounts.resize(nin);
+    void BuildStaging(Work &w) {
+        const size_t nin = (size_t)w.cur.nin;
+        w.spk_off.resize(nin + 1);
+        w.amounts.resize(nin);
         size_t total = 0;
-        for (size_t i = 0; i < nin; i++) total += stage[i].len;
-        spk_cat.resize(total + 1);
+        for (size_t i = 0; i < nin; i++) total += w.stage[i].len;
+        w.spk_cat.resize(total + 1);
         uint32_t o = 0;
         for (size_t i = 0; i < nin; i++) {
-            const Staged &s = stage[i];
-            spk_off[i] = o;
-            amounts[i] = s.amount;
-            const uint8_t *src = (s.state == ST_BIG || s.state == ST_INBLOCK_BIG) ? bigStore[s.big].data() : s.spk;
-            memcpy(&spk_cat[o], src, s.len);
+            const Staged &s = w.stage[i];
+            w.spk_off[i] = o;
+            w.amounts[i] = s.amount;
+            const uint8_t *src = (s.state == ST_BIG || s.state == ST_INBLOCK_BIG) ? w.bigStore[s.big].data() : s.spk;
+            memcpy(&w.spk_cat[o], src, s.len);
             o += s.len;
         }
-        spk_off[nin] = o;
+        w.spk_off[nin] = o;
     }
     static uint64_t ReadCompact(const uint8_t *p, size_t &pos) { // already validated by the framing scan
         uint8_t c = p[pos++];
@@ -631,40 +754,41 @@ private:
         pos += nb;
         return v;
     }
-    // Undo a partially applied block (one thread; a rejected block is the rare case): drop the coins it created, then
-    // put back the coins it spent that existed before it — from the staging records, which still hold them.
-    void Rollback(const uint8_t *blk) {
-        for (size_t o = 0; o < createdUpTo; o++) {
+    // Undo a (partially) applied block (one thread; a rejected block is the rare case): drop the coins it created, then
+    // put back the coins it spent that existed before it — from the staging records, which still hold them.  Blocks are
+    // undone in reverse order of application.
+    void Rollback(Work &w) {
+        const Scan &cur = w.cur;
+        for (size_t o = 0; o < w.createdUpTo; o++) {
             OutPoint op;
-            memcpy(op.b, &txids[(size_t)cur.out_tx[o] * 32], 32);
+            memcpy(op.b, &cur.txids[(size_t)cur.out_tx[o] * 32], 32);
             memcpy(op.b + 32, &cur.out_n[o], 4);
             CoinTable &T = ShardOf(op);
             CoinSlot *c = T.find(op);
             if (c) T.erase(c);
         }
-        for (size_t i = 0; i < spentUpTo; i++) {
-            const Staged &s = stage[i];
+        for (size_t i = 0; i < w.spentUpTo; i++) {
+            const Staged &s = w.stage[i];
             if (s.state != ST_TAKEN && s.state != ST_BIG) continue; // misses, and coins this block itself had created
             OutPoint op;
-            memcpy(op.b, blk + cur.in_off[i], 36);
-            const uint8_t *src = s.state == ST_BIG ? bigStore[s.big].data() : s.spk;
+            memcpy(op.b, w.blk + cur.in_off[i], 36);
+            const uint8_t *src = s.state == ST_BIG ? w.bigStore[s.big].data() : s.spk;
             ShardOf(op).insert(op, src, s.len, s.amount);
         }
-        spentUpTo = createdUpTo = 0;
+        w.spentUpTo = w.createdUpTo = 0;
     }
 
     std::vector<int> devs;
+    int devAux = 0;
     uint32_t flags;
     unsigned ehN, ehK;
     int shardBits;
     std::vector<std::unique_ptr<CoinTable>> shards;
     std::unique_ptr<WorkerTeam> team;
-    std::vector<Staged> stage;
-    std::vector<std::vector<uint8_t>> bigStore;
-    size_t spentUpTo = 0, createdUpTo = 0; // how far the current block has been applied (for Rollback)
-    std::vector<uint32_t> spk_off;
-    std::vector<uint8_t> txids, spk_cat, errs;
-    std::vector<int64_t> amounts;
+    Scan ahead[2];
+    unsigned nextSlot = 0;
+    Work work[2];
+    int lastWork = 0;
     uint8_t lastHash[32] = {0};
     size_t nInputs = 0;
 };
