@@ -229,21 +229,25 @@ int bcp_gpu_ecdsa_verify_batch(int device, const uint8_t *msg32, const uint8_t *
     if (n == 0) return BCP_OK;
     std::lock_guard<std::mutex> lk(c->mu);
     BCP_CUDA(cudaSetDevice(c->device));
-    const size_t CH = BCP_E2E_CHUNK; // signatures per chunk: three full waves
+    // Chunk schedule: a first chunk of one wave (its copy is the only one nothing hides, so it is kept short), then
+    // chunks of three waves; a remainder of less than a wave rides with the chunk before it.
+    const size_t CH = BCP_E2E_CHUNK, W1 = BCP_WAVE;
     const size_t per = 32 + 65 + 64 + 1;
-    const size_t chunk = n < CH ? n : CH;
-    const size_t slot = ((chunk * per + 255) / 256) * 256;
+    const size_t cap = n < CH + W1 ? n : CH + W1; // largest chunk the schedule can produce
+    const size_t slot = ((cap * per + 255) / 256) * 256;
     int rc = bcp_ctx_reserve_stage(c, 2 * slot);
     if (rc != BCP_OK) return rc;
-    rc = bcp_ctx_reserve_scratch(c, 2 * bcp_gpu_ecdsa_scratch_bytes(chunk));
+    rc = bcp_ctx_reserve_scratch(c, 2 * bcp_gpu_ecdsa_scratch_bytes(cap));
     if (rc != BCP_OK) return rc;
     cudaStream_t st[2] = {c->stream, c->copy_stream};
     int k = 0;
-    for (size_t off = 0; off < n; off += chunk, k ^= 1) {
-        size_t m = n - off < chunk ? n - off : chunk;
+    for (size_t off = 0; off < n; k ^= 1) {
+        size_t m = off == 0 && n > CH ? W1 : CH;
+        if (m > n - off) m = n - off;
+        if (n - off - m < W1) m = n - off; // swallow a short tail
         uint8_t *base = c->stage + (size_t)k * slot;
         uint8_t *d_msg = base, *d_pub = d_msg + m * 32, *d_sig = d_pub + m * 65, *d_ok = d_sig + m * 64;
-        uint32_t *d_rec = reinterpret_cast<uint32_t *>(c->scratch + (size_t)k * bcp_gpu_ecdsa_scratch_bytes(chunk));
+        uint32_t *d_rec = reinterpret_cast<uint32_t *>(c->scratch + (size_t)k * bcp_gpu_ecdsa_scratch_bytes(cap));
         // each slot is reused every second chunk: work on a slot is ordered by its own stream
         BCP_CUDA(cudaMemcpyAsync(d_msg, msg32 + off * 32, m * 32, cudaMemcpyHostToDevice, st[k]));
         BCP_CUDA(cudaMemcpyAsync(d_pub, pub65 + off * 65, m * 65, cudaMemcpyHostToDevice, st[k]));
@@ -251,6 +255,7 @@ int bcp_gpu_ecdsa_verify_batch(int device, const uint8_t *msg32, const uint8_t *
         rc = bcp_ecdsa_launch(c, d_msg, d_pub, d_sig, m, flags, d_ok, d_rec, st[k]);
         if (rc != BCP_OK) return rc;
         BCP_CUDA(cudaMemcpyAsync(ok + off, d_ok, m, cudaMemcpyDeviceToHost, st[k]));
+        off += m;
     }
     BCP_CUDA(cudaStreamSynchronize(st[0]));
     BCP_CUDA(cudaStreamSynchronize(st[1]));
