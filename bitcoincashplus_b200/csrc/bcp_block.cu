@@ -18,11 +18,41 @@
 #include <thread>
 #include <vector>
 
+// Both per-transaction kernels parse transactions byte by byte.  Done straight from global memory that is one LDG.U8
+// per byte and the load/store queue is the limit (ncu: lg_throttle 19 and long_scoreboard 16 stalls per issue).  The
+// transactions a 128-thread block works on are CONTIGUOUS in the block buffer, so the block first copies that span into
+// shared memory with coalesced 16-byte loads and parses from there; a span that does not fit (a block holding a huge
+// transaction) keeps the global path — the choice is uniform for the thread block.
+#define BCP_SPAN_MAX 98304u /* most shared memory a span may take (opt-in dynamic shared memory) */
+
+// copies blk[lo16, hi) to shared memory (lo16 = lo rounded down to 16); the 16-byte loads may run up to 15 bytes past
+// `hi`, which stays inside the staging allocation (the block region is followed by the offset arrays)
+__device__ __forceinline__ bool stage_span(uint4 *span4, const uint8_t *blk, uint32_t lo, uint32_t hi, uint32_t cap,
+                                           uint32_t &lo16) {
+    lo16 = lo & ~15u;
+    if (hi - lo16 > cap) return false;
+    const uint4 *src = reinterpret_cast<const uint4 *>(blk + lo16);
+    const uint32_t n16 = (hi - lo16 + 15u) >> 4;
+    for (uint32_t k = threadIdx.x; k < n16; k += blockDim.x) span4[k] = __ldg(src + k);
+    __syncthreads();
+    return true;
+}
+
+// dynamic shared memory: [32 words x 128 threads of streaming-hash scratch][span of `cap` bytes]
 __global__ void __launch_bounds__(128) k_tx_midstate(const uint8_t *__restrict__ blk, const uint32_t *__restrict__ tx_off,
-                                                     size_t ntx, uint8_t *__restrict__ mid) {
-    size_t t = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+                                                     size_t ntx, uint8_t *__restrict__ mid, uint32_t cap) {
+    extern __shared__ uint4 smem4[];
+    uint32_t *wbuf = reinterpret_cast<uint32_t *>(smem4);
+    uint4 *span4 = smem4 + (32 * 128 * 4) / 16;
+    const size_t t0 = (size_t)blockIdx.x * blockDim.x;
+    const size_t t1 = t0 + blockDim.x < ntx ? t0 + blockDim.x : ntx;
+    uint32_t lo16;
+    const bool staged = stage_span(span4, blk, tx_off[t0], tx_off[t1], cap, lo16);
+    const size_t t = t0 + threadIdx.x;
     if (t >= ntx) return;
-    tx_midstate(mid + t * BCP_TXMID_BYTES, blk + tx_off[t], tx_off[t + 1] - tx_off[t]);
+    const uint32_t o = tx_off[t];
+    const uint8_t *tx = staged ? reinterpret_cast<const uint8_t *>(span4) + (o - lo16) : blk + o;
+    tx_midstate(mid + t * BCP_TXMID_BYTES, tx, tx_off[t + 1] - o, wbuf + threadIdx.x, 128);
 }
 
 __global__ void __launch_bounds__(128)
@@ -30,14 +60,60 @@ __global__ void __launch_bounds__(128)
                     const uint32_t *__restrict__ in_tx, const uint32_t *__restrict__ in_n, size_t nin,
                     const uint8_t *__restrict__ spk, const uint32_t *__restrict__ spk_off, const int64_t *__restrict__ amounts,
                     const uint8_t *__restrict__ mid, uint8_t *__restrict__ status, uint8_t *__restrict__ msg32,
-                    uint8_t *__restrict__ pub65, uint8_t *__restrict__ sig64) {
-    size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+                    uint8_t *__restrict__ pub65, uint8_t *__restrict__ sig64, uint32_t cap) {
+    extern __shared__ uint4 smem4[];
+    const size_t i0 = (size_t)blockIdx.x * blockDim.x;
+    const size_t i1 = i0 + blockDim.x < nin ? i0 + blockDim.x : nin;
+    // inputs are listed in block order, so this thread block's inputs live in transactions in_tx[i0] .. in_tx[i1-1]
+    uint32_t lo16;
+    const bool staged = stage_span(smem4, blk, tx_off[in_tx[i0]], tx_off[in_tx[i1 - 1] + 1], cap, lo16);
+    const size_t i = i0 + threadIdx.x;
     if (i >= nin) return;
     const uint32_t t = in_tx[i];
     const uint32_t o = tx_off[t];
-    status[i] = (uint8_t)p2pkh_extract_one(blk + o, tx_off[t + 1] - o, in_off[i] - o, in_n[i], spk + spk_off[i],
+    const uint8_t *tx = staged ? reinterpret_cast<const uint8_t *>(smem4) + (o - lo16) : blk + o;
+    status[i] = (uint8_t)p2pkh_extract_one(tx, tx_off[t + 1] - o, in_off[i] - o, in_n[i], spk + spk_off[i],
                                            spk_off[i + 1] - spk_off[i], amounts[i], mid + (size_t)t * BCP_TXMID_BYTES,
                                            msg32 + 32 * i, pub65 + 65 * i, sig64 + 64 * i);
+}
+
+// Host side of the span staging: the largest span any thread block of the launch needs (plus the 15 bytes the start may
+// be rounded down by), capped; the launch asks for exactly that much dynamic shared memory, so ordinary blocks (128
+// transactions of ~200 bytes = 25 KB) keep a high occupancy and only unusual ones pay for more.
+static uint32_t span_cap_tx(const uint32_t *tx_off, size_t ntx) {
+    uint32_t need = 0;
+    for (size_t t0 = 0; t0 < ntx; t0 += 128) {
+        const size_t t1 = t0 + 128 < ntx ? t0 + 128 : ntx;
+        need = std::max(need, tx_off[t1] - tx_off[t0]);
+    }
+    return std::min(BCP_SPAN_MAX, (need + 15u + 15u) & ~15u);
+}
+static uint32_t span_cap_inputs(const uint32_t *tx_off, const uint32_t *in_tx, size_t nin) {
+    uint32_t need = 0;
+    for (size_t i0 = 0; i0 < nin; i0 += 128) {
+        const size_t i1 = i0 + 128 < nin ? i0 + 128 : nin;
+        need = std::max(need, tx_off[in_tx[i1 - 1] + 1] - tx_off[in_tx[i0]]);
+    }
+    return std::min(BCP_SPAN_MAX, (need + 15u + 15u) & ~15u);
+}
+#define BCP_MID_WBUF_BYTES (32u * 128u * 4u)
+// sighash midstates per transaction, then template match + sighash per input (host arrays only size the spans)
+static int launch_mid_extract(bcp_ctx *c, const uint8_t *d_blk, const uint32_t *d_txoff, const uint32_t *h_txoff, size_t ntx,
+                              const uint32_t *d_inoff, const uint32_t *d_intx, const uint32_t *d_inn, const uint32_t *h_intx,
+                              size_t nin, const uint8_t *d_spk, const uint32_t *d_spkoff, const int64_t *d_amt, uint8_t *d_mid,
+                              uint8_t *d_stat, uint8_t *d_msg, uint8_t *d_pub, uint8_t *d_sig, cudaStream_t st) {
+    if (!c->block_attrs) { /* per device: allow the kernels more than the default 48 KB of dynamic shared memory */
+        BCP_CUDA(cudaFuncSetAttribute(k_tx_midstate, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                      (int)(BCP_SPAN_MAX + BCP_MID_WBUF_BYTES + 16)));
+        BCP_CUDA(cudaFuncSetAttribute(k_p2pkh_extract, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(BCP_SPAN_MAX + 16)));
+        c->block_attrs = true;
+    }
+    const uint32_t cap_t = span_cap_tx(h_txoff, ntx), cap_i = span_cap_inputs(h_txoff, h_intx, nin);
+    k_tx_midstate<<<(unsigned)((ntx + 127) / 128), 128, BCP_MID_WBUF_BYTES + cap_t + 16, st>>>(d_blk, d_txoff, ntx, d_mid, cap_t);
+    k_p2pkh_extract<<<(unsigned)((nin + 127) / 128), 128, cap_i + 16, st>>>(d_blk, d_txoff, d_inoff, d_intx, d_inn, nin, d_spk,
+                                                                           d_spkoff, d_amt, d_mid, d_stat, d_msg, d_pub, d_sig, cap_i);
+    BCP_CUDA(cudaGetLastError());
+    return BCP_OK;
 }
 
 __global__ void k_script_finish(const uint8_t *__restrict__ status, const uint8_t *__restrict__ ok, size_t nin,
@@ -233,12 +309,11 @@ BCP_API int bcp_gpu_block_scripts_p2pkh(int device, const uint8_t *blk, size_t l
     BCP_CUDA(cudaMemcpyAsync(d + o_amt, amounts, nin * 8, cudaMemcpyHostToDevice, st));
     BCP_CUDA(cudaMemcpyAsync(d + o_flag, &one, sizeof(int), cudaMemcpyHostToDevice, st));
     uint32_t *d_txoff = reinterpret_cast<uint32_t *>(d + o_txoff);
-    k_tx_midstate<<<(unsigned)((ntx + 127) / 128), 128, 0, st>>>(d + o_blk, d_txoff, ntx, d + o_mid);
-    k_p2pkh_extract<<<(unsigned)((nin + 127) / 128), 128, 0, st>>>(
-        d + o_blk, d_txoff, reinterpret_cast<uint32_t *>(d + o_inoff), reinterpret_cast<uint32_t *>(d + o_intx),
-        reinterpret_cast<uint32_t *>(d + o_inn), nin, d + o_spk, reinterpret_cast<uint32_t *>(d + o_spkoff),
-        reinterpret_cast<int64_t *>(d + o_amt), d + o_mid, d + o_stat, d + o_msg, d + o_pub, d + o_sig);
-    BCP_CUDA(cudaGetLastError());
+    rc = launch_mid_extract(c, d + o_blk, d_txoff, tx_off, ntx, reinterpret_cast<uint32_t *>(d + o_inoff),
+                            reinterpret_cast<uint32_t *>(d + o_intx), reinterpret_cast<uint32_t *>(d + o_inn), in_tx, nin,
+                            d + o_spk, reinterpret_cast<uint32_t *>(d + o_spkoff), reinterpret_cast<int64_t *>(d + o_amt),
+                            d + o_mid, d + o_stat, d + o_msg, d + o_pub, d + o_sig, st);
+    if (rc != BCP_OK) return rc;
     rc = bcp_ecdsa_launch(c, d + o_msg, d + o_pub, d + o_sig, nin, BCP_ECDSA_FLAG_NORMALIZE_S, d + o_ok,
                           reinterpret_cast<uint32_t *>(c->scratch), st);
     if (rc != BCP_OK) return rc;
@@ -335,12 +410,11 @@ BCP_API int bcp_gpu_block_connect_p2pkh(int device, const uint8_t *blk, size_t l
         BCP_CUDA(cudaMemcpyAsync(d + o_spk, spk, spk_bytes, cudaMemcpyHostToDevice, st));
         BCP_CUDA(cudaMemcpyAsync(d + o_spkoff, spk_off, (nin + 1) * 4, cudaMemcpyHostToDevice, st));
         BCP_CUDA(cudaMemcpyAsync(d + o_amt, amounts, nin * 8, cudaMemcpyHostToDevice, st));
-        k_tx_midstate<<<(unsigned)((ntx + 127) / 128), 128, 0, st>>>(d + o_blk, d_txoff, ntx, d + o_mid);
-        k_p2pkh_extract<<<(unsigned)((nin + 127) / 128), 128, 0, st>>>(
-            d + o_blk, d_txoff, reinterpret_cast<uint32_t *>(d + o_inoff), reinterpret_cast<uint32_t *>(d + o_intx),
-            reinterpret_cast<uint32_t *>(d + o_inn), nin, d + o_spk, reinterpret_cast<uint32_t *>(d + o_spkoff),
-            reinterpret_cast<int64_t *>(d + o_amt), d + o_mid, d + o_stat, d + o_msg, d + o_pub, d + o_sig);
-        BCP_CUDA(cudaGetLastError());
+        rc = launch_mid_extract(c, d + o_blk, d_txoff, tx_off.data(), ntx, reinterpret_cast<uint32_t *>(d + o_inoff),
+                                reinterpret_cast<uint32_t *>(d + o_intx), reinterpret_cast<uint32_t *>(d + o_inn), in_tx.data(), nin,
+                                d + o_spk, reinterpret_cast<uint32_t *>(d + o_spkoff), reinterpret_cast<int64_t *>(d + o_amt),
+                                d + o_mid, d + o_stat, d + o_msg, d + o_pub, d + o_sig, st);
+        if (rc != BCP_OK) return rc;
         rc = bcp_ecdsa_launch(c, d + o_msg, d + o_pub, d + o_sig, nin, BCP_ECDSA_FLAG_NORMALIZE_S, d + o_ok,
                               reinterpret_cast<uint32_t *>(c->scratch), st);
         if (rc != BCP_OK) return rc;
@@ -520,12 +594,11 @@ BCP_API int bcp_gpu_blocks_connect_p2pkh(int device, size_t nblk, const uint8_t 
         BCP_CUDA(cudaMemcpyAsync(d + o_spk, spk, spk_bytes, cudaMemcpyHostToDevice, st));
         BCP_CUDA(cudaMemcpyAsync(d + o_spkoff, spk_off, (total_in + 1) * 4, cudaMemcpyHostToDevice, st));
         BCP_CUDA(cudaMemcpyAsync(d + o_amt, amounts, total_in * 8, cudaMemcpyHostToDevice, st));
-        k_tx_midstate<<<(unsigned)((total_tx + 127) / 128), 128, 0, st>>>(d + o_blk, d_txoff, total_tx, d + o_mid);
-        k_p2pkh_extract<<<(unsigned)((total_in + 127) / 128), 128, 0, st>>>(
-            d + o_blk, d_txoff, reinterpret_cast<uint32_t *>(d + o_inoff), reinterpret_cast<uint32_t *>(d + o_intx),
-            reinterpret_cast<uint32_t *>(d + o_inn), total_in, d + o_spk, reinterpret_cast<uint32_t *>(d + o_spkoff),
-            reinterpret_cast<int64_t *>(d + o_amt), d + o_mid, d + o_stat, d + o_msg, d + o_pub, d + o_sig);
-        BCP_CUDA(cudaGetLastError());
+        rc = launch_mid_extract(c, d + o_blk, d_txoff, tx_off.data(), total_tx, reinterpret_cast<uint32_t *>(d + o_inoff),
+                                reinterpret_cast<uint32_t *>(d + o_intx), reinterpret_cast<uint32_t *>(d + o_inn), in_tx.data(), total_in,
+                                d + o_spk, reinterpret_cast<uint32_t *>(d + o_spkoff), reinterpret_cast<int64_t *>(d + o_amt),
+                                d + o_mid, d + o_stat, d + o_msg, d + o_pub, d + o_sig, st);
+        if (rc != BCP_OK) return rc;
         rc = bcp_ecdsa_launch(c, d + o_msg, d + o_pub, d + o_sig, total_in, BCP_ECDSA_FLAG_NORMALIZE_S, d + o_ok,
                               reinterpret_cast<uint32_t *>(c->scratch), st);
         if (rc != BCP_OK) return rc;

@@ -22,6 +22,7 @@ struct bcp_ctx {
     uint8_t *stage = nullptr;           // device staging for the host-pointer entry points
     size_t stage_bytes = 0;
     std::vector<uint32_t> h_tx_off, h_in_off, h_in_tx, h_in_n; // host scratch of the block framing scan (reused)
+    bool block_attrs = false;           // shared-memory opt-in of the block kernels done on this device
     std::mutex mu;
 };
 
