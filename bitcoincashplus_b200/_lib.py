@@ -46,7 +46,7 @@ SIGNATURES = {
     "bcp_gpu_merkle_root_dev_static": (C.c_int, [C.c_int, vp, sz, vp, vp, vp]),
     "bcp_block_index_inputs": (C.c_long, [vp, sz, C.c_int, vp, sz, vp, vp, vp, sz, C.POINTER(C.c_long)]),
     "bcp_block_index_full": (C.c_long, [vp, sz, C.c_int, vp, vp, sz, vp, vp, vp, sz, C.POINTER(C.c_long), vp, vp, vp, sz,
-                                        C.POINTER(C.c_long)]),
+                                        C.POINTER(C.c_long), vp]),
     "bcp_gpu_block_scripts_p2pkh": (C.c_int, [C.c_int, vp, sz, vp, sz, vp, vp, vp, sz, vp, vp, vp, C.c_uint32, vp,
                                               C.POINTER(C.c_int)]),
     "bcp_gpu_block_connect_p2pkh": (C.c_int, [C.c_int, vp, sz, C.c_int, vp, vp, vp, sz, C.c_uint32, vp, vp, C.POINTER(C.c_int),

@@ -166,17 +166,18 @@ extern "C" {
 BCP_API long bcp_block_index_inputs(const uint8_t *blk, size_t len, int legacy_header, uint32_t *tx_off, size_t max_tx,
                                     uint32_t *in_off, uint32_t *in_tx, uint32_t *in_n, size_t max_inputs, long *ntx_out) {
     return bcp_block_index_full(blk, len, legacy_header, tx_off, nullptr, max_tx, in_off, in_tx, in_n, max_inputs, ntx_out,
-                                nullptr, nullptr, nullptr, 0, nullptr);
+                                nullptr, nullptr, nullptr, 0, nullptr, nullptr);
 }
 
 // The same scan, additionally reporting where each transaction's output list starts (the offset of its output count)
 // and, flat like the inputs, every output: out_off = offset of its 8-byte amount, out_tx = its transaction, out_n = its
-// index.  A block connector inserts the new coins from these without parsing anything again.  The extra arrays may be
-// NULL (max_outputs is then ignored); more than max_outputs outputs is the capacity error -2.
+// index.  A block connector inserts the new coins from these without parsing anything again.  in_key[i] = a 64-bit mix
+// of input i's outpoint (first 8 txid bytes, little-endian, XOR 0x9E3779B97F4A7C15 * vout) for hash-table lookups.  The
+// extra arrays may be NULL (max_outputs is then ignored); more than max_outputs outputs is the capacity error -2.
 BCP_API long bcp_block_index_full(const uint8_t *blk, size_t len, int legacy_header, uint32_t *tx_off, uint32_t *tx_out_off,
                                   size_t max_tx, uint32_t *in_off, uint32_t *in_tx, uint32_t *in_n, size_t max_inputs,
                                   long *ntx_out, uint32_t *out_off, uint32_t *out_tx, uint32_t *out_n, size_t max_outputs,
-                                  long *nout_out) {
+                                  long *nout_out, uint64_t *in_key) {
     size_t ocnt = 0;
     // One pass (this scan sits on the critical path of a block: nothing can launch before the offsets exist).
     // Same acceptance rules as bcp_block_index: canonical compact sizes, MAX_SIZE, everything inside the buffer.
@@ -214,6 +215,13 @@ BCP_API long bcp_block_index_full(const uint8_t *blk, size_t len, int legacy_hea
             if (!coinbase) {
                 if (cnt >= max_inputs) return -2;
                 in_off[cnt] = (uint32_t)pos; in_tx[cnt] = (uint32_t)t; in_n[cnt] = (uint32_t)i;
+                if (in_key) { /* while the bytes are in the cache: the 64-bit mix of the outpoint a hash table would use */
+                    uint64_t h8;
+                    uint32_t vout;
+                    memcpy(&h8, blk + pos, 8);
+                    memcpy(&vout, blk + pos + 32, 4);
+                    in_key[cnt] = h8 ^ (0x9E3779B97F4A7C15ull * vout);
+                }
                 cnt++;
             }
             pos += 36;

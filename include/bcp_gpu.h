@@ -154,11 +154,13 @@ BCP_API long bcp_block_index_inputs(const uint8_t *blk, size_t len, int legacy_h
 /* Same scan for callers that go on to read the outputs (a block connector inserting the new coins):
  *   tx_out_off[t] (optional)            offset of transaction t's output count
  *   out_off / out_tx / out_n (optional) every output, flat like the inputs: offset of its 8-byte amount, its
- *                                       transaction, its index; *nout_out = how many (max_outputs = capacity, -2 beyond) */
+ *                                       transaction, its index; *nout_out = how many (max_outputs = capacity, -2 beyond)
+ *   in_key (optional)                   per input, a 64-bit mix of its outpoint for hash tables:
+ *                                       le64(txid[0..8)) ^ 0x9E3779B97F4A7C15 * vout */
 BCP_API long bcp_block_index_full(const uint8_t *blk, size_t len, int legacy_header, uint32_t *tx_off, uint32_t *tx_out_off,
                                   size_t max_tx, uint32_t *in_off, uint32_t *in_tx, uint32_t *in_n, size_t max_inputs,
                                   long *ntx_out, uint32_t *out_off, uint32_t *out_tx, uint32_t *out_n, size_t max_outputs,
-                                  long *nout_out);
+                                  long *nout_out, uint64_t *in_key);
 /* The script checks alone, for any subset of a block's inputs chosen by the caller (arrays describe the subset;
  * spk_off may point into a larger offsets array).  This is the unit that shards across GPUs: one call per device
  * over its index range, verdicts AND-ed on the host like `fAllOk &= fOk` (src/checkqueue.h:77). */

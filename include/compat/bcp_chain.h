@@ -22,6 +22,8 @@
 #include <chrono>
 #include <condition_variable>
 #include <cstdint>
+#include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <functional>
 #include <memory>
@@ -77,8 +79,9 @@ public:
     size_t size() const { return live; }
     // the table is far larger than the CPU caches and every probe is a random access: callers hint the slots of the
     // next few outpoints while they work on the current one
-    void prefetch(const OutPoint &k) const {
-        const char *p = reinterpret_cast<const char *>(&slots[OutPointHash()(k) & mask]);
+    void prefetch(const OutPoint &k) const { prefetch_hash(OutPointHash()(k)); }
+    void prefetch_hash(size_t h) const {
+        const char *p = reinterpret_cast<const char *>(&slots[h & mask]);
         __builtin_prefetch(p);
         __builtin_prefetch(p + 64);
         __builtin_prefetch(p + 128); // probe line of the next slot: erase() and colliding inserts look at it
@@ -221,6 +224,29 @@ private:
     bool quit_ = false;
 };
 
+// Growable array WITHOUT value initialisation: the framing arrays are sized for the worst case a block of that length
+// could hold (an output needs 9 bytes: 900 k entries for 8 MB) while a real block uses a few percent of that; a
+// std::vector would zero-fill, and so page in, all of it.
+template <class T> struct RawBuf {
+    T *p = nullptr;
+    size_t cap = 0;
+    RawBuf() {}
+    RawBuf(const RawBuf &) = delete;
+    RawBuf &operator=(const RawBuf &) = delete;
+    ~RawBuf() { delete[] p; }
+    void need(size_t n) {
+        if (cap >= n) return;
+        delete[] p;
+        p = new T[n];
+        cap = n;
+    }
+    T *data() { return p; }
+    const T *data() const { return p; }
+    T &operator[](size_t i) { return p[i]; }
+    const T &operator[](size_t i) const { return p[i]; }
+    void swap(RawBuf &o) { std::swap(p, o.p); std::swap(cap, o.cap); }
+};
+
 class ChainValidator {
 public:
     // walk_threads: host threads for the UTXO passes (rounded down to a power of two, at most 16).  The table is split
@@ -235,6 +261,12 @@ public:
     ~ChainValidator() {
         for (Scan &a : ahead)
             if (a.th.joinable()) a.th.join();
+        if (getenv("BCP_CHAIN_DEBUG")) {
+            double f = 0, d = 0;
+            for (Scan &a : ahead) { f += a.frameSecs; d += a.deviceSecs; }
+            for (Work &w : work) { f += w.cur.frameSecs; d += w.cur.deviceSecs; }
+            fprintf(stderr, "[bcp_chain] scan threads: framing %.1f ms, device pre-checks %.1f ms in total\n", f * 1e3, d * 1e3);
+        }
         for (Work &w : work)
             for (auto &t : w.th)
                 if (t.joinable()) t.join();
@@ -284,7 +316,7 @@ public:
     void ScanAhead(const uint8_t *blk, size_t len) {
         for (Scan &a : ahead)
             if (a.blk == blk && a.len == len && (a.th.joinable() || a.valid)) return; // already on its way
-        Scan &a = ahead[(nextSlot++) % 2];
+        Scan &a = ahead[(nextSlot++) % NAHEAD];
         if (a.th.joinable()) a.th.join();
         a.valid = false;
         a.blk = blk;
@@ -314,10 +346,10 @@ public:
             uint32_t sz;
             memcpy(&sz, data + pos + 4, 4);
             if (pos + 8 + sz > len) break;
-            // the framing scans and device pre-checks of the next two blocks run on helper threads meanwhile
-            Hint hints[2];
+            // the framing scans and device pre-checks of the next few blocks run on helper threads meanwhile
+            Hint hints[NAHEAD];
             size_t nh = 0, nx = pos + 8 + (size_t)sz;
-            while (nh < 2 && nx + 8 <= len && memcmp(data + nx, magic, 4) == 0) {
+            while (nh < NAHEAD && nx + 8 <= len && memcmp(data + nx, magic, 4) == 0) {
                 uint32_t nsz;
                 memcpy(&nsz, data + nx + 4, 4);
                 if (nx + 8 + nsz > len) break;
@@ -353,8 +385,10 @@ public:
 
 private:
     struct Scan { // result of the framing scan of one block
-        std::vector<uint32_t> tx_off, tx_out_off, in_off, in_tx, in_n, out_off, out_tx, out_n;
+        RawBuf<uint32_t> tx_off, tx_out_off, in_off, in_tx, in_n, out_off, out_tx, out_n;
         std::vector<uint32_t> by_shard, shard_start; // input numbers grouped by table shard (block order inside a group)
+        RawBuf<uint64_t> in_key;                     // OutPointHash of every input's outpoint, computed by the scan
+        std::vector<uint32_t> fillTmp;
         long ntx = 0, nin = -1, nout = 0;
         const uint8_t *blk = nullptr;
         size_t len = 0;
@@ -366,7 +400,9 @@ private:
         int mutated = 0, rcTx = BCP_OK, rcEq = BCP_OK;
         uint8_t eqOk = 1;
         std::string errTx, errEq;
+        double frameSecs = 0, deviceSecs = 0; // time this slot's thread spent in each part (diagnostics)
         void Device(int dev, unsigned ehN, unsigned ehK) {
+            const auto td0 = std::chrono::steady_clock::now();
             const size_t soln = ehN ? ((size_t)1 << ehK) * (ehN / (ehK + 1) + 1) / 8 : 0;
             const size_t hdr_len = 140 + (soln < 253 ? 1 : 3) + soln;
             rcEq = rcTx = BCP_OK;
@@ -381,47 +417,49 @@ private:
                 if (rcTx != BCP_OK) errTx = bcp_gpu_last_error();
             }
             deviceDone = true;
+            deviceSecs += std::chrono::duration<double>(std::chrono::steady_clock::now() - td0).count();
         }
         void Frame(const uint8_t *b, size_t l, int shardBits) {
+            const auto tf0 = std::chrono::steady_clock::now();
             deviceDone = false;
             const size_t max_tx = l / 60 + 2, max_in = l / 41 + 2, max_out = l / 9 + 2;
-            if (tx_off.size() < max_tx + 1) { tx_off.resize(max_tx + 1); tx_out_off.resize(max_tx + 1); }
-            if (in_off.size() < max_in) { in_off.resize(max_in); in_tx.resize(max_in); in_n.resize(max_in); }
-            if (out_off.size() < max_out) { out_off.resize(max_out); out_tx.resize(max_out); out_n.resize(max_out); }
+            tx_off.need(max_tx + 1); tx_out_off.need(max_tx + 1);
+            in_off.need(max_in); in_tx.need(max_in); in_n.need(max_in); in_key.need(max_in);
+            out_off.need(max_out); out_tx.need(max_out); out_n.need(max_out);
             ntx = nout = 0;
             nin = bcp_block_index_full(b, l, 0, tx_off.data(), tx_out_off.data(), max_tx, in_off.data(), in_tx.data(), in_n.data(),
-                                       max_in, &ntx, out_off.data(), out_tx.data(), out_n.data(), max_out, &nout);
+                                       max_in, &ntx, out_off.data(), out_tx.data(), out_n.data(), max_out, &nout, in_key.data());
             // counting sort of the inputs by shard, here (on the scan-ahead thread) so that each worker of pass A only
             // ever touches its own inputs
             const size_t S = (size_t)1 << shardBits;
             shard_start.assign(S + 1, 0);
             if (nin > 0) {
                 by_shard.resize((size_t)nin);
-                std::vector<uint8_t> sh((size_t)nin);
-                for (long i = 0; i < nin; i++) {
-                    OutPoint op;
-                    memcpy(op.b, b + in_off[(size_t)i], 36);
-                    sh[(size_t)i] = shardBits ? (uint8_t)(OutPointHash()(op) >> (64 - shardBits)) : 0;
-                    shard_start[sh[(size_t)i] + 1]++;
-                }
+                const int sh = 64 - shardBits;
+                if (shardBits)
+                    for (long i = 0; i < nin; i++) shard_start[(size_t)(in_key[(size_t)i] >> sh) + 1]++;
+                else
+                    shard_start[1] = (uint32_t)nin;
                 for (size_t k = 0; k < S; k++) shard_start[k + 1] += shard_start[k];
-                std::vector<uint32_t> fill(shard_start.begin(), shard_start.end() - 1);
-                for (long i = 0; i < nin; i++) by_shard[fill[sh[(size_t)i]]++] = (uint32_t)i;
+                fillTmp.assign(shard_start.begin(), shard_start.end() - 1);
+                for (long i = 0; i < nin; i++) by_shard[fillTmp[shardBits ? (size_t)(in_key[(size_t)i] >> sh) : 0]++] = (uint32_t)i;
             }
             blk = b;
             len = l;
             valid = true;
+            frameSecs += std::chrono::duration<double>(std::chrono::steady_clock::now() - tf0).count();
         }
     };
     static void SwapScan(Scan &a, Scan &b) {
         a.tx_off.swap(b.tx_off); a.tx_out_off.swap(b.tx_out_off); a.in_off.swap(b.in_off); a.in_tx.swap(b.in_tx); a.in_n.swap(b.in_n);
         a.out_off.swap(b.out_off); a.out_tx.swap(b.out_tx); a.out_n.swap(b.out_n);
-        a.by_shard.swap(b.by_shard); a.shard_start.swap(b.shard_start);
+        a.by_shard.swap(b.by_shard); a.shard_start.swap(b.shard_start); a.in_key.swap(b.in_key);
         a.txids.swap(b.txids); a.errTx.swap(b.errTx); a.errEq.swap(b.errEq);
         std::swap(a.root, b.root); std::swap(a.hash, b.hash); std::swap(a.mutated, b.mutated); std::swap(a.rcTx, b.rcTx);
         std::swap(a.rcEq, b.rcEq); std::swap(a.eqOk, b.eqOk); std::swap(a.deviceDone, b.deviceDone);
         std::swap(a.ntx, b.ntx); std::swap(a.nin, b.nin); std::swap(a.nout, b.nout); std::swap(a.blk, b.blk); std::swap(a.len, b.len);
         std::swap(a.valid, b.valid);
+        std::swap(a.frameSecs, b.frameSecs); std::swap(a.deviceSecs, b.deviceSecs);
     }
 
     // what pass A / C found for one input; 128 bytes so that two threads never write the same cache line
@@ -507,27 +545,40 @@ private:
         w.spentUpTo = (size_t)nin;
         team->Run([&](int s_) { PassA(w, s_); });
         walk[0] += Secs(t2, now());
-        size_t unresolved = 0;
-        for (size_t i = 0; i < (size_t)nin; i++) {
-            Staged &st = w.stage[i];
-            if (st.state == ST_BIG) { // rare: a script too long for the staging slot; done here, on one thread
-                OutPoint op;
-                memcpy(op.b, blk + cur.in_off[i], 36);
-                CoinTable &T = ShardOf(op);
-                CoinSlot *c = T.find(op);
-                if (!c) { // spent a moment ago by another input of this block
-                    st.state = ST_MISS;
-                    unresolved++;
-                    continue;
+        // what pass A left open, counted by the team over contiguous slices of the staging records
+        size_t unresolved = 0, nBig = 0;
+        {
+            const int P = team->size();
+            std::vector<size_t> miss((size_t)P, 0), big((size_t)P, 0);
+            team->Run([&](int s_) {
+                const size_t lo = (size_t)nin * (size_t)s_ / (size_t)P, hi = (size_t)nin * ((size_t)s_ + 1) / (size_t)P;
+                size_t m = 0, b = 0;
+                for (size_t i = lo; i < hi; i++) {
+                    m += w.stage[i].state == ST_MISS;
+                    b += w.stage[i].state == ST_BIG;
                 }
-                st.amount = c->amount;
-                st.len = c->spk_len;
-                st.big = (uint32_t)w.bigStore.size();
-                w.bigStore.emplace_back(CoinTable::script(*c), CoinTable::script(*c) + c->spk_len);
-                T.erase(c);
-            } else if (st.state == ST_MISS) {
+                miss[(size_t)s_] = m;
+                big[(size_t)s_] = b;
+            });
+            for (int k = 0; k < P; k++) { unresolved += miss[(size_t)k]; nBig += big[(size_t)k]; }
+        }
+        for (size_t i = 0; nBig && i < (size_t)nin; i++) { // rare: scripts too long for the staging slot, done on one thread
+            Staged &st = w.stage[i];
+            if (st.state != ST_BIG) continue;
+            OutPoint op;
+            memcpy(op.b, blk + cur.in_off[i], 36);
+            CoinTable &T = ShardOf(op);
+            CoinSlot *c = T.find(op);
+            if (!c) { // spent a moment ago by another input of this block
+                st.state = ST_MISS;
                 unresolved++;
+                continue;
             }
+            st.amount = c->amount;
+            st.len = c->spk_len;
+            st.big = (uint32_t)w.bigStore.size();
+            w.bigStore.emplace_back(CoinTable::script(*c), CoinTable::script(*c) + c->spk_len);
+            T.erase(c);
         }
         auto t3 = now();
         if (thDev.joinable()) thDev.join();
@@ -659,7 +710,7 @@ private:
         CoinTable &T = *shards[(size_t)w];
         const Scan &cur = wk.cur;
         const uint8_t *blk = wk.blk;
-        const size_t RING = 8;
+        const size_t RING = 12;
         size_t ring[RING], head = 0, count = 0;
         auto take = [&](size_t i) {
             OutPoint op;
@@ -676,9 +727,11 @@ private:
         };
         for (size_t q = cur.shard_start[(size_t)w]; q < cur.shard_start[(size_t)w + 1]; q++) {
             const size_t i = cur.by_shard[q];
-            OutPoint op;
-            memcpy(op.b, blk + cur.in_off[i], 36);
-            T.prefetch(op);
+            T.prefetch_hash((size_t)cur.in_key[i]);      /* the table slot, from the key the scan computed ...      */
+            __builtin_prefetch(blk + cur.in_off[i]);     /* ... the outpoint bytes, last touched by the scan thread */
+            __builtin_prefetch(blk + cur.in_off[i] + 35);
+            __builtin_prefetch(&wk.stage[i], 1);         /* ... and the staging record this input will be written to */
+            __builtin_prefetch(reinterpret_cast<const char *>(&wk.stage[i]) + 64, 1);
             if (count == RING) {
                 take(ring[head]);
                 ring[head] = i;
@@ -716,6 +769,7 @@ private:
             if (ShardIndex(op) != w) continue;
             memcpy(op.b + 8, &txids[(size_t)cur.out_tx[o] * 32 + 8], 24);
             T.prefetch(op);
+            __builtin_prefetch(blk + cur.out_off[o]); /* amount + script of the output, read when it is inserted */
             if (count == RING) {
                 put(ring[head]);
                 ring[head] = o;
@@ -727,23 +781,33 @@ private:
         for (size_t k = 0; k < count; k++) put(ring[(head + k) % RING]);
     }
     // staging records -> the concatenated scriptPubKeys / offsets / amounts the script-check call takes
-    void BuildStaging(Work &w) {
+    void BuildStaging(Work &w) { // two rounds of the team over contiguous slices: lengths, then the copies
         const size_t nin = (size_t)w.cur.nin;
+        const int P = team->size();
         w.spk_off.resize(nin + 1);
         w.amounts.resize(nin);
-        size_t total = 0;
-        for (size_t i = 0; i < nin; i++) total += w.stage[i].len;
-        w.spk_cat.resize(total + 1);
-        uint32_t o = 0;
-        for (size_t i = 0; i < nin; i++) {
-            const Staged &s = w.stage[i];
-            w.spk_off[i] = o;
-            w.amounts[i] = s.amount;
-            const uint8_t *src = (s.state == ST_BIG || s.state == ST_INBLOCK_BIG) ? w.bigStore[s.big].data() : s.spk;
-            memcpy(&w.spk_cat[o], src, s.len);
-            o += s.len;
-        }
-        w.spk_off[nin] = o;
+        std::vector<size_t> sum((size_t)P + 1, 0);
+        team->Run([&](int s_) {
+            const size_t lo = nin * (size_t)s_ / (size_t)P, hi = nin * ((size_t)s_ + 1) / (size_t)P;
+            size_t t = 0;
+            for (size_t i = lo; i < hi; i++) t += w.stage[i].len;
+            sum[(size_t)s_ + 1] = t;
+        });
+        for (int k = 0; k < P; k++) sum[(size_t)k + 1] += sum[(size_t)k];
+        w.spk_cat.resize(sum[(size_t)P] + 1);
+        team->Run([&](int s_) {
+            const size_t lo = nin * (size_t)s_ / (size_t)P, hi = nin * ((size_t)s_ + 1) / (size_t)P;
+            uint32_t o = (uint32_t)sum[(size_t)s_];
+            for (size_t i = lo; i < hi; i++) {
+                const Staged &s = w.stage[i];
+                w.spk_off[i] = o;
+                w.amounts[i] = s.amount;
+                const uint8_t *src = (s.state == ST_BIG || s.state == ST_INBLOCK_BIG) ? w.bigStore[s.big].data() : s.spk;
+                memcpy(&w.spk_cat[o], src, s.len);
+                o += s.len;
+            }
+        });
+        w.spk_off[nin] = (uint32_t)sum[(size_t)P];
     }
     static uint64_t ReadCompact(const uint8_t *p, size_t &pos) { // already validated by the framing scan
         uint8_t c = p[pos++];
@@ -785,7 +849,8 @@ private:
     int shardBits;
     std::vector<std::unique_ptr<CoinTable>> shards;
     std::unique_ptr<WorkerTeam> team;
-    Scan ahead[2];
+    static const unsigned NAHEAD = 3; // blocks being scanned / pre-checked ahead of the one being connected
+    Scan ahead[NAHEAD];
     unsigned nextSlot = 0;
     Work work[2];
     int lastWork = 0;

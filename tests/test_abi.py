@@ -165,10 +165,14 @@ def test_block_index_full_lists_inputs_and_outputs():
         a = {k: np.zeros(n, dtype=np.uint32) for k, n in (("tx", mt + 1), ("txo", mt + 1), ("io", mi), ("it", mi), ("in", mi),
                                                           ("oo", mo), ("ot", mo), ("on", mo))}
         ntx, nout = C.c_long(0), C.c_long(0)
+        keys = np.zeros(mi, dtype=np.uint64)
         nin = L.bcp_block_index_full(blk, len(blk), int(legacy), a["tx"].ctypes.data, a["txo"].ctypes.data, mt, a["io"].ctypes.data,
                                      a["it"].ctypes.data, a["in"].ctypes.data, mi, C.byref(ntx), a["oo"].ctypes.data,
-                                     a["ot"].ctypes.data, a["on"].ctypes.data, mo, C.byref(nout))
+                                     a["ot"].ctypes.data, a["on"].ctypes.data, mo, C.byref(nout), keys.ctypes.data)
         assert (nin, ntx.value, nout.value) == (len(ins), len(tx_off) - 1, len(outs))
+        for (pos, _, _), k in zip(ins, keys[:nin]):
+            want = int.from_bytes(blk[pos:pos + 8], "little") ^ ((0x9E3779B97F4A7C15 * int.from_bytes(blk[pos + 32:pos + 36], "little")) & (2**64 - 1))
+            assert int(k) == want
         assert list(a["tx"][:ntx.value + 1]) == tx_off and list(a["txo"][:ntx.value]) == tx_out
         assert list(zip(a["io"][:nin], a["it"][:nin], a["in"][:nin])) == ins
         assert list(zip(a["oo"][:nout.value], a["ot"][:nout.value], a["on"][:nout.value])) == outs
@@ -176,6 +180,6 @@ def test_block_index_full_lists_inputs_and_outputs():
         if len(outs) > 1:
             assert L.bcp_block_index_full(blk, len(blk), int(legacy), a["tx"].ctypes.data, None, mt, a["io"].ctypes.data,
                                           a["it"].ctypes.data, a["in"].ctypes.data, mi, C.byref(ntx), a["oo"].ctypes.data,
-                                          a["ot"].ctypes.data, a["on"].ctypes.data, len(outs) - 1, C.byref(nout)) == -2
+                                          a["ot"].ctypes.data, a["on"].ctypes.data, len(outs) - 1, C.byref(nout), None) == -2
         assert L.bcp_block_index_full(blk, len(blk), int(legacy), a["tx"].ctypes.data, None, mt, a["io"].ctypes.data,
-                                      a["it"].ctypes.data, a["in"].ctypes.data, mi, C.byref(ntx), None, None, None, 0, None) == len(ins)
+                                      a["it"].ctypes.data, a["in"].ctypes.data, mi, C.byref(ntx), None, None, None, 0, None, None) == len(ins)
