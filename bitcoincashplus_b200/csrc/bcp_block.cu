@@ -206,9 +206,13 @@ BCP_API long bcp_block_index_full(const uint8_t *blk, size_t len, int legacy_hea
         BCP_RD_COMPACT(nin);
         bool coinbase = false;
         if (nin == 1 && pos + 36 <= len) {
-            coinbase = true;
-            for (int b = 0; b < 32; b++) coinbase = coinbase && blk[pos + b] == 0;
-            for (int b = 32; b < 36; b++) coinbase = coinbase && blk[pos + b] == 0xFF;
+            uint64_t first8;
+            memcpy(&first8, blk + pos, 8);
+            if (first8 == 0) { /* a real txid practically never starts with eight zero bytes: look closer only then */
+                coinbase = true;
+                for (int b = 8; b < 32; b++) coinbase = coinbase && blk[pos + b] == 0;
+                for (int b = 32; b < 36; b++) coinbase = coinbase && blk[pos + b] == 0xFF;
+            }
         }
         for (uint64_t i = 0; i < nin; i++) {
             if (pos + 36 > len) return -1;
