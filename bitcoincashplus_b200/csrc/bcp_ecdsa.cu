@@ -33,6 +33,9 @@
 #endif
 /* signatures per slice: 16 full waves of the point kernel on a 148-SM part (148 SMs x 512 resident threads) */
 #define BCP_WAVE ((size_t)148 * 512)
+#ifndef BCP_POINT_SMALL_TPB
+#define BCP_POINT_SMALL_TPB 128u
+#endif
 #define BCP_SLICE (16 * BCP_WAVE)
 #define BCP_E2E_CHUNK (3 * BCP_WAVE)
 #define BCP_SIG_SCRATCH_WORDS (BCP_REC_WORDS + BCP_QTAB_WORDS) /* 80-byte record + 768-byte table per signature */
@@ -153,8 +156,12 @@ int bcp_ecdsa_launch(bcp_ctx *c, const uint8_t *d_msg, const uint8_t *d_pub, con
         else if (K >= 16) k_ecdsa_prep<16><<<prep_blocks, 128, 0, st>>>(d_msg + 32 * off, d_sig + 64 * off, m, flags, d_rec);
         else if (K >= 8) k_ecdsa_prep<8><<<prep_blocks, 128, 0, st>>>(d_msg + 32 * off, d_sig + 64 * off, m, flags, d_rec);
         else k_ecdsa_prep<4><<<prep_blocks, 128, 0, st>>>(d_msg + 32 * off, d_sig + 64 * off, m, flags, d_rec);
-        unsigned blocks = (unsigned)((m + BCP_POINT_THREADS - 1) / BCP_POINT_THREADS);
-        k_ecdsa_point<<<blocks, BCP_POINT_THREADS, 0, st>>>(d_pub + 65 * off, d_sig + 64 * off, m, d_rec, d_tab, c->gcomb,
+        // Less than about one wave: smaller thread blocks spread the signatures evenly over the SMs (the kernel ends when
+        // the fullest SM does); from a wave up, 256-thread blocks keep the warps of an SM in the same code region.
+        static const int forced_tpb = getenv("BCP_POINT_TPB") ? atoi(getenv("BCP_POINT_TPB")) : 0;
+        const unsigned tpb = forced_tpb ? (unsigned)forced_tpb : (m <= BCP_WAVE ? BCP_POINT_SMALL_TPB : BCP_POINT_THREADS);
+        unsigned blocks = (unsigned)((m + tpb - 1) / tpb);
+        k_ecdsa_point<<<blocks, tpb, 0, st>>>(d_pub + 65 * off, d_sig + 64 * off, m, d_rec, d_tab, c->gcomb,
                                                            d_ok + off);
     }
     BCP_CUDA(cudaGetLastError());
