@@ -407,12 +407,17 @@ BCP_API int bcp_gpu_block_connect_p2pkh(int device, const uint8_t *blk, size_t l
     }
     BCP_CUDA(cudaMemcpyAsync(d + o_txoff, tx_off.data(), (ntx + 1) * 4, cudaMemcpyHostToDevice, st));
     uint32_t *d_txoff = reinterpret_cast<uint32_t *>(d + o_txoff);
-    // txids + Merkle
-    rc = bcp_sha256d_offsets_dev(c, d + o_blk, d_txoff, ntx, d + o_txid, st);
+    // txids + Merkle on the second stream, beside the script checks (nothing below needs them)
+    cudaStream_t st2 = c->copy_stream;
+    BCP_CUDA(cudaEventRecord(c->ev[0], st));
+    BCP_CUDA(cudaStreamWaitEvent(st2, c->ev[0], 0));
+    rc = bcp_sha256d_offsets_dev(c, d + o_blk, d_txoff, ntx, d + o_txid, st2);
     if (rc != BCP_OK) return rc;
     int *d_flags = reinterpret_cast<int *>(d + o_root + 32);
-    rc = bcp_merkle_dev(c, d + o_txid, ntx, d + o_root, d_flags, reinterpret_cast<uint32_t *>(d + o_mtmp), st);
+    rc = bcp_merkle_dev(c, d + o_txid, ntx, d + o_root, d_flags, reinterpret_cast<uint32_t *>(d + o_mtmp), st2);
     if (rc != BCP_OK) return rc;
+    if (txids) BCP_CUDA(cudaMemcpyAsync(txids, d + o_txid, (size_t)ntx * 32, cudaMemcpyDeviceToHost, st2));
+    BCP_CUDA(cudaEventRecord(c->ev[1], st2));
     int one = 1;
     BCP_CUDA(cudaMemcpyAsync(d_flags + 1, &one, sizeof(int), cudaMemcpyHostToDevice, st));
     if (nin) {
@@ -434,7 +439,7 @@ BCP_API int bcp_gpu_block_connect_p2pkh(int device, const uint8_t *blk, size_t l
         BCP_CUDA(cudaGetLastError());
         BCP_CUDA(cudaMemcpyAsync(script_err, d + o_err, nin, cudaMemcpyDeviceToHost, st));
     }
-    if (txids) BCP_CUDA(cudaMemcpyAsync(txids, d + o_txid, (size_t)ntx * 32, cudaMemcpyDeviceToHost, st));
+    BCP_CUDA(cudaStreamWaitEvent(st, c->ev[1], 0));
     uint8_t res[40];
     BCP_CUDA(cudaMemcpyAsync(res, d + o_root, 40, cudaMemcpyDeviceToHost, st));
     BCP_CUDA(cudaStreamSynchronize(st));
