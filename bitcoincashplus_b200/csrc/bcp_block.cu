@@ -187,10 +187,10 @@ BCP_API long bcp_block_index_full(const uint8_t *blk, size_t len, int legacy_hea
         pos = 80;
     } else {
         pos = 140;
-        if (len < 140 || !rd_compact_h(blk, len, &pos, &v)) return -1;
+        if (len < 140 || !rd_compact_canon(blk, len, &pos, &v)) return -1;
         pos += v;
     }
-    if (pos > len || !rd_compact_h(blk, len, &pos, &ntx)) return -1;
+    if (pos > len || !rd_compact_canon(blk, len, &pos, &ntx)) return -1;
     if (ntx > max_tx) return -2;
     size_t cnt = 0;
 #define BCP_RD_COMPACT(dst)                                                                  \
@@ -205,7 +205,7 @@ BCP_API long bcp_block_index_full(const uint8_t *blk, size_t len, int legacy_hea
         pos += 4;
         BCP_RD_COMPACT(nin);
         bool coinbase = false;
-        if (nin == 1 && pos + 36 <= len) {
+        if (in_off && nin == 1 && pos + 36 <= len) {
             uint64_t first8;
             memcpy(&first8, blk + pos, 8);
             if (first8 == 0) { /* a real txid practically never starts with eight zero bytes: look closer only then */
@@ -216,7 +216,7 @@ BCP_API long bcp_block_index_full(const uint8_t *blk, size_t len, int legacy_hea
         }
         for (uint64_t i = 0; i < nin; i++) {
             if (pos + 36 > len) return -1;
-            if (!coinbase) {
+            if (!coinbase && in_off) {
                 if (cnt >= max_inputs) return -2;
                 in_off[cnt] = (uint32_t)pos; in_tx[cnt] = (uint32_t)t; in_n[cnt] = (uint32_t)i;
                 if (in_key) { /* while the bytes are in the cache: the 64-bit mix of the outpoint a hash table would use */

@@ -168,56 +168,12 @@ extern "C" {
 
 // Compact-size + transaction framing scan (src/serialize.h:260-300, src/primitives/transaction.h:223-243,
 // header layout src/primitives/block.h:49-73).  Sequential byte parsing: stays on the host by design.
-static int rd_compact(const uint8_t *p, size_t len, size_t *pos, uint64_t *v) {
-    if (*pos >= len) return 0;
-    uint8_t ch = p[(*pos)++];
-    if (ch < 253) { *v = ch; return 1; }
-    int nb = ch == 253 ? 2 : ch == 254 ? 4 : 8;
-    if (*pos + nb > len) return 0;
-    uint64_t x = 0;
-    for (int i = 0; i < nb; i++) x |= (uint64_t)p[*pos + i] << (8 * i);
-    *pos += nb;
-    if ((nb == 2 && x < 253) || (nb == 4 && x < 0x10000ull) || (nb == 8 && x < 0x100000000ull)) return 0; /* non-canonical */
-    if (x > 0x02000000ull) return 0;                                                                        /* MAX_SIZE */
-    *v = x;
-    return 1;
-}
 BCP_API long bcp_block_index(const uint8_t *blk, size_t len, int legacy_header, uint32_t *tx_off, size_t max_tx) {
-    size_t pos;
-    uint64_t v, ntx;
-    if (legacy_header) {
-        pos = 80;
-    } else {
-        pos = 140;
-        if (len < 140 || !rd_compact(blk, len, &pos, &v)) return -1;
-        pos += v;
-    }
-    if (pos > len || !rd_compact(blk, len, &pos, &ntx)) return -1;
-    if (ntx > max_tx) return -2;
-    for (uint64_t t = 0; t < ntx; t++) {
-        tx_off[t] = (uint32_t)pos;
-        uint64_t nin, nout, sl;
-        if (pos + 4 > len) return -1;
-        pos += 4;
-        if (!rd_compact(blk, len, &pos, &nin)) return -1;
-        for (uint64_t i = 0; i < nin; i++) {
-            if (pos + 36 > len) return -1;
-            pos += 36;
-            if (!rd_compact(blk, len, &pos, &sl) || pos + sl + 4 > len) return -1;
-            pos += sl + 4;
-        }
-        if (!rd_compact(blk, len, &pos, &nout)) return -1;
-        for (uint64_t i = 0; i < nout; i++) {
-            if (pos + 8 > len) return -1;
-            pos += 8;
-            if (!rd_compact(blk, len, &pos, &sl) || pos + sl > len) return -1;
-            pos += sl;
-        }
-        if (pos + 4 > len) return -1;
-        pos += 4;
-    }
-    tx_off[ntx] = (uint32_t)pos;
-    return (long)ntx;
+    // one scanner for the whole library: the framing scan of bcp_block.cu without its input and output lists
+    long ntx = 0;
+    const long rc = bcp_block_index_full(blk, len, legacy_header, tx_off, nullptr, max_tx, nullptr, nullptr, nullptr, 0, &ntx,
+                                         nullptr, nullptr, nullptr, 0, nullptr, nullptr);
+    return rc < 0 ? rc : ntx;
 }
 
 BCP_API int bcp_gpu_sha256d_batch_dev(int device, const uint8_t *d_data, const uint32_t *d_off, size_t count,

@@ -183,3 +183,37 @@ def test_block_index_full_lists_inputs_and_outputs():
                                           a["ot"].ctypes.data, a["on"].ctypes.data, len(outs) - 1, C.byref(nout), None) == -2
         assert L.bcp_block_index_full(blk, len(blk), int(legacy), a["tx"].ctypes.data, None, mt, a["io"].ctypes.data,
                                       a["it"].ctypes.data, a["in"].ctypes.data, mi, C.byref(ntx), None, None, None, 0, None, None) == len(ins)
+
+
+def test_scanners_reject_non_canonical_counts(oracle):
+    """ReadCompactSize (src/serialize.h:260-300) refuses a count written in a longer form than needed; so do all three
+    scan entry points — for the transaction count, an input count and a script length alike — and the oracle."""
+    import ctypes as C
+
+    import bitcoincashplus_b200 as bcp
+    import synth
+
+    L = bcp.lib()
+    blk = synth.synthetic_block(ntx=5, sign=False)
+    tx_off, tx_out, ins, outs = _py_scan(blk, False)
+    base = tx_off[0] - 1                       # the transaction count byte (6 transactions incl. the coinbase)
+    assert blk[base] == 6
+    variants = {
+        "ntx": blk[:base] + b"\xfd\x06\x00" + blk[base + 1:],
+        "nin": blk[:tx_off[1] + 4] + b"\xfd\x01\x00" + blk[tx_off[1] + 5:],
+        "script_len": blk[:ins[0][0] + 36] + b"\xfd" + blk[ins[0][0] + 36:ins[0][0] + 37] + b"\x00" + blk[ins[0][0] + 37:],
+    }
+    mt, mi, mo = len(blk) // 60 + 8, len(blk) // 41 + 8, len(blk) // 9 + 8
+    a = [np.zeros(n, dtype=np.uint32) for n in (mt + 1, mt + 1, mi, mi, mi, mo, mo, mo)]
+    ntx, nout = C.c_long(0), C.c_long(0)
+    for name, bad in variants.items():
+        assert L.bcp_block_index(bad, len(bad), 0, a[0].ctypes.data, mt) == -1, name
+        assert L.bcp_block_index_inputs(bad, len(bad), 0, a[0].ctypes.data, mt, a[2].ctypes.data, a[3].ctypes.data,
+                                        a[4].ctypes.data, mi, C.byref(ntx)) == -1, name
+        assert L.bcp_block_index_full(bad, len(bad), 0, a[0].ctypes.data, a[1].ctypes.data, mt, a[2].ctypes.data, a[3].ctypes.data,
+                                      a[4].ctypes.data, mi, C.byref(ntx), a[5].ctypes.data, a[6].ctypes.data, a[7].ctypes.data, mo,
+                                      C.byref(nout), None) == -1, name
+        with pytest.raises(Exception):
+            n, _ = oracle.block_index(bad, False)
+            assert n >= 0
+    assert L.bcp_block_index(blk, len(blk), 0, a[0].ctypes.data, mt) == 6
