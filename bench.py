@@ -251,17 +251,40 @@ def window_bench(eng, args, bcp, sync=None, W=8):
     for t in th:
         t.join()
     s2 = (time.perf_counter() - t0) / (2 * reps)
+    # four host threads on four lanes, windows of four blocks: finer interleaving of copies, scans and kernels
+    W4, reps4 = 4, 10
+    off4 = pinned(off0[: n * W4 + 1].copy())
+    engs4 = [eng, eng2] + [bcp.Engine(eng.device & 0xFF, lane=k) for k in (2, 3)]
+    args4 = (blks[:W4], cat[: int(off0[n * W4])], off4, am[: n * W4], [n] * W4, synth.POSTFORK_FLAGS)
+    for e in engs4:
+        assert all(e.blocks_connect_p2pkh(*args4)["all_ok"])
+
+    def worker4(e):
+        for _ in range(reps4):
+            e.blocks_connect_p2pkh(*args4)
+
+    th = [threading.Thread(target=worker4, args=(e,)) for e in engs4]
+    if sync is not None:
+        sync(0.0)
+    t0 = time.perf_counter()
+    for t in th:
+        t.start()
+    for t in th:
+        t.join()
+    s4 = (time.perf_counter() - t0) / (4 * reps4)
     world = 1
     if sync is not None:  # every rank measured its own GPU at the same time: take the slowest
         world = sync(0.0, count=True)
-        s, s2 = sync(s), sync(s2)
+        s, s2, s4 = sync(s), sync(s2), sync(s4)
         if int(os.environ.get("RANK", "0")) != 0:
             return None
     return {"window_blocks": W, "inputs_per_block": n, "gpus": world, "gpu_ms_per_window": s * 1e3, "gpu_ms_per_block": s * 1e3 / W,
             "gpu_blocks_per_s": world * W / s, "gpu_inputs_per_s": world * W * n / s,
             "two_lanes": {"gpu_ms_per_window": s2 * 1e3, "gpu_blocks_per_s": world * W / s2, "gpu_inputs_per_s": world * W * n / s2},
+            "four_lanes": {"window_blocks": W4, "gpu_ms_per_window": s4 * 1e3, "gpu_blocks_per_s": world * W4 / s4,
+                           "gpu_inputs_per_s": world * W4 * n / s4},
             "timed": "bcp_gpu_blocks_connect_p2pkh end to end (host framing scans on W threads + H2D + kernels + D2H), pinned "
-                     "host buffers; two_lanes = two host threads on two lanes of the same GPU"}
+                     "host buffers; two_lanes / four_lanes = that many host threads, each on its own lane of the same GPU"}
 
 
 def equihash_bench(eng):

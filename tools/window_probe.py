@@ -32,6 +32,24 @@ off0 = np.zeros(n * W + 1, dtype=np.uint32)
 off0[1:] = np.cumsum(np.array([len(x) for x in spk] * W, dtype=np.uint64))
 blks = [pinned(np.frombuffer(blk, dtype=np.uint8)) for _ in range(W)]
 cat, off, am = pinned(np.frombuffer(b"".join(spk) * W, dtype=np.uint8)), pinned(off0), pinned(np.asarray(list(amt) * W, dtype=np.int64))
+lanes = int(sys.argv[3]) if len(sys.argv) > 3 else 1
+if lanes > 1:
+    import threading
+    engs = [eng] + [bcp.Engine(0, lane=k) for k in range(1, lanes)]
+    for e in engs:
+        e.blocks_connect_p2pkh(blks, cat, off, am, [n] * W, synth.POSTFORK_FLAGS)
+
+    def work(e):
+        for _ in range(reps):
+            e.blocks_connect_p2pkh(blks, cat, off, am, [n] * W, synth.POSTFORK_FLAGS)
+
+    th = [threading.Thread(target=work, args=(e,)) for e in engs]
+    t0 = time.perf_counter()
+    [t.start() for t in th]
+    [t.join() for t in th]
+    dt = time.perf_counter() - t0
+    print("W=%d lanes=%d: %.2f ms per window, %.0f blocks/s" % (W, lanes, dt * 1e3 / (reps * lanes), W * reps * lanes / dt))
+    sys.exit(0)
 for r in range(reps):
     t0 = time.perf_counter()
     res = eng.blocks_connect_p2pkh(blks, cat, off, am, [n] * W, synth.POSTFORK_FLAGS)
