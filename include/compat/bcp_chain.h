@@ -274,11 +274,13 @@ public:
 
     bool Init(std::string &err) {
         if (devs.empty()) { err = "no device"; return false; }
+        // Lanes (independent contexts on one GPU): the two blocks ConnectFile keeps in flight send their script checks
+        // through lanes 0 and 1 of each device, so that block b+1's copies and extraction run under block b's ECDSA
+        // kernels; header checks and txids of the blocks being scanned ahead go through lane 2 of the first device.
         for (int d : devs)
-            if (bcp_gpu_init(d) != BCP_OK) { err = bcp_gpu_last_error(); return false; }
-        // header checks and txids go through a lane of their own, so that they do not queue behind the script checks of
-        // the block before (ConnectFile keeps two blocks in flight)
-        devAux = BCP_DEVICE_LANE(devs[0] & 0xFF, ((devs[0] >> 8) + 1) % 4);
+            for (int lane = 0; lane < 2; lane++)
+                if (bcp_gpu_init(BCP_DEVICE_LANE(d & 0xFF, lane)) != BCP_OK) { err = bcp_gpu_last_error(); return false; }
+        devAux = BCP_DEVICE_LANE(devs[0] & 0xFF, 2);
         if (bcp_gpu_init(devAux) != BCP_OK) { err = bcp_gpu_last_error(); return false; }
         return true;
     }
@@ -604,7 +606,7 @@ private:
                 const size_t lo = std::min((size_t)nin, g * per), hi = std::min((size_t)nin, lo + per);
                 if (lo >= hi) continue;
                 Work *pw = &w;
-                const int dev = devs[g];
+                const int dev = BCP_DEVICE_LANE(devs[g] & 0xFF, (int)(&w - work)); /* work[0] -> lane 0, work[1] -> lane 1 */
                 const uint32_t fl = flags;
                 w.th.emplace_back([pw, g, lo, hi, dev, fl] {
                     int all = 0;
@@ -849,7 +851,7 @@ private:
     int shardBits;
     std::vector<std::unique_ptr<CoinTable>> shards;
     std::unique_ptr<WorkerTeam> team;
-    static const unsigned NAHEAD = 3; // blocks being scanned / pre-checked ahead of the one being connected
+    static const unsigned NAHEAD = 4; // blocks being scanned / pre-checked ahead of the one being connected
     Scan ahead[NAHEAD];
     unsigned nextSlot = 0;
     Work work[2];
