@@ -328,7 +328,7 @@ public:
         Scan *pa = &a;
         a.th = std::thread([pa, blk, len, sb, dev, n_, k_] {
             pa->Frame(blk, len, sb);
-            pa->Device(dev, n_, k_);
+            pa->Device(dev, n_, k_, sb);
         });
     }
     const uint8_t *LastBlockHash() const { return lastHash; }
@@ -391,6 +391,8 @@ private:
         std::vector<uint32_t> by_shard, shard_start; // input numbers grouped by table shard (block order inside a group)
         RawBuf<uint64_t> in_key;                     // OutPointHash of every input's outpoint, computed by the scan
         std::vector<uint32_t> fillTmp;
+        std::vector<uint32_t> out_by_shard, out_shard_start; // output numbers grouped by shard (needs the txids: Device())
+        RawBuf<uint64_t> out_key;
         long ntx = 0, nin = -1, nout = 0;
         const uint8_t *blk = nullptr;
         size_t len = 0;
@@ -403,7 +405,7 @@ private:
         uint8_t eqOk = 1;
         std::string errTx, errEq;
         double frameSecs = 0, deviceSecs = 0; // time this slot's thread spent in each part (diagnostics)
-        void Device(int dev, unsigned ehN, unsigned ehK) {
+        void Device(int dev, unsigned ehN, unsigned ehK, int shardBits) {
             const auto td0 = std::chrono::steady_clock::now();
             const size_t soln = ehN ? ((size_t)1 << ehK) * (ehN / (ehK + 1) + 1) / 8 : 0;
             const size_t hdr_len = 140 + (soln < 253 ? 1 : 3) + soln;
@@ -417,6 +419,25 @@ private:
                 txids.resize((size_t)ntx * 32);
                 rcTx = bcp_gpu_sha256d_txids_merkle(dev, blk, len, tx_off.data(), (size_t)ntx, txids.data(), root, &mutated);
                 if (rcTx != BCP_OK) errTx = bcp_gpu_last_error();
+            }
+            // the new coins' hash keys need the txids; with them the outputs are grouped by shard here, off the
+            // connecting thread, exactly like the inputs were by Frame()
+            const size_t S = (size_t)1 << shardBits;
+            out_shard_start.assign(S + 1, 0);
+            if (rcTx == BCP_OK && nin >= 0 && nout > 0) {
+                out_key.need((size_t)nout);
+                out_by_shard.resize((size_t)nout);
+                const int sh = 64 - shardBits;
+                for (long o = 0; o < nout; o++) {
+                    uint64_t h8;
+                    memcpy(&h8, &txids[(size_t)out_tx[(size_t)o] * 32], 8);
+                    const uint64_t k = h8 ^ (0x9E3779B97F4A7C15ull * out_n[(size_t)o]);
+                    out_key[(size_t)o] = k;
+                    out_shard_start[(shardBits ? (size_t)(k >> sh) : 0) + 1]++;
+                }
+                for (size_t k = 0; k < S; k++) out_shard_start[k + 1] += out_shard_start[k];
+                fillTmp.assign(out_shard_start.begin(), out_shard_start.end() - 1);
+                for (long o = 0; o < nout; o++) out_by_shard[fillTmp[shardBits ? (size_t)(out_key[(size_t)o] >> sh) : 0]++] = (uint32_t)o;
             }
             deviceDone = true;
             deviceSecs += std::chrono::duration<double>(std::chrono::steady_clock::now() - td0).count();
@@ -456,6 +477,7 @@ private:
         a.tx_off.swap(b.tx_off); a.tx_out_off.swap(b.tx_out_off); a.in_off.swap(b.in_off); a.in_tx.swap(b.in_tx); a.in_n.swap(b.in_n);
         a.out_off.swap(b.out_off); a.out_tx.swap(b.out_tx); a.out_n.swap(b.out_n);
         a.by_shard.swap(b.by_shard); a.shard_start.swap(b.shard_start); a.in_key.swap(b.in_key);
+        a.out_by_shard.swap(b.out_by_shard); a.out_shard_start.swap(b.out_shard_start); a.out_key.swap(b.out_key);
         a.txids.swap(b.txids); a.errTx.swap(b.errTx); a.errEq.swap(b.errEq);
         std::swap(a.root, b.root); std::swap(a.hash, b.hash); std::swap(a.mutated, b.mutated); std::swap(a.rcTx, b.rcTx);
         std::swap(a.rcEq, b.rcEq); std::swap(a.eqOk, b.eqOk); std::swap(a.deviceDone, b.deviceDone);
@@ -526,7 +548,8 @@ private:
             Scan *pc = &w.cur;
             const int dev = devAux;
             const unsigned n_ = ehN, k_ = ehK;
-            thDev = std::thread([pc, dev, n_, k_] { pc->Device(dev, n_, k_); });
+            const int sb_ = shardBits;
+            thDev = std::thread([pc, dev, n_, k_, sb_] { pc->Device(dev, n_, k_, sb_); });
         }
         for (size_t k = 0; k < nhints; k++) ScanAhead(hints[k].first, hints[k].second);
         const Scan &cur = w.cur;
@@ -764,13 +787,10 @@ private:
             const uint64_t sl = ReadCompact(blk, pos);
             T.insert(op, blk + pos, sl, amt);
         };
-        for (size_t o = 0; o < nout; o++) {
-            OutPoint op;
-            memcpy(op.b, &txids[(size_t)cur.out_tx[o] * 32], 8); // the hash reads the first 8 bytes and the index only
-            memcpy(op.b + 32, &cur.out_n[o], 4);
-            if (ShardIndex(op) != w) continue;
-            memcpy(op.b + 8, &txids[(size_t)cur.out_tx[o] * 32 + 8], 24);
-            T.prefetch(op);
+        (void)nout;
+        for (size_t q = cur.out_shard_start[(size_t)w]; q < cur.out_shard_start[(size_t)w + 1]; q++) {
+            const size_t o = cur.out_by_shard[q];
+            T.prefetch_hash((size_t)cur.out_key[o]);
             __builtin_prefetch(blk + cur.out_off[o]); /* amount + script of the output, read when it is inserted */
             if (count == RING) {
                 put(ring[head]);
