@@ -70,9 +70,10 @@ def test_ragged_sizes(engine, oracle, n):
 
 
 def test_chunked_large_batch_properties(engine, oracle):
-    """Full-size property check (1M signatures is BASELINE config 2; here the chunking path, > 2^18):
+    """Full-size property check (1M signatures is BASELINE config 2; here the chunking path: more than six waves, so the
+    host-pointer call cuts the batch into a one-wave chunk and a second one on the other stream):
     corrupting a signature flips exactly its verdict; a sample is compared with the oracle."""
-    n = 300000
+    n = 520000
     msg, pub, sig, kinds = synth.sigset(n, nkeys=4096, corrupt_pct=1)
     got = engine.ecdsa_verify_batch(msg, pub, sig)
     benign = np.isin(kinds, [synth.CORRUPTIONS.index("hybrid_ok"), synth.CORRUPTIONS.index("msg_plus_n")])
