@@ -187,3 +187,56 @@ def test_two_lanes_of_one_gpu_run_concurrently_and_agree(engine, oracle):
     assert len(got) == 8
     with pytest.raises(bcp.BcpError):
         bcp.Engine(0, lane=9)
+
+
+def test_huge_transaction_takes_the_global_memory_path(engine, oracle):
+    """The per-transaction kernels parse from a shared-memory copy of their thread block's span of the block; a span that
+    does not fit (here: a transaction with a 150,000-byte output script in the middle of ordinary ones) must fall back
+    to global memory for that thread block only — same txids, Merkle root, sighashes and verdicts as the oracle."""
+    import hashlib
+
+    o = oracle
+    nkeys = 8
+    keys = [synth.seckey(9000 + j) for j in range(nkeys)]
+    pubs = [o.pubkey_create(kb, True) for kb in keys]
+    spks = [synth.p2pkh_script(pb) for pb in pubs]
+    big_script = b"\x6a" + bytes(range(256)) * 586  # OP_RETURN + 150,016 bytes
+    cb = (2).to_bytes(4, "little") + b"\x01" + bytes(32) + b"\xff\xff\xff\xff" + b"\x04" + (700123).to_bytes(4, "little")
+    cb += b"\xff\xff\xff\xff" + b"\x01" + (1250000000).to_bytes(8, "little") + bytes([25]) + spks[0] + bytes(4)
+    txs, spent_spk, spent_amt = [cb], [], []
+    ntx = 300
+    for j in range(ntx):
+        kj = j % nkeys
+        prev = hashlib.sha256(b"huge-tx-test" + j.to_bytes(4, "little")).digest()
+        amount = 10**7 + j
+        outs = (amount - 1000).to_bytes(8, "little") + bytes([25]) + spks[(kj + 1) % nkeys]
+        nout = 1
+        if j == 137:  # the big one: a second output carrying the long script
+            outs += (0).to_bytes(8, "little") + synth._compact(len(big_script)) + big_script
+            nout = 2
+
+        def build(ss):
+            return ((2).to_bytes(4, "little") + b"\x01" + prev + (0).to_bytes(4, "little") + synth._compact(len(ss)) + ss
+                    + b"\xff\xff\xff\xff" + bytes([nout]) + outs + bytes(4))
+        sh = o.sighash_forkid(spks[kj], build(b""), 0, 0x41, amount)
+        s64 = o.sign(keys[kj], sh)
+        der = synth._der(int.from_bytes(s64[:32], "big"), int.from_bytes(s64[32:], "big")) + b"\x41"
+        txs.append(build(bytes([len(der)]) + der + bytes([33]) + pubs[kj]))
+        spent_spk.append(spks[kj])
+        spent_amt.append(amount)
+    root, _ = o.merkle_root(b"".join(o.sha256d(t) for t in txs))
+    blk = synth.synthetic_header(height=700123, merkle_root=root, n=48, k=5) + synth._compact(len(txs)) + b"".join(txs)
+    want = o.block_script_errors(blk, False, spent_spk, spent_amt, synth.POSTFORK_FLAGS, NT)
+    assert not want.any()
+    res = engine.block_connect_p2pkh(blk, spent_spk, spent_amt, synth.POSTFORK_FLAGS, want_txids=True)
+    n, txids, root2, mutated = o.block_txids(blk, False)
+    assert res["root"] == root == root2 and (res["txids"][:n] == txids).all()
+    assert (res["script_err"] == want).all() and res["all_ok"]
+    # the same block inside a window, and with a wrong amount for the big transaction's input
+    arrs, cat, off, am, nin = _window([(blk, spent_spk, spent_amt), synth.synthetic_block(200, True, nkeys=8, with_prevouts=True)])
+    w = engine.blocks_connect_p2pkh(arrs, cat, off, am, nin, synth.POSTFORK_FLAGS)
+    assert w["all_ok"] == [True, True] and bytes(w["roots"][0]) == root
+    bad_amt = list(spent_amt)
+    bad_amt[137] += 1
+    res2 = engine.block_connect_p2pkh(blk, spent_spk, bad_amt, synth.POSTFORK_FLAGS)
+    assert list(np.nonzero(res2["script_err"])[0]) == [137] and res2["script_err"][137] == 31
