@@ -56,6 +56,7 @@ SIGNATURES = {
     "bcp_gpu_equihash_scratch_bytes": (sz, [sz]),
     "bcp_gpu_header_check_batch": (C.c_int, [C.c_int, C.c_uint, C.c_uint, vp, sz, sz, sz, vp, vp, C.c_uint32, vp, vp, vp, vp]),
     "bcp_gpu_equihash_verify_batch_dev": (C.c_int, [C.c_int, C.c_uint, C.c_uint, vp, sz, sz, sz, vp, vp, vp]),
+    "bcp_gpu_selftest": (C.c_int, [C.c_int]),
     "bcp_gpu_measure_int_peak": (C.c_int, [C.c_int, C.c_int, C.POINTER(C.c_double)]),
 }
 

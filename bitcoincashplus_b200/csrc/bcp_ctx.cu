@@ -6,6 +6,7 @@
 #include <cstring>
 
 int bcp_ecdsa_build_tables(bcp_ctx *c); // bcp_ecdsa.cu
+int bcp_fe_selftest(bcp_ctx *c);          // bcp_ecdsa.cu
 
 static bcp_ctx g_ctx[BCP_MAX_DEVICES][BCP_MAX_LANES];
 static std::mutex g_init_mu;
@@ -110,7 +111,9 @@ static int init_locked(int device, int lane) {
     BCP_CUDA(cudaStreamCreateWithFlags(&c->copy_stream, cudaStreamNonBlocking));
     for (int i = 0; i < 4; i++) BCP_CUDA(cudaEventCreateWithFlags(&c->ev[i], cudaEventDisableTiming));
     if (lane == 0) {
-        int rc = bcp_ecdsa_build_tables(c);
+        int rc = bcp_fe_selftest(c); // a few hundred crafted operand pairs, ~0.1 ms: refuse to start on a wrong answer
+        if (rc != BCP_OK) return rc;
+        rc = bcp_ecdsa_build_tables(c);
         if (rc != BCP_OK) return rc;
     } else {
         c->gcomb = g_ctx[device][0].gcomb;
@@ -142,6 +145,14 @@ int bcp_gpu_shutdown(int id) { // lane 0 (the plain device ordinal) takes the GP
         c->ready = false;
     }
     return BCP_OK;
+}
+
+int bcp_gpu_selftest(int device) {
+    bcp_ctx *c = bcp_get_ctx(device);
+    if (!c) return BCP_ERR_NOT_INIT;
+    std::lock_guard<std::mutex> lk(c->mu);
+    BCP_CUDA(cudaSetDevice(c->device));
+    return bcp_fe_selftest(c);
 }
 
 void *bcp_gpu_host_alloc(size_t bytes) {

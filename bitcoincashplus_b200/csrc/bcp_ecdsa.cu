@@ -128,6 +128,66 @@ __global__ void __launch_bounds__(128) k_pubkey_parse(const uint8_t *__restrict_
     ok[i] = v ? 1 : 0;
 }
 
+// Device self-test of the field arithmetic's rarely taken paths.  fe_add / fe_sub / fe_reduce_wide finish the folds
+// that practically never propagate (probability about 2^-32 per operation) out of line; random test inputs do not reach
+// that code, so crafted operands (fe_selftest_data.cuh) are run through the short-cut forms AND the always-full-chain
+// forms, on the device, and must agree limb for limb.  The counterpart of ECC_InitSanityCheck (src/key.cpp) at start-up.
+#include "fe_selftest_data.cuh"
+__global__ void k_fe_selftest(int *fail) {
+    const int t = blockIdx.x * blockDim.x + threadIdx.x;
+    int bad = 0;
+    if (t < BCP_FE_ST_EDGES * BCP_FE_ST_EDGES) {
+        fe a, b, r1, r2;
+        for (int i = 0; i < 8; i++) { a.v[i] = FE_ST_EDGE[t / BCP_FE_ST_EDGES][i]; b.v[i] = FE_ST_EDGE[t % BCP_FE_ST_EDGES][i]; }
+        fe_add(r1, a, b);
+        fe_add_full(r2, a, b);
+        for (int i = 0; i < 8; i++) bad |= r1.v[i] != r2.v[i];
+        fe_sub(r1, a, b);
+        fe_sub_full(r2, a, b);
+        for (int i = 0; i < 8; i++) bad |= r1.v[i] != r2.v[i];
+        uint32_t w[16];
+        mul_wide(w, a.v, b.v);
+        fe_reduce_wide_t<true>(r1, w);
+        fe_reduce_wide_t<false>(r2, w);
+        for (int i = 0; i < 8; i++) bad |= r1.v[i] != r2.v[i];
+        fe m1 = fe_mul_f(a, b); /* the product path the kernels use */
+        for (int i = 0; i < 8; i++) bad |= m1.v[i] != r2.v[i];
+        // a*b computed two ways must also agree after the sum of the operands went through add/sub: (a+b)-b == a (mod p)
+        fe_add(r1, a, b);
+        fe_sub(r1, r1, b);
+        fe na = a;
+        fe_normalize(r1);
+        fe_normalize(na);
+        for (int i = 0; i < 8; i++) bad |= r1.v[i] != na.v[i];
+    }
+    if (t < BCP_FE_ST_WIDE) {
+        fe r1, r2;
+        uint32_t w[16];
+        for (int i = 0; i < 16; i++) w[i] = FE_ST_WIDE[t][i];
+        fe_reduce_wide_t<true>(r1, w);
+        fe_reduce_wide_t<false>(r2, w);
+        for (int i = 0; i < 8; i++) bad |= r1.v[i] != r2.v[i];
+    }
+    if (bad) atomicAdd(fail, 1);
+}
+int bcp_fe_selftest(bcp_ctx *c) {
+    int *d_fail = nullptr, h_fail = -1;
+    BCP_CUDA(cudaMalloc(&d_fail, sizeof(int)));
+    BCP_CUDA(cudaMemsetAsync(d_fail, 0, sizeof(int), c->stream));
+    k_fe_selftest<<<(BCP_FE_ST_EDGES * BCP_FE_ST_EDGES + 127) / 128, 128, 0, c->stream>>>(d_fail);
+    cudaError_t e = cudaGetLastError();
+    if (e == cudaSuccess) e = cudaMemcpyAsync(&h_fail, d_fail, sizeof(int), cudaMemcpyDeviceToHost, c->stream);
+    if (e == cudaSuccess) e = cudaStreamSynchronize(c->stream);
+    cudaFree(d_fail);
+    if (e != cudaSuccess) return bcp_cuda_fail(e, "field self-test");
+    if (h_fail != 0) {
+        bcp_set_error("field arithmetic self-test failed on device %d: %d operand pairs disagree between the short-cut and the "
+                      "full carry chains", c->device, h_fail);
+        return BCP_ERR_CUDA;
+    }
+    return BCP_OK;
+}
+
 int bcp_ecdsa_build_tables(bcp_ctx *c) {
     BCP_CUDA(cudaMalloc(&c->gcomb, (size_t)BCP_GCOMB_WORDS * 4));
     int total = BCP_GCOMB_WINDOWS * BCP_GCOMB_ENTRIES;

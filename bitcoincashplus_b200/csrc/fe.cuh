@@ -22,6 +22,9 @@ struct fe {
 #define BCP_P0 0xFFFFFC2Fu
 #define BCP_P1 0xFFFFFFFEu
 #define BCP_FOLD 977u /* 2^256 = 2^32 + 977 (mod p) */
+#ifndef BCP_FE_SHORT_FOLD
+#define BCP_FE_SHORT_FOLD 1 /* finish the folds that practically never propagate out of line (see fe_add) */
+#endif
 
 // ------------------------------------------------------------------ limb primitives
 // X[0..7] = { a0*b, a2*b, a4*b, a6*b } as four independent 64-bit products
@@ -481,7 +484,7 @@ BCP_DEV void mul_wide_karatsuba(uint32_t *r /*16*/, const uint32_t *a, const uin
 }
 
 // ------------------------------------------------------------------ 512 -> [0, 2^256) mod p
-BCP_DEV void fe_reduce_wide(fe &r, const uint32_t *t /*16*/) {
+template <bool SHORT> BCP_DEV void fe_reduce_wide_t(fe &r, const uint32_t *t /*16*/) {
     // first fold: S = L + H*977 + (H << 32), accumulated in place as two interleaved arrays
     uint32_t EV[9], OD[9];
     BCP_UNROLL
@@ -496,12 +499,24 @@ BCP_DEV void fe_reduce_wide(fe &r, const uint32_t *t /*16*/) {
     uint64_t m = (uint64_t)s[8] * BCP_FOLD + ((uint64_t)(s[9] * BCP_FOLD) << 32);
     uint64_t a1 = (m >> 32) + s[8];
     uint32_t A[8] = {(uint32_t)m, (uint32_t)a1, s[9] + (uint32_t)(a1 >> 32), 0, 0, 0, 0, 0};
+    // T*977 + (T << 32) only reaches limbs 0..2; a carry out of limb 2 (probability about 2^-30) is the only way the
+    // upper limbs — or a third fold — can be affected, and then the full chains below run instead
+    if (SHORT) {
+        uint32_t lo3[3];
+        if (__builtin_expect(addn_cc<3>(lo3, s, A) == 0, 1)) {
+            r.v[0] = lo3[0]; r.v[1] = lo3[1]; r.v[2] = lo3[2];
+            BCP_UNROLL
+            for (int i = 3; i < 8; i++) r.v[i] = s[i];
+            return;
+        }
+    }
     uint32_t c = addn_cc<8>(r.v, s, A);
     // third fold: a carry means S' wrapped past 2^256 (== 2^32+977); the wrapped value is < 2^67,
     // so only limbs 0..2 can change and no further wrap is possible
     uint32_t B[3] = {(0u - c) & BCP_FOLD, c, 0}; /* c is 0/1: mask instead of a multiply (keeps the IMAD pipe free) */
     addn_cc<3>(r.v, r.v, B);
 }
+BCP_DEV void fe_reduce_wide(fe &r, const uint32_t *t /*16*/) { fe_reduce_wide_t<BCP_FE_SHORT_FOLD != 0>(r, t); }
 
 // The multiplication and the squaring are real (non-inlined) device functions taking and returning the
 // element BY VALUE: ptxas passes the 8+8 limbs in registers (no local-memory traffic, checked in SASS), a call
@@ -572,23 +587,59 @@ BCP_FE_FN fe fe_sqr_f(fe a) {
 BCP_DEV void fe_sqr(fe &r, const fe &a) { r = fe_sqr_f(a); }
 
 // ------------------------------------------------------------------ add / sub / neg (weakly reduced in and out)
-BCP_DEV void fe_add(fe &r, const fe &a, const fe &b) {
-    uint32_t c = addn_cc<8>(r.v, a.v, b.v);
-    // a + b - 2^256 == a + b - 2^256 + (2^32 + 977) (mod p)
+// The folds after the first chain almost never propagate: c * (2^32 + 977) lands in limbs 0 and 1, and only a carry (borrow)
+// out of limb 1 — probability about 2^-32 — can reach further or wrap a second time.  That case is finished by these
+// out-of-line full chains; the inline path is one 8-limb chain plus a 2-limb one.
+BCP_DEV_NOINLINE fe fe_add_fold_slow(fe r, uint32_t c) { /* by value: the element travels in registers */
     uint32_t A[8] = {(0u - c) & BCP_FOLD, c, 0, 0, 0, 0, 0, 0};
     uint32_t c2 = addn_cc<8>(r.v, r.v, A);
     // a second wrap needs both inputs within 2^33 of 2^256; afterwards the value is < 2^34
     uint32_t B[2] = {(0u - c2) & BCP_FOLD, c2};
     addn_cc<2>(r.v, r.v, B);
+    return r;
 }
-BCP_DEV void fe_sub(fe &r, const fe &a, const fe &b) {
-    uint32_t bw = subn_cc<8>(r.v, a.v, b.v);
-    // a - b + 2^256 == a - b + 2^256 - (2^32 + 977) (mod p)
+BCP_DEV_NOINLINE fe fe_sub_fold_slow(fe r, uint32_t bw) {
     uint32_t A[8] = {(0u - bw) & BCP_FOLD, bw, 0, 0, 0, 0, 0, 0};
     uint32_t bw2 = subn_cc<8>(r.v, r.v, A);
     // second borrow: value is now within 2^34 of 2^256, subtracting again cannot borrow
     uint32_t B[2] = {(0u - bw2) & BCP_FOLD, bw2};
     subn_cc<2>(r.v, r.v, B);
+    return r;
+}
+BCP_DEV void fe_add(fe &r, const fe &a, const fe &b) {
+    uint32_t c = addn_cc<8>(r.v, a.v, b.v);
+    // a + b - 2^256 == a + b - 2^256 + (2^32 + 977) (mod p)
+#if BCP_FE_SHORT_FOLD
+    uint32_t A2[2] = {(0u - c) & BCP_FOLD, c}, lo2[2];
+    if (__builtin_expect(addn_cc<2>(lo2, r.v, A2) == 0, 1)) {
+        r.v[0] = lo2[0];
+        r.v[1] = lo2[1];
+        return;
+    }
+#endif
+    r = fe_add_fold_slow(r, c);
+}
+BCP_DEV void fe_sub(fe &r, const fe &a, const fe &b) {
+    uint32_t bw = subn_cc<8>(r.v, a.v, b.v);
+    // a - b + 2^256 == a - b + 2^256 - (2^32 + 977) (mod p)
+#if BCP_FE_SHORT_FOLD
+    uint32_t A2[2] = {(0u - bw) & BCP_FOLD, bw}, lo2[2];
+    if (__builtin_expect(subn_cc<2>(lo2, r.v, A2) == 0, 1)) {
+        r.v[0] = lo2[0];
+        r.v[1] = lo2[1];
+        return;
+    }
+#endif
+    r = fe_sub_fold_slow(r, bw);
+}
+// the always-full-chain forms (what fe_add / fe_sub were before the short cut): reference for the device self-test
+BCP_DEV void fe_add_full(fe &r, const fe &a, const fe &b) {
+    uint32_t c = addn_cc<8>(r.v, a.v, b.v);
+    r = fe_add_fold_slow(r, c);
+}
+BCP_DEV void fe_sub_full(fe &r, const fe &a, const fe &b) {
+    uint32_t bw = subn_cc<8>(r.v, a.v, b.v);
+    r = fe_sub_fold_slow(r, bw);
 }
 BCP_DEV void fe_set_zero(fe &r) {
     BCP_UNROLL

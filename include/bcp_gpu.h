@@ -57,6 +57,9 @@ BCP_API int bcp_gpu_device_count(void);
 BCP_API int bcp_gpu_init(int device);
 /* Destroy it (secp256k1_context_destroy, secp256k1.c:96-105); the plain ordinal also destroys the GPU's other lanes. */
 BCP_API int bcp_gpu_shutdown(int device);
+/* Device self-test of the field arithmetic's rarely taken carry paths on crafted operands (run by bcp_gpu_init as well;
+ * the counterpart of ECC_InitSanityCheck, src/key.cpp:336-342, which init.cpp runs at start-up). */
+BCP_API int bcp_gpu_selftest(int device);
 /* Text of the last error on the calling thread. */
 BCP_API const char *bcp_gpu_last_error(void);
 /* Pinned host memory for staging buffers (what "pinned buffers" in the north star refers to). */

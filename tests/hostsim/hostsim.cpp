@@ -48,8 +48,22 @@ void hs_fe_op(int op, const uint8_t *a32, const uint8_t *b32, uint8_t *out32) {
         case 3: fe_sqr(r, a); break;
         case 4: fe_neg(r, a); break;
         case 5: fe_inv(r, a); break;
+        case 7: fe_add_full(r, a, b); break;
+        case 8: fe_sub_full(r, a, b); break;
         default: fe_sqrt_candidate(r, a); break;
     }
+    fe_to_be(out32, r);
+}
+// fe_reduce_wide on a chosen 512-bit input (big-endian), with and without the short-cut second fold
+void hs_fe_reduce(const uint8_t *t64_be, int short_fold, uint8_t *out32) {
+    uint32_t w[16];
+    for (int i = 0; i < 16; i++) {
+        const uint8_t *q = t64_be + 60 - 4 * i;
+        w[i] = (uint32_t)q[0] << 24 | (uint32_t)q[1] << 16 | (uint32_t)q[2] << 8 | q[3];
+    }
+    fe r;
+    if (short_fold) fe_reduce_wide_t<true>(r, w);
+    else fe_reduce_wide_t<false>(r, w);
     fe_to_be(out32, r);
 }
 // 512-bit product via the Karatsuba variant (an experiment kept in fe.cuh), big-endian in/out

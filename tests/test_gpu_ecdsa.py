@@ -122,3 +122,11 @@ def test_reference_golden_verdicts_on_gpu(engine):
     z = np.load(os.path.join(os.path.dirname(__file__), "golden", "ecdsa_ref.npz"))
     assert (engine.ecdsa_verify_batch(z["msg"], z["pub"], z["sig"]) == z["verdict_raw"]).all()
     assert (engine.ecdsa_verify_batch(z["msg"], z["pub"], z["sig"], flags=bcp.ECDSA_FLAG_NORMALIZE_S) == z["verdict_cpubkey"]).all()
+
+
+def test_device_field_selftest(engine):
+    """bcp_gpu_selftest: crafted operands through the short-cut and the full carry chains of the field code, on the device
+    (also run by bcp_gpu_init).  0 = every pair agrees."""
+    import bitcoincashplus_b200 as bcp
+
+    assert bcp.lib().bcp_gpu_selftest(engine.device) == 0, bcp.lib().bcp_gpu_last_error()

@@ -72,6 +72,35 @@ def test_field_ops_on_weakly_reduced_inputs(hs):
         assert bool(hs.hs_fe_is_zero(b32(a))) == (a % P == 0)
 
 
+def test_short_cut_folds_on_crafted_operands(hs):
+    """fe_add / fe_sub / fe_reduce_wide finish the folds that practically never propagate out of line.  Random inputs
+    do not reach that code: these operands do (the same set the device self-test uses, tools/gen_fe_selftest.py), and
+    the short-cut forms must equal both the always-full-chain forms and Python's integers."""
+    import importlib.util
+
+    spec = importlib.util.spec_from_file_location("gen_fe_selftest", os.path.join(ROOT, "tools", "gen_fe_selftest.py"))
+    g = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(g)
+    for a in g.edge:
+        for b in g.edge:
+            for op, full, want in ((1, 7, (a + b) % P), (2, 8, (a - b) % P)):
+                got, ref = op3(hs.hs_fe_op, op, a, b), op3(hs.hs_fe_op, full, a, b)
+                assert got % P == want and ref % P == want and got == ref, (op, hex(a), hex(b))
+            assert op3(hs.hs_fe_op, 0, a, b) % P == a * b % P
+    hit = 0
+    for w in g.wide:
+        out1, out0 = (C.c_uint8 * 32)(), (C.c_uint8 * 32)()
+        t = C.cast(C.c_char_p(w.to_bytes(64, "big")), u8p)
+        hs.hs_fe_reduce(t, 1, out1)
+        hs.hs_fe_reduce(t, 0, out0)
+        v1, v0 = int.from_bytes(bytes(out1), "big"), int.from_bytes(bytes(out0), "big")
+        assert v1 == v0 and v1 % P == w % P, hex(w)
+        # does this input really need the slow path?  S = L + H*(2^32+977); T = S >> 256; low 96 bits + T*(2^32+977) carries
+        S = (w % 2**256) + (w >> 256) * (2**32 + 977)
+        hit += ((S % 2**96) + (S >> 256) * (2**32 + 977)) >= 2**96
+    assert hit >= 8
+
+
 def test_wide_products_schoolbook_and_karatsuba(hs):
     rnd = random.Random(17)
     vals = EDGE + [2**128 - 1, 2**128, 2**128 + 1, (2**128 - 1) << 128, 2**256 - 2**128] + [rnd.randrange(2**256) for _ in range(200)]
