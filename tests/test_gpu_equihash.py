@@ -118,3 +118,74 @@ def test_equihash_structural_corruptions(engine, oracle, n, k, fixture):
     want = oracle.equihash_verify_batch(n, k, allh, nthreads=os.cpu_count() or 1)
     assert (got == want).all(), np.nonzero(got != want)[0]
     assert not want.any()
+
+
+def _solve_48_5_allowing_duplicates(input140, max_out=8):
+    """Wagner's algorithm for (48,5) like synth.equihash_solve_48_5, but WITHOUT the "index sets must be disjoint" filter:
+    returns index lists whose XOR conditions and ordering all hold and in which some index occurs twice — inputs that
+    only the distinctness rule (DistinctIndices, src/crypto/equihash.cpp:742-748) rejects."""
+    import hashlib
+
+    pers = b"ZcashPoW" + (48).to_bytes(4, "little") + (5).to_bytes(4, "little")
+    rows = []
+    for g in range(52):
+        d = hashlib.blake2b(input140 + g.to_bytes(4, "little"), digest_size=60, person=pers).digest()
+        for j in range(10):
+            i = g * 10 + j
+            if i < 512:
+                rows.append((d[6 * j:6 * j + 6], (i,)))
+    for rnd in range(5):
+        width = 2 if rnd == 4 else 1
+        buckets = {}
+        for h, idx in rows:
+            buckets.setdefault(h[:width], []).append((h, idx))
+        nxt = []
+        for grp in buckets.values():
+            for a in range(len(grp)):
+                for b in range(a + 1, len(grp)):
+                    (ha, ia), (hb, ib) = grp[a], grp[b]
+                    if ia[0] == ib[0]:
+                        continue  # the ordering rule needs different first indices
+                    if rnd < 3 and set(ia) & set(ib):
+                        continue  # keep the early rounds clean so that the table stays small
+                    x = bytes(p ^ q for p, q in zip(ha[width:], hb[width:]))
+                    nxt.append((x, ia + ib if ia[0] < ib[0] else ib + ia))
+        rows = nxt
+    out = []
+    for h, idx in rows:
+        if len(set(idx)) < 32:
+            out.append(idx)
+            if len(out) >= max_out:
+                break
+    return out
+
+
+def test_equihash_duplicate_indices_are_the_only_defect(engine, oracle):
+    """Solutions whose XOR chunks vanish at every level and whose sub-trees are ordered, but in which an index occurs
+    twice: only the distinctness check stands between them and acceptance."""
+    import synth
+
+    found = []
+    nonce = 0
+    while len(found) < 12 and nonce < 400:
+        hdr = synth.synthetic_header(height=700000, merkle_root=bytes(32), nonce_tag=(77 << 20) | nonce, n=48, k=5)
+        for idx in _solve_48_5_allowing_duplicates(hdr[:140]):
+            v = 0
+            for x in idx:
+                v = (v << 9) | x
+            found.append(hdr[:140] + b"\x24" + v.to_bytes(36, "big"))
+        nonce += 1
+    assert len(found) >= 4, "no duplicate-index pseudo-solutions found"
+    # and genuine solutions of the same headers' family, as the control group
+    good = []
+    nonce = 0
+    while len(good) < 4:
+        hdr = synth.synthetic_header(height=700000, merkle_root=bytes(32), nonce_tag=(78 << 20) | nonce, n=48, k=5)
+        for sol in synth.equihash_solve_48_5(hdr[:140])[:1]:
+            good.append(hdr[:140] + b"\x24" + sol)
+        nonce += 1
+    arr = np.frombuffer(b"".join(found + good), dtype=np.uint8).reshape(len(found) + len(good), 177)
+    ok, _ = engine.equihash_verify_batch(48, 5, arr)
+    want = oracle.equihash_verify_batch(48, 5, arr, 2)
+    assert (ok.astype(bool) == (want == 1)).all()
+    assert not ok[:len(found)].any() and ok[len(found):].all()
