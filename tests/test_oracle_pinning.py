@@ -222,3 +222,44 @@ def test_ref_equihash_differential(oracle):
                     # the shim reports a header that no longer deserializes as -1; both mean "not valid"
                     assert (r.equihash_verify(n, k, bytes(b)) == 1) == (oracle.equihash_verify(n, k, bytes(b)) == 1)
         assert found > 0
+
+
+def test_equihash_duplicate_index_pseudo_solutions_oracle_vs_reference():
+    """Index lists that satisfy every XOR and ordering condition but repeat an index (tests/test_gpu_equihash.py builds them
+    with a Wagner search that skips the disjointness filter): rejected by the oracle and, where it is built, by the
+    reference's own IsValidSolution — the distinctness rule pinned in isolation."""
+    import importlib.util
+    import os
+    import sys
+
+    import numpy as np
+
+    here = os.path.dirname(os.path.abspath(__file__))
+    sys.path.insert(0, here)
+    import synth
+    from oracle import pyoracle as po
+
+    spec = importlib.util.spec_from_file_location("eqh", os.path.join(here, "test_gpu_equihash.py"))
+    eqh = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(eqh)
+    rows = []
+    for nonce in range(12):
+        hdr = synth.synthetic_header(height=700000, merkle_root=bytes(32), nonce_tag=(79 << 20) | nonce, n=48, k=5)
+        for idx in eqh._solve_48_5_allowing_duplicates(hdr[:140], max_out=4):
+            v = 0
+            for x in idx:
+                v = (v << 9) | x
+            rows.append(hdr[:140] + b"\x24" + v.to_bytes(36, "big"))
+        for sol in synth.equihash_solve_48_5(hdr[:140])[:1]:
+            rows.append(hdr[:140] + b"\x24" + sol)
+    arr = np.frombuffer(b"".join(rows), dtype=np.uint8).reshape(len(rows), 177)
+    got = po.oracle().equihash_verify_batch(48, 5, arr, 2)
+    # a row is a control (genuine solution) iff its 32 indices are distinct
+    def distinct(r):
+        v = int.from_bytes(bytes(r[141:177]), "big")
+        return len({(v >> (9 * i)) & 511 for i in range(32)}) == 32
+    want = np.array([1 if distinct(r) else 0 for r in arr])
+    assert want.sum() >= 3 and (want == 0).sum() >= 8
+    assert (got == want).all()
+    if po.have_ref():
+        assert ((po.ref().equihash_verify_batch(48, 5, arr, 2) == 1).astype(int) == want).all()
