@@ -21,6 +21,7 @@
 #include "bcp_ctx.cuh"
 #include "blake2b.cuh"
 #include "pow.cuh"
+#include <algorithm>
 #include <cstring>
 
 template <unsigned N, unsigned K>
@@ -287,17 +288,27 @@ BCP_API int bcp_gpu_equihash_verify_batch(int device, unsigned n, unsigned k, co
     int rc = bcp_ctx_reserve_stage(c, total);
     if (rc != BCP_OK) return rc;
     uint8_t *d = c->stage;
-    cudaStream_t st = c->stream;
-    BCP_CUDA(cudaMemcpyAsync(d, hdrs, bytes, cudaMemcpyHostToDevice, st));
-    rc = eh_dispatch(c, n, k, d, stride, hdr_len, count, reinterpret_cast<uint64_t *>(d + o_mid), d + o_ok, st);
-    if (rc != BCP_OK) return rc;
-    BCP_CUDA(cudaMemcpyAsync(ok, d + o_ok, count, cudaMemcpyDeviceToHost, st));
-    if (hash32) {
-        rc = bcp_sha256d_strided_dev(c, d, stride, hdr_len, count, d + o_hash, st);
+    // Chunks on alternating streams: with pinned host buffers chunk i+1's upload runs under chunk i's kernels (a (200,9)
+    // header is 1,487 bytes, so 10,000 of them are 15 MB: as long on the bus as in the verify kernel).
+    cudaStream_t sts[2] = {c->stream, c->copy_stream};
+    const size_t chunk = count <= 2048 ? count : std::max<size_t>(1024, (count + 3) / 4);
+    int q = 0;
+    for (size_t off = 0; off < count; off += chunk, q ^= 1) {
+        const size_t m = std::min(chunk, count - off);
+        cudaStream_t st = sts[q];
+        BCP_CUDA(cudaMemcpyAsync(d + off * stride, hdrs + off * stride, m * stride, cudaMemcpyHostToDevice, st));
+        rc = eh_dispatch(c, n, k, d + off * stride, stride, hdr_len, m, reinterpret_cast<uint64_t *>(d + o_mid + off * 64),
+                         d + o_ok + off, st);
         if (rc != BCP_OK) return rc;
-        BCP_CUDA(cudaMemcpyAsync(hash32, d + o_hash, count * 32, cudaMemcpyDeviceToHost, st));
+        BCP_CUDA(cudaMemcpyAsync(ok + off, d + o_ok + off, m, cudaMemcpyDeviceToHost, st));
+        if (hash32) {
+            rc = bcp_sha256d_strided_dev(c, d + off * stride, stride, hdr_len, m, d + o_hash + off * 32, st);
+            if (rc != BCP_OK) return rc;
+            BCP_CUDA(cudaMemcpyAsync(hash32 + off * 32, d + o_hash + off * 32, m * 32, cudaMemcpyDeviceToHost, st));
+        }
     }
-    BCP_CUDA(cudaStreamSynchronize(st));
+    BCP_CUDA(cudaStreamSynchronize(sts[0]));
+    BCP_CUDA(cudaStreamSynchronize(sts[1]));
     return BCP_OK;
 }
 
