@@ -618,6 +618,16 @@ def main():
     if not args.no_cpu_baseline:
         line["cpu_baseline"] = cpu_baseline(msg, pub, sig)
     if not args.no_block:
+        # the block numbers as a fraction of the integer roofline too (same convention as `roofline`: the reference
+        # algorithm's 151,228 mul32 per input against the measured IMAD.WIDE peak, per GPU)
+        def roof(inputs_per_s):
+            return inputs_per_s / world * MUL32_PER_VERIFY / peak_imad
+        if blk_section:
+            blk_section["frac_of_int_roofline"] = roof(blk_section["gpu_inputs_per_s"])
+        if win_section:
+            win_section["frac_of_int_roofline"] = roof(win_section["gpu_inputs_per_s"])
+            for k_ in ("two_lanes", "four_lanes"):
+                win_section[k_]["frac_of_int_roofline"] = roof(win_section[k_]["gpu_inputs_per_s"])
         line["block8mb"] = blk_section
         line["block8mb_window"] = win_section
         line["checkqueue_dropin"] = queue_dropin_bench(args)
