@@ -211,8 +211,11 @@ BCP_API int bcp_gpu_merkle_root_dev(int device, const uint8_t *d_leaves32, size_
 #define BCP_MERKLE_STATIC_WORDS (2 * ((BCP_MERKLE_STATIC_MAX_LEAVES / MERKLE_NODES) * 8) + 16)
 static __device__ __align__(256) uint32_t g_merkle_static_scratch[BCP_MERKLE_STATIC_WORDS];
 // In host code the name above is only a handle for the symbol, not an address a kernel can use; the
-// device address is looked up once per device (with that device current) and cached here.
+// device address is looked up once per device (with that device current) and cached here.  The cache is
+// per GPU ordinal — every lane of a GPU shares the one array — and has a lock of its own, because two
+// lanes of the same GPU hold different context locks.
 static uint32_t *g_merkle_static_ptr[BCP_MAX_DEVICES];
+static std::mutex g_merkle_static_mu;
 
 BCP_API int bcp_gpu_merkle_root_dev_static(int device, const uint8_t *d_leaves32, size_t n, uint8_t *d_root32,
                                            int *d_mutated, void *stream) {
@@ -230,16 +233,21 @@ BCP_API int bcp_gpu_merkle_root_dev_static(int device, const uint8_t *d_leaves32
     }
     std::lock_guard<std::mutex> lk(c->mu);
     BCP_CUDA(cudaSetDevice(c->device));
-    if (!g_merkle_static_ptr[device]) { /* first call on this device: resolve the symbol's device address */
-        uint32_t *p = nullptr;
-        BCP_CUDA(cudaGetSymbolAddress((void **)&p, g_merkle_static_scratch));
-        g_merkle_static_ptr[device] = p;
+    uint32_t *scratch = nullptr;
+    { /* `device` may carry a lane in its upper bits: the cache is indexed by the GPU ordinal alone */
+        std::lock_guard<std::mutex> lk2(g_merkle_static_mu);
+        uint32_t *&slot = g_merkle_static_ptr[c->device];
+        if (!slot) { /* first call on this GPU: resolve the symbol's device address */
+            uint32_t *p = nullptr;
+            BCP_CUDA(cudaGetSymbolAddress((void **)&p, g_merkle_static_scratch));
+            slot = p;
+        }
+        scratch = slot;
     }
     // Nothing in the array has to start at zero: each launch writes every node the next launch reads, and
     // the mutated flag (caller memory) is cleared by merkle_dev on every call.  Stale nodes of an earlier,
     // larger tree are never read.
-    return merkle_dev(c, d_leaves32, n, d_root32, d_mutated, g_merkle_static_ptr[device],
-                      stream ? (cudaStream_t)stream : c->stream);
+    return merkle_dev(c, d_leaves32, n, d_root32, d_mutated, scratch, stream ? (cudaStream_t)stream : c->stream);
 }
 
 // Host-pointer forms.  Staging layout in c->stage: [data + pad][offsets][digests][merkle tmp][root][mutated]

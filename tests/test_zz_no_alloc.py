@@ -18,7 +18,7 @@ pytestmark = pytest.mark.gpu
 _STREAM = {}
 
 
-def _roots(L, dev, torch, leaves, static):
+def _roots(L, dev, torch, leaves, static, dev_id=0):
     # one explicit (non-default) stream orders the buffer fills, both entry points and the read-back
     st = _STREAM.setdefault("s", torch.cuda.Stream(dev))
     n = leaves.shape[0]
@@ -28,10 +28,10 @@ def _roots(L, dev, torch, leaves, static):
         d_mut = torch.full((1,), 7, dtype=torch.int32, device=dev)
         d_scr = torch.empty(L.bcp_gpu_merkle_scratch_bytes(n), dtype=torch.uint8, device=dev)
         if static:
-            rc = L.bcp_gpu_merkle_root_dev_static(0, d_leaves.data_ptr(), n, d_root.data_ptr(), d_mut.data_ptr(),
+            rc = L.bcp_gpu_merkle_root_dev_static(dev_id, d_leaves.data_ptr(), n, d_root.data_ptr(), d_mut.data_ptr(),
                                                   st.cuda_stream)
         else:
-            rc = L.bcp_gpu_merkle_root_dev(0, d_leaves.data_ptr(), n, d_root.data_ptr(), d_mut.data_ptr(),
+            rc = L.bcp_gpu_merkle_root_dev(dev_id, d_leaves.data_ptr(), n, d_root.data_ptr(), d_mut.data_ptr(),
                                            d_scr.data_ptr(), st.cuda_stream)
         assert rc == 0, L.bcp_gpu_last_error()
         st.synchronize()
@@ -60,6 +60,30 @@ def test_static_scratch_merkle_matches_existing_entry_point_twice_in_a_row():
     for n in (0, 1, 2, 3, 257):
         leaves = rng.integers(0, 256, size=(n, 32), dtype=np.uint8)
         assert _roots(L, dev, torch, leaves, static=True) == _roots(L, dev, torch, leaves, static=False)
+
+
+def test_static_scratch_merkle_from_other_lanes_and_against_the_oracle():
+    """Every `device` argument of the library may carry a lane (BCP_DEVICE_LANE(ordinal, lane) = ordinal | lane << 8).
+    All lanes of a GPU share the one built-in array; a call through lane 1, 2 or 3 must find it (it is looked up by
+    the GPU ordinal, not by the raw id) and give the root the CPU oracle gives."""
+    import torch
+
+    import bitcoincashplus_b200 as bcp
+    from oracle import pyoracle as po
+
+    bcp.Engine(0)
+    L = bcp.lib()
+    dev = torch.device("cuda", 0)
+    rng = np.random.default_rng(7)
+    for lane, n in ((1, 41651), (2, 777), (3, 1 << 16), (0, 12345)):
+        bcp.Engine(0, lane=lane)
+        leaves = rng.integers(0, 256, size=(n, 32), dtype=np.uint8)
+        if lane == 2:
+            leaves[501] = leaves[500]
+        want_root, want_mut = po.oracle().merkle_root(leaves)
+        got = _roots(L, dev, torch, leaves, static=True, dev_id=lane << 8)
+        assert got == (want_root, int(want_mut)), "lane %d" % lane
+        assert got == _roots(L, dev, torch, leaves, static=False, dev_id=0)
 
 
 def test_static_scratch_merkle_rejects_oversize():
