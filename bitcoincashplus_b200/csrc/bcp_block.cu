@@ -141,6 +141,31 @@ static int rd_compact_h(const uint8_t *p, size_t len, size_t *pos, uint64_t *v) 
 
 #define BCP_FLAGS_POSTFORK_REQUIRED ((1u << 1) | (1u << 2) | (1u << 3) | (1u << 14) | (1u << 16))
 #define BCP_FLAG_ALLOW_NON_FORKID (1u << 17)
+// SCRIPT_VERIFY_* bits (src/script/interpreter.h:32-121) that cannot change the verdict or the ScriptError of a
+// `<sig> <pubkey>` scriptSig (direct pushes only) against a P2PKH scriptPubKey: P2SH, NULLDUMMY, SIGPUSHONLY,
+// DISCOURAGE_UPGRADABLE_NOPS, CLEANSTACK (one element is left), CLTV, CSV, MINIMALIF — next to the required ones.
+// MINIMALDATA (1<<6: a one-byte direct push of 1..16 / 0x81 would be an error) and COMPRESSED_PUBKEYTYPE (1<<15:
+// NONCOMPRESSED_PUBKEY for 65-byte keys) do change it and are not implemented here, so they are refused, like any
+// bit this file does not know.
+#define BCP_FLAGS_FASTPATH_NEUTRAL ((1u << 0) | (1u << 4) | (1u << 5) | (1u << 7) | (1u << 8) | (1u << 9) | (1u << 10) | (1u << 13))
+static int check_fastpath_flags(uint32_t flags, const char *fn) {
+    if ((flags & BCP_FLAGS_POSTFORK_REQUIRED) != BCP_FLAGS_POSTFORK_REQUIRED || (flags & BCP_FLAG_ALLOW_NON_FORKID)) {
+        bcp_set_error("%s: the fast path implements the post-fork script flags (STRICTENC|DERSIG|LOW_S|NULLFAIL|"
+                      "SIGHASH_FORKID, no ALLOW_NON_FORKID); got 0x%x", fn, flags);
+        return BCP_ERR_INVALID;
+    }
+    const uint32_t unknown = flags & ~(BCP_FLAGS_POSTFORK_REQUIRED | BCP_FLAGS_FASTPATH_NEUTRAL);
+    if (unknown) {
+        bcp_set_error("%s: script flag bits 0x%x would change the result for this script shape and are not implemented by "
+                      "the fast path (MINIMALDATA, COMPRESSED_PUBKEYTYPE, unknown bits)", fn, unknown);
+        return BCP_ERR_INVALID;
+    }
+    if ((flags & (1u << 8)) && !(flags & 1u)) { /* VerifyScript asserts P2SH whenever CLEANSTACK is set (interpreter.cpp:1619) */
+        bcp_set_error("%s: CLEANSTACK without P2SH is not a valid flag combination", fn);
+        return BCP_ERR_INVALID;
+    }
+    return BCP_OK;
+}
 
 // compact size with the canonical-encoding and MAX_SIZE rules of ReadCompactSize (src/serialize.h:260-300)
 static int rd_compact_canon(const uint8_t *p, size_t len, size_t *pos, uint64_t *v) {
@@ -274,11 +299,17 @@ BCP_API int bcp_gpu_block_scripts_p2pkh(int device, const uint8_t *blk, size_t l
         bcp_set_error("bcp_gpu_block_scripts_p2pkh: NULL buffer");
         return BCP_ERR_INVALID;
     }
-    if ((flags & BCP_FLAGS_POSTFORK_REQUIRED) != BCP_FLAGS_POSTFORK_REQUIRED || (flags & BCP_FLAG_ALLOW_NON_FORKID)) {
-        bcp_set_error("bcp_gpu_block_scripts_p2pkh: unsupported script flags 0x%x for the fast path", flags);
-        return BCP_ERR_INVALID;
-    }
+    if (check_fastpath_flags(flags, "bcp_gpu_block_scripts_p2pkh") != BCP_OK) return BCP_ERR_INVALID;
     if (len > 0xFFFFFFF0ull || tx_off[ntx] > len) { bcp_set_error("bcp_gpu_block_scripts_p2pkh: offsets exceed the block"); return BCP_ERR_INVALID; }
+    // The kernels stage the bytes between the first and the last transaction of each 128-input group in shared memory,
+    // so the subset must be in block order and every input must lie inside the transaction it names.
+    for (size_t i = 0; i < n_inputs; i++) {
+        const uint32_t t = in_tx[i];
+        if (t >= ntx || (i && t < in_tx[i - 1]) || in_off[i] < tx_off[t] + 5 || (uint64_t)in_off[i] + 41 > tx_off[t + 1]) {
+            bcp_set_error("bcp_gpu_block_scripts_p2pkh: input %zu is out of block order or outside transaction %u", i, t);
+            return BCP_ERR_INVALID;
+        }
+    }
     std::lock_guard<std::mutex> lk(c->mu);
     BCP_CUDA(cudaSetDevice(c->device));
     auto up = [](size_t x) { return (x + 255) / 256 * 256; };
@@ -349,11 +380,7 @@ BCP_API int bcp_gpu_block_connect_p2pkh(int device, const uint8_t *blk, size_t l
         bcp_set_error("bcp_gpu_block_connect_p2pkh: NULL buffer");
         return BCP_ERR_INVALID;
     }
-    if ((flags & BCP_FLAGS_POSTFORK_REQUIRED) != BCP_FLAGS_POSTFORK_REQUIRED || (flags & BCP_FLAG_ALLOW_NON_FORKID)) {
-        bcp_set_error("bcp_gpu_block_connect_p2pkh: the fast path implements the post-fork script flags "
-                      "(STRICTENC|DERSIG|LOW_S|NULLFAIL|SIGHASH_FORKID, no ALLOW_NON_FORKID); got 0x%x", flags);
-        return BCP_ERR_INVALID;
-    }
+    if (check_fastpath_flags(flags, "bcp_gpu_block_connect_p2pkh") != BCP_OK) return BCP_ERR_INVALID;
     if (len > 0xFFFFFFF0ull) { bcp_set_error("block too large"); return BCP_ERR_INVALID; }
     // Device layout is sized from upper bounds (a transaction is at least 60 bytes, an input at least 41) so that
     // the raw block can start its way to the device BEFORE the host framing scan runs; with a pinned `blk` the copy
@@ -480,11 +507,7 @@ BCP_API int bcp_gpu_blocks_connect_p2pkh(int device, size_t nblk, const uint8_t 
     if (!c) return BCP_ERR_NOT_INIT;
     if (nblk == 0) return BCP_OK;
     if (!blks || !lens || !n_inputs || !roots32) { bcp_set_error("bcp_gpu_blocks_connect_p2pkh: NULL buffer"); return BCP_ERR_INVALID; }
-    if ((flags & BCP_FLAGS_POSTFORK_REQUIRED) != BCP_FLAGS_POSTFORK_REQUIRED || (flags & BCP_FLAG_ALLOW_NON_FORKID)) {
-        bcp_set_error("bcp_gpu_blocks_connect_p2pkh: the fast path implements the post-fork script flags "
-                      "(STRICTENC|DERSIG|LOW_S|NULLFAIL|SIGHASH_FORKID, no ALLOW_NON_FORKID); got 0x%x", flags);
-        return BCP_ERR_INVALID;
-    }
+    if (check_fastpath_flags(flags, "bcp_gpu_blocks_connect_p2pkh") != BCP_OK) return BCP_ERR_INVALID;
     auto up = [](size_t x) { return (x + 255) / 256 * 256; };
     // body[b] = where block b's transactions start in its host buffer; base[b] = where they start in the device buffer
     std::vector<size_t> body(nblk), base(nblk + 1, 0), in_base(nblk + 1, 0);

@@ -147,7 +147,11 @@ BCP_API int bcp_gpu_merkle_root_dev_static(int device, const uint8_t *d_leaves32
  *   spk / spk_off / amounts   the spent scriptPubKeys (concatenated, spk_off[n_inputs+1]) and values, one per
  *                             non-coinbase input in block order
  *   flags                     SCRIPT_VERIFY_* bits as in src/script/interpreter.h:32-121; must contain
- *                             STRICTENC|DERSIG|LOW_S|NULLFAIL|ENABLE_SIGHASH_FORKID and not ALLOW_NON_FORKID
+ *                             STRICTENC|DERSIG|LOW_S|NULLFAIL|ENABLE_SIGHASH_FORKID and not ALLOW_NON_FORKID.  Of the
+ *                             other bits only those that cannot change the result for this script shape are accepted
+ *                             (P2SH, NULLDUMMY, SIGPUSHONLY, DISCOURAGE_UPGRADABLE_NOPS, CLEANSTACK with P2SH, CLTV,
+ *                             CSV, MINIMALIF); MINIMALDATA, COMPRESSED_PUBKEYTYPE and unknown bits are refused with
+ *                             BCP_ERR_INVALID rather than silently ignored
  *   script_err[i]             the ScriptError VerifyScript reports for input i (src/script/script_error.h; 0 = OK), or
  *                             255 when the input is not of this shape and must be run through the host interpreter
  *   all_ok                    1 iff every script_err is 0 (the `fAllOk` of the check queue)
@@ -166,7 +170,9 @@ BCP_API long bcp_block_index_full(const uint8_t *blk, size_t len, int legacy_hea
                                   long *nout_out, uint64_t *in_key);
 /* The script checks alone, for any subset of a block's inputs chosen by the caller (arrays describe the subset;
  * spk_off may point into a larger offsets array).  This is the unit that shards across GPUs: one call per device
- * over its index range, verdicts AND-ed on the host like `fAllOk &= fOk` (src/checkqueue.h:77). */
+ * over its index range, verdicts AND-ed on the host like `fAllOk &= fOk` (src/checkqueue.h:77).  The subset must be
+ * listed in block order (in_tx non-decreasing) and every in_off must lie inside the transaction in_tx names — the
+ * kernels stage the span of transactions each 128-input group touches; anything else is BCP_ERR_INVALID. */
 BCP_API int bcp_gpu_block_scripts_p2pkh(int device, const uint8_t *blk, size_t len, const uint32_t *tx_off, size_t ntx,
                                         const uint32_t *in_off, const uint32_t *in_tx, const uint32_t *in_n, size_t n_inputs,
                                         const uint8_t *spk, const uint32_t *spk_off, const int64_t *amounts, uint32_t flags,

@@ -12,8 +12,12 @@
 //   script checks (CScriptCheck, src/validation.cpp:1350-1359) for every input                 -> GPUs, sharded by input index range,
 //            one bcp_gpu_block_scripts_p2pkh call per device, verdicts AND-ed here (src/checkqueue.h:77)
 //   commit: spend inputs, add outputs
-// Not done (outside the hot path): amounts/fees/maturity (Consensus::CheckTxInputs), sigop limits, BIP68 locks,
-// difficulty, undo data.  Inputs that are not of the P2PKH shape are reported (reason "script-not-in-fast-path"):
+// Context-free structure rules of CheckBlock / CheckCoinbase / CheckRegularTransaction (src/validation.cpp:476-570,
+// 3255-3330) that need nothing but the framing are applied by the scan: bad-cb-missing, bad-cb-length, bad-tx-coinbase,
+// bad-txns-vin-empty, bad-txns-vout-empty, bad-txns-oversize, bad-txns-vout-negative / -toolarge /
+// -txouttotal-toolarge, bad-txns-prevout-null.
+// Not done (outside the hot path): fees/maturity (Consensus::CheckTxInputs), sigop limits, block size limit, BIP68
+// locks, difficulty, undo data.  Inputs that are not of the P2PKH shape are reported (reason "script-not-in-fast-path"):
 // a node would run them through its interpreter.
 #ifndef BCP_COMPAT_CHAIN_H
 #define BCP_COMPAT_CHAIN_H
@@ -405,6 +409,59 @@ private:
         uint8_t eqOk = 1;
         std::string errTx, errEq;
         double frameSecs = 0, deviceSecs = 0; // time this slot's thread spent in each part (diagnostics)
+        const char *structErr = nullptr;      // first structure rule of CheckBlock the block breaks (reference reject string)
+        // CheckBlock's context-free transaction rules, from the framing arrays (src/validation.cpp:3255-3330 calling
+        // CheckCoinbase :531-549 and CheckRegularTransaction :551-570, both over CheckTransactionCommon :476-529), in
+        // the reference's order: the coinbase first, then every other transaction in turn.
+        void CheckStructure(const uint8_t *b) {
+            structErr = nullptr;
+            if (nin < 0 || ntx < 1) { structErr = "bad-cb-missing"; return; }
+            static const int64_t MAX_MONEY_SAT = 21000000ll * 100000000ll; // src/amount.h:127
+            size_t o = 0, i = 0; // cursors into the flat output / input lists (both in block order)
+            for (long t = 0; t < ntx; t++) {
+                size_t pos = (size_t)tx_off[(size_t)t] + 4;
+                const uint64_t n_in = ReadCompact(b, pos);
+                bool cb = false;
+                uint64_t cbScriptLen = 0;
+                if (n_in == 1) {
+                    cb = true;
+                    for (int k = 0; k < 32; k++) cb = cb && b[pos + k] == 0;
+                    for (int k = 32; k < 36; k++) cb = cb && b[pos + k] == 0xFF;
+                    size_t q = pos + 36;
+                    cbScriptLen = ReadCompact(b, q);
+                }
+                size_t po = tx_out_off[(size_t)t];
+                const uint64_t n_out = ReadCompact(b, po);
+                const char *e = nullptr;
+                if (t == 0 && !cb) e = "bad-cb-missing";
+                else if (t > 0 && cb) e = "bad-tx-coinbase";
+                else if (n_in == 0) e = "bad-txns-vin-empty";
+                else if (n_out == 0) e = "bad-txns-vout-empty";
+                else if (tx_off[(size_t)t + 1] - tx_off[(size_t)t] > 1000000u) e = "bad-txns-oversize"; // MAX_TX_SIZE, consensus.h:14
+                int64_t total = 0;
+                for (; o < (size_t)nout && out_tx[o] == (uint32_t)t; o++) {
+                    if (e) continue;
+                    int64_t v;
+                    memcpy(&v, b + out_off[o], 8);
+                    if (v < 0) e = "bad-txns-vout-negative";
+                    else if (v > MAX_MONEY_SAT) e = "bad-txns-vout-toolarge";
+                    else if ((total += v) > MAX_MONEY_SAT) e = "bad-txns-txouttotal-toolarge";
+                }
+                if (!e && t == 0 && (cbScriptLen < 2 || cbScriptLen > 100)) e = "bad-cb-length";
+                for (; i < (size_t)nin && in_tx[i] == (uint32_t)t; i++) { // listed inputs = those of non-coinbase-shaped txs
+                    if (e) continue;
+                    const uint8_t *op = b + in_off[i];
+                    uint64_t h8;
+                    memcpy(&h8, op, 8);
+                    if (h8 != 0) continue;
+                    bool null = true;
+                    for (int k = 8; k < 32; k++) null = null && op[k] == 0;
+                    for (int k = 32; k < 36; k++) null = null && op[k] == 0xFF;
+                    if (null) e = "bad-txns-prevout-null";
+                }
+                if (e) { structErr = e; return; }
+            }
+        }
         void Device(int dev, unsigned ehN, unsigned ehK, int shardBits) {
             const auto td0 = std::chrono::steady_clock::now();
             const size_t soln = ehN ? ((size_t)1 << ehK) * (ehN / (ehK + 1) + 1) / 8 : 0;
@@ -469,6 +526,7 @@ private:
             }
             blk = b;
             len = l;
+            if (nin >= 0 && ntx >= 1) CheckStructure(b);
             valid = true;
             frameSecs += std::chrono::duration<double>(std::chrono::steady_clock::now() - tf0).count();
         }
@@ -482,7 +540,7 @@ private:
         std::swap(a.root, b.root); std::swap(a.hash, b.hash); std::swap(a.mutated, b.mutated); std::swap(a.rcTx, b.rcTx);
         std::swap(a.rcEq, b.rcEq); std::swap(a.eqOk, b.eqOk); std::swap(a.deviceDone, b.deviceDone);
         std::swap(a.ntx, b.ntx); std::swap(a.nin, b.nin); std::swap(a.nout, b.nout); std::swap(a.blk, b.blk); std::swap(a.len, b.len);
-        std::swap(a.valid, b.valid);
+        std::swap(a.valid, b.valid); std::swap(a.structErr, b.structErr);
         std::swap(a.frameSecs, b.frameSecs); std::swap(a.deviceSecs, b.deviceSecs);
     }
 
@@ -615,6 +673,7 @@ private:
         if (cur.rcTx != BCP_OK) { Rollback(w); reason = "device-error: " + cur.errTx; return false; }
         if (memcmp(cur.root, blk + 36, 32) != 0) { Rollback(w); reason = "bad-txnmrklroot"; return false; }
         if (cur.mutated) { Rollback(w); reason = "bad-txns-duplicate"; return false; }
+        if (cur.structErr) { Rollback(w); reason = cur.structErr; return false; } // after the Merkle checks, like CheckBlock
         memcpy(w.hash, cur.hash, 32);
         // Script checks, sharded by input index range over the devices.  When pass A resolved every input they start
         // now, from helper threads, and run while the team inserts the block's outputs (pass B).
@@ -655,25 +714,25 @@ private:
         // each such coin only once.
         bool missing = false;
         if (unresolved) {
-            std::unordered_map<uint64_t, uint32_t> txIndex; // first 8 bytes of a txid -> transaction number (verified below)
+            // first 8 bytes of a txid -> transaction number.  A multimap: two transactions of a block may share those
+            // 8 bytes (2^32 work to craft), and every candidate is compared on all 32 bytes below.
+            std::unordered_multimap<uint64_t, uint32_t> txIndex;
             txIndex.reserve((size_t)ntx * 2);
-            for (long t = 0; t < ntx; t++) {
-                uint64_t k;
-                memcpy(&k, &cur.txids[(size_t)t * 32], 8);
-                txIndex.emplace(k, (uint32_t)t);
-            }
+            for (long t = 0; t < ntx; t++) txIndex.emplace(TxKey(&cur.txids[(size_t)t * 32]), (uint32_t)t);
             for (size_t i = 0; i < (size_t)nin && !missing; i++) {
                 Staged &st = w.stage[i];
                 if (st.state != ST_MISS) continue;
                 OutPoint op;
                 memcpy(op.b, blk + cur.in_off[i], 36);
-                uint64_t k;
-                memcpy(&k, op.b, 8);
-                auto it = txIndex.find(k);
+                // the creating transaction: the EARLIEST one of this block with that txid (identical transactions have
+                // identical outputs, and UpdateCoins applies each as it is met)
+                bool created_before = false;
+                auto range = txIndex.equal_range(TxKey(op.b));
+                for (auto it = range.first; it != range.second; ++it)
+                    if (it->second < cur.in_tx[i] && memcmp(&cur.txids[(size_t)it->second * 32], op.b, 32) == 0) created_before = true;
                 CoinTable &T = ShardOf(op);
                 CoinSlot *c = T.find(op);
-                if (!c || it == txIndex.end() || memcmp(&cur.txids[(size_t)it->second * 32], op.b, 32) != 0 ||
-                    it->second >= cur.in_tx[i]) {
+                if (!c || !created_before) {
                     missing = true;
                     break;
                 }
@@ -830,6 +889,16 @@ private:
             }
         });
         w.spk_off[nin] = (uint32_t)sum[(size_t)P];
+    }
+    // Key of the in-block transaction index.  BCP_CHAIN_TEST_TXKEY_BITS (tests only) narrows it so that collisions,
+    // which take 2^32 hashes to find for the real 64-bit key, can be exercised.
+    static uint64_t TxKey(const uint8_t *txid) {
+        uint64_t k;
+        memcpy(&k, txid, 8);
+#ifdef BCP_CHAIN_TEST_TXKEY_BITS
+        k &= (1ull << BCP_CHAIN_TEST_TXKEY_BITS) - 1;
+#endif
+        return k;
     }
     static uint64_t ReadCompact(const uint8_t *p, size_t &pos) { // already validated by the framing scan
         uint8_t c = p[pos++];

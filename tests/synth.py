@@ -369,11 +369,18 @@ def equihash_solve_48_5(input140):
     return sorted(set(sols))
 
 
+STRUCTURE_KINDS = {"second_coinbase": b"bad-tx-coinbase", "no_coinbase": b"bad-cb-missing", "cb_length": b"bad-cb-length",
+                   "prevout_null": b"bad-txns-prevout-null", "vin_empty": b"bad-txns-vin-empty",
+                   "vout_empty": b"bad-txns-vout-empty", "vout_negative": b"bad-txns-vout-negative",
+                   "vout_toolarge": b"bad-txns-vout-toolarge"}
+
+
 def synthetic_chain(nblocks=6, ntx=20, nkeys=8, equihash=True, corrupt=None, inblock=()):
     """A chain of post-fork blocks with REAL UTXO dependencies: block b's transaction j spends
     output 0 of block b-1's transaction j; block 0 spends seeded "prev" coins.  With equihash=True every header
     carries a valid regtest (48,5) solution.  corrupt = (block, kind) with kind in {"bad_sig", "double_spend",
-    "bad_merkle", "missing_input", "bad_equihash", "inblock_reversed", "inblock_double"} damages exactly one block.
+    "bad_merkle", "missing_input", "bad_equihash", "inblock_reversed", "inblock_double"} or a key of STRUCTURE_KINDS
+    (value = the reference's reject reason) damages exactly one block.
     inblock = positions j (>= 1) whose transaction spends output 0 of transaction j-1 of the SAME block in every block
     (the coin it would have spent stays unspent and is handed to the next block's transaction j-1 instead);
     "inblock_reversed" makes transaction 5 spend the output of transaction 6 (created AFTER it), "inblock_double" makes
@@ -438,6 +445,28 @@ def synthetic_chain(nblocks=6, ntx=20, nkeys=8, equihash=True, corrupt=None, inb
         for j in range(ntx):
             txs.append(built[("tx", j)])
             new_out.append(built.get(("keep", j), built[j]))
+        # structure damage (CheckBlock's context-free rules, src/validation.cpp:476-570, 3255-3330); signatures do not matter:
+        # the reference rejects these in CheckBlock, before any script runs
+        if kind in STRUCTURE_KINDS:
+            t2 = txs[3]  # transaction j = 2: version(4) nin(1) outpoint(36) ...
+            sslen = t2[41]
+            in_end = 42 + sslen + 4
+            if kind == "second_coinbase":
+                txs.insert(2, cb[:41] + b"\x04" + (800000 + b).to_bytes(4, "little") + cb[46:])
+            elif kind == "no_coinbase":
+                txs = txs[1:]
+            elif kind == "cb_length":
+                txs[0] = cb[:41] + b"\x01\x00" + cb[46:]
+            elif kind == "prevout_null":
+                txs[3] = t2[:4] + b"\x02" + t2[5:in_end] + bytes(32) + b"\xff\xff\xff\xff" + b"\x00" + b"\xff\xff\xff\xff" + t2[in_end:]
+            elif kind == "vin_empty":
+                txs[3] = t2[:4] + b"\x00" + t2[in_end:]
+            elif kind == "vout_empty":
+                txs[3] = t2[:in_end] + b"\x00" + t2[-4:]
+            elif kind == "vout_negative":
+                txs[3] = t2[:in_end + 1] + (2**64 - 1).to_bytes(8, "little") + t2[in_end + 9:]
+            elif kind == "vout_toolarge":
+                txs[3] = t2[:in_end + 1] + (21000000 * 10**8 + 1).to_bytes(8, "little") + t2[in_end + 9:]
         prevs.append(([built[("prev", j)][0] for j in range(ntx)], [built[("prev", j)][1] for j in range(ntx)]))
         root, _ = o.merkle_root(b"".join(o.sha256d(t) for t in txs))
         if kind == "bad_merkle":

@@ -13,8 +13,8 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 MAGIC = bytes.fromhex("e48f1d1c")
 
 
-def chain_lib():
-    L = C.CDLL(os.path.join(ROOT, "bitcoincashplus_b200", "libbcp_chain.so"))
+def chain_lib(path=None):
+    L = C.CDLL(path or os.path.join(ROOT, "bitcoincashplus_b200", "libbcp_chain.so"))
     L.bcp_chain_new.restype = C.c_void_p
     L.bcp_chain_new.argtypes = [C.POINTER(C.c_int), C.c_int, C.c_uint32, C.c_uint, C.c_uint, C.c_char_p, C.c_size_t]
     L.bcp_chain_new_threads.restype = C.c_void_p
@@ -84,6 +84,52 @@ def test_chain_rejects_the_damaged_block_with_the_reference_reason(kind, expect)
     size_before = L.bcp_chain_utxo_size(h)
     assert size_before == 12 + 3  # a rejected block leaves the UTXO set untouched
     L.bcp_chain_free(h)
+
+
+@pytest.mark.parametrize("kind", sorted(synth.STRUCTURE_KINDS))
+def test_chain_applies_checkblock_structure_rules(kind):
+    """CheckBlock's context-free transaction rules (src/validation.cpp:3255-3330 -> CheckCoinbase / CheckRegularTransaction
+    :476-570): a second coinbase-shaped transaction, a missing coinbase, null prevouts, empty input / output lists and
+    out-of-range amounts are rejected with the reference's reason and leave the UTXO set untouched."""
+    L = chain_lib()
+    blocks, seeds, _ = synth.synthetic_chain(3, 10, corrupt=(1, kind))
+    good, _, _ = synth.synthetic_chain(3, 10)
+    reason = C.create_string_buffer(256)
+    for threads in (1, 4):
+        h = new_chain(L, seeds, walk_threads=threads)
+        assert L.bcp_chain_connect_block(h, blocks[0], len(blocks[0]), reason, 256) == 1, reason.value
+        assert L.bcp_chain_connect_block(h, blocks[1], len(blocks[1]), reason, 256) == 0
+        assert reason.value == synth.STRUCTURE_KINDS[kind], (kind, reason.value)
+        assert L.bcp_chain_utxo_size(h) == 10 + 1
+        assert L.bcp_chain_connect_block(h, good[1], len(good[1]), reason, 256) == 1, (kind, reason.value)
+        L.bcp_chain_free(h)
+
+
+def test_chain_in_block_index_survives_txid_prefix_collisions(oracle):
+    """The in-block transaction index is keyed by the first 8 bytes of the txid; two transactions of a block sharing them
+    (2^32 hashes to craft) must not hide one another.  A test build of the connector narrows the key to 4 bits
+    (BCP_CHAIN_TEST_TXKEY_BITS), so nearly every pair of transactions collides, and the chains of in-block spends must
+    connect exactly as with the full key — and the two failure modes must still be caught."""
+    path = os.path.join(ROOT, "tests", "cpp", "libbcp_chain_txkey4.so")
+    if not os.path.exists(path):
+        pytest.skip("tests/cpp/libbcp_chain_txkey4.so not built (__graft_entry__.build())")
+    L = chain_lib(path)
+    inb = (2, 7, 8, 9, 15, 16, 17, 30, 31)
+    blocks, seeds, _ = synth.synthetic_chain(3, 40, inblock=inb)
+    reason = C.create_string_buffer(256)
+    for threads in (1, 8):
+        h = new_chain(L, seeds, walk_threads=threads)
+        for i, b in enumerate(blocks):
+            assert L.bcp_chain_connect_block(h, b, len(b), reason, 256) == 1, (threads, i, reason.value)
+            assert L.bcp_chain_utxo_size(h) == 40 + (i + 1)
+        L.bcp_chain_free(h)
+    for kind in ("inblock_reversed", "inblock_double"):
+        bad, seeds2, _ = synth.synthetic_chain(2, 20, corrupt=(1, kind))
+        h = new_chain(L, seeds2)
+        assert L.bcp_chain_connect_block(h, bad[0], len(bad[0]), reason, 256) == 1
+        assert L.bcp_chain_connect_block(h, bad[1], len(bad[1]), reason, 256) == 0
+        assert reason.value == b"bad-txns-inputs-missingorspent", (kind, reason.value)
+        L.bcp_chain_free(h)
 
 
 def test_chain_shards_inputs_over_two_devices_when_present():
