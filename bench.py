@@ -36,6 +36,14 @@ MUL32_PER_VERIFY = 151228  # 64*(1348+39) + 36*(1482+253)
 BYTES_PER_VERIFY = 32 + 33 + 64 + 1
 
 
+def workload_config(n):
+    """The `config` object, identical in both arms (`--impl ours` and `--impl reference`) so the driver can match them."""
+    return {"workload": "configs[1]: batched secp256k1_ecdsa_verify, %d synthetic signatures per GPU incl. 1%% corrupted" % n,
+            "sigs_per_gpu": n, "sharding": "by signature index, one process per GPU, no collective",
+            "l2_policy": "inputs + scratch touched per step = %.0f MB (> 126 MB L2 at the default size)"
+                         % ((n * (161 + 80 + 768 + 1)) / 1e6)}
+
+
 def clocks_sampler(stop, out, gpu_index):
     q = "clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown," \
         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap"
@@ -63,7 +71,9 @@ def summarize_clocks(samples):
 
 
 def cpu_baseline(msg, pub, sig, budget_s=12.0):
-    """Reference libsecp256k1 (or the oracle port) on all host threads over a bounded sample."""
+    """Reference libsecp256k1 (or the oracle port) on all host threads over a bounded sample.  Returns the JSON object
+    and the verdicts of the sample (the first `len(verdicts)` signatures of the batch), which the caller compares
+    with the GPU's verdicts for the same signatures outside the timed region."""
     from oracle import pyoracle as po
 
     impl = po.ref() if po.have_ref() else po.oracle()
@@ -73,17 +83,17 @@ def cpu_baseline(msg, pub, sig, budget_s=12.0):
     impl.ecdsa_verify_batch(msg[:256 * min(cores, 8)].copy(), pub[:256 * min(cores, 8)].copy(),
                             sig[:256 * min(cores, 8)].copy(), cores)  # warm-up (context/tables)
     t0 = time.perf_counter()
-    impl.ecdsa_verify_batch(msg[:sample], pub[:sample], sig[:sample], cores)
+    verdicts = impl.ecdsa_verify_batch(msg[:sample], pub[:sample], sig[:sample], cores)
     dt = time.perf_counter() - t0
     # grow the sample until ~budget_s of wall time is spent (bounded by the batch)
     target = min(n, int(sample * max(1.0, budget_s / max(dt, 1e-3))))
     if target > sample * 1.5:
         sample = target
         t0 = time.perf_counter()
-        impl.ecdsa_verify_batch(msg[:sample], pub[:sample], sig[:sample], cores)
+        verdicts = impl.ecdsa_verify_batch(msg[:sample], pub[:sample], sig[:sample], cores)
         dt = time.perf_counter() - t0
     return {"value": sample / dt, "unit": "sigverifies/s", "cores": cores, "kind": impl.kind,
-            "sample": "first %d of the %d-signature batch, %.1f s wall, %d threads" % (sample, n, dt, cores)}
+            "sample": "first %d of the %d-signature batch, %.1f s wall, %d threads" % (sample, n, dt, cores)}, verdicts
 
 
 def traffic_from_profile(n):
@@ -331,6 +341,49 @@ def equihash_bench(eng):
             "timed": "bcp_gpu_equihash_verify_batch on pinned host buffers incl. H2D of 14.9 MB (four chunks on two streams), verdicts + header hashes D2H"}
 
 
+def sharded_single_caller_bench(args, devices, msg, pub, sig, expected):
+    """The multi-GPU form north_star describes, measured as ONE caller sees it: one host process holds one batch in
+    pinned memory, bcp::VerifyTriples (include/compat/bcp_recorder.h) splits it by signature index over the N GPUs from
+    N host threads (each through bcp_gpu_ecdsa_verify_batch: H2D, kernels, D2H), the verdict bytes land in one array and
+    are AND-ed on the host like `fAllOk &= fOk` (src/checkqueue.h:77).  Two batch sizes: the 1M batch of configs[1] and
+    8 x that.  Runs on rank 0 over every GPU of the job after the per-rank sections are done."""
+    import numpy as np
+
+    import bitcoincashplus_b200 as bcp
+
+    G = bcp.lib()
+    L = C.CDLL(os.path.join(ROOT, "bitcoincashplus_b200", "libbcp_chain.so"))
+    L.bcp_sharded_ecdsa_verify.argtypes = [C.POINTER(C.c_int), C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_size_t,
+                                           C.c_uint32, C.c_void_p, C.POINTER(C.c_int)]
+    n1 = len(msg)
+    out = {"gpus": len(devices), "host_threads": len(devices),
+           "timed": "bcp_sharded_ecdsa_verify = bcp::VerifyTriples: one pinned host batch split by index over the GPUs, one host "
+                    "thread per GPU, H2D + kernels + D2H + the host-side AND inside the timed region; wall clock of the one caller"}
+    devs = (C.c_int * len(devices))(*devices)
+    for mult in (1, 8):
+        n = n1 * mult
+        hm, hp, hs, ho = G.bcp_gpu_host_alloc(n * 32), G.bcp_gpu_host_alloc(n * 65), G.bcp_gpu_host_alloc(n * 64), G.bcp_gpu_host_alloc(n)
+        for k in range(mult):
+            C.memmove(hm + k * n1 * 32, msg.ctypes.data, n1 * 32)
+            C.memmove(hp + k * n1 * 65, pub.ctypes.data, n1 * 65)
+            C.memmove(hs + k * n1 * 64, sig.ctypes.data, n1 * 64)
+        allok = C.c_int(-1)
+        reps = 5 if mult == 1 else 3
+        for _ in range(2):
+            assert L.bcp_sharded_ecdsa_verify(devs, len(devices), hm, hp, hs, n, 0, ho, C.byref(allok)) == 0
+        t0 = time.perf_counter()
+        for _ in range(reps):
+            assert L.bcp_sharded_ecdsa_verify(devs, len(devices), hm, hp, hs, n, 0, ho, C.byref(allok)) == 0
+        dt = (time.perf_counter() - t0) / reps
+        got = np.ctypeslib.as_array(C.cast(ho, C.POINTER(C.c_uint8)), shape=(n,)).astype(bool)
+        assert (got == np.tile(expected, mult)).all() and allok.value == 0
+        out["batch_%dM" % (n // 1000000) if n % 1000000 == 0 else "batch_%d" % n] = {
+            "signatures": n, "ms": dt * 1e3, "sigverifies_per_s": n / dt, "h2d_bytes": n * 161, "d2h_bytes": n}
+        for p_ in (hm, hp, hs, ho):
+            G.bcp_gpu_host_free(p_)
+    return out
+
+
 def chain_bench(args, devices):
     """Secondary measurement in the shape of BASELINE.json configs[4]: a synthetic chain of 8 MB blocks with real UTXO
     dependencies (block b spends block b-1) and valid regtest Equihash (48,5) headers, connected block by block by the
@@ -445,11 +498,12 @@ def run_reference(args):
     line = {"metric": "ecdsa_sigverifies_per_s", "value": v, "unit": "sigverifies/s", "n_gpus": args.gpus,
             "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * dt / args.steps, "higher_is_better": True,
             "scaling": "weak", "vs_baseline": None, "dtype": "u32", "data": "synthetic", "impl": "reference",
-            "config": {"workload": "configs[1]: batched secp256k1_ecdsa_verify, %d synthetic signatures incl. 1%% corrupted"
-                       % n, "sigs_per_gpu": n},
+            "config": workload_config(n),
             "cpu_baseline": {"value": v, "unit": "sigverifies/s", "cores": cores, "kind": impl.kind,
                              "sample": "%d signatures per step (bounded sample of the batch), %d threads" % (sample, cores)},
             "e2e": {"value": v, "unit": "sigverifies/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+            "sample_note": "each step verifies a bounded sample (%d signatures = 1,500 x %d threads) of the %d-signature batch, "
+                           "not the whole batch; the metric is a throughput" % (sample, cores, n),
             "gpu_launches": 0}
     print(json.dumps(line))
 
@@ -480,13 +534,13 @@ def main():
     local = int(os.environ.get("LOCAL_RANK", "0"))
     dist = world > 1
     if dist:
-        # stdout carries exactly one JSON line: keep NCCL's own banner ("NCCL version ...", printed to stdout under
-        # NCCL_DEBUG=VERSION/INFO) out of it
-        os.environ["NCCL_DEBUG"] = "WARN"
+        # The data path has no collective (signatures shard by index, verdicts are AND-ed by the caller), so there is no
+        # NCCL here: torch.distributed is only the launcher's rendezvous, a barrier and the max over ranks of a few
+        # timings, all on the host through gloo.
         import torch.distributed as td
 
-        td.init_process_group("nccl", device_id=torch.device("cuda", local))
-        hostgrp = td.new_group(backend="gloo")  # host-side barriers/maxima for the secondary sections (no GPU spin)
+        td.init_process_group("gloo")
+        hostgrp = td.group.WORLD
     torch.cuda.set_device(local)
     dev = torch.device("cuda", local)
     eng = bcp.Engine(local)
@@ -556,7 +610,7 @@ def main():
     assert (ok_host == expected).all(), "verdict mismatch in e2e leg"
 
     if dist:
-        t = torch.tensor([ms, e2e_s * 1e3], device=dev, dtype=torch.float64)
+        t = torch.tensor([ms, e2e_s * 1e3], dtype=torch.float64)
         td.all_reduce(t, op=td.ReduceOp.MAX)
         ms, e2e_ms = t[0].item(), t[1].item()
     else:
@@ -598,10 +652,7 @@ def main():
         "metric": "ecdsa_sigverifies_per_s", "value": value, "unit": "sigverifies/s", "n_gpus": world, "steps": args.steps,
         "warmup": args.warmup, "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak",
         "vs_baseline": None, "dtype": "u32", "data": "synthetic",
-        "config": {"workload": "configs[1]: batched secp256k1_ecdsa_verify, 1M synthetic signatures incl. 1% corrupted",
-                   "sigs_per_gpu": n, "sharding": "by signature index, one process per GPU, no collective",
-                   "l2_policy": "inputs + scratch touched per step = %.0f MB (> 126 MB L2 at the default size)"
-                   % ((n * (161 + 80 + 512 + 1)) / 1e6)},
+        "config": workload_config(n),
         "roofline": {"bound": "int32",
                      "bound_note": "32x32->64 multiply-add pipe (IMAD.WIDE on fmaheavy): nothing on this path is HBM- or "
                                    "tensor-bound (SURVEY.md 8d); the HBM view is under 'hbm'",
@@ -616,7 +667,16 @@ def main():
         "gpu_launches": 2 * args.steps, "clocks": summarize_clocks(samples), "gen_seconds": gen_s,
     }
     if not args.no_cpu_baseline:
-        line["cpu_baseline"] = cpu_baseline(msg, pub, sig)
+        # the CPU baseline verifies the very same signatures: its verdicts are the parity check of the timed batch
+        line["cpu_baseline"], cpu_verdicts = cpu_baseline(msg, pub, sig)
+        k = len(cpu_verdicts)
+        bad = np.nonzero((np.asarray(cpu_verdicts) != 0) != got[:k])[0]
+        assert bad.size == 0, "GPU verdicts differ from the CPU %s at %r" % (line["cpu_baseline"]["kind"], bad[:10])
+        bad = np.nonzero((np.asarray(cpu_verdicts) != 0) != ok_host[:k])[0]
+        assert bad.size == 0, "e2e verdicts differ from the CPU %s at %r" % (line["cpu_baseline"]["kind"], bad[:10])
+        line["parity_checked"] = int(k)
+        line["parity_note"] = ("verdicts of the device-resident leg and of the e2e leg compared, outside the timed regions, with the "
+                               "CPU baseline's verdicts for the same %d signatures (%d rejected by both)" % (k, int((np.asarray(cpu_verdicts) == 0).sum())))
     if not args.no_block:
         # the block numbers as a fraction of the integer roofline too (same convention as `roofline`: the reference
         # algorithm's 151,228 mul32 per input against the measured IMAD.WIDE peak, per GPU)
@@ -632,6 +692,7 @@ def main():
         line["block8mb_window"] = win_section
         line["checkqueue_dropin"] = queue_dropin_bench(args)
         line["equihash10k"] = equihash_bench(eng)
+        line["sharded_single_caller"] = sharded_single_caller_bench(args, list(range(world)), msg, pub, sig, expected)
         if args.chain_blocks > 0:
             line["chain"] = chain_bench(args, list(range(world)))
     print(json.dumps(line), flush=True)

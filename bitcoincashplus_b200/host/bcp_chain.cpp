@@ -6,6 +6,7 @@
 #include <string>
 
 #include "../../include/compat/bcp_chain.h"
+#include "../../include/compat/bcp_recorder.h"
 
 #define CHAIN_API extern "C" __attribute__((visibility("default")))
 
@@ -69,4 +70,19 @@ CHAIN_API void bcp_chain_phase_seconds(void *h, double *out5) {
 CHAIN_API void bcp_chain_walk_seconds(void *h, double out4[4]) {
     auto *v = static_cast<bcp::ChainValidator *>(h);
     for (int i = 0; i < 4; i++) out4[i] = v->walk[i];
+}
+
+// One caller, one batch, every GPU: bcp::VerifyTriples (include/compat/bcp_recorder.h) splits the batch by index range over
+// `devices`, one host thread per device, and the per-signature verdicts land in one array; *all_ok is their AND, the
+// `fAllOk &= fOk` of the check queue (src/checkqueue.h:77).  Returns 0, or -1 on a device failure (never a verdict then).
+CHAIN_API int bcp_sharded_ecdsa_verify(const int *devices, int ndev, const uint8_t *msg32, const uint8_t *pub65, const uint8_t *sig64,
+                                       size_t n, uint32_t flags, uint8_t *ok, int *all_ok) {
+    if (!bcp::SetDevices(std::vector<int>(devices, devices + ndev))) return -1;
+    if (!bcp::VerifyTriples(msg32, pub65, sig64, n, ok, flags)) return -1;
+    if (all_ok) {
+        int a = 1;
+        for (size_t i = 0; i < n; i++) a &= ok[i] != 0;
+        *all_ok = a;
+    }
+    return 0;
 }

@@ -281,9 +281,11 @@ public:
         // Lanes (independent contexts on one GPU): the two blocks ConnectFile keeps in flight send their script checks
         // through lanes 0 and 1 of each device, so that block b+1's copies and extraction run under block b's ECDSA
         // kernels; header checks and txids of the blocks being scanned ahead go through lane 2 of the first device.
+        // A `devices` entry may itself carry a lane base in its upper bits (BCP_DEVICE_LANE(ordinal, base)): that entry then
+        // uses lanes base and base+1 of the GPU, so one GPU can stand in for two devices (tests on a one-GPU box).
         for (int d : devs)
             for (int lane = 0; lane < 2; lane++)
-                if (bcp_gpu_init(BCP_DEVICE_LANE(d & 0xFF, lane)) != BCP_OK) { err = bcp_gpu_last_error(); return false; }
+                if (bcp_gpu_init(BCP_DEVICE_LANE(d & 0xFF, (d >> 8) + lane)) != BCP_OK) { err = bcp_gpu_last_error(); return false; }
         devAux = BCP_DEVICE_LANE(devs[0] & 0xFF, 2);
         if (bcp_gpu_init(devAux) != BCP_OK) { err = bcp_gpu_last_error(); return false; }
         return true;
@@ -688,7 +690,7 @@ private:
                 const size_t lo = std::min((size_t)nin, g * per), hi = std::min((size_t)nin, lo + per);
                 if (lo >= hi) continue;
                 Work *pw = &w;
-                const int dev = BCP_DEVICE_LANE(devs[g] & 0xFF, (int)(&w - work)); /* work[0] -> lane 0, work[1] -> lane 1 */
+                const int dev = BCP_DEVICE_LANE(devs[g] & 0xFF, (devs[g] >> 8) + (int)(&w - work)); /* work[0] -> lane 0, work[1] -> lane 1 */
                 const uint32_t fl = flags;
                 w.th.emplace_back([pw, g, lo, hi, dev, fl] {
                     int all = 0;

@@ -112,7 +112,8 @@ inline bool SetDevices(const std::vector<int> &devs) {
 }
 
 //! Verifies n triples, sharded by index range over Devices(); ok[i] = verdict.  false = device failure.
-inline bool VerifyTriples(const uint8_t *msg, const uint8_t *pub, const uint8_t *sig, size_t n, uint8_t *ok) {
+inline bool VerifyTriples(const uint8_t *msg, const uint8_t *pub, const uint8_t *sig, size_t n, uint8_t *ok,
+                          uint32_t flags = BCP_ECDSA_FLAG_NORMALIZE_S) {
     if (n == 0) return true;
     const std::vector<int> devs = Devices();
     const size_t G = devs.size();
@@ -125,8 +126,7 @@ inline bool VerifyTriples(const uint8_t *msg, const uint8_t *pub, const uint8_t 
         auto work = [&, g, lo, hi] {
             rc[g] = bcp_gpu_init(devs[g]);
             if (rc[g] == BCP_OK)
-                rc[g] = bcp_gpu_ecdsa_verify_batch(devs[g], msg + lo * 32, pub + lo * 65, sig + lo * 64, hi - lo,
-                                                   BCP_ECDSA_FLAG_NORMALIZE_S, ok + lo);
+                rc[g] = bcp_gpu_ecdsa_verify_batch(devs[g], msg + lo * 32, pub + lo * 65, sig + lo * 64, hi - lo, flags, ok + lo);
         };
         if (G == 1) work();
         else th.emplace_back(work);

@@ -435,6 +435,8 @@ def synthetic_chain(nblocks=6, ntx=20, nkeys=8, equihash=True, corrupt=None, inb
             r_, s_ = int.from_bytes(s64[:32], "big"), int.from_bytes(s64[32:], "big")
             if kind == "bad_sig" and j == 3:
                 r_ ^= 2
+            if kind and kind.startswith("bad_sig@") and j == int(kind[8:]):
+                r_ ^= 2
             der = _der(r_, s_) + b"\x41"
             tx = build(bytes([len(der)]) + der + bytes([33]) + pubs[kj])
             built[j] = (o.sha256d(tx), 0, nk, amt_ - 1000)

@@ -146,6 +146,29 @@ def test_chain_shards_inputs_over_two_devices_when_present():
     L.bcp_chain_free(h)
 
 
+def test_chain_shards_inputs_over_two_lane_pairs_of_one_gpu():
+    """The multi-device path on a one-GPU box: lanes 0-1 and lanes 2-3 of GPU 0 stand in for two devices, each block's
+    inputs are split in two index ranges, and a bad signature in the SECOND range (owned by the second "device") must be
+    found there and reported with its block-wide input number; valid blocks connect, and the ConnectFile pipeline (two
+    blocks in flight) reports the same."""
+    L = chain_lib()
+    devs = (0, 2 << 8)
+    for ntx, bad_at in ((50, 40), (7, 6)):
+        blocks, seeds, _ = synth.synthetic_chain(4, ntx, corrupt=(2, "bad_sig@%d" % bad_at))
+        h = new_chain(L, seeds, devices=devs)
+        reason = C.create_string_buffer(256)
+        res = [L.bcp_chain_connect_block(h, b, len(b), reason, 256) for b in blocks[:3]]
+        assert res == [1, 1, 0] and reason.value == b"blk-bad-inputs (input %d, script error 31)" % bad_at, reason.value
+        assert L.bcp_chain_utxo_size(h) == ntx + 2
+        L.bcp_chain_free(h)
+        h = new_chain(L, seeds, devices=devs)
+        data = b"".join(MAGIC + len(b).to_bytes(4, "little") + b for b in blocks)
+        failed = C.c_long(-2)
+        n = L.bcp_chain_connect_file(h, data, len(data), MAGIC, reason, 256, C.byref(failed))
+        assert n == 2 and failed.value == 2 and reason.value.startswith(b"blk-bad-inputs (input %d," % bad_at)
+        L.bcp_chain_free(h)
+
+
 def test_chain_in_block_spends_and_their_failure_modes(oracle):
     """Transactions that spend outputs created earlier in the SAME block (chains of them), over several blocks; then the
     two ways this can go wrong: spending an output of a LATER transaction, and spending an in-block output twice.  After a
