@@ -20,7 +20,9 @@
 #ifndef BCP_STEP_SYNC_EVERY
 #define BCP_STEP_SYNC_EVERY 4
 #endif
-#define BCP_STEP_SYNC() do { if (BCP_STEP_SYNC_EVERY == 1 || (t % BCP_STEP_SYNC_EVERY) == 0) __syncthreads(); } while (0)
+/* a named barrier over the sync_n threads that walk the steps together: in the last, partly filled round of the persistent
+ * kernel only the warps that hold signatures take part, the others have left */
+#define BCP_STEP_SYNC() do { if (BCP_STEP_SYNC_EVERY == 1 || (t % BCP_STEP_SYNC_EVERY) == 0) asm volatile("bar.sync 1, %0;" :: "r"(sync_n) : "memory"); } while (0)
 #endif
 #include "ecdsa.cuh"
 #include <cstdlib>
@@ -43,7 +45,6 @@
 #endif
 #define BCP_SLICE (16 * BCP_WAVE)
 #define BCP_E2E_CHUNK (6 * BCP_WAVE)
-#define BCP_SIG_SCRATCH_WORDS (BCP_REC_WORDS + BCP_QTAB_WORDS) /* 80-byte record + 768-byte table per signature */
 
 __global__ void __launch_bounds__(128) k_gcomb_build(uint32_t *gcomb) {
     int idx = blockIdx.x * blockDim.x + threadIdx.x;
@@ -110,8 +111,63 @@ __global__ void __launch_bounds__(BCP_POINT_THREADS, BCP_POINT_BLOCKS_PER_SM)
     const size_t i = gi < n ? gi : n - 1; /* tail threads shadow the last signature (they must reach the barriers) */
     qtable_packed tab;
     tab.base = qtabs + gi * BCP_QTAB_WORDS; /* own slab even when shadowing: scratch is sized for whole blocks */
-    bool v = ecdsa_point_phase(rec + i * BCP_REC_WORDS, pub65 + 65 * i, sig64 + 64 * i, tab, gcomb);
+    bool v = ecdsa_point_phase(rec + i * BCP_REC_WORDS, pub65 + 65 * i, sig64 + 64 * i, tab, gcomb, (int)blockDim.x);
     if (gi < n) ok[gi] = v ? 1 : 0;
+}
+
+// Persistent form: the grid is exactly the resident set (BCP_POINT_BLOCKS_PER_SM blocks on every SM) and each block walks
+// over the batch in rounds, so that
+//   * a thread's {1..8}Q slab belongs to the RESIDENT SLOT (block, thread), not to the signature: the slabs of a whole
+//     launch are 148 x 512 x 768 B = 58 MB, written and re-read round after round inside the 126 MB L2, instead of 768 B
+//     of scratch per signature streaming through it (848 MB per million signatures, DRAM traffic 24x the algorithmic bytes);
+//   * the last, partly filled round is dealt out EVENLY: every block takes per_last signatures (a multiple of 32) and
+//     only the warps that hold some walk the steps, so what is left over runs on every SM at a few warps each (and
+//     correspondingly faster) instead of as whole 256-thread blocks on a fifth of the chip.
+__global__ void __launch_bounds__(BCP_POINT_THREADS, BCP_POINT_BLOCKS_PER_SM)
+    k_ecdsa_point_rounds(const uint8_t *__restrict__ pub65, const uint8_t *__restrict__ sig64, uint32_t n,
+                         const uint32_t *__restrict__ rec, uint32_t *__restrict__ qtabs, const uint32_t *__restrict__ gcomb,
+                         uint8_t *__restrict__ ok, uint32_t per_last) {
+    // Everything a round needs is recomputed from the kernel parameters (constant bank) and the round number, so that the
+    // only values this outer loop keeps alive across the point phase are `r` and the barrier width — the phase itself uses
+    // all 128 registers.
+    const uint32_t full = n / (gridDim.x * blockDim.x);
+    qtable_packed tab; /* slabs are packed per block: blockDim.x per block once there is a full round, else per_last */
+    tab.base = qtabs + ((size_t)blockIdx.x * (full ? blockDim.x : per_last) + threadIdx.x) * BCP_QTAB_WORDS;
+#pragma unroll 1
+    for (uint32_t r = 0; r <= n / (gridDim.x * blockDim.x); r++) {
+        uint32_t gi, i;
+        int sync_n = (int)blockDim.x;
+        {
+            const uint32_t stride = gridDim.x * blockDim.x;
+            if (r < n / stride) {
+                gi = r * stride + blockIdx.x * blockDim.x + threadIdx.x;
+                i = gi;
+            } else {
+                const uint32_t base = r * stride + blockIdx.x * per_last;
+                if (base >= n) break; /* uniform for the block */
+                const uint32_t left = n - base < per_last ? n - base : per_last;
+                const uint32_t warps = (left + 31u) >> 5;
+                if ((threadIdx.x >> 5) >= warps) break; /* whole warps without a signature leave */
+                sync_n = (int)(warps * 32u);
+                gi = base + threadIdx.x;
+                i = threadIdx.x < left ? gi : n - 1u; /* lanes past the end shadow the last signature (they must reach the barriers) */
+            }
+        }
+        bool v = ecdsa_point_phase(rec + (size_t)i * BCP_REC_WORDS, pub65 + (size_t)65 * i, sig64 + (size_t)64 * i, tab, gcomb, sync_n);
+        {
+            const uint32_t stride = gridDim.x * blockDim.x;
+            bool live = true;
+            if (r < n / stride) {
+                gi = r * stride + blockIdx.x * blockDim.x + threadIdx.x;
+            } else {
+                const uint32_t base = r * stride + blockIdx.x * per_last;
+                const uint32_t left = n - base < per_last ? n - base : per_last;
+                gi = base + threadIdx.x;
+                live = threadIdx.x < left;
+            }
+            if (live) ok[gi] = v ? 1 : 0;
+        }
+    }
 }
 
 // secp256k1_ec_pubkey_parse for a batch: affine x || y (big-endian) per key, ok byte per key
@@ -202,12 +258,28 @@ int bcp_ecdsa_build_tables(bcp_ctx *c) {
     return BCP_OK;
 }
 
-// d_scratch: bcp_gpu_ecdsa_scratch_bytes(n) bytes = [records of one slice][tables of one slice]
+// 1 (default): batches of more than a wave go through the persistent rounds kernel; 2: every batch; 0: never (A/B switch)
+static int point_rounds_mode() {
+    static const int mode = getenv("BCP_POINT_ROUNDS") ? atoi(getenv("BCP_POINT_ROUNDS")) : 1;
+    return mode;
+}
+#define BCP_MAX_RESIDENT_BLOCKS (160 * BCP_POINT_BLOCKS_PER_SM) /* upper bound of the persistent grid on any sm_100 part */
+// slabs a launch over `cap` signatures (one slice at most, whole blocks) can touch
+static size_t point_slabs(size_t cap) {
+    const int mode = point_rounds_mode();
+    const size_t resident = (size_t)BCP_MAX_RESIDENT_BLOCKS * BCP_POINT_THREADS;
+    if (mode == 0) return cap;
+    if (cap > BCP_WAVE) return resident;                        /* rounds kernel with at least one full round */
+    return cap + (mode == 2 ? (size_t)BCP_MAX_RESIDENT_BLOCKS * 32 : 0); /* sub-wave: per-signature, plus the warp rounding of the even split */
+}
+// d_scratch: bcp_gpu_ecdsa_scratch_bytes(n) bytes = [records of one slice][tables: one slab per resident thread, or per
+// signature of a sub-wave batch]
 int bcp_ecdsa_launch(bcp_ctx *c, const uint8_t *d_msg, const uint8_t *d_pub, const uint8_t *d_sig, size_t n,
                          uint32_t flags, uint8_t *d_ok, uint32_t *d_scratch, cudaStream_t st) {
     size_t cap = n < BCP_SLICE ? n : BCP_SLICE;
     cap = (cap + BCP_POINT_THREADS - 1) / BCP_POINT_THREADS * BCP_POINT_THREADS;
     uint32_t *d_rec = d_scratch, *d_tab = d_scratch + cap * BCP_REC_WORDS;
+    const int rounds_mode = point_rounds_mode();
     for (size_t off = 0; off < n; off += BCP_SLICE) {
         const size_t m = n - off < BCP_SLICE ? n - off : BCP_SLICE;
         // signatures per prep thread: one 334-multiplication inversion is shared by K signatures, but a thread's work is
@@ -224,6 +296,15 @@ int bcp_ecdsa_launch(bcp_ctx *c, const uint8_t *d_msg, const uint8_t *d_pub, con
         // Less than about one wave: smaller thread blocks spread the signatures evenly over the SMs (the kernel ends when
         // the fullest SM does); from a wave up, 256-thread blocks keep the warps of an SM in the same code region.
         static const int forced_tpb = getenv("BCP_POINT_TPB") ? atoi(getenv("BCP_POINT_TPB")) : 0;
+        if (rounds_mode == 2 || (rounds_mode == 1 && m > BCP_WAVE)) {
+            const unsigned grid = (unsigned)c->sm_count * BCP_POINT_BLOCKS_PER_SM;
+            const size_t stride = (size_t)grid * BCP_POINT_THREADS, rem = m % stride;
+            uint32_t per_last = (uint32_t)((rem + grid - 1) / grid);
+            per_last = (per_last + 31u) & ~31u; /* whole warps; at most BCP_POINT_THREADS because rem < stride */
+            k_ecdsa_point_rounds<<<grid, BCP_POINT_THREADS, 0, st>>>(d_pub + 65 * off, d_sig + 64 * off, (uint32_t)m, d_rec, d_tab,
+                                                                     c->gcomb, d_ok + off, per_last);
+            continue;
+        }
         const unsigned tpb = forced_tpb ? (unsigned)forced_tpb : (m <= BCP_WAVE ? BCP_POINT_SMALL_TPB : BCP_POINT_THREADS);
         unsigned blocks = (unsigned)((m + tpb - 1) / tpb);
         k_ecdsa_point<<<blocks, tpb, 0, st>>>(d_pub + 65 * off, d_sig + 64 * off, m, d_rec, d_tab, c->gcomb,
@@ -238,7 +319,7 @@ extern "C" {
 size_t bcp_gpu_ecdsa_scratch_bytes(size_t n) {
     size_t cap = n < BCP_SLICE ? n : BCP_SLICE;
     cap = (cap + BCP_POINT_THREADS - 1) / BCP_POINT_THREADS * BCP_POINT_THREADS; /* whole blocks */
-    return cap * BCP_SIG_SCRATCH_WORDS * 4 + 256;
+    return (cap * BCP_REC_WORDS + point_slabs(cap) * BCP_QTAB_WORDS) * 4 + 256;
 }
 
 int bcp_gpu_ecdsa_reserve(int device, size_t n) {

@@ -183,9 +183,11 @@ struct qtable_packed {
 //   t in [7, 7 + 34*6)     window w = 33..0: four doublings, add digit(k1,w)*Q, add digit(k2,w)*lambda*Q
 //   next step              leave the isomorphic curve: Z *= Z_8
 //   last 16 steps          u1*G: one comb lookup + mixed addition per 16-bit window, no doublings
+// sync_n = how many threads of the block walk the steps together (what BCP_STEP_SYNC waits for); unused on the host build.
 template <class Table>
 BCP_DEV bool ecdsa_point_phase(const uint32_t *rec, const uint8_t *pub65, const uint8_t *sig64, Table tab,
-                               const uint32_t *gcomb) {
+                               const uint32_t *gcomb, const int sync_n = 0) {
+    (void)sync_n;
     const uint32_t fl = rec[18];
     gej acc;
     // A signature that is already known to be invalid keeps walking (on the generator instead of its own
