@@ -35,6 +35,8 @@ SIGNATURES = {
     "bcp_gpu_ecdsa_scratch_bytes": (sz, [sz]),
     "bcp_gpu_ecdsa_reserve": (C.c_int, [C.c_int, sz]),
     "bcp_gpu_pubkey_parse_batch": (C.c_int, [C.c_int, vp, sz, vp, vp]),
+    "bcp_gpu_ecdsa_recover_batch": (C.c_int, [C.c_int, vp, vp, vp, sz, vp, vp]),
+    "bcp_gpu_pubkey_tweak_add_batch": (C.c_int, [C.c_int, vp, vp, sz, vp, vp]),
     "bcp_der_lax_parse": (C.c_int, [vp, sz, vp]),
     "bcp_block_index": (C.c_long, [vp, sz, C.c_int, vp, sz]),
     "bcp_gpu_sha256d_txids_merkle": (C.c_int, [C.c_int, vp, sz, vp, sz, vp, vp, C.POINTER(C.c_int)]),

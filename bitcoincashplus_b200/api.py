@@ -77,6 +77,25 @@ class Engine:
               "bcp_gpu_pubkey_parse_batch")
         return xy, ok
 
+    def ecdsa_recover_batch(self, msg32, sig64, recid):
+        """secp256k1_ecdsa_recover per item -> (xy64 (n,64), ok (n,))."""
+        msg32, sig64 = _np(msg32, 32), _np(sig64, 64)
+        rid = np.ascontiguousarray(recid, dtype=np.uint8)
+        n = len(rid)
+        xy, ok = np.zeros((n, 64), dtype=np.uint8), np.zeros(n, dtype=np.uint8)
+        check(lib().bcp_gpu_ecdsa_recover_batch(self.device, msg32.ctypes.data, sig64.ctypes.data, rid.ctypes.data, n,
+                                                xy.ctypes.data, ok.ctypes.data), "bcp_gpu_ecdsa_recover_batch")
+        return xy, ok
+
+    def pubkey_tweak_add_batch(self, pub65, tweak32):
+        """secp256k1_ec_pubkey_tweak_add per item -> (xy64 (n,64), ok (n,))."""
+        pub65, tweak32 = _np(pub65, 65), _np(tweak32, 32)
+        n = len(pub65)
+        xy, ok = np.zeros((n, 64), dtype=np.uint8), np.zeros(n, dtype=np.uint8)
+        check(lib().bcp_gpu_pubkey_tweak_add_batch(self.device, pub65.ctypes.data, tweak32.ctypes.data, n, xy.ctypes.data,
+                                                   ok.ctypes.data), "bcp_gpu_pubkey_tweak_add_batch")
+        return xy, ok
+
     def ecdsa_reserve(self, n):
         check(lib().bcp_gpu_ecdsa_reserve(self.device, n), "bcp_gpu_ecdsa_reserve")
 

@@ -26,6 +26,8 @@
 #endif
 #include "ecdsa.cuh"
 #include <cstdlib>
+#include <cstring>
+#include <vector>
 
 #if BCP_POINT_VARIANT == 1
 #ifndef BCP_POINT_THREADS
@@ -115,58 +117,53 @@ __global__ void __launch_bounds__(BCP_POINT_THREADS, BCP_POINT_BLOCKS_PER_SM)
     if (gi < n) ok[gi] = v ? 1 : 0;
 }
 
-// Persistent form: the grid is exactly the resident set (BCP_POINT_BLOCKS_PER_SM blocks on every SM) and each block walks
-// over the batch in rounds, so that
+// Persistent form: the grid is exactly the resident set (BCP_POINT_BLOCKS_PER_SM blocks on every SM); a block CLAIMS
+// whole chunks of blockDim.x signatures from a counter until none is left, then takes its share of the remainder, so that
 //   * a thread's {1..8}Q slab belongs to the RESIDENT SLOT (block, thread), not to the signature: the slabs of a whole
-//     launch are 148 x 512 x 768 B = 58 MB, written and re-read round after round inside the 126 MB L2, instead of 768 B
-//     of scratch per signature streaming through it (848 MB per million signatures, DRAM traffic 24x the algorithmic bytes);
-//   * the last, partly filled round is dealt out EVENLY: every block takes per_last signatures (a multiple of 32) and
-//     only the warps that hold some walk the steps, so what is left over runs on every SM at a few warps each (and
-//     correspondingly faster) instead of as whole 256-thread blocks on a fifth of the chip.
+//     launch are 148 x 512 x 768 B = 58 MB instead of 768 B of scratch per signature;
+//   * claiming (not a fixed stride) keeps every SM at two blocks to the end: the two blocks of an SM do not run at the same
+//     speed (with a fixed assignment the faster one ran out of rounds early and left the SM half empty for the rest of the
+//     launch: ncu showed 13.8 instead of 15.7 active warps per SM and the launch was 6 % slower);
+//   * the remainder (less than one chunk per block) is dealt out EVENLY: every block takes per_last signatures (a multiple
+//     of 32) and only the warps that hold some walk the steps, so what is left over runs on every SM at a few warps each
+//     (and correspondingly faster) instead of as whole 256-thread blocks on a fifth of the chip.
+// `counter` must be zero at launch.
 __global__ void __launch_bounds__(BCP_POINT_THREADS, BCP_POINT_BLOCKS_PER_SM)
     k_ecdsa_point_rounds(const uint8_t *__restrict__ pub65, const uint8_t *__restrict__ sig64, uint32_t n,
                          const uint32_t *__restrict__ rec, uint32_t *__restrict__ qtabs, const uint32_t *__restrict__ gcomb,
-                         uint8_t *__restrict__ ok, uint32_t per_last) {
-    // Everything a round needs is recomputed from the kernel parameters (constant bank) and the round number, so that the
-    // only values this outer loop keeps alive across the point phase are `r` and the barrier width — the phase itself uses
-    // all 128 registers.
-    const uint32_t full = n / (gridDim.x * blockDim.x);
-    qtable_packed tab; /* slabs are packed per block: blockDim.x per block once there is a full round, else per_last */
+                         uint8_t *__restrict__ ok, uint32_t per_last, uint32_t *__restrict__ counter) {
+    // Everything a chunk needs is recomputed from the kernel parameters (constant bank) and the chunk number, which lives
+    // in shared memory: the point phase itself uses all 128 registers.
+    __shared__ uint32_t s_chunk;
+    const uint32_t full = (n / (gridDim.x * blockDim.x)) * gridDim.x; /* whole chunks handed out by the counter */
+    qtable_packed tab; /* slabs are packed per block: blockDim.x per block once there is a full chunk, else per_last */
     tab.base = qtabs + ((size_t)blockIdx.x * (full ? blockDim.x : per_last) + threadIdx.x) * BCP_QTAB_WORDS;
 #pragma unroll 1
-    for (uint32_t r = 0; r <= n / (gridDim.x * blockDim.x); r++) {
-        uint32_t gi, i;
-        int sync_n = (int)blockDim.x;
+    for (;;) {
+        if (threadIdx.x == 0) s_chunk = atomicAdd(counter, 1u);
+        __syncthreads(); /* every thread of the block is still here: threads only leave in the last pass */
+        uint32_t i, width;
         {
-            const uint32_t stride = gridDim.x * blockDim.x;
-            if (r < n / stride) {
-                gi = r * stride + blockIdx.x * blockDim.x + threadIdx.x;
-                i = gi;
-            } else {
-                const uint32_t base = r * stride + blockIdx.x * per_last;
-                if (base >= n) break; /* uniform for the block */
-                const uint32_t left = n - base < per_last ? n - base : per_last;
-                const uint32_t warps = (left + 31u) >> 5;
-                if ((threadIdx.x >> 5) >= warps) break; /* whole warps without a signature leave */
-                sync_n = (int)(warps * 32u);
-                gi = base + threadIdx.x;
-                i = threadIdx.x < left ? gi : n - 1u; /* lanes past the end shadow the last signature (they must reach the barriers) */
-            }
+            const uint32_t chunks = (n / (gridDim.x * blockDim.x)) * gridDim.x;
+            const bool last = s_chunk >= chunks; /* no whole chunk left: this block's share of the remainder, then out */
+            const uint32_t base = last ? chunks * blockDim.x + blockIdx.x * per_last : s_chunk * blockDim.x;
+            if (base >= n) return; /* uniform for the block */
+            const uint32_t left = last ? (n - base < per_last ? n - base : per_last) : blockDim.x;
+            width = ((left + 31u) >> 5) * 32u;
+            if (threadIdx.x >= width) return; /* whole warps without a signature leave (last pass only) */
+            i = threadIdx.x < left ? base + threadIdx.x : n - 1u; /* lanes past the end shadow the last signature (barriers) */
         }
-        bool v = ecdsa_point_phase(rec + (size_t)i * BCP_REC_WORDS, pub65 + (size_t)65 * i, sig64 + (size_t)64 * i, tab, gcomb, sync_n);
+        const bool v = ecdsa_point_phase(rec + (size_t)i * BCP_REC_WORDS, pub65 + (size_t)65 * i, sig64 + (size_t)64 * i, tab,
+                                         gcomb, (int)width);
         {
-            const uint32_t stride = gridDim.x * blockDim.x;
-            bool live = true;
-            if (r < n / stride) {
-                gi = r * stride + blockIdx.x * blockDim.x + threadIdx.x;
-            } else {
-                const uint32_t base = r * stride + blockIdx.x * per_last;
-                const uint32_t left = n - base < per_last ? n - base : per_last;
-                gi = base + threadIdx.x;
-                live = threadIdx.x < left;
-            }
-            if (live) ok[gi] = v ? 1 : 0;
+            const uint32_t chunks = (n / (gridDim.x * blockDim.x)) * gridDim.x;
+            const bool last = s_chunk >= chunks;
+            const uint32_t base = last ? chunks * blockDim.x + blockIdx.x * per_last : s_chunk * blockDim.x;
+            const uint32_t left = last ? (n - base < per_last ? n - base : per_last) : blockDim.x;
+            if (threadIdx.x < left) ok[base + threadIdx.x] = v ? 1 : 0;
+            if (last) return;
         }
+        __syncthreads(); /* s_chunk is read above until the very end of the chunk: thread 0 may only replace it now */
     }
 }
 
@@ -187,6 +184,59 @@ __global__ void __launch_bounds__(128) k_pubkey_parse(const uint8_t *__restrict_
         o[32 + 4 * k] = b >> 24; o[32 + 4 * k + 1] = b >> 16; o[32 + 4 * k + 2] = b >> 8; o[32 + 4 * k + 3] = b;
     }
     ok[i] = v ? 1 : 0;
+}
+
+// R = u2*P + u1*G as an affine point, for the two verify-side libsecp256k1 calls that are not a verification:
+//   mode 1  secp256k1_ecdsa_recover (src/secp256k1/src/modules/recovery/main_impl.h:87-121, 170-190): P = the point with
+//           x = r (+ n) and the parity of the recovery id (built by the host as a compressed key), u2 = s/r, u1 = -m/r
+//   mode 0  secp256k1_ec_pubkey_tweak_add (src/secp256k1/src/secp256k1.c:477-499, eckey_impl.h:63-75): u2 = 1, u1 = tweak
+// One thread per item; the walk is the verification's (ecdsa_point_phase), so the GLV split, the {1..8}P table and the
+// comb for G are shared code.  Not a hot path in the node (message signatures, BIP32 public derivation): batches of one
+// through the compat API, but the kernel takes any n.
+__global__ void __launch_bounds__(128) k_ec_lincomb(const uint8_t *__restrict__ pub65, const uint8_t *__restrict__ in_a,
+                                                    const uint8_t *__restrict__ msg32, int mode, size_t n,
+                                                    uint32_t *__restrict__ qtabs, const uint32_t *__restrict__ gcomb,
+                                                    uint8_t *__restrict__ xy64, uint8_t *__restrict__ ok) {
+    const size_t gi = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    const size_t i = gi < n ? gi : n - 1; /* tail threads shadow the last item (they must reach the barriers) */
+    sig_scalars g;
+    scalar sinv;
+    BCP_UNROLL
+    for (int k = 0; k < 8; k++) { sinv.v[k] = (k == 0); g.r.v[k] = (k == 0); g.s.v[k] = (k == 0); }
+    bool valid;
+    if (mode == 1) {
+        scalar r, s, m;
+        const bool ov_r = sc_set_b32(r, in_a + 64 * i), ov_s = sc_set_b32(s, in_a + 64 * i + 32);
+        sc_set_b32(m, msg32 + 32 * i); /* reduced mod n silently (main_impl.h:184) */
+        valid = !(ov_r || ov_s) && !sc_is_zero(r) && !sc_is_zero(s); /* parse_compact overflow; :97-99 */
+        if (!valid) {
+            BCP_UNROLL
+            for (int k = 0; k < 8; k++) r.v[k] = (k == 0);
+        }
+        sc_inverse(sinv, r);
+        g.r = s;            /* u2 = s / r  */
+        sc_negate(g.m, m);  /* u1 = -m / r */
+    } else {
+        valid = !sc_set_b32(g.m, in_a + 32 * i); /* tweak >= n fails (secp256k1.c:487-488) */
+    }
+    g.valid = valid;
+    uint32_t rec[BCP_REC_WORDS];
+    sig_finish(rec, g, sinv);
+    qtable_packed tab;
+    tab.base = qtabs + gi * BCP_QTAB_WORDS;
+    gej R;
+    const bool fin = ecdsa_point_phase<qtable_packed, true>(rec, pub65 + 65 * i, nullptr, tab, gcomb, (int)blockDim.x, &R);
+    if (gi >= n) return;
+    fe ax, ay;
+    if (fin) gej_to_affine(ax, ay, R);
+    uint8_t *o = xy64 + 64 * gi;
+#pragma unroll
+    for (int k = 0; k < 8; k++) {
+        const uint32_t a = fin ? ax.v[7 - k] : 0u, b = fin ? ay.v[7 - k] : 0u;
+        o[4 * k] = a >> 24; o[4 * k + 1] = a >> 16; o[4 * k + 2] = a >> 8; o[4 * k + 3] = a;
+        o[32 + 4 * k] = b >> 24; o[32 + 4 * k + 1] = b >> 16; o[32 + 4 * k + 2] = b >> 8; o[32 + 4 * k + 3] = b;
+    }
+    ok[gi] = fin ? 1 : 0;
 }
 
 // Device self-test of the field arithmetic's rarely taken paths.  fe_add / fe_sub / fe_reduce_wide finish the folds
@@ -301,8 +351,10 @@ int bcp_ecdsa_launch(bcp_ctx *c, const uint8_t *d_msg, const uint8_t *d_pub, con
             const size_t stride = (size_t)grid * BCP_POINT_THREADS, rem = m % stride;
             uint32_t per_last = (uint32_t)((rem + grid - 1) / grid);
             per_last = (per_last + 31u) & ~31u; /* whole warps; at most BCP_POINT_THREADS because rem < stride */
+            uint32_t *d_counter = d_tab + point_slabs(cap) * BCP_QTAB_WORDS; /* in the 256 spare bytes behind the slabs */
+            BCP_CUDA(cudaMemsetAsync(d_counter, 0, sizeof(uint32_t), st));
             k_ecdsa_point_rounds<<<grid, BCP_POINT_THREADS, 0, st>>>(d_pub + 65 * off, d_sig + 64 * off, (uint32_t)m, d_rec, d_tab,
-                                                                     c->gcomb, d_ok + off, per_last);
+                                                                     c->gcomb, d_ok + off, per_last, d_counter);
             continue;
         }
         const unsigned tpb = forced_tpb ? (unsigned)forced_tpb : (m <= BCP_WAVE ? BCP_POINT_SMALL_TPB : BCP_POINT_THREADS);
@@ -367,6 +419,83 @@ int bcp_gpu_pubkey_parse_batch(int device, const uint8_t *pub65, size_t n, uint8
     BCP_CUDA(cudaMemcpyAsync(ok, d_ok, n, cudaMemcpyDeviceToHost, c->stream));
     BCP_CUDA(cudaStreamSynchronize(c->stream));
     return BCP_OK;
+}
+
+static int lincomb_host(bcp_ctx *c, int mode, const uint8_t *pub65, const uint8_t *in_a, size_t a_bytes, const uint8_t *msg32,
+                        size_t n, uint8_t *xy64, uint8_t *ok) {
+    auto up = [](size_t x) { return (x + 255) / 256 * 256; };
+    const size_t o_pub = 0, o_a = up(n * 65), o_msg = o_a + up(n * a_bytes), o_xy = o_msg + up(n * 32), o_ok = o_xy + up(n * 64);
+    int rc = bcp_ctx_reserve_stage(c, o_ok + up(n));
+    if (rc != BCP_OK) return rc;
+    const size_t blocks = (n + 127) / 128;
+    rc = bcp_ctx_reserve_scratch(c, blocks * 128 * BCP_QTAB_WORDS * 4);
+    if (rc != BCP_OK) return rc;
+    uint8_t *d = c->stage;
+    cudaStream_t st = c->stream;
+    BCP_CUDA(cudaMemcpyAsync(d + o_pub, pub65, n * 65, cudaMemcpyHostToDevice, st));
+    BCP_CUDA(cudaMemcpyAsync(d + o_a, in_a, n * a_bytes, cudaMemcpyHostToDevice, st));
+    if (msg32) BCP_CUDA(cudaMemcpyAsync(d + o_msg, msg32, n * 32, cudaMemcpyHostToDevice, st));
+    k_ec_lincomb<<<(unsigned)blocks, 128, 0, st>>>(d + o_pub, d + o_a, d + o_msg, mode, n, reinterpret_cast<uint32_t *>(c->scratch),
+                                                   c->gcomb, d + o_xy, d + o_ok);
+    BCP_CUDA(cudaGetLastError());
+    BCP_CUDA(cudaMemcpyAsync(xy64, d + o_xy, n * 64, cudaMemcpyDeviceToHost, st));
+    BCP_CUDA(cudaMemcpyAsync(ok, d + o_ok, n, cudaMemcpyDeviceToHost, st));
+    BCP_CUDA(cudaStreamSynchronize(st));
+    return BCP_OK;
+}
+
+// secp256k1_ecdsa_recoverable_signature_parse_compact + secp256k1_ecdsa_recover for n items
+// (src/secp256k1/src/modules/recovery/main_impl.h:38-58, 87-121, 170-190).
+int bcp_gpu_ecdsa_recover_batch(int device, const uint8_t *msg32, const uint8_t *sig64, const uint8_t *recid, size_t n,
+                                uint8_t *xy64, uint8_t *ok) {
+    bcp_ctx *c = bcp_get_ctx(device);
+    if (!c) return BCP_ERR_NOT_INIT;
+    if (n == 0) return BCP_OK;
+    if (!msg32 || !sig64 || !recid || !xy64 || !ok) {
+        bcp_set_error("bcp_gpu_ecdsa_recover_batch: NULL buffer");
+        return BCP_ERR_INVALID;
+    }
+    // byte-level part on the host: the x coordinate the key is lifted from is r, or r + n when bit 1 of the recovery id is
+    // set and r < p - n (:104-110); bit 0 is the parity of y.  A slot whose first byte is 0 never parses: that item fails.
+    static const uint8_t N_BE[32] = {0xFF, 0xFF, 0xFF, 0xFF, 0xFF, 0xFF, 0xFF, 0xFF, 0xFF, 0xFF, 0xFF, 0xFF, 0xFF, 0xFF, 0xFF, 0xFE,
+                                     0xBA, 0xAE, 0xDC, 0xE6, 0xAF, 0x48, 0xA0, 0x3B, 0xBF, 0xD2, 0x5E, 0x8C, 0xD0, 0x36, 0x41, 0x41};
+    static const uint8_t PMN_BE[32] = {0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0x01, 0x45, 0x51, 0x23, 0x19, 0x50, 0xB7, 0x5F, 0xC4,
+                                       0x40, 0x2D, 0xA1, 0x72, 0x2F, 0xC9, 0xBA, 0xEE}; /* p - n (ecdsa_impl.h:45-47) */
+    std::vector<uint8_t> pub(n * 65, 0);
+    for (size_t i = 0; i < n; i++) {
+        const uint8_t *r = sig64 + 64 * i;
+        uint8_t *slot = &pub[65 * i];
+        if (recid[i] > 3) continue;
+        memcpy(slot + 1, r, 32);
+        if (recid[i] & 2) {
+            if (memcmp(r, PMN_BE, 32) >= 0) continue;
+            int carry = 0;
+            for (int k = 31; k >= 0; k--) {
+                const int v = (int)r[k] + (int)N_BE[k] + carry;
+                slot[1 + k] = (uint8_t)v;
+                carry = v >> 8;
+            }
+        }
+        slot[0] = (recid[i] & 1) ? 0x03 : 0x02;
+    }
+    std::lock_guard<std::mutex> lk(c->mu);
+    BCP_CUDA(cudaSetDevice(c->device));
+    return lincomb_host(c, 1, pub.data(), sig64, 64, msg32, n, xy64, ok);
+}
+
+// secp256k1_ec_pubkey_tweak_add for n keys in the 65-byte-slot layout (src/secp256k1/src/secp256k1.c:477-499).
+int bcp_gpu_pubkey_tweak_add_batch(int device, const uint8_t *pub65, const uint8_t *tweak32, size_t n, uint8_t *xy64,
+                                   uint8_t *ok) {
+    bcp_ctx *c = bcp_get_ctx(device);
+    if (!c) return BCP_ERR_NOT_INIT;
+    if (n == 0) return BCP_OK;
+    if (!pub65 || !tweak32 || !xy64 || !ok) {
+        bcp_set_error("bcp_gpu_pubkey_tweak_add_batch: NULL buffer");
+        return BCP_ERR_INVALID;
+    }
+    std::lock_guard<std::mutex> lk(c->mu);
+    BCP_CUDA(cudaSetDevice(c->device));
+    return lincomb_host(c, 0, pub65, tweak32, 32, nullptr, n, xy64, ok);
 }
 
 // Host-pointer form: the batch is cut into chunks; chunk k+1's host->device copy overlaps chunk k's

@@ -184,9 +184,11 @@ struct qtable_packed {
 //   next step              leave the isomorphic curve: Z *= Z_8
 //   last 16 steps          u1*G: one comb lookup + mixed addition per 16-bit window, no doublings
 // sync_n = how many threads of the block walk the steps together (what BCP_STEP_SYNC waits for); unused on the host build.
-template <class Table>
+// WANT_POINT: hand back R = u1*G + u2*Q itself (Jacobian) instead of comparing its x with r — the recovery and
+// tweak-add entry points are the same walk with other scalars; returns whether R is a finite point of a valid input.
+template <class Table, bool WANT_POINT = false>
 BCP_DEV bool ecdsa_point_phase(const uint32_t *rec, const uint8_t *pub65, const uint8_t *sig64, Table tab,
-                               const uint32_t *gcomb, const int sync_n = 0) {
+                               const uint32_t *gcomb, const int sync_n = 0, gej *out = nullptr) {
     (void)sync_n;
     const uint32_t fl = rec[18];
     gej acc;
@@ -319,6 +321,10 @@ BCP_DEV bool ecdsa_point_phase(const uint32_t *rec, const uint8_t *pub65, const 
             tab.store(t + 1, acc.x, acc.y);
             zr[t + 1] = (t == 0) ? acc.z : h;
         }
+    }
+    if (WANT_POINT) {
+        *out = acc;
+        return valid && !acc.inf;
     }
     if (acc.inf || !valid) return false; /* ecdsa_impl.h:220 */
 

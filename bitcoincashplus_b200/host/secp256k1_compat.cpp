@@ -14,6 +14,7 @@
 
 #include "../../include/bcp_gpu.h"
 #include "../../include/compat/secp256k1.h"
+#include "../../include/compat/secp256k1_recovery.h"
 
 struct secp256k1_context_struct {
     int device;
@@ -161,6 +162,71 @@ int secp256k1_ecdsa_verify_batch(const secp256k1_context *ctx, const secp256k1_e
     static_assert(sizeof(secp256k1_ecdsa_signature) == 64, "signature blob is r||s");
     if (bcp_gpu_ecdsa_verify_batch(ctx->device, msgs32, pub.data(), sigs[0].data, n, 0, ok.data()) != BCP_OK) return 0;
     memcpy(results, ok.data(), n);
+    return 1;
+}
+
+int secp256k1_ec_pubkey_tweak_add(const secp256k1_context *ctx, secp256k1_pubkey *pubkey, const unsigned char *tweak) {
+    ARG_CHECK(ctx != nullptr);
+    ARG_CHECK(pubkey != nullptr);
+    ARG_CHECK(tweak != nullptr);
+    bool zero = true;
+    for (int i = 0; i < 32; i++) zero = zero && pubkey->data[i] == 0;
+    unsigned char slot[65], xy[64], ok = 0;
+    slot[0] = 0x04;
+    memcpy(slot + 1, pubkey->data, 64);
+    memset(pubkey, 0, sizeof(*pubkey)); /* secp256k1.c:489: cleared before the outcome is known */
+    ARG_CHECK(!zero);                   /* secp256k1_pubkey_load (secp256k1.c:132) */
+    if (bcp_gpu_pubkey_tweak_add_batch(ctx->device, slot, tweak, 1, xy, &ok) != BCP_OK || !ok) return 0;
+    memcpy(pubkey->data, xy, 64);
+    return 1;
+}
+
+int secp256k1_ecdsa_recoverable_signature_parse_compact(const secp256k1_context *ctx, secp256k1_ecdsa_recoverable_signature *sig,
+                                                        const unsigned char *input64, int recid) {
+    ARG_CHECK(sig != nullptr);
+    ARG_CHECK(input64 != nullptr);
+    ARG_CHECK(recid >= 0 && recid <= 3);
+    const bool overflow = memcmp(input64, N_BE, 32) >= 0 || memcmp(input64 + 32, N_BE, 32) >= 0;
+    if (overflow) {
+        memset(sig, 0, sizeof(*sig));
+        return 0;
+    }
+    memcpy(sig->data, input64, 64);
+    sig->data[64] = (unsigned char)recid;
+    return 1;
+}
+
+int secp256k1_ecdsa_recoverable_signature_convert(const secp256k1_context *ctx, secp256k1_ecdsa_signature *sig,
+                                                  const secp256k1_ecdsa_recoverable_signature *sigin) {
+    ARG_CHECK(sig != nullptr);
+    ARG_CHECK(sigin != nullptr);
+    memcpy(sig->data, sigin->data, 64);
+    return 1;
+}
+
+int secp256k1_ecdsa_recoverable_signature_serialize_compact(const secp256k1_context *ctx, unsigned char *output64, int *recid,
+                                                            const secp256k1_ecdsa_recoverable_signature *sig) {
+    ARG_CHECK(output64 != nullptr);
+    ARG_CHECK(sig != nullptr);
+    ARG_CHECK(recid != nullptr);
+    memcpy(output64, sig->data, 64);
+    *recid = sig->data[64];
+    return 1;
+}
+
+int secp256k1_ecdsa_recover(const secp256k1_context *ctx, secp256k1_pubkey *pubkey, const secp256k1_ecdsa_recoverable_signature *sig,
+                            const unsigned char *msg32) {
+    ARG_CHECK(ctx != nullptr);
+    ARG_CHECK(msg32 != nullptr);
+    ARG_CHECK(sig != nullptr);
+    ARG_CHECK(pubkey != nullptr);
+    unsigned char xy[64], ok = 0;
+    const unsigned char rid = sig->data[64];
+    if (bcp_gpu_ecdsa_recover_batch(ctx->device, msg32, sig->data, &rid, 1, xy, &ok) != BCP_OK || !ok) {
+        memset(pubkey, 0, sizeof(*pubkey));
+        return 0;
+    }
+    memcpy(pubkey->data, xy, 64);
     return 1;
 }
 

@@ -92,6 +92,19 @@ BCP_API int bcp_gpu_ecdsa_reserve(int device, size_t n);
  * same 65-byte-slot layout: xy64[i] = affine x || y big-endian (zeros when invalid), ok[i] = 1/0. */
 BCP_API int bcp_gpu_pubkey_parse_batch(int device, const uint8_t *pub65, size_t n, uint8_t *xy64, uint8_t *ok);
 
+/* secp256k1_ecdsa_recoverable_signature_parse_compact + secp256k1_ecdsa_recover
+ * (src/secp256k1/include/secp256k1_recovery.h:36,99; src/secp256k1/src/modules/recovery/main_impl.h:38-58, 87-121,
+ * 170-190) for n items — what CPubKey::RecoverCompact (src/pubkey.cpp:195-218) calls: sig64[i] = r || s big-endian,
+ * recid[i] in 0..3, msg32[i] = the signed hash.  xy64[i] = affine x || y of the recovered key (zeros on failure),
+ * ok[i] = 1/0 (r or s out of range or zero, recid > 3, no point with that x, result at infinity => 0). */
+BCP_API int bcp_gpu_ecdsa_recover_batch(int device, const uint8_t *msg32, const uint8_t *sig64, const uint8_t *recid, size_t n,
+                                        uint8_t *xy64, uint8_t *ok);
+/* secp256k1_ec_pubkey_tweak_add (src/secp256k1/include/secp256k1.h:544, src/secp256k1/src/secp256k1.c:477-499) for n
+ * keys in the 65-byte-slot layout — what CPubKey::Derive (src/pubkey.cpp:240-264) calls: xy64[i] = pub[i] + tweak32[i]*G,
+ * ok[i] = 0 when the key does not parse, the tweak is >= n or the sum is the point at infinity. */
+BCP_API int bcp_gpu_pubkey_tweak_add_batch(int device, const uint8_t *pub65, const uint8_t *tweak32, size_t n, uint8_t *xy64,
+                                           uint8_t *ok);
+
 /* Host-side byte parsing that stays on the CPU by design (branchy, a few dozen bytes):
  * ecdsa_signature_parse_der_lax (src/pubkey.cpp:26-168).  Returns 1 and writes r||s (zeros when a
  * component overflows, which later verifies as invalid), or 0 on a structural failure. */

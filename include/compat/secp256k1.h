@@ -2,7 +2,12 @@
  * libsecp256k1 C API that the node's src/pubkey.cpp uses, with the reference's exact names, argument
  * meaning and return conventions (src/secp256k1/include/secp256k1.h:46-70, 176-610), implemented on top of
  * libbcp_b200.so (bitcoincashplus_b200/host/secp256k1_compat.cpp).  Put this directory in front of
- * src/secp256k1/include on the include path and src/pubkey.cpp compiles unchanged.
+ * src/secp256k1/include on the include path and src/pubkey.cpp compiles unchanged and links against
+ * libbcp_secp256k1_compat.so alone (tests/test_compat_cpp.py builds exactly that: the reference's pubkey.cpp over these
+ * headers, CPubKey::Verify / RecoverCompact / Derive / Decompress / CheckLowS running on the GPU).  Everything
+ * pubkey.cpp calls is here and in secp256k1_recovery.h next to this file.  The signing side (src/key.cpp:
+ * secp256k1_ecdsa_sign, ec_pubkey_create, privkey tweaks) is NOT: a wallet keeps the stock library for that, built
+ * with a symbol prefix or as a separate shared object, since both define the names below.
  *
  * All curve arithmetic runs on the GPU; there is no CPU fallback.  A single secp256k1_ecdsa_verify is a
  * batch of one (correct, but latency-bound): block validation should go through
@@ -67,6 +72,10 @@ SECP256K1_API int secp256k1_ecdsa_signature_normalize(const secp256k1_context *c
 /* secp256k1.c:293-308 */
 SECP256K1_API int secp256k1_ecdsa_verify(const secp256k1_context *ctx, const secp256k1_ecdsa_signature *sig,
                                          const unsigned char *msg32, const secp256k1_pubkey *pubkey);
+
+/* secp256k1.c:477-499 (declared src/secp256k1/include/secp256k1.h:544): pubkey := pubkey + tweak*G.  Returns 0 (and
+ * zeroes the key) when the tweak is >= n or the result is the point at infinity. */
+SECP256K1_API int secp256k1_ec_pubkey_tweak_add(const secp256k1_context *ctx, secp256k1_pubkey *pubkey, const unsigned char *tweak);
 
 /* Extension (no reference counterpart): n independent secp256k1_ecdsa_verify calls in one launch.
  * results[i] receives 1/0.  Returns 1 on success, 0 if the device call failed (then results are untouched). */

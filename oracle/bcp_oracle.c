@@ -935,6 +935,58 @@ int orc_ecdsa_verify(const uint8_t msg32[32], const uint8_t *pub, size_t publen,
     u256_from_be(&r, sig); u256_from_be(&s, sig + 32);
     return ecdsa_verify_core(&r, &s, msg32, &q);
 }
+/* secp256k1_ecdsa_recoverable_signature_parse_compact + secp256k1_ecdsa_recover
+ * (src/secp256k1/src/modules/recovery/main_impl.h:38-58, 170-190) with secp256k1_ecdsa_sig_recover (:87-121):
+ * x = r (+ n when recid & 2, only if r < p - n), lift with the parity recid & 1, Q = (s/r) X - (m/r) G.
+ * xy64 = affine x || y of the recovered key; returns 0 (and zeros) when nothing can be recovered. */
+int orc_ecdsa_recover(const uint8_t msg32[32], const uint8_t sig64[64], int recid, uint8_t xy64[64]) {
+    memset(xy64, 0, 64);
+    if (recid < 0 || recid > 3) return 0;
+    u256 r, s, m;
+    if (sc_set_b32(&r, sig64) || sc_set_b32(&s, sig64 + 32)) return 0; /* parse_compact: overflow => fail */
+    if (u256_is_zero(&r) || u256_is_zero(&s)) return 0;                /* :97-99 */
+    u256 fx = r;
+    if (recid & 2) {
+        if (u256_cmp(&fx, &P_MINUS_N) >= 0) return 0;                  /* :106-108 */
+        u256_add(&fx, &fx, &SC_N);
+    }
+    uint8_t pub[33];
+    pub[0] = (recid & 1) ? 0x03 : 0x02;
+    u256_to_be(pub + 1, &fx);
+    ge x;
+    if (!pubkey_parse_ge(&x, pub, 33)) return 0;                       /* ge_set_xo_var :111 */
+    sc_set_b32(&m, msg32);
+    u256 rn, u1, u2;
+    sc_inv(&rn, &r);
+    sc_mul(&u1, &rn, &m);
+    mod_neg(&u1, &u1, &SC_N);
+    sc_mul(&u2, &rn, &s);
+    gej xj, q;
+    gej_set_ge(&xj, &x);
+    ecmult(&q, &xj, &u2, &u1);
+    if (q.inf) return 0;
+    ge qa;
+    ge_set_gej(&qa, &q);
+    u256_to_be(xy64, &qa.x); u256_to_be(xy64 + 32, &qa.y);
+    return 1;
+}
+/* secp256k1_ec_pubkey_tweak_add (src/secp256k1/src/secp256k1.c:477-499) + secp256k1_eckey_pubkey_tweak_add
+ * (eckey_impl.h:63-75): Q = P + tweak*G; fails when tweak >= n or the sum is the point at infinity. */
+int orc_pubkey_tweak_add(const uint8_t *pub, size_t publen, const uint8_t tweak32[32], uint8_t xy64[64]) {
+    memset(xy64, 0, 64);
+    ge p;
+    u256 t, one = {{1, 0, 0, 0}};
+    if (!pubkey_parse_ge(&p, pub, publen)) return 0;
+    if (sc_set_b32(&t, tweak32)) return 0;
+    gej pj, q;
+    gej_set_ge(&pj, &p);
+    ecmult(&q, &pj, &one, &t);
+    if (q.inf) return 0;
+    ge qa;
+    ge_set_gej(&qa, &q);
+    u256_to_be(xy64, &qa.x); u256_to_be(xy64 + 32, &qa.y);
+    return 1;
+}
 /* CPubKey::Verify (src/pubkey.cpp:170-193); CPubKey validity/length by prefix (src/pubkey.h:47-66) */
 static size_t publen_by_prefix(uint8_t h) {
     if (h == 2 || h == 3) return 33;

@@ -59,6 +59,9 @@ int orc_der_lax_parse(const uint8_t *in, size_t len, uint8_t sig64[64]);
 int orc_check_low_s(const uint8_t *der, size_t len);
 int orc_ecdsa_verify(const uint8_t msg32[32], const uint8_t *pub, size_t publen, const uint8_t sig64[64]);
 int orc_pubkey_verify(const uint8_t hash32[32], const uint8_t *pub, size_t publen, const uint8_t *der, size_t derlen);
+/* src/secp256k1/src/modules/recovery/main_impl.h:38-58, 87-121, 170-190; src/secp256k1/src/secp256k1.c:477-499 */
+int orc_ecdsa_recover(const uint8_t msg32[32], const uint8_t sig64[64], int recid, uint8_t xy64[64]);
+int orc_pubkey_tweak_add(const uint8_t *pub, size_t publen, const uint8_t tweak32[32], uint8_t xy64[64]);
 /* B4 batch layout: pubkeys at stride 65, length by prefix byte (src/pubkey.h:47-51) */
 void orc_ecdsa_verify_batch(const uint8_t *msg32, const uint8_t *pub65, const uint8_t *sig64, size_t n, int nthreads,
                             uint8_t *ok);

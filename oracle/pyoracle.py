@@ -66,6 +66,8 @@ class Impl:
         self._equihash_verify = L.fn("equihash_verify", i, C.c_uint, C.c_uint, u8p, sz)
         self._equihash_verify_batch = L.fn("equihash_verify_batch", None, C.c_uint, C.c_uint, u8p, sz, sz, sz, i, u8p)
         self._pubkey_parse = L.fn("pubkey_parse", i, u8p, sz, u8p)
+        self._recover = L.fn("ecdsa_recover", i, u8p, u8p, i, u8p)
+        self._tweak_add = L.fn("pubkey_tweak_add", i, u8p, sz, u8p, u8p)
         if prefix == "orc_":
             self._sign = L.fn("sign_rfc6979", i, u8p, u8p, u8p)
             self._header_hash = L.fn("header_hash", None, u8p, sz, u8p)
@@ -82,6 +84,9 @@ class Impl:
             self._gen_chain_txs = L.fn("gen_chain_txs", sz, u8p, sz, sz, sz, sz, u8p, C.POINTER(u32), C.POINTER(i64), i, u8p, sz)
         else:
             L.fn("init", i)()
+            self._sign_rec = L.fn("sign_recoverable", i, u8p, u8p, u8p, C.POINTER(i))
+            self._recover_compact = L.fn("cpubkey_recover_compact", i, u8p, u8p, u8p)
+            self._derive = L.fn("cpubkey_derive", i, u8p, u8p, C.c_uint, u8p, u8p)
             self._sign = L.fn("sign", i, u8p, u8p, u8p)
             self._header_hash_ref = L.fn("header_hash", i, u8p, sz, i, u8p)
             self._solve = L.fn("equihash_solve", i, C.c_uint, C.c_uint, u8p, i, u8p, sz, i)
@@ -161,6 +166,37 @@ class Impl:
         if not self._sig_to_der(_p(bytes(sig64)), out, C.byref(ln)):
             return None
         return bytes(out)[: ln.value]
+
+    def ecdsa_recover(self, msg32, sig64, recid):
+        """secp256k1_ecdsa_recover: affine x || y (64 bytes) of the recovered key, or None."""
+        out = (C.c_uint8 * 64)()
+        ok = self._recover(_p(bytes(msg32)), _p(bytes(sig64)), int(recid), out)
+        return bytes(out) if ok else None
+
+    def pubkey_tweak_add(self, pub, tweak32):
+        """secp256k1_ec_pubkey_tweak_add: affine x || y of pub + tweak*G, or None."""
+        out = (C.c_uint8 * 64)()
+        ok = self._tweak_add(_p(bytes(pub)), len(pub), _p(bytes(tweak32)), out)
+        return bytes(out) if ok else None
+
+    def sign_recoverable(self, seckey, msg32):
+        """reference only: (sig64, recid) from secp256k1_ecdsa_sign_recoverable."""
+        out = (C.c_uint8 * 64)()
+        rid = C.c_int(-1)
+        assert self._sign_rec(_p(bytes(seckey)), _p(bytes(msg32)), out, C.byref(rid)) == 1
+        return bytes(out), rid.value
+
+    def cpubkey_recover_compact(self, hash32, sig65):
+        """reference only: CPubKey::RecoverCompact -> serialized key bytes or None."""
+        out = (C.c_uint8 * 65)()
+        n = self._recover_compact(_p(bytes(hash32)), _p(bytes(sig65)), out)
+        return bytes(out)[:n] if n else None
+
+    def cpubkey_derive(self, pub33, cc32, nchild):
+        """reference only: CPubKey::Derive -> (child33, chaincode32) or None."""
+        o, c = (C.c_uint8 * 33)(), (C.c_uint8 * 32)()
+        ok = self._derive(_p(bytes(pub33)), _p(bytes(cc32)), int(nchild), o, c)
+        return (bytes(o), bytes(c)) if ok else None
 
     def pubkey_parse(self, pub):
         out = (C.c_uint8 * 64)()

@@ -33,6 +33,7 @@
 #include <algorithm>
 
 #include "secp256k1.h"
+#include "secp256k1_recovery.h"
 #include "pubkey.h"
 #include "hash.h"
 #include "uint256.h"
@@ -125,6 +126,65 @@ void ref_ecdsa_verify_batch(const uint8_t *msg32, const uint8_t *pub65, const ui
             ok[i] = len ? (uint8_t)ref_ecdsa_verify(msg32 + 32 * i, pub65 + 65 * i, len, sig64 + 64 * i) : 0;
         }
     });
+}
+
+// secp256k1_ecdsa_recoverable_signature_parse_compact + secp256k1_ecdsa_recover
+// (src/secp256k1/src/modules/recovery/main_impl.h:38-58, 170-190): xy64 = x || y of the recovered key
+int ref_ecdsa_recover(const uint8_t *msg32, const uint8_t *sig64, int recid, uint8_t *xy64) {
+    ensure_init();
+    memset(xy64, 0, 64);
+    secp256k1_ecdsa_recoverable_signature rs;
+    secp256k1_pubkey pk;
+    if (recid < 0 || recid > 3) return 0;
+    if (!secp256k1_ecdsa_recoverable_signature_parse_compact(g_ctx, &rs, sig64, recid)) return 0;
+    if (!secp256k1_ecdsa_recover(g_ctx, &pk, &rs, msg32)) return 0;
+    uint8_t out[65];
+    size_t ol = 65;
+    secp256k1_ec_pubkey_serialize(g_ctx, out, &ol, &pk, SECP256K1_EC_UNCOMPRESSED);
+    memcpy(xy64, out + 1, 64);
+    return 1;
+}
+// secp256k1_ecdsa_sign_recoverable (:123-168): compact signature + recovery id, RFC 6979 nonce (fixture generation)
+int ref_sign_recoverable(const uint8_t *seckey32, const uint8_t *msg32, uint8_t *sig64, int *recid) {
+    ensure_init();
+    secp256k1_ecdsa_recoverable_signature rs;
+    if (!secp256k1_ecdsa_sign_recoverable(g_ctx, &rs, msg32, seckey32, nullptr, nullptr)) return 0;
+    secp256k1_ecdsa_recoverable_signature_serialize_compact(g_ctx, sig64, recid, &rs);
+    return 1;
+}
+// secp256k1_ec_pubkey_tweak_add (src/secp256k1/src/secp256k1.c:477-499)
+int ref_pubkey_tweak_add(const uint8_t *pub, size_t publen, const uint8_t *tweak32, uint8_t *xy64) {
+    ensure_init();
+    memset(xy64, 0, 64);
+    secp256k1_pubkey pk;
+    if (!secp256k1_ec_pubkey_parse(g_ctx, &pk, pub, publen)) return 0;
+    if (!secp256k1_ec_pubkey_tweak_add(g_ctx, &pk, tweak32)) return 0;
+    uint8_t out[65];
+    size_t ol = 65;
+    secp256k1_ec_pubkey_serialize(g_ctx, out, &ol, &pk, SECP256K1_EC_UNCOMPRESSED);
+    memcpy(xy64, out + 1, 64);
+    return 1;
+}
+// CPubKey::RecoverCompact (src/pubkey.cpp:195-218) on the 65-byte compact form: out = serialized key, returns its length or 0
+int ref_cpubkey_recover_compact(const uint8_t *hash32, const uint8_t *sig65, uint8_t *out65) {
+    ensure_init();
+    CPubKey pk;
+    uint256 h;
+    memcpy(h.begin(), hash32, 32);
+    if (!pk.RecoverCompact(h, std::vector<uint8_t>(sig65, sig65 + 65))) return 0;
+    memcpy(out65, pk.begin(), pk.size());
+    return (int)pk.size();
+}
+// CPubKey::Derive (src/pubkey.cpp:240-264): BIP32 public child; out33 = child key, cc_out32 = child chain code
+int ref_cpubkey_derive(const uint8_t *pub33, const uint8_t *cc32, unsigned nChild, uint8_t *out33, uint8_t *cc_out32) {
+    ensure_init();
+    CPubKey pk(pub33, pub33 + 33), child;
+    ChainCode cc, ccChild;
+    memcpy(cc.begin(), cc32, 32);
+    if (!pk.Derive(child, ccChild, nChild, cc)) return 0;
+    memcpy(out33, child.begin(), 33);
+    memcpy(cc_out32, ccChild.begin(), 32);
+    return 1;
 }
 
 // CPubKey::Verify path (what the node calls): DER signature WITHOUT the hashtype byte.

@@ -11,6 +11,10 @@ travel with the repo so that the GPU box, which has neither, can check parity ag
                             accepted by its IsValidSolution
   ecdsa_ref.npz             signature set with every corruption class + the reference's verdicts
                             (secp256k1_ecdsa_verify path and CPubKey::Verify path)
+  recovery_ref.npz          public-key recovery and tweak-add cases (random, corrupted, and the hard-coded edge vectors of
+                            src/secp256k1/src/modules/recovery/tests_impl.h:208-258) with the results of the reference's
+                            secp256k1_ecdsa_recover / secp256k1_ec_pubkey_tweak_add, plus CPubKey::RecoverCompact and
+                            CPubKey::Derive (src/pubkey.cpp:195-264) outputs for the B3 compat test
   sha256_kat.json           src/test/crypto_tests.cpp:282-316 SHA-256 known answers re-derived with the
                             reference's CSHA256 (and hashlib as a third opinion)
   secp_vectors.json         hard-coded vectors of src/secp256k1/src/tests.c (pubkey parse valid/invalid
@@ -111,6 +115,111 @@ def gen_ecdsa():
     print("ecdsa_ref:", len(msg), "raw valid", int(raw.sum()), "cpubkey valid", int(cpk.sum()))
 
 
+def gen_recovery():
+    from oracle import pyoracle as po
+    import synth
+
+    r = po.ref()
+    N = synth.N
+    rec = []  # (msg32, sig64, recid)
+    for i in range(500):
+        k = synth.seckey(20000 + i)
+        m = hashlib.sha256(b"recover-msg%d" % i).digest()
+        sig, rid = r.sign_recoverable(k, m)
+        for rr in range(4):
+            rec.append((m, sig, rr))
+        if i % 5 == 0:  # damaged: a flipped bit in r, s or the message
+            bit = synth.prng(i, b"recbit")
+            b = bytearray(sig)
+            b[(bit >> 3) % 64] ^= 1 << (bit & 7)
+            rec.append((m, bytes(b), rid))
+            mm = bytearray(m)
+            mm[(bit >> 11) % 32] ^= 1 << ((bit >> 8) & 7)
+            rec.append((bytes(mm), sig, rid))
+    # edge vectors of tests_impl.h:208-258: a signature made with secret key 0 (recoverable only with recid 1) and
+    # (r, s) = (4, 4), which every recid recovers
+    msg_e = b"This is a very secret message..."
+    sig_e = bytes.fromhex("67CB285F9CD194E840D629397AF5569662FDE446499959631 79A7DD17BD23532".replace(" ", "")
+                          + "4B1B7DF34CE1F68E694FF6F11AC751DD7DD73E387EE4FC866E1BE8ECC7DD9557")
+    sig_44 = (4).to_bytes(32, "big") * 2
+    for rr in range(4):
+        rec.append((msg_e, sig_e, rr))
+        rec.append((msg_e, sig_44, rr))
+    # range rules: r = 0, s = 0, r = n, s = n, r just below p - n with recid 2/3 (x = r + n < p), r = p - n (refused)
+    pmn = synth.P - N
+    m0 = hashlib.sha256(b"range").digest()
+    for rv, sv in ((0, 5), (5, 0), (N, 5), (5, N), (pmn - 1, 7), (pmn, 7), (pmn + 1, 7), (N - 1, N - 1), (1, 1)):
+        for rr in range(4):
+            rec.append((m0, rv.to_bytes(32, "big") + sv.to_bytes(32, "big"), rr))
+    rec_msg = np.array([np.frombuffer(a, np.uint8) for a, _, _ in rec])
+    rec_sig = np.array([np.frombuffer(b, np.uint8) for _, b, _ in rec])
+    rec_id = np.array([c for _, _, c in rec], dtype=np.uint8)
+    rec_xy = np.zeros((len(rec), 64), np.uint8)
+    rec_ok = np.zeros(len(rec), np.uint8)
+    for i, (m, sg, rr) in enumerate(rec):
+        xy = r.ecdsa_recover(m, sg, rr)
+        if xy is not None:
+            rec_ok[i] = 1
+            rec_xy[i] = np.frombuffer(xy, np.uint8)
+    # the two tests_impl.h expectations, asserted here so the fixture cannot silently drift from them
+    base = len(rec) - 36 - 8
+    assert [int(rec_ok[base + 2 * rr]) for rr in range(4)] == [0, 1, 0, 0]
+    assert all(rec_ok[base + 2 * rr + 1] for rr in range(4))
+    tw = []  # (pub slot 65, tweak32)
+    for i in range(400):
+        k = synth.seckey(30000 + i)
+        d = int.from_bytes(k, "big")
+        pub = r.pubkey_create(k, i % 3 != 0)
+        slot = pub + bytes(65 - len(pub))
+        t = hashlib.sha256(b"tweak%d" % i).digest()
+        tw.append((slot, t))
+        if i % 10 == 0:
+            for tv in (0, 1, N - 1, N, N + 1, 2**256 - 1, (N - d) % N, (N - d + 1) % N):
+                tw.append((slot, tv.to_bytes(32, "big")))
+        if i % 25 == 0:  # keys that do not parse
+            tw.append((bytes([5]) + slot[1:], t))
+            tw.append((bytes([2]) + (synth.P).to_bytes(32, "big") + bytes(32), t))
+    tw_pub = np.array([np.frombuffer(a, np.uint8) for a, _ in tw])
+    tw_t = np.array([np.frombuffer(b, np.uint8) for _, b in tw])
+    tw_xy = np.zeros((len(tw), 64), np.uint8)
+    tw_ok = np.zeros(len(tw), np.uint8)
+    for i, (slot, t) in enumerate(tw):
+        plen = 33 if slot[0] in (2, 3) else 65
+        xy = r.pubkey_tweak_add(slot[:plen], t)
+        if xy is not None:
+            tw_ok[i] = 1
+            tw_xy[i] = np.frombuffer(xy, np.uint8)
+    # CPubKey level (src/pubkey.cpp:195-264): RecoverCompact on 65-byte compact signatures, Derive on compressed keys
+    rc_hash, rc_sig, rc_out, rc_len = [], [], [], []
+    for i in range(60):
+        k = synth.seckey(40000 + i)
+        m = hashlib.sha256(b"compact%d" % i).digest()
+        sig, rid = r.sign_recoverable(k, m)
+        hdr = 27 + rid + (4 if i % 2 else 0)
+        s65 = bytes([hdr]) + sig
+        if i % 7 == 3:
+            s65 = bytes([hdr]) + bytes([sig[0] ^ 0x40]) + sig[1:]
+        out = r.cpubkey_recover_compact(m, s65)
+        rc_hash.append(np.frombuffer(m, np.uint8)); rc_sig.append(np.frombuffer(s65, np.uint8))
+        rc_len.append(len(out) if out else 0)
+        rc_out.append(np.frombuffer((out or b"") + bytes(65 - len(out or b"")), np.uint8))
+    dv_pub, dv_cc, dv_n, dv_out, dv_ccout = [], [], [], [], []
+    for i in range(60):
+        pub = r.pubkey_create(synth.seckey(50000 + i), True)
+        cc = hashlib.sha256(b"chaincode%d" % i).digest()
+        res = r.cpubkey_derive(pub, cc, i * 7919)
+        assert res is not None
+        dv_pub.append(np.frombuffer(pub, np.uint8)); dv_cc.append(np.frombuffer(cc, np.uint8)); dv_n.append(i * 7919)
+        dv_out.append(np.frombuffer(res[0], np.uint8)); dv_ccout.append(np.frombuffer(res[1], np.uint8))
+    np.savez_compressed(os.path.join(HERE, "recovery_ref.npz"), rec_msg=rec_msg, rec_sig=rec_sig, rec_id=rec_id, rec_xy=rec_xy,
+                        rec_ok=rec_ok, tw_pub=tw_pub, tw_tweak=tw_t, tw_xy=tw_xy, tw_ok=tw_ok, rc_hash=np.array(rc_hash),
+                        rc_sig=np.array(rc_sig), rc_out=np.array(rc_out), rc_len=np.array(rc_len, np.uint8),
+                        dv_pub=np.array(dv_pub), dv_cc=np.array(dv_cc), dv_n=np.array(dv_n, np.uint32), dv_out=np.array(dv_out),
+                        dv_ccout=np.array(dv_ccout))
+    print("recovery_ref: recover", len(rec), "ok", int(rec_ok.sum()), "| tweak_add", len(tw), "ok", int(tw_ok.sum()),
+          "| RecoverCompact", len(rc_len), "ok", sum(1 for x in rc_len if x), "| Derive", len(dv_n))
+
+
 def gen_sha_kat():
     from oracle import pyoracle as po
 
@@ -134,8 +243,13 @@ if __name__ == "__main__":
     ap.add_argument("--eh200", type=int, default=0)
     ap.add_argument("--procs", type=int, default=6)
     ap.add_argument("--skip-small", action="store_true")
+    ap.add_argument("--only-recovery", action="store_true")
     a = ap.parse_args()
+    if a.only_recovery:
+        gen_recovery()
+        sys.exit(0)
     if not a.skip_small:
+        gen_recovery()
         gen_block()
         gen_sha_kat()
         gen_ecdsa()

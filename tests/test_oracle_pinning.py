@@ -263,3 +263,22 @@ def test_equihash_duplicate_index_pseudo_solutions_oracle_vs_reference():
     assert (got == want).all()
     if po.have_ref():
         assert ((po.ref().equihash_verify_batch(48, 5, arr, 2) == 1).astype(int) == want).all()
+
+
+def test_recover_and_tweak_add_match_the_reference_fixture(oracle):
+    """tests/golden/recovery_ref.npz (secp256k1_ecdsa_recover / secp256k1_ec_pubkey_tweak_add of the reference, incl. the
+    hard-coded edge vectors of src/secp256k1/src/modules/recovery/tests_impl.h:208-258) vs the oracle restatement."""
+    g = np.load(os.path.join(GOLD, "recovery_ref.npz"))
+    for i in range(len(g["rec_id"])):
+        got = oracle.ecdsa_recover(g["rec_msg"][i].tobytes(), g["rec_sig"][i].tobytes(), int(g["rec_id"][i]))
+        assert (got is not None) == bool(g["rec_ok"][i]), i
+        if got is not None:
+            assert got == g["rec_xy"][i].tobytes(), i
+    for i in range(len(g["tw_ok"])):
+        slot = g["tw_pub"][i].tobytes()
+        plen = 33 if slot[0] in (2, 3) else 65
+        got = oracle.pubkey_tweak_add(slot[:plen], g["tw_tweak"][i].tobytes())
+        assert (got is not None) == bool(g["tw_ok"][i]), i
+        if got is not None:
+            assert got == g["tw_xy"][i].tobytes(), i
+    assert 0 < int(g["rec_ok"].sum()) < len(g["rec_ok"]) and 0 < int(g["tw_ok"].sum()) < len(g["tw_ok"])
