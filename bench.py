@@ -384,80 +384,131 @@ def sharded_single_caller_bench(args, devices, msg, pub, sig, expected):
     return out
 
 
-def chain_bench(args, devices):
-    """Secondary measurement in the shape of BASELINE.json configs[4]: a synthetic chain of 8 MB blocks with real UTXO
-    dependencies (block b spends block b-1) and valid regtest Equihash (48,5) headers, connected block by block by the
-    host-side connector (include/compat/bcp_chain.h): Equihash + header hash, txids + Merkle, UTXO lookups, P2PKH script
-    checks + batched ECDSA, UTXO commit.  CPU side: the reference's deserialization + txids + Merkle + VerifyScript on
-    all threads for a 2-block sample of the same chain."""
+_CHAIN_CACHE = {}
+
+
+def _chain_blocks(nb, ntx):
+    """the synthetic chain, generated once per process: (blocks, seeds, seconds)"""
+    import synth
+
+    key = (nb, ntx)
+    if key not in _CHAIN_CACHE:
+        t0 = time.perf_counter()
+        blocks = list(synth.synthetic_chain_fast(nb, ntx))
+        seeds = synth.chain_seeds(ntx, 4096)
+        _CHAIN_CACHE[key] = (blocks, seeds, time.perf_counter() - t0)
+    return _CHAIN_CACHE[key]
+
+
+def chain_bench(args, devices, impl="device"):
+    """BASELINE.json configs[4]: a synthetic chain of 8 MB blocks with real UTXO dependencies (block b spends block b-1)
+    and valid regtest Equihash (48,5) headers, in blk*.dat framing in one pinned buffer, connected by
+      impl "device": bcp::DeviceChain (include/compat/bcp_chain_gpu.h) — coin table in HBM on GPU 0 (txids + Merkle, inserts,
+                     lookups + spends as kernels in chain order), whole blocks dealt out to the GPUs for the header and
+                     script checks, several blocks in flight, verdicts taken in order;
+      impl "host":   bcp::ChainValidator (include/compat/bcp_chain.h) — coin map walked by host threads, each block's inputs
+                     split over the GPUs, two blocks in flight.
+    CPU side: the reference's deserialization + txids + Merkle + VerifyScript on all threads for one block of the chain."""
     import ctypes as C
-    import numpy as np
     import synth
     from oracle import pyoracle as po
 
-    nb, ntx = args.chain_blocks + 1, args.block_txs
-    t0 = time.perf_counter()
-    blocks = list(synth.synthetic_chain_fast(nb, ntx))
-    seeds = synth.chain_seeds(ntx, 4096)
-    gen_s = time.perf_counter() - t0
+    warm = 16 if impl == "device" else 1
+    nblk = args.chain_blocks if impl == "device" else min(args.chain_blocks, 20)
+    ntx = args.block_txs
+    G_ = len(devices)
+    allb, seeds, gen_s = _chain_blocks(args.chain_blocks + 16 + 8, ntx)
+    blocks = allb[: warm + nblk]
+    extra = allb[warm + nblk: warm + nblk + G_]  # the next blocks of the chain: the last of them is also connected damaged
     L = C.CDLL(os.path.join(ROOT, "bitcoincashplus_b200", "libbcp_chain.so"))
-    L.bcp_chain_new.restype = C.c_void_p
-    L.bcp_chain_new.argtypes = [C.POINTER(C.c_int), C.c_int, C.c_uint32, C.c_uint, C.c_uint, C.c_char_p, C.c_size_t]
-    L.bcp_chain_add_coin.argtypes = [C.c_void_p, C.c_char_p, C.c_uint32, C.c_char_p, C.c_size_t, C.c_int64]
-    L.bcp_chain_connect_block.argtypes = [C.c_void_p, C.c_char_p, C.c_size_t, C.c_char_p, C.c_size_t]
-    L.bcp_chain_free.argtypes = [C.c_void_p]
+    pre = "bcp_dchain_" if impl == "device" else "bcp_chain_"
+    fn = lambda name: getattr(L, pre + name)
     err = C.create_string_buffer(256)
-    h = L.bcp_chain_new((C.c_int * len(devices))(*devices), len(devices), synth.POSTFORK_FLAGS, 48, 5, err, 256)
+    devs = (C.c_int * len(devices))(*devices)
+    if impl == "device":
+        L.bcp_dchain_new.restype = C.c_void_p
+        L.bcp_dchain_new.argtypes = [C.POINTER(C.c_int), C.c_int, C.c_uint32, C.c_uint, C.c_uint, C.c_uint, C.c_int, C.c_int, C.c_char_p, C.c_size_t]
+        lanes = 3 if len(devices) == 1 else 2
+        scan_threads = max(2, min(8, (os.cpu_count() or 4) // 2))
+        h = L.bcp_dchain_new(devs, len(devices), synth.POSTFORK_FLAGS, 48, 5, 20, lanes, scan_threads, err, 256)
+    else:
+        L.bcp_chain_new.restype = C.c_void_p
+        L.bcp_chain_new.argtypes = [C.POINTER(C.c_int), C.c_int, C.c_uint32, C.c_uint, C.c_uint, C.c_char_p, C.c_size_t]
+        h = L.bcp_chain_new(devs, len(devices), synth.POSTFORK_FLAGS, 48, 5, err, 256)
     assert h, err.value
+    fn("add_coin").argtypes = [C.c_void_p, C.c_char_p, C.c_uint32, C.c_char_p, C.c_size_t, C.c_int64]
     for txid, vout, spk, amount in seeds:
-        L.bcp_chain_add_coin(h, txid, vout, spk, len(spk), amount)
+        fn("add_coin")(h, txid, vout, spk, len(spk), amount)
     reason = C.create_string_buffer(256)
-    # the blocks live in ONE pinned buffer in blk*.dat framing (magic | size | block), as the import loop of -reindex reads
-    # them (LoadExternalBlockFile, src/validation.cpp:4486-4516); block 0 is connected separately as the warm-up
+    # the blocks live in pinned buffers in blk*.dat framing (magic | size | block), as the import loop of -reindex reads them
+    # (LoadExternalBlockFile, src/validation.cpp:4486-4516); the first `warm` blocks are connected untimed (allocations)
     import bitcoincashplus_b200 as bcp
     G = bcp.lib()
     magic = bytes.fromhex("e48f1d1c")
-    framed = b"".join(magic + len(b).to_bytes(4, "little") + b for b in blocks[1:])
-    p0 = G.bcp_gpu_host_alloc(len(blocks[0]))
-    C.memmove(p0, blocks[0], len(blocks[0]))
-    pf = G.bcp_gpu_host_alloc(len(framed))
-    C.memmove(pf, framed, len(framed))
-    L.bcp_chain_connect_block.argtypes = [C.c_void_p, C.c_void_p, C.c_size_t, C.c_char_p, C.c_size_t]
-    ok = L.bcp_chain_connect_block(h, p0, len(blocks[0]), reason, 256)
-    assert ok == 1, reason.value
-    ph0 = (C.c_double * 5)()
-    L.bcp_chain_phase_seconds.argtypes = [C.c_void_p, C.POINTER(C.c_double)]
-    L.bcp_chain_phase_seconds(h, ph0)
-    nb -= 1
-    L.bcp_chain_connect_file.restype = C.c_long
-    L.bcp_chain_connect_file.argtypes = [C.c_void_p, C.c_void_p, C.c_size_t, C.c_char_p, C.c_char_p, C.c_size_t, C.POINTER(C.c_long)]
+    frame = lambda bl: b"".join(magic + len(b).to_bytes(4, "little") + b for b in bl)
+    bufs = []
+    for part in (blocks[:warm], blocks[warm:]):
+        data = frame(part)
+        p_ = G.bcp_gpu_host_alloc(len(data))
+        C.memmove(p_, data, len(data))
+        bufs.append((p_, len(data)))
+    fn("connect_file").restype = C.c_long
+    fn("connect_file").argtypes = [C.c_void_p, C.c_void_p, C.c_size_t, C.c_char_p, C.c_char_p, C.c_size_t, C.POINTER(C.c_long)]
+    fn("free").argtypes = [C.c_void_p]
     failed = C.c_long(-1)
+    n_ok = fn("connect_file")(h, bufs[0][0], bufs[0][1], magic, reason, 256, C.byref(failed))
+    assert n_ok == warm, (n_ok, failed.value, reason.value)
+    nph = 6 if impl == "device" else 5
+    fn("phase_seconds").argtypes = [C.c_void_p, C.POINTER(C.c_double)]
+    ph0 = (C.c_double * nph)()
+    fn("phase_seconds")(h, ph0)
     t0 = time.perf_counter()
-    n_ok = L.bcp_chain_connect_file(h, pf, len(framed), magic, reason, 256, C.byref(failed))
+    n_ok = fn("connect_file")(h, bufs[1][0], bufs[1][1], magic, reason, 256, C.byref(failed))
     total = time.perf_counter() - t0
-    assert n_ok == nb, (n_ok, failed.value, reason.value)
-    ph = (C.c_double * 5)()
-    L.bcp_chain_phase_seconds.argtypes = [C.c_void_p, C.POINTER(C.c_double)]
-    L.bcp_chain_phase_seconds(h, ph)
-    phases = dict(zip(["header_equihash", "framing_scan", "txids_wait_after_lookups", "utxo_walk", "scripts_wait_after_inserts"],
-                      [1e3 * (x - x0) / nb for x, x0 in zip(ph, ph0)]))
-    wk = (C.c_double * 4)()
-    L.bcp_chain_walk_seconds.argtypes = [C.c_void_p, C.POINTER(C.c_double)]
-    L.bcp_chain_walk_seconds(h, wk)
-    phases["utxo_walk_parts"] = dict(zip(["pass_a_lookups", "staging_and_launch", "pass_b_inserts", "pass_c_in_block"],
-                                         [1e3 * x / (nb + 1) for x in wk]))
-    G.bcp_gpu_host_free(p0)
-    G.bcp_gpu_host_free(pf)
-    L.bcp_chain_free(h)
-    out = {"blocks": nb, "inputs_per_block": ntx, "block_bytes": len(blocks[0]), "gpus": len(devices),
-           "sharding": "one host chain walk; each block's inputs split by index across the GPUs, verdicts ANDed on the host",
-           "gpu_seconds_total": total,
-           "gpu_blocks_per_s": nb / total, "gpu_ms_per_block": 1e3 * total / nb,
-           "ms_per_block_by_phase": phases, "gen_seconds": gen_s, "warmup_blocks": 1,
-           "timed": "bcp::ChainValidator::ConnectFile over the blocks in blk*.dat framing in one pinned buffer: two blocks in "
-                    "flight (block b+1 is scanned, looked up and applied while the devices check block b's scripts), in-memory "
-                    "UTXO table on the host"}
-    if po.have_ref():
+    assert n_ok == nblk, (n_ok, failed.value, reason.value)
+    ph = (C.c_double * nph)()
+    fn("phase_seconds")(h, ph)
+    if impl == "device":
+        names = ["connecting_thread_apply_calls", "connecting_thread_waiting", "check_threads_wait_for_spent_coins",
+                 "check_threads_header", "check_threads_scripts", "scan_threads"]
+    else:
+        names = ["header_equihash", "framing_scan", "txids_wait_after_lookups", "utxo_walk", "scripts_wait_after_inserts"]
+    phases = dict(zip(names, [1e3 * (x - x0) / nblk for x, x0 in zip(ph, ph0)]))
+    if impl == "host":
+        wk = (C.c_double * 4)()
+        L.bcp_chain_walk_seconds.argtypes = [C.c_void_p, C.POINTER(C.c_double)]
+        L.bcp_chain_walk_seconds(h, wk)
+        phases["utxo_walk_parts"] = dict(zip(["pass_a_lookups", "staging_and_launch", "pass_b_inserts", "pass_c_in_block"],
+                                             [1e3 * x / (nblk + warm) for x in wk]))
+    # A rejected block on the LAST device: the next G blocks of the chain, the last of them (dealt to device G-1 by the
+    # device connector; input range of device G-1 in the host one) with one broken signature under a consistent header.
+    # It must be refused with exactly that input, the blocks before it stay connected, and the undamaged block connects after.
+    bad_input = ntx - 7
+    tail = list(extra[:-1]) + [synth.damage_chain_block(extra[-1], warm + nblk + G_ - 1, bad_input)]
+    data = frame(tail)
+    n_ok = fn("connect_file")(h, data, len(data), magic, reason, 256, C.byref(failed))
+    assert n_ok == G_ - 1 and failed.value == G_ - 1, (n_ok, failed.value, reason.value)
+    assert reason.value == b"blk-bad-inputs (input %d, script error 31)" % bad_input, reason.value
+    data = frame(extra[-1:])
+    assert fn("connect_file")(h, data, len(data), magic, reason, 256, C.byref(failed)) == 1, reason.value
+    for p_, _ in bufs:
+        G.bcp_gpu_host_free(p_)
+    fn("free")(h)
+    out = {"impl": "bcp::DeviceChain (coin table in HBM)" if impl == "device" else "bcp::ChainValidator (coin map on host threads)",
+           "blocks": nblk, "inputs_per_block": ntx, "block_bytes": len(blocks[0]), "gpus": len(devices),
+           "sharding": ("whole blocks dealt out to the GPUs (block b's header + script checks on GPU b mod N); coin table, txids and "
+                        "Merkle roots on GPU 0 in chain order; verdicts taken in order on the host" if impl == "device" else
+                        "one host chain walk; each block's inputs split by index across the GPUs, verdicts ANDed on the host"),
+           "gpu_seconds_total": total, "gpu_blocks_per_s": nblk / total, "gpu_ms_per_block": 1e3 * total / nblk,
+           "gpu_inputs_per_s": nblk * ntx / total,
+           "ms_per_block_by_phase": phases, "gen_seconds": gen_s, "warmup_blocks": warm,
+           "rejected_block_check": "block %d of the chain with a broken signature at input %d, checked by GPU %d: refused with that "
+                                   "input, table rolled back, the undamaged block connected afterwards" % (warm + nblk + G_ - 1, bad_input, G_ - 1),
+           "timed": "ConnectFile over %d blocks in blk*.dat framing in one pinned buffer, wall clock of the caller" % nblk}
+    if impl == "device":
+        out["phase_note"] = ("thread-seconds per block summed over the threads of each kind, not a critical path: the connecting thread "
+                             "is the only sequential part (apply calls + waiting); check threads = %d per GPU" % lanes)
+    if po.have_ref() and impl == "device":
         r = po.ref()
         cores = os.cpu_count() or 1
         spk = [s[2] for s in seeds]
@@ -469,7 +520,7 @@ def chain_bench(args, devices):
         cpu_s = time.perf_counter() - t0
         assert not e.any() and okh == 1 and root == blocks[0][36:68]
         out.update({"cpu_kind": "reference", "cpu_cores": cores, "cpu_ms_per_block": cpu_s * 1e3,
-                    "cpu_blocks_per_s": 1.0 / cpu_s, "speedup_vs_cpu": (nb / total) * cpu_s,
+                    "cpu_blocks_per_s": 1.0 / cpu_s, "speedup_vs_cpu": (nblk / total) * cpu_s,
                     "cpu_sample": "block 0 of the chain: CBlock deserialize + txids + Merkle (1 thread), VerifyScript per input (all threads), Equihash; no UTXO map work"})
     return out
 
@@ -518,7 +569,7 @@ def main():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-block", action="store_true", help="skip the secondary 8 MB block measurement (configs[2])")
     ap.add_argument("--block-txs", type=int, default=41650)
-    ap.add_argument("--chain-blocks", type=int, default=20, help="blocks of the synthetic chain reindex (configs[4] shape); 0 = skip")
+    ap.add_argument("--chain-blocks", type=int, default=100, help="blocks of the synthetic chain reindex (configs[4]); 0 = skip")
     args = ap.parse_args()
     if args.impl == "reference":
         return run_reference(args)
@@ -694,7 +745,8 @@ def main():
         line["equihash10k"] = equihash_bench(eng)
         line["sharded_single_caller"] = sharded_single_caller_bench(args, list(range(world)), msg, pub, sig, expected)
         if args.chain_blocks > 0:
-            line["chain"] = chain_bench(args, list(range(world)))
+            line["chain"] = chain_bench(args, list(range(world)), "device")
+            line["chain_host_table"] = chain_bench(args, list(range(world)), "host")
     print(json.dumps(line), flush=True)
     if dist:
         td.barrier(group=hostgrp)

@@ -38,6 +38,14 @@ SIGNATURES = {
     "bcp_gpu_ecdsa_recover_batch": (C.c_int, [C.c_int, vp, vp, vp, sz, vp, vp]),
     "bcp_gpu_pubkey_tweak_add_batch": (C.c_int, [C.c_int, vp, vp, sz, vp, vp]),
     "bcp_der_lax_parse": (C.c_int, [vp, sz, vp]),
+    "bcp_gpu_utxo_create": (vp, [C.c_int, C.c_uint, sz]),
+    "bcp_gpu_utxo_destroy": (None, [vp]),
+    "bcp_gpu_utxo_add_coins": (C.c_int, [vp, vp, vp, vp, vp, sz]),
+    "bcp_gpu_utxo_size": (C.c_longlong, [vp]),
+    "bcp_gpu_utxo_apply_block": (C.c_int, [vp, C.c_uint32, vp, sz, vp, sz, vp, vp, sz, vp, vp, vp, sz, vp, vp, vp, vp, sz, vp, vp]),
+    "bcp_gpu_utxo_wait": (C.c_int, [vp, C.c_uint32, vp]),
+    "bcp_gpu_utxo_confirm": (C.c_int, [vp, C.c_uint32]),
+    "bcp_gpu_utxo_rollback": (C.c_int, [vp, C.c_uint32]),
     "bcp_block_index": (C.c_long, [vp, sz, C.c_int, vp, sz]),
     "bcp_gpu_sha256d_txids_merkle": (C.c_int, [C.c_int, vp, sz, vp, sz, vp, vp, C.POINTER(C.c_int)]),
     "bcp_gpu_merkle_root": (C.c_int, [C.c_int, vp, sz, vp, C.POINTER(C.c_int)]),

@@ -308,9 +308,13 @@ int bcp_ecdsa_build_tables(bcp_ctx *c) {
     return BCP_OK;
 }
 
-// 1 (default): batches of more than a wave go through the persistent rounds kernel; 2: every batch; 0: never (A/B switch)
+// 0 (default): one block per 256 signatures (128 below a wave); 1: batches of more than a wave go through the persistent
+// kernel with chunk claiming; 2: every batch does.  Measured on B200 (1 M signatures): 21.24 ms vs 21.61 ms — the
+// persistent form needs 58 MB of table scratch instead of 768 B per signature and deals the last partial wave out evenly,
+// but its two extra live values cost more in the 128-register point phase than that brings, so it is the memory-saving
+// option (BCP_POINT_ROUNDS=1), not the default.
 static int point_rounds_mode() {
-    static const int mode = getenv("BCP_POINT_ROUNDS") ? atoi(getenv("BCP_POINT_ROUNDS")) : 1;
+    static const int mode = getenv("BCP_POINT_ROUNDS") ? atoi(getenv("BCP_POINT_ROUNDS")) : 0;
     return mode;
 }
 #define BCP_MAX_RESIDENT_BLOCKS (160 * BCP_POINT_BLOCKS_PER_SM) /* upper bound of the persistent grid on any sm_100 part */

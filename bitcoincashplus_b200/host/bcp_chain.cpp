@@ -6,6 +6,7 @@
 #include <string>
 
 #include "../../include/compat/bcp_chain.h"
+#include "../../include/compat/bcp_chain_gpu.h"
 #include "../../include/compat/bcp_recorder.h"
 
 #define CHAIN_API extern "C" __attribute__((visibility("default")))
@@ -85,4 +86,43 @@ CHAIN_API int bcp_sharded_ecdsa_verify(const int *devices, int ndev, const uint8
         *all_ok = a;
     }
     return 0;
+}
+
+// ---- bcp::DeviceChain (include/compat/bcp_chain_gpu.h): the connector whose coin table lives on the device ----
+CHAIN_API void *bcp_dchain_new(const int *devices, int ndev, uint32_t script_flags, unsigned eh_n, unsigned eh_k, unsigned log2_slots,
+                               int lanes, int scan_threads, char *err, size_t errlen) {
+    std::vector<int> d(devices, devices + ndev);
+    auto *v = new bcp::DeviceChain(d, script_flags, eh_n, eh_k, log2_slots, lanes, scan_threads);
+    std::string e;
+    if (!v->Init(e)) {
+        if (err && errlen) snprintf(err, errlen, "%s", e.c_str());
+        delete v;
+        return nullptr;
+    }
+    return v;
+}
+CHAIN_API void bcp_dchain_free(void *h) { delete static_cast<bcp::DeviceChain *>(h); }
+CHAIN_API void bcp_dchain_add_coin(void *h, const uint8_t *txid32, uint32_t vout, const uint8_t *spk, size_t len, int64_t amount) {
+    static_cast<bcp::DeviceChain *>(h)->AddCoin(txid32, vout, spk, len, amount);
+}
+CHAIN_API size_t bcp_dchain_utxo_size(void *h) { return (size_t)static_cast<bcp::DeviceChain *>(h)->UtxoSize(); }
+CHAIN_API size_t bcp_dchain_inputs_checked(void *h) { return static_cast<bcp::DeviceChain *>(h)->InputsChecked(); }
+CHAIN_API int bcp_dchain_connect_block(void *h, const uint8_t *blk, size_t len, char *reason, size_t reasonlen) {
+    std::string r;
+    bool ok = static_cast<bcp::DeviceChain *>(h)->ConnectBlock(blk, len, r);
+    if (reason && reasonlen) snprintf(reason, reasonlen, "%s", r.c_str());
+    return ok ? 1 : 0;
+}
+CHAIN_API long bcp_dchain_connect_file(void *h, const uint8_t *data, size_t len, const uint8_t *magic4, char *reason, size_t reasonlen,
+                                       long *failed_index) {
+    std::string r;
+    long fi = -1;
+    long n = static_cast<bcp::DeviceChain *>(h)->ConnectFile(data, len, magic4, r, fi);
+    if (reason && reasonlen) snprintf(reason, reasonlen, "%s", r.c_str());
+    if (failed_index) *failed_index = fi;
+    return n;
+}
+CHAIN_API void bcp_dchain_last_hash(void *h, uint8_t *out32) { memcpy(out32, static_cast<bcp::DeviceChain *>(h)->LastBlockHash(), 32); }
+CHAIN_API void bcp_dchain_phase_seconds(void *h, double *out6) {
+    for (int i = 0; i < 6; i++) out6[i] = static_cast<bcp::DeviceChain *>(h)->phase[i];
 }

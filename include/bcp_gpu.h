@@ -245,6 +245,45 @@ BCP_API int bcp_gpu_header_check_batch(int device, unsigned n, unsigned k, const
  * (the last four only to place the wide multiply against the other pipes). */
 BCP_API int bcp_gpu_measure_int_peak(int device, int which, double *ops_per_second);
 
+/* ---- Device-resident coin table (the device side): the working set of unspent outputs of a
+ *      reindex / initial block download kept in HBM, so that what ConnectBlock does per input and per output against its
+ *      coin view — "the spent coin exists and is unspent", fetch its amount and scriptPubKey, spend it, add the new coins,
+ *      the BIP30 overwrite test (src/validation.cpp:1975-1990, 2030-2100; UpdateCoins :1327-1347; src/coins.cpp:71-97) —
+ *      is a few kernels per block on one stream (bitcoincashplus_b200/csrc/bcp_utxo.cu).  Blocks are applied in call
+ *      order; block b+1 sees the table as block b left it, whether or not b's script checks have finished, and a block
+ *      whose checks fail is undone with bcp_gpu_utxo_rollback (newest first).  Sequence numbers are the caller's, start at
+ *      1 and must increase; at most 16 blocks may be applied and neither confirmed nor rolled back.
+ *   bcp_gpu_utxo_create     2^log2_slots slots of 128 bytes (keep the table under half full); arena_bytes for scriptPubKeys
+ *                           longer than 64 bytes (never freed).  NULL on failure.
+ *   bcp_gpu_utxo_add_coins  seeds coins: outpoints36[i] = txid || vout (LE), spk / spk_off / amounts as elsewhere
+ *   bcp_gpu_utxo_apply_block   ASYNCHRONOUS.  Inputs: the raw block and the arrays of bcp_block_index_full (non-coinbase
+ *                           inputs, all outputs).  Enqueues upload, txids + Merkle root, insertion of the outputs (an
+ *                           output a transaction of the SAME block spends must belong to an earlier transaction), the
+ *                           lookups + spends, and the copies of the results into the caller's HOST buffers, which must
+ *                           stay valid until bcp_gpu_utxo_wait(seq) returns (pinned memory keeps the call asynchronous):
+ *                           txids (optional), root32, mutated, and for the script checks amounts[nin], spk_off[nin+1],
+ *                           spk_cat (spk_cap bytes: the spent scriptPubKeys back to back)
+ *   bcp_gpu_utxo_wait       blocks until block seq's results are in the host buffers.  status8: [0] inputs whose coin is
+ *                           missing or already spent (bad-txns-inputs-missingorspent when non-zero), [1] the first such
+ *                           input, [2] outputs that overwrite a live coin (bad-txns-BIP30), [3] bytes of spk_cat used,
+ *                           [4] coins that did not fit the table, [5] long scripts that did not fit the arena
+ *   bcp_gpu_utxo_confirm    block seq is final (oldest first): its undo record is dropped, coins it spent may be overwritten
+ *   bcp_gpu_utxo_rollback   undoes block seq (newest first): its spent coins are unspent again, its new coins are gone
+ *   bcp_gpu_utxo_size       number of unspent coins (synchronises with the table's stream) */
+typedef struct bcp_utxo bcp_utxo;
+BCP_API bcp_utxo *bcp_gpu_utxo_create(int device, unsigned log2_slots, size_t arena_bytes);
+BCP_API void bcp_gpu_utxo_destroy(bcp_utxo *u);
+BCP_API int bcp_gpu_utxo_add_coins(bcp_utxo *u, const uint8_t *outpoints36, const uint8_t *spk, const uint32_t *spk_off,
+                                   const int64_t *amounts, size_t n);
+BCP_API long long bcp_gpu_utxo_size(bcp_utxo *u);
+BCP_API int bcp_gpu_utxo_apply_block(bcp_utxo *u, uint32_t seq, const uint8_t *blk, size_t len, const uint32_t *tx_off, size_t ntx,
+                                     const uint32_t *in_off, const uint32_t *in_tx, size_t nin, const uint32_t *out_off,
+                                     const uint32_t *out_tx, const uint32_t *out_n, size_t nout, uint8_t *txids, uint8_t *root32,
+                                     int *mutated, uint8_t *spk_cat, size_t spk_cap, uint32_t *spk_off, int64_t *amounts);
+BCP_API int bcp_gpu_utxo_wait(bcp_utxo *u, uint32_t seq, uint32_t status8[8]);
+BCP_API int bcp_gpu_utxo_confirm(bcp_utxo *u, uint32_t seq);
+BCP_API int bcp_gpu_utxo_rollback(bcp_utxo *u, uint32_t seq);
+
 #ifdef __cplusplus
 }
 #endif

@@ -1,0 +1,486 @@
+// include/compat/bcp_chain_gpu.h — block connector for a chain of blocks (reindex / initial block download,
+// LoadExternalBlockFile src/validation.cpp:4461-4560 feeding ConnectBlock :1868-2188) whose coin table lives in HBM
+// (bcp_gpu_utxo_*, bitcoincashplus_b200/csrc/bcp_utxo.cu) and whose blocks are spread over the GPUs of the box.
+// BASELINE.json configs[4]: "100-block synthetic chain reindex, signature batches sharded across 2/4/8 B200".
+//
+// bcp::ChainValidator (bcp_chain.h) walks an in-memory coin map on host threads and splits every block's inputs over the
+// devices; its connecting thread (~1 ms of table passes per 8 MB block) is the ceiling whatever the number of GPUs.  Here
+// nothing that is proportional to a block's size runs on the connecting thread:
+//
+//   scan threads     framing scan of the next blocks (bcp_block_index_full) + CheckBlock's context-free structure rules
+//   connecting thread  (the caller) per block: ONE asynchronous call, bcp_gpu_utxo_apply_block — the table's stream does
+//                    txids + Merkle root, inserts the outputs, looks up and spends the inputs in block order and returns the
+//                    spent (amount, scriptPubKey) arrays; stream order is the chain's order, so block b+1 is applied on top
+//                    of block b while b's script checks are still running
+//   check threads    one per (GPU, lane); block b belongs to thread b mod W: waits for b's spent-coin arrays, verifies the
+//                    header (Equihash + hash) and runs the script checks of the WHOLE block on its GPU
+//                    (bcp_gpu_block_scripts_p2pkh).  Blocks, not inputs, are what is dealt out to the devices: a block is
+//                    less than one wave of the point kernel on a B200, so splitting it further would not shorten it
+//   connecting thread  takes the verdicts in order: confirm, or — first failure — let the blocks applied after it finish,
+//                    roll them back newest first, then the failed block; the table is then exactly as before that block
+//
+// Reject reasons and their order are those of bcp::ChainValidator (the reference's strings).
+#ifndef BCP_COMPAT_CHAIN_GPU_H
+#define BCP_COMPAT_CHAIN_GPU_H
+
+#include <chrono>
+#include <condition_variable>
+#include <cstdint>
+#include <cstring>
+#include <memory>
+#include <mutex>
+#include <string>
+#include <thread>
+#include <vector>
+
+#include "../bcp_gpu.h"
+
+namespace bcp {
+
+class DeviceChain {
+public:
+    // devices: GPU ordinals; the coin table lives on devices[0].  lanes: check threads per GPU (1..3).
+    DeviceChain(const std::vector<int> &devices, uint32_t script_flags, unsigned eh_n, unsigned eh_k, unsigned log2_slots = 22,
+                int lanes = 2, int scan_threads = 4)
+        : devs(devices), flags(script_flags), ehN(eh_n), ehK(eh_k), log2Slots(log2_slots), lanes_(lanes < 1 ? 1 : lanes > 3 ? 3 : lanes),
+          nScan(scan_threads < 1 ? 1 : scan_threads) {}
+    ~DeviceChain() {
+        Stop();
+        for (Job &j : jobs) j.Free();
+        if (utxo) bcp_gpu_utxo_destroy(utxo);
+    }
+    DeviceChain(const DeviceChain &) = delete;
+    DeviceChain &operator=(const DeviceChain &) = delete;
+
+    bool Init(std::string &err) {
+        if (devs.empty()) { err = "no device"; return false; }
+        for (int d : devs)
+            for (int l = 0; l < lanes_; l++)
+                if (bcp_gpu_init(BCP_DEVICE_LANE(d & 0xFF, l)) != BCP_OK) { err = bcp_gpu_last_error(); return false; }
+        utxo = bcp_gpu_utxo_create(devs[0] & 0xFF, log2Slots, (size_t)64 << 20);
+        if (!utxo) { err = bcp_gpu_last_error(); return false; }
+        const size_t W = devs.size() * (size_t)lanes_;
+        inflightMax = W + 2 < 14 ? W + 2 : 14; /* the table keeps undo records of at most 16 pending blocks */
+        jobs.resize(inflightMax + (size_t)nScan + 2);
+        return true;
+    }
+    void AddCoin(const uint8_t txid[32], uint32_t vout, const uint8_t *spk, size_t len, int64_t amount) {
+        seedOp.insert(seedOp.end(), txid, txid + 32);
+        for (int k = 0; k < 4; k++) seedOp.push_back((uint8_t)(vout >> (8 * k)));
+        seedSpk.insert(seedSpk.end(), spk, spk + len);
+        seedOff.push_back((uint32_t)seedSpk.size());
+        seedAmt.push_back(amount);
+    }
+    long long UtxoSize() {
+        std::string e;
+        if (!FlushSeeds(e)) return -1;
+        return bcp_gpu_utxo_size(utxo);
+    }
+    size_t InputsChecked() const { return nInputs; }
+    const uint8_t *LastBlockHash() const { return lastHash; }
+
+    // seconds, summed over blocks: [0] connecting thread inside bcp_gpu_utxo_apply_block, [1] connecting thread waiting
+    // (for a scan, a free slot or a verdict), [2] check threads waiting for the spent-coin arrays, [3] check threads in
+    // the header check, [4] check threads in the script checks, [5] scan threads
+    double phase[6] = {0, 0, 0, 0, 0, 0};
+
+    bool ConnectBlock(const uint8_t *blk, size_t len, std::string &reason) {
+        std::vector<std::pair<const uint8_t *, size_t>> one{{blk, len}};
+        long failed = -1;
+        return Run(one, reason, failed) == 1;
+    }
+    // blk*.dat framing (src/validation.cpp:4486-4516): [magic 4][size u32 LE][block] ...; returns the number of blocks
+    // connected, stops at the first failure (reason set, failed_index = its ordinal, table as before that block).
+    long ConnectFile(const uint8_t *data, size_t len, const uint8_t magic[4], std::string &reason, long &failed_index) {
+        std::vector<std::pair<const uint8_t *, size_t>> blocks;
+        size_t pos = 0;
+        while (pos + 8 <= len) {
+            if (memcmp(data + pos, magic, 4) != 0) { pos++; continue; } // resynchronise on the magic like :4489-4498
+            uint32_t sz;
+            memcpy(&sz, data + pos + 4, 4);
+            if (pos + 8 + sz > len) break;
+            blocks.emplace_back(data + pos + 8, (size_t)sz);
+            pos += 8 + (size_t)sz;
+        }
+        return Run(blocks, reason, failed_index);
+    }
+
+private:
+    typedef std::chrono::steady_clock Clock;
+    static double Secs(Clock::time_point a, Clock::time_point b) { return std::chrono::duration<double>(b - a).count(); }
+
+    template <class T> struct Pinned { // host arrays the device copies from / into: pinned, grow-only, never value-initialised
+        T *p = nullptr;
+        size_t cap = 0;
+        void need(size_t n) {
+            if (cap >= n) return;
+            if (p) bcp_gpu_host_free(p);
+            p = static_cast<T *>(bcp_gpu_host_alloc((n + n / 4 + 64) * sizeof(T)));
+            cap = p ? n + n / 4 + 64 : 0;
+        }
+        void release() {
+            if (p) bcp_gpu_host_free(p);
+            p = nullptr;
+            cap = 0;
+        }
+    };
+    enum State { FREE = 0, SCANNING, SCANNED, APPLIED, DONE };
+    struct Job {
+        State state = FREE;
+        long index = -1; // ordinal of the block in this run
+        const uint8_t *blk = nullptr;
+        size_t len = 0;
+        Pinned<uint32_t> tx_off, tx_out_off, in_off, in_tx, in_n, out_off, out_tx, out_n, spk_off;
+        Pinned<int64_t> amounts;
+        Pinned<uint8_t> spk_cat, errs, small; // small: root[32] | mutated(int) at 32
+        long ntx = 0, nin = -1, nout = 0;
+        const char *structErr = nullptr;
+        uint32_t seq = 0;
+        bool ok = false;
+        std::string reason;
+        uint8_t hash[32];
+        void Free() {
+            tx_off.release(); tx_out_off.release(); in_off.release(); in_tx.release(); in_n.release(); out_off.release();
+            out_tx.release(); out_n.release(); spk_off.release(); amounts.release(); spk_cat.release(); errs.release(); small.release();
+        }
+    };
+
+    bool FlushSeeds(std::string &err) {
+        if (seedAmt.empty()) return true;
+        std::vector<uint32_t> off(1, 0);
+        off.insert(off.end(), seedOff.begin(), seedOff.end());
+        if (seedSpk.empty()) seedSpk.push_back(0);
+        const int rc = bcp_gpu_utxo_add_coins(utxo, seedOp.data(), seedSpk.data(), off.data(), seedAmt.data(), seedAmt.size());
+        seedOp.clear(); seedSpk.clear(); seedOff.clear(); seedAmt.clear();
+        if (rc != BCP_OK) { err = bcp_gpu_last_error(); return false; }
+        return true;
+    }
+
+    // framing scan + structure rules of one block into its job (scan thread)
+    void Scan(Job &j) {
+        const uint8_t *b = j.blk;
+        const size_t l = j.len;
+        size_t max_tx = l / 60 + 2, max_in = l / 41 + 2, max_out = l / 34 + 2; /* outputs: first guess, P2PKH-sized */
+        for (int attempt = 0; attempt < 2; attempt++) {
+            j.tx_off.need(max_tx + 1); j.tx_out_off.need(max_tx + 1);
+            j.in_off.need(max_in); j.in_tx.need(max_in); j.in_n.need(max_in);
+            j.out_off.need(max_out); j.out_tx.need(max_out); j.out_n.need(max_out);
+            j.ntx = j.nout = 0;
+            j.nin = bcp_block_index_full(b, l, 0, j.tx_off.p, j.tx_out_off.p, max_tx, j.in_off.p, j.in_tx.p, j.in_n.p, max_in, &j.ntx,
+                                         j.out_off.p, j.out_tx.p, j.out_n.p, max_out, &j.nout, nullptr);
+            if (j.nin != -2) break;
+            max_out = l / 9 + 2; /* the worst case a block of this size can hold */
+        }
+        j.structErr = nullptr;
+        if (j.nin >= 0 && j.ntx >= 1) j.structErr = CheckStructure(j, b);
+        if (j.nin >= 0) {
+            j.amounts.need((size_t)j.nin + 1); j.spk_off.need((size_t)j.nin + 2); j.errs.need((size_t)j.nin + 1);
+            j.spk_cat.need((size_t)j.nin * 64 + 4096);
+        }
+        j.small.need(64);
+    }
+    static uint64_t ReadCompact(const uint8_t *p, size_t &pos) { // already validated by the framing scan
+        uint8_t c = p[pos++];
+        if (c < 253) return c;
+        int nb = c == 253 ? 2 : c == 254 ? 4 : 8;
+        uint64_t v = 0;
+        for (int i = 0; i < nb; i++) v |= (uint64_t)p[pos + i] << (8 * i);
+        pos += nb;
+        return v;
+    }
+    // CheckBlock's context-free transaction rules from the framing arrays (src/validation.cpp:3255-3330 calling CheckCoinbase
+    // :531-549 and CheckRegularTransaction :551-570, both over CheckTransactionCommon :476-529), in the reference's order
+    static const char *CheckStructure(const Job &j, const uint8_t *b) {
+        static const int64_t MAX_MONEY_SAT = 21000000ll * 100000000ll; // src/amount.h:127
+        size_t o = 0, i = 0;
+        for (long t = 0; t < j.ntx; t++) {
+            size_t pos = (size_t)j.tx_off.p[t] + 4;
+            const uint64_t n_in = ReadCompact(b, pos);
+            bool cb = false;
+            uint64_t cbScriptLen = 0;
+            if (n_in == 1) {
+                cb = true;
+                for (int k = 0; k < 32; k++) cb = cb && b[pos + k] == 0;
+                for (int k = 32; k < 36; k++) cb = cb && b[pos + k] == 0xFF;
+                size_t q = pos + 36;
+                cbScriptLen = ReadCompact(b, q);
+            }
+            size_t po = j.tx_out_off.p[t];
+            const uint64_t n_out = ReadCompact(b, po);
+            const char *e = nullptr;
+            if (t == 0 && !cb) e = "bad-cb-missing";
+            else if (t > 0 && cb) e = "bad-tx-coinbase";
+            else if (n_in == 0) e = "bad-txns-vin-empty";
+            else if (n_out == 0) e = "bad-txns-vout-empty";
+            else if (j.tx_off.p[t + 1] - j.tx_off.p[t] > 1000000u) e = "bad-txns-oversize"; // MAX_TX_SIZE, consensus.h:14
+            int64_t total = 0;
+            for (; o < (size_t)j.nout && j.out_tx.p[o] == (uint32_t)t; o++) {
+                if (e) continue;
+                int64_t v;
+                memcpy(&v, b + j.out_off.p[o], 8);
+                if (v < 0) e = "bad-txns-vout-negative";
+                else if (v > MAX_MONEY_SAT) e = "bad-txns-vout-toolarge";
+                else if ((total += v) > MAX_MONEY_SAT) e = "bad-txns-txouttotal-toolarge";
+            }
+            if (!e && t == 0 && (cbScriptLen < 2 || cbScriptLen > 100)) e = "bad-cb-length";
+            for (; i < (size_t)j.nin && j.in_tx.p[i] == (uint32_t)t; i++) {
+                if (e) continue;
+                const uint8_t *op = b + j.in_off.p[i];
+                bool null = true;
+                for (int k = 0; k < 32; k++) null = null && op[k] == 0;
+                for (int k = 32; k < 36; k++) null = null && op[k] == 0xFF;
+                if (null) e = "bad-txns-prevout-null";
+            }
+            if (e) return e;
+        }
+        return nullptr;
+    }
+
+    // everything a check thread does for one applied block
+    void Check(Job &j, int dev) {
+        auto t0 = Clock::now();
+        uint32_t st[8] = {0};
+        const int rcw = bcp_gpu_utxo_wait(utxo, j.seq, st);
+        auto t1 = Clock::now();
+        j.ok = false;
+        // header first, like CheckBlockHeader before anything of the body (src/validation.cpp:3202-3220)
+        const size_t soln = ehN ? ((size_t)1 << ehK) * (ehN / (ehK + 1) + 1) / 8 : 0;
+        const size_t hdr_len = 140 + (soln < 253 ? 1 : 3) + soln;
+        uint8_t eqOk = 1;
+        int rcEq = BCP_OK;
+        if (ehN) {
+            rcEq = bcp_gpu_equihash_verify_batch(dev, ehN, ehK, j.blk, hdr_len, hdr_len, 1, &eqOk, j.hash);
+            if (rcEq != BCP_OK) j.reason = std::string("device-error: ") + bcp_gpu_last_error();
+        }
+        auto t2 = Clock::now();
+        double tScripts = 0;
+        if (rcEq != BCP_OK) {
+        } else if (!eqOk) {
+            j.reason = "invalid-solution"; // CheckEquihashSolution (src/pow.cpp:298-323)
+        } else if (rcw != BCP_OK) {
+            j.reason = std::string("device-error: ") + bcp_gpu_last_error();
+        } else if (memcmp(j.small.p, j.blk + 36, 32) != 0) {
+            j.reason = "bad-txnmrklroot";
+        } else if (*reinterpret_cast<const int *>(j.small.p + 32)) {
+            j.reason = "bad-txns-duplicate";
+        } else if (j.structErr) {
+            j.reason = j.structErr;
+        } else if (st[4] || st[5]) {
+            j.reason = "device-error: coin table full";
+        } else if (st[2]) {
+            j.reason = "bad-txns-BIP30"; // src/validation.cpp:1975-1990
+        } else if (st[0]) {
+            j.reason = "bad-txns-inputs-missingorspent";
+        } else {
+            int all = 1;
+            int rc = BCP_OK;
+            if (j.nin > 0)
+                rc = bcp_gpu_block_scripts_p2pkh(dev, j.blk, j.len, j.tx_off.p, (size_t)j.ntx, j.in_off.p, j.in_tx.p, j.in_n.p, (size_t)j.nin,
+                                                 j.spk_cat.p, j.spk_off.p, j.amounts.p, flags, j.errs.p, &all);
+            tScripts = Secs(t2, Clock::now());
+            if (rc != BCP_OK) {
+                j.reason = std::string("device-error: ") + bcp_gpu_last_error();
+            } else {
+                j.ok = true;
+                for (long k = 0; k < j.nin; k++) {
+                    const uint8_t e = j.errs.p[k];
+                    if (e == 0) continue;
+                    j.ok = false;
+                    if (e == 255) j.reason = "script-not-in-fast-path (input " + std::to_string(k) + ")";
+                    else j.reason = "blk-bad-inputs (input " + std::to_string(k) + ", script error " + std::to_string(e) + ")"; // :2124-2128
+                    break;
+                }
+            }
+        }
+        std::lock_guard<std::mutex> l(mu);
+        phase[2] += Secs(t0, t1);
+        phase[3] += Secs(t1, t2);
+        phase[4] += tScripts;
+    }
+
+    void Stop() {
+        {
+            std::lock_guard<std::mutex> l(mu);
+            quit = true;
+        }
+        cv.notify_all();
+        for (auto &t : threads) t.join();
+        threads.clear();
+        quit = false;
+    }
+
+    long Run(const std::vector<std::pair<const uint8_t *, size_t>> &blocks, std::string &reason, long &failed_index) {
+        failed_index = -1;
+        if (!FlushSeeds(reason)) return 0;
+        const long n = (long)blocks.size();
+        if (n == 0) return 0;
+        const size_t R = jobs.size(), W = devs.size() * (size_t)lanes_;
+        for (Job &j : jobs) { j.state = FREE; j.index = -1; }
+        long nextScan = 0;     // next block a scan thread takes
+        long nextApply = 0;    // next block the connecting thread applies
+        long nextCommit = 0;   // next verdict the connecting thread takes
+        long stopAt = n;       // blocks at or beyond this ordinal are not started (set on the first failure)
+        auto jobOf = [&](long b) -> Job & { return jobs[(size_t)b % R]; };
+        // scan threads: block b may be scanned once its ring slot is free (its previous user was committed)
+        for (int s = 0; s < nScan; s++)
+            threads.emplace_back([&] {
+                for (;;) {
+                    long b;
+                    {
+                        std::unique_lock<std::mutex> l(mu);
+                        cv.wait(l, [&] { return quit || (nextScan < stopAt && nextScan < nextCommit + (long)R && jobOf(nextScan).state == FREE); });
+                        if (quit) return;
+                        b = nextScan++;
+                        Job &j = jobOf(b);
+                        j.state = SCANNING;
+                        j.index = b;
+                        j.blk = blocks[(size_t)b].first;
+                        j.len = blocks[(size_t)b].second;
+                    }
+                    auto t0 = Clock::now();
+                    Scan(jobOf(b));
+                    {
+                        std::lock_guard<std::mutex> l(mu);
+                        jobOf(b).state = SCANNED;
+                        phase[5] += Secs(t0, Clock::now());
+                    }
+                    cv.notify_all();
+                }
+            });
+        // check threads: thread w owns lane w / G of device w % G and the blocks b with b % W == w
+        for (size_t w = 0; w < W; w++)
+            threads.emplace_back([&, w] {
+                const int dev = BCP_DEVICE_LANE(devs[w % devs.size()] & 0xFF, (int)(w / devs.size()));
+                for (long b = (long)w;; b += (long)W) {
+                    {
+                        std::unique_lock<std::mutex> l(mu);
+                        cv.wait(l, [&] { return quit || (jobOf(b).index == b && jobOf(b).state == APPLIED); });
+                        if (quit) return;
+                    }
+                    Check(jobOf(b), dev);
+                    {
+                        std::lock_guard<std::mutex> l(mu);
+                        jobOf(b).state = DONE;
+                    }
+                    cv.notify_all();
+                }
+            });
+        // the connecting thread
+        long connected = 0;
+        std::string devErr;
+        for (;;) {
+            long b = -1;
+            bool commit = false;
+            auto tw0 = Clock::now();
+            {
+                std::unique_lock<std::mutex> l(mu);
+                cv.wait(l, [&] {
+                    if (nextCommit < nextApply && jobOf(nextCommit).state == DONE) return true;                      // a verdict is in
+                    if (nextApply < stopAt && nextApply - nextCommit < (long)inflightMax && jobOf(nextApply).index == nextApply &&
+                        jobOf(nextApply).state == SCANNED) return true;                                               // a block can go
+                    return nextCommit >= stopAt && nextCommit >= nextApply;                                           // nothing left
+                });
+                phase[1] += Secs(tw0, Clock::now());
+                if (nextCommit < nextApply && jobOf(nextCommit).state == DONE) { commit = true; b = nextCommit; }
+                else if (nextApply < stopAt && nextApply - nextCommit < (long)inflightMax && jobOf(nextApply).index == nextApply &&
+                         jobOf(nextApply).state == SCANNED) b = nextApply;
+                else break;
+            }
+            Job &j = jobOf(b);
+            if (!commit) {
+                j.seq = ++seqCounter;
+                if (j.nin < 0 || j.ntx < 1) { // framing broken: nothing to apply; the header still decides the reason
+                    const size_t soln = ehN ? ((size_t)1 << ehK) * (ehN / (ehK + 1) + 1) / 8 : 0;
+                    const size_t hdr_len = 140 + (soln < 253 ? 1 : 3) + soln;
+                    j.ok = false;
+                    j.reason = (ehN && j.len < hdr_len) ? "bad-blk-length" : "bad-blk-framing";
+                    if (ehN && j.len >= hdr_len) {
+                        uint8_t eqOk = 1;
+                        if (bcp_gpu_equihash_verify_batch(BCP_DEVICE_LANE(devs[0] & 0xFF, 0), ehN, ehK, j.blk, hdr_len, hdr_len, 1, &eqOk, j.hash) == BCP_OK && !eqOk)
+                            j.reason = "invalid-solution";
+                    }
+                    j.seq = 0; // never applied
+                    --seqCounter;
+                    std::lock_guard<std::mutex> l(mu);
+                    j.state = DONE;
+                    nextApply++;
+                    stopAt = b + 1 < stopAt ? b + 1 : stopAt;
+                    cv.notify_all();
+                    continue;
+                }
+                auto ta0 = Clock::now();
+                const int rc = bcp_gpu_utxo_apply_block(utxo, j.seq, j.blk, j.len, j.tx_off.p, (size_t)j.ntx, j.in_off.p, j.in_tx.p, (size_t)j.nin,
+                                                        j.out_off.p, j.out_tx.p, j.out_n.p, (size_t)j.nout, nullptr, j.small.p,
+                                                        reinterpret_cast<int *>(j.small.p + 32), j.spk_cat.p, j.spk_cat.cap, j.spk_off.p,
+                                                        j.amounts.p);
+                std::lock_guard<std::mutex> l(mu);
+                phase[0] += Secs(ta0, Clock::now());
+                nextApply++;
+                if (rc != BCP_OK) { // could not even be enqueued: treat like a failed block that was never applied
+                    j.ok = false;
+                    j.reason = std::string("device-error: ") + bcp_gpu_last_error();
+                    j.seq = 0;
+                    --seqCounter;
+                    j.state = DONE;
+                    stopAt = b + 1 < stopAt ? b + 1 : stopAt;
+                } else {
+                    j.state = APPLIED;
+                }
+                cv.notify_all();
+                continue;
+            }
+            // a verdict, in chain order
+            if (j.ok) {
+                bcp_gpu_utxo_confirm(utxo, j.seq);
+                nInputs += (size_t)j.nin;
+                memcpy(lastHash, j.hash, 32);
+                connected++;
+                std::lock_guard<std::mutex> l(mu);
+                j.state = FREE;
+                j.index = -1;
+                nextCommit++;
+                cv.notify_all();
+                continue;
+            }
+            // First failure: no further block is started; the ones applied after it finish their checks (their verdicts no
+            // longer matter), then everything is undone newest first.
+            reason = j.reason;
+            failed_index = b;
+            {
+                std::unique_lock<std::mutex> l(mu);
+                stopAt = b + 1 < stopAt ? b + 1 : stopAt;
+                cv.wait(l, [&] {
+                    for (long k = b + 1; k < nextApply; k++)
+                        if (jobOf(k).state != DONE) return false;
+                    return true;
+                });
+            }
+            for (long k = nextApply - 1; k >= b; k--)
+                if (jobOf(k).seq) bcp_gpu_utxo_rollback(utxo, jobOf(k).seq);
+            break;
+        }
+        Stop();
+        return connected;
+    }
+
+    std::vector<int> devs;
+    uint32_t flags;
+    unsigned ehN, ehK, log2Slots;
+    int lanes_, nScan;
+    bcp_utxo *utxo = nullptr;
+    size_t inflightMax = 4;
+    std::vector<Job> jobs;
+    std::vector<std::thread> threads;
+    std::mutex mu;
+    std::condition_variable cv;
+    bool quit = false;
+    uint32_t seqCounter = 0;
+    std::vector<uint8_t> seedOp, seedSpk;
+    std::vector<uint32_t> seedOff;
+    std::vector<int64_t> seedAmt;
+    uint8_t lastHash[32] = {0};
+    size_t nInputs = 0;
+};
+
+} // namespace bcp
+#endif

@@ -516,6 +516,27 @@ def synthetic_chain_fast(nblocks=100, ntx=41650, nkeys=4096, equihash=True):
         yield hdr + _compact(ntx + 1) + cb + body
 
 
+def damage_chain_block(blk, b, input_no):
+    """blk = block number b of synthetic_chain_fast.  Returns a copy whose input `input_no` carries a broken signature (one
+    bit of r flipped: strict DER still holds, the signature no longer verifies) under a header that is consistent again:
+    Merkle root recomputed over the changed transactions, Equihash (48,5) solved anew."""
+    o = po.oracle()
+    n, off = o.block_index(blk, False)
+    t = input_no + 1  # transaction 0 is the coinbase, every other transaction has one input
+    body = bytearray(blk)
+    body[off[t] + 4 + 1 + 36 + 1 + 1 + 12] ^= 0x04  # version | nin | outpoint | script length | push | 30 len 02 lenR R[8]
+    body = bytes(body)
+    _, _, root, _ = o.block_txids(body, False, max_tx=n + 8)
+    txs = body[177:]
+    nonce = 1 << 18
+    while True:
+        hdr = synthetic_header(height=700000 + b, merkle_root=root, nonce_tag=(b << 20) | nonce, n=48, k=5)
+        sols = equihash_solve_48_5(hdr[:140])
+        if sols:
+            return hdr[:140] + _compact(36) + sols[0] + txs
+        nonce += 1
+
+
 def chain_seed_arrays(ntx, nkeys):
     prev_txid = np.zeros((ntx, 32), dtype=np.uint8)
     for j in range(ntx):

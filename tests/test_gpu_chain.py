@@ -13,29 +13,47 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 MAGIC = bytes.fromhex("e48f1d1c")
 
 
-def chain_lib(path=None):
+def chain_lib(path=None, impl="host"):
+    """ctypes face of libbcp_chain.so.  impl = "host": bcp::ChainValidator (coin map on host threads); "device":
+    bcp::DeviceChain (coin table in HBM, whole blocks dealt out to the GPUs) behind the same function names."""
     L = C.CDLL(path or os.path.join(ROOT, "bitcoincashplus_b200", "libbcp_chain.so"))
     L.bcp_chain_new.restype = C.c_void_p
     L.bcp_chain_new.argtypes = [C.POINTER(C.c_int), C.c_int, C.c_uint32, C.c_uint, C.c_uint, C.c_char_p, C.c_size_t]
     L.bcp_chain_new_threads.restype = C.c_void_p
     L.bcp_chain_new_threads.argtypes = [C.POINTER(C.c_int), C.c_int, C.c_uint32, C.c_uint, C.c_uint, C.c_int, C.c_char_p, C.c_size_t]
-    L.bcp_chain_free.argtypes = [C.c_void_p]
-    L.bcp_chain_add_coin.argtypes = [C.c_void_p, C.c_char_p, C.c_uint32, C.c_char_p, C.c_size_t, C.c_int64]
-    L.bcp_chain_utxo_size.restype = C.c_size_t
-    L.bcp_chain_utxo_size.argtypes = [C.c_void_p]
-    L.bcp_chain_inputs_checked.restype = C.c_size_t
-    L.bcp_chain_inputs_checked.argtypes = [C.c_void_p]
-    L.bcp_chain_connect_block.argtypes = [C.c_void_p, C.c_char_p, C.c_size_t, C.c_char_p, C.c_size_t]
-    L.bcp_chain_connect_file.restype = C.c_long
-    L.bcp_chain_connect_file.argtypes = [C.c_void_p, C.c_char_p, C.c_size_t, C.c_char_p, C.c_char_p, C.c_size_t, C.POINTER(C.c_long)]
-    L.bcp_chain_last_hash.argtypes = [C.c_void_p, C.c_char_p]
-    return L
+    L.bcp_dchain_new.restype = C.c_void_p
+    L.bcp_dchain_new.argtypes = [C.POINTER(C.c_int), C.c_int, C.c_uint32, C.c_uint, C.c_uint, C.c_uint, C.c_int, C.c_int, C.c_char_p, C.c_size_t]
+    for pre in ("bcp_chain_", "bcp_dchain_"):
+        getattr(L, pre + "free").argtypes = [C.c_void_p]
+        getattr(L, pre + "add_coin").argtypes = [C.c_void_p, C.c_char_p, C.c_uint32, C.c_char_p, C.c_size_t, C.c_int64]
+        getattr(L, pre + "utxo_size").restype = C.c_size_t
+        getattr(L, pre + "utxo_size").argtypes = [C.c_void_p]
+        getattr(L, pre + "inputs_checked").restype = C.c_size_t
+        getattr(L, pre + "inputs_checked").argtypes = [C.c_void_p]
+        getattr(L, pre + "connect_block").argtypes = [C.c_void_p, C.c_char_p, C.c_size_t, C.c_char_p, C.c_size_t]
+        getattr(L, pre + "connect_file").restype = C.c_long
+        getattr(L, pre + "connect_file").argtypes = [C.c_void_p, C.c_char_p, C.c_size_t, C.c_char_p, C.c_char_p, C.c_size_t, C.POINTER(C.c_long)]
+        getattr(L, pre + "last_hash").argtypes = [C.c_void_p, C.c_char_p]
+    if impl == "host":
+        L.impl = "host"
+        return L
+
+    class DeviceFace:  # the DeviceChain entry points under the names the tests use
+        impl = "device"
+        bcp_dchain_new = L.bcp_dchain_new
+
+    for name in ("free", "add_coin", "utxo_size", "inputs_checked", "connect_block", "connect_file", "last_hash"):
+        setattr(DeviceFace, "bcp_chain_" + name, staticmethod(getattr(L, "bcp_dchain_" + name)))
+    return DeviceFace
 
 
 def new_chain(L, seeds, devices=(0,), eh=(48, 5), walk_threads=None):
     devs = (C.c_int * len(devices))(*devices)
     err = C.create_string_buffer(256)
-    if walk_threads is None:
+    if L.impl == "device":  # walk_threads has no meaning there: vary the check threads per GPU instead
+        lanes = 2 if walk_threads is None else 1 + (walk_threads > 1) + (walk_threads > 4)
+        h = L.bcp_dchain_new(devs, len(devices), synth.POSTFORK_FLAGS, eh[0], eh[1], 12, lanes, 2, err, 256)
+    elif walk_threads is None:
         h = L.bcp_chain_new(devs, len(devices), synth.POSTFORK_FLAGS, eh[0], eh[1], err, 256)
     else:
         h = L.bcp_chain_new_threads(devs, len(devices), synth.POSTFORK_FLAGS, eh[0], eh[1], walk_threads, err, 256)
@@ -45,8 +63,13 @@ def new_chain(L, seeds, devices=(0,), eh=(48, 5), walk_threads=None):
     return h
 
 
-def test_chain_connects_and_tracks_the_utxo_set(oracle):
-    L = chain_lib()
+@pytest.fixture(params=["host", "device"])
+def impl(request):
+    return request.param
+
+
+def test_chain_connects_and_tracks_the_utxo_set(oracle, impl):
+    L = chain_lib(impl=impl)
     blocks, seeds, prevs = synth.synthetic_chain(8, 30)
     # the generator's own claim, checked with the oracle: every block's inputs verify against the coins they spend
     for b, (spk, amt) in zip(blocks, prevs):
@@ -71,8 +94,8 @@ def test_chain_connects_and_tracks_the_utxo_set(oracle):
                                          ("double_spend", b"bad-txns-inputs-missingorspent"),
                                          ("missing_input", b"bad-txns-inputs-missingorspent"),
                                          ("bad_merkle", b"bad-txnmrklroot"), ("bad_equihash", b"invalid-solution")])
-def test_chain_rejects_the_damaged_block_with_the_reference_reason(kind, expect):
-    L = chain_lib()
+def test_chain_rejects_the_damaged_block_with_the_reference_reason(kind, expect, impl):
+    L = chain_lib(impl=impl)
     blocks, seeds, _ = synth.synthetic_chain(5, 12, corrupt=(3, kind))
     h = new_chain(L, seeds)
     data = b"".join(MAGIC + len(b).to_bytes(4, "little") + b for b in blocks)
@@ -87,11 +110,11 @@ def test_chain_rejects_the_damaged_block_with_the_reference_reason(kind, expect)
 
 
 @pytest.mark.parametrize("kind", sorted(synth.STRUCTURE_KINDS))
-def test_chain_applies_checkblock_structure_rules(kind):
+def test_chain_applies_checkblock_structure_rules(kind, impl):
     """CheckBlock's context-free transaction rules (src/validation.cpp:3255-3330 -> CheckCoinbase / CheckRegularTransaction
     :476-570): a second coinbase-shaped transaction, a missing coinbase, null prevouts, empty input / output lists and
     out-of-range amounts are rejected with the reference's reason and leave the UTXO set untouched."""
-    L = chain_lib()
+    L = chain_lib(impl=impl)
     blocks, seeds, _ = synth.synthetic_chain(3, 10, corrupt=(1, kind))
     good, _, _ = synth.synthetic_chain(3, 10)
     reason = C.create_string_buffer(256)
@@ -132,12 +155,12 @@ def test_chain_in_block_index_survives_txid_prefix_collisions(oracle):
         L.bcp_chain_free(h)
 
 
-def test_chain_shards_inputs_over_two_devices_when_present():
+def test_chain_shards_inputs_over_two_devices_when_present(impl):
     import bitcoincashplus_b200 as bcp
 
     if bcp.device_count() < 2:
         pytest.skip("needs 2 GPUs (run with gpurun --gpus 2)")
-    L = chain_lib()
+    L = chain_lib(impl=impl)
     blocks, seeds, _ = synth.synthetic_chain(4, 50, corrupt=(2, "bad_sig"))
     h = new_chain(L, seeds, devices=(0, 1))
     reason = C.create_string_buffer(256)
@@ -169,11 +192,43 @@ def test_chain_shards_inputs_over_two_lane_pairs_of_one_gpu():
         L.bcp_chain_free(h)
 
 
-def test_chain_in_block_spends_and_their_failure_modes(oracle):
+def test_device_chain_deals_blocks_over_several_check_threads_and_unwinds_a_failure_in_the_middle():
+    """bcp::DeviceChain with GPU 0 listed twice (two "devices" x two lanes = four check threads, six blocks in flight): a
+    long chain connects in order; with a bad signature in block 5 of 12 the blocks applied on top of it — already in the
+    table when its verdict arrives — are rolled back newest first, the table is exactly as after block 4 (the undamaged
+    rest of the chain connects from there), and the first failure is the one reported even though later blocks finish
+    their checks earlier or later than it."""
+    L = chain_lib(impl="device")
+    good, seeds, _ = synth.synthetic_chain(12, 30, inblock=(3, 4, 11))
+    bad, _, _ = synth.synthetic_chain(12, 30, inblock=(3, 4, 11), corrupt=(5, "bad_sig@17"))
+    reason = C.create_string_buffer(256)
+    failed = C.c_long(-2)
+    frame = lambda blocks: b"".join(MAGIC + len(b).to_bytes(4, "little") + b for b in blocks)
+    h = new_chain(L, seeds, devices=(0, 0))
+    data = frame(good)
+    assert L.bcp_chain_connect_file(h, data, len(data), MAGIC, reason, 256, C.byref(failed)) == 12, reason.value
+    assert failed.value == -1 and L.bcp_chain_utxo_size(h) == 30 + 12 and L.bcp_chain_inputs_checked(h) == 12 * 30
+    L.bcp_chain_free(h)
+    h = new_chain(L, seeds, devices=(0, 0))
+    data = frame(bad)
+    assert L.bcp_chain_connect_file(h, data, len(data), MAGIC, reason, 256, C.byref(failed)) == 5
+    assert failed.value == 5 and reason.value == b"blk-bad-inputs (input 17, script error 31)", reason.value
+    assert L.bcp_chain_utxo_size(h) == 30 + 5
+    data = frame(good[5:])
+    assert L.bcp_chain_connect_file(h, data, len(data), MAGIC, reason, 256, C.byref(failed)) == 7, reason.value
+    assert L.bcp_chain_utxo_size(h) == 30 + 12
+    out = C.create_string_buffer(32)
+    L.bcp_chain_last_hash(h, out)
+    from oracle import pyoracle as po
+    assert out.raw == po.oracle().header_hash(good[-1][:177])
+    L.bcp_chain_free(h)
+
+
+def test_chain_in_block_spends_and_their_failure_modes(oracle, impl):
     """Transactions that spend outputs created earlier in the SAME block (chains of them), over several blocks; then the
     two ways this can go wrong: spending an output of a LATER transaction, and spending an in-block output twice.  After a
     rejection the UTXO set is exactly what it was, so the undamaged version of the same block still connects."""
-    L = chain_lib()
+    L = chain_lib(impl=impl)
     inb = (2, 7, 8, 9, 15)
     blocks, seeds, prevs = synth.synthetic_chain(4, 20, inblock=inb)
     for b, (spk, amt) in zip(blocks, prevs):
@@ -201,13 +256,14 @@ def test_chain_in_block_spends_and_their_failure_modes(oracle):
             L.bcp_chain_free(h)
 
 
-def test_chain_rollback_restores_coins_with_long_scripts():
+def test_chain_rollback_restores_coins_with_long_scripts(impl):
     """Coins whose scriptPubKey does not fit the staging slot (> 64 bytes) take the one-thread path; a block spending one
     is refused by the P2PKH fast path (script-not-in-fast-path), and the rollback must put every coin back, long ones
-    included — shown by the same block failing the same way again and by the count."""
-    L = chain_lib()
+    included — shown by the same block failing the same way again and by the count.  (In the device table such scripts
+    live in the arena behind the 64-byte slots.)"""
+    L = chain_lib(impl=impl)
     blocks, seeds, _ = synth.synthetic_chain(2, 16)
-    long_spk = bytes([0x6a, 0x4c, 100]) + bytes(100)  # OP_RETURN-style, 103 bytes
+    long_spk = bytes([0x51, 0x4c, 100]) + bytes(100)  # 103 bytes, not the P2PKH shape
     seeds = list(seeds)
     seeds[4] = (seeds[4][0], seeds[4][1], long_spk, seeds[4][3])
     seeds[9] = (seeds[9][0], seeds[9][1], long_spk + b"\x00", seeds[9][3])

@@ -1,5 +1,6 @@
-"""-m gpu: randomized differential test of the host block connector (include/compat/bcp_chain.h: sharded UTXO table,
-worker team, two blocks in flight, scan-ahead, rollback) against a small Python model of ConnectBlock's coin rules
+"""-m gpu: randomized differential test of both block connectors (include/compat/bcp_chain.h: sharded UTXO table on the
+host, worker team, two blocks in flight, scan-ahead, rollback; include/compat/bcp_chain_gpu.h: coin table in HBM, blocks
+dealt out to check threads, several blocks in flight, rollback by kernel) against a small Python model of ConnectBlock's coin rules
 (dict of coins; per transaction: every input's coin must exist — coins created earlier in the same block included —
 and is spent; then the outputs are added) with the oracle deciding the script checks."""
 import ctypes as C
@@ -56,10 +57,11 @@ def model_connect(coins, blk, oracle):
     return True, b""
 
 
+@pytest.mark.parametrize("impl", ["host", "device"])
 @pytest.mark.parametrize("seed", range(12))
-def test_random_chains_against_the_python_model(oracle, seed):
+def test_random_chains_against_the_python_model(oracle, seed, impl):
     rng = random.Random(100 + seed)
-    L = chain_lib()
+    L = chain_lib(impl=impl)
     nblocks, ntx = 6, 26
     inblock = tuple(sorted(rng.sample(range(1, ntx), rng.randrange(0, 9))))
     kinds = [None, "bad_sig", "double_spend", "missing_input", "bad_merkle", "inblock_reversed", "inblock_double"]
