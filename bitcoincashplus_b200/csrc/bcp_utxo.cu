@@ -121,7 +121,7 @@ __device__ uint32_t utxo_put(const utxo_dev &T, const uint32_t *key, const uint8
         *reinterpret_cast<volatile uint32_t *>(&d->state) = UTXO_LIVE;
         return take;
     }
-    atomicAdd(&status[ST_TABLE_FULL], 1u);
+    atomicAdd(&status[ST_TABLE_FULL], 1u); /* every slot looked at, none free (tombstones of pending blocks do not count) */
     return UTXO_NONE;
 }
 
@@ -295,6 +295,25 @@ __global__ void __launch_bounds__(128) k_utxo_undo(utxo_dev T, uint32_t seq, con
     }
 }
 
+// Run when a block becomes final, over the coins it spent.  Tombstones only exist so that probe runs of other keys are
+// not cut; one whose NEXT slot is empty ends a run and cuts nothing, so it is emptied — and then the final tombstones
+// before it, which now end the run in turn.  In a table kept well under half full almost every spent coin is freed this way
+// and probe runs stay a slot or two long however many blocks pass through; the rest is reused by insertions that walk
+// over it.  Tombstones of blocks that are still pending are never touched: a rollback finds its coins by slot number.
+__global__ void __launch_bounds__(128) k_utxo_reclaim(utxo_dev T, uint32_t seq, const uint32_t *__restrict__ rec_in, size_t nin) {
+    const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= nin) return;
+    uint32_t idx = rec_in[i];
+    if (idx == UTXO_NONE) return;
+    for (uint32_t steps = 0; steps <= T.mask; steps++) {
+        utxo_slot *s = T.slots + idx;
+        if (ld_state(s) != UTXO_SPENT || s->spent_seq > seq) return; /* seq = the newest final block */
+        if (ld_state(T.slots + ((idx + 1) & T.mask)) != UTXO_EMPTY) return;
+        *reinterpret_cast<volatile uint32_t *>(&s->state) = UTXO_EMPTY;
+        idx = (idx + T.mask) & T.mask;
+    }
+}
+
 struct ring_slot {
     uint8_t *d = nullptr; /* one allocation carved below */
     size_t cap = 0;
@@ -302,7 +321,8 @@ struct ring_slot {
     bool used = false;
     size_t nin = 0, nout = 0, ntx = 0;
     size_t o_rec_in = 0, o_rec_out = 0;
-    cudaEvent_t uploaded = nullptr, done = nullptr;
+    cudaEvent_t uploaded = nullptr, done = nullptr, reclaimed = nullptr;
+    bool reclaim_pending = false;
     // host destinations of the results
     uint32_t *h_status = nullptr;
     uint8_t *h_spk_cat = nullptr;
@@ -354,6 +374,7 @@ BCP_API bcp_utxo *bcp_gpu_utxo_create(int device, unsigned log2_slots, size_t ar
     for (int k = 0; k < UTXO_RING && e == cudaSuccess; k++) {
         e = cudaEventCreateWithFlags(&u->ring[k].uploaded, cudaEventDisableTiming);
         if (e == cudaSuccess) e = cudaEventCreateWithFlags(&u->ring[k].done, cudaEventDisableTiming);
+        if (e == cudaSuccess) e = cudaEventCreateWithFlags(&u->ring[k].reclaimed, cudaEventDisableTiming);
     }
     if (e != cudaSuccess) {
         bcp_cuda_fail(e, "bcp_gpu_utxo_create");
@@ -377,6 +398,7 @@ BCP_API void bcp_gpu_utxo_destroy(bcp_utxo *u) {
         if (u->ring[k].d) cudaFree(u->ring[k].d);
         if (u->ring[k].uploaded) cudaEventDestroy(u->ring[k].uploaded);
         if (u->ring[k].done) cudaEventDestroy(u->ring[k].done);
+        if (u->ring[k].reclaimed) cudaEventDestroy(u->ring[k].reclaimed);
     }
     if (u->T.slots) cudaFree(u->T.slots);
     if (u->T.arena) cudaFree(u->T.arena);
@@ -479,7 +501,12 @@ BCP_API int bcp_gpu_utxo_apply_block(bcp_utxo *u, uint32_t seq, const uint8_t *b
         r.cap = o + o / 8;
     }
     uint8_t *d = r.d;
-    // upload on the second stream (it runs under the kernels of the block before); the slot's previous user is long done
+    // upload on the second stream (it runs under the kernels of the block before); the slot's previous user is done except,
+    // possibly, for the clean-up kernel its confirmation queued, which still reads its spent-slot list
+    if (r.reclaim_pending) {
+        BCP_CUDA(cudaStreamWaitEvent(u->up, r.reclaimed, 0));
+        r.reclaim_pending = false;
+    }
     BCP_CUDA(cudaMemcpyAsync(d + o_blk, blk, len, cudaMemcpyHostToDevice, u->up));
     BCP_CUDA(cudaMemcpyAsync(d + o_txoff, tx_off, (ntx + 1) * 4, cudaMemcpyHostToDevice, u->up));
     if (nin) {
@@ -567,6 +594,13 @@ BCP_API int bcp_gpu_utxo_confirm(bcp_utxo *u, uint32_t seq) {
     if (!r.used || r.seq != seq) { bcp_set_error("bcp_gpu_utxo_confirm: block %u is not pending", seq); return BCP_ERR_INVALID; }
     r.used = false;
     if (seq > u->confirmed) u->confirmed = seq; /* tombstones left by blocks up to here may be reused from now on */
+    if (r.nin) {
+        BCP_CUDA(cudaSetDevice(u->device));
+        k_utxo_reclaim<<<(unsigned)((r.nin + 127) / 128), 128, 0, u->st>>>(u->T, u->confirmed, reinterpret_cast<uint32_t *>(r.d + r.o_rec_in), r.nin);
+        BCP_CUDA(cudaGetLastError());
+        BCP_CUDA(cudaEventRecord(r.reclaimed, u->st));
+        r.reclaim_pending = true;
+    }
     return BCP_OK;
 }
 

@@ -15,7 +15,7 @@
 // Context-free structure rules of CheckBlock / CheckCoinbase / CheckRegularTransaction (src/validation.cpp:476-570,
 // 3255-3330) that need nothing but the framing are applied by the scan: bad-cb-missing, bad-cb-length, bad-tx-coinbase,
 // bad-txns-vin-empty, bad-txns-vout-empty, bad-txns-oversize, bad-txns-vout-negative / -toolarge /
-// -txouttotal-toolarge, bad-txns-prevout-null.
+// -txouttotal-toolarge, bad-txns-prevout-null; and ConnectBlock's BIP30 rule (bad-txns-BIP30).
 // Not done (outside the hot path): fees/maturity (Consensus::CheckTxInputs), sigop limits, block size limit, BIP68
 // locks, difficulty, undo data.  Inputs that are not of the P2PKH shape are reported (reason "script-not-in-fast-path"):
 // a node would run them through its interpreter.
@@ -566,6 +566,7 @@ private:
         std::vector<int64_t> amounts;
         std::vector<Staged> stage;
         std::vector<std::vector<uint8_t>> bigStore;
+        std::vector<uint8_t> dupOut;           // outputs NOT inserted because a live coin with that outpoint exists (BIP30)
         size_t spentUpTo = 0, createdUpTo = 0; // how far the block has been applied to the table (for Rollback)
         std::vector<std::thread> th;
         std::vector<int> rc;
@@ -706,11 +707,21 @@ private:
         if (overlapped) launchScripts();
         auto tb0 = now();
         walk[1] += Secs(t3b, tb0);
-        // Pass B, all shards in parallel: the block's outputs become coins.
+        // Pass B, all shards in parallel: the block's outputs become coins.  An output whose outpoint is still unspent in
+        // the table is the BIP30 case (src/validation.cpp:1975-1990: no transaction may overwrite an unspent one) — the
+        // reference tests it before it looks at any input.
+        w.dupOut.assign((size_t)nout, 0);
         w.createdUpTo = (size_t)nout;
         team->Run([&](int s_) { PassB(w, s_); });
         auto tb1 = now();
         walk[2] += Secs(tb0, tb1);
+        for (size_t o = 0; o < (size_t)nout; o++)
+            if (w.dupOut[o]) {
+                if (overlapped) Abandon(w);
+                Rollback(w);
+                reason = "bad-txns-BIP30";
+                return false;
+            }
         // Pass C, only when pass A left inputs open: they may spend coins created EARLIER in this block (the creating
         // transaction must come first, src/validation.cpp:2095 applies each transaction before the next is looked at) and
         // each such coin only once.
@@ -846,6 +857,7 @@ private:
             memcpy(&amt, blk + pos, 8);
             pos += 8;
             const uint64_t sl = ReadCompact(blk, pos);
+            if (T.find(op)) { wk.dupOut[o] = 1; return; }
             T.insert(op, blk + pos, sl, amt);
         };
         (void)nout;
@@ -917,6 +929,7 @@ private:
     void Rollback(Work &w) {
         const Scan &cur = w.cur;
         for (size_t o = 0; o < w.createdUpTo; o++) {
+            if (o < w.dupOut.size() && w.dupOut[o]) continue; // was there before this block and is not this block's to remove
             OutPoint op;
             memcpy(op.b, &cur.txids[(size_t)cur.out_tx[o] * 32], 32);
             memcpy(op.b + 32, &cur.out_n[o], 4);

