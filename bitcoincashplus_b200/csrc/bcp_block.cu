@@ -183,6 +183,54 @@ static int rd_compact_canon(const uint8_t *p, size_t len, size_t *pos, uint64_t 
     return 1;
 }
 
+// The script checks of one block with every INPUT array already on c's device (the resident-block path of the coin table,
+// bcp_utxo.cu): sighash midstates, template match + sighash, batched ECDSA, verdicts; only the ScriptError bytes travel
+// back.  h_tx_off / h_in_tx are the host copies of two of the arrays (they size the shared-memory spans).  The caller
+// holds c->mu and has made c's device current; work is queued on st and waited for here.
+int bcp_block_scripts_resident(bcp_ctx *c, const uint8_t *d_blk, const uint32_t *d_txoff, const uint32_t *h_tx_off, size_t ntx,
+                               const uint32_t *d_inoff, const uint32_t *d_intx, const uint32_t *d_inn, const uint32_t *h_in_tx,
+                               size_t nin, const uint8_t *d_spk, const uint32_t *d_spkoff, const int64_t *d_amt, size_t stage_used,
+                               uint8_t *script_err, int *all_ok, cudaStream_t st) {
+    auto up = [](size_t x) { return (x + 255) / 256 * 256; };
+    size_t o = up(stage_used);
+    const size_t o_flag = o; o += 256;
+    const size_t o_mid = o; o += up(ntx * BCP_TXMID_BYTES + 16);
+    const size_t o_stat = o; o += up(nin + 8);
+    const size_t o_msg = o; o += up(nin * 32 + 32);
+    const size_t o_pub = o; o += up(nin * 65 + 65);
+    const size_t o_sig = o; o += up(nin * 64 + 64);
+    const size_t o_ok = o; o += up(nin + 8);
+    const size_t o_err = o; o += up(nin + 8);
+    if (o > c->stage_bytes) { /* the caller reserved stage_used + bcp_block_scripts_resident_bytes(ntx, nin) */
+        bcp_set_error("bcp_block_scripts_resident: staging area too small");
+        return BCP_ERR_INVALID;
+    }
+    int rc = bcp_ctx_reserve_scratch(c, bcp_gpu_ecdsa_scratch_bytes(nin));
+    if (rc != BCP_OK) return rc;
+    uint8_t *d = c->stage;
+    int one = 1;
+    BCP_CUDA(cudaMemcpyAsync(d + o_flag, &one, sizeof(int), cudaMemcpyHostToDevice, st));
+    rc = launch_mid_extract(c, d_blk, d_txoff, h_tx_off, ntx, d_inoff, d_intx, d_inn, h_in_tx, nin, d_spk, d_spkoff, d_amt, d + o_mid,
+                            d + o_stat, d + o_msg, d + o_pub, d + o_sig, st);
+    if (rc != BCP_OK) return rc;
+    rc = bcp_ecdsa_launch(c, d + o_msg, d + o_pub, d + o_sig, nin, BCP_ECDSA_FLAG_NORMALIZE_S, d + o_ok,
+                          reinterpret_cast<uint32_t *>(c->scratch), st);
+    if (rc != BCP_OK) return rc;
+    k_script_finish<<<(unsigned)((nin + 255) / 256), 256, 0, st>>>(d + o_stat, d + o_ok, nin, d + o_err, reinterpret_cast<int *>(d + o_flag));
+    BCP_CUDA(cudaGetLastError());
+    BCP_CUDA(cudaMemcpyAsync(script_err, d + o_err, nin, cudaMemcpyDeviceToHost, st));
+    int a = 0;
+    BCP_CUDA(cudaMemcpyAsync(&a, d + o_flag, sizeof(int), cudaMemcpyDeviceToHost, st));
+    BCP_CUDA(cudaStreamSynchronize(st));
+    if (all_ok) *all_ok = a ? 1 : 0;
+    return BCP_OK;
+}
+size_t bcp_block_scripts_resident_bytes(size_t ntx, size_t nin) {
+    auto up = [](size_t x) { return (x + 255) / 256 * 256; };
+    return 512 + up(ntx * BCP_TXMID_BYTES + 16) + up(nin + 8) * 3 + up(nin * 32 + 32) + up(nin * 65 + 65) + up(nin * 64 + 64);
+}
+int bcp_block_check_flags(uint32_t flags, const char *fn) { return check_fastpath_flags(flags, fn); }
+
 extern "C" {
 
 // Framing scan that also lists every non-coinbase input (CTransaction::IsCoinBase: a single input with a null
@@ -226,6 +274,12 @@ BCP_API long bcp_block_index_full(const uint8_t *blk, size_t len, int legacy_hea
     for (uint64_t t = 0; t < ntx; t++) {
         tx_off[t] = (uint32_t)pos;
         uint64_t nin, nout, sl;
+        // Every step of this walk depends on a byte the previous step loaded (a length), so on a block that is not in the
+        // cache it runs at memory LATENCY: measured 4-10 ms for 8 MB against 0.9 ms from the L3.  The walk only ever moves
+        // forward, so the lines a few transactions ahead are requested now (4 KB = about twenty 192-byte transactions).
+        __builtin_prefetch(blk + pos + 4096);
+        __builtin_prefetch(blk + pos + 4096 + 64);
+        __builtin_prefetch(blk + pos + 4096 + 128);
         if (pos + 4 > len) return -1;
         pos += 4;
         BCP_RD_COMPACT(nin);

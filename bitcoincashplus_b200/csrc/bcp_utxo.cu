@@ -36,8 +36,8 @@
 #define UTXO_INLINE 64u
 #define UTXO_RING 16 /* blocks that may be applied and not yet confirmed or rolled back */
 
-// status words of one applied block (device -> host)
-enum { ST_MISSING = 0, ST_FIRST_MISSING = 1, ST_DUPLICATE = 2, ST_SPK_BYTES = 3, ST_TABLE_FULL = 4, ST_ARENA_FULL = 5, ST_WORDS = 8 };
+// status words of one applied block (device -> host); [6] = spent scripts that did not fit the script buffer
+enum { ST_MISSING = 0, ST_FIRST_MISSING = 1, ST_DUPLICATE = 2, ST_SPK_BYTES = 3, ST_TABLE_FULL = 4, ST_ARENA_FULL = 5, ST_SPK_OVERFLOW = 6, ST_WORDS = 8 };
 
 struct __align__(16) utxo_slot {
     uint32_t state;
@@ -72,9 +72,9 @@ __device__ __forceinline__ bool utxo_key_eq(const utxo_slot *s, const uint32_t *
 }
 __device__ __forceinline__ uint32_t ld_state(const utxo_slot *s) { return *reinterpret_cast<const volatile uint32_t *>(&s->state); }
 
-// Puts one coin into the table.  Returns the slot number, UTXO_NONE when the table is full; *dup is raised when a LIVE
-// coin with the same outpoint is already there (the BIP30 situation; the new coin is stored all the same, like
-// CCoinsViewCache::AddCoin with possible_overwrite).
+// Puts one coin into the table.  Returns the slot number, UTXO_NONE when the table is full; status[ST_DUPLICATE] counts the
+// coins put on top of a LIVE coin with the same outpoint that an EARLIER block (or the caller) created — the BIP30
+// situation; the new coin is stored all the same and the block is expected to be rolled back.
 __device__ uint32_t utxo_put(const utxo_dev &T, const uint32_t *key, const uint8_t *spk, uint32_t len, int64_t amount, uint32_t seq,
                              uint32_t tx, uint32_t confirmed, uint32_t *status) {
     uint32_t idx = utxo_home(key, T.mask);
@@ -83,7 +83,9 @@ __device__ uint32_t utxo_put(const utxo_dev &T, const uint32_t *key, const uint8
         utxo_slot *s = T.slots + idx;
         const uint32_t st = ld_state(s);
         if (st == UTXO_LIVE) {
-            if (utxo_key_eq(s, key)) atomicAdd(&status[ST_DUPLICATE], 1u);
+            // BIP30 looks at the table as it was BEFORE this block: a twin made by an identical transaction of the same block
+            // does not count (that transaction fails on its spent inputs instead)
+            if (s->created_seq != seq && utxo_key_eq(s, key)) atomicAdd(&status[ST_DUPLICATE], 1u);
             continue;
         }
         if (st == UTXO_SPENT && reuse == UTXO_NONE && s->spent_seq <= confirmed) reuse = idx; /* a final tombstone */
@@ -260,13 +262,17 @@ __global__ void __launch_bounds__(1024) k_utxo_offsets(const uint32_t *__restric
 
 __global__ void __launch_bounds__(128)
     k_utxo_gather(utxo_dev T, const uint32_t *__restrict__ rec_in, const uint32_t *__restrict__ spk_off, size_t nin,
-                  uint8_t *__restrict__ spk_cat) {
+                  uint8_t *__restrict__ spk_cat, size_t cap, uint32_t *__restrict__ status) {
     const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= nin) return;
     const uint32_t r = rec_in[i];
     if (r == UTXO_NONE) return;
     const utxo_slot *s = T.slots + r;
     const uint32_t len = s->spk_len;
+    if ((size_t)spk_off[i] + len > cap) { /* the buffer the caller sized cannot hold this block's spent scripts */
+        atomicAdd(&status[ST_SPK_OVERFLOW], 1u);
+        return;
+    }
     const uint8_t *src = len <= UTXO_INLINE ? s->spk : T.arena + *reinterpret_cast<const unsigned long long *>(s->spk);
     uint8_t *dst = spk_cat + spk_off[i];
     for (uint32_t k = 0; k < len; k++) dst[k] = src[k];
@@ -319,8 +325,9 @@ struct ring_slot {
     size_t cap = 0;
     uint32_t seq = 0;
     bool used = false;
-    size_t nin = 0, nout = 0, ntx = 0;
+    size_t nin = 0, nout = 0, ntx = 0, len = 0;
     size_t o_rec_in = 0, o_rec_out = 0;
+    size_t o_txoff = 0, o_inoff = 0, o_intx = 0, o_amt = 0, o_spkoff = 0, in_area = 0; /* script-check inputs: one contiguous area */
     cudaEvent_t uploaded = nullptr, done = nullptr, reclaimed = nullptr;
     bool reclaim_pending = false;
     // host destinations of the results
@@ -340,6 +347,7 @@ struct bcp_utxo {
     ring_slot ring[UTXO_RING];
     uint32_t *d_seed_status = nullptr;
     uint32_t *h_pinned_status = nullptr; /* UTXO_RING x ST_WORDS, pinned */
+    bool peer_tried[BCP_MAX_DEVICES] = {false}; /* peer access between the table's GPU and that GPU has been asked for */
     std::mutex mu;
 };
 
@@ -458,8 +466,8 @@ BCP_API int bcp_gpu_utxo_apply_block(bcp_utxo *u, uint32_t seq, const uint8_t *b
                                      const uint32_t *out_tx, const uint32_t *out_n, size_t nout, uint8_t *txids, uint8_t *root32,
                                      int *mutated, uint8_t *spk_cat, size_t spk_cap, uint32_t *spk_off, int64_t *amounts) {
     if (!u) return BCP_ERR_INVALID;
-    if (seq == 0 || !blk || !tx_off || ntx == 0 || !root32 || !mutated || (nin && (!in_off || !in_tx || !spk_cat || !spk_off || !amounts)) ||
-        (nout && (!out_off || !out_tx || !out_n))) {
+    if (seq == 0 || !blk || !tx_off || ntx == 0 || !root32 || !mutated || (nin && (!in_off || !in_tx)) ||
+        (nout && (!out_off || !out_tx || !out_n)) || ((spk_cat || spk_off || amounts) && !(spk_cat && spk_off && amounts))) {
         bcp_set_error("bcp_gpu_utxo_apply_block: NULL buffer, no transaction or sequence number 0 (numbers start at 1)");
         return BCP_ERR_INVALID;
     }
@@ -473,11 +481,18 @@ BCP_API int bcp_gpu_utxo_apply_block(bcp_utxo *u, uint32_t seq, const uint8_t *b
     }
     BCP_CUDA(cudaSetDevice(u->device));
     // device layout of this block's slot
+    // The arrays the script checks need come first and back to back (block, offsets, inputs, spent amounts / script offsets /
+    // scripts): bcp_gpu_utxo_block_scripts reads them in place or moves them to another GPU in one peer copy.
     size_t o = 0;
     const size_t o_blk = o; o += up256(len + 16);
     const size_t o_txoff = o; o += up256((ntx + 1) * 4);
     const size_t o_inoff = o; o += up256(nin * 4 + 4);
     const size_t o_intx = o; o += up256(nin * 4 + 4);
+    const size_t o_amt = o; o += up256(nin * 8 + 8);
+    const size_t o_spkoff = o; o += up256((nin + 1) * 4);
+    const size_t dev_spk_cap = spk_cat ? spk_cap : nin * 80 + 65536; /* without a host buffer: room for P2PKH-sized scripts and more */
+    const size_t o_spk = o; o += up256(dev_spk_cap + 16);
+    const size_t in_area = o;
     const size_t o_outoff = o; o += up256(nout * 4 + 4);
     const size_t o_outtx = o; o += up256(nout * 4 + 4);
     const size_t o_outn = o; o += up256(nout * 4 + 4);
@@ -487,10 +502,7 @@ BCP_API int bcp_gpu_utxo_apply_block(bcp_utxo *u, uint32_t seq, const uint8_t *b
     const size_t o_stat = o; o += 256;
     const size_t o_recin = o; o += up256(nin * 4 + 4);
     const size_t o_recout = o; o += up256(nout * 4 + 4);
-    const size_t o_amt = o; o += up256(nin * 8 + 8);
     const size_t o_lens = o; o += up256(nin * 4 + 4);
-    const size_t o_spkoff = o; o += up256((nin + 1) * 4);
-    const size_t o_spk = o; o += up256(spk_cap + 16);
     if (o > r.cap) { /* grow-only; happens while the first blocks of a run pass through */
         BCP_CUDA(cudaStreamSynchronize(u->st));
         BCP_CUDA(cudaStreamSynchronize(u->up));
@@ -540,7 +552,7 @@ BCP_API int bcp_gpu_utxo_apply_block(bcp_utxo *u, uint32_t seq, const uint8_t *b
                                                                    reinterpret_cast<uint32_t *>(d + o_lens), d_stat);
         k_utxo_offsets<<<1, 1024, 0, st>>>(reinterpret_cast<uint32_t *>(d + o_lens), nin, reinterpret_cast<uint32_t *>(d + o_spkoff), d_stat);
         k_utxo_gather<<<(unsigned)((nin + 127) / 128), 128, 0, st>>>(u->T, reinterpret_cast<uint32_t *>(d + o_recin),
-                                                                    reinterpret_cast<uint32_t *>(d + o_spkoff), nin, d + o_spk);
+                                                                    reinterpret_cast<uint32_t *>(d + o_spkoff), nin, d + o_spk, dev_spk_cap, d_stat);
     }
     BCP_CUDA(cudaGetLastError());
     // results to the host: the fixed-size ones now; of the scripts as much as P2PKH-sized coins would need (the rest, if the
@@ -551,7 +563,8 @@ BCP_API int bcp_gpu_utxo_apply_block(bcp_utxo *u, uint32_t seq, const uint8_t *b
     BCP_CUDA(cudaMemcpyAsync(mutated, d + o_root + 32, sizeof(int), cudaMemcpyDeviceToHost, st));
     if (txids) BCP_CUDA(cudaMemcpyAsync(txids, d + o_txid, ntx * 32, cudaMemcpyDeviceToHost, st));
     size_t first = 0;
-    if (nin) {
+    if (!spk_cat) spk_cap = 0; /* the spent-coin arrays stay on the device (bcp_gpu_utxo_block_scripts reads them there) */
+    if (nin && spk_cat) {
         BCP_CUDA(cudaMemcpyAsync(amounts, d + o_amt, nin * 8, cudaMemcpyDeviceToHost, st));
         BCP_CUDA(cudaMemcpyAsync(spk_off, d + o_spkoff, (nin + 1) * 4, cudaMemcpyDeviceToHost, st));
         first = nin * 25 + 1024 < spk_cap ? nin * 25 + 1024 : spk_cap;
@@ -560,8 +573,9 @@ BCP_API int bcp_gpu_utxo_apply_block(bcp_utxo *u, uint32_t seq, const uint8_t *b
     BCP_CUDA(cudaEventRecord(r.done, st));
     r.used = true;
     r.seq = seq;
-    r.nin = nin; r.nout = nout; r.ntx = ntx;
+    r.nin = nin; r.nout = nout; r.ntx = ntx; r.len = len;
     r.o_rec_in = o_recin; r.o_rec_out = o_recout;
+    r.o_txoff = o_txoff; r.o_inoff = o_inoff; r.o_intx = o_intx; r.o_amt = o_amt; r.o_spkoff = o_spkoff; r.in_area = in_area;
     r.h_status = hst;
     r.h_spk_cat = spk_cat; r.spk_cap = spk_cap; r.spk_copied = first; r.o_spk = o_spk;
     return BCP_OK;
@@ -575,6 +589,7 @@ BCP_API int bcp_gpu_utxo_wait(bcp_utxo *u, uint32_t seq, uint32_t status8[8]) {
     BCP_CUDA(cudaEventSynchronize(r.done));
     memcpy(status8, r.h_status, ST_WORDS * 4);
     const size_t total = status8[ST_SPK_BYTES];
+    if (!r.h_spk_cat) return BCP_OK; /* the spent-coin arrays were left on the device */
     if (total > r.spk_cap) {
         bcp_set_error("bcp_gpu_utxo_wait: the spent scripts of block %u need %zu bytes, the caller's buffer holds %zu", seq, total, r.spk_cap);
         return BCP_ERR_INVALID;
@@ -585,6 +600,60 @@ BCP_API int bcp_gpu_utxo_wait(bcp_utxo *u, uint32_t seq, uint32_t status8[8]) {
         r.spk_copied = total;
     }
     return BCP_OK;
+}
+
+// The script checks of applied block `seq` straight from the arrays bcp_gpu_utxo_apply_block left on the table's GPU: the
+// raw block, its offsets, and the spent (amount, scriptPubKey) of every input.  On the table's own GPU they are read in
+// place; on another GPU one peer-to-peer copy over NVLink brings them over — either way the block does not cross the
+// host's memory a second time and the spent-coin arrays never visit the host at all.
+BCP_API int bcp_gpu_utxo_block_scripts(bcp_utxo *u, uint32_t seq, int device, const uint32_t *tx_off, const uint32_t *in_tx,
+                                       const uint32_t *in_n, uint32_t flags, uint8_t *script_err, int *all_ok, uint32_t status8[8]) {
+    if (!u || !status8) return BCP_ERR_INVALID;
+    bcp_ctx *c = bcp_get_ctx(device);
+    if (!c) return BCP_ERR_NOT_INIT;
+    ring_slot &r = u->ring[seq % UTXO_RING];
+    if (!r.used || r.seq != seq) { bcp_set_error("bcp_gpu_utxo_block_scripts: block %u is not pending", seq); return BCP_ERR_INVALID; }
+    if (all_ok) *all_ok = 1;
+    if (r.nin && (!tx_off || !in_tx || !in_n || !script_err)) { bcp_set_error("bcp_gpu_utxo_block_scripts: NULL buffer"); return BCP_ERR_INVALID; }
+    if (bcp_block_check_flags(flags, "bcp_gpu_utxo_block_scripts") != BCP_OK) return BCP_ERR_INVALID;
+    BCP_CUDA(cudaSetDevice(u->device));
+    BCP_CUDA(cudaEventSynchronize(r.done));
+    memcpy(status8, r.h_status, ST_WORDS * 4);
+    if (status8[ST_SPK_OVERFLOW]) {
+        bcp_set_error("bcp_gpu_utxo_block_scripts: the spent scripts of block %u (%u bytes) do not fit the device buffer", seq, status8[ST_SPK_BYTES]);
+        return BCP_ERR_INVALID;
+    }
+    if (r.nin == 0 || status8[ST_MISSING]) return BCP_OK; /* nothing to check / the block is refused anyway */
+    std::lock_guard<std::mutex> lk(c->mu);
+    BCP_CUDA(cudaSetDevice(c->device));
+    cudaStream_t st = c->stream;
+    const size_t nin = r.nin, ntx = r.ntx;
+    const size_t in_bytes = r.o_spk + ((size_t)status8[ST_SPK_BYTES] + 255) / 256 * 256; /* the part of the input area in use */
+    const size_t o_inn = (in_bytes + 255) / 256 * 256, used = o_inn + (nin * 4 + 4 + 255) / 256 * 256;
+    int rc = bcp_ctx_reserve_stage(c, used + bcp_block_scripts_resident_bytes(ntx, nin) + 1024);
+    if (rc != BCP_OK) return rc;
+    const uint8_t *base = r.d;
+    if (c->device != u->device) { /* bring the input area over: one device-to-device copy, NVLink when peer access is on */
+        if (!u->peer_tried[c->device]) { /* once per pair, both directions; "already enabled" and "not supported" are fine */
+            std::lock_guard<std::mutex> lk2(u->mu);
+            int can = 0;
+            if (cudaDeviceCanAccessPeer(&can, c->device, u->device) == cudaSuccess && can) cudaDeviceEnablePeerAccess(u->device, 0);
+            cudaSetDevice(u->device);
+            if (cudaDeviceCanAccessPeer(&can, u->device, c->device) == cudaSuccess && can) cudaDeviceEnablePeerAccess(c->device, 0);
+            cudaGetLastError();
+            BCP_CUDA(cudaSetDevice(c->device));
+            u->peer_tried[c->device] = true;
+        }
+        BCP_CUDA(cudaMemcpyPeerAsync(c->stage, c->device, r.d, u->device, in_bytes, st));
+        base = c->stage;
+    }
+    uint8_t *d_inn = c->stage + o_inn; /* the one array the table did not need */
+    BCP_CUDA(cudaMemcpyAsync(d_inn, in_n, nin * 4, cudaMemcpyHostToDevice, st));
+    return bcp_block_scripts_resident(c, base, reinterpret_cast<const uint32_t *>(base + r.o_txoff), tx_off, ntx,
+                                      reinterpret_cast<const uint32_t *>(base + r.o_inoff), reinterpret_cast<const uint32_t *>(base + r.o_intx),
+                                      reinterpret_cast<const uint32_t *>(d_inn), in_tx, nin, base + r.o_spk,
+                                      reinterpret_cast<const uint32_t *>(base + r.o_spkoff), reinterpret_cast<const int64_t *>(base + r.o_amt),
+                                      used, script_err, all_ok, st);
 }
 
 BCP_API int bcp_gpu_utxo_confirm(bcp_utxo *u, uint32_t seq) {

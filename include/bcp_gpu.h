@@ -262,11 +262,13 @@ BCP_API int bcp_gpu_measure_int_peak(int device, int which, double *ops_per_seco
  *                           lookups + spends, and the copies of the results into the caller's HOST buffers, which must
  *                           stay valid until bcp_gpu_utxo_wait(seq) returns (pinned memory keeps the call asynchronous):
  *                           txids (optional), root32, mutated, and for the script checks amounts[nin], spk_off[nin+1],
- *                           spk_cat (spk_cap bytes: the spent scriptPubKeys back to back)
+ *                           spk_cat (spk_cap bytes: the spent scriptPubKeys back to back) — all three, or all three NULL
+ *                           when the checks will run from the device copies (bcp_gpu_utxo_block_scripts)
  *   bcp_gpu_utxo_wait       blocks until block seq's results are in the host buffers.  status8: [0] inputs whose coin is
  *                           missing or already spent (bad-txns-inputs-missingorspent when non-zero), [1] the first such
  *                           input, [2] outputs that overwrite a live coin (bad-txns-BIP30), [3] bytes of spk_cat used,
- *                           [4] coins that did not fit the table, [5] long scripts that did not fit the arena
+ *                           [4] coins that did not fit the table, [5] long scripts that did not fit the arena, [6] spent
+ *                           scripts that did not fit the script buffer
  *   bcp_gpu_utxo_confirm    block seq is final (oldest first): its undo record is dropped, coins it spent may be overwritten
  *   bcp_gpu_utxo_rollback   undoes block seq (newest first): its spent coins are unspent again, its new coins are gone
  *   bcp_gpu_utxo_size       number of unspent coins (synchronises with the table's stream) */
@@ -281,6 +283,13 @@ BCP_API int bcp_gpu_utxo_apply_block(bcp_utxo *u, uint32_t seq, const uint8_t *b
                                      const uint32_t *out_tx, const uint32_t *out_n, size_t nout, uint8_t *txids, uint8_t *root32,
                                      int *mutated, uint8_t *spk_cat, size_t spk_cap, uint32_t *spk_off, int64_t *amounts);
 BCP_API int bcp_gpu_utxo_wait(bcp_utxo *u, uint32_t seq, uint32_t status8[8]);
+/* The script checks of applied block seq (bcp_gpu_block_scripts_p2pkh's work and result) from the arrays apply_block left on
+ * the table's GPU — the block, its offsets, the spent amounts and scriptPubKeys — on `device` (may carry a lane): read in
+ * place on the table's own GPU, brought over by one peer-to-peer copy otherwise.  The host only supplies in_n (each input's
+ * index in its transaction) and, to size the kernels' staging, its copies of tx_off and in_tx.  Waits for the block's table
+ * work first and returns its status words like bcp_gpu_utxo_wait; with missing inputs no script is run. */
+BCP_API int bcp_gpu_utxo_block_scripts(bcp_utxo *u, uint32_t seq, int device, const uint32_t *tx_off, const uint32_t *in_tx,
+                                       const uint32_t *in_n, uint32_t flags, uint8_t *script_err, int *all_ok, uint32_t status8[8]);
 BCP_API int bcp_gpu_utxo_confirm(bcp_utxo *u, uint32_t seq);
 BCP_API int bcp_gpu_utxo_rollback(bcp_utxo *u, uint32_t seq);
 

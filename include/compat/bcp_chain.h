@@ -65,7 +65,7 @@ struct alignas(128) CoinSlot {
     uint8_t pad[3];
     uint32_t spk_len;
     OutPoint key;       // bytes 8..43
-    uint32_t pad2;
+    uint32_t stamp;     // which block created the coin (0: seeded) — tells an in-block twin from a coin that was there before
     int64_t amount;     // 48
     std::vector<uint8_t> *big; // 56; only for scripts longer than the inline space
     // second cache line
@@ -99,7 +99,7 @@ public:
             i = (i + 1) & mask;
         }
     }
-    CoinSlot *insert(const OutPoint &k, const uint8_t *spk, size_t len, int64_t amount) {
+    CoinSlot *insert(const OutPoint &k, const uint8_t *spk, size_t len, int64_t amount, uint32_t stamp = 0) {
         if ((live + 1) * 2 > slots.size()) grow();
         size_t i = OutPointHash()(k) & mask;
         for (;;) {
@@ -112,6 +112,7 @@ public:
         d.key = k;
         d.state = 1;
         d.big = nullptr;
+        d.stamp = stamp;
         fill(d, spk, len, amount);
         live++;
         return &d;
@@ -157,7 +158,7 @@ private:
         live = 0;
         for (auto &o : old)
             if (o.state == 1) {
-                CoinSlot *n = insert(o.key, script(o), o.spk_len, o.amount);
+                CoinSlot *n = insert(o.key, script(o), o.spk_len, o.amount, o.stamp);
                 (void)n;
                 delete o.big;
                 o.big = nullptr;
@@ -566,7 +567,9 @@ private:
         std::vector<int64_t> amounts;
         std::vector<Staged> stage;
         std::vector<std::vector<uint8_t>> bigStore;
-        std::vector<uint8_t> dupOut;           // outputs NOT inserted because a live coin with that outpoint exists (BIP30)
+        std::vector<uint8_t> dupOut;           // outputs NOT inserted: 1 = a coin with that outpoint was there before the block
+                                               // (BIP30), 2 = an identical transaction earlier in this block created it
+        uint32_t stamp = 0;                    // this block's mark on the coins it creates
         size_t spentUpTo = 0, createdUpTo = 0; // how far the block has been applied to the table (for Rollback)
         std::vector<std::thread> th;
         std::vector<int> rc;
@@ -711,12 +714,13 @@ private:
         // the table is the BIP30 case (src/validation.cpp:1975-1990: no transaction may overwrite an unspent one) — the
         // reference tests it before it looks at any input.
         w.dupOut.assign((size_t)nout, 0);
+        w.stamp = ++blockStamp;
         w.createdUpTo = (size_t)nout;
         team->Run([&](int s_) { PassB(w, s_); });
         auto tb1 = now();
         walk[2] += Secs(tb0, tb1);
         for (size_t o = 0; o < (size_t)nout; o++)
-            if (w.dupOut[o]) {
+            if (w.dupOut[o] == 1) {
                 if (overlapped) Abandon(w);
                 Rollback(w);
                 reason = "bad-txns-BIP30";
@@ -857,8 +861,10 @@ private:
             memcpy(&amt, blk + pos, 8);
             pos += 8;
             const uint64_t sl = ReadCompact(blk, pos);
-            if (T.find(op)) { wk.dupOut[o] = 1; return; }
-            T.insert(op, blk + pos, sl, amt);
+            // The reference's BIP30 test looks at the view as it was BEFORE the block; a twin created by an identical
+            // transaction of this same block is not its business (that transaction then fails on its spent inputs).
+            if (CoinSlot *have = T.find(op)) { wk.dupOut[o] = have->stamp == wk.stamp ? 2 : 1; return; }
+            T.insert(op, blk + pos, sl, amt, wk.stamp);
         };
         (void)nout;
         for (size_t q = cur.out_shard_start[(size_t)w]; q < cur.out_shard_start[(size_t)w + 1]; q++) {
@@ -959,6 +965,7 @@ private:
     Scan ahead[NAHEAD];
     unsigned nextSlot = 0;
     Work work[2];
+    uint32_t blockStamp = 0;
     int lastWork = 0;
     uint8_t lastHash[32] = {0};
     size_t nInputs = 0;

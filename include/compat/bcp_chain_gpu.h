@@ -12,9 +12,11 @@
 //                    txids + Merkle root, inserts the outputs, looks up and spends the inputs in block order and returns the
 //                    spent (amount, scriptPubKey) arrays; stream order is the chain's order, so block b+1 is applied on top
 //                    of block b while b's script checks are still running
-//   check threads    one per (GPU, lane); block b belongs to thread b mod W: waits for b's spent-coin arrays, verifies the
+//   check threads    one per (GPU, lane); block b belongs to thread b mod W: waits for b's table work, verifies the
 //                    header (Equihash + hash) and runs the script checks of the WHOLE block on its GPU
-//                    (bcp_gpu_block_scripts_p2pkh).  Blocks, not inputs, are what is dealt out to the devices: a block is
+//                    (bcp_gpu_utxo_block_scripts: from the copy of the block and the spent-coin arrays that are already in
+//                    device memory — in place on the table's GPU, one NVLink copy away on the others; the host's memory
+//                    is crossed once per block, by the upload).  Blocks, not inputs, are what is dealt out to the devices: a block is
 //                    less than one wave of the point kernel on a B200, so splitting it further would not shorten it
 //   connecting thread  takes the verdicts in order: confirm, or — first failure — let the blocks applied after it finish,
 //                    roll them back newest first, then the failed block; the table is then exactly as before that block
@@ -173,10 +175,7 @@ private:
         }
         j.structErr = nullptr;
         if (j.nin >= 0 && j.ntx >= 1) j.structErr = CheckStructure(j, b);
-        if (j.nin >= 0) {
-            j.amounts.need((size_t)j.nin + 1); j.spk_off.need((size_t)j.nin + 2); j.errs.need((size_t)j.nin + 1);
-            j.spk_cat.need((size_t)j.nin * 64 + 4096);
-        }
+        if (j.nin >= 0) j.errs.need((size_t)j.nin + 1);
         j.small.need(64);
     }
     static uint64_t ReadCompact(const uint8_t *p, size_t &pos) { // already validated by the framing scan
@@ -240,7 +239,7 @@ private:
     void Check(Job &j, int dev) {
         auto t0 = Clock::now();
         uint32_t st[8] = {0};
-        const int rcw = bcp_gpu_utxo_wait(utxo, j.seq, st);
+        int rcw = bcp_gpu_utxo_wait(utxo, j.seq, st);
         auto t1 = Clock::now();
         j.ok = false;
         // header first, like CheckBlockHeader before anything of the body (src/validation.cpp:3202-3220)
@@ -274,9 +273,8 @@ private:
         } else {
             int all = 1;
             int rc = BCP_OK;
-            if (j.nin > 0)
-                rc = bcp_gpu_block_scripts_p2pkh(dev, j.blk, j.len, j.tx_off.p, (size_t)j.ntx, j.in_off.p, j.in_tx.p, j.in_n.p, (size_t)j.nin,
-                                                 j.spk_cat.p, j.spk_off.p, j.amounts.p, flags, j.errs.p, &all);
+            if (j.nin > 0) // from the block and the spent-coin arrays that are already on the table's GPU
+                rc = bcp_gpu_utxo_block_scripts(utxo, j.seq, dev, j.tx_off.p, j.in_tx.p, j.in_n.p, flags, j.errs.p, &all, st);
             tScripts = Secs(t2, Clock::now());
             if (rc != BCP_OK) {
                 j.reason = std::string("device-error: ") + bcp_gpu_last_error();
@@ -339,10 +337,11 @@ private:
                     }
                     auto t0 = Clock::now();
                     Scan(jobOf(b));
+                    const double dt = Secs(t0, Clock::now());
                     {
                         std::lock_guard<std::mutex> l(mu);
                         jobOf(b).state = SCANNED;
-                        phase[5] += Secs(t0, Clock::now());
+                        phase[5] += dt;
                     }
                     cv.notify_all();
                 }
@@ -411,8 +410,7 @@ private:
                 auto ta0 = Clock::now();
                 const int rc = bcp_gpu_utxo_apply_block(utxo, j.seq, j.blk, j.len, j.tx_off.p, (size_t)j.ntx, j.in_off.p, j.in_tx.p, (size_t)j.nin,
                                                         j.out_off.p, j.out_tx.p, j.out_n.p, (size_t)j.nout, nullptr, j.small.p,
-                                                        reinterpret_cast<int *>(j.small.p + 32), j.spk_cat.p, j.spk_cat.cap, j.spk_off.p,
-                                                        j.amounts.p);
+                                                        reinterpret_cast<int *>(j.small.p + 32), nullptr, 0, nullptr, nullptr);
                 std::lock_guard<std::mutex> l(mu);
                 phase[0] += Secs(ta0, Clock::now());
                 nextApply++;

@@ -28,7 +28,9 @@
 #include "pubkey.h"
 #include "script/interpreter.h"
 #include "script/script.h"
+#include "streams.h"
 #include "uint256.h"
+#include "version.h"
 
 #include "compat/checkqueue.h" // this project's drop-in (include/compat/), not the reference's src/checkqueue.h
 
@@ -270,8 +272,123 @@ static void make_cases(std::vector<Case> &out) {
     }
 }
 
+// ---- the reference's own script corpus (src/test/data/script_tests.json as binary scripts, tests/golden/script_tests.json.gz
+// turned into a flat file by tests/test_gpu_replay.py): [u64 n] n x { u32 flags, i64 amount, u8 ok, u32 len + scriptSig,
+// u32 len + scriptPubKey, u32 len + spending transaction }.  Each vector is evaluated like DoTest (src/test/script_tests.cpp:
+// 153-170) — but through this project's CCheckQueue with the recording checker, signatures on the GPU.
+struct Vector {
+    uint32_t flags = 0;
+    Amount amount{0};
+    bool ok = false;
+    CScript sig, spk;
+    CTransactionRef tx;
+};
+static bool load_vectors(const char *path, std::vector<Vector> &out) {
+    FILE *f = fopen(path, "rb");
+    if (!f) return false;
+    std::vector<uint8_t> buf;
+    uint8_t tmp[65536];
+    size_t k;
+    while ((k = fread(tmp, 1, sizeof tmp, f)) > 0) buf.insert(buf.end(), tmp, tmp + k);
+    fclose(f);
+    size_t pos = 0;
+    auto rd = [&](void *dst, size_t n) { memcpy(dst, &buf[pos], n); pos += n; };
+    uint64_t n;
+    rd(&n, 8);
+    for (uint64_t i = 0; i < n; i++) {
+        Vector v;
+        int64_t amt;
+        uint8_t ok;
+        uint32_t len;
+        rd(&v.flags, 4); rd(&amt, 8); rd(&ok, 1);
+        v.amount = Amount(amt);
+        v.ok = ok != 0;
+        rd(&len, 4); v.sig = CScript(&buf[pos], &buf[pos] + len); pos += len;
+        rd(&len, 4); v.spk = CScript(&buf[pos], &buf[pos] + len); pos += len;
+        rd(&len, 4);
+        CDataStream ss((const char *)&buf[pos], (const char *)&buf[pos] + len, SER_NETWORK, PROTOCOL_VERSION);
+        pos += len;
+        v.tx = MakeTransactionRef(CTransaction(deserialize, ss));
+        out.push_back(std::move(v));
+    }
+    return pos == buf.size();
+}
+static int run_vectors(const char *path, bool gpu) {
+    std::vector<Vector> vs;
+    if (!load_vectors(path, vs)) {
+        fprintf(stderr, "cannot read %s\n", path);
+        return 2;
+    }
+    int failures = 0;
+    size_t n_ok = 0;
+    for (const Vector &v : vs) { // the fixture's expectation against the reference's plain CPU checker
+        ScriptError e;
+        const bool cpu = VerifyScript(v.sig, v.spk, v.flags, TransactionSignatureChecker(v.tx.get(), 0, v.amount), &e);
+        if (cpu != v.ok) { printf("FIXTURE MISMATCH: expected %d, reference CPU %d\n", (int)v.ok, (int)cpu); failures++; }
+        n_ok += v.ok;
+    }
+    printf("%zu vectors, %zu expected to verify\n", vs.size(), n_ok);
+    if (!gpu) return failures ? 1 : 0;
+    if (bcp_gpu_init(0) != BCP_OK) {
+        fprintf(stderr, "no CUDA device: %s\n", bcp_gpu_last_error());
+        return 2;
+    }
+    CCheckQueue<ScriptCheck> queue(16);
+    std::vector<std::thread> workers;
+    for (int i = 0; i < 3; i++) workers.emplace_back([&] { queue.Thread(); });
+    g_seen.clear();
+    // every vector alone
+    for (size_t i = 0; i < vs.size(); i++) {
+        const Vector &v = vs[i];
+        CCheckQueueControl<ScriptCheck> control(&queue);
+        std::vector<ScriptCheck> c;
+        c.emplace_back(v.spk, v.amount, v.tx.get(), 0, v.flags);
+        control.Add(c);
+        const bool got = control.Wait();
+        if (got != v.ok) { printf("MISMATCH vector %zu: queue %d, expected %d\n", i, (int)got, (int)v.ok); failures++; }
+    }
+    const size_t comparisons = g_seen.size();
+    // all verifying vectors as one block
+    {
+        CCheckQueueControl<ScriptCheck> control(&queue);
+        std::vector<ScriptCheck> c;
+        for (const Vector &v : vs)
+            if (v.ok) c.emplace_back(v.spk, v.amount, v.tx.get(), 0, v.flags);
+        control.Add(c);
+        if (!control.Wait()) { printf("MISMATCH: block of all verifying vectors rejected\n"); failures++; }
+    }
+    // that block plus one failing vector that reaches a signature comparison, a few times
+    size_t k = 0;
+    for (const Vector &bad : vs) {
+        if (bad.ok) continue;
+        const std::vector<uint8_t> raw(bad.spk.begin(), bad.spk.end()), raws(bad.sig.begin(), bad.sig.end());
+        bool has_sigop = false;
+        for (uint8_t b : raw) has_sigop = has_sigop || b == 0xac || b == 0xad || b == 0xae || b == 0xaf;
+        for (uint8_t b : raws) has_sigop = has_sigop || b == 0xac || b == 0xae;
+        if (!has_sigop || (k++ % 5) != 0) continue;
+        CCheckQueueControl<ScriptCheck> control(&queue);
+        std::vector<ScriptCheck> c;
+        for (const Vector &v : vs)
+            if (v.ok) c.emplace_back(v.spk, v.amount, v.tx.get(), 0, v.flags);
+        c.emplace(c.begin() + c.size() / 2, bad.spk, bad.amount, bad.tx.get(), 0, bad.flags);
+        control.Add(c);
+        if (control.Wait()) { printf("MISMATCH: block with a failing vector accepted\n"); failures++; }
+    }
+    queue.Quit();
+    for (auto &t : workers) t.join();
+    printf("%zu signature comparisons went to the device while the vectors ran one by one\n", comparisons);
+    if (failures) {
+        printf("vectors FAILED: %d mismatches\n", failures);
+        return 1;
+    }
+    printf("vectors ok\n");
+    return 0;
+}
+
 int main(int argc, char **argv) {
     ref_init();
+    if (argc > 2 && std::string(argv[1]) == "vectors-cpu") return run_vectors(argv[2], false);
+    if (argc > 2 && std::string(argv[1]) == "vectors") return run_vectors(argv[2], true);
     if (argc > 1 && std::string(argv[1]) == "cases") { // CPU-only: the case set and the reference's verdicts on it
         std::vector<Case> cases;
         make_cases(cases);

@@ -28,3 +28,43 @@ def test_reference_interpreter_through_checkqueue_gpu():
     out = subprocess.run([EXE], capture_output=True, text=True, timeout=600)
     assert out.returncode == 0, out.stdout[-3000:] + out.stderr[-2000:]
     assert "replay ok" in out.stdout
+
+
+def _vector_file(tmp_path):
+    import gzip
+    import json
+    import struct
+
+    vs = json.loads(gzip.open(os.path.join(ROOT, "tests", "golden", "script_tests.json.gz")).read())
+    path = tmp_path / "script_vectors.bin"
+    with open(path, "wb") as f:
+        f.write(struct.pack("<Q", len(vs)))
+        for v in vs:
+            sig, spk, tx = bytes.fromhex(v["sig"]), bytes.fromhex(v["spk"]), bytes.fromhex(v["tx"])
+            f.write(struct.pack("<IqB", v["flags"], v["amount"], 1 if v["err"] == 0 else 0))
+            for b in (sig, spk, tx):
+                f.write(struct.pack("<I", len(b)) + b)
+    return str(path), len(vs)
+
+
+@needs_exe
+def test_script_tests_json_fixture_matches_the_reference_cpu(tmp_path):
+    """tests/golden/script_tests.json.gz (the reference's src/test/data/script_tests.json as binary scripts,
+    tests/golden/make_script_vectors.py) evaluated by the reference's own VerifyScript: every expectation holds."""
+    path, n = _vector_file(tmp_path)
+    assert n > 1000
+    out = subprocess.run([EXE, "vectors-cpu", path], capture_output=True, text=True, timeout=300)
+    assert out.returncode == 0, out.stdout[-2000:] + out.stderr[-2000:]
+
+
+@needs_exe
+@pytest.mark.gpu
+def test_script_tests_json_through_checkqueue_gpu(tmp_path):
+    """The reference's own script corpus (1,108 vectors: DER / high-S / hybrid keys / NULLFAIL / FORKID / NULLDUMMY /
+    multisig / P2SH / every opcode family) through the CCheckQueue drop-in with the recording checker and the GPU: each
+    vector alone gives the expected verdict; all verifying vectors form an accepted block; adding one failing vector that
+    reaches a signature comparison makes the block fail."""
+    path, _ = _vector_file(tmp_path)
+    out = subprocess.run([EXE, "vectors", path], capture_output=True, text=True, timeout=900)
+    assert out.returncode == 0, out.stdout[-3000:] + out.stderr[-2000:]
+    assert "vectors ok" in out.stdout
