@@ -45,6 +45,7 @@ SIGNATURES = {
     "bcp_gpu_utxo_apply_block": (C.c_int, [vp, C.c_uint32, vp, sz, vp, sz, vp, vp, sz, vp, vp, vp, sz, vp, vp, vp, vp, sz, vp, vp]),
     "bcp_gpu_utxo_wait": (C.c_int, [vp, C.c_uint32, vp]),
     "bcp_gpu_utxo_block_scripts": (C.c_int, [vp, C.c_uint32, C.c_int, vp, vp, vp, C.c_uint32, vp, C.POINTER(C.c_int), vp]),
+    "bcp_gpu_utxo_fetch_spent": (C.c_int, [vp, C.c_uint32, vp, sz, vp, vp]),
     "bcp_gpu_utxo_confirm": (C.c_int, [vp, C.c_uint32]),
     "bcp_gpu_utxo_rollback": (C.c_int, [vp, C.c_uint32]),
     "bcp_block_index": (C.c_long, [vp, sz, C.c_int, vp, sz]),

@@ -656,6 +656,26 @@ BCP_API int bcp_gpu_utxo_block_scripts(bcp_utxo *u, uint32_t seq, int device, co
                                       used, script_err, all_ok, st);
 }
 
+// The spent-coin arrays of applied block seq, for a caller that left them on the device at apply time and needs them on
+// the host after all (inputs the fast path hands back to the host interpreter).  Synchronous.
+BCP_API int bcp_gpu_utxo_fetch_spent(bcp_utxo *u, uint32_t seq, uint8_t *spk_cat, size_t spk_cap, uint32_t *spk_off, int64_t *amounts) {
+    if (!u || !spk_cat || !spk_off || !amounts) return BCP_ERR_INVALID;
+    ring_slot &r = u->ring[seq % UTXO_RING];
+    if (!r.used || r.seq != seq) { bcp_set_error("bcp_gpu_utxo_fetch_spent: block %u is not pending", seq); return BCP_ERR_INVALID; }
+    BCP_CUDA(cudaSetDevice(u->device));
+    BCP_CUDA(cudaEventSynchronize(r.done));
+    const size_t total = r.h_status[ST_SPK_BYTES];
+    if (total > spk_cap || r.h_status[ST_SPK_OVERFLOW]) {
+        bcp_set_error("bcp_gpu_utxo_fetch_spent: the spent scripts of block %u need %zu bytes, the buffer holds %zu", seq, total, spk_cap);
+        return BCP_ERR_INVALID;
+    }
+    std::lock_guard<std::mutex> lk(u->mu);
+    BCP_CUDA(cudaMemcpy(amounts, r.d + r.o_amt, r.nin * 8, cudaMemcpyDeviceToHost));
+    BCP_CUDA(cudaMemcpy(spk_off, r.d + r.o_spkoff, (r.nin + 1) * 4, cudaMemcpyDeviceToHost));
+    if (total) BCP_CUDA(cudaMemcpy(spk_cat, r.d + r.o_spk, total, cudaMemcpyDeviceToHost));
+    return BCP_OK;
+}
+
 BCP_API int bcp_gpu_utxo_confirm(bcp_utxo *u, uint32_t seq) {
     if (!u) return BCP_ERR_INVALID;
     std::lock_guard<std::mutex> lk(u->mu);

@@ -290,6 +290,9 @@ BCP_API int bcp_gpu_utxo_wait(bcp_utxo *u, uint32_t seq, uint32_t status8[8]);
  * work first and returns its status words like bcp_gpu_utxo_wait; with missing inputs no script is run. */
 BCP_API int bcp_gpu_utxo_block_scripts(bcp_utxo *u, uint32_t seq, int device, const uint32_t *tx_off, const uint32_t *in_tx,
                                        const uint32_t *in_n, uint32_t flags, uint8_t *script_err, int *all_ok, uint32_t status8[8]);
+/* Copies the spent-coin arrays of applied block seq to the host after the fact (synchronous): for a caller that applied
+ * the block with NULL result arrays and then finds inputs it must evaluate on the host. */
+BCP_API int bcp_gpu_utxo_fetch_spent(bcp_utxo *u, uint32_t seq, uint8_t *spk_cat, size_t spk_cap, uint32_t *spk_off, int64_t *amounts);
 BCP_API int bcp_gpu_utxo_confirm(bcp_utxo *u, uint32_t seq);
 BCP_API int bcp_gpu_utxo_rollback(bcp_utxo *u, uint32_t seq);
 

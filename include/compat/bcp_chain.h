@@ -38,6 +38,7 @@
 #include <vector>
 
 #include "../bcp_gpu.h"
+#include "bcp_other_scripts.h"
 
 namespace bcp {
 
@@ -303,6 +304,9 @@ public:
         return n;
     }
     size_t InputsChecked() const { return nInputs; }
+    //! Who evaluates the inputs the device fast path does not (bcp_other_scripts.h).  Unset: such a block is refused with
+    //! "script-not-in-fast-path".  Called on the connecting thread, once per block at most.
+    void SetOtherScripts(OtherScripts f) { other = std::move(f); }
 
     // seconds since construction: [0] header (Equihash + hash), [1] framing scan on the connecting thread (0 when the
     // scan ran ahead), [2] waiting for the txids after the lookups, [3] the UTXO passes, [4] waiting for script checks
@@ -786,14 +790,24 @@ private:
         lastWork = (int)(&w - work);
         for (size_t g = 0; g < w.rc.size(); g++)
             if (w.rc[g] != BCP_OK) { reason = "device-error: " + w.msg[g]; return false; }
+        std::vector<OtherInput> others; // inputs that are not of the fast path's shape: decided after the ones the device decided
         for (size_t k = 0; k < (size_t)w.cur.nin; k++) {
-            if (w.errs[k] == 255) { reason = "script-not-in-fast-path (input " + std::to_string(k) + ")"; return false; }
+            if (w.errs[k] == 255) {
+                others.push_back(OtherInput{(uint32_t)k, w.cur.in_tx[k], w.cur.in_n[k], &w.spk_cat[w.spk_off[k]], w.spk_off[k + 1] - w.spk_off[k],
+                                            w.amounts[k]});
+                continue;
+            }
             if (w.errs[k] != 0) { // ConnectBlock: "blk-bad-inputs" (src/validation.cpp:2124-2128)
                 reason = "blk-bad-inputs (input " + std::to_string(k) + ", script error " + std::to_string(w.errs[k]) + ")";
                 return false;
             }
         }
-        return true;
+        if (others.empty()) return true;
+        if (!other) { reason = "script-not-in-fast-path (input " + std::to_string(others[0].input_no) + ")"; return false; }
+        std::string why;
+        if (other(w.blk, w.len, w.cur.tx_off.data(), (size_t)w.cur.ntx, others.data(), others.size(), flags, why)) return true;
+        reason = why.empty() ? "blk-bad-inputs" : why;
+        return false;
     }
     void Abandon(Work &w) { // a block whose verdict no longer matters: just let its device calls finish
         for (auto &t : w.th) t.join();
@@ -965,6 +979,7 @@ private:
     Scan ahead[NAHEAD];
     unsigned nextSlot = 0;
     Work work[2];
+    OtherScripts other;
     uint32_t blockStamp = 0;
     int lastWork = 0;
     uint8_t lastHash[32] = {0};

@@ -36,6 +36,7 @@
 #include <vector>
 
 #include "../bcp_gpu.h"
+#include "bcp_other_scripts.h"
 
 namespace bcp {
 
@@ -80,6 +81,9 @@ public:
     }
     size_t InputsChecked() const { return nInputs; }
     const uint8_t *LastBlockHash() const { return lastHash; }
+    //! Who evaluates the inputs the device fast path does not (bcp_other_scripts.h).  Unset: such a block is refused with
+    //! "script-not-in-fast-path".  Called from check threads: at most one call per block, several blocks concurrently.
+    void SetOtherScripts(OtherScripts f) { other = std::move(f); }
 
     // seconds, summed over blocks: [0] connecting thread inside bcp_gpu_utxo_apply_block, [1] connecting thread waiting
     // (for a scan, a free slot or a verdict), [2] check threads waiting for the spent-coin arrays, [3] check threads in
@@ -280,20 +284,51 @@ private:
                 j.reason = std::string("device-error: ") + bcp_gpu_last_error();
             } else {
                 j.ok = true;
+                long firstOther = -1, nOther = 0;
                 for (long k = 0; k < j.nin; k++) {
                     const uint8_t e = j.errs.p[k];
                     if (e == 0) continue;
+                    if (e == 255) { // not the fast path's shape: decided below, after the inputs the device did decide
+                        if (firstOther < 0) firstOther = k;
+                        nOther++;
+                        continue;
+                    }
                     j.ok = false;
-                    if (e == 255) j.reason = "script-not-in-fast-path (input " + std::to_string(k) + ")";
-                    else j.reason = "blk-bad-inputs (input " + std::to_string(k) + ", script error " + std::to_string(e) + ")"; // :2124-2128
+                    j.reason = "blk-bad-inputs (input " + std::to_string(k) + ", script error " + std::to_string(e) + ")"; // :2124-2128
                     break;
                 }
+                if (j.ok && nOther) j.ok = CheckOthers(j, firstOther, nOther);
             }
         }
         std::lock_guard<std::mutex> l(mu);
         phase[2] += Secs(t0, t1);
         phase[3] += Secs(t1, t2);
         phase[4] += tScripts;
+    }
+
+    // the inputs the fast path answered 255 for, through the caller's interpreter (bcp_other_scripts.h)
+    bool CheckOthers(Job &j, long firstOther, long nOther) {
+        if (!other) {
+            j.reason = "script-not-in-fast-path (input " + std::to_string(firstOther) + ")";
+            return false;
+        }
+        // the spent scripts and amounts were left on the device: fetch them now (rare path)
+        std::vector<uint8_t> spk((size_t)j.nin * 80 + 65536);
+        std::vector<uint32_t> off((size_t)j.nin + 1);
+        std::vector<int64_t> amt((size_t)j.nin);
+        if (bcp_gpu_utxo_fetch_spent(utxo, j.seq, spk.data(), spk.size(), off.data(), amt.data()) != BCP_OK) {
+            j.reason = std::string("device-error: ") + bcp_gpu_last_error();
+            return false;
+        }
+        std::vector<OtherInput> in;
+        in.reserve((size_t)nOther);
+        for (long k = firstOther; k < j.nin; k++)
+            if (j.errs.p[k] == 255)
+                in.push_back(OtherInput{(uint32_t)k, j.in_tx.p[k], j.in_n.p[k], spk.data() + off[(size_t)k], off[(size_t)k + 1] - off[(size_t)k], amt[(size_t)k]});
+        std::string why;
+        if (other(j.blk, j.len, j.tx_off.p, (size_t)j.ntx, in.data(), in.size(), flags, why)) return true;
+        j.reason = why.empty() ? "blk-bad-inputs" : why;
+        return false;
     }
 
     void Stop() {
@@ -466,6 +501,7 @@ private:
     unsigned ehN, ehK, log2Slots;
     int lanes_, nScan;
     bcp_utxo *utxo = nullptr;
+    OtherScripts other;
     size_t inflightMax = 4;
     std::vector<Job> jobs;
     std::vector<std::thread> threads;

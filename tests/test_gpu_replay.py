@@ -68,3 +68,18 @@ def test_script_tests_json_through_checkqueue_gpu(tmp_path):
     out = subprocess.run([EXE, "vectors", path], capture_output=True, text=True, timeout=900)
     assert out.returncode == 0, out.stdout[-3000:] + out.stderr[-2000:]
     assert "vectors ok" in out.stdout
+
+
+MIXED = os.path.join(ROOT, "oracle", "_ref", "test_mixed_ref")
+
+
+@pytest.mark.skipif(not os.path.exists(MIXED), reason="oracle/_ref/test_mixed_ref not built (reference sources absent)")
+@pytest.mark.gpu
+def test_mixed_blocks_connect_through_both_connectors_gpu():
+    """Blocks mixing P2PKH, pay-to-pubkey, bare multisig, P2SH multisig and P2SH-P2PKH inputs: the device fast path takes the
+    P2PKH inputs, everything else goes through the OtherScripts callback = the reference's interpreter inside the check
+    queue drop-in (signatures on the GPU); verdicts (valid block, corrupted multisig signature, wrong signature order, bad
+    P2PKH signature) equal the reference's CPU VerifyScript over all inputs; refusals leave the coin table untouched."""
+    out = subprocess.run([MIXED], capture_output=True, text=True, timeout=600)
+    assert out.returncode == 0, out.stdout[-3000:] + out.stderr[-2000:]
+    assert "mixed ok" in out.stdout
