@@ -428,7 +428,7 @@ def chain_bench(args, devices, impl="device"):
     if impl == "device":
         L.bcp_dchain_new.restype = C.c_void_p
         L.bcp_dchain_new.argtypes = [C.POINTER(C.c_int), C.c_int, C.c_uint32, C.c_uint, C.c_uint, C.c_uint, C.c_int, C.c_int, C.c_char_p, C.c_size_t]
-        lanes = 3 if len(devices) == 1 else 2
+        lanes = args.chain_lanes or (3 if len(devices) == 1 else 2)
         scan_threads = max(2, min(8, (os.cpu_count() or 4) // 2))
         h = L.bcp_dchain_new(devs, len(devices), synth.POSTFORK_FLAGS, 48, 5, 20, lanes, scan_threads, err, 256)
     else:
@@ -570,6 +570,8 @@ def main():
     ap.add_argument("--no-block", action="store_true", help="skip the secondary 8 MB block measurement (configs[2])")
     ap.add_argument("--block-txs", type=int, default=41650)
     ap.add_argument("--chain-blocks", type=int, default=100, help="blocks of the synthetic chain reindex (configs[4]); 0 = skip")
+    ap.add_argument("--chain-lanes", type=int, default=0, help="check threads per GPU of the chain section (0 = 3 on one GPU, else 2)")
+    ap.add_argument("--only", default="", help="comma list of secondary sections to run (block8mb,window,queue,equihash,sharded,chain,chain_host); empty = all")
     args = ap.parse_args()
     if args.impl == "reference":
         return run_reference(args)
@@ -672,10 +674,14 @@ def main():
         td.all_reduce(t, op=td.ReduceOp.MAX, group=hostgrp)
         return world if count else t[0].item()
 
+    only = set(x for x in args.only.split(",") if x)
+    want = lambda name: not only or name in only
     blk_section = win_section = None
     if not args.no_block:
-        blk_section = block_bench(eng, args, bcp, host_sync if dist else None)
-        win_section = window_bench(eng, args, bcp, host_sync if dist else None)
+        if want("block8mb"):
+            blk_section = block_bench(eng, args, bcp, host_sync if dist else None)
+        if want("window"):
+            win_section = window_bench(eng, args, bcp, host_sync if dist else None)
     if rank != 0:
         if dist:
             td.barrier(group=hostgrp)  # rank 0 is still measuring its secondary sections; leave together
@@ -741,11 +747,15 @@ def main():
                 win_section[k_]["frac_of_int_roofline"] = roof(win_section[k_]["gpu_inputs_per_s"])
         line["block8mb"] = blk_section
         line["block8mb_window"] = win_section
-        line["checkqueue_dropin"] = queue_dropin_bench(args)
-        line["equihash10k"] = equihash_bench(eng)
-        line["sharded_single_caller"] = sharded_single_caller_bench(args, list(range(world)), msg, pub, sig, expected)
-        if args.chain_blocks > 0:
+        if want("queue"):
+            line["checkqueue_dropin"] = queue_dropin_bench(args)
+        if want("equihash"):
+            line["equihash10k"] = equihash_bench(eng)
+        if want("sharded"):
+            line["sharded_single_caller"] = sharded_single_caller_bench(args, list(range(world)), msg, pub, sig, expected)
+        if args.chain_blocks > 0 and want("chain"):
             line["chain"] = chain_bench(args, list(range(world)), "device")
+        if args.chain_blocks > 0 and want("chain_host"):
             line["chain_host_table"] = chain_bench(args, list(range(world)), "host")
     print(json.dumps(line), flush=True)
     if dist:

@@ -9,15 +9,20 @@
 //                  32-bit words and re-aligned + byte-swapped with one PRMT per word; only the tail goes
 //                  through byte loads.  Messages of one warp are adjacent in memory, so the lines a warp
 //                  touches are shared by its lanes.
-// k_merkle_levels  256 nodes per 128-thread block, eight tree levels per launch, staged in shared
-//                  memory; a 41,650-leaf block needs two launches.
+// k_merkle_levels  256 nodes per 128-thread block, staged in shared memory, LEVELS tree levels per launch.  Three levels
+//                  (128, 64, 32 pairs: four, two, one FULL warp) is the default: with eight levels per launch the five
+//                  upper ones ran on 16, 8, 4, 2, 1 lanes of one warp, which costs a warp's full issue time each, and the
+//                  kernel sat at 0.31 of the issue rate (0.50 ms per million leaves); the price is more launches (seven
+//                  instead of three for a million leaves).  The eight-level form remains for the entry point whose scratch
+//                  is a fixed static array (it needs 1/32 of the scratch).
 #include "bcp_ctx.cuh"
 #include "sha256.cuh"
 #include <cstring>
 
 #define MERKLE_THREADS 128
 #define MERKLE_NODES 256
-#define MERKLE_LEVELS 8
+#define MERKLE_LEVELS_WIDE 3  /* default: every warp that works is full */
+#define MERKLE_LEVELS_DEEP 8  /* least scratch: one node out per 256 in */
 
 // off != nullptr: message i is data[off[i] .. off[i+1]);  off == nullptr: message i is data[i*stride .. +fixed_len)
 __global__ void __launch_bounds__(128) k_sha256d_msgs(const uint8_t *__restrict__ data, const uint32_t *__restrict__ off,
@@ -60,10 +65,11 @@ __global__ void __launch_bounds__(128) k_sha256d_msgs(const uint8_t *__restrict_
 }
 
 // in: `count` nodes of tree level `level0` (each spans 2^level0 leaves) of a tree with `nleaves` leaves.
-// out: ceil(count / 256) nodes of level level0 + 8 (or the root earlier).  A pair (L, R) at level l is
+// out: per block the 256 >> LEVELS nodes of level level0 + LEVELS it owns (fewer at the tree's edge, or the root earlier).  A pair (L, R) at level l is
 // hashed as SHA256d(L || R); a missing R (odd tail) is replaced by L.  `mutated` is raised when L == R
 // for a pair whose right node lies wholly inside the real leaves (merkle.cpp:86; the final sweep :109-140
 // never tests).
+template <int LEVELS>
 __global__ void __launch_bounds__(MERKLE_THREADS)
     k_merkle_levels(const uint32_t *__restrict__ in, size_t count, int level0, size_t nleaves, uint32_t *__restrict__ out,
                     int *__restrict__ mutated) {
@@ -78,7 +84,7 @@ __global__ void __launch_bounds__(MERKLE_THREADS)
     size_t first = base;         /* global index of this block's node 0 at the current level */
     int mut = 0;
 #pragma unroll 1
-    for (int l = 0; l < MERKLE_LEVELS && cnt > 1; l++) {
+    for (int l = 0; l < LEVELS && cnt > 1; l++) {
         const int pairs = MERKLE_NODES >> (l + 1);
         uint32_t s[8];
         bool active = false;
@@ -110,12 +116,22 @@ __global__ void __launch_bounds__(MERKLE_THREADS)
         first >>= 1;
     }
     if (mut) atomicOr(mutated, 1);
-    if (threadIdx.x < 8) out[(size_t)blockIdx.x * 8 + threadIdx.x] = __byte_perm(node[0][threadIdx.x], 0, 0x0123);
+    // the nodes this block is left with: positions first .. of the level reached (cnt nodes in all)
+    constexpr int LEFT = MERKLE_NODES >> LEVELS;
+    for (int t = threadIdx.x; t < LEFT * 8; t += MERKLE_THREADS) {
+        const size_t g = first + (size_t)(t >> 3);
+        if (g < cnt) out[g * 8 + (t & 7)] = __byte_perm(node[t >> 3][t & 7], 0, 0x0123);
+    }
 }
 
+// scratch words for a tree of n leaves: two halves, each as large as the first launch's output
+static size_t merkle_tmp_words_for(size_t n, int levels) {
+    const size_t per = MERKLE_NODES >> levels; /* nodes a full block leaves behind */
+    return 2 * (((n + MERKLE_NODES - 1) / MERKLE_NODES) * per * 8) + 16;
+}
 // root of `n` leaves already on the device; nodes ping-pong between two scratch halves
 static int merkle_dev(bcp_ctx *c, const uint8_t *d_leaves, size_t n, uint8_t *d_root32, int *d_mut, uint32_t *d_tmp,
-                      cudaStream_t st) {
+                      cudaStream_t st, int levels = MERKLE_LEVELS_WIDE) {
     BCP_CUDA(cudaMemsetAsync(d_mut, 0, sizeof(int), st));
     if (n == 0) {
         BCP_CUDA(cudaMemsetAsync(d_root32, 0, 32, st));
@@ -124,22 +140,23 @@ static int merkle_dev(bcp_ctx *c, const uint8_t *d_leaves, size_t n, uint8_t *d_
     const uint32_t *cur = reinterpret_cast<const uint32_t *>(d_leaves);
     size_t cnt = n;
     int level = 0;
-    size_t half = ((n + MERKLE_NODES - 1) / MERKLE_NODES) * 8;
+    const size_t half = (merkle_tmp_words_for(n, levels) - 16) / 2;
     uint32_t *buf[2] = {d_tmp, d_tmp + half};
     int k = 0;
     while (cnt > 1) {
         unsigned blocks = (unsigned)((cnt + MERKLE_NODES - 1) / MERKLE_NODES);
-        k_merkle_levels<<<blocks, MERKLE_THREADS, 0, st>>>(cur, cnt, level, n, buf[k], d_mut);
+        if (levels == MERKLE_LEVELS_WIDE) k_merkle_levels<MERKLE_LEVELS_WIDE><<<blocks, MERKLE_THREADS, 0, st>>>(cur, cnt, level, n, buf[k], d_mut);
+        else k_merkle_levels<MERKLE_LEVELS_DEEP><<<blocks, MERKLE_THREADS, 0, st>>>(cur, cnt, level, n, buf[k], d_mut);
         cur = buf[k];
         k ^= 1;
-        for (int l = 0; l < MERKLE_LEVELS && cnt > 1; l++) cnt = (cnt + 1) >> 1;
-        level += MERKLE_LEVELS;
+        for (int l = 0; l < levels && cnt > 1; l++) cnt = (cnt + 1) >> 1;
+        level += levels;
     }
     BCP_CUDA(cudaGetLastError());
     BCP_CUDA(cudaMemcpyAsync(d_root32, cur, 32, cudaMemcpyDeviceToDevice, st));
     return BCP_OK;
 }
-static size_t merkle_tmp_words(size_t n) { return 2 * (((n + MERKLE_NODES - 1) / MERKLE_NODES) * 8) + 16; }
+static size_t merkle_tmp_words(size_t n) { return merkle_tmp_words_for(n, MERKLE_LEVELS_WIDE); }
 
 int bcp_sha256d_offsets_dev(bcp_ctx *c, const uint8_t *d_data, const uint32_t *d_off, size_t count, uint8_t *d_out,
                             cudaStream_t st) {
@@ -208,7 +225,7 @@ BCP_API int bcp_gpu_merkle_root_dev(int device, const uint8_t *d_leaves32, size_
 // inner-node ping-pong buffers therefore live in this file-scope device array instead of a
 // caller-supplied or context-owned buffer.  Every GPU that loads the library carries the array
 // (BCP_MERKLE_STATIC_BYTES, about 256 KiB) until the process exits.
-#define BCP_MERKLE_STATIC_WORDS (2 * ((BCP_MERKLE_STATIC_MAX_LEAVES / MERKLE_NODES) * 8) + 16)
+#define BCP_MERKLE_STATIC_WORDS (2 * ((BCP_MERKLE_STATIC_MAX_LEAVES / MERKLE_NODES) * 8) + 16) /* eight levels per launch */
 static __device__ __align__(256) uint32_t g_merkle_static_scratch[BCP_MERKLE_STATIC_WORDS];
 // In host code the name above is only a handle for the symbol, not an address a kernel can use; the
 // device address is looked up once per device (with that device current) and cached here.  The cache is
@@ -247,7 +264,7 @@ BCP_API int bcp_gpu_merkle_root_dev_static(int device, const uint8_t *d_leaves32
     // Nothing in the array has to start at zero: each launch writes every node the next launch reads, and
     // the mutated flag (caller memory) is cleared by merkle_dev on every call.  Stale nodes of an earlier,
     // larger tree are never read.
-    return merkle_dev(c, d_leaves32, n, d_root32, d_mutated, scratch, stream ? (cudaStream_t)stream : c->stream);
+    return merkle_dev(c, d_leaves32, n, d_root32, d_mutated, scratch, stream ? (cudaStream_t)stream : c->stream, MERKLE_LEVELS_DEEP);
 }
 
 // Host-pointer forms.  Staging layout in c->stage: [data + pad][offsets][digests][merkle tmp][root][mutated]

@@ -376,8 +376,13 @@ BCP_API bcp_utxo *bcp_gpu_utxo_create(int device, unsigned log2_slots, size_t ar
     uint8_t *ctr = nullptr;
     if (e == cudaSuccess) e = cudaMalloc(&ctr, 256);
     if (e == cudaSuccess) e = cudaMemset(ctr, 0, 256);
-    if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&u->st, cudaStreamNonBlocking);
-    if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&u->up, cudaStreamNonBlocking);
+    // The table's kernels are small (tens of microseconds per block) and everything downstream waits for them, while the
+    // same GPU usually also runs script checks whose point kernel fills the SMs for a millisecond at a time: the table's
+    // streams get the highest priority, so its thread blocks are placed first whenever an SM has room.
+    int prLow = 0, prHigh = 0;
+    if (e == cudaSuccess) e = cudaDeviceGetStreamPriorityRange(&prLow, &prHigh);
+    if (e == cudaSuccess) e = cudaStreamCreateWithPriority(&u->st, cudaStreamNonBlocking, prHigh);
+    if (e == cudaSuccess) e = cudaStreamCreateWithPriority(&u->up, cudaStreamNonBlocking, prHigh);
     if (e == cudaSuccess) e = cudaHostAlloc(&u->h_pinned_status, UTXO_RING * ST_WORDS * sizeof(uint32_t), cudaHostAllocPortable);
     for (int k = 0; k < UTXO_RING && e == cudaSuccess; k++) {
         e = cudaEventCreateWithFlags(&u->ring[k].uploaded, cudaEventDisableTiming);
