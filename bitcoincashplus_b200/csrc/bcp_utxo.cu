@@ -219,7 +219,9 @@ __global__ void __launch_bounds__(128)
     }
 }
 
-// spk_off[0..n] = exclusive prefix sums of lens (one block walks the array in tiles of its size; n is a block's input count)
+// spk_off[0..n] = exclusive prefix sums of lens.  One block walks the array in tiles of 1024 threads x 8 items (a block of
+// 41,650 inputs is six tiles); n is a block's input count.
+#define UTXO_SCAN_ITEMS 8
 __global__ void __launch_bounds__(1024) k_utxo_offsets(const uint32_t *__restrict__ lens, size_t n, uint32_t *__restrict__ spk_off,
                                                        uint32_t *__restrict__ status) {
     __shared__ uint32_t warp_sum[32];
@@ -227,10 +229,15 @@ __global__ void __launch_bounds__(1024) k_utxo_offsets(const uint32_t *__restric
     if (threadIdx.x == 0) carry = 0;
     __syncthreads();
     const unsigned lane = threadIdx.x & 31, w = threadIdx.x >> 5;
-    for (size_t base = 0; base < n; base += blockDim.x) {
-        const size_t i = base + threadIdx.x;
-        const uint32_t v = i < n ? lens[i] : 0u;
-        uint32_t x = v;
+    for (size_t base = 0; base < n; base += (size_t)blockDim.x * UTXO_SCAN_ITEMS) {
+        const size_t i0 = base + (size_t)threadIdx.x * UTXO_SCAN_ITEMS;
+        uint32_t v[UTXO_SCAN_ITEMS], mine = 0;
+#pragma unroll
+        for (int k = 0; k < UTXO_SCAN_ITEMS; k++) {
+            v[k] = i0 + k < n ? lens[i0 + k] : 0u;
+            mine += v[k];
+        }
+        uint32_t x = mine;
 #pragma unroll
         for (int d = 1; d < 32; d <<= 1) {
             const uint32_t y = __shfl_up_sync(0xFFFFFFFFu, x, d);
@@ -248,8 +255,12 @@ __global__ void __launch_bounds__(1024) k_utxo_offsets(const uint32_t *__restric
             warp_sum[lane] = s; /* inclusive over warps */
         }
         __syncthreads();
-        const uint32_t before = carry + (w ? warp_sum[w - 1] : 0u) + x - v;
-        if (i < n) spk_off[i] = before;
+        uint32_t run = carry + (w ? warp_sum[w - 1] : 0u) + x - mine;
+#pragma unroll
+        for (int k = 0; k < UTXO_SCAN_ITEMS; k++) {
+            if (i0 + k < n) spk_off[i0 + k] = run;
+            run += v[k];
+        }
         __syncthreads();
         if (threadIdx.x == blockDim.x - 1) carry += warp_sum[31];
         __syncthreads();
@@ -331,6 +342,9 @@ struct ring_slot {
     cudaEvent_t uploaded = nullptr, done = nullptr, reclaimed = nullptr;
     bool reclaim_pending = false;
     // host destinations of the results
+    uint8_t *h_root32 = nullptr;
+    int *h_mutated = nullptr;
+    cudaEvent_t hashed = nullptr, merkled = nullptr;
     uint32_t *h_status = nullptr;
     uint8_t *h_spk_cat = nullptr;
     size_t spk_cap = 0, spk_copied = 0, o_spk = 0;
@@ -342,11 +356,11 @@ struct bcp_utxo {
     bcp_ctx *ctx = nullptr;
     utxo_dev T{};
     unsigned log2_slots = 0;
-    cudaStream_t st = nullptr, up = nullptr;
+    cudaStream_t st = nullptr, up = nullptr, aux = nullptr; /* table kernels | uploads | Merkle reductions */
     uint32_t confirmed = 0;
     ring_slot ring[UTXO_RING];
     uint32_t *d_seed_status = nullptr;
-    uint32_t *h_pinned_status = nullptr; /* UTXO_RING x ST_WORDS, pinned */
+    uint32_t *h_pinned_status = nullptr; /* UTXO_RING x 32 words, pinned: per pending block status[8] | root[32 bytes] | mutated */
     bool peer_tried[BCP_MAX_DEVICES] = {false}; /* peer access between the table's GPU and that GPU has been asked for */
     std::mutex mu;
 };
@@ -383,11 +397,14 @@ BCP_API bcp_utxo *bcp_gpu_utxo_create(int device, unsigned log2_slots, size_t ar
     if (e == cudaSuccess) e = cudaDeviceGetStreamPriorityRange(&prLow, &prHigh);
     if (e == cudaSuccess) e = cudaStreamCreateWithPriority(&u->st, cudaStreamNonBlocking, prHigh);
     if (e == cudaSuccess) e = cudaStreamCreateWithPriority(&u->up, cudaStreamNonBlocking, prHigh);
-    if (e == cudaSuccess) e = cudaHostAlloc(&u->h_pinned_status, UTXO_RING * ST_WORDS * sizeof(uint32_t), cudaHostAllocPortable);
+    if (e == cudaSuccess) e = cudaStreamCreateWithPriority(&u->aux, cudaStreamNonBlocking, prHigh);
+    if (e == cudaSuccess) e = cudaHostAlloc(&u->h_pinned_status, UTXO_RING * 32 * sizeof(uint32_t), cudaHostAllocPortable);
     for (int k = 0; k < UTXO_RING && e == cudaSuccess; k++) {
         e = cudaEventCreateWithFlags(&u->ring[k].uploaded, cudaEventDisableTiming);
         if (e == cudaSuccess) e = cudaEventCreateWithFlags(&u->ring[k].done, cudaEventDisableTiming);
         if (e == cudaSuccess) e = cudaEventCreateWithFlags(&u->ring[k].reclaimed, cudaEventDisableTiming);
+        if (e == cudaSuccess) e = cudaEventCreateWithFlags(&u->ring[k].hashed, cudaEventDisableTiming);
+        if (e == cudaSuccess) e = cudaEventCreateWithFlags(&u->ring[k].merkled, cudaEventDisableTiming);
     }
     if (e != cudaSuccess) {
         bcp_cuda_fail(e, "bcp_gpu_utxo_create");
@@ -407,11 +424,14 @@ BCP_API void bcp_gpu_utxo_destroy(bcp_utxo *u) {
     cudaSetDevice(u->device);
     if (u->st) cudaStreamSynchronize(u->st);
     if (u->up) cudaStreamSynchronize(u->up);
+    if (u->aux) cudaStreamSynchronize(u->aux);
     for (int k = 0; k < UTXO_RING; k++) {
         if (u->ring[k].d) cudaFree(u->ring[k].d);
         if (u->ring[k].uploaded) cudaEventDestroy(u->ring[k].uploaded);
         if (u->ring[k].done) cudaEventDestroy(u->ring[k].done);
         if (u->ring[k].reclaimed) cudaEventDestroy(u->ring[k].reclaimed);
+        if (u->ring[k].hashed) cudaEventDestroy(u->ring[k].hashed);
+        if (u->ring[k].merkled) cudaEventDestroy(u->ring[k].merkled);
     }
     if (u->T.slots) cudaFree(u->T.slots);
     if (u->T.arena) cudaFree(u->T.arena);
@@ -419,6 +439,7 @@ BCP_API void bcp_gpu_utxo_destroy(bcp_utxo *u) {
     if (u->h_pinned_status) cudaFreeHost(u->h_pinned_status);
     if (u->st) cudaStreamDestroy(u->st);
     if (u->up) cudaStreamDestroy(u->up);
+    if (u->aux) cudaStreamDestroy(u->aux);
     delete u;
 }
 
@@ -503,14 +524,15 @@ BCP_API int bcp_gpu_utxo_apply_block(bcp_utxo *u, uint32_t seq, const uint8_t *b
     const size_t o_outn = o; o += up256(nout * 4 + 4);
     const size_t o_txid = o; o += up256(ntx * 32 + 32);
     const size_t o_mtmp = o; o += up256(bcp_merkle_tmp_words(ntx) * 4);
-    const size_t o_root = o; o += 256; /* root[32], mutated(int) */
-    const size_t o_stat = o; o += 256;
+    const size_t o_stat = o; o += 256; /* status[8 words] | root[32 bytes] | mutated(int): one copy brings all three home */
+    const size_t o_root = o_stat + ST_WORDS * 4;
     const size_t o_recin = o; o += up256(nin * 4 + 4);
     const size_t o_recout = o; o += up256(nout * 4 + 4);
     const size_t o_lens = o; o += up256(nin * 4 + 4);
     if (o > r.cap) { /* grow-only; happens while the first blocks of a run pass through */
         BCP_CUDA(cudaStreamSynchronize(u->st));
         BCP_CUDA(cudaStreamSynchronize(u->up));
+        BCP_CUDA(cudaStreamSynchronize(u->aux));
         if (r.d) BCP_CUDA(cudaFree(r.d));
         r.d = nullptr;
         r.cap = 0;
@@ -543,8 +565,13 @@ BCP_API int bcp_gpu_utxo_apply_block(bcp_utxo *u, uint32_t seq, const uint8_t *b
     BCP_CUDA(cudaMemsetAsync(d_stat + ST_FIRST_MISSING, 0xFF, 4, st));
     int rc = bcp_sha256d_offsets_dev(u->ctx, d + o_blk, reinterpret_cast<uint32_t *>(d + o_txoff), ntx, d + o_txid, st);
     if (rc != BCP_OK) return rc;
-    rc = bcp_merkle_dev(u->ctx, d + o_txid, ntx, d + o_root, reinterpret_cast<int *>(d + o_root + 32), reinterpret_cast<uint32_t *>(d + o_mtmp), st);
+    // the Merkle reduction (a chain of small launches, each as long as its three tree levels) needs the txids only: it
+    // runs on the third stream while the table kernels go on
+    BCP_CUDA(cudaEventRecord(r.hashed, st));
+    BCP_CUDA(cudaStreamWaitEvent(u->aux, r.hashed, 0));
+    rc = bcp_merkle_dev(u->ctx, d + o_txid, ntx, d + o_root, reinterpret_cast<int *>(d + o_root + 32), reinterpret_cast<uint32_t *>(d + o_mtmp), u->aux);
     if (rc != BCP_OK) return rc;
+    BCP_CUDA(cudaEventRecord(r.merkled, u->aux));
     if (nout)
         k_utxo_insert<<<(unsigned)((nout + 127) / 128), 128, 0, st>>>(u->T, seq, u->confirmed, d + o_blk, d + o_txid,
                                                                      reinterpret_cast<uint32_t *>(d + o_outoff), reinterpret_cast<uint32_t *>(d + o_outtx),
@@ -562,10 +589,9 @@ BCP_API int bcp_gpu_utxo_apply_block(bcp_utxo *u, uint32_t seq, const uint8_t *b
     BCP_CUDA(cudaGetLastError());
     // results to the host: the fixed-size ones now; of the scripts as much as P2PKH-sized coins would need (the rest, if the
     // block spent longer scripts, is fetched by bcp_gpu_utxo_wait once the total is known)
-    uint32_t *hst = u->h_pinned_status + (seq % UTXO_RING) * ST_WORDS;
-    BCP_CUDA(cudaMemcpyAsync(hst, d_stat, ST_WORDS * 4, cudaMemcpyDeviceToHost, st));
-    BCP_CUDA(cudaMemcpyAsync(root32, d + o_root, 32, cudaMemcpyDeviceToHost, st));
-    BCP_CUDA(cudaMemcpyAsync(mutated, d + o_root + 32, sizeof(int), cudaMemcpyDeviceToHost, st));
+    uint32_t *hst = u->h_pinned_status + (seq % UTXO_RING) * 32;
+    BCP_CUDA(cudaStreamWaitEvent(st, r.merkled, 0)); /* the Merkle root ran beside the table kernels on the third stream */
+    BCP_CUDA(cudaMemcpyAsync(hst, d_stat, ST_WORDS * 4 + 32 + 4, cudaMemcpyDeviceToHost, st));
     if (txids) BCP_CUDA(cudaMemcpyAsync(txids, d + o_txid, ntx * 32, cudaMemcpyDeviceToHost, st));
     size_t first = 0;
     if (!spk_cat) spk_cap = 0; /* the spent-coin arrays stay on the device (bcp_gpu_utxo_block_scripts reads them there) */
@@ -582,6 +608,8 @@ BCP_API int bcp_gpu_utxo_apply_block(bcp_utxo *u, uint32_t seq, const uint8_t *b
     r.o_rec_in = o_recin; r.o_rec_out = o_recout;
     r.o_txoff = o_txoff; r.o_inoff = o_inoff; r.o_intx = o_intx; r.o_amt = o_amt; r.o_spkoff = o_spkoff; r.in_area = in_area;
     r.h_status = hst;
+    r.h_root32 = root32;
+    r.h_mutated = mutated;
     r.h_spk_cat = spk_cat; r.spk_cap = spk_cap; r.spk_copied = first; r.o_spk = o_spk;
     return BCP_OK;
 }
@@ -593,6 +621,8 @@ BCP_API int bcp_gpu_utxo_wait(bcp_utxo *u, uint32_t seq, uint32_t status8[8]) {
     BCP_CUDA(cudaSetDevice(u->device));
     BCP_CUDA(cudaEventSynchronize(r.done));
     memcpy(status8, r.h_status, ST_WORDS * 4);
+    memcpy(r.h_root32, r.h_status + ST_WORDS, 32);
+    memcpy(r.h_mutated, r.h_status + ST_WORDS + 8, sizeof(int));
     const size_t total = status8[ST_SPK_BYTES];
     if (!r.h_spk_cat) return BCP_OK; /* the spent-coin arrays were left on the device */
     if (total > r.spk_cap) {
@@ -624,6 +654,8 @@ BCP_API int bcp_gpu_utxo_block_scripts(bcp_utxo *u, uint32_t seq, int device, co
     BCP_CUDA(cudaSetDevice(u->device));
     BCP_CUDA(cudaEventSynchronize(r.done));
     memcpy(status8, r.h_status, ST_WORDS * 4);
+    memcpy(r.h_root32, r.h_status + ST_WORDS, 32);
+    memcpy(r.h_mutated, r.h_status + ST_WORDS + 8, sizeof(int));
     if (status8[ST_SPK_OVERFLOW]) {
         bcp_set_error("bcp_gpu_utxo_block_scripts: the spent scripts of block %u (%u bytes) do not fit the device buffer", seq, status8[ST_SPK_BYTES]);
         return BCP_ERR_INVALID;

@@ -62,7 +62,15 @@ public:
                 if (bcp_gpu_init(BCP_DEVICE_LANE(d & 0xFF, l)) != BCP_OK) { err = bcp_gpu_last_error(); return false; }
         utxo = bcp_gpu_utxo_create(devs[0] & 0xFF, log2Slots, (size_t)64 << 20);
         if (!utxo) { err = bcp_gpu_last_error(); return false; }
-        const size_t W = devs.size() * (size_t)lanes_;
+        // The check threads, in the order blocks are dealt to them: lane by lane across the GPUs, so that consecutive
+        // blocks go to different GPUs.  With more than one GPU the table's GPU gets one check thread less: its SMs must
+        // have room for the table's kernels, which every other block waits for (a sub-wave point kernel holds the
+        // registers of the SMs it runs on for a millisecond; two of them at once fill the chip).
+        workers.clear();
+        for (int l = 0; l < lanes_; l++)
+            for (size_t g = 0; g < devs.size(); g++)
+                if (!(devs.size() > 1 && g == 0 && l == lanes_ - 1 && lanes_ > 1)) workers.push_back(BCP_DEVICE_LANE(devs[g] & 0xFF, l));
+        const size_t W = workers.size();
         inflightMax = W + 2 < 14 ? W + 2 : 14; /* the table keeps undo records of at most 16 pending blocks */
         jobs.resize(inflightMax + (size_t)nScan + 2);
         return true;
@@ -347,7 +355,7 @@ private:
         if (!FlushSeeds(reason)) return 0;
         const long n = (long)blocks.size();
         if (n == 0) return 0;
-        const size_t R = jobs.size(), W = devs.size() * (size_t)lanes_;
+        const size_t R = jobs.size(), W = workers.size();
         for (Job &j : jobs) { j.state = FREE; j.index = -1; }
         long nextScan = 0;     // next block a scan thread takes
         long nextApply = 0;    // next block the connecting thread applies
@@ -381,10 +389,10 @@ private:
                     cv.notify_all();
                 }
             });
-        // check threads: thread w owns lane w / G of device w % G and the blocks b with b % W == w
+        // check threads: thread w owns one (GPU, lane) pair and the blocks b with b % W == w
         for (size_t w = 0; w < W; w++)
             threads.emplace_back([&, w] {
-                const int dev = BCP_DEVICE_LANE(devs[w % devs.size()] & 0xFF, (int)(w / devs.size()));
+                const int dev = workers[w];
                 for (long b = (long)w;; b += (long)W) {
                     {
                         std::unique_lock<std::mutex> l(mu);
@@ -497,6 +505,7 @@ private:
     }
 
     std::vector<int> devs;
+    std::vector<int> workers; // (GPU, lane) of each check thread
     uint32_t flags;
     unsigned ehN, ehK, log2Slots;
     int lanes_, nScan;
