@@ -429,8 +429,8 @@ def chain_bench(args, devices, impl="device"):
         L.bcp_dchain_new.restype = C.c_void_p
         L.bcp_dchain_new.argtypes = [C.POINTER(C.c_int), C.c_int, C.c_uint32, C.c_uint, C.c_uint, C.c_uint, C.c_int, C.c_int, C.c_char_p, C.c_size_t]
         lanes = args.chain_lanes or (3 if len(devices) == 1 else 2)
-        scan_threads = max(2, min(8, (os.cpu_count() or 4) // 2))
-        h = L.bcp_dchain_new(devs, len(devices), synth.POSTFORK_FLAGS, 48, 5, 20, lanes, scan_threads, err, 256)
+        scan_threads = max(2, min(8, (os.cpu_count() or 4) // 4))
+        h = L.bcp_dchain_new(devs, len(devices), synth.POSTFORK_FLAGS, 48, 5, 22, lanes, scan_threads, err, 256)
     else:
         L.bcp_chain_new.restype = C.c_void_p
         L.bcp_chain_new.argtypes = [C.POINTER(C.c_int), C.c_int, C.c_uint32, C.c_uint, C.c_uint, C.c_char_p, C.c_size_t]

@@ -221,7 +221,10 @@ int bcp_block_scripts_resident(bcp_ctx *c, const uint8_t *d_blk, const uint32_t 
     BCP_CUDA(cudaMemcpyAsync(script_err, d + o_err, nin, cudaMemcpyDeviceToHost, st));
     int a = 0;
     BCP_CUDA(cudaMemcpyAsync(&a, d + o_flag, sizeof(int), cudaMemcpyDeviceToHost, st));
-    BCP_CUDA(cudaStreamSynchronize(st));
+    // this path is driven by one host thread per (GPU, lane) next to scan threads and a connecting thread — more threads
+    // than cores on a small host — so the wait sleeps on a blocking-sync event instead of spinning in cudaStreamSynchronize
+    BCP_CUDA(cudaEventRecord(c->ev[3], st));
+    BCP_CUDA(cudaEventSynchronize(c->ev[3]));
     if (all_ok) *all_ok = a ? 1 : 0;
     return BCP_OK;
 }

@@ -109,7 +109,8 @@ static int init_locked(int device, int lane) {
     c->sm_count = prop.multiProcessorCount;
     BCP_CUDA(cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking));
     BCP_CUDA(cudaStreamCreateWithFlags(&c->copy_stream, cudaStreamNonBlocking));
-    for (int i = 0; i < 4; i++) BCP_CUDA(cudaEventCreateWithFlags(&c->ev[i], cudaEventDisableTiming));
+    for (int i = 0; i < 4; i++) // ev[3] is the one host threads sleep on (blocking sync): pipelines with more threads than cores
+        BCP_CUDA(cudaEventCreateWithFlags(&c->ev[i], cudaEventDisableTiming | (i == 3 ? cudaEventBlockingSync : 0)));
     if (lane == 0) {
         int rc = bcp_fe_selftest(c); // a few hundred crafted operand pairs, ~0.1 ms: refuse to start on a wrong answer
         if (rc != BCP_OK) return rc;

@@ -215,7 +215,7 @@ __global__ void __launch_bounds__(128)
         amounts[i] = 0;
         lens[i] = 0;
         atomicAdd(&status[ST_MISSING], 1u);
-        atomicMin(&status[ST_FIRST_MISSING], (uint32_t)i);
+        atomicMax(&status[ST_FIRST_MISSING], ~(uint32_t)i); /* the smallest index wins; decoded by the host side */
     }
 }
 
@@ -312,22 +312,32 @@ __global__ void __launch_bounds__(128) k_utxo_undo(utxo_dev T, uint32_t seq, con
     }
 }
 
-// Run when a block becomes final, over the coins it spent.  Tombstones only exist so that probe runs of other keys are
-// not cut; one whose NEXT slot is empty ends a run and cuts nothing, so it is emptied — and then the final tombstones
-// before it, which now end the run in turn.  In a table kept well under half full almost every spent coin is freed this way
-// and probe runs stay a slot or two long however many blocks pass through; the rest is reused by insertions that walk
-// over it.  Tombstones of blocks that are still pending are never touched: a rollback finds its coins by slot number.
+// Run when a block becomes final, over the coins it spent.  A tombstone only exists so that the probe runs of OTHER coins
+// are not cut: coin j (home slot h, stored at j) needs every slot from h to j to be non-empty.  So the tombstone at i may be
+// emptied iff no coin stored after it in the same run has i on its path, i.e. iff every later entry of the run that may
+// still have to be found — live coins, and the spent coins of blocks that are not final yet (a rollback makes them live
+// again) — has its home behind i.  Each thread decides that for one tombstone by walking to the end of the run.  The
+// decisions are independent of one another (emptying a slot that is on nobody's path changes nobody's path), so a whole
+// block's tombstones go in one launch.  In a table kept under half full runs are a few slots long and almost every spent
+// coin is freed this way; what stays is reused by insertions that walk over it (utxo_put).
 __global__ void __launch_bounds__(128) k_utxo_reclaim(utxo_dev T, uint32_t seq, const uint32_t *__restrict__ rec_in, size_t nin) {
-    const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= nin) return;
-    uint32_t idx = rec_in[i];
-    if (idx == UTXO_NONE) return;
-    for (uint32_t steps = 0; steps <= T.mask; steps++) {
-        utxo_slot *s = T.slots + idx;
-        if (ld_state(s) != UTXO_SPENT || s->spent_seq > seq) return; /* seq = the newest final block */
-        if (ld_state(T.slots + ((idx + 1) & T.mask)) != UTXO_EMPTY) return;
-        *reinterpret_cast<volatile uint32_t *>(&s->state) = UTXO_EMPTY;
-        idx = (idx + T.mask) & T.mask;
+    const size_t k = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (k >= nin) return;
+    const uint32_t i = rec_in[k];
+    if (i == UTXO_NONE) return;
+    utxo_slot *s = T.slots + i;
+    if (ld_state(s) != UTXO_SPENT || s->spent_seq > seq) return; /* seq = the newest final block */
+    uint32_t j = (i + 1) & T.mask;
+    for (uint32_t steps = 0; steps < 512; steps++, j = (j + 1) & T.mask) {
+        const utxo_slot *e = T.slots + j;
+        const uint32_t st = ld_state(e);
+        if (st == UTXO_EMPTY) { /* end of the run: nobody needs slot i */
+            *reinterpret_cast<volatile uint32_t *>(&s->state) = UTXO_EMPTY;
+            return;
+        }
+        if (st == UTXO_SPENT && e->spent_seq <= seq) continue; /* a final tombstone never has to be found again */
+        const uint32_t h = utxo_home(e->key, T.mask);
+        if (((i - h) & T.mask) <= ((j - h) & T.mask)) return; /* slot i lies between that coin's home and the coin */
     }
 }
 
@@ -401,7 +411,7 @@ BCP_API bcp_utxo *bcp_gpu_utxo_create(int device, unsigned log2_slots, size_t ar
     if (e == cudaSuccess) e = cudaHostAlloc(&u->h_pinned_status, UTXO_RING * 32 * sizeof(uint32_t), cudaHostAllocPortable);
     for (int k = 0; k < UTXO_RING && e == cudaSuccess; k++) {
         e = cudaEventCreateWithFlags(&u->ring[k].uploaded, cudaEventDisableTiming);
-        if (e == cudaSuccess) e = cudaEventCreateWithFlags(&u->ring[k].done, cudaEventDisableTiming);
+        if (e == cudaSuccess) e = cudaEventCreateWithFlags(&u->ring[k].done, cudaEventDisableTiming | cudaEventBlockingSync); /* waited for by host threads: sleep, do not spin */
         if (e == cudaSuccess) e = cudaEventCreateWithFlags(&u->ring[k].reclaimed, cudaEventDisableTiming);
         if (e == cudaSuccess) e = cudaEventCreateWithFlags(&u->ring[k].hashed, cudaEventDisableTiming);
         if (e == cudaSuccess) e = cudaEventCreateWithFlags(&u->ring[k].merkled, cudaEventDisableTiming);
@@ -561,8 +571,7 @@ BCP_API int bcp_gpu_utxo_apply_block(bcp_utxo *u, uint32_t seq, const uint8_t *b
     cudaStream_t st = u->st;
     BCP_CUDA(cudaStreamWaitEvent(st, r.uploaded, 0));
     uint32_t *d_stat = reinterpret_cast<uint32_t *>(d + o_stat);
-    BCP_CUDA(cudaMemsetAsync(d_stat, 0, ST_WORDS * 4, st));
-    BCP_CUDA(cudaMemsetAsync(d_stat + ST_FIRST_MISSING, 0xFF, 4, st));
+    BCP_CUDA(cudaMemsetAsync(d_stat, 0, ST_WORDS * 4, st)); /* [ST_FIRST_MISSING] holds ~index under atomicMax: 0 = none */
     int rc = bcp_sha256d_offsets_dev(u->ctx, d + o_blk, reinterpret_cast<uint32_t *>(d + o_txoff), ntx, d + o_txid, st);
     if (rc != BCP_OK) return rc;
     // the Merkle reduction (a chain of small launches, each as long as its three tree levels) needs the txids only: it
@@ -621,6 +630,7 @@ BCP_API int bcp_gpu_utxo_wait(bcp_utxo *u, uint32_t seq, uint32_t status8[8]) {
     BCP_CUDA(cudaSetDevice(u->device));
     BCP_CUDA(cudaEventSynchronize(r.done));
     memcpy(status8, r.h_status, ST_WORDS * 4);
+    status8[ST_FIRST_MISSING] = ~status8[ST_FIRST_MISSING]; /* 0xFFFFFFFF when nothing is missing */
     memcpy(r.h_root32, r.h_status + ST_WORDS, 32);
     memcpy(r.h_mutated, r.h_status + ST_WORDS + 8, sizeof(int));
     const size_t total = status8[ST_SPK_BYTES];
@@ -654,6 +664,7 @@ BCP_API int bcp_gpu_utxo_block_scripts(bcp_utxo *u, uint32_t seq, int device, co
     BCP_CUDA(cudaSetDevice(u->device));
     BCP_CUDA(cudaEventSynchronize(r.done));
     memcpy(status8, r.h_status, ST_WORDS * 4);
+    status8[ST_FIRST_MISSING] = ~status8[ST_FIRST_MISSING];
     memcpy(r.h_root32, r.h_status + ST_WORDS, 32);
     memcpy(r.h_mutated, r.h_status + ST_WORDS + 8, sizeof(int));
     if (status8[ST_SPK_OVERFLOW]) {
