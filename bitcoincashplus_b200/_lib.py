@@ -38,6 +38,8 @@ SIGNATURES = {
     "bcp_gpu_ecdsa_recover_batch": (C.c_int, [C.c_int, vp, vp, vp, sz, vp, vp]),
     "bcp_gpu_pubkey_tweak_add_batch": (C.c_int, [C.c_int, vp, vp, sz, vp, vp]),
     "bcp_der_lax_parse": (C.c_int, [vp, sz, vp]),
+    "bcp_block_index_rules": (C.c_long, [vp, sz, C.c_int, vp, vp, sz, vp, vp, vp, sz, vp, vp, vp, vp, sz, vp, vp, vp, vp]),
+    "bcp_block_rule_name": (C.c_char_p, [C.c_int]),
     "bcp_gpu_utxo_create": (vp, [C.c_int, C.c_uint, sz]),
     "bcp_gpu_utxo_destroy": (None, [vp]),
     "bcp_gpu_utxo_add_coins": (C.c_int, [vp, vp, vp, vp, vp, sz]),

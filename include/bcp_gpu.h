@@ -181,6 +181,16 @@ BCP_API long bcp_block_index_full(const uint8_t *blk, size_t len, int legacy_hea
                                   size_t max_tx, uint32_t *in_off, uint32_t *in_tx, uint32_t *in_n, size_t max_inputs,
                                   long *ntx_out, uint32_t *out_off, uint32_t *out_tx, uint32_t *out_n, size_t max_outputs,
                                   long *nout_out, uint64_t *in_key);
+/* The same scan applying, in the same pass, CheckBlock's context-free transaction rules (src/validation.cpp:3255-3330 ->
+ * CheckCoinbase :531-549, CheckRegularTransaction :551-570, CheckTransactionCommon :476-529) in the reference's order.
+ * *rule = 0 or the first violation: 1 bad-cb-missing, 2 bad-tx-coinbase, 3 bad-txns-vin-empty, 4 bad-txns-vout-empty,
+ * 5 bad-txns-oversize, 6 bad-txns-vout-negative, 7 bad-txns-vout-toolarge, 8 bad-txns-txouttotal-toolarge, 9 bad-cb-length,
+ * 10 bad-txns-prevout-null (bcp_block_rule_name gives the string); *rule_tx = the transaction.  Not covered: sigop counts. */
+BCP_API long bcp_block_index_rules(const uint8_t *blk, size_t len, int legacy_header, uint32_t *tx_off, uint32_t *tx_out_off,
+                                   size_t max_tx, uint32_t *in_off, uint32_t *in_tx, uint32_t *in_n, size_t max_inputs,
+                                   long *ntx_out, uint32_t *out_off, uint32_t *out_tx, uint32_t *out_n, size_t max_outputs,
+                                   long *nout_out, uint64_t *in_key, int *rule, long *rule_tx);
+BCP_API const char *bcp_block_rule_name(int rule);
 /* The script checks alone, for any subset of a block's inputs chosen by the caller (arrays describe the subset;
  * spk_off may point into a larger offsets array).  This is the unit that shards across GPUs: one call per device
  * over its index range, verdicts AND-ed on the host like `fAllOk &= fOk` (src/checkqueue.h:77).  The subset must be

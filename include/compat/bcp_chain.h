@@ -417,58 +417,6 @@ private:
         std::string errTx, errEq;
         double frameSecs = 0, deviceSecs = 0; // time this slot's thread spent in each part (diagnostics)
         const char *structErr = nullptr;      // first structure rule of CheckBlock the block breaks (reference reject string)
-        // CheckBlock's context-free transaction rules, from the framing arrays (src/validation.cpp:3255-3330 calling
-        // CheckCoinbase :531-549 and CheckRegularTransaction :551-570, both over CheckTransactionCommon :476-529), in
-        // the reference's order: the coinbase first, then every other transaction in turn.
-        void CheckStructure(const uint8_t *b) {
-            structErr = nullptr;
-            if (nin < 0 || ntx < 1) { structErr = "bad-cb-missing"; return; }
-            static const int64_t MAX_MONEY_SAT = 21000000ll * 100000000ll; // src/amount.h:127
-            size_t o = 0, i = 0; // cursors into the flat output / input lists (both in block order)
-            for (long t = 0; t < ntx; t++) {
-                size_t pos = (size_t)tx_off[(size_t)t] + 4;
-                const uint64_t n_in = ReadCompact(b, pos);
-                bool cb = false;
-                uint64_t cbScriptLen = 0;
-                if (n_in == 1) {
-                    cb = true;
-                    for (int k = 0; k < 32; k++) cb = cb && b[pos + k] == 0;
-                    for (int k = 32; k < 36; k++) cb = cb && b[pos + k] == 0xFF;
-                    size_t q = pos + 36;
-                    cbScriptLen = ReadCompact(b, q);
-                }
-                size_t po = tx_out_off[(size_t)t];
-                const uint64_t n_out = ReadCompact(b, po);
-                const char *e = nullptr;
-                if (t == 0 && !cb) e = "bad-cb-missing";
-                else if (t > 0 && cb) e = "bad-tx-coinbase";
-                else if (n_in == 0) e = "bad-txns-vin-empty";
-                else if (n_out == 0) e = "bad-txns-vout-empty";
-                else if (tx_off[(size_t)t + 1] - tx_off[(size_t)t] > 1000000u) e = "bad-txns-oversize"; // MAX_TX_SIZE, consensus.h:14
-                int64_t total = 0;
-                for (; o < (size_t)nout && out_tx[o] == (uint32_t)t; o++) {
-                    if (e) continue;
-                    int64_t v;
-                    memcpy(&v, b + out_off[o], 8);
-                    if (v < 0) e = "bad-txns-vout-negative";
-                    else if (v > MAX_MONEY_SAT) e = "bad-txns-vout-toolarge";
-                    else if ((total += v) > MAX_MONEY_SAT) e = "bad-txns-txouttotal-toolarge";
-                }
-                if (!e && t == 0 && (cbScriptLen < 2 || cbScriptLen > 100)) e = "bad-cb-length";
-                for (; i < (size_t)nin && in_tx[i] == (uint32_t)t; i++) { // listed inputs = those of non-coinbase-shaped txs
-                    if (e) continue;
-                    const uint8_t *op = b + in_off[i];
-                    uint64_t h8;
-                    memcpy(&h8, op, 8);
-                    if (h8 != 0) continue;
-                    bool null = true;
-                    for (int k = 8; k < 32; k++) null = null && op[k] == 0;
-                    for (int k = 32; k < 36; k++) null = null && op[k] == 0xFF;
-                    if (null) e = "bad-txns-prevout-null";
-                }
-                if (e) { structErr = e; return; }
-            }
-        }
         void Device(int dev, unsigned ehN, unsigned ehK, int shardBits) {
             const auto td0 = std::chrono::steady_clock::now();
             const size_t soln = ehN ? ((size_t)1 << ehK) * (ehN / (ehK + 1) + 1) / 8 : 0;
@@ -514,8 +462,13 @@ private:
             in_off.need(max_in); in_tx.need(max_in); in_n.need(max_in); in_key.need(max_in);
             out_off.need(max_out); out_tx.need(max_out); out_n.need(max_out);
             ntx = nout = 0;
-            nin = bcp_block_index_full(b, l, 0, tx_off.data(), tx_out_off.data(), max_tx, in_off.data(), in_tx.data(), in_n.data(),
-                                       max_in, &ntx, out_off.data(), out_tx.data(), out_n.data(), max_out, &nout, in_key.data());
+            // the scan applies CheckBlock's context-free transaction rules while it has the bytes in the cache
+            int rule = 0;
+            long ruleTx = -1;
+            nin = bcp_block_index_rules(b, l, 0, tx_off.data(), tx_out_off.data(), max_tx, in_off.data(), in_tx.data(), in_n.data(),
+                                        max_in, &ntx, out_off.data(), out_tx.data(), out_n.data(), max_out, &nout, in_key.data(), &rule,
+                                        &ruleTx);
+            structErr = (nin >= 0 && rule) ? bcp_block_rule_name(rule) : nullptr;
             // counting sort of the inputs by shard, here (on the scan-ahead thread) so that each worker of pass A only
             // ever touches its own inputs
             const size_t S = (size_t)1 << shardBits;
@@ -533,7 +486,6 @@ private:
             }
             blk = b;
             len = l;
-            if (nin >= 0 && ntx >= 1) CheckStructure(b);
             valid = true;
             frameSecs += std::chrono::duration<double>(std::chrono::steady_clock::now() - tf0).count();
         }

@@ -71,7 +71,7 @@ public:
             for (size_t g = 0; g < devs.size(); g++)
                 if (!(devs.size() > 1 && g == 0 && l == lanes_ - 1 && lanes_ > 1)) workers.push_back(BCP_DEVICE_LANE(devs[g] & 0xFF, l));
         const size_t W = workers.size();
-        inflightMax = W + 2 < 14 ? W + 2 : 14; /* the table keeps undo records of at most 16 pending blocks */
+        inflightMax = W + 3 < 14 ? W + 3 : 14; /* the table keeps undo records of at most 16 pending blocks */
         jobs.resize(inflightMax + (size_t)nScan + 2);
         return true;
     }
@@ -138,7 +138,7 @@ private:
             cap = 0;
         }
     };
-    enum State { FREE = 0, SCANNING, SCANNED, APPLIED, DONE };
+    enum State { FREE = 0, SCANNING, SCANNED, APPLIED, CHECKING, DONE };
     struct Job {
         State state = FREE;
         long index = -1; // ordinal of the block in this run
@@ -175,78 +175,23 @@ private:
         const uint8_t *b = j.blk;
         const size_t l = j.len;
         size_t max_tx = l / 60 + 2, max_in = l / 41 + 2, max_out = l / 34 + 2; /* outputs: first guess, P2PKH-sized */
+        int rule = 0; // the scan applies CheckBlock's context-free transaction rules while it has the bytes in the cache
+        long ruleTx = -1;
         for (int attempt = 0; attempt < 2; attempt++) {
             j.tx_off.need(max_tx + 1); j.tx_out_off.need(max_tx + 1);
             j.in_off.need(max_in); j.in_tx.need(max_in); j.in_n.need(max_in);
             j.out_off.need(max_out); j.out_tx.need(max_out); j.out_n.need(max_out);
             j.ntx = j.nout = 0;
-            j.nin = bcp_block_index_full(b, l, 0, j.tx_off.p, j.tx_out_off.p, max_tx, j.in_off.p, j.in_tx.p, j.in_n.p, max_in, &j.ntx,
-                                         j.out_off.p, j.out_tx.p, j.out_n.p, max_out, &j.nout, nullptr);
+            rule = 0;
+            j.nin = bcp_block_index_rules(b, l, 0, j.tx_off.p, j.tx_out_off.p, max_tx, j.in_off.p, j.in_tx.p, j.in_n.p, max_in, &j.ntx,
+                                          j.out_off.p, j.out_tx.p, j.out_n.p, max_out, &j.nout, nullptr, &rule, &ruleTx);
             if (j.nin != -2) break;
             max_out = l / 9 + 2; /* the worst case a block of this size can hold */
         }
-        j.structErr = nullptr;
-        if (j.nin >= 0 && j.ntx >= 1) j.structErr = CheckStructure(j, b);
+        j.structErr = (j.nin >= 0 && rule) ? bcp_block_rule_name(rule) : nullptr;
         if (j.nin >= 0) j.errs.need((size_t)j.nin + 1);
         j.small.need(64);
     }
-    static uint64_t ReadCompact(const uint8_t *p, size_t &pos) { // already validated by the framing scan
-        uint8_t c = p[pos++];
-        if (c < 253) return c;
-        int nb = c == 253 ? 2 : c == 254 ? 4 : 8;
-        uint64_t v = 0;
-        for (int i = 0; i < nb; i++) v |= (uint64_t)p[pos + i] << (8 * i);
-        pos += nb;
-        return v;
-    }
-    // CheckBlock's context-free transaction rules from the framing arrays (src/validation.cpp:3255-3330 calling CheckCoinbase
-    // :531-549 and CheckRegularTransaction :551-570, both over CheckTransactionCommon :476-529), in the reference's order
-    static const char *CheckStructure(const Job &j, const uint8_t *b) {
-        static const int64_t MAX_MONEY_SAT = 21000000ll * 100000000ll; // src/amount.h:127
-        size_t o = 0, i = 0;
-        for (long t = 0; t < j.ntx; t++) {
-            size_t pos = (size_t)j.tx_off.p[t] + 4;
-            const uint64_t n_in = ReadCompact(b, pos);
-            bool cb = false;
-            uint64_t cbScriptLen = 0;
-            if (n_in == 1) {
-                cb = true;
-                for (int k = 0; k < 32; k++) cb = cb && b[pos + k] == 0;
-                for (int k = 32; k < 36; k++) cb = cb && b[pos + k] == 0xFF;
-                size_t q = pos + 36;
-                cbScriptLen = ReadCompact(b, q);
-            }
-            size_t po = j.tx_out_off.p[t];
-            const uint64_t n_out = ReadCompact(b, po);
-            const char *e = nullptr;
-            if (t == 0 && !cb) e = "bad-cb-missing";
-            else if (t > 0 && cb) e = "bad-tx-coinbase";
-            else if (n_in == 0) e = "bad-txns-vin-empty";
-            else if (n_out == 0) e = "bad-txns-vout-empty";
-            else if (j.tx_off.p[t + 1] - j.tx_off.p[t] > 1000000u) e = "bad-txns-oversize"; // MAX_TX_SIZE, consensus.h:14
-            int64_t total = 0;
-            for (; o < (size_t)j.nout && j.out_tx.p[o] == (uint32_t)t; o++) {
-                if (e) continue;
-                int64_t v;
-                memcpy(&v, b + j.out_off.p[o], 8);
-                if (v < 0) e = "bad-txns-vout-negative";
-                else if (v > MAX_MONEY_SAT) e = "bad-txns-vout-toolarge";
-                else if ((total += v) > MAX_MONEY_SAT) e = "bad-txns-txouttotal-toolarge";
-            }
-            if (!e && t == 0 && (cbScriptLen < 2 || cbScriptLen > 100)) e = "bad-cb-length";
-            for (; i < (size_t)j.nin && j.in_tx.p[i] == (uint32_t)t; i++) {
-                if (e) continue;
-                const uint8_t *op = b + j.in_off.p[i];
-                bool null = true;
-                for (int k = 0; k < 32; k++) null = null && op[k] == 0;
-                for (int k = 32; k < 36; k++) null = null && op[k] == 0xFF;
-                if (null) e = "bad-txns-prevout-null";
-            }
-            if (e) return e;
-        }
-        return nullptr;
-    }
-
     // everything a check thread does for one applied block
     void Check(Job &j, int dev) {
         auto t0 = Clock::now();
@@ -389,15 +334,21 @@ private:
                     cv.notify_all();
                 }
             });
-        // check threads: thread w owns one (GPU, lane) pair and the blocks b with b % W == w
+        // check threads: thread w owns one (GPU, lane) pair and takes the next applied block whenever it is free (the
+        // threads are not equally fast — the table's GPU is busier, a peer copy costs the others a little — and verdicts
+        // are taken in order, so a fixed assignment would make every thread wait for the slowest one)
+        long nextCheck = 0;
         for (size_t w = 0; w < W; w++)
             threads.emplace_back([&, w] {
                 const int dev = workers[w];
-                for (long b = (long)w;; b += (long)W) {
+                for (;;) {
+                    long b;
                     {
                         std::unique_lock<std::mutex> l(mu);
-                        cv.wait(l, [&] { return quit || (jobOf(b).index == b && jobOf(b).state == APPLIED); });
+                        cv.wait(l, [&] { return quit || (nextCheck < nextApply && jobOf(nextCheck).index == nextCheck && jobOf(nextCheck).state == APPLIED); });
                         if (quit) return;
+                        b = nextCheck++;
+                        jobOf(b).state = CHECKING;
                     }
                     Check(jobOf(b), dev);
                     {
@@ -446,6 +397,7 @@ private:
                     std::lock_guard<std::mutex> l(mu);
                     j.state = DONE;
                     nextApply++;
+                    if (nextCheck == b) nextCheck++; // nothing to check: the check threads pass over it
                     stopAt = b + 1 < stopAt ? b + 1 : stopAt;
                     cv.notify_all();
                     continue;
@@ -463,6 +415,7 @@ private:
                     j.seq = 0;
                     --seqCounter;
                     j.state = DONE;
+                    if (nextCheck == b) nextCheck++;
                     stopAt = b + 1 < stopAt ? b + 1 : stopAt;
                 } else {
                     j.state = APPLIED;

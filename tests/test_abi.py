@@ -217,3 +217,37 @@ def test_scanners_reject_non_canonical_counts(oracle):
             n, _ = oracle.block_index(bad, False)
             assert n >= 0
     assert L.bcp_block_index(blk, len(blk), 0, a[0].ctypes.data, mt) == 6
+
+
+def test_block_index_rules_reports_the_reference_reject_string():
+    """bcp_block_index_rules: the framing scan applies CheckBlock's context-free transaction rules
+    (src/validation.cpp:476-570, 3255-3330) in the same pass; every damaged block of synth.STRUCTURE_KINDS gives the
+    reference's reject string and names the transaction, an undamaged block gives 0.  Host code only: runs without a GPU."""
+    import ctypes as C
+
+    import numpy as np
+
+    import bitcoincashplus_b200 as bcp
+    import synth
+
+    L = bcp.lib()
+
+    def rules(blk):
+        b = np.frombuffer(blk, np.uint8)
+        n = len(blk)
+        arrs = [np.zeros(n // 9 + 8, np.uint32) for _ in range(8)]
+        ntx, nout, rule, rtx = C.c_long(), C.c_long(), C.c_int(-1), C.c_long(-2)
+        nin = L.bcp_block_index_rules(b.ctypes.data, n, 0, arrs[0].ctypes.data, arrs[1].ctypes.data, n // 60 + 2, arrs[2].ctypes.data,
+                                      arrs[3].ctypes.data, arrs[4].ctypes.data, n // 41 + 2, C.byref(ntx), arrs[5].ctypes.data,
+                                      arrs[6].ctypes.data, arrs[7].ctypes.data, n // 9 + 2, C.byref(nout), None, C.byref(rule), C.byref(rtx))
+        assert nin >= 0
+        return L.bcp_block_rule_name(rule.value), rtx.value
+
+    good, _, _ = synth.synthetic_chain(2, 8, equihash=False)
+    assert rules(good[1]) == (b"", -1)
+    where = {"second_coinbase": 2, "no_coinbase": 0, "cb_length": 0}
+    for kind, want in synth.STRUCTURE_KINDS.items():
+        bad, _, _ = synth.synthetic_chain(2, 8, equihash=False, corrupt=(1, kind))
+        name, tx = rules(bad[1])
+        assert name == want and tx == where.get(kind, 3), (kind, name, tx)
+    assert L.bcp_block_rule_name(99) == b""
