@@ -458,7 +458,7 @@ def chain_bench(args, devices, impl="device"):
     failed = C.c_long(-1)
     n_ok = fn("connect_file")(h, bufs[0][0], bufs[0][1], magic, reason, 256, C.byref(failed))
     assert n_ok == warm, (n_ok, failed.value, reason.value)
-    nph = 6 if impl == "device" else 5
+    nph = 9 if impl == "device" else 5
     fn("phase_seconds").argtypes = [C.c_void_p, C.POINTER(C.c_double)]
     ph0 = (C.c_double * nph)()
     fn("phase_seconds")(h, ph0)
@@ -470,7 +470,8 @@ def chain_bench(args, devices, impl="device"):
     fn("phase_seconds")(h, ph)
     if impl == "device":
         names = ["connecting_thread_apply_calls", "connecting_thread_waiting", "check_threads_wait_for_spent_coins",
-                 "check_threads_header", "check_threads_scripts", "scan_threads"]
+                 "check_threads_header", "check_threads_scripts", "scan_threads", "connecting_thread_confirm",
+                 "latency_applied_to_table_done", "latency_applied_to_verdict"]
     else:
         names = ["header_equihash", "framing_scan", "txids_wait_after_lookups", "utxo_walk", "scripts_wait_after_inserts"]
     phases = dict(zip(names, [1e3 * (x - x0) / nblk for x, x0 in zip(ph, ph0)]))

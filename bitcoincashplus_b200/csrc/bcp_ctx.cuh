@@ -39,6 +39,8 @@ int bcp_sha256d_offsets_dev(bcp_ctx *c, const uint8_t *d_data, const uint32_t *d
                             cudaStream_t st);                                          // bcp_hash.cu
 int bcp_merkle_dev(bcp_ctx *c, const uint8_t *d_leaves, size_t n, uint8_t *d_root32, int *d_mut, uint32_t *d_tmp,
                    cudaStream_t st);                                                   // bcp_hash.cu
+int bcp_merkle_dev_few_launches(bcp_ctx *c, const uint8_t *d_leaves, size_t n, uint8_t *d_root32, int *d_mut, uint32_t *d_tmp,
+                                cudaStream_t st);                                      // bcp_hash.cu
 size_t bcp_merkle_tmp_words(size_t n);                                                 // bcp_hash.cu
 int bcp_block_scripts_resident(bcp_ctx *c, const uint8_t *d_blk, const uint32_t *d_txoff, const uint32_t *h_tx_off, size_t ntx,
                                const uint32_t *d_inoff, const uint32_t *d_intx, const uint32_t *d_inn, const uint32_t *h_in_tx,

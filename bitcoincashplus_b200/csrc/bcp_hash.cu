@@ -169,6 +169,11 @@ int bcp_merkle_dev(bcp_ctx *c, const uint8_t *d_leaves, size_t n, uint8_t *d_roo
                    cudaStream_t st) {
     return merkle_dev(c, d_leaves, n, d_root32, d_mut, d_tmp, st);
 }
+// fewest launches (eight levels each): for a caller that has the result off its critical path and pays per API call
+int bcp_merkle_dev_few_launches(bcp_ctx *c, const uint8_t *d_leaves, size_t n, uint8_t *d_root32, int *d_mut, uint32_t *d_tmp,
+                                cudaStream_t st) {
+    return merkle_dev(c, d_leaves, n, d_root32, d_mut, d_tmp, st, MERKLE_LEVELS_DEEP);
+}
 size_t bcp_merkle_tmp_words(size_t n) { return merkle_tmp_words(n); }
 
 // fixed-size messages at a fixed stride (serialized block headers)

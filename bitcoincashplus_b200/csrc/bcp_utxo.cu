@@ -574,11 +574,12 @@ BCP_API int bcp_gpu_utxo_apply_block(bcp_utxo *u, uint32_t seq, const uint8_t *b
     BCP_CUDA(cudaMemsetAsync(d_stat, 0, ST_WORDS * 4, st)); /* [ST_FIRST_MISSING] holds ~index under atomicMax: 0 = none */
     int rc = bcp_sha256d_offsets_dev(u->ctx, d + o_blk, reinterpret_cast<uint32_t *>(d + o_txoff), ntx, d + o_txid, st);
     if (rc != BCP_OK) return rc;
-    // the Merkle reduction (a chain of small launches, each as long as its three tree levels) needs the txids only: it
-    // runs on the third stream while the table kernels go on
+    // the Merkle reduction needs the txids only: it runs on the third stream while the table kernels go on (in its
+    // eight-levels-per-launch form: off the critical path its latency does not matter, the connecting thread's API calls do)
     BCP_CUDA(cudaEventRecord(r.hashed, st));
     BCP_CUDA(cudaStreamWaitEvent(u->aux, r.hashed, 0));
-    rc = bcp_merkle_dev(u->ctx, d + o_txid, ntx, d + o_root, reinterpret_cast<int *>(d + o_root + 32), reinterpret_cast<uint32_t *>(d + o_mtmp), u->aux);
+    rc = bcp_merkle_dev_few_launches(u->ctx, d + o_txid, ntx, d + o_root, reinterpret_cast<int *>(d + o_root + 32),
+                                     reinterpret_cast<uint32_t *>(d + o_mtmp), u->aux);
     if (rc != BCP_OK) return rc;
     BCP_CUDA(cudaEventRecord(r.merkled, u->aux));
     if (nout)

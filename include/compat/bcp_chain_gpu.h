@@ -95,8 +95,10 @@ public:
 
     // seconds, summed over blocks: [0] connecting thread inside bcp_gpu_utxo_apply_block, [1] connecting thread waiting
     // (for a scan, a free slot or a verdict), [2] check threads waiting for the spent-coin arrays, [3] check threads in
-    // the header check, [4] check threads in the script checks, [5] scan threads
-    double phase[6] = {0, 0, 0, 0, 0, 0};
+    // the header check, [4] check threads in the script checks, [5] scan threads, [6] connecting thread confirming,
+    // [7] from "applied" to "table work done" (the table stream's queue + work), [8] from "applied" to "verdict taken"
+    // (how long a block occupies one of the in-flight slots)
+    double phase[9] = {0, 0, 0, 0, 0, 0, 0, 0, 0};
 
     bool ConnectBlock(const uint8_t *blk, size_t len, std::string &reason) {
         std::vector<std::pair<const uint8_t *, size_t>> one{{blk, len}};
@@ -150,6 +152,7 @@ private:
         long ntx = 0, nin = -1, nout = 0;
         const char *structErr = nullptr;
         uint32_t seq = 0;
+        Clock::time_point tApplied;
         bool ok = false;
         std::string reason;
         uint8_t hash[32];
@@ -198,6 +201,7 @@ private:
         uint32_t st[8] = {0};
         int rcw = bcp_gpu_utxo_wait(utxo, j.seq, st);
         auto t1 = Clock::now();
+        const double tableLatency = Secs(j.tApplied, t1);
         j.ok = false;
         // header first, like CheckBlockHeader before anything of the body (src/validation.cpp:3202-3220)
         const size_t soln = ehN ? ((size_t)1 << ehK) * (ehN / (ehK + 1) + 1) / 8 : 0;
@@ -257,6 +261,7 @@ private:
         phase[2] += Secs(t0, t1);
         phase[3] += Secs(t1, t2);
         phase[4] += tScripts;
+        phase[7] += tableLatency;
     }
 
     // the inputs the fast path answered 255 for, through the caller's interpreter (bcp_other_scripts.h)
@@ -406,8 +411,9 @@ private:
                 const int rc = bcp_gpu_utxo_apply_block(utxo, j.seq, j.blk, j.len, j.tx_off.p, (size_t)j.ntx, j.in_off.p, j.in_tx.p, (size_t)j.nin,
                                                         j.out_off.p, j.out_tx.p, j.out_n.p, (size_t)j.nout, nullptr, j.small.p,
                                                         reinterpret_cast<int *>(j.small.p + 32), nullptr, 0, nullptr, nullptr);
+                j.tApplied = Clock::now();
                 std::lock_guard<std::mutex> l(mu);
-                phase[0] += Secs(ta0, Clock::now());
+                phase[0] += Secs(ta0, j.tApplied);
                 nextApply++;
                 if (rc != BCP_OK) { // could not even be enqueued: treat like a failed block that was never applied
                     j.ok = false;
@@ -425,11 +431,14 @@ private:
             }
             // a verdict, in chain order
             if (j.ok) {
+                auto tc0 = Clock::now();
                 bcp_gpu_utxo_confirm(utxo, j.seq);
                 nInputs += (size_t)j.nin;
                 memcpy(lastHash, j.hash, 32);
                 connected++;
                 std::lock_guard<std::mutex> l(mu);
+                phase[6] += Secs(tc0, Clock::now());
+                phase[8] += Secs(j.tApplied, tc0);
                 j.state = FREE;
                 j.index = -1;
                 nextCommit++;

@@ -4,7 +4,7 @@ N=${1:-4}
 mkdir -p gpurun_out
 nvidia-smi -L | wc -l
 timeout 600 python -m pytest tests/test_gpu_utxo.py tests/test_gpu_chain.py tests/test_gpu_hash.py -x -q 2>&1 | tail -3
-for lanes in 2 3; do
+for lanes in ${LANES:-2}; do
 timeout 900 python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1 --master-port 2953$lanes bench.py --gpus $N --steps 3 --warmup 3 --no-cpu-baseline --only chain --chain-lanes $lanes > gpurun_out/chain${N}_l$lanes.json 2> gpurun_out/chain${N}_l$lanes.err; echo "rc=$?"; tail -2 gpurun_out/chain${N}_l$lanes.err
 python - <<PY
 import json
