@@ -507,6 +507,15 @@ def chain_bench(args, devices, impl="device"):
                                    "input, table rolled back, the undamaged block connected afterwards" % (warm + nblk + G_ - 1, bad_input, G_ - 1),
            "timed": "ConnectFile over %d blocks in blk*.dat framing in one pinned buffer, wall clock of the caller" % nblk}
     if impl == "device":
+        # every block crosses the host's memory twice on this path (framing scan, upload): the box's read bandwidth is a ceiling
+        L.bcp_host_read_bandwidth.restype = C.c_double
+        L.bcp_host_read_bandwidth.argtypes = [C.c_int, C.c_size_t]
+        nthr = min(os.cpu_count() or 1, 16)
+        bw = max(L.bcp_host_read_bandwidth(nthr, 256 << 20) for _ in range(2))
+        out["host_memory"] = {"read_gbs_measured": bw, "threads": nthr,
+                              "bytes_read_per_block": 2 * len(blocks[0]),
+                              "chain_read_gbs": 2 * len(blocks[0]) * nblk / total / 1e9,
+                              "note": "host DRAM reads the chain causes (scan + upload DMA) against what this box's cores can read"}
         out["phase_note"] = ("thread-seconds per block summed over the threads of each kind, not a critical path: the connecting thread "
                              "is the only sequential part (apply calls + waiting); check threads = %d per GPU" % lanes)
     if po.have_ref() and impl == "device":

@@ -126,3 +126,28 @@ CHAIN_API void bcp_dchain_last_hash(void *h, uint8_t *out32) { memcpy(out32, sta
 CHAIN_API void bcp_dchain_phase_seconds(void *h, double *out9) {
     for (int i = 0; i < 9; i++) out9[i] = static_cast<bcp::DeviceChain *>(h)->phase[i];
 }
+
+// Measurement helper for bench.py (not part of the validation path): how fast `threads` host threads can READ memory that
+// is not in their caches — each sums its own buffer of `bytes_per_thread` bytes once, after writing it.  The chain connectors
+// move every block through host memory (framing scan, upload), so this is the box's ceiling for them; returns GB/s.
+CHAIN_API double bcp_host_read_bandwidth(int threads, size_t bytes_per_thread) {
+    if (threads < 1) threads = 1;
+    std::vector<std::vector<uint64_t>> bufs((size_t)threads);
+    for (auto &b : bufs) b.assign(bytes_per_thread / 8, 0x0101010101010101ull);
+    std::vector<uint64_t> sums((size_t)threads, 0);
+    const auto t0 = std::chrono::steady_clock::now();
+    std::vector<std::thread> th;
+    for (int t = 0; t < threads; t++)
+        th.emplace_back([&, t] {
+            uint64_t s = 0;
+            const uint64_t *p = bufs[(size_t)t].data();
+            const size_t n = bufs[(size_t)t].size();
+            for (size_t i = 0; i < n; i += 8) s += p[i]; /* one word per 64-byte line */
+            sums[(size_t)t] = s;
+        });
+    for (auto &x : th) x.join();
+    const double dt = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
+    uint64_t keep = 0;
+    for (uint64_t v : sums) keep += v;
+    return keep == 0 ? 0.0 : (double)threads * (double)bytes_per_thread / dt / 1e9;
+}
