@@ -429,7 +429,7 @@ def chain_bench(args, devices, impl="device"):
         L.bcp_dchain_new.restype = C.c_void_p
         L.bcp_dchain_new.argtypes = [C.POINTER(C.c_int), C.c_int, C.c_uint32, C.c_uint, C.c_uint, C.c_uint, C.c_int, C.c_int, C.c_char_p, C.c_size_t]
         lanes = args.chain_lanes or (3 if len(devices) == 1 else 2)
-        scan_threads = max(2, min(8, (os.cpu_count() or 4) // 4))
+        scan_threads = max(2, min(16, (os.cpu_count() or 4) // 2))
         h = L.bcp_dchain_new(devs, len(devices), synth.POSTFORK_FLAGS, 48, 5, 22, lanes, scan_threads, err, 256)
     else:
         L.bcp_chain_new.restype = C.c_void_p
@@ -458,7 +458,7 @@ def chain_bench(args, devices, impl="device"):
     failed = C.c_long(-1)
     n_ok = fn("connect_file")(h, bufs[0][0], bufs[0][1], magic, reason, 256, C.byref(failed))
     assert n_ok == warm, (n_ok, failed.value, reason.value)
-    nph = 9 if impl == "device" else 5
+    nph = 11 if impl == "device" else 5
     fn("phase_seconds").argtypes = [C.c_void_p, C.POINTER(C.c_double)]
     ph0 = (C.c_double * nph)()
     fn("phase_seconds")(h, ph0)
@@ -471,7 +471,8 @@ def chain_bench(args, devices, impl="device"):
     if impl == "device":
         names = ["connecting_thread_apply_calls", "connecting_thread_waiting", "check_threads_wait_for_spent_coins",
                  "check_threads_header", "check_threads_scripts", "scan_threads", "connecting_thread_confirm",
-                 "latency_applied_to_table_done", "latency_applied_to_verdict"]
+                 "latency_applied_to_table_done", "latency_applied_to_verdict", "connecting_thread_waiting_window_full",
+                 "connecting_thread_waiting_for_scan"]
     else:
         names = ["header_equihash", "framing_scan", "txids_wait_after_lookups", "utxo_walk", "scripts_wait_after_inserts"]
     phases = dict(zip(names, [1e3 * (x - x0) / nblk for x, x0 in zip(ph, ph0)]))

@@ -123,8 +123,8 @@ CHAIN_API long bcp_dchain_connect_file(void *h, const uint8_t *data, size_t len,
     return n;
 }
 CHAIN_API void bcp_dchain_last_hash(void *h, uint8_t *out32) { memcpy(out32, static_cast<bcp::DeviceChain *>(h)->LastBlockHash(), 32); }
-CHAIN_API void bcp_dchain_phase_seconds(void *h, double *out9) {
-    for (int i = 0; i < 9; i++) out9[i] = static_cast<bcp::DeviceChain *>(h)->phase[i];
+CHAIN_API void bcp_dchain_phase_seconds(void *h, double *out11) {
+    for (int i = 0; i < 11; i++) out11[i] = static_cast<bcp::DeviceChain *>(h)->phase[i];
 }
 
 // Measurement helper for bench.py (not part of the validation path): how fast `threads` host threads can READ memory that

@@ -98,7 +98,8 @@ public:
     // the header check, [4] check threads in the script checks, [5] scan threads, [6] connecting thread confirming,
     // [7] from "applied" to "table work done" (the table stream's queue + work), [8] from "applied" to "verdict taken"
     // (how long a block occupies one of the in-flight slots)
-    double phase[9] = {0, 0, 0, 0, 0, 0, 0, 0, 0};
+    // [9] of [1]: waiting with the in-flight window full (for a verdict), [10] of [1]: waiting for the next block's scan
+    double phase[11] = {0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0};
 
     bool ConnectBlock(const uint8_t *blk, size_t len, std::string &reason) {
         std::vector<std::pair<const uint8_t *, size_t>> one{{blk, len}};
@@ -372,13 +373,19 @@ private:
             auto tw0 = Clock::now();
             {
                 std::unique_lock<std::mutex> l(mu);
+                // what the thread is short of when it starts to wait (for the report): a scanned block, or room in flight
+                const bool windowFull = nextApply - nextCommit >= (long)inflightMax;
+                const bool scanMissing = !windowFull && nextApply < stopAt && !(jobOf(nextApply).index == nextApply && jobOf(nextApply).state == SCANNED);
                 cv.wait(l, [&] {
                     if (nextCommit < nextApply && jobOf(nextCommit).state == DONE) return true;                      // a verdict is in
                     if (nextApply < stopAt && nextApply - nextCommit < (long)inflightMax && jobOf(nextApply).index == nextApply &&
                         jobOf(nextApply).state == SCANNED) return true;                                               // a block can go
                     return nextCommit >= stopAt && nextCommit >= nextApply;                                           // nothing left
                 });
-                phase[1] += Secs(tw0, Clock::now());
+                const double waited = Secs(tw0, Clock::now());
+                phase[1] += waited;
+                if (windowFull) phase[9] += waited;
+                else if (scanMissing) phase[10] += waited;
                 if (nextCommit < nextApply && jobOf(nextCommit).state == DONE) { commit = true; b = nextCommit; }
                 else if (nextApply < stopAt && nextApply - nextCommit < (long)inflightMax && jobOf(nextApply).index == nextApply &&
                          jobOf(nextApply).state == SCANNED) b = nextApply;

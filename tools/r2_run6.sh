@@ -3,12 +3,12 @@
 N=${1:-4}
 mkdir -p gpurun_out
 nvidia-smi -L | wc -l
-timeout 600 python -m pytest tests/test_gpu_utxo.py tests/test_gpu_chain.py tests/test_gpu_hash.py -x -q 2>&1 | tail -3
+nproc; lscpu | grep 'Model name'
 for lanes in ${LANES:-2}; do
 timeout 900 python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1 --master-port 2953$lanes bench.py --gpus $N --steps 3 --warmup 3 --no-cpu-baseline --only chain --chain-lanes $lanes > gpurun_out/chain${N}_l$lanes.json 2> gpurun_out/chain${N}_l$lanes.err; echo "rc=$?"; tail -2 gpurun_out/chain${N}_l$lanes.err
 python - <<PY
 import json
 d=json.loads(open('gpurun_out/chain${N}_l$lanes.json').read().strip().splitlines()[-1])
-c=d['chain']; print('gpus $N lanes $lanes chain',c['gpu_blocks_per_s'],c['ms_per_block_by_phase'])
+c=d['chain']; print('gpus $N lanes $lanes chain',c['gpu_blocks_per_s'],c['ms_per_block_by_phase'],c.get('host_memory'))
 PY
 done
