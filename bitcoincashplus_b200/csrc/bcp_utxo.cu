@@ -517,21 +517,24 @@ BCP_API int bcp_gpu_utxo_apply_block(bcp_utxo *u, uint32_t seq, const uint8_t *b
     }
     BCP_CUDA(cudaSetDevice(u->device));
     // device layout of this block's slot
-    // The arrays the script checks need come first and back to back (block, offsets, inputs, spent amounts / script offsets /
-    // scripts): bcp_gpu_utxo_block_scripts reads them in place or moves them to another GPU in one peer copy.
+    // The arrays the script checks need come first and back to back (block, offsets, inputs, outputs, spent amounts /
+    // script offsets / scripts): bcp_gpu_utxo_block_scripts reads them in place or moves them to another GPU in one peer
+    // copy.  The six offset arrays are adjacent, each padded to 256 bytes: a caller that keeps them laid out the same way
+    // in host memory gets them uploaded with one copy.
     size_t o = 0;
     const size_t o_blk = o; o += up256(len + 16);
     const size_t o_txoff = o; o += up256((ntx + 1) * 4);
     const size_t o_inoff = o; o += up256(nin * 4 + 4);
     const size_t o_intx = o; o += up256(nin * 4 + 4);
+    const size_t o_outoff = o; o += up256(nout * 4 + 4);
+    const size_t o_outtx = o; o += up256(nout * 4 + 4);
+    const size_t o_outn = o; o += up256(nout * 4 + 4);
+    const size_t arrays_bytes = o - o_txoff;
     const size_t o_amt = o; o += up256(nin * 8 + 8);
     const size_t o_spkoff = o; o += up256((nin + 1) * 4);
     const size_t dev_spk_cap = spk_cat ? spk_cap : nin * 80 + 65536; /* without a host buffer: room for P2PKH-sized scripts and more */
     const size_t o_spk = o; o += up256(dev_spk_cap + 16);
     const size_t in_area = o;
-    const size_t o_outoff = o; o += up256(nout * 4 + 4);
-    const size_t o_outtx = o; o += up256(nout * 4 + 4);
-    const size_t o_outn = o; o += up256(nout * 4 + 4);
     const size_t o_txid = o; o += up256(ntx * 32 + 32);
     const size_t o_mtmp = o; o += up256(bcp_merkle_tmp_words(ntx) * 4);
     const size_t o_stat = o; o += 256; /* status[8 words] | root[32 bytes] | mutated(int): one copy brings all three home */
@@ -557,15 +560,25 @@ BCP_API int bcp_gpu_utxo_apply_block(bcp_utxo *u, uint32_t seq, const uint8_t *b
         r.reclaim_pending = false;
     }
     BCP_CUDA(cudaMemcpyAsync(d + o_blk, blk, len, cudaMemcpyHostToDevice, u->up));
-    BCP_CUDA(cudaMemcpyAsync(d + o_txoff, tx_off, (ntx + 1) * 4, cudaMemcpyHostToDevice, u->up));
-    if (nin) {
-        BCP_CUDA(cudaMemcpyAsync(d + o_inoff, in_off, nin * 4, cudaMemcpyHostToDevice, u->up));
-        BCP_CUDA(cudaMemcpyAsync(d + o_intx, in_tx, nin * 4, cudaMemcpyHostToDevice, u->up));
-    }
-    if (nout) {
-        BCP_CUDA(cudaMemcpyAsync(d + o_outoff, out_off, nout * 4, cudaMemcpyHostToDevice, u->up));
-        BCP_CUDA(cudaMemcpyAsync(d + o_outtx, out_tx, nout * 4, cudaMemcpyHostToDevice, u->up));
-        BCP_CUDA(cudaMemcpyAsync(d + o_outn, out_n, nout * 4, cudaMemcpyHostToDevice, u->up));
+    const uint8_t *hb = reinterpret_cast<const uint8_t *>(tx_off);
+    const bool packed = nin && nout && reinterpret_cast<const uint8_t *>(in_off) == hb + (o_inoff - o_txoff) &&
+                        reinterpret_cast<const uint8_t *>(in_tx) == hb + (o_intx - o_txoff) &&
+                        reinterpret_cast<const uint8_t *>(out_off) == hb + (o_outoff - o_txoff) &&
+                        reinterpret_cast<const uint8_t *>(out_tx) == hb + (o_outtx - o_txoff) &&
+                        reinterpret_cast<const uint8_t *>(out_n) == hb + (o_outn - o_txoff);
+    if (packed) { /* the caller's arrays are laid out like the device's: one copy (every runtime call costs the connecting thread) */
+        BCP_CUDA(cudaMemcpyAsync(d + o_txoff, tx_off, arrays_bytes, cudaMemcpyHostToDevice, u->up));
+    } else {
+        BCP_CUDA(cudaMemcpyAsync(d + o_txoff, tx_off, (ntx + 1) * 4, cudaMemcpyHostToDevice, u->up));
+        if (nin) {
+            BCP_CUDA(cudaMemcpyAsync(d + o_inoff, in_off, nin * 4, cudaMemcpyHostToDevice, u->up));
+            BCP_CUDA(cudaMemcpyAsync(d + o_intx, in_tx, nin * 4, cudaMemcpyHostToDevice, u->up));
+        }
+        if (nout) {
+            BCP_CUDA(cudaMemcpyAsync(d + o_outoff, out_off, nout * 4, cudaMemcpyHostToDevice, u->up));
+            BCP_CUDA(cudaMemcpyAsync(d + o_outtx, out_tx, nout * 4, cudaMemcpyHostToDevice, u->up));
+            BCP_CUDA(cudaMemcpyAsync(d + o_outn, out_n, nout * 4, cudaMemcpyHostToDevice, u->up));
+        }
     }
     BCP_CUDA(cudaEventRecord(r.uploaded, u->up));
     cudaStream_t st = u->st;

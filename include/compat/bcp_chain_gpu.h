@@ -150,6 +150,8 @@ private:
         Pinned<uint32_t> tx_off, tx_out_off, in_off, in_tx, in_n, out_off, out_tx, out_n, spk_off;
         Pinned<int64_t> amounts;
         Pinned<uint8_t> spk_cat, errs, small; // small: root[32] | mutated(int) at 32
+        Pinned<uint8_t> packed;               // the six offset arrays back to back, each padded to 256 bytes (one upload)
+        uint32_t *p_tx_off = nullptr, *p_in_off = nullptr, *p_in_tx = nullptr, *p_out_off = nullptr, *p_out_tx = nullptr, *p_out_n = nullptr;
         long ntx = 0, nin = -1, nout = 0;
         const char *structErr = nullptr;
         uint32_t seq = 0;
@@ -160,6 +162,7 @@ private:
         void Free() {
             tx_off.release(); tx_out_off.release(); in_off.release(); in_tx.release(); in_n.release(); out_off.release();
             out_tx.release(); out_n.release(); spk_off.release(); amounts.release(); spk_cat.release(); errs.release(); small.release();
+            packed.release();
         }
     };
 
@@ -193,7 +196,22 @@ private:
             max_out = l / 9 + 2; /* the worst case a block of this size can hold */
         }
         j.structErr = (j.nin >= 0 && rule) ? bcp_block_rule_name(rule) : nullptr;
-        if (j.nin >= 0) j.errs.need((size_t)j.nin + 1);
+        if (j.nin >= 0) {
+            j.errs.need((size_t)j.nin + 1);
+            // the arrays bcp_gpu_utxo_apply_block uploads, laid out as it lays them out on the device: it then needs ONE
+            // copy for all six (the connecting thread pays for every runtime call)
+            auto up = [](size_t x) { return (x + 255) / 256 * 256; };
+            const size_t ntx = (size_t)j.ntx, nin = (size_t)j.nin, nout = (size_t)j.nout;
+            const size_t s_tx = up((ntx + 1) * 4), s_in = up(nin * 4 + 4), s_out = up(nout * 4 + 4);
+            j.packed.need(s_tx + 2 * s_in + 3 * s_out);
+            uint8_t *q = j.packed.p;
+            j.p_tx_off = reinterpret_cast<uint32_t *>(q); memcpy(q, j.tx_off.p, (ntx + 1) * 4); q += s_tx;
+            j.p_in_off = reinterpret_cast<uint32_t *>(q); memcpy(q, j.in_off.p, nin * 4); q += s_in;
+            j.p_in_tx = reinterpret_cast<uint32_t *>(q); memcpy(q, j.in_tx.p, nin * 4); q += s_in;
+            j.p_out_off = reinterpret_cast<uint32_t *>(q); memcpy(q, j.out_off.p, nout * 4); q += s_out;
+            j.p_out_tx = reinterpret_cast<uint32_t *>(q); memcpy(q, j.out_tx.p, nout * 4); q += s_out;
+            j.p_out_n = reinterpret_cast<uint32_t *>(q); memcpy(q, j.out_n.p, nout * 4);
+        }
         j.small.need(64);
     }
     // everything a check thread does for one applied block
@@ -415,8 +433,8 @@ private:
                     continue;
                 }
                 auto ta0 = Clock::now();
-                const int rc = bcp_gpu_utxo_apply_block(utxo, j.seq, j.blk, j.len, j.tx_off.p, (size_t)j.ntx, j.in_off.p, j.in_tx.p, (size_t)j.nin,
-                                                        j.out_off.p, j.out_tx.p, j.out_n.p, (size_t)j.nout, nullptr, j.small.p,
+                const int rc = bcp_gpu_utxo_apply_block(utxo, j.seq, j.blk, j.len, j.p_tx_off, (size_t)j.ntx, j.p_in_off, j.p_in_tx, (size_t)j.nin,
+                                                        j.p_out_off, j.p_out_tx, j.p_out_n, (size_t)j.nout, nullptr, j.small.p,
                                                         reinterpret_cast<int *>(j.small.p + 32), nullptr, 0, nullptr, nullptr);
                 j.tApplied = Clock::now();
                 std::lock_guard<std::mutex> l(mu);
