@@ -44,6 +44,22 @@ def workload_config(n):
                          % ((n * (161 + 80 + 768 + 1)) / 1e6)}
 
 
+def effective_cpus():
+    """cores this process may really use: the affinity mask and the cgroup CPU quota, not just os.cpu_count()"""
+    n = os.cpu_count() or 1
+    try:
+        n = min(n, len(os.sched_getaffinity(0)))
+    except Exception:
+        pass
+    try:
+        quota, period = open("/sys/fs/cgroup/cpu.max").read().split()
+        if quota != "max":
+            n = max(1, min(n, int(int(quota) / int(period))))
+    except Exception:
+        pass
+    return n
+
+
 def clocks_sampler(stop, out, gpu_index):
     q = "clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown," \
         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap"
@@ -429,7 +445,7 @@ def chain_bench(args, devices, impl="device"):
         L.bcp_dchain_new.restype = C.c_void_p
         L.bcp_dchain_new.argtypes = [C.POINTER(C.c_int), C.c_int, C.c_uint32, C.c_uint, C.c_uint, C.c_uint, C.c_int, C.c_int, C.c_char_p, C.c_size_t]
         lanes = args.chain_lanes or (3 if len(devices) == 1 else 2)
-        scan_threads = max(2, min(16, (os.cpu_count() or 4) // 2))
+        scan_threads = max(2, min(8, effective_cpus() // 4))
         h = L.bcp_dchain_new(devs, len(devices), synth.POSTFORK_FLAGS, 48, 5, 22, lanes, scan_threads, err, 256)
     else:
         L.bcp_chain_new.restype = C.c_void_p
@@ -513,6 +529,8 @@ def chain_bench(args, devices, impl="device"):
         L.bcp_host_read_bandwidth.argtypes = [C.c_int, C.c_size_t]
         nthr = min(os.cpu_count() or 1, 16)
         bw = max(L.bcp_host_read_bandwidth(nthr, 256 << 20) for _ in range(2))
+        out["host_threads"] = {"scan": scan_threads, "check": "%d per GPU (one less on the table's GPU when there are several)" % lanes,
+                               "connecting": 1, "effective_cpus": effective_cpus(), "os_cpu_count": os.cpu_count()}
         out["host_memory"] = {"read_gbs_measured": bw, "threads": nthr,
                               "bytes_read_per_block": 2 * len(blocks[0]),
                               "chain_read_gbs": 2 * len(blocks[0]) * nblk / total / 1e9,
