@@ -213,8 +213,10 @@ int bcp_block_scripts_resident(bcp_ctx *c, const uint8_t *d_blk, const uint32_t 
     rc = launch_mid_extract(c, d_blk, d_txoff, h_tx_off, ntx, d_inoff, d_intx, d_inn, h_in_tx, nin, d_spk, d_spkoff, d_amt, d + o_mid,
                             d + o_stat, d + o_msg, d + o_pub, d + o_sig, st);
     if (rc != BCP_OK) return rc;
+    c->prep_throughput = true; /* this path is the chain connector's: other lanes keep the GPU busy meanwhile */
     rc = bcp_ecdsa_launch(c, d + o_msg, d + o_pub, d + o_sig, nin, BCP_ECDSA_FLAG_NORMALIZE_S, d + o_ok,
                           reinterpret_cast<uint32_t *>(c->scratch), st);
+    c->prep_throughput = false;
     if (rc != BCP_OK) return rc;
     k_script_finish<<<(unsigned)((nin + 255) / 256), 256, 0, st>>>(d + o_stat, d + o_ok, nin, d + o_err, reinterpret_cast<int *>(d + o_flag));
     BCP_CUDA(cudaGetLastError());

@@ -23,6 +23,7 @@ struct bcp_ctx {
     size_t stage_bytes = 0;
     std::vector<uint32_t> h_tx_off, h_in_off, h_in_tx, h_in_n; // host scratch of the block framing scan (reused)
     bool block_attrs = false;           // shared-memory opt-in of the block kernels done on this device
+    bool prep_throughput = false;       // set while a caller with several batches in flight uses this context (see bcp_ecdsa_launch)
     std::mutex mu;
 };
 

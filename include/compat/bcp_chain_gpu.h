@@ -60,6 +60,8 @@ public:
         for (int d : devs)
             for (int l = 0; l < lanes_; l++)
                 if (bcp_gpu_init(BCP_DEVICE_LANE(d & 0xFF, l)) != BCP_OK) { err = bcp_gpu_last_error(); return false; }
+        for (int d : devs) // lane 3: the header checks, made by the scan threads as soon as a block's bytes are at hand
+            if (bcp_gpu_init(BCP_DEVICE_LANE(d & 0xFF, 3)) != BCP_OK) { err = bcp_gpu_last_error(); return false; }
         utxo = bcp_gpu_utxo_create(devs[0] & 0xFF, log2Slots, (size_t)64 << 20);
         if (!utxo) { err = bcp_gpu_last_error(); return false; }
         // The check threads, in the order blocks are dealt to them: lane by lane across the GPUs, so that consecutive
@@ -155,6 +157,9 @@ private:
         long ntx = 0, nin = -1, nout = 0;
         const char *structErr = nullptr;
         uint32_t seq = 0;
+        int rcEq = BCP_OK;     // header check (Equihash + hash), done by the scan thread
+        uint8_t eqOk = 1;
+        std::string eqErr;
         Clock::time_point tApplied;
         bool ok = false;
         std::string reason;
@@ -177,10 +182,22 @@ private:
         return true;
     }
 
-    // framing scan + structure rules of one block into its job (scan thread)
-    void Scan(Job &j) {
+    // framing scan + structure rules of one block into its job, and its header check (scan thread `who`)
+    void Scan(Job &j, size_t who) {
         const uint8_t *b = j.blk;
         const size_t l = j.len;
+        // CheckBlockHeader's part that needs nothing but the header (src/validation.cpp:3202-3220): Equihash + block hash,
+        // one small launch on lane 3 of one of the GPUs — here, not on a check thread, whose time is the GPU's
+        j.rcEq = BCP_OK;
+        j.eqOk = 1;
+        if (ehN) {
+            const size_t soln = ((size_t)1 << ehK) * (ehN / (ehK + 1) + 1) / 8;
+            const size_t hdr_len = 140 + (soln < 253 ? 1 : 3) + soln;
+            if (l >= hdr_len) {
+                j.rcEq = bcp_gpu_equihash_verify_batch(BCP_DEVICE_LANE(devs[who % devs.size()] & 0xFF, 3), ehN, ehK, b, hdr_len, hdr_len, 1, &j.eqOk, j.hash);
+                if (j.rcEq != BCP_OK) j.eqErr = bcp_gpu_last_error();
+            }
+        }
         size_t max_tx = l / 60 + 2, max_in = l / 41 + 2, max_out = l / 34 + 2; /* outputs: first guess, P2PKH-sized */
         int rule = 0; // the scan applies CheckBlock's context-free transaction rules while it has the bytes in the cache
         long ruleTx = -1;
@@ -222,15 +239,11 @@ private:
         auto t1 = Clock::now();
         const double tableLatency = Secs(j.tApplied, t1);
         j.ok = false;
-        // header first, like CheckBlockHeader before anything of the body (src/validation.cpp:3202-3220)
-        const size_t soln = ehN ? ((size_t)1 << ehK) * (ehN / (ehK + 1) + 1) / 8 : 0;
-        const size_t hdr_len = 140 + (soln < 253 ? 1 : 3) + soln;
-        uint8_t eqOk = 1;
-        int rcEq = BCP_OK;
-        if (ehN) {
-            rcEq = bcp_gpu_equihash_verify_batch(dev, ehN, ehK, j.blk, hdr_len, hdr_len, 1, &eqOk, j.hash);
-            if (rcEq != BCP_OK) j.reason = std::string("device-error: ") + bcp_gpu_last_error();
-        }
+        // header first, like CheckBlockHeader before anything of the body (src/validation.cpp:3202-3220); the scan thread
+        // has already run it
+        const uint8_t eqOk = j.eqOk;
+        const int rcEq = j.rcEq;
+        if (rcEq != BCP_OK) j.reason = std::string("device-error: ") + j.eqErr;
         auto t2 = Clock::now();
         double tScripts = 0;
         if (rcEq != BCP_OK) {
@@ -333,7 +346,7 @@ private:
         auto jobOf = [&](long b) -> Job & { return jobs[(size_t)b % R]; };
         // scan threads: block b may be scanned once its ring slot is free (its previous user was committed)
         for (int s = 0; s < nScan; s++)
-            threads.emplace_back([&] {
+            threads.emplace_back([&, s] {
                 for (;;) {
                     long b;
                     {
@@ -348,7 +361,7 @@ private:
                         j.len = blocks[(size_t)b].second;
                     }
                     auto t0 = Clock::now();
-                    Scan(jobOf(b));
+                    Scan(jobOf(b), (size_t)s);
                     const double dt = Secs(t0, Clock::now());
                     {
                         std::lock_guard<std::mutex> l(mu);
@@ -417,11 +430,7 @@ private:
                     const size_t hdr_len = 140 + (soln < 253 ? 1 : 3) + soln;
                     j.ok = false;
                     j.reason = (ehN && j.len < hdr_len) ? "bad-blk-length" : "bad-blk-framing";
-                    if (ehN && j.len >= hdr_len) {
-                        uint8_t eqOk = 1;
-                        if (bcp_gpu_equihash_verify_batch(BCP_DEVICE_LANE(devs[0] & 0xFF, 0), ehN, ehK, j.blk, hdr_len, hdr_len, 1, &eqOk, j.hash) == BCP_OK && !eqOk)
-                            j.reason = "invalid-solution";
-                    }
+                    if (ehN && j.len >= hdr_len && j.rcEq == BCP_OK && !j.eqOk) j.reason = "invalid-solution";
                     j.seq = 0; // never applied
                     --seqCounter;
                     std::lock_guard<std::mutex> l(mu);
