@@ -447,6 +447,9 @@ def chain_bench(args, devices, impl="device"):
         lanes = args.chain_lanes or (3 if len(devices) == 1 else 2)
         scan_threads = max(2, min(8, effective_cpus() // 4))
         h = L.bcp_dchain_new(devs, len(devices), synth.POSTFORK_FLAGS, 48, 5, 22, lanes, scan_threads, err, 256)
+        if h:
+            L.bcp_dchain_reserve.argtypes = [C.c_void_p, C.c_size_t]
+            L.bcp_dchain_reserve(h, max(len(b) for b in blocks) + 4096)  # every pipeline slot's pinned buffers, before the clock starts
     else:
         L.bcp_chain_new.restype = C.c_void_p
         L.bcp_chain_new.argtypes = [C.POINTER(C.c_int), C.c_int, C.c_uint32, C.c_uint, C.c_uint, C.c_char_p, C.c_size_t]

@@ -77,6 +77,21 @@ public:
         jobs.resize(inflightMax + (size_t)nScan + 2);
         return true;
     }
+    //! Optional: allocate the pinned per-block buffers of every pipeline slot now, for blocks of up to max_block_bytes, so
+    //! that no allocation (a pinned allocation mapped into every GPU takes milliseconds and stalls the runtime) happens
+    //! while blocks are being connected.  Without it the buffers grow on first use.
+    void Reserve(size_t max_block_bytes) {
+        const size_t l = max_block_bytes, max_tx = l / 60 + 2, max_in = l / 41 + 2, max_out = l / 34 + 2;
+        auto up = [](size_t x) { return (x + 255) / 256 * 256; };
+        for (Job &j : jobs) {
+            j.tx_off.need(max_tx + 1); j.tx_out_off.need(max_tx + 1);
+            j.in_off.need(max_in); j.in_tx.need(max_in); j.in_n.need(max_in);
+            j.out_off.need(max_out); j.out_tx.need(max_out); j.out_n.need(max_out);
+            j.errs.need(max_in + 1);
+            j.small.need(64);
+            j.packed.need(up((max_tx + 1) * 4) + 2 * up(max_in * 4 + 4) + 3 * up(max_out * 4 + 4));
+        }
+    }
     void AddCoin(const uint8_t txid[32], uint32_t vout, const uint8_t *spk, size_t len, int64_t amount) {
         seedOp.insert(seedOp.end(), txid, txid + 32);
         for (int k = 0; k < 4; k++) seedOp.push_back((uint8_t)(vout >> (8 * k)));
