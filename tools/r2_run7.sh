@@ -1,6 +1,6 @@
 #!/bin/bash
-# round-2 final 1-GPU call: full GPU suite, bench line, launch list of the bench command, ncu --set full of the point kernel
-# (default form) and of the big hash launches
+# round-2 final 1-GPU call: full GPU suite, bench line, launch list of the bench command
+# (one profiler pass per call: the launch list of the bench command)
 mkdir -p gpurun_out
 timeout 900 python -m pytest tests -m gpu -x -q > gpurun_out/pytest_gpu_final.log 2>&1; echo "pytest rc=$?" | tee -a gpurun_out/pytest_gpu_final.log
 tail -4 gpurun_out/pytest_gpu_final.log
@@ -12,12 +12,6 @@ tail -2 gpurun_out/bench_final_1gpu.err
 timeout 600 python bench.py --impl reference --steps 5 --warmup 2 > gpurun_out/bench_final_reference.json 2>/dev/null; echo "ref rc=$?"
 timeout 600 python bench.py --steps 2 --warmup 3 --no-cpu-baseline --no-block > gpurun_out/plain_bench_short.log 2>&1 &&
 timeout 600 ncu --metrics gpu__time_duration.sum --clock-control none --csv --log-file gpurun_out/launches_bench_final.csv python bench.py --steps 2 --warmup 3 --no-cpu-baseline --no-block > gpurun_out/ncu_launches.log 2>&1
-timeout 300 python tools/quick_bench.py 1000000 2 > gpurun_out/plain.log 2>&1 &&
-timeout 900 ncu --set full --clock-control none --import-source on -k regex:k_ecdsa_point -s 2 -c 1 -o gpurun_out/prof_point_final python tools/quick_bench.py 1000000 2 > gpurun_out/ncu_full_final.log 2>&1
-timeout 300 python tools/secondary_probe.py > gpurun_out/plain_secondary.log 2>&1 &&
-timeout 900 ncu --set full --clock-control none -k regex:k_merkle_levels -c 1 -o gpurun_out/prof_merkle python tools/secondary_probe.py > gpurun_out/ncu_merkle.log 2>&1
-timeout 900 ncu --set full --clock-control none -k regex:k_sha256d_msgs -s 4 -c 1 -o gpurun_out/prof_sha256d python tools/secondary_probe.py > gpurun_out/ncu_sha.log 2>&1
-ls -la gpurun_out/*.ncu-rep
 python - <<'PY'
 import json
 d=json.loads(open('gpurun_out/bench_final_1gpu.json').read().strip().splitlines()[-1])
