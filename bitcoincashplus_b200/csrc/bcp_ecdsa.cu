@@ -22,7 +22,7 @@
 #endif
 /* a named barrier over the sync_n threads that walk the steps together: in the last, partly filled round of the persistent
  * kernel only the warps that hold signatures take part, the others have left */
-#define BCP_STEP_SYNC() do { if (BCP_STEP_SYNC_EVERY == 1 || (t % BCP_STEP_SYNC_EVERY) == 0) asm volatile("bar.sync 1, %0;" :: "r"(sync_n) : "memory"); } while (0)
+#define BCP_STEP_SYNC() do { if (sync_n != 0 && (BCP_STEP_SYNC_EVERY == 1 || (t % BCP_STEP_SYNC_EVERY) == 0)) asm volatile("bar.sync 1, %0;" :: "r"(sync_n) : "memory"); } while (0)
 #endif
 #include "ecdsa.cuh"
 #include <cstdlib>
@@ -108,12 +108,20 @@ __global__ void __launch_bounds__(128) k_ecdsa_prep(const uint8_t *__restrict__ 
 __global__ void __launch_bounds__(BCP_POINT_THREADS, BCP_POINT_BLOCKS_PER_SM)
     k_ecdsa_point(const uint8_t *__restrict__ pub65, const uint8_t *__restrict__ sig64, size_t n,
                   const uint32_t *__restrict__ rec, uint32_t *__restrict__ qtabs, const uint32_t *__restrict__ gcomb,
-                  uint8_t *__restrict__ ok) {
+                  uint8_t *__restrict__ ok, uint32_t redo_every) {
     const size_t gi = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
     const size_t i = gi < n ? gi : n - 1; /* tail threads shadow the last signature (they must reach the barriers) */
     qtable_packed tab;
     tab.base = qtabs + gi * BCP_QTAB_WORDS; /* own slab even when shadowing: scratch is sized for whole blocks */
-    bool v = ecdsa_point_phase(rec + i * BCP_REC_WORDS, pub65 + 65 * i, sig64 + 64 * i, tab, gcomb, (int)blockDim.x);
+    // The walk with the branch-free field operations; `bad` counts the folds they left unfinished (about two signatures
+    // in a million have one).  Such a signature is walked again with the exact operations, alone: no barrier.
+    // redo_every (test hook, BCP_POINT_FORCE_REDO): every redo_every-th signature is treated as if it had one.
+    uint32_t bad = 0;
+    bool v = ecdsa_point_phase<qtable_packed, false, fe_quick>(rec + i * BCP_REC_WORDS, pub65 + 65 * i, sig64 + 64 * i, tab, gcomb,
+                                                               (int)blockDim.x, nullptr, &bad);
+    if (redo_every != 0 && gi % redo_every == 0) bad = 1;
+    if (__builtin_expect(bad != 0, 0))
+        v = ecdsa_point_phase<qtable_packed, false, fe_exact>(rec + i * BCP_REC_WORDS, pub65 + 65 * i, sig64 + 64 * i, tab, gcomb, 0);
     if (gi < n) ok[gi] = v ? 1 : 0;
 }
 
@@ -270,6 +278,44 @@ __global__ void k_fe_selftest(int *fail) {
         fe_normalize(r1);
         fe_normalize(na);
         for (int i = 0; i < 8; i++) bad |= r1.v[i] != na.v[i];
+        // the quick forms of the point kernel (carry counted, not finished): a count of zero promises the exact value
+        uint32_t q = 0;
+        fe_add_q(r1, a, b, q);
+        fe_add_full(r2, a, b);
+        if (q) atomicAdd(fail + 1, 1);
+        else for (int i = 0; i < 8; i++) bad |= r1.v[i] != r2.v[i];
+        q = 0;
+        fe_sub_q(r1, a, b, q);
+        fe_sub_full(r2, a, b);
+        if (q) atomicAdd(fail + 1, 1);
+        else for (int i = 0; i < 8; i++) bad |= r1.v[i] != r2.v[i];
+        q = 0;
+        fe_reduce_wide_q(r1, w, q);
+        fe_reduce_wide_t<false>(r2, w);
+        if (q) atomicAdd(fail + 1, 1);
+        else for (int i = 0; i < 8; i++) bad |= r1.v[i] != r2.v[i];
+        q = 0;
+        sqr_wide(w, a.v);
+        fe_reduce_wide_q(r1, w, q);
+        fe_reduce_wide_t<false>(r2, w);
+        m1 = fe_mul_f(a, a);
+        fe_normalize(r2);
+        fe_normalize(m1);
+        for (int i = 0; i < 8; i++) bad |= r2.v[i] != m1.v[i]; /* the squaring against the multiplication */
+        if (!q) { fe_normalize(r1); for (int i = 0; i < 8; i++) bad |= r1.v[i] != m1.v[i]; }
+        q = 0;
+        fe_neg_q(r1, a, q);
+        fe_neg(r2, a);
+        fe_normalize(r1);
+        fe_normalize(r2);
+        if (q) atomicAdd(fail + 1, 1);
+        else for (int i = 0; i < 8; i++) bad |= r1.v[i] != r2.v[i];
+        q = 0;
+        fe_mul8_q(r1, a, q);
+        fe_dbl(r2, a); fe_dbl(r2, r2); fe_dbl(r2, r2);
+        fe_normalize(r1);
+        fe_normalize(r2);
+        if (!q) for (int i = 0; i < 8; i++) bad |= r1.v[i] != r2.v[i];
     }
     if (t < BCP_FE_ST_WIDE) {
         fe r1, r2;
@@ -278,22 +324,34 @@ __global__ void k_fe_selftest(int *fail) {
         fe_reduce_wide_t<true>(r1, w);
         fe_reduce_wide_t<false>(r2, w);
         for (int i = 0; i < 8; i++) bad |= r1.v[i] != r2.v[i];
+        uint32_t q = 0;
+        fe_reduce_wide_q(r1, w, q);
+        if (q) atomicAdd(fail + 1, 1);
+        else for (int i = 0; i < 8; i++) bad |= r1.v[i] != r2.v[i];
     }
     if (bad) atomicAdd(fail, 1);
 }
 int bcp_fe_selftest(bcp_ctx *c) {
-    int *d_fail = nullptr, h_fail = -1;
-    BCP_CUDA(cudaMalloc(&d_fail, sizeof(int)));
-    BCP_CUDA(cudaMemsetAsync(d_fail, 0, sizeof(int), c->stream));
+    int *d_fail = nullptr, h_fail[2] = {-1, -1}; /* [0] disagreements; [1] how often a quick form counted a carry */
+    BCP_CUDA(cudaMalloc(&d_fail, 2 * sizeof(int)));
+    BCP_CUDA(cudaMemsetAsync(d_fail, 0, 2 * sizeof(int), c->stream));
     k_fe_selftest<<<(BCP_FE_ST_EDGES * BCP_FE_ST_EDGES + 127) / 128, 128, 0, c->stream>>>(d_fail);
     cudaError_t e = cudaGetLastError();
-    if (e == cudaSuccess) e = cudaMemcpyAsync(&h_fail, d_fail, sizeof(int), cudaMemcpyDeviceToHost, c->stream);
+    if (e == cudaSuccess) e = cudaMemcpyAsync(h_fail, d_fail, 2 * sizeof(int), cudaMemcpyDeviceToHost, c->stream);
     if (e == cudaSuccess) e = cudaStreamSynchronize(c->stream);
     cudaFree(d_fail);
     if (e != cudaSuccess) return bcp_cuda_fail(e, "field self-test");
-    if (h_fail != 0) {
-        bcp_set_error("field arithmetic self-test failed on device %d: %d operand pairs disagree between the short-cut and the "
-                      "full carry chains", c->device, h_fail);
+    if (h_fail[0] != 0) {
+        bcp_set_error("field arithmetic self-test failed on device %d: %d operand pairs disagree between the short-cut or quick forms "
+                      "and the full carry chains", c->device, h_fail[0]);
+        return BCP_ERR_CUDA;
+    }
+    // the crafted operands exist to leave limb 1 / limb 2: the quick forms must have counted carries on many of them, and
+    // not on all (a form that always counts would send every signature through the exact walk as well)
+    const int cases = BCP_FE_ST_EDGES * BCP_FE_ST_EDGES * 5 + BCP_FE_ST_WIDE;
+    if (h_fail[1] < 8 || h_fail[1] > cases / 2) {
+        bcp_set_error("field arithmetic self-test failed on device %d: the quick forms counted a carry in %d of %d crafted cases",
+                      c->device, h_fail[1], cases);
         return BCP_ERR_CUDA;
     }
     return BCP_OK;
@@ -365,8 +423,9 @@ int bcp_ecdsa_launch(bcp_ctx *c, const uint8_t *d_msg, const uint8_t *d_pub, con
         }
         const unsigned tpb = forced_tpb ? (unsigned)forced_tpb : (m <= BCP_WAVE ? BCP_POINT_SMALL_TPB : BCP_POINT_THREADS);
         unsigned blocks = (unsigned)((m + tpb - 1) / tpb);
+        static const unsigned redo_every = getenv("BCP_POINT_FORCE_REDO") ? (unsigned)atoi(getenv("BCP_POINT_FORCE_REDO")) : 0u; /* tests */
         k_ecdsa_point<<<blocks, tpb, 0, st>>>(d_pub + 65 * off, d_sig + 64 * off, m, d_rec, d_tab, c->gcomb,
-                                                           d_ok + off);
+                                                           d_ok + off, redo_every);
     }
     BCP_CUDA(cudaGetLastError());
     return BCP_OK;

@@ -189,10 +189,13 @@ struct qtable_packed {
 // sync_n = how many threads of the block walk the steps together (what BCP_STEP_SYNC waits for); unused on the host build.
 // WANT_POINT: hand back R = u1*G + u2*Q itself (Jacobian) instead of comparing its x with r — the recovery and
 // tweak-add entry points are the same walk with other scalars; returns whether R is a finite point of a valid input.
-template <class Table, bool WANT_POINT = false>
+// F: the field operations of the walk (ge.cuh): fe_exact, or fe_quick with the count of unfinished folds in *bad_out — the
+// caller then repeats the call with fe_exact (and sync_n = 0: no barrier, the other threads are not coming).
+template <class Table, bool WANT_POINT = false, class F = fe_exact>
 BCP_DEV bool ecdsa_point_phase(const uint32_t *rec, const uint8_t *pub65, const uint8_t *sig64, Table tab,
-                               const uint32_t *gcomb, const int sync_n = 0, gej *out = nullptr) {
+                               const uint32_t *gcomb, const int sync_n = 0, gej *out = nullptr, uint32_t *bad_out = nullptr) {
     (void)sync_n;
+    uint32_t bad = 0;
     const uint32_t fl = rec[18];
     gej acc;
     // A signature that is already known to be invalid keeps walking (on the generator instead of its own
@@ -236,14 +239,14 @@ BCP_DEV bool ecdsa_point_phase(const uint32_t *rec, const uint8_t *pub65, const 
                     fe ex, ey, zs2, zs3;
                     tab.load(k, ex, ey);
                     if (k < BCP_QTAB_ENTRIES - 1) {
-                        fe_sqr(zs2, zs);
-                        fe_mul(zs3, zs2, zs);
-                        fe_mul(ex, ex, zs2);
-                        fe_mul(ey, ey, zs3);
+                        F::sqr(zs2, zs, bad);
+                        F::mul(zs3, zs2, zs, bad);
+                        F::mul(ex, ex, zs2, bad);
+                        F::mul(ey, ey, zs3, bad);
                         tab.store(k, ex, ey);
-                        if (k > 0) fe_mul(zs, zs, zr[k]);
+                        if (k > 0) F::mul(zs, zs, zr[k], bad);
                     }
-                    fe_mul(ex, ex, beta); /* x of lambda * (k+1)Q: one product per entry instead of one per use */
+                    F::mul(ex, ex, beta, bad); /* x of lambda * (k+1)Q: one product per entry instead of one per use */
                     tab.store_xb(k, ex);
                 }
                 acc.inf = true;
@@ -260,12 +263,12 @@ BCP_DEV bool ecdsa_point_phase(const uint32_t *rec, const uint8_t *pub65, const 
                     const bool neg = (d < 0) != (second ? n2 : n1);
                     if (second) tab.load_b((d < 0 ? -d : d) - 1, x, y); /* lambda * (x, y) = (beta * x, y) */
                     else tab.load((d < 0 ? -d : d) - 1, x, y);
-                    if (neg) fe_neg(y, y);
+                    if (neg) F::neg(y, y, bad);
                     have = true;
                 }
             }
         } else if (t == T_TAB + T_MAIN) {
-            if (!acc.inf) fe_mul(acc.z, acc.z, zglob);
+            if (!acc.inf) F::mul(acc.z, acc.z, zglob, bad);
             continue;
         } else {
             const int j = t - (T_TAB + T_MAIN + 1);
@@ -297,34 +300,35 @@ BCP_DEV bool ecdsa_point_phase(const uint32_t *rec, const uint8_t *pub65, const 
             }
             // mixed addition acc += (x, y): 8M + 3S, with the degenerate branches of gej_add_ge_var (:438-448)
             fe z2, u2, s2, rr, h2, h3, v, tt;
-            fe_sqr(z2, acc.z);
-            fe_mul(u2, x, z2);
-            fe_mul(tt, acc.z, z2);
-            fe_mul(s2, y, tt);
-            fe_sub(h, u2, acc.x);
-            fe_sub(rr, s2, acc.y);
+            F::sqr(z2, acc.z, bad);
+            F::mul(u2, x, z2, bad);
+            F::mul(tt, acc.z, z2, bad);
+            F::mul(s2, y, tt, bad);
+            F::sub(h, u2, acc.x, bad);
+            F::sub(rr, s2, acc.y, bad);
             if (fe_is_zero(h)) {
                 if (fe_is_zero(rr)) dbl = true;           /* P + P: fall through to the shared doubling  */
                 else { acc.inf = true; continue; }        /* P + (-P)                                       */
             } else {
-                fe_sqr(h2, h);
-                fe_mul(h3, h2, h);
-                fe_mul(v, acc.x, h2);
-                fe_mul(acc.z, acc.z, h);
-                fe_sqr(tt, rr);
-                fe_sub(tt, tt, h3); fe_sub(tt, tt, v); fe_sub(acc.x, tt, v);
-                fe_sub(tt, v, acc.x);
-                fe_mul(tt, tt, rr);
-                fe_mul(h3, h3, acc.y);
-                fe_sub(acc.y, tt, h3);
+                F::sqr(h2, h, bad);
+                F::mul(h3, h2, h, bad);
+                F::mul(v, acc.x, h2, bad);
+                F::mul(acc.z, acc.z, h, bad);
+                F::sqr(tt, rr, bad);
+                F::sub(tt, tt, h3, bad); F::sub(tt, tt, v, bad); F::sub(acc.x, tt, v, bad);
+                F::sub(tt, v, acc.x, bad);
+                F::mul(tt, tt, rr, bad);
+                F::mul(h3, h3, acc.y, bad);
+                F::sub(acc.y, tt, h3, bad);
             }
         }
-        if (dbl && !acc.inf) gej_double(acc, acc);
+        if (dbl && !acc.inf) gej_double_t<F>(acc, acc, bad);
         if (t < T_TAB) {
             tab.store(t + 1, acc.x, acc.y);
             zr[t + 1] = (t == 0) ? acc.z : h;
         }
     }
+    if (bad_out) *bad_out = bad;
     if (WANT_POINT) {
         *out = acc;
         return valid && !acc.inf;

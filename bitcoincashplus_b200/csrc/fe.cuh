@@ -30,10 +30,10 @@ struct fe {
 // X[0..7] = { a0*b, a2*b, a4*b, a6*b } as four independent 64-bit products
 BCP_DEV void row_set(uint32_t *X, uint32_t a0, uint32_t a2, uint32_t a4, uint32_t a6, uint32_t b) {
 #if BCP_PTX
-    asm("mul.lo.u32 %0, %8, %12;\n\tmul.hi.u32 %1, %8, %12;\n\t"
-        "mul.lo.u32 %2, %9, %12;\n\tmul.hi.u32 %3, %9, %12;\n\t"
-        "mul.lo.u32 %4, %10, %12;\n\tmul.hi.u32 %5, %10, %12;\n\t"
-        "mul.lo.u32 %6, %11, %12;\n\tmul.hi.u32 %7, %11, %12;"
+    /* mul.wide, not a mul.lo / mul.hi pair: ptxas splits a pair into IMAD + IMAD.HI (2 + 4 issue cycles) when it likes */
+    asm("{\n\t.reg .u64 p0, p1, p2, p3;\n\t"
+        "mul.wide.u32 p0, %8, %12;\n\tmul.wide.u32 p1, %9, %12;\n\tmul.wide.u32 p2, %10, %12;\n\tmul.wide.u32 p3, %11, %12;\n\t"
+        "mov.b64 {%0, %1}, p0;\n\tmov.b64 {%2, %3}, p1;\n\tmov.b64 {%4, %5}, p2;\n\tmov.b64 {%6, %7}, p3;\n\t}"
         : "=r"(X[0]), "=r"(X[1]), "=r"(X[2]), "=r"(X[3]), "=r"(X[4]), "=r"(X[5]), "=r"(X[6]), "=r"(X[7])
         : "r"(a0), "r"(a2), "r"(a4), "r"(a6), "r"(b));
 #else
@@ -130,7 +130,7 @@ BCP_DEV void row_acc_k(uint32_t *X, const uint32_t *a, uint32_t b) {
 }
 BCP_DEV void wide_mul(uint32_t &lo, uint32_t &hi, uint32_t a, uint32_t b) {
 #if BCP_PTX
-    asm("mul.lo.u32 %0, %2, %3;\n\tmul.hi.u32 %1, %2, %3;" : "=r"(lo), "=r"(hi) : "r"(a), "r"(b));
+    asm("{\n\t.reg .u64 p;\n\tmul.wide.u32 p, %2, %3;\n\tmov.b64 {%0, %1}, p;\n\t}" : "=r"(lo), "=r"(hi) : "r"(a), "r"(b));
 #else
     uint64_t p = (uint64_t)a * b;
     lo = (uint32_t)p;
@@ -568,14 +568,30 @@ BCP_DEV void sqr_wide(uint32_t *r /*16*/, const uint32_t *a) {
     { const uint32_t m[1] = {a[6]}; row_acc_k<1>(O + 10, m, a[5]); }              /* limb 11       */
     { const uint32_t m[1] = {a[7]}; row_acc_k<1>(E + 12, m, a[5]); }              /* limb 12       */
     { const uint32_t m[1] = {a[7]}; row_acc_k<1>(O + 12, m, a[6]); }              /* limb 13       */
-    uint32_t S[16], T[16], D[16];
+    uint32_t S[16], T[16];
     merge_even_odd(S, E, O);
     T[0] = S[0] << 1;
     BCP_UNROLL
     for (int k = 1; k < 16; k++) T[k] = (S[k] << 1) | (S[k - 1] >> 31);
-    BCP_UNROLL
+#if BCP_PTX
+    // r = T + the eight diagonal squares, as one carry chain of multiply-adds (8 IMAD.WIDE.U32.X, no separate additions)
+    asm("mad.lo.cc.u32 %0, %16, %16, %24;\n\tmadc.hi.cc.u32 %1, %16, %16, %25;\n\t"
+        "madc.lo.cc.u32 %2, %17, %17, %26;\n\tmadc.hi.cc.u32 %3, %17, %17, %27;\n\t"
+        "madc.lo.cc.u32 %4, %18, %18, %28;\n\tmadc.hi.cc.u32 %5, %18, %18, %29;\n\t"
+        "madc.lo.cc.u32 %6, %19, %19, %30;\n\tmadc.hi.cc.u32 %7, %19, %19, %31;\n\t"
+        "madc.lo.cc.u32 %8, %20, %20, %32;\n\tmadc.hi.cc.u32 %9, %20, %20, %33;\n\t"
+        "madc.lo.cc.u32 %10, %21, %21, %34;\n\tmadc.hi.cc.u32 %11, %21, %21, %35;\n\t"
+        "madc.lo.cc.u32 %12, %22, %22, %36;\n\tmadc.hi.cc.u32 %13, %22, %22, %37;\n\t"
+        "madc.lo.cc.u32 %14, %23, %23, %38;\n\tmadc.hi.u32 %15, %23, %23, %39;"
+        : "=&r"(r[0]), "=&r"(r[1]), "=&r"(r[2]), "=&r"(r[3]), "=&r"(r[4]), "=&r"(r[5]), "=&r"(r[6]), "=&r"(r[7]), "=&r"(r[8]), "=&r"(r[9]),
+          "=&r"(r[10]), "=&r"(r[11]), "=&r"(r[12]), "=&r"(r[13]), "=&r"(r[14]), "=&r"(r[15])
+        : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(a[4]), "r"(a[5]), "r"(a[6]), "r"(a[7]), "r"(T[0]), "r"(T[1]), "r"(T[2]), "r"(T[3]),
+          "r"(T[4]), "r"(T[5]), "r"(T[6]), "r"(T[7]), "r"(T[8]), "r"(T[9]), "r"(T[10]), "r"(T[11]), "r"(T[12]), "r"(T[13]), "r"(T[14]), "r"(T[15]));
+#else
+    uint32_t D[16];
     for (int i = 0; i < 8; i++) wide_mul(D[2 * i], D[2 * i + 1], a[i], a[i]);
     add16(r, T, D);
+#endif
 }
 BCP_FE_FN fe fe_sqr_f(fe a) {
     uint32_t t[16];
@@ -655,6 +671,140 @@ BCP_DEV void fe_neg(fe &r, const fe &a) {
     fe_sub(r, z, a);
 }
 BCP_DEV void fe_dbl(fe &r, const fe &a) { fe_add(r, a, a); }
+
+// ------------------------------------------------------------------ quick forms (the point kernel's hot loop)
+// Same results as fe_mul / fe_sqr / fe_add / fe_sub / fe_neg, without their out-of-line branch: the carry that would
+// send those to the full chains (out of limb 2 in the reduction, out of limb 1 in an addition: probability about 2^-30
+// and 2^-33 per operation, two signatures in a million hit one somewhere) is COUNTED in `bad` and the result is then not
+// reduced correctly.  The caller checks `bad` once at the end and redoes the whole computation with the exact forms
+// above when it is not zero.  What this buys: three to four instructions per field operation (branch, reconvergence
+// pair, flag test) — every instruction of the point kernel costs an issue slot next to the multiplier instructions
+// (tools/ubench/pipe_mix.cu).
+BCP_DEV void fe_reduce_wide_q(fe &r, const uint32_t *t /*16*/, uint32_t &bad) {
+    // first fold as in fe_reduce_wide_t: S = L + H*977 + (H << 32) in two interleaved arrays
+    uint32_t EV[9], OD[9];
+    BCP_UNROLL
+    for (int k = 0; k < 8; k++) { EV[k] = t[k]; OD[k] = t[8 + k]; }
+    EV[8] = 0; OD[8] = 0;
+    row_acc9(EV, t[8], t[10], t[12], t[14], BCP_FOLD);
+    row_acc9(OD, t[9], t[11], t[13], t[15], BCP_FOLD);
+    uint32_t s[10];
+    s[0] = EV[0];
+#if BCP_PTX
+    // s[1..8] = EV[1..8] + OD[0..7]; s[9] = OD[8] + carry (<= 3)
+    asm("add.cc.u32 %0, %9, %17;\n\taddc.cc.u32 %1, %10, %18;\n\taddc.cc.u32 %2, %11, %19;\n\taddc.cc.u32 %3, %12, %20;\n\t"
+        "addc.cc.u32 %4, %13, %21;\n\taddc.cc.u32 %5, %14, %22;\n\taddc.cc.u32 %6, %15, %23;\n\taddc.cc.u32 %7, %16, %24;\n\t"
+        "addc.u32 %8, %25, 0;"
+        : "=&r"(s[1]), "=&r"(s[2]), "=&r"(s[3]), "=&r"(s[4]), "=&r"(s[5]), "=&r"(s[6]), "=&r"(s[7]), "=&r"(s[8]), "=r"(s[9])
+        : "r"(EV[1]), "r"(EV[2]), "r"(EV[3]), "r"(EV[4]), "r"(EV[5]), "r"(EV[6]), "r"(EV[7]), "r"(EV[8]), "r"(OD[0]), "r"(OD[1]),
+          "r"(OD[2]), "r"(OD[3]), "r"(OD[4]), "r"(OD[5]), "r"(OD[6]), "r"(OD[7]), "r"(OD[8]));
+#else
+    s[9] = OD[8] + addn_cc<8>(s + 1, EV + 1, OD);
+#endif
+    // second fold: T = s[9]:s[8] < 2^34;  S' = s[0..7] + T*977 + (T << 32) reaches limbs 0..2 only
+    uint32_t mlo, mhi;
+#if BCP_PTX
+    asm("{\n\t.reg .u64 m;\n\tmul.wide.u32 m, %2, 977;\n\tmov.b64 {%0, %1}, m;\n\t}" : "=r"(mlo), "=r"(mhi) : "r"(s[8])); /* one IMAD.WIDE */
+#else
+    wide_mul(mlo, mhi, s[8], BCP_FOLD);
+#endif
+    const uint32_t h = s[9] * BCP_FOLD + mhi; /* < 977 + 3 * 977: no overflow */
+#if BCP_PTX
+    uint32_t r0, r1, r2;
+    asm("{\n\t.reg .u32 a1, a2;\n\t"
+        "add.cc.u32 a1, %4, %5;\n\taddc.u32 a2, %6, 0;\n\t"                          /* a2:a1 = h + s8 + (s9 << 32) */
+        "add.cc.u32 %0, %7, %10;\n\taddc.cc.u32 %1, %8, a1;\n\taddc.cc.u32 %2, %9, a2;\n\t"
+        "addc.u32 %3, %3, 0;\n\t}"                                                      /* the carry out of limb 2 is counted */
+        : "=&r"(r0), "=&r"(r1), "=&r"(r2), "+r"(bad)
+        : "r"(h), "r"(s[8]), "r"(s[9]), "r"(s[0]), "r"(s[1]), "r"(s[2]), "r"(mlo));
+    r.v[0] = r0; r.v[1] = r1; r.v[2] = r2;
+#else
+    const uint64_t a1 = (uint64_t)h + s[8];
+    const uint32_t A[3] = {mlo, (uint32_t)a1, s[9] + (uint32_t)(a1 >> 32)};
+    uint32_t lo3[3];
+    bad += addn_cc<3>(lo3, s, A);
+    r.v[0] = lo3[0]; r.v[1] = lo3[1]; r.v[2] = lo3[2];
+#endif
+    BCP_UNROLL
+    for (int i = 3; i < 8; i++) r.v[i] = s[i];
+}
+BCP_DEV void fe_mul_q(fe &r, const fe &a, const fe &b, uint32_t &bad) {
+    uint32_t t[16];
+    mul_wide(t, a.v, b.v);
+    fe_reduce_wide_q(r, t, bad);
+}
+BCP_DEV void fe_sqr_q(fe &r, const fe &a, uint32_t &bad) {
+    uint32_t t[16];
+    sqr_wide(t, a.v);
+    fe_reduce_wide_q(r, t, bad);
+}
+BCP_DEV void fe_add_q(fe &r, const fe &a, const fe &b, uint32_t &bad) {
+#if BCP_PTX
+    uint32_t r0, r1, r2, r3, r4, r5, r6, r7;
+    asm("{\n\t.reg .u32 c, k;\n\t.reg .pred p;\n\t"
+        "add.cc.u32 %0, %9, %17;\n\taddc.cc.u32 %1, %10, %18;\n\taddc.cc.u32 %2, %11, %19;\n\taddc.cc.u32 %3, %12, %20;\n\t"
+        "addc.cc.u32 %4, %13, %21;\n\taddc.cc.u32 %5, %14, %22;\n\taddc.cc.u32 %6, %15, %23;\n\taddc.cc.u32 %7, %16, %24;\n\t"
+        "addc.u32 c, 0, 0;\n\t"
+        "setp.ne.u32 p, c, 0;\n\tselp.u32 k, 977, 0, p;\n\t" /* + c * (2^32 + 977) */
+        "add.cc.u32 %0, %0, k;\n\taddc.cc.u32 %1, %1, c;\n\taddc.u32 %8, %8, 0;\n\t}"
+        : "=&r"(r0), "=&r"(r1), "=&r"(r2), "=&r"(r3), "=&r"(r4), "=&r"(r5), "=&r"(r6), "=&r"(r7), "+r"(bad)
+        : "r"(a.v[0]), "r"(a.v[1]), "r"(a.v[2]), "r"(a.v[3]), "r"(a.v[4]), "r"(a.v[5]), "r"(a.v[6]), "r"(a.v[7]), "r"(b.v[0]),
+          "r"(b.v[1]), "r"(b.v[2]), "r"(b.v[3]), "r"(b.v[4]), "r"(b.v[5]), "r"(b.v[6]), "r"(b.v[7]));
+    r.v[0] = r0; r.v[1] = r1; r.v[2] = r2; r.v[3] = r3; r.v[4] = r4; r.v[5] = r5; r.v[6] = r6; r.v[7] = r7;
+#else
+    uint32_t t[8];
+    const uint32_t c = addn_cc<8>(t, a.v, b.v);
+    const uint32_t A2[2] = {(0u - c) & BCP_FOLD, c};
+    uint32_t lo2[2];
+    bad += addn_cc<2>(lo2, t, A2);
+    r.v[0] = lo2[0]; r.v[1] = lo2[1];
+    for (int i = 2; i < 8; i++) r.v[i] = t[i];
+#endif
+}
+BCP_DEV void fe_sub_q(fe &r, const fe &a, const fe &b, uint32_t &bad) {
+#if BCP_PTX
+    uint32_t r0, r1, r2, r3, r4, r5, r6, r7;
+    asm("{\n\t.reg .u32 c, k;\n\t.reg .pred p;\n\t"
+        "sub.cc.u32 %0, %9, %17;\n\tsubc.cc.u32 %1, %10, %18;\n\tsubc.cc.u32 %2, %11, %19;\n\tsubc.cc.u32 %3, %12, %20;\n\t"
+        "subc.cc.u32 %4, %13, %21;\n\tsubc.cc.u32 %5, %14, %22;\n\tsubc.cc.u32 %6, %15, %23;\n\tsubc.cc.u32 %7, %16, %24;\n\t"
+        "addc.u32 c, 0, 0;\n\t"                                  /* CC.CF after a subtraction is the borrow: 0 or 1 */
+        "setp.ne.u32 p, c, 0;\n\tselp.u32 k, 977, 0, p;\n\t"   /* - borrow * (2^32 + 977) */
+        "sub.cc.u32 %0, %0, k;\n\tsubc.cc.u32 %1, %1, c;\n\taddc.u32 %8, %8, 0;\n\t}" /* counts the borrow out of limb 1 */
+        : "=&r"(r0), "=&r"(r1), "=&r"(r2), "=&r"(r3), "=&r"(r4), "=&r"(r5), "=&r"(r6), "=&r"(r7), "+r"(bad)
+        : "r"(a.v[0]), "r"(a.v[1]), "r"(a.v[2]), "r"(a.v[3]), "r"(a.v[4]), "r"(a.v[5]), "r"(a.v[6]), "r"(a.v[7]), "r"(b.v[0]),
+          "r"(b.v[1]), "r"(b.v[2]), "r"(b.v[3]), "r"(b.v[4]), "r"(b.v[5]), "r"(b.v[6]), "r"(b.v[7]));
+    r.v[0] = r0; r.v[1] = r1; r.v[2] = r2; r.v[3] = r3; r.v[4] = r4; r.v[5] = r5; r.v[6] = r6; r.v[7] = r7;
+#else
+    uint32_t t[8];
+    const uint32_t bw = subn_cc<8>(t, a.v, b.v);
+    const uint32_t A2[2] = {(0u - bw) & BCP_FOLD, bw};
+    uint32_t lo2[2];
+    bad += subn_cc<2>(lo2, t, A2);
+    r.v[0] = lo2[0]; r.v[1] = lo2[1];
+    for (int i = 2; i < 8; i++) r.v[i] = t[i];
+#endif
+}
+BCP_DEV void fe_dbl_q(fe &r, const fe &a, uint32_t &bad) { fe_add_q(r, a, a, bad); }
+// r = 8a: shift by three bits, the three bits that leave the top limb come back times 2^32 + 977
+BCP_DEV void fe_mul8_q(fe &r, const fe &a, uint32_t &bad) {
+    const uint32_t top = a.v[7] >> 29;
+    uint32_t s[8];
+    BCP_UNROLL
+    for (int i = 7; i > 0; i--) s[i] = (a.v[i] << 3) | (a.v[i - 1] >> 29);
+    s[0] = a.v[0] << 3;
+    const uint32_t A2[2] = {top * BCP_FOLD, top};
+    uint32_t lo2[2];
+    bad += addn_cc<2>(lo2, s, A2);
+    r.v[0] = lo2[0]; r.v[1] = lo2[1];
+    BCP_UNROLL
+    for (int i = 2; i < 8; i++) r.v[i] = s[i];
+}
+// r = -a = p - a for a <= p; an element above p (possible for a weakly reduced value, never seen on random data) borrows
+// out of the top limb and is counted in `bad`
+BCP_DEV void fe_neg_q(fe &r, const fe &a, uint32_t &bad) {
+    const uint32_t P[8] = {BCP_P0, BCP_P1, 0xFFFFFFFFu, 0xFFFFFFFFu, 0xFFFFFFFFu, 0xFFFFFFFFu, 0xFFFFFFFFu, 0xFFFFFFFFu};
+    bad += subn_cc<8>(r.v, P, a.v);
+}
 
 // canonical representative in [0, p)
 BCP_DEV void fe_normalize(fe &a) {

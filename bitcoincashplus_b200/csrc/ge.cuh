@@ -20,29 +20,56 @@ BCP_CONST uint32_t FE_GX[8] = {0x16f81798u, 0x59f2815bu, 0x2dce28d9u, 0x029bfcdb
 BCP_CONST uint32_t FE_GY[8] = {0xfb10d4b8u, 0x9c47d08fu, 0xa6855419u, 0xfd17b448u,
                                0x0e1108a8u, 0x5da4fbfcu, 0x26a3c465u, 0x483ada77u};
 
+// The field operations a group formula is written over: `fe_exact` finishes every fold in place (out-of-line branch for
+// the practically-never carries), `fe_quick` counts those carries in `bad` instead and leaves the result unreduced then —
+// the caller redoes the whole computation with fe_exact when bad != 0 (fe.cuh, "quick forms").
+struct fe_exact {
+    static BCP_DEV_M void mul(fe &r, const fe &a, const fe &b, uint32_t &) { fe_mul(r, a, b); }
+    static BCP_DEV_M void sqr(fe &r, const fe &a, uint32_t &) { fe_sqr(r, a); }
+    static BCP_DEV_M void add(fe &r, const fe &a, const fe &b, uint32_t &) { fe_add(r, a, b); }
+    static BCP_DEV_M void sub(fe &r, const fe &a, const fe &b, uint32_t &) { fe_sub(r, a, b); }
+    static BCP_DEV_M void dbl(fe &r, const fe &a, uint32_t &) { fe_dbl(r, a); }
+    static BCP_DEV_M void mul8(fe &r, const fe &a, uint32_t &) { fe_dbl(r, a); fe_dbl(r, r); fe_dbl(r, r); }
+    static BCP_DEV_M void neg(fe &r, const fe &a, uint32_t &) { fe_neg(r, a); }
+};
+struct fe_quick {
+    static BCP_DEV_M void mul(fe &r, const fe &a, const fe &b, uint32_t &bad) { fe_mul_q(r, a, b, bad); }
+    static BCP_DEV_M void sqr(fe &r, const fe &a, uint32_t &bad) { fe_sqr_q(r, a, bad); }
+    static BCP_DEV_M void add(fe &r, const fe &a, const fe &b, uint32_t &bad) { fe_add_q(r, a, b, bad); }
+    static BCP_DEV_M void sub(fe &r, const fe &a, const fe &b, uint32_t &bad) { fe_sub_q(r, a, b, bad); }
+    static BCP_DEV_M void dbl(fe &r, const fe &a, uint32_t &bad) { fe_dbl_q(r, a, bad); }
+    static BCP_DEV_M void mul8(fe &r, const fe &a, uint32_t &bad) { fe_mul8_q(r, a, bad); }
+    static BCP_DEV_M void neg(fe &r, const fe &a, uint32_t &bad) { fe_neg_q(r, a, bad); }
+};
+
 // r = 2a.  2M + 5S (the a = 0 doubling with X*Y^2 taken from (X + Y^2)^2: one multiplication becomes a squaring,
 // which is 28 IMAD.WIDE cheaper here, for three more additions).  No point of order two exists on this curve, so
 // y = 0 never occurs for a finite point and the only special case is infinity (group_impl.h:320-326).
-BCP_DEV void gej_double(gej &r, const gej &a) {
+template <class F>
+BCP_DEV void gej_double_t(gej &r, const gej &a, uint32_t &bad) {
     if (a.inf) { r = a; return; }
     fe t, A, B, C, D, E;
-    fe_mul(t, a.y, a.z);
-    fe_sqr(A, a.x);
-    fe_sqr(B, a.y);
-    fe_dbl(r.z, t);                 /* Z3 = 2YZ */
-    fe_add(t, a.x, B);
-    fe_sqr(C, B);                   /* C = Y^4 */
-    fe_sqr(t, t);                   /* (X + Y^2)^2 */
-    fe_sub(t, t, A); fe_sub(t, t, C);
-    fe_dbl(D, t);                   /* D = 4XY^2 */
-    fe_dbl(E, A); fe_add(E, E, A);  /* E = 3X^2 */
-    fe_sqr(t, E);
-    fe_sub(t, t, D); fe_sub(r.x, t, D);       /* X3 = E^2 - 2D */
-    fe_dbl(C, C); fe_dbl(C, C); fe_dbl(C, C); /* 8Y^4 */
-    fe_sub(t, D, r.x);
-    fe_mul(t, E, t);
-    fe_sub(r.y, t, C);              /* Y3 = E(D - X3) - 8Y^4 */
+    F::mul(t, a.y, a.z, bad);
+    F::sqr(A, a.x, bad);
+    F::sqr(B, a.y, bad);
+    F::dbl(r.z, t, bad);                 /* Z3 = 2YZ */
+    F::add(t, a.x, B, bad);
+    F::sqr(C, B, bad);                   /* C = Y^4 */
+    F::sqr(t, t, bad);                   /* (X + Y^2)^2 */
+    F::sub(t, t, A, bad); F::sub(t, t, C, bad);
+    F::dbl(D, t, bad);                   /* D = 4XY^2 */
+    F::dbl(E, A, bad); F::add(E, E, A, bad);  /* E = 3X^2 */
+    F::sqr(t, E, bad);
+    F::sub(t, t, D, bad); F::sub(r.x, t, D, bad); /* X3 = E^2 - 2D */
+    F::mul8(C, C, bad);                  /* 8Y^4 */
+    F::sub(t, D, r.x, bad);
+    F::mul(t, E, t, bad);
+    F::sub(r.y, t, C, bad);              /* Y3 = E(D - X3) - 8Y^4 */
     r.inf = false;
+}
+BCP_DEV void gej_double(gej &r, const gej &a) {
+    uint32_t unused = 0;
+    gej_double_t<fe_exact>(r, a, unused);
 }
 
 // a += (bx, by) with (bx, by) affine and finite.  8M + 3S.  If rzr != nullptr it receives the

@@ -34,7 +34,40 @@ static void words_to_be(uint8_t *b, const uint32_t *v) {
     }
 }
 
+#include <atomic>
+static std::atomic<long> hs_quick_redone{0}, hs_quick_mismatch{0};
 extern "C" {
+long hs_quick_counters(int which) { return which ? hs_quick_mismatch.load() : hs_quick_redone.load(); }
+// the quick (branch-free, carry-counting) field forms: op 0 mul, 1 add, 2 sub, 3 sqr(a), 4 neg(a), 9 8*a; returns `bad`,
+// out32 = the canonical value of whatever the form produced (only meaningful when bad == 0)
+uint32_t hs_fe_op_q(int op, const uint8_t *a32, const uint8_t *b32, uint8_t *out32) {
+    fe a, b, r;
+    uint32_t bad = 0;
+    words_from_be(a.v, a32);
+    words_from_be(b.v, b32);
+    switch (op) {
+        case 0: fe_mul_q(r, a, b, bad); break;
+        case 1: fe_add_q(r, a, b, bad); break;
+        case 2: fe_sub_q(r, a, b, bad); break;
+        case 3: fe_sqr_q(r, a, bad); break;
+        case 4: fe_neg_q(r, a, bad); break;
+        default: fe_mul8_q(r, a, bad); break;
+    }
+    fe_to_be(out32, r);
+    return bad;
+}
+// fe_reduce_wide_q on a chosen 512-bit input (big-endian)
+uint32_t hs_fe_reduce_q(const uint8_t *t64_be, uint8_t *out32) {
+    uint32_t w[16], bad = 0;
+    for (int i = 0; i < 16; i++) {
+        const uint8_t *q = t64_be + 60 - 4 * i;
+        w[i] = (uint32_t)q[0] << 24 | (uint32_t)q[1] << 16 | (uint32_t)q[2] << 8 | q[3];
+    }
+    fe r;
+    fe_reduce_wide_q(r, w, bad);
+    fe_to_be(out32, r);
+    return bad;
+}
 // op: 0 mul, 1 add, 2 sub, 3 sqr(a), 4 neg(a), 5 inv(a), 6 sqrt candidate(a); inputs are ANY 256-bit values
 // (weakly reduced representation), outputs canonical
 void hs_fe_op(int op, const uint8_t *a32, const uint8_t *b32, uint8_t *out32) {
@@ -194,7 +227,14 @@ void hs_ecdsa_verify_batch(const uint8_t *msg32, const uint8_t *pub65, const uin
             qtable tab;
             tab.base = smem.data();
             tab.stride = 1;
-            ok[i] = ecdsa_point_phase(&rec[i * BCP_REC_WORDS], pub65 + 65 * i, sig64 + 64 * i, tab, gcomb) ? 1 : 0;
+            // like k_ecdsa_point: the walk over the quick field forms, repeated with the exact ones when a fold was left
+            // unfinished; both walks must give the same verdict whenever the quick one is trusted
+            uint32_t bad = 0;
+            bool v = ecdsa_point_phase<qtable, false, fe_quick>(&rec[i * BCP_REC_WORDS], pub65 + 65 * i, sig64 + 64 * i, tab, gcomb, 0, nullptr, &bad);
+            const bool vx = ecdsa_point_phase<qtable, false, fe_exact>(&rec[i * BCP_REC_WORDS], pub65 + 65 * i, sig64 + 64 * i, tab, gcomb);
+            if (bad) { hs_quick_redone++; v = vx; }
+            else if (v != vx) hs_quick_mismatch++;
+            ok[i] = v ? 1 : 0;
         }
     };
     auto run = [&](size_t total, auto fn) {

@@ -174,3 +174,28 @@ def test_recover_and_tweak_add_against_reference_fixture_and_oracle(engine, orac
     # empty batch
     xy, ok = engine.ecdsa_recover_batch(np.zeros((0, 32), np.uint8), np.zeros((0, 64), np.uint8), np.zeros(0, np.uint8))
     assert len(ok) == 0
+
+
+def test_exact_walk_behind_the_quick_one(oracle, tmp_path):
+    """k_ecdsa_point walks a signature over branch-free field forms that count the practically-never carry instead of
+    finishing it, and walks it again over the exact forms when the count is not zero (about two signatures in a
+    million).  BCP_POINT_FORCE_REDO=3 sends every third signature through that second walk (the variable is read once
+    per process, hence the child process); the verdicts must not change."""
+    import subprocess
+    import sys
+
+    msg, pub, sig, kinds = synth.sigset(30000, nkeys=256, corrupt_pct=10)
+    want = oracle.ecdsa_verify_batch(msg, pub, sig, nthreads=NT)
+    np.savez(tmp_path / "in.npz", msg=msg, pub=pub, sig=sig)
+    child = (
+        "import sys, numpy as np\n"
+        "sys.path.insert(0, %r)\n"
+        "import bitcoincashplus_b200 as bcp\n"
+        "z = np.load(%r)\n"
+        "got = bcp.Engine(0).ecdsa_verify_batch(z['msg'], z['pub'], z['sig'])\n"
+        "np.save(%r, got)\n" % (os.path.dirname(os.path.dirname(os.path.abspath(__file__))), str(tmp_path / "in.npz"), str(tmp_path / "out.npy"))
+    )
+    env = dict(os.environ, BCP_POINT_FORCE_REDO="3")
+    subprocess.check_call([sys.executable, "-c", child], env=env)
+    got = np.load(tmp_path / "out.npy")
+    assert (got == want).all(), np.nonzero(got != want)[0][:20]

@@ -101,6 +101,51 @@ def test_short_cut_folds_on_crafted_operands(hs):
     assert hit >= 8
 
 
+def test_quick_forms_count_every_unfinished_fold(hs):
+    """The point kernel's hot loop uses branch-free field forms that COUNT the practically-never carry instead of
+    finishing it (fe.cuh "quick forms"); the kernel redoes a signature with the exact forms when the count is not zero.
+    So: whenever the count is zero the value must be right, and the crafted operands must raise it where the exact
+    forms take their slow path."""
+    import importlib.util
+
+    spec = importlib.util.spec_from_file_location("gen_fe_selftest", os.path.join(ROOT, "tools", "gen_fe_selftest.py"))
+    g = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(g)
+    hs.hs_fe_op_q.restype = C.c_uint32
+    hs.hs_fe_reduce_q.restype = C.c_uint32
+    rnd = random.Random(11)
+    vals = list(g.edge) + EDGE + [rnd.randrange(2**256) for _ in range(60)]
+    flagged = {0: 0, 1: 0, 2: 0, 3: 0, 4: 0, 9: 0}
+
+    def q(op, a, b):
+        out = (C.c_uint8 * 32)()
+        bad = hs.hs_fe_op_q(op, b32(a), b32(b), out)
+        return bad, int.from_bytes(bytes(out), "big")
+
+    for a in vals:
+        for b in vals:
+            for op, want in ((0, a * b % P), (1, (a + b) % P), (2, (a - b) % P)):
+                bad, got = q(op, a, b)
+                flagged[op] += bad != 0
+                assert bad or got == want, (op, hex(a), hex(b))
+        for op, want in ((3, a * a % P), (4, (-a) % P), (9, 8 * a % P)):
+            bad, got = q(op, a, 0)
+            flagged[op] += bad != 0
+            assert bad or got == want, (op, hex(a))
+    # additions and subtractions of the crafted operands do leave limb 1; -a borrows for a > p
+    assert flagged[1] > 0 and flagged[2] > 0 and flagged[4] > 0, flagged
+    hit = 0
+    for w in g.wide:
+        out = (C.c_uint8 * 32)()
+        bad = hs.hs_fe_reduce_q(C.cast(C.c_char_p(w.to_bytes(64, "big")), u8p), out)
+        S = (w % 2**256) + (w >> 256) * (2**32 + 977)
+        needs = ((S % 2**96) + (S >> 256) * (2**32 + 977)) >= 2**96
+        assert bool(bad) == needs, hex(w)
+        assert bad or int.from_bytes(bytes(out), "big") == w % P
+        hit += needs
+    assert hit >= 8
+
+
 def test_wide_products_schoolbook_and_karatsuba(hs):
     rnd = random.Random(17)
     vals = EDGE + [2**128 - 1, 2**128, 2**128 + 1, (2**128 - 1) << 128, 2**256 - 2**128] + [rnd.randrange(2**256) for _ in range(200)]
@@ -180,6 +225,10 @@ def test_verify_pipeline_matches_oracle(hs, gcomb, oracle):
     assert (got == want).all()
     m2, p2, s2 = synth.edge_cases()
     assert (_run(hs, gcomb, m2, p2, s2) == oracle.ecdsa_verify_batch(m2, p2, s2, 1)).all()
+    # every signature was walked twice, over the quick and over the exact field forms (as k_ecdsa_point does when the
+    # quick walk reports an unfinished fold): a trusted quick walk never disagreed with the exact one
+    hs.hs_quick_counters.restype = C.c_long
+    assert hs.hs_quick_counters(1) == 0
 
 
 def test_verify_pipeline_on_reference_golden(hs, gcomb):
