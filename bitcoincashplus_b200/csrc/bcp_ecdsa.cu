@@ -23,6 +23,13 @@
 /* a named barrier over the sync_n threads that walk the steps together: in the last, partly filled round of the persistent
  * kernel only the warps that hold signatures take part, the others have left */
 #define BCP_STEP_SYNC() do { if (sync_n != 0 && (BCP_STEP_SYNC_EVERY == 1 || (t % BCP_STEP_SYNC_EVERY) == 0)) asm volatile("bar.sync 1, %0;" :: "r"(sync_n) : "memory"); } while (0)
+#ifndef BCP_STEP_SYNC_EVERY_V2
+#define BCP_STEP_SYNC_EVERY_V2 4 /* iterations of ecdsa_point_phase_v2 between barriers (4 = two windows); B200, 1M: every iteration 51.91 M/s, 2nd 52.04, 4th 52.23 */
+#endif
+#define BCP_STEP_SYNC_V2() do { if (sync_n != 0 && (BCP_STEP_SYNC_EVERY_V2 == 1 || (t % BCP_STEP_SYNC_EVERY_V2) == 0)) asm volatile("bar.sync 1, %0;" :: "r"(sync_n) : "memory"); } while (0)
+#ifndef BCP_POINT_PHASE
+#define BCP_POINT_PHASE 2 /* 1: ecdsa_point_phase (one group operation per step, 51.23 M/s); 2: ecdsa_point_phase_v2 (addition + doublings per iteration, 52.23 M/s) */
+#endif
 #endif
 #include "ecdsa.cuh"
 #include <cstdlib>
@@ -117,8 +124,13 @@ __global__ void __launch_bounds__(BCP_POINT_THREADS, BCP_POINT_BLOCKS_PER_SM)
     // in a million have one).  Such a signature is walked again with the exact operations, alone: no barrier.
     // redo_every (test hook, BCP_POINT_FORCE_REDO): every redo_every-th signature is treated as if it had one.
     uint32_t bad = 0;
+#if BCP_POINT_PHASE == 2
+    bool v = ecdsa_point_phase_v2<qtable_packed, false, fe_quick>(rec + i * BCP_REC_WORDS, pub65 + 65 * i, sig64 + 64 * i, tab, gcomb,
+                                                                  (int)blockDim.x, nullptr, &bad);
+#else
     bool v = ecdsa_point_phase<qtable_packed, false, fe_quick>(rec + i * BCP_REC_WORDS, pub65 + 65 * i, sig64 + 64 * i, tab, gcomb,
                                                                (int)blockDim.x, nullptr, &bad);
+#endif
     if (redo_every != 0 && gi % redo_every == 0) bad = 1;
     if (__builtin_expect(bad != 0, 0))
         v = ecdsa_point_phase<qtable_packed, false, fe_exact>(rec + i * BCP_REC_WORDS, pub65 + 65 * i, sig64 + 64 * i, tab, gcomb, 0);
@@ -278,44 +290,54 @@ __global__ void k_fe_selftest(int *fail) {
         fe_normalize(r1);
         fe_normalize(na);
         for (int i = 0; i < 8; i++) bad |= r1.v[i] != na.v[i];
-        // the quick forms of the point kernel (carry counted, not finished): a count of zero promises the exact value
+        // the quick forms of the point kernel (carry counted, not finished): a count of zero promises the exact value.
+        // fail[2..7]: disagreements per form (add, sub, reduce, square, neg, times 8) for the error message
         uint32_t q = 0;
+        int d = 0;
         fe_add_q(r1, a, b, q);
         fe_add_full(r2, a, b);
         if (q) atomicAdd(fail + 1, 1);
-        else for (int i = 0; i < 8; i++) bad |= r1.v[i] != r2.v[i];
-        q = 0;
+        else for (int i = 0; i < 8; i++) d |= r1.v[i] != r2.v[i];
+        if (d) atomicAdd(fail + 2, 1);
+        bad |= d; d = 0; q = 0;
         fe_sub_q(r1, a, b, q);
         fe_sub_full(r2, a, b);
         if (q) atomicAdd(fail + 1, 1);
-        else for (int i = 0; i < 8; i++) bad |= r1.v[i] != r2.v[i];
-        q = 0;
+        else for (int i = 0; i < 8; i++) d |= r1.v[i] != r2.v[i];
+        if (d) atomicAdd(fail + 3, 1);
+        bad |= d; d = 0; q = 0;
+        mul_wide(w, a.v, b.v);
         fe_reduce_wide_q(r1, w, q);
         fe_reduce_wide_t<false>(r2, w);
         if (q) atomicAdd(fail + 1, 1);
-        else for (int i = 0; i < 8; i++) bad |= r1.v[i] != r2.v[i];
-        q = 0;
+        else for (int i = 0; i < 8; i++) d |= r1.v[i] != r2.v[i];
+        if (d) atomicAdd(fail + 4, 1);
+        bad |= d; d = 0; q = 0;
         sqr_wide(w, a.v);
         fe_reduce_wide_q(r1, w, q);
         fe_reduce_wide_t<false>(r2, w);
         m1 = fe_mul_f(a, a);
         fe_normalize(r2);
         fe_normalize(m1);
-        for (int i = 0; i < 8; i++) bad |= r2.v[i] != m1.v[i]; /* the squaring against the multiplication */
-        if (!q) { fe_normalize(r1); for (int i = 0; i < 8; i++) bad |= r1.v[i] != m1.v[i]; }
-        q = 0;
+        for (int i = 0; i < 8; i++) d |= r2.v[i] != m1.v[i]; /* the squaring against the multiplication */
+        if (!q) { fe_normalize(r1); for (int i = 0; i < 8; i++) d |= r1.v[i] != m1.v[i]; }
+        if (d) atomicAdd(fail + 5, 1);
+        bad |= d; d = 0; q = 0;
         fe_neg_q(r1, a, q);
         fe_neg(r2, a);
         fe_normalize(r1);
         fe_normalize(r2);
         if (q) atomicAdd(fail + 1, 1);
-        else for (int i = 0; i < 8; i++) bad |= r1.v[i] != r2.v[i];
-        q = 0;
+        else for (int i = 0; i < 8; i++) d |= r1.v[i] != r2.v[i];
+        if (d) atomicAdd(fail + 6, 1);
+        bad |= d; d = 0; q = 0;
         fe_mul8_q(r1, a, q);
         fe_dbl(r2, a); fe_dbl(r2, r2); fe_dbl(r2, r2);
         fe_normalize(r1);
         fe_normalize(r2);
-        if (!q) for (int i = 0; i < 8; i++) bad |= r1.v[i] != r2.v[i];
+        if (!q) for (int i = 0; i < 8; i++) d |= r1.v[i] != r2.v[i];
+        if (d) atomicAdd(fail + 7, 1);
+        bad |= d;
     }
     if (t < BCP_FE_ST_WIDE) {
         fe r1, r2;
@@ -332,18 +354,19 @@ __global__ void k_fe_selftest(int *fail) {
     if (bad) atomicAdd(fail, 1);
 }
 int bcp_fe_selftest(bcp_ctx *c) {
-    int *d_fail = nullptr, h_fail[2] = {-1, -1}; /* [0] disagreements; [1] how often a quick form counted a carry */
-    BCP_CUDA(cudaMalloc(&d_fail, 2 * sizeof(int)));
-    BCP_CUDA(cudaMemsetAsync(d_fail, 0, 2 * sizeof(int), c->stream));
+    int *d_fail = nullptr, h_fail[8] = {-1, -1, 0, 0, 0, 0, 0, 0}; /* [0] disagreements; [1] how often a quick form counted a carry; [2..7] per form */
+    BCP_CUDA(cudaMalloc(&d_fail, 8 * sizeof(int)));
+    BCP_CUDA(cudaMemsetAsync(d_fail, 0, 8 * sizeof(int), c->stream));
     k_fe_selftest<<<(BCP_FE_ST_EDGES * BCP_FE_ST_EDGES + 127) / 128, 128, 0, c->stream>>>(d_fail);
     cudaError_t e = cudaGetLastError();
-    if (e == cudaSuccess) e = cudaMemcpyAsync(h_fail, d_fail, 2 * sizeof(int), cudaMemcpyDeviceToHost, c->stream);
+    if (e == cudaSuccess) e = cudaMemcpyAsync(h_fail, d_fail, 8 * sizeof(int), cudaMemcpyDeviceToHost, c->stream);
     if (e == cudaSuccess) e = cudaStreamSynchronize(c->stream);
     cudaFree(d_fail);
     if (e != cudaSuccess) return bcp_cuda_fail(e, "field self-test");
     if (h_fail[0] != 0) {
         bcp_set_error("field arithmetic self-test failed on device %d: %d operand pairs disagree between the short-cut or quick forms "
-                      "and the full carry chains", c->device, h_fail[0]);
+                      "and the full carry chains (quick add %d, sub %d, reduce %d, square %d, neg %d, times-8 %d)", c->device, h_fail[0],
+                      h_fail[2], h_fail[3], h_fail[4], h_fail[5], h_fail[6], h_fail[7]);
         return BCP_ERR_CUDA;
     }
     // the crafted operands exist to leave limb 1 / limb 2: the quick forms must have counted carries on many of them, and

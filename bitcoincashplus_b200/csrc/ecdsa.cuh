@@ -25,6 +25,9 @@
 #ifndef BCP_STEP_SYNC
 #define BCP_STEP_SYNC() ((void)0)
 #endif
+#ifndef BCP_STEP_SYNC_V2
+#define BCP_STEP_SYNC_V2() ((void)0)
+#endif
 
 #define BCP_ECDSA_NORMALIZE_S 1u /* CPubKey::Verify semantics: s := min(s, n-s) instead of rejecting high s */
 
@@ -355,6 +358,180 @@ BCP_DEV bool ecdsa_point_phase(const uint32_t *rec, const uint8_t *pub65, const 
         if (fe_equal(t1, acc.x)) ok = true;
         if (ok || !second_chance) break;
         addn_cc<8>(fr.v, r.v, n); /* r + n < p: no overflow */
+    }
+    return ok;
+}
+
+// The same walk with the steps bracketed differently: one iteration = at most one mixed addition FOLLOWED by `nd`
+// doublings (an inner loop around the single doubling instance).  The order of the group operations is the same as in
+// ecdsa_point_phase (window w: four doublings, add digit(k1)*Q, add digit(k2)*lambda*Q); what changes is the code shape:
+// no "is this step a doubling" flag merges with the addition's values, the doublings run with only the accumulator
+// live, and the P + P case of an addition becomes one more doubling of the same iteration.
+//   iteration 0                 table build: no addition, one doubling (2Q)
+//   iterations 1..6             table build: add Q
+//   then, for w = 33..0         A: add digit(k1,w)*Q;  B: add digit(k2,w)*lambda*Q, then (w > 0) the four doublings of window w-1
+//   one iteration               Z *= Z_8 (leave the isomorphic curve)
+//   last BCP_GCOMB_WINDOWS      add the comb entry of u1
+template <class Table, bool WANT_POINT = false, class F = fe_exact>
+BCP_DEV bool ecdsa_point_phase_v2(const uint32_t *rec, const uint8_t *pub65, const uint8_t *sig64, Table tab,
+                                  const uint32_t *gcomb, const int sync_n = 0, gej *out = nullptr, uint32_t *bad_out = nullptr) {
+    (void)sync_n;
+    uint32_t bad = 0;
+    const uint32_t fl = rec[18];
+    gej acc;
+    bool valid = (fl & BCP_REC_VALID) != 0;
+    valid = pubkey_parse(acc.x, acc.y, pub65) && valid;
+    if (!valid) {
+        BCP_UNROLL
+        for (int i = 0; i < 8; i++) { acc.x.v[i] = FE_GX[i]; acc.y.v[i] = FE_GY[i]; }
+    }
+    fe_set_u32(acc.z, 1);
+    acc.inf = false;
+    tab.store(0, acc.x, acc.y);
+    const bool n1 = fl & BCP_REC_NEG1, n2 = fl & BCP_REC_NEG2;
+    fe zr[BCP_QTAB_ENTRIES]; /* zr[k] = Z_{k+1} / Z_k */
+    fe zglob;
+    fe_set_u32(zglob, 1);
+    const int T_TAB = BCP_QTAB_ENTRIES - 1, T_MAIN = 34 * 2, T_ALL = T_TAB + T_MAIN + 1 + BCP_GCOMB_WINDOWS;
+#if BCP_PTX
+#pragma unroll 1
+#endif
+    for (int t = 0; t < T_ALL; t++) {
+        BCP_STEP_SYNC_V2();
+        bool have = false;
+        int nd = 0;
+        fe x, y, h;
+        if (t < T_TAB) {
+            if (t == 0) nd = 1;
+            else { tab.load(0, x, y); have = true; }
+        } else if (t < T_TAB + T_MAIN) {
+            const int u = t - T_TAB;
+            if (u == 0) {
+                zglob = acc.z;
+                fe zs = zr[BCP_QTAB_ENTRIES - 1], beta;
+                BCP_UNROLL
+                for (int i = 0; i < 8; i++) beta.v[i] = FE_BETA[i];
+#if BCP_PTX
+#pragma unroll 1
+#endif
+                for (int k = BCP_QTAB_ENTRIES - 1; k >= 0; k--) {
+                    fe ex, ey, zs2, zs3;
+                    tab.load(k, ex, ey);
+                    if (k < BCP_QTAB_ENTRIES - 1) {
+                        F::sqr(zs2, zs, bad);
+                        F::mul(zs3, zs2, zs, bad);
+                        F::mul(ex, ex, zs2, bad);
+                        F::mul(ey, ey, zs3, bad);
+                        tab.store(k, ex, ey);
+                        if (k > 0) F::mul(zs, zs, zr[k], bad);
+                    }
+                    F::mul(ex, ex, beta, bad);
+                    tab.store_xb(k, ex);
+                }
+                acc.inf = true;
+            }
+            const int w = 33 - (u >> 1);
+            const bool second = (u & 1) != 0;
+            if (second && w > 0) nd = 4;
+            const uint32_t word = rec[(second ? 13 : 8) + (w >> 3)];
+            int d = (int)((word >> ((w & 7) * 4)) & 15u);
+            if (w <= 32) d -= 8;
+            if (d != 0) {
+                const bool neg = (d < 0) != (second ? n2 : n1);
+                if (second) tab.load_b((d < 0 ? -d : d) - 1, x, y);
+                else tab.load((d < 0 ? -d : d) - 1, x, y);
+                if (neg) F::neg(y, y, bad);
+                have = true;
+            }
+        } else if (t == T_TAB + T_MAIN) {
+            if (!acc.inf) F::mul(acc.z, acc.z, zglob, bad);
+            continue;
+        } else {
+            const int j = t - (T_TAB + T_MAIN + 1);
+            const int bit = j * BCP_GCOMB_BITS;
+            const int limb = bit >> 5, sh = bit & 31;
+            const uint32_t lo = rec[limb];
+            const uint32_t hi = (limb + 1 < 8) ? rec[limb + 1] : 0u;
+            const uint32_t d = (sh == 0 ? lo : ((lo >> sh) | (hi << (32 - sh)))) & (BCP_GCOMB_ENTRIES - 1);
+            if (d != 0) {
+                const uint32_t *e = gcomb + ((size_t)j * BCP_GCOMB_ENTRIES + d) * 16;
+#if BCP_PTX
+                const uint4 *e4 = reinterpret_cast<const uint4 *>(e);
+                uint4 qa = __ldg(e4), qb = __ldg(e4 + 1), qc = __ldg(e4 + 2), qd = __ldg(e4 + 3);
+                x.v[0] = qa.x; x.v[1] = qa.y; x.v[2] = qa.z; x.v[3] = qa.w; x.v[4] = qb.x; x.v[5] = qb.y; x.v[6] = qb.z; x.v[7] = qb.w;
+                y.v[0] = qc.x; y.v[1] = qc.y; y.v[2] = qc.z; y.v[3] = qc.w; y.v[4] = qd.x; y.v[5] = qd.y; y.v[6] = qd.z; y.v[7] = qd.w;
+#else
+                for (int i = 0; i < 8; i++) { x.v[i] = e[i]; y.v[i] = e[8 + i]; }
+#endif
+                have = true;
+            }
+        }
+        if (have) {
+            if (acc.inf) { /* first addition into infinity copies the operand (group_impl.h:417-421) */
+                acc.x = x; acc.y = y;
+                fe_set_u32(acc.z, 1);
+                acc.inf = false;
+            } else {
+                // mixed addition acc += (x, y): 8M + 3S, with the degenerate branches of gej_add_ge_var (:438-448)
+                fe z2, u2, s2, rr, h2, h3, v, tt;
+                F::sqr(z2, acc.z, bad);
+                F::mul(u2, x, z2, bad);
+                F::mul(tt, acc.z, z2, bad);
+                F::mul(s2, y, tt, bad);
+                F::sub(h, u2, acc.x, bad);
+                F::sub(rr, s2, acc.y, bad);
+                if (fe_is_zero(h)) {
+                    if (fe_is_zero(rr)) nd += 1;              /* P + P: one more doubling of this iteration      */
+                    else acc.inf = true;                      /* P + (-P)                                       */
+                } else {
+                    F::sqr(h2, h, bad);
+                    F::mul(h3, h2, h, bad);
+                    F::mul(v, acc.x, h2, bad);
+                    F::mul(acc.z, acc.z, h, bad);
+                    F::sqr(tt, rr, bad);
+                    F::sub(tt, tt, h3, bad); F::sub(tt, tt, v, bad); F::sub(acc.x, tt, v, bad);
+                    F::sub(tt, v, acc.x, bad);
+                    F::mul(tt, tt, rr, bad);
+                    F::mul(h3, h3, acc.y, bad);
+                    F::sub(acc.y, tt, h3, bad);
+                }
+            }
+        }
+#if BCP_PTX
+#pragma unroll 1
+#endif
+        for (int k = 0; k < nd; k++)
+            if (!acc.inf) gej_double_t<F>(acc, acc, bad);
+        if (t < T_TAB) {
+            tab.store(t + 1, acc.x, acc.y);
+            zr[t + 1] = (t == 0) ? acc.z : h;
+        }
+    }
+    if (bad_out) *bad_out = bad;
+    if (WANT_POINT) {
+        *out = acc;
+        return valid && !acc.inf;
+    }
+    if (acc.inf || !valid) return false; /* ecdsa_impl.h:220 */
+    scalar r;
+    sc_set_b32(r, sig64);
+    fe z2, t1, fr;
+    fe_sqr(z2, acc.z);
+    BCP_UNROLL
+    for (int i = 0; i < 8; i++) fr.v[i] = r.v[i];
+    uint32_t pmn[8], n[8];
+    BCP_UNROLL
+    for (int i = 0; i < 8; i++) { pmn[i] = SC_P_MINUS_N[i]; n[i] = SC_N[i]; }
+    const bool second_chance = !u256_ge(r.v, pmn);
+    bool ok = false;
+#if BCP_PTX
+#pragma unroll 1
+#endif
+    for (int pass = 0; pass < 2; pass++) {
+        fe_mul(t1, fr, z2);
+        if (fe_equal(t1, acc.x)) ok = true;
+        if (ok || !second_chance) break;
+        addn_cc<8>(fr.v, r.v, n);
     }
     return ok;
 }

@@ -764,12 +764,13 @@ BCP_DEV void fe_add_q(fe &r, const fe &a, const fe &b, uint32_t &bad) {
 BCP_DEV void fe_sub_q(fe &r, const fe &a, const fe &b, uint32_t &bad) {
 #if BCP_PTX
     uint32_t r0, r1, r2, r3, r4, r5, r6, r7;
-    asm("{\n\t.reg .u32 c, k;\n\t.reg .pred p;\n\t"
+    asm("{\n\t.reg .u32 c, k;\n\t"
         "sub.cc.u32 %0, %9, %17;\n\tsubc.cc.u32 %1, %10, %18;\n\tsubc.cc.u32 %2, %11, %19;\n\tsubc.cc.u32 %3, %12, %20;\n\t"
         "subc.cc.u32 %4, %13, %21;\n\tsubc.cc.u32 %5, %14, %22;\n\tsubc.cc.u32 %6, %15, %23;\n\tsubc.cc.u32 %7, %16, %24;\n\t"
-        "addc.u32 c, 0, 0;\n\t"                                  /* CC.CF after a subtraction is the borrow: 0 or 1 */
-        "setp.ne.u32 p, c, 0;\n\tselp.u32 k, 977, 0, p;\n\t"   /* - borrow * (2^32 + 977) */
-        "sub.cc.u32 %0, %0, k;\n\tsubc.cc.u32 %1, %1, c;\n\taddc.u32 %8, %8, 0;\n\t}" /* counts the borrow out of limb 1 */
+        "subc.u32 c, 0, 0;\n\t"                                  /* 0 or 0xFFFFFFFF (only subc reads a borrow) */
+        "and.b32 k, c, 977;\n\tshr.u32 c, c, 31;\n\t"          /* - borrow * (2^32 + 977) */
+        "sub.cc.u32 %0, %0, k;\n\tsubc.cc.u32 %1, %1, c;\n\tsubc.u32 c, 0, 0;\n\t"
+        "sub.u32 %8, %8, c;\n\t}"                                /* c is 0 or -1: counts the borrow out of limb 1 */
         : "=&r"(r0), "=&r"(r1), "=&r"(r2), "=&r"(r3), "=&r"(r4), "=&r"(r5), "=&r"(r6), "=&r"(r7), "+r"(bad)
         : "r"(a.v[0]), "r"(a.v[1]), "r"(a.v[2]), "r"(a.v[3]), "r"(a.v[4]), "r"(a.v[5]), "r"(a.v[6]), "r"(a.v[7]), "r"(b.v[0]),
           "r"(b.v[1]), "r"(b.v[2]), "r"(b.v[3]), "r"(b.v[4]), "r"(b.v[5]), "r"(b.v[6]), "r"(b.v[7]));

@@ -234,6 +234,11 @@ void hs_ecdsa_verify_batch(const uint8_t *msg32, const uint8_t *pub65, const uin
             const bool vx = ecdsa_point_phase<qtable, false, fe_exact>(&rec[i * BCP_REC_WORDS], pub65 + 65 * i, sig64 + 64 * i, tab, gcomb);
             if (bad) { hs_quick_redone++; v = vx; }
             else if (v != vx) hs_quick_mismatch++;
+            // the other bracketing of the same walk (ecdsa_point_phase_v2), over both sets of field forms
+            uint32_t bad2 = 0;
+            const bool v2q = ecdsa_point_phase_v2<qtable, false, fe_quick>(&rec[i * BCP_REC_WORDS], pub65 + 65 * i, sig64 + 64 * i, tab, gcomb, 0, nullptr, &bad2);
+            const bool v2x = ecdsa_point_phase_v2<qtable, false, fe_exact>(&rec[i * BCP_REC_WORDS], pub65 + 65 * i, sig64 + 64 * i, tab, gcomb);
+            if (v2x != vx || (!bad2 && v2q != vx)) hs_quick_mismatch++;
             ok[i] = v ? 1 : 0;
         }
     };

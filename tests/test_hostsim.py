@@ -275,6 +275,8 @@ def test_group_law_degenerate_branches(hs, gcomb, oracle):
     want = oracle.ecdsa_verify_batch(msg, pub, sig, 1)
     assert (got == want).all(), np.nonzero(got != want)[0]
     assert want.any() and not want.all()
+    hs.hs_quick_counters.restype = C.c_long
+    assert hs.hs_quick_counters(1) == 0  # both bracketings of the walk, over the quick and the exact field forms, agreed
 
 
 def test_hash_device_functions(hs, oracle):
