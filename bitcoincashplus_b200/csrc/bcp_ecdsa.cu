@@ -95,7 +95,7 @@ __global__ void __launch_bounds__(128) k_ecdsa_prep(const uint8_t *__restrict__ 
         cnt++;
     }
     scalar inv;
-    sc_inverse(inv, acc);
+    sc_inverse_divsteps(inv, acc);
 #pragma unroll 1
     for (int j = cnt - 1; j >= 0; j--) {
         size_t i = t + (size_t)j * T;
@@ -233,7 +233,7 @@ __global__ void __launch_bounds__(128) k_ec_lincomb(const uint8_t *__restrict__ 
             BCP_UNROLL
             for (int k = 0; k < 8; k++) r.v[k] = (k == 0);
         }
-        sc_inverse(sinv, r);
+        sc_inverse_divsteps(sinv, r);
         g.r = s;            /* u2 = s / r  */
         sc_negate(g.m, m);  /* u1 = -m / r */
     } else {
@@ -351,22 +351,39 @@ __global__ void k_fe_selftest(int *fail) {
         if (q) atomicAdd(fail + 1, 1);
         else for (int i = 0; i < 8; i++) bad |= r1.v[i] != r2.v[i];
     }
+    if (t < BCP_FE_ST_EDGES * BCP_FE_ST_EDGES) {
+        // the prep kernel's inversion by division steps against a^(n-2), and a * a^-1 == 1, on products of the crafted values
+        scalar x, y, i1, i2, one;
+        for (int i = 0; i < 8; i++) { x.v[i] = FE_ST_EDGE[t / BCP_FE_ST_EDGES][i] ^ (0x9e3779b9u * (uint32_t)(t + 1)); y.v[i] = FE_ST_EDGE[t % BCP_FE_ST_EDGES][i]; }
+        x.v[7] &= 0x7fffffffu; y.v[7] &= 0x7fffffffu; /* below n */
+        sc_mul(x, x, y);
+        if (t == 0) for (int i = 0; i < 8; i++) x.v[i] = (i == 0);
+        if (!sc_is_zero(x)) {
+            sc_inverse_divsteps(i1, x);
+            sc_inverse(i2, x);
+            sc_mul(one, i1, x);
+            int d = 0;
+            for (int i = 0; i < 8; i++) d |= (i1.v[i] != i2.v[i]) | (one.v[i] != (i == 0 ? 1u : 0u));
+            if (d) atomicAdd(fail + 8, 1);
+            bad |= d;
+        }
+    }
     if (bad) atomicAdd(fail, 1);
 }
 int bcp_fe_selftest(bcp_ctx *c) {
-    int *d_fail = nullptr, h_fail[8] = {-1, -1, 0, 0, 0, 0, 0, 0}; /* [0] disagreements; [1] how often a quick form counted a carry; [2..7] per form */
-    BCP_CUDA(cudaMalloc(&d_fail, 8 * sizeof(int)));
-    BCP_CUDA(cudaMemsetAsync(d_fail, 0, 8 * sizeof(int), c->stream));
+    int *d_fail = nullptr, h_fail[9] = {-1, -1, 0, 0, 0, 0, 0, 0, 0}; /* [0] disagreements; [1] how often a quick form counted a carry; [2..8] per form */
+    BCP_CUDA(cudaMalloc(&d_fail, 9 * sizeof(int)));
+    BCP_CUDA(cudaMemsetAsync(d_fail, 0, 9 * sizeof(int), c->stream));
     k_fe_selftest<<<(BCP_FE_ST_EDGES * BCP_FE_ST_EDGES + 127) / 128, 128, 0, c->stream>>>(d_fail);
     cudaError_t e = cudaGetLastError();
-    if (e == cudaSuccess) e = cudaMemcpyAsync(h_fail, d_fail, 8 * sizeof(int), cudaMemcpyDeviceToHost, c->stream);
+    if (e == cudaSuccess) e = cudaMemcpyAsync(h_fail, d_fail, 9 * sizeof(int), cudaMemcpyDeviceToHost, c->stream);
     if (e == cudaSuccess) e = cudaStreamSynchronize(c->stream);
     cudaFree(d_fail);
     if (e != cudaSuccess) return bcp_cuda_fail(e, "field self-test");
     if (h_fail[0] != 0) {
         bcp_set_error("field arithmetic self-test failed on device %d: %d operand pairs disagree between the short-cut or quick forms "
-                      "and the full carry chains (quick add %d, sub %d, reduce %d, square %d, neg %d, times-8 %d)", c->device, h_fail[0],
-                      h_fail[2], h_fail[3], h_fail[4], h_fail[5], h_fail[6], h_fail[7]);
+                      "and the full carry chains (quick add %d, sub %d, reduce %d, square %d, neg %d, times-8 %d; scalar inversion %d)", c->device,
+                      h_fail[0], h_fail[2], h_fail[3], h_fail[4], h_fail[5], h_fail[6], h_fail[7], h_fail[8]);
         return BCP_ERR_CUDA;
     }
     // the crafted operands exist to leave limb 1 / limb 2: the quick forms must have counted carries on many of them, and
@@ -417,13 +434,14 @@ int bcp_ecdsa_launch(bcp_ctx *c, const uint8_t *d_msg, const uint8_t *d_pub, con
     const int rounds_mode = point_rounds_mode();
     for (size_t off = 0; off < n; off += BCP_SLICE) {
         const size_t m = n - off < BCP_SLICE ? n - off : BCP_SLICE;
-        // signatures per prep thread: one 334-multiplication inversion is shared by K signatures, but a thread's work is
-        // serial, so small batches trade total work for parallelism (measured on B200 with tools/prep_sweep.py:
-        // 41,650 signatures K=4 1.96 ms vs K=32 2.25 ms; 227k K=16 best; 1M K=32 best)
+        // signatures per prep thread: one inversion is shared by K signatures (Montgomery's trick), but a thread's work is
+        // serial.  With the division-step inversion (about a tenth of a^(n-2)) small K wins everywhere; measured on B200
+        // (prep + point, tools/r2_run11.sh): 1M signatures K=2 18.97 ms, 4 18.82, 8 18.76, 16 18.77, 32 18.85; 333k: 6.40,
+        // 6.37, 6.38, 6.45, 6.53; one block's 41,650: 1.187, 1.188, 1.236, 1.322, 1.486.  (With a^(n-2) it was K=32 at 1M: 19.5.)
         static const int forced = getenv("BCP_PREP_K") ? atoi(getenv("BCP_PREP_K")) : 0;
         // c->prep_throughput: the caller keeps several batches in flight on this GPU (the chain connector's check lanes), so
-        // what counts is the total work — one inversion per 16 signatures instead of per 4 is 5 % less of it per block
-        const int K = forced ? forced : (m >= 600000 ? 32 : (m >= 150000 || (c->prep_throughput && m >= 4096)) ? 16 : m >= 100000 ? 8 : 4);
+        // what counts is the total work, not one batch's latency
+        const int K = forced ? forced : (m >= 100000 || (c->prep_throughput && m >= 4096)) ? 8 : 4;
         size_t prep_threads = (m + K - 1) / K;
         unsigned prep_blocks = (unsigned)((prep_threads + 127) / 128);
         if (K >= 32) k_ecdsa_prep<32><<<prep_blocks, 128, 0, st>>>(d_msg + 32 * off, d_sig + 64 * off, m, flags, d_rec);

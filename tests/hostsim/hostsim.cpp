@@ -126,6 +126,7 @@ void hs_sc_op(int op, const uint8_t *a32, const uint8_t *b32, uint8_t *out32) {
         case 1: sc_add(r, a, b); break;
         case 2: sc_sub(r, a, b); break;
         case 3: sc_inverse(r, a); break;
+        case 5: sc_inverse_divsteps(r, a); break;
         default: sc_negate(r, a); break;
     }
     words_to_be(out32, r.v);
@@ -211,7 +212,7 @@ void hs_ecdsa_verify_batch(const uint8_t *msg32, const uint8_t *pub65, const uin
                 sc_mul(acc, acc, g[j].s);
                 cnt++;
             }
-            sc_inverse(inv, acc);
+            sc_inverse_divsteps(inv, acc); /* what k_ecdsa_prep calls */
             for (int j = cnt - 1; j >= 0; j--) {
                 size_t i = t + (size_t)j * T;
                 scalar sinv;

@@ -170,6 +170,13 @@ def test_scalar_ops_and_reduction(hs):
         assert op3(hs.hs_sc_op, 4, a, 0) == (-a) % N
         if a:
             assert op3(hs.hs_sc_op, 3, a, 0) == pow(a, -1, N)
+            assert op3(hs.hs_sc_op, 5, a, 0) == pow(a, -1, N)  # the division-step inversion the prep kernel uses
+    # the division-step inversion on many more values, and on the shapes that stress its 30-bit limbs and its sign handling
+    more = [2**k for k in range(0, 256, 7)] + [N - 2**k for k in range(0, 256, 11)] + [2**30 - 1, 2**30, 2**60 - 1, 2**240, 2**255, (N + 1) // 2,
+            (N - 1) // 3, 0x3FFFFFFF << 30, int("3fffffff" * 8, 16) % N] + [rnd.randrange(1, N) for _ in range(3000)]
+    for a in more:
+        assert op3(hs.hs_sc_op, 5, a, 0) == pow(a, -1, N), hex(a)
+    assert op3(hs.hs_sc_op, 5, 0, 0) == 0  # like the reference's scalar_inverse
     for t in [0, 1, 2**512 - 1, 2**256, 2**256 - 1, N * N, (N - 1) ** 2, 2**511] + [rnd.randrange(2**512) for _ in range(300)]:
         out = (C.c_uint8 * 32)()
         hs.hs_sc_reduce512(C.cast(C.c_char_p(t.to_bytes(64, "big")), u8p), out)
