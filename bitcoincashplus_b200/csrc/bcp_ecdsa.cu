@@ -173,8 +173,12 @@ __global__ void __launch_bounds__(BCP_POINT_THREADS, BCP_POINT_BLOCKS_PER_SM)
             if (threadIdx.x >= width) return; /* whole warps without a signature leave (last pass only) */
             i = threadIdx.x < left ? base + threadIdx.x : n - 1u; /* lanes past the end shadow the last signature (barriers) */
         }
-        const bool v = ecdsa_point_phase(rec + (size_t)i * BCP_REC_WORDS, pub65 + (size_t)65 * i, sig64 + (size_t)64 * i, tab,
-                                         gcomb, (int)width);
+        uint32_t bad = 0; /* as in k_ecdsa_point: the quick walk, and the exact one behind it when a fold was left unfinished */
+        bool v = ecdsa_point_phase_v2<qtable_packed, false, fe_quick>(rec + (size_t)i * BCP_REC_WORDS, pub65 + (size_t)65 * i,
+                                                                      sig64 + (size_t)64 * i, tab, gcomb, (int)width, nullptr, &bad);
+        if (__builtin_expect(bad != 0, 0))
+            v = ecdsa_point_phase<qtable_packed, false, fe_exact>(rec + (size_t)i * BCP_REC_WORDS, pub65 + (size_t)65 * i,
+                                                                  sig64 + (size_t)64 * i, tab, gcomb, 0);
         {
             const uint32_t chunks = (n / (gridDim.x * blockDim.x)) * gridDim.x;
             const bool last = s_chunk >= chunks;
