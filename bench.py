@@ -429,11 +429,11 @@ def chain_bench(args, devices, impl="device"):
     import synth
     from oracle import pyoracle as po
 
-    warm = 16 if impl == "device" else 1
+    warm = 32 if impl == "device" else 1  # at least two blocks per check thread at 8 GPUs: every lane's scratch exists before the clock starts
     nblk = args.chain_blocks if impl == "device" else min(args.chain_blocks, 20)
     ntx = args.block_txs
     G_ = len(devices)
-    allb, seeds, gen_s = _chain_blocks(args.chain_blocks + 16 + 8, ntx)
+    allb, seeds, gen_s = _chain_blocks(args.chain_blocks + 32 + 8, ntx)
     blocks = allb[: warm + nblk]
     extra = allb[warm + nblk: warm + nblk + G_]  # the next blocks of the chain: the last of them is also connected damaged
     L = C.CDLL(os.path.join(ROOT, "bitcoincashplus_b200", "libbcp_chain.so"))
@@ -446,7 +446,7 @@ def chain_bench(args, devices, impl="device"):
         L.bcp_dchain_new.argtypes = [C.POINTER(C.c_int), C.c_int, C.c_uint32, C.c_uint, C.c_uint, C.c_uint, C.c_int, C.c_int, C.c_char_p, C.c_size_t]
         lanes = args.chain_lanes or (3 if len(devices) == 1 else 2)
         scan_threads = max(2, min(8, effective_cpus() // 4))
-        h = L.bcp_dchain_new(devs, len(devices), synth.POSTFORK_FLAGS, 48, 5, 22, lanes, scan_threads, err, 256)
+        h = L.bcp_dchain_new(devs, len(devices), synth.POSTFORK_FLAGS, 48, 5, 23, lanes, scan_threads, err, 256)  # 2^23 slots of 128 B = 1 GB of HBM
         if h:
             L.bcp_dchain_reserve.argtypes = [C.c_void_p, C.c_size_t]
             L.bcp_dchain_reserve(h, max(len(b) for b in blocks) + 4096)  # every pipeline slot's pinned buffers, before the clock starts

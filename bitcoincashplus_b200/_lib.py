@@ -50,6 +50,7 @@ SIGNATURES = {
     "bcp_gpu_utxo_fetch_spent": (C.c_int, [vp, C.c_uint32, vp, sz, vp, vp]),
     "bcp_gpu_utxo_confirm": (C.c_int, [vp, C.c_uint32]),
     "bcp_gpu_utxo_rollback": (C.c_int, [vp, C.c_uint32]),
+    "bcp_gpu_utxo_reserve": (C.c_int, [vp, C.c_size_t]),
     "bcp_block_index": (C.c_long, [vp, sz, C.c_int, vp, sz]),
     "bcp_gpu_sha256d_txids_merkle": (C.c_int, [C.c_int, vp, sz, vp, sz, vp, vp, C.POINTER(C.c_int)]),
     "bcp_gpu_merkle_root": (C.c_int, [C.c_int, vp, sz, vp, C.POINTER(C.c_int)]),

@@ -34,7 +34,7 @@
 #define UTXO_SPENT 3u
 #define UTXO_NONE 0xFFFFFFFFu
 #define UTXO_INLINE 64u
-#define UTXO_RING 16 /* blocks that may be applied and not yet confirmed or rolled back */
+#define UTXO_RING 32 /* blocks that may be applied and not yet confirmed or rolled back */
 
 // status words of one applied block (device -> host); [6] = spent scripts that did not fit the script buffer
 enum { ST_MISSING = 0, ST_FIRST_MISSING = 1, ST_DUPLICATE = 2, ST_SPK_BYTES = 3, ST_TABLE_FULL = 4, ST_ARENA_FULL = 5, ST_SPK_OVERFLOW = 6, ST_WORDS = 8 };
@@ -495,6 +495,30 @@ BCP_API long long bcp_gpu_utxo_size(bcp_utxo *u) {
     if (cudaMemcpyAsync(&v, u->T.live, 8, cudaMemcpyDeviceToHost, u->st) != cudaSuccess) return -1;
     if (cudaStreamSynchronize(u->st) != cudaSuccess) return -1;
     return v;
+}
+
+// Allocate every pending-block area for blocks of up to max_block_bytes now (counts bounded as for P2PKH-shaped
+// transactions: the layout below with ntx <= len/60, nin <= len/41, nout <= len/34), so that no block of a run meets
+// cudaMalloc — a device-wide synchronisation — on its way through bcp_gpu_utxo_apply_block.  Optional: areas still grow on demand.
+BCP_API int bcp_gpu_utxo_reserve(bcp_utxo *u, size_t max_block_bytes) {
+    if (!u) return BCP_ERR_INVALID;
+    const size_t len = max_block_bytes, ntx = len / 60 + 2, nin = len / 41 + 2, nout = len / 34 + 2;
+    size_t o = up256(len + 16) + up256((ntx + 1) * 4) + 2 * up256(nin * 4 + 4) + 3 * up256(nout * 4 + 4);
+    o += up256(nin * 8 + 8) + up256((nin + 1) * 4) + up256(nin * 80 + 65536 + 16);
+    o += up256(ntx * 32 + 32) + up256(bcp_merkle_tmp_words(ntx) * 4) + 256;
+    o += 2 * up256(nin * 4 + 4) + up256(nout * 4 + 4);
+    std::lock_guard<std::mutex> lk(u->mu);
+    BCP_CUDA(cudaSetDevice(u->device));
+    for (int k = 0; k < UTXO_RING; k++) {
+        ring_slot &r = u->ring[k];
+        if (r.used || r.cap >= o) continue;
+        if (r.d) BCP_CUDA(cudaFree(r.d));
+        r.d = nullptr;
+        r.cap = 0;
+        BCP_CUDA(cudaMalloc(&r.d, o));
+        r.cap = o;
+    }
+    return BCP_OK;
 }
 
 BCP_API int bcp_gpu_utxo_apply_block(bcp_utxo *u, uint32_t seq, const uint8_t *blk, size_t len, const uint32_t *tx_off, size_t ntx,

@@ -262,7 +262,7 @@ BCP_API int bcp_gpu_measure_int_peak(int device, int which, double *ops_per_seco
  *      is a few kernels per block on one stream (bitcoincashplus_b200/csrc/bcp_utxo.cu).  Blocks are applied in call
  *      order; block b+1 sees the table as block b left it, whether or not b's script checks have finished, and a block
  *      whose checks fail is undone with bcp_gpu_utxo_rollback (newest first).  Sequence numbers are the caller's, start at
- *      1 and must increase; at most 16 blocks may be applied and neither confirmed nor rolled back.
+ *      1 and must increase; at most 32 blocks may be applied and neither confirmed nor rolled back.
  *   bcp_gpu_utxo_create     2^log2_slots slots of 128 bytes (keep the table under half full); arena_bytes for scriptPubKeys
  *                           longer than 64 bytes (never freed).  NULL on failure.
  *   bcp_gpu_utxo_add_coins  seeds coins: outpoints36[i] = txid || vout (LE), spk / spk_off / amounts as elsewhere
@@ -288,6 +288,9 @@ BCP_API void bcp_gpu_utxo_destroy(bcp_utxo *u);
 BCP_API int bcp_gpu_utxo_add_coins(bcp_utxo *u, const uint8_t *outpoints36, const uint8_t *spk, const uint32_t *spk_off,
                                    const int64_t *amounts, size_t n);
 BCP_API long long bcp_gpu_utxo_size(bcp_utxo *u);
+/* Optional: allocate every pending-block area for blocks of up to max_block_bytes now, so that no block of a run meets a
+ * device allocation (a device-wide synchronisation) inside bcp_gpu_utxo_apply_block.  No reference counterpart. */
+BCP_API int bcp_gpu_utxo_reserve(bcp_utxo *u, size_t max_block_bytes);
 BCP_API int bcp_gpu_utxo_apply_block(bcp_utxo *u, uint32_t seq, const uint8_t *blk, size_t len, const uint32_t *tx_off, size_t ntx,
                                      const uint32_t *in_off, const uint32_t *in_tx, size_t nin, const uint32_t *out_off,
                                      const uint32_t *out_tx, const uint32_t *out_n, size_t nout, uint8_t *txids, uint8_t *root32,

@@ -73,7 +73,8 @@ public:
             for (size_t g = 0; g < devs.size(); g++)
                 if (!(devs.size() > 1 && g == 0 && l == lanes_ - 1 && lanes_ > 1)) workers.push_back(BCP_DEVICE_LANE(devs[g] & 0xFF, l));
         const size_t W = workers.size();
-        inflightMax = W + 3 < 14 ? W + 3 : 14; /* the table keeps undo records of at most 16 pending blocks */
+        inflightMax = 2 * W + 2 < 30 ? 2 * W + 2 : 30; /* blocks applied and awaiting their verdict: two per check thread (one
+                                                          being checked, one waiting), and the table keeps undo records of at most 32 */
         jobs.resize(inflightMax + (size_t)nScan + 2);
         return true;
     }
@@ -91,6 +92,7 @@ public:
             j.small.need(64);
             j.packed.need(up((max_tx + 1) * 4) + 2 * up(max_in * 4 + 4) + 3 * up(max_out * 4 + 4));
         }
+        bcp_gpu_utxo_reserve(utxo, max_block_bytes); /* the table's pending-block areas on the device, likewise */
     }
     void AddCoin(const uint8_t txid[32], uint32_t vout, const uint8_t *spk, size_t len, int64_t amount) {
         seedOp.insert(seedOp.end(), txid, txid + 32);
