@@ -514,6 +514,7 @@ def chain_bench(args, devices, impl="device"):
     assert fn("connect_file")(h, data, len(data), magic, reason, 256, C.byref(failed)) == 1, reason.value
     for p_, _ in bufs:
         G.bcp_gpu_host_free(p_)
+    gpus_in_use = L.bcp_dchain_gpus_in_use(h) if impl == "device" else len(devices)
     fn("free")(h)
     out = {"impl": "bcp::DeviceChain (coin table in HBM)" if impl == "device" else "bcp::ChainValidator (coin map on host threads)",
            "blocks": nblk, "inputs_per_block": ntx, "block_bytes": len(blocks[0]), "gpus": len(devices),
@@ -525,6 +526,9 @@ def chain_bench(args, devices, impl="device"):
            "ms_per_block_by_phase": phases, "gen_seconds": gen_s, "warmup_blocks": warm,
            "rejected_block_check": "block %d of the chain with a broken signature at input %d, checked by GPU %d: refused with that "
                                    "input, table rolled back, the undamaged block connected afterwards" % (warm + nblk + G_ - 1, bad_input, G_ - 1),
+           "gpus_in_use": gpus_in_use,
+           "peer_access_to_table_gpu": [int(G.bcp_gpu_peer_access(devices[0] & 0xFF, d & 0xFF)) for d in devices],
+           "gpus_in_use_note": "GPUs without direct peer access to the coin table's GPU are left out (a staged copy per block costs more than they bring)",
            "timed": "ConnectFile over %d blocks in blk*.dat framing in one pinned buffer, wall clock of the caller" % nblk}
     if impl == "device":
         # every block crosses the host's memory twice on this path (framing scan, upload): the box's read bandwidth is a ceiling

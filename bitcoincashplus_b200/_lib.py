@@ -25,6 +25,7 @@ sz = C.c_size_t
 # name -> (restype, argtypes): exactly the declarations of include/bcp_gpu.h
 SIGNATURES = {
     "bcp_gpu_device_count": (C.c_int, []),
+    "bcp_gpu_peer_access": (C.c_int, [C.c_int, C.c_int]),
     "bcp_gpu_init": (C.c_int, [C.c_int]),
     "bcp_gpu_shutdown": (C.c_int, [C.c_int]),
     "bcp_gpu_last_error": (C.c_char_p, []),

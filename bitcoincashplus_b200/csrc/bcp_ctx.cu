@@ -66,6 +66,19 @@ int bcp_gpu_device_count(void) {
     return n;
 }
 
+// 1 when GPU a and GPU b can read and write each other's memory directly (NVLink / NVSwitch or PCIe peer-to-peer), 0 when
+// a copy between them would be staged through host memory, negative on error.  a == b is 1.
+int bcp_gpu_peer_access(int a, int b) {
+    a &= 0xFF; b &= 0xFF;
+    if (a == b) return 1;
+    int ab = 0, ba = 0;
+    if (cudaDeviceCanAccessPeer(&ab, a, b) != cudaSuccess || cudaDeviceCanAccessPeer(&ba, b, a) != cudaSuccess) {
+        cudaGetLastError();
+        return BCP_ERR_CUDA;
+    }
+    return ab && ba ? 1 : 0;
+}
+
 static int init_locked(int device, int lane);
 
 int bcp_gpu_init(int id) {

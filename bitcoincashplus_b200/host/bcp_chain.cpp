@@ -103,6 +103,8 @@ CHAIN_API void *bcp_dchain_new(const int *devices, int ndev, uint32_t script_fla
 }
 CHAIN_API void bcp_dchain_reserve(void *h, size_t max_block_bytes) { static_cast<bcp::DeviceChain *>(h)->Reserve(max_block_bytes); }
 CHAIN_API void bcp_dchain_free(void *h) { delete static_cast<bcp::DeviceChain *>(h); }
+// GPUs the connector deals blocks to: the constructor's list minus those without direct peer access to the table's GPU
+CHAIN_API int bcp_dchain_gpus_in_use(void *h) { return (int)static_cast<bcp::DeviceChain *>(h)->GpusInUse(); }
 CHAIN_API void bcp_dchain_add_coin(void *h, const uint8_t *txid32, uint32_t vout, const uint8_t *spk, size_t len, int64_t amount) {
     static_cast<bcp::DeviceChain *>(h)->AddCoin(txid32, vout, spk, len, amount);
 }

@@ -45,6 +45,10 @@ extern "C" {
 /* ---- life cycle ------------------------------------------------------------------------------- */
 /* Number of usable CUDA devices (0 when there is no driver/GPU). */
 BCP_API int bcp_gpu_device_count(void);
+/* 1 when two GPUs can access each other's memory directly (NVLink / NVSwitch, PCIe peer-to-peer), 0 when a copy between them
+ * would be staged through host memory, negative on error.  bcp::DeviceChain deals blocks only to GPUs that reach the coin
+ * table's GPU this way.  No reference counterpart. */
+BCP_API int bcp_gpu_peer_access(int device_a, int device_b);
 /* Create the per-device context: stream, fixed-base comb table for G (generated on the device; the
  * counterpart of secp256k1_ecmult_context_build, src/secp256k1/src/ecmult_impl.h:164-194, which
  * secp256k1_context_create(SECP256K1_CONTEXT_VERIFY) runs, src/secp256k1/src/secp256k1.c:59-83).

@@ -31,6 +31,7 @@
 #include <cstring>
 #include <memory>
 #include <mutex>
+#include <cstdlib>
 #include <string>
 #include <thread>
 #include <vector>
@@ -57,6 +58,21 @@ public:
 
     bool Init(std::string &err) {
         if (devs.empty()) { err = "no device"; return false; }
+        // A block's input area reaches its checking GPU by ONE device-to-device copy from the table's GPU.  Without direct peer
+        // access that copy is staged through host memory by the runtime (measured on a 2-GPU box without it: 8.7 ms per block
+        // instead of 2, and every other runtime call of the process stalls behind it: 340 blocks/s instead of 1,200).  Such a GPU
+        // is left out; BCP_CHAIN_NO_PEER=1 treats every other GPU that way (test hook).
+        {
+            const char *np = getenv("BCP_CHAIN_NO_PEER");
+            std::vector<int> usable(1, devs[0]);
+            for (size_t g = 1; g < devs.size(); g++) {
+                const bool same = (devs[g] & 0xFF) == (devs[0] & 0xFF);
+                if (same || (!(np && atoi(np)) && bcp_gpu_peer_access(devs[0], devs[g]) == 1)) usable.push_back(devs[g]);
+                else skipped.push_back(devs[g] & 0xFF);
+            }
+            devs.swap(usable);
+            // alone on its GPU the table shares it with all the check threads there are: give it the full count
+        }
         for (int d : devs)
             for (int l = 0; l < lanes_; l++)
                 if (bcp_gpu_init(BCP_DEVICE_LANE(d & 0xFF, l)) != BCP_OK) { err = bcp_gpu_last_error(); return false; }
@@ -119,6 +135,8 @@ public:
     // (how long a block occupies one of the in-flight slots)
     // [9] of [1]: waiting with the in-flight window full (for a verdict), [10] of [1]: waiting for the next block's scan
     double phase[11] = {0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0};
+    std::vector<int> skipped; //!< GPUs of the constructor's list that were left out (no direct peer access to the table's GPU)
+    size_t GpusInUse() const { return devs.size(); }
 
     bool ConnectBlock(const uint8_t *blk, size_t len, std::string &reason) {
         std::vector<std::pair<const uint8_t *, size_t>> one{{blk, len}};

@@ -175,6 +175,31 @@ def test_chain_shards_inputs_over_two_devices_when_present(impl):
     L.bcp_chain_free(h)
 
 
+def test_device_chain_leaves_out_a_gpu_without_peer_access(monkeypatch):
+    """bcp::DeviceChain deals blocks only to GPUs that reach the coin table's GPU by a direct device-to-device copy (a
+    staged one per block costs more than the GPU brings: measured 340 instead of 1,200 blocks/s on a 2-GPU box without
+    peer access).  BCP_CHAIN_NO_PEER=1 treats every other GPU as such a one: the chain must then run on the table's GPU
+    alone, with the same verdicts."""
+    import bitcoincashplus_b200 as bcp
+
+    if bcp.device_count() < 2:
+        pytest.skip("needs 2 GPUs (run with gpurun --gpus 2)")
+    import ctypes
+
+    raw = ctypes.CDLL(os.path.join(os.path.dirname(bcp.__file__), "libbcp_chain.so"))
+    L = chain_lib(impl="device")
+    blocks, seeds, _ = synth.synthetic_chain(4, 50, corrupt=(2, "bad_sig"))
+    for no_peer, want in (("1", 1), ("0", None)):
+        monkeypatch.setenv("BCP_CHAIN_NO_PEER", no_peer)
+        h = new_chain(L, seeds, devices=(0, 1))
+        in_use = raw.bcp_dchain_gpus_in_use(C.c_void_p(h))
+        assert in_use == (want if want else (2 if bcp._lib.lib().bcp_gpu_peer_access(0, 1) == 1 else 1))
+        reason = C.create_string_buffer(256)
+        res = [L.bcp_chain_connect_block(h, b, len(b), reason, 256) for b in blocks[:3]]
+        assert res == [1, 1, 0] and reason.value.startswith(b"blk-bad-inputs (input 3")
+        L.bcp_chain_free(h)
+
+
 def test_chain_shards_inputs_over_two_lane_pairs_of_one_gpu():
     """The multi-device path on a one-GPU box: lanes 0-1 and lanes 2-3 of GPU 0 stand in for two devices, each block's
     inputs are split in two index ranges, and a bad signature in the SECOND range (owned by the second "device") must be
