@@ -2,11 +2,14 @@
 // points (include/bcp_gpu.h).  The arithmetic lives in fe.cuh / scalar.cuh / ge.cuh / ecdsa.cuh.
 //
 // Launch shape
-//   k_ecdsa_prep   one thread per K signatures (K = 8, 16 or 32 by batch size) (thread t takes signatures t, t+T, t+2T, ...
-//                  so that the byte loads of a warp stay adjacent), 128 threads per block
-//   k_ecdsa_point  one thread per signature, 128 threads per block, four blocks per SM; the per-thread
+//   k_ecdsa_prep   one thread per K signatures (K = 8, 4 for small batches; thread t takes signatures t, t+T, t+2T, ...
+//                  so that the byte loads of a warp stay adjacent), 128 threads per block; one scalar inversion per
+//                  thread by division steps (scalar.cuh)
+//   k_ecdsa_point  one thread per signature, 256 threads per block, two blocks per SM (128 registers); the per-thread
 //                  {1..8}Q tables (768 B: x, y, beta*x per entry) live in global scratch next to the phase-1 records (the first
-//                  version kept them in shared memory, which capped occupancy at 12 warps per SM)
+//                  version kept them in shared memory, which capped occupancy at 12 warps per SM).  The walk uses the
+//                  branch-free "quick" field forms (fe.cuh); a signature whose walk left a fold unfinished is walked again
+//                  over the exact forms
 // A batch is processed in slices of BCP_SLICE signatures (16 full waves) so that scratch is bounded (718 MB).
 //   k_gcomb_build  one thread per comb-table entry, once per device at bcp_gpu_init
 #include "bcp_ctx.cuh"

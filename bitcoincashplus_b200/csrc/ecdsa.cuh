@@ -11,13 +11,13 @@
 // How the multiplication is evaluated is NOT the reference's (wNAF Strauss with a 1 MiB G table,
 // ecmult_impl.h:286-404): a warp must stay convergent, so
 //   phase 1 (prep, one thread per K signatures): range checks, ONE scalar inversion per K signatures
-//           (Montgomery's trick), u1 = m/s, u2 = r/s, lattice split u2 = k1 + k2*lambda, signed 4-bit
-//           window recoding.  Output: a 80-byte record per signature in scratch memory.
-//   phase 2 (point, one thread per signature; one rolled loop, see ecdsa_point_phase): decompress Q, build {1..8}Q on a common Z without any
+//           (Montgomery's trick; the inversion itself by division steps, scalar.cuh), u1 = m/s, u2 = r/s, lattice
+//           split u2 = k1 + k2*lambda, signed 4-bit window recoding.  Output: a 80-byte record per signature in scratch memory.
+//   phase 2 (point, one thread per signature; one rolled loop, see ecdsa_point_phase_v2): decompress Q, build {1..8}Q on a common Z without any
 //           inversion (z-ratio rescaling, the idea of ge_globalz_set_table_gej group_impl.h:173-194),
 //           34 windows of 4 doublings + 2 mixed additions (Q and lambda*Q share the table: lambda*(x,y) =
-//           (beta*x, y)), then u1*G from a fixed-position comb table (16 windows of 16 bits, no doublings),
-//           then the projective x comparison.
+//           (beta*x, y)), then u1*G from a fixed-position comb table (BCP_GCOMB_WINDOWS windows of BCP_GCOMB_BITS
+//           bits, no doublings), then the projective x comparison.
 #pragma once
 #include "ge.cuh"
 #include "scalar.cuh"
