@@ -81,7 +81,7 @@ __global__ void __launch_bounds__(128) k_ecdsa_prep(const uint8_t *__restrict__ 
     if (t >= n) return;
     // Montgomery's trick over this thread's signatures: pre[j] = s_0 * ... * s_{j-1}.  Only the prefix products
     // are kept (local memory); the second pass re-parses each signature, which is far cheaper than holding
-    // K x (r, s, m) per thread.  K = 32: one 334-multiplication inversion per 32 signatures.
+    // K x (r, s, m) per thread.  One inversion (division steps, scalar.cuh) per K signatures.
     scalar pre[K];
     scalar acc;
 #pragma unroll
